@@ -1,0 +1,304 @@
+/*
+ * aten_b200 -- C ABI of the B200-native path-tracing hot path.
+ *
+ * This is the drop-in boundary for the reference's GPU renderer object
+ * (idaten::PathTracing : PathTracingImplBase : Renderer, reference
+ * src/libidaten/kernel/pathtracing.h:13-152 and src/libidaten/kernel/renderer.h:17-179).
+ * Every entry point below names the reference interface it replaces.  All arguments are plain
+ * pointers and sizes; no CUDA, torch or C++ types cross the boundary.  The POD structs mirror the
+ * reference's own parameter structs byte for byte (sizes/offsets are static_assert'ed in
+ * aten_b200/csrc and again against the real reference headers in include/idaten_b200_shim.h), so
+ * the arrays returned by aten::context's getters can be passed without conversion.
+ *
+ * Threading: one handle owns one CUDA device + one stream; a handle is not re-entrant (the
+ * reference renderer is single threaded on stream 0, renderer.h:161).  Different handles may be
+ * used from different threads.
+ *
+ * Errors: every function returns ATN_OK (0) or a negative AtnStatus; atn_last_error() returns the
+ * message of the calling thread's last failure.  Unlike the reference (cudautil.h:9-54, which
+ * prints, cudaDeviceReset()s and exit()s) the library never terminates the process.  There is no
+ * CPU fallback: without a CUDA device every call fails with ATN_ERR_CUDA.
+ */
+#ifndef ATEN_B200_H_
+#define ATEN_B200_H_
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define ATN_API __declspec(dllexport)
+#else
+#define ATN_API __attribute__((visibility("default")))
+#endif
+
+typedef enum AtnStatus {
+    ATN_OK = 0,
+    ATN_ERR_INVALID_ARGUMENT = -1,
+    ATN_ERR_CUDA = -2,
+    ATN_ERR_NO_SCENE = -3,
+    ATN_ERR_UNSUPPORTED = -4,
+    ATN_ERR_TOO_LARGE = -5,
+} AtnStatus;
+
+/* ---- POD mirrors of the reference's parameter structs ---------------- */
+
+typedef struct AtnVec3 { float x, y, z; } AtnVec3;                 /* aten::vec3, 12 B */
+typedef struct AtnVec4 { float x, y, z, w; } AtnVec4;              /* aten::vec4, 16 B */
+typedef struct AtnMat4 { float m[16]; } AtnMat4;                   /* aten::mat4, row major, 64 B */
+
+/* aten::ray (src/libaten/math/ray.h:7-83), 24 B */
+typedef struct AtnRay { AtnVec3 org; AtnVec3 dir; } AtnRay;
+
+/* aten::Intersection (src/libaten/scene/hit_parameter.h:28-64), 32 B */
+typedef struct AtnHit {
+    float t;          /* AT_MATH_INF (FLT_MAX) on miss */
+    int32_t objid;    /* -1 on miss */
+    int32_t mtrlid;
+    int32_t meshid;
+    int32_t primid;   /* hit.tri.id */
+    float a, b;       /* barycentrics, p = (1-a-b) v0 + a v1 + b v2 */
+    int32_t isVoxel;
+} AtnHit;
+
+/* aten::ThreadedBvhNode == ThreadedSbvhNode == GPUBvhNode
+ * (src/libaten/accelerator/threaded_bvh.h:13-56, sbvh.h:19-66), 48 B; all links/ids are floats. */
+typedef struct AtnBvhNode {
+    float boxmin[3]; float hit;
+    float boxmax[3]; float miss;
+    float object_id;  /* sbvh: isleaf */
+    float primid;     /* sbvh: triid */
+    float exid;       /* bit field mainExid:15 lodExid:15 hasLod:1 noExternal:1; sbvh: voxeldepth */
+    float meshid;     /* sbvh: mtrlid */
+} AtnBvhNode;
+
+/* aten::TriangleParameter (src/libaten/geometry/geomparam.h:66-98), 32 B */
+typedef struct AtnTriangleParameter {
+    int32_t idx[3]; float padding;
+    float area; int32_t needNormal; int32_t mtrlid; int32_t mesh_id;
+} AtnTriangleParameter;
+
+/* aten::ObjectParameter (geomparam.h:23-64), 64 B */
+typedef struct AtnObjectParameter {
+    int32_t type;         /* 0 Polygons, 1 Instance, 2 Sphere */
+    float area;
+    int32_t object_id;    /* Instance: index of the real object */
+    int32_t mtx_id;       /* HOST semantics: absolute index of L2W; W2L is mtx_id + 1 */
+    int32_t triangle_id;
+    int32_t triangle_num;
+    int32_t light_id;
+    int32_t pad0;
+    float sphere_center[3]; float sphere_radius;
+    int32_t sphere_mtrl_id; int32_t pad1[3];
+} AtnObjectParameter;
+
+/* aten::StandardMaterialParameter (src/libaten/material/material.h:66-120), 48 B */
+typedef struct AtnStandardMaterialParameter {
+    float ior, roughness, shininess, subsurface, metallic, specular, specularTint, anisotropic,
+          sheen, sheenTint, clearcoat, clearcoatGloss;
+} AtnStandardMaterialParameter;
+
+/* aten::MaterialParameter (material.h:242-325), 248 B */
+typedef struct AtnMaterialParameter {
+    AtnVec4 baseColor;                 /*   0 */
+    int32_t type;                      /*  16  aten::MaterialType */
+    uint32_t attrib;                   /*  20  bit0 emissive, bit1 singular, bit2 translucent, bit3 glossy */
+    uint16_t id;                       /*  24 */
+    uint8_t isIdealRefraction;         /*  26 */
+    uint8_t is_medium;                 /*  27 */
+    int32_t albedoMap;                 /*  28 */
+    int32_t normalMap;                 /*  32 */
+    int32_t roughnessMap;              /*  36 */
+    int32_t stencil_type;              /*  40 */
+    AtnStandardMaterialParameter standard; /* 44 (union with carpaint, 64 B) */
+    uint8_t carpaint_tail[16];         /*  92 */
+    uint8_t medium[32];                /* 108 */
+    uint8_t toon[100];                 /* 140 */
+    uint8_t feature_line[8];           /* 240 */
+} AtnMaterialParameter;
+
+enum {  /* aten::MaterialType (material.h:41-64) */
+    ATN_MTRL_EMISSIVE = 0, ATN_MTRL_DIFFUSE = 1, ATN_MTRL_ORENNAYAR = 2, ATN_MTRL_SPECULAR = 3,
+    ATN_MTRL_REFRACTION = 4, ATN_MTRL_GGX = 5, ATN_MTRL_BECKMAN = 6, ATN_MTRL_VELVET = 7,
+    ATN_MTRL_MICROFACET_REFRACTION = 8, ATN_MTRL_RETROREFLECTIVE = 9, ATN_MTRL_CARPAINT = 10,
+    ATN_MTRL_DISNEY = 11, ATN_MTRL_TOON = 12, ATN_MTRL_STYLIZED = 13
+};
+
+/* aten::LightParameter (src/libaten/light/light_parameter.h:47-86), 80 B */
+typedef struct AtnLightParameter {
+    AtnVec4 pos; AtnVec4 dir;
+    int32_t type;            /* 0 Area, 1 IBL, 2 Direction, 3 Point, 4 Spot */
+    AtnVec3 light_color;
+    float innerAngle, outerAngle;
+    uint32_t attrib;         /* bit0 singular, bit1 infinite, bit2 IBL */
+    float scale;
+    float intensity;
+    int32_t arealight_objid;
+    int32_t envmapidx;
+    int32_t padding;
+} AtnLightParameter;
+
+/* aten::CameraParameter (src/libaten/camera/camera.h:15-38), 124 B */
+typedef struct AtnCameraParameter {
+    AtnVec3 origin, lookat; float aspect; AtnVec3 center, u, v, dir, right, up;
+    float dist, vfov; int32_t width, height; float znear, zfar;
+} AtnCameraParameter;
+
+/* The fields of aten::SceneRenderingConfig the path reads (scene_rendering_config.h:7-41). */
+typedef struct AtnSceneConfig {
+    float bvh_hit_min;            /* <= 0: use AT_MATH_EPSILON */
+    AtnVec3 bg_color;             /* BackgroundResource */
+    int32_t envmap_tex_idx;
+    float avgIllum;
+    float multiplyer;
+    int32_t enable_env_map;
+    float scene_bbox_min[3];      /* aten::context::GetSceneBoundingBox() (IBL light distance) */
+    float scene_bbox_max[3];
+} AtnSceneConfig;
+
+/* aten::texture: float4 texels, row major (src/libaten/image/texture.h).  The path point-samples
+ * with the host rule int(u*(w-1)) + repeat wrap (texture.cpp:64-75), as the CPU oracle does. */
+typedef struct AtnTextureDesc {
+    const AtnVec4* texels;
+    int32_t width, height;
+    int32_t filter_mode;   /* aten::TextureFilterMode, recorded; see DESIGN.md (Q12) */
+    int32_t address_mode;  /* aten::TextureAddressMode */
+} AtnTextureDesc;
+
+/* Everything Renderer::UpdateSceneData reads from aten::context
+ * (src/libidaten/kernel/renderer.cpp:12-131). The library copies all of it; the caller keeps
+ * ownership. */
+typedef struct AtnSceneBlob {
+    const AtnObjectParameter* objects;       uint32_t object_count;
+    const AtnMat4* matrices;                 uint32_t matrix_count;
+    const AtnMaterialParameter* materials;   uint32_t material_count;
+    const AtnLightParameter* lights;         uint32_t light_count;
+    const AtnTriangleParameter* triangles;   uint32_t triangle_count;
+    const AtnVec4* positions;                /* (x,y,z,u) per vertex */
+    const AtnVec4* normals;                  /* (nx,ny,nz,v) per vertex */
+    uint32_t vertex_count;
+    const AtnBvhNode* const* node_lists;     /* list 0 = top layer, list k = bottom layer k */
+    const uint32_t* node_list_sizes;
+    uint32_t node_list_count;
+    const AtnTextureDesc* textures;          uint32_t texture_count;
+    AtnSceneConfig config;
+} AtnSceneBlob;
+
+/* Work counters of the last atn_render / atn_trace_* call. */
+typedef struct AtnStats {
+    uint64_t closest_rays;     /* closest-hit traversals launched (primary + bounce rays) */
+    uint64_t shadow_rays;      /* shadow-ray traversals launched */
+    uint64_t camera_samples;   /* W*H*spp of the call */
+    uint64_t kernel_launches;  /* CUDA kernels launched by the call */
+    float    device_ms;        /* CUDA-event time of the call on the handle's stream */
+    float    trace_ms;         /* sum of CUDA-event times of the traversal kernels (if profiling on) */
+} AtnStats;
+
+typedef struct AtnRenderer AtnRenderer;
+
+/* ---- lifetime -------------------------------------------------------------------------------- */
+/* idaten::Renderer::Renderer() (renderer.cpp:5-9) */
+ATN_API int atn_create(int device_ordinal, AtnRenderer** out);
+ATN_API int atn_destroy(AtnRenderer* r);
+ATN_API const char* atn_last_error(void);
+ATN_API const char* atn_version(void);
+
+/* ---- scene upload ----------------------------------------------------------------------------- */
+/* Renderer::UpdateSceneData (renderer.cpp:12-131 / pathtracing.h:117-125): copies the scene,
+ * re-encodes the threaded node lists into the traversal layout and allocates the
+ * W*H path state. */
+ATN_API int atn_upload_scene(AtnRenderer* r, const AtnSceneBlob* scene,
+                             const AtnCameraParameter* camera, int32_t width, int32_t height);
+/* Renderer::updateCamera (renderer.h:85-88) */
+ATN_API int atn_update_camera(AtnRenderer* r, const AtnCameraParameter* camera);
+/* Renderer::updateBVH (renderer.cpp:133-153): new top layer (list 0), objects and matrices. */
+ATN_API int atn_update_top_layer(AtnRenderer* r, const AtnBvhNode* top_nodes, uint32_t node_count,
+                                 const AtnObjectParameter* objects, uint32_t object_count,
+                                 const AtnMat4* matrices, uint32_t matrix_count);
+/* Renderer::updateMaterial (renderer.cpp:190-200) */
+ATN_API int atn_update_materials(AtnRenderer* r, const AtnMaterialParameter* m, uint32_t count);
+/* Renderer::updateLight (renderer.cpp:202-220) */
+ATN_API int atn_update_lights(AtnRenderer* r, const AtnLightParameter* l, uint32_t count);
+/* Renderer::UpdateSceneRenderingConfig (renderer.h:103-106) */
+ATN_API int atn_update_config(AtnRenderer* r, const AtnSceneConfig* cfg);
+/* Renderer::initSamplerParameter (renderer.h:113-124): per-pixel seeds = aten::getRandom(). */
+ATN_API int atn_set_seeds(AtnRenderer* r, const uint32_t* seeds, uint32_t count);
+
+/* ---- frame control ----------------------------------------------------------------------------- */
+/* Renderer::GetFrameCount / reset (renderer.h:66-83).  Frame k here == host frame k. */
+ATN_API int atn_set_frame(AtnRenderer* r, uint32_t frame);
+ATN_API int atn_get_frame(AtnRenderer* r, uint32_t* frame);
+/* Renderer::reset + clearing the accumulation image. */
+ATN_API int atn_reset(AtnRenderer* r);
+/* PathTracing::SetEnableProgressive (pathtracing.h:127-135): 1 = running mean in the image exactly
+ * as FilmProgressive::put (src/libaten/renderer/film.cpp:61-71), 0 = sum of samples + count in .w
+ * (the form the multi-GPU reduce combines). */
+ATN_API int atn_set_progressive(AtnRenderer* r, int enable);
+/* Renderer::setHitDistanceLimit (renderer.h:108-111) */
+ATN_API int atn_set_hit_distance_limit(AtnRenderer* r, float d);
+
+/* ---- render ------------------------------------------------------------------------------------ */
+/* PathTracingImplBase::render(width,height,maxSamples,maxBounce) (pathtracing.cpp:49-89) followed
+ * by PathTracing::OnRender (pathtracing.cpp:91-153).  Renders `spp` samples per pixel, sample i of
+ * the call using host frame index (frame + i); advances the frame counter by spp.  Asynchronous on
+ * the handle's stream. */
+ATN_API int atn_render(AtnRenderer* r, int32_t width, int32_t height,
+                       int32_t spp, int32_t max_bounce, int32_t rr_bounce);
+/* Same, restricted to the pixel rectangle [x0,x1) x [y0,y1) and to samples
+ * [sample_begin, sample_end) of the frame sequence -- the multi-GPU partition.
+ * Does not advance the frame counter. */
+ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height,
+                              int32_t x0, int32_t y0, int32_t x1, int32_t y1,
+                              int32_t sample_begin, int32_t sample_end,
+                              int32_t max_bounce, int32_t rr_bounce);
+/* Blocks until the handle's stream is idle. */
+ATN_API int atn_synchronize(AtnRenderer* r);
+/* Replaces the CUDA-GL surface the reference writes with surf2Dwrite (pathtracing_impl.cu:282-324):
+ * copies the float4 W*H image to host memory. */
+ATN_API int atn_readback(AtnRenderer* r, AtnVec4* host_image, size_t pixel_count);
+/* Device pointer (float4[W*H]) of the image, for NCCL / torch interop; owned by the handle. */
+ATN_API int atn_device_image(AtnRenderer* r, void** device_ptr, size_t* pixel_count);
+ATN_API int atn_get_stats(AtnRenderer* r, AtnStats* out);
+/* 1: time the traversal kernels separately with CUDA events (fills AtnStats.trace_ms). */
+ATN_API int atn_set_profiling(AtnRenderer* r, int enable);
+/* CUDA stream of the handle (Renderer::GetCudaStream, renderer.h:113-116) as an opaque pointer. */
+ATN_API int atn_get_stream(AtnRenderer* r, void** stream);
+
+/* ---- ray queries (config C5; the traversal the renderer uses, exposed on its own) ------------- */
+/* ThreadedBvhTraverser<true>::Traverse<Closest>(isect, ctxt, ray, t_min=1e-9, t_max)
+ * (src/libaten/accelerator/threaded_bvh_traverser.h:98-304) for n host rays. */
+ATN_API int atn_trace_closest(AtnRenderer* r, const AtnRay* rays, const float* t_max /* may be NULL */,
+                              size_t n, AtnHit* hits);
+/* Shadow-ray query with the reference semantics of HitTestToTargetLight + scene::hitLight
+ * (pathtracing_impl.h:266-351, scene.h:120-133) for a singular light at distance dist[i]:
+ * visible[i] = 1 iff nothing is hit closer than dist[i]. */
+ATN_API int atn_trace_any(AtnRenderer* r, const AtnRay* rays, const float* dist, size_t n,
+                          uint8_t* visible);
+/* Device-resident variants (pointers are CUDA device pointers; asynchronous on the stream). */
+ATN_API int atn_trace_closest_device(AtnRenderer* r, const void* rays_dev, const void* t_max_dev,
+                                     size_t n, void* hits_dev);
+ATN_API int atn_trace_any_device(AtnRenderer* r, const void* rays_dev, const void* dist_dev,
+                                 size_t n, void* visible_dev);
+
+/* ---- debug / parity taps ------------------------------------------------------------------------ */
+/* Per-bounce dump of the wavefront state for parity tests: after atn_render with a tap installed,
+ * `records` holds one AtnBounceRecord per (pixel, bounce) for the LAST sample rendered.
+ * Host memory; bounce_capacity records per pixel. Pass NULL to remove. */
+typedef struct AtnBounceRecord {
+    AtnRay ray;            /* ray traced at this bounce */
+    AtnHit hit;            /* closest hit found */
+    float shadow_org[3]; float shadow_dist;
+    float shadow_dir[3]; int32_t shadow_active;   /* 1 if a shadow ray was cast */
+    float light_contrib[3]; int32_t shadow_visible;
+    float throughput[3]; float pdfb;              /* after the bounce */
+    float contrib[3]; int32_t flags;              /* bit0 valid, bit1 terminated after bounce */
+} AtnBounceRecord;
+ATN_API int atn_set_bounce_tap(AtnRenderer* r, AtnBounceRecord* records, int32_t bounce_capacity);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ATEN_B200_H_ */

@@ -1,0 +1,300 @@
+// idaten_b200_shim.h -- host-side C++ mirror of the reference's GPU renderer class over the C ABI.
+//
+// A maintainer of the reference swaps `idaten::PathTracing renderer_;` (src/device_renderer/main.cpp)
+// for `idaten_b200::PathTracing renderer_;` and links libaten_b200.so: same method names, argument
+// meaning and call order as src/libidaten/kernel/pathtracing.h:107-152 and
+// src/libidaten/kernel/renderer.h:17-179.  This header is compiled against the reference's OWN
+// headers ("aten.h"); it contains no CUDA and no copy of reference code -- it only reads the scene
+// through the same aten::context getters Renderer::UpdateSceneData uses
+// (src/libidaten/kernel/renderer.cpp:12-131) and hands the flat arrays to the C ABI.
+//
+// Differences from the reference, all deliberate:
+//  * gltex is ignored (no graphics stack on the target): the image lives in a device float4 buffer,
+//    read with ReadbackImage() or shared through DeviceImage().
+//  * Q3: the reference's GPU upload rewrites ObjectParameter::mtx_id and mutates the host scene
+//    (host_scene_context.cpp:285-307).  The shim emits the HOST indices (L2W at mtx_id, W2L at
+//    mtx_id + 1) and does not touch the context.
+//  * Q7: the frame counter starts at 0 like the host renderer (src/libaten/renderer/renderer.h:71).
+//  * errors throw std::runtime_error instead of exit() (cudautil.h:9-54).
+#pragma once
+
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <functional>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "aten.h"
+#include "aten_b200.h"
+
+namespace idaten_b200 {
+
+// The structs must be layout-identical to the reference's, otherwise the zero-copy hand-over below
+// would be wrong.  Checked here against the real headers.
+static_assert(sizeof(AtnVec3) == sizeof(aten::vec3), "vec3");
+static_assert(sizeof(AtnVec4) == sizeof(aten::vec4), "vec4");
+static_assert(sizeof(AtnMat4) == sizeof(aten::mat4), "mat4");
+static_assert(sizeof(AtnRay) == sizeof(aten::ray), "ray");
+static_assert(sizeof(AtnHit) == sizeof(aten::Intersection), "Intersection");
+static_assert(sizeof(AtnBvhNode) == sizeof(aten::GPUBvhNode), "GPUBvhNode");
+static_assert(sizeof(AtnTriangleParameter) == sizeof(aten::TriangleParameter), "TriangleParameter");
+static_assert(sizeof(AtnObjectParameter) == sizeof(aten::ObjectParameter), "ObjectParameter");
+static_assert(sizeof(AtnMaterialParameter) == sizeof(aten::MaterialParameter), "MaterialParameter");
+static_assert(sizeof(AtnLightParameter) == sizeof(aten::LightParameter), "LightParameter");
+static_assert(sizeof(AtnCameraParameter) == sizeof(aten::CameraParameter), "CameraParameter");
+static_assert(offsetof(AtnMaterialParameter, standard) == 44, "MaterialParameter::standard");
+static_assert(offsetof(AtnMaterialParameter, albedoMap) == 28, "MaterialParameter::albedoMap");
+static_assert(offsetof(AtnLightParameter, arealight_objid) == 68, "LightParameter::arealight_objid");
+static_assert(offsetof(AtnObjectParameter, sphere_center) == 32, "ObjectParameter::sphere");
+
+/// Owning flat copy of everything the path reads from aten::context -- the host half of
+/// Renderer::UpdateSceneData (renderer.cpp:12-131).
+struct FlatScene {
+    std::vector<aten::ObjectParameter> objects;
+    std::vector<aten::mat4> matrices;
+    std::vector<aten::MaterialParameter> materials;
+    std::vector<aten::LightParameter> lights;
+    std::vector<aten::TriangleParameter> triangles;
+    std::vector<aten::vec4> positions, normals;
+    std::vector<std::vector<aten::GPUBvhNode>> nodes;
+    std::vector<AtnTextureDesc> textures;
+    std::vector<std::shared_ptr<aten::texture>> texture_refs;
+    AtnSceneConfig config{};
+
+    // scratch for the blob view
+    std::vector<const AtnBvhNode*> node_ptrs;
+    std::vector<uint32_t> node_sizes;
+
+    void Gather(const aten::context& ctxt, const std::vector<std::vector<aten::GPUBvhNode>>& node_lists)
+    {
+        const auto obj_num = ctxt.GetObjectNum();
+        objects.clear();
+        int32_t max_mtx = -1;
+        for (size_t i = 0; i < obj_num; i++) {
+            objects.push_back(ctxt.GetObject(static_cast<uint32_t>(i)));   // host mtx_id, unmodified
+            if (objects.back().type == aten::ObjectType::Instance) {
+                max_mtx = std::max(max_mtx, objects.back().mtx_id);
+            }
+        }
+        matrices.clear();
+        for (int32_t i = 0; i <= max_mtx + 1 && max_mtx >= 0; i++) {
+            matrices.push_back(ctxt.GetMatrix(static_cast<uint32_t>(i)));
+        }
+        materials = ctxt.GetMetarialParemeters();
+        lights = ctxt.GetLightParameters();
+        triangles = ctxt.GetPrimitiveParameters();
+        aten::tie(positions, normals) = ctxt.GetExtractedPosAndNmlInVertices();
+        nodes = node_lists;
+
+        textures.clear();
+        texture_refs.clear();
+        const auto tex_num = ctxt.GetTextureNum();
+        for (int32_t i = 0; i < static_cast<int32_t>(tex_num); i++) {
+            auto t = ctxt.GetTexture(i);
+            texture_refs.push_back(t);
+            AtnTextureDesc d{};
+            d.texels = reinterpret_cast<const AtnVec4*>(t->colors().data());
+            d.width = t->width();
+            d.height = t->height();
+            d.filter_mode = static_cast<int32_t>(t->GetFilterMode());
+            d.address_mode = static_cast<int32_t>(t->GetAddressMode());
+            textures.push_back(d);
+        }
+
+        const auto& cfg = ctxt.scene_rendering_config;
+        config.bvh_hit_min = cfg.bvh_hit_min;
+        config.bg_color = AtnVec3{ cfg.bg.bg_color.x, cfg.bg.bg_color.y, cfg.bg.bg_color.z };
+        config.envmap_tex_idx = cfg.bg.envmap_tex_idx;
+        config.avgIllum = cfg.bg.avgIllum;
+        config.multiplyer = cfg.bg.multiplyer;
+        config.enable_env_map = cfg.bg.enable_env_map ? 1 : 0;
+        const auto& bb = ctxt.GetSceneBoundingBox();
+        const auto bmin = bb.minPos();
+        const auto bmax = bb.maxPos();
+        config.scene_bbox_min[0] = bmin.x; config.scene_bbox_min[1] = bmin.y; config.scene_bbox_min[2] = bmin.z;
+        config.scene_bbox_max[0] = bmax.x; config.scene_bbox_max[1] = bmax.y; config.scene_bbox_max[2] = bmax.z;
+    }
+
+    AtnSceneBlob View()
+    {
+        node_ptrs.clear();
+        node_sizes.clear();
+        for (const auto& l : nodes) {
+            node_ptrs.push_back(reinterpret_cast<const AtnBvhNode*>(l.data()));
+            node_sizes.push_back(static_cast<uint32_t>(l.size()));
+        }
+        AtnSceneBlob b{};
+        b.objects = reinterpret_cast<const AtnObjectParameter*>(objects.data());
+        b.object_count = static_cast<uint32_t>(objects.size());
+        b.matrices = reinterpret_cast<const AtnMat4*>(matrices.data());
+        b.matrix_count = static_cast<uint32_t>(matrices.size());
+        b.materials = reinterpret_cast<const AtnMaterialParameter*>(materials.data());
+        b.material_count = static_cast<uint32_t>(materials.size());
+        b.lights = reinterpret_cast<const AtnLightParameter*>(lights.data());
+        b.light_count = static_cast<uint32_t>(lights.size());
+        b.triangles = reinterpret_cast<const AtnTriangleParameter*>(triangles.data());
+        b.triangle_count = static_cast<uint32_t>(triangles.size());
+        b.positions = reinterpret_cast<const AtnVec4*>(positions.data());
+        b.normals = reinterpret_cast<const AtnVec4*>(normals.data());
+        b.vertex_count = static_cast<uint32_t>(positions.size());
+        b.node_lists = node_ptrs.data();
+        b.node_list_sizes = node_sizes.data();
+        b.node_list_count = static_cast<uint32_t>(nodes.size());
+        b.textures = textures.data();
+        b.texture_count = static_cast<uint32_t>(textures.size());
+        b.config = config;
+        return b;
+    }
+
+    /// Serialise the blob (+ camera, size, seeds) as a `.atnscene` file: the portable form of a
+    /// scene for machines that have no reference checkout (tests/golden, the GPU box).
+    /// Layout: see aten_b200/scene_io.py.
+    bool Save(const std::string& path, const aten::CameraParameter& camera, int32_t width, int32_t height,
+              const std::vector<uint32_t>& seeds)
+    {
+        FILE* fp = fopen(path.c_str(), "wb");
+        if (!fp) return false;
+        auto w = [&](const void* p, size_t n) { if (n) fwrite(p, 1, n, fp); };
+        const char magic[8] = { 'A','T','N','S','C','N','0','1' };
+        w(magic, 8);
+        uint32_t counts[10] = {
+            (uint32_t)objects.size(), (uint32_t)matrices.size(), (uint32_t)materials.size(),
+            (uint32_t)lights.size(), (uint32_t)triangles.size(), (uint32_t)positions.size(),
+            (uint32_t)nodes.size(), (uint32_t)textures.size(), (uint32_t)seeds.size(), 0u };
+        w(counts, sizeof(counts));
+        w(&config, sizeof(config));
+        w(&camera, sizeof(camera));
+        int32_t wh[2] = { width, height };
+        w(wh, sizeof(wh));
+        w(objects.data(), objects.size() * sizeof(aten::ObjectParameter));
+        w(matrices.data(), matrices.size() * sizeof(aten::mat4));
+        w(materials.data(), materials.size() * sizeof(aten::MaterialParameter));
+        w(lights.data(), lights.size() * sizeof(aten::LightParameter));
+        w(triangles.data(), triangles.size() * sizeof(aten::TriangleParameter));
+        w(positions.data(), positions.size() * sizeof(aten::vec4));
+        w(normals.data(), normals.size() * sizeof(aten::vec4));
+        for (const auto& l : nodes) { uint32_t n = (uint32_t)l.size(); w(&n, 4); }
+        for (const auto& l : nodes) w(l.data(), l.size() * sizeof(aten::GPUBvhNode));
+        for (const auto& t : textures) {
+            int32_t hdr[4] = { t.width, t.height, t.filter_mode, t.address_mode };
+            w(hdr, sizeof(hdr));
+            w(t.texels, sizeof(AtnVec4) * (size_t)t.width * (size_t)t.height);
+        }
+        w(seeds.data(), seeds.size() * 4);
+        fclose(fp);
+        return true;
+    }
+};
+
+/// Same public surface as idaten::PathTracing (pathtracing.h:107-152) + the idaten::Renderer
+/// methods the apps call (renderer.h:61-116).
+class PathTracing {
+public:
+    enum class Mode { PT, AOV };
+
+    PathTracing() = default;
+    explicit PathTracing(int device_ordinal) : device_(device_ordinal) {}
+    ~PathTracing() { if (h_) atn_destroy(h_); }
+    PathTracing(const PathTracing&) = delete;
+    PathTracing& operator=(const PathTracing&) = delete;
+
+    /// idaten::PathTracing::UpdateSceneData (pathtracing.h:117-125).  `gltex` is ignored.
+    void UpdateSceneData(
+        uint32_t /*gltex*/,
+        int32_t width, int32_t height,
+        const aten::CameraParameter& camera,
+        const aten::context& scene_ctxt,
+        const std::vector<std::vector<aten::GPUBvhNode>>& nodes,
+        uint32_t /*advance_prim_num*/ = 0,
+        uint32_t /*advance_vtx_num*/ = 0,
+        std::function<const aten::Grid*(const aten::context&)> /*proxy*/ = nullptr)
+    {
+        Ensure();
+        flat_.Gather(scene_ctxt, nodes);
+        auto blob = flat_.View();
+        Check(atn_upload_scene(h_, &blob, reinterpret_cast<const AtnCameraParameter*>(&camera), width, height));
+        // Renderer::initSamplerParameter (renderer.h:113-124)
+        const auto& rnd = aten::getRandom();
+        Check(atn_set_seeds(h_, rnd.data(), static_cast<uint32_t>(rnd.size())));
+    }
+
+    /// PathTracingImplBase::render (pathtracing.cpp:49-89)
+    void render(int32_t width, int32_t height, int32_t maxSamples, int32_t maxBounce)
+    {
+        Check(atn_render(h_, width, height, maxSamples, maxBounce, /*rrBounce (pathtracing.cpp:97)*/ 3));
+    }
+
+    void updateCamera(const aten::CameraParameter& camera)
+    {
+        Check(atn_update_camera(h_, reinterpret_cast<const AtnCameraParameter*>(&camera)));
+    }
+
+    /// Renderer::updateBVH (renderer.cpp:133-153)
+    void updateBVH(const aten::context& scene_ctxt, const std::vector<std::vector<aten::GPUBvhNode>>& nodes)
+    {
+        flat_.Gather(scene_ctxt, nodes);
+        Check(atn_update_top_layer(
+            h_, reinterpret_cast<const AtnBvhNode*>(flat_.nodes[0].data()), (uint32_t)flat_.nodes[0].size(),
+            reinterpret_cast<const AtnObjectParameter*>(flat_.objects.data()), (uint32_t)flat_.objects.size(),
+            reinterpret_cast<const AtnMat4*>(flat_.matrices.data()), (uint32_t)flat_.matrices.size()));
+    }
+
+    void updateMaterial(const std::vector<aten::MaterialParameter>& mtrls)
+    {
+        Check(atn_update_materials(h_, reinterpret_cast<const AtnMaterialParameter*>(mtrls.data()), (uint32_t)mtrls.size()));
+    }
+
+    void updateLight(const aten::context& scene_ctxt, bool /*is_npr_target_light*/ = false)
+    {
+        const auto lights = scene_ctxt.GetLightParameters();
+        Check(atn_update_lights(h_, reinterpret_cast<const AtnLightParameter*>(lights.data()), (uint32_t)lights.size()));
+    }
+
+    void UpdateSceneRenderingConfig(const aten::context& ctxt)
+    {
+        FlatScene tmp;
+        tmp.config = flat_.config;
+        const auto& cfg = ctxt.scene_rendering_config;
+        tmp.config.bvh_hit_min = cfg.bvh_hit_min;
+        tmp.config.bg_color = AtnVec3{ cfg.bg.bg_color.x, cfg.bg.bg_color.y, cfg.bg.bg_color.z };
+        tmp.config.envmap_tex_idx = cfg.bg.envmap_tex_idx;
+        tmp.config.avgIllum = cfg.bg.avgIllum;
+        tmp.config.multiplyer = cfg.bg.multiplyer;
+        tmp.config.enable_env_map = cfg.bg.enable_env_map ? 1 : 0;
+        flat_.config = tmp.config;
+        Check(atn_update_config(h_, &flat_.config));
+    }
+
+    void reset() { Check(atn_reset(h_)); }
+    uint32_t GetFrameCount() const { uint32_t f = 0; atn_get_frame(h_, &f); return f; }
+    void SetEnableProgressive(bool b) { progressive_ = b; Check(atn_set_progressive(h_, b ? 1 : 0)); }
+    bool IsEnableProgressive() const { return progressive_; }
+    void setHitDistanceLimit(float d) { Check(atn_set_hit_distance_limit(h_, d)); }
+    void SetRenderingMode(Mode m) { mode_ = m; }
+    Mode GetRenderingMode() const { return mode_; }
+    void* GetCudaStream() const { void* s = nullptr; atn_get_stream(h_, &s); return s; }
+
+    /// Replacement for the GL surface: copy the RGBA32F image to the host.
+    void ReadbackImage(aten::vec4* dst, size_t pixel_count)
+    {
+        Check(atn_readback(h_, reinterpret_cast<AtnVec4*>(dst), pixel_count));
+    }
+    void* DeviceImage() { void* p = nullptr; size_t n = 0; Check(atn_device_image(h_, &p, &n)); return p; }
+
+    AtnRenderer* handle() { Ensure(); return h_; }
+    FlatScene& flat() { return flat_; }
+
+private:
+    void Ensure() { if (!h_) Check(atn_create(device_, &h_)); }
+    static void Check(int rc) { if (rc != ATN_OK) throw std::runtime_error(atn_last_error()); }
+
+    AtnRenderer* h_{ nullptr };
+    int device_{ 0 };
+    bool progressive_{ false };
+    Mode mode_{ Mode::PT };
+    FlatScene flat_;
+};
+
+}  // namespace idaten_b200

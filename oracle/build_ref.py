@@ -140,7 +140,9 @@ def main():
         print(out[-4000:], file=sys.stderr)
         return 1
     # assets (not source) needed at run time on a box without /root/reference
-    for rel in ASSETS:
+    sponza_maps = [os.path.join("sponza", f) for f in sorted(os.listdir(os.path.join(ref, "asset", "sponza")))
+                   if f.lower().endswith((".jpg", ".png"))]
+    for rel in ASSETS + sponza_maps:
         s = os.path.join(ref, "asset", rel)
         d = os.path.join(OUT, "asset", rel)
         if os.path.exists(s):

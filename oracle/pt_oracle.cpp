@@ -1,0 +1,294 @@
+// oracle/pt_oracle.cpp -- TEST INFRASTRUCTURE.  CPU restatement of the reference's path-tracing
+// hot path over the flat scene blob (include/aten_b200.h).  Only tests/, __graft_entry__.smoke()
+// and bench.py's cpu_baseline leg may load this library; the product (libaten_b200.so) never
+// links or calls it and has no CPU fallback.
+//
+// What is restated here, and from where:
+//   * closest-hit traversal on the REFERENCE node layout and in the reference's visit order:
+//     ThreadedBvhTraverser<true>::Traverse<Closest>
+//     (src/libaten/accelerator/threaded_bvh_traverser.h:98-304), triangle::hit
+//     (src/libaten/geometry/triangle.h:40-67);
+//   * the per-pixel loop aten::PathTracing::radiance / OnRender
+//     (src/libaten/renderer/pathtracing/pathtracing.cpp:23-89, 269-366) and FilmProgressive::put
+//     (src/libaten/renderer/film.cpp:61-71);
+//   * the shading / sampling math lives in aten_b200/csrc/atn_math.cuh (one text, compiled here
+//     with g++ and by nvcc for the kernels); each function there cites its reference lines.
+//
+// Parity is PINNED: tests/test_oracle_cpu.py checks this restatement bit-exactly (hits, rays) and
+// to 1e-6 (radiance) against vectors produced by the reference's own CPU renderer compiled in
+// place (oracle/_ref, see oracle/build_ref.py and tests/golden/make_golden.py).
+#include <omp.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+
+#include "../aten_b200/csrc/atn_math.cuh"
+
+using namespace atn;
+
+namespace {
+
+struct Scene {
+    SceneView view;
+    std::vector<const AtnBvhNode*> lists;
+    std::vector<TexView> tex;
+    float t_min;
+};
+
+Scene MakeScene(const AtnSceneBlob* b)
+{
+    Scene s;
+    s.view.objects = b->objects; s.view.matrices = b->matrices; s.view.materials = b->materials;
+    s.view.lights = b->lights; s.view.triangles = b->triangles; s.view.positions = b->positions;
+    s.view.normals = b->normals; s.view.light_count = (int32_t)b->light_count; s.view.cfg = b->config;
+    for (uint32_t i = 0; i < b->texture_count; i++) {
+        TexView t; t.texels = b->textures[i].texels; t.w = b->textures[i].width; t.h = b->textures[i].height;
+        s.tex.push_back(t);
+    }
+    s.view.textures = s.tex.data();
+    for (uint32_t i = 0; i < b->node_list_count; i++) s.lists.push_back(b->node_lists[i]);
+    // ImageBasedLight::sample's scene radius (src/libaten/light/ibl.h:105-110, aabb.h:231-234,345-362)
+    const float* mn = b->config.scene_bbox_min; const float* mx = b->config.scene_bbox_max;
+    const bool valid = !((mn[0] >= mx[0]) || (mn[1] >= mx[1]) || (mn[2] >= mx[2]));
+    float radius = 10000.0f;
+    if (valid) {
+        const V3 vmin(mn[0], mn[1], mn[2]), vmax(mx[0], mx[1], mx[2]);
+        const V3 center = (vmin + vmax) * 0.5f;
+        const float r = length(vmax - center);
+        const float theta = kPi * 30.0f / 180.0f;
+        radius = r / tanf(theta / 2);
+    }
+    s.view.scene_radius = radius;
+    s.t_min = b->config.bvh_hit_min > 0 ? b->config.bvh_hit_min : kEps;
+    return s;
+}
+
+struct Counters { uint64_t nodes, boxes, tris, insts; };
+
+// ThreadedBvhTraverser<true>::Traverse<Closest> (threaded_bvh_traverser.h:98-304); lod_depth = -1.
+bool Traverse(const Scene& s, const Ray& r, float t_max, AtnHit* isect, Counters* cnt)
+{
+    const float t_min = s.t_min;
+    isect->t = kInf; isect->objid = -1; isect->mtrlid = -1; isect->meshid = -1;
+    isect->primid = -1; isect->a = 0; isect->b = 0; isect->isVoxel = 0;
+    const AtnBvhNode* list = s.lists[0];
+    Ray tr = r;
+    RayInv ri = ray_inv(tr.org, tr.dir);
+    int32_t nodeid = 0, objid = -1, meshid = -1, top_hit = -1, top_miss = -1;
+    while (nodeid >= 0) {
+        bool is_hit = false;
+        AtnBvhNode node = list[nodeid];
+        if (cnt) cnt->nodes++;
+        if (node.object_id >= 0 || node.primid >= 0) {
+            if (node.exid >= 0) {
+                const AtnObjectParameter& obj = s.view.objects[(uint32_t)node.object_id];
+                if (obj.mtx_id >= 0) {
+                    const AtnMat4& W2L = s.view.matrices[obj.mtx_id + 1];
+                    tr = make_ray(mat_apply(W2L, r.org), mat_apply_xyz(W2L, r.dir));   // mat4::applyRay
+                }
+                else tr = r;
+                ri = ray_inv(tr.org, tr.dir);
+                const uint32_t bits = (uint32_t)f2i(node.exid);
+                const int32_t exid = (int32_t)(bits & 0x7fffu);
+                list = s.lists[exid];
+                objid = (int32_t)node.object_id;
+                meshid = (int32_t)node.meshid;
+                top_hit = (int32_t)node.hit;
+                top_miss = (int32_t)node.miss;
+                is_hit = true;
+                node.hit = 0;
+                if (cnt) cnt->insts++;
+            }
+            else if (node.primid >= 0) {
+                const AtnTriangleParameter& prim = s.view.triangles[(uint32_t)node.primid];
+                const V3 v0(s.view.positions[prim.idx[0]]), v1(s.view.positions[prim.idx[1]]), v2(s.view.positions[prim.idx[2]]);
+                const TriHit h = intersect_triangle(tr.org, tr.dir, v0, v1, v2);
+                if (cnt) cnt->tris++;
+                is_hit = h.hit && h.t < kInf;          // triangle::hit against isect_tmp.t = INF
+                const float tt = is_hit ? h.t : kInf;
+                const bool is_intersect = t_min < tt && (is_hit && tt < isect->t);
+                if (is_intersect) {
+                    isect->t = h.t; isect->a = h.a; isect->b = h.b;
+                    isect->objid = objid;
+                    isect->primid = (int32_t)node.primid;
+                    isect->mtrlid = prim.mtrlid;
+                    isect->meshid = prim.mesh_id < 0 ? meshid : prim.mesh_id;
+                    isect->isVoxel = 0;
+                    t_max = isect->t;
+                }
+            }
+        }
+        else {
+            float t0;
+            is_hit = aabb_hit(ri, V3(node.boxmin[0], node.boxmin[1], node.boxmin[2]),
+                              V3(node.boxmax[0], node.boxmax[1], node.boxmax[2]), t_min, t_max, &t0);
+            if (cnt) cnt->boxes++;
+        }
+        nodeid = is_hit ? (int32_t)node.hit : (int32_t)node.miss;
+        if (nodeid < 0) {
+            nodeid = is_hit ? top_hit : top_miss;
+            top_hit = -1; top_miss = -1;
+            list = s.lists[0];
+            tr = r;
+            ri = ray_inv(tr.org, tr.dir);
+        }
+    }
+    return isect->objid >= 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+__attribute__((visibility("default")))
+int oracle_trace_closest(const AtnSceneBlob* blob, const AtnRay* rays, const float* t_max, size_t n, AtnHit* hits,
+                         uint64_t* counters /* [4] nodes, boxes, tris, insts; may be NULL */)
+{
+    const Scene s = MakeScene(blob);
+    uint64_t cn = 0, cb = 0, ct = 0, ci = 0;
+#pragma omp parallel for reduction(+:cn,cb,ct,ci) schedule(dynamic, 256)
+    for (long i = 0; i < (long)n; i++) {
+        Ray r; r.org = V3(rays[i].org); r.dir = V3(rays[i].dir);
+        Counters c{0, 0, 0, 0};
+        Traverse(s, r, t_max ? t_max[i] : kInf, &hits[i], counters ? &c : nullptr);
+        cn += c.nodes; cb += c.boxes; ct += c.tris; ci += c.insts;
+    }
+    if (counters) { counters[0] = cn; counters[1] = cb; counters[2] = ct; counters[3] = ci; }
+    return 0;
+}
+
+// Shadow query with the semantics of atn_trace_any (singular light at distance dist[i]).
+__attribute__((visibility("default")))
+int oracle_trace_any(const AtnSceneBlob* blob, const AtnRay* rays, const float* dist, size_t n, uint8_t* visible)
+{
+    const Scene s = MakeScene(blob);
+#pragma omp parallel for schedule(dynamic, 256)
+    for (long i = 0; i < (long)n; i++) {
+        Ray r; r.org = V3(rays[i].org); r.dir = V3(rays[i].dir);
+        AtnHit h;
+        const bool hit = Traverse(s, r, dist[i] - kEps, &h, nullptr);
+        visible[i] = (!hit || h.t > dist[i]) ? 1 : 0;
+    }
+    return 0;
+}
+
+// aten::PathTracing::OnRender driven as `frames` successive frames of one sample, with
+// FilmProgressive accumulation; `records` (optional) receives AtnBounceRecord[pixel][max_depth]
+// of the LAST frame; stats = {closest rays, shadow rays}.
+__attribute__((visibility("default")))
+int oracle_render(const AtnSceneBlob* blob, const AtnCameraParameter* cam, const uint32_t* seeds, uint32_t seed_count,
+                  int32_t W, int32_t H, uint32_t first_frame, int32_t frames, int32_t max_depth, int32_t rr_depth,
+                  AtnVec4* image /* in/out progressive film, W*H */, AtnBounceRecord* records, uint64_t* stats)
+{
+    const Scene s = MakeScene(blob);
+    if (rr_depth > max_depth) rr_depth = max_depth - 1;
+    uint64_t n_closest = 0, n_shadow = 0;
+    for (int32_t f = 0; f < frames; f++) {
+        const uint32_t frame = first_frame + (uint32_t)f;
+        AtnBounceRecord* recs = (f == frames - 1) ? records : nullptr;
+#pragma omp parallel for reduction(+:n_closest,n_shadow) schedule(dynamic, 4)
+        for (int32_t y = 0; y < H; y++) {
+            for (int32_t x = 0; x < W; x++) {
+                const int32_t idx = y * W + x;
+                const uint32_t rnd = seeds[(uint32_t)idx % seed_count];
+                PathState st;
+                st.sampler = sampler_for_path(frame, rnd);
+                const float r1 = st.sampler.next();
+                const float r2 = st.sampler.next();
+                const float sx = (x + r1) / (float)(cam->width);
+                const float sy = (y + r2) / (float)(cam->height);
+                Ray ray = camera_sample(*cam, sx, sy);
+                st.throughput = V3(1.0f); st.pdfb = 1.0f; st.contrib = V3(0.0f);
+                st.terminated = false; st.singular = false;
+                int32_t depth = 0;
+                while (depth < max_depth) {
+                    AtnHit isect;
+                    const bool is_hit = Traverse(s, ray, kInf, &isect, nullptr);
+                    n_closest++;
+                    AtnBounceRecord rec;
+                    memset(&rec, 0, sizeof(rec));
+                    rec.ray.org = AtnVec3{ray.org.x, ray.org.y, ray.org.z};
+                    rec.ray.dir = AtnVec3{ray.dir.x, ray.dir.y, ray.dir.z};
+                    rec.hit = isect;
+                    rec.flags = 1;
+                    bool will_continue = true;
+                    if (is_hit) {
+                        ShadowRayOut sh;
+                        Ray next = ray;
+                        shade_hit(s.view, ray, isect.objid, isect.primid, isect.a, isect.b, isect.t, isect.mtrlid,
+                                  depth, rr_depth, &st, &sh, &next);
+                        // HitShadowRay (pathtracing_impl.h:353-393)
+                        if (!st.terminated && sh.active) {
+                            n_shadow++;
+                            Ray sr; sr.org = sh.org; sr.dir = normalize(sh.dir);   // aten::ray(org, dir) renormalises
+                            AtnHit shit;
+                            Traverse(s, sr, sh.dist - kEps, &shit, nullptr);
+                            const bool vis = shadow_visible(s.view, s.view.lights[sh.light_id], sr, sh.dist,
+                                                            shit.objid, shit.primid, shit.a, shit.b, shit.t, shit.mtrlid);
+                            if (vis) st.contrib = st.contrib + sh.lightcontrib;
+                            rec.shadow_active = 1;
+                            rec.shadow_org[0] = sh.org.x; rec.shadow_org[1] = sh.org.y; rec.shadow_org[2] = sh.org.z;
+                            rec.shadow_dist = sh.dist;
+                            rec.shadow_dir[0] = sh.dir.x; rec.shadow_dir[1] = sh.dir.y; rec.shadow_dir[2] = sh.dir.z;
+                            rec.light_contrib[0] = sh.lightcontrib.x; rec.light_contrib[1] = sh.lightcontrib.y; rec.light_contrib[2] = sh.lightcontrib.z;
+                            rec.shadow_visible = vis ? 1 : 0;
+                        }
+                        will_continue = !st.terminated;
+                        ray = next;
+                    }
+                    else {
+                        shade_miss(s.view, *cam, x, y, W, H, depth, ray, &st);
+                        will_continue = false;
+                    }
+                    rec.throughput[0] = st.throughput.x; rec.throughput[1] = st.throughput.y; rec.throughput[2] = st.throughput.z;
+                    rec.pdfb = st.pdfb;
+                    rec.contrib[0] = st.contrib.x; rec.contrib[1] = st.contrib.y; rec.contrib[2] = st.contrib.z;
+                    if (!will_continue) rec.flags |= 2;
+                    if (recs) recs[(size_t)idx * max_depth + depth] = rec;
+                    if (!will_continue) break;
+                    depth++;
+                }
+                // dst.buffer->put(x, y, vec4(col / cnt, 1)) with cnt = 1, FilmProgressive::put
+                AtnVec4& cur = image[idx];
+                const float n = (float)((int32_t)cur.w);
+                const V3 col = st.contrib / 1.0f;
+                cur.x = (n * cur.x + col.x) / (n + 1);
+                cur.y = (n * cur.y + col.y) / (n + 1);
+                cur.z = (n * cur.z + col.z) / (n + 1);
+                cur.w = n + 1;
+            }
+        }
+    }
+    if (stats) { stats[0] = n_closest; stats[1] = n_shadow; }
+    return 0;
+}
+
+__attribute__((visibility("default")))
+int oracle_cmj(uint32_t idx, uint32_t scramble, int32_t n, float* out)
+{
+    Sampler s; s.idx = idx; s.dim = 0; s.scramble = scramble;
+    for (int32_t i = 0; i < n; i++) out[i] = s.next();
+    return 0;
+}
+
+// Camera rays of GeneratePath (pathtracing_impl.h:65-110) for a whole frame.
+__attribute__((visibility("default")))
+int oracle_camera_rays(const AtnCameraParameter* cam, const uint32_t* seeds, uint32_t seed_count,
+                       int32_t W, int32_t H, uint32_t frame, AtnRay* rays)
+{
+    for (int32_t y = 0; y < H; y++) for (int32_t x = 0; x < W; x++) {
+        const int32_t idx = y * W + x;
+        Sampler sp = sampler_for_path(frame, seeds[(uint32_t)idx % seed_count]);
+        const float r1 = sp.next(), r2 = sp.next();
+        const Ray r = camera_sample(*cam, (x + r1) / (float)cam->width, (y + r2) / (float)cam->height);
+        rays[idx].org = AtnVec3{r.org.x, r.org.y, r.org.z};
+        rays[idx].dir = AtnVec3{r.dir.x, r.dir.y, r.dir.z};
+    }
+    return 0;
+}
+
+__attribute__((visibility("default")))
+void oracle_set_threads(int n) { omp_set_num_threads(n); }
+
+}  // extern "C"

@@ -21,6 +21,7 @@
 #include <string>
 #include <vector>
 #include <unistd.h>
+#include <dirent.h>
 #include <omp.h>
 
 #include "aten.h"
@@ -48,6 +49,20 @@ std::shared_ptr<aten::material> MakeMtrlP(
 {
     p.type = type;
     return ctxt.CreateMaterialWithMaterialParameter(name, p, nullptr, nullptr, nullptr);
+}
+
+std::string FindNoCase(const std::string& dir, const std::string& file)
+{
+    auto lower = [](std::string v) { for (auto& ch : v) ch = (char)tolower(ch); return v; };
+    DIR* d = opendir(dir.c_str());
+    std::string found = dir + "/" + file;
+    if (!d) return found;
+    const std::string want = lower(file);
+    while (auto* e = readdir(d)) {
+        if (lower(e->d_name) == want) { found = dir + "/" + e->d_name; break; }
+    }
+    closedir(d);
+    return found;
 }
 
 // Analytic sky written into an aten::texture: the snapshot has no asset/envmap/*.hdr.
@@ -178,8 +193,9 @@ struct Harness {
                 const std::string& albedo, const std::string& nml) -> std::shared_ptr<aten::material> {
                 std::shared_ptr<aten::texture> at, nt;
                 if (textured) {
-                    if (!albedo.empty()) at = aten::ImageLoader::load(g_asset + "/sponza/" + albedo, c);
-                    if (!nml.empty()) nt = aten::ImageLoader::load(g_asset + "/sponza/" + nml, c);
+                    // sponza.mtl names its maps in another letter case than the files on disk
+                    if (!albedo.empty()) at = aten::ImageLoader::load(FindNoCase(g_asset + "/sponza", albedo), c);
+                    if (!nml.empty()) nt = aten::ImageLoader::load(FindNoCase(g_asset + "/sponza", nml), c);
                 }
                 const std::string n(name);
                 if (n.find("stup") != std::string::npos || n.find("luk") != std::string::npos) {
@@ -461,7 +477,8 @@ int main(int argc, char** argv)
         if (!hs.Build(name, atoi(argv[4]), atoi(argv[5]))) return 1;
         idaten_b200::FlatScene flat;
         flat.Gather(hs.ctxt, hs.scene.getAccel()->getNodes());
-        if (!flat.Save(argv[6], hs.camera.param(), hs.W, hs.H, aten::getRandom())) return 1;
+        // seeds are std::mt19937(0) outputs; readers regenerate them (aten_b200/scene_io.py:mt19937_seeds)
+        if (!flat.Save(argv[6], hs.camera.param(), hs.W, hs.H, std::vector<uint32_t>())) return 1;
         size_t nn = 0; for (auto& l : flat.nodes) nn += l.size();
         printf("{\"scene\": \"%s\", \"objects\": %zu, \"matrices\": %zu, \"materials\": %zu, \"lights\": %zu, "
                "\"triangles\": %zu, \"vertices\": %zu, \"node_lists\": %zu, \"nodes\": %zu, \"textures\": %zu}\n",

@@ -1,0 +1,141 @@
+"""TEST INFRASTRUCTURE: ctypes access to the checkers under oracle/ -- the CPU restatement
+(oracle/_build/libpt_oracle.so) and the reference itself compiled in place (oracle/_ref/ref_harness).
+Only tests/, __graft_entry__.smoke() and bench.py's reference arm use this module."""
+from __future__ import annotations
+
+import ctypes as C
+import json
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+
+from aten_b200 import scene_io as sio
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+REF_BIN = os.path.join(ORACLE_DIR, "_ref", "ref_harness")
+REF_ASSET = os.path.join(ORACLE_DIR, "_ref", "asset")
+_lib = None
+
+
+def build_oracle():
+    subprocess.run(["make", "-s", "-C", ORACLE_DIR], check=True)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        path = os.path.join(ORACLE_DIR, "_build", "libpt_oracle.so")
+        if not os.path.exists(path):
+            build_oracle()
+        _lib = C.CDLL(path)
+    return _lib
+
+
+def trace_closest(scene: sio.Scene, rays: np.ndarray, t_max=None, counters=False):
+    rays = np.ascontiguousarray(rays, dtype=sio.RAY_DTYPE)
+    hits = np.zeros(len(rays), dtype=sio.HIT_DTYPE)
+    blob = scene.blob()
+    cnt = np.zeros(4, np.uint64)
+    tm = None if t_max is None else np.ascontiguousarray(t_max, dtype=np.float32)
+    lib().oracle_trace_closest(C.byref(blob), C.c_void_p(rays.ctypes.data),
+                               C.c_void_p(tm.ctypes.data) if tm is not None else None,
+                               C.c_size_t(len(rays)), C.c_void_p(hits.ctypes.data),
+                               C.c_void_p(cnt.ctypes.data) if counters else None)
+    return (hits, cnt) if counters else hits
+
+
+def trace_any(scene: sio.Scene, rays: np.ndarray, dist: np.ndarray):
+    rays = np.ascontiguousarray(rays, dtype=sio.RAY_DTYPE)
+    dist = np.ascontiguousarray(dist, dtype=np.float32)
+    vis = np.zeros(len(rays), dtype=np.uint8)
+    blob = scene.blob()
+    lib().oracle_trace_any(C.byref(blob), C.c_void_p(rays.ctypes.data), C.c_void_p(dist.ctypes.data),
+                           C.c_size_t(len(rays)), C.c_void_p(vis.ctypes.data))
+    return vis
+
+
+def render(scene: sio.Scene, frames=1, max_depth=5, rr_depth=3, first_frame=0, records=False, image=None, threads=None):
+    W, H = scene.width, scene.height
+    if threads:
+        lib().oracle_set_threads(int(threads))
+    img = np.zeros((H * W, 4), np.float32) if image is None else np.ascontiguousarray(image, np.float32).reshape(H * W, 4)
+    recs = np.zeros((H * W, max_depth), sio.BOUNCE_DTYPE) if records else None
+    seeds = scene.seeds_for(W * H)
+    stats = np.zeros(2, np.uint64)
+    blob = scene.blob()
+    cam = np.ascontiguousarray(scene.camera)
+    lib().oracle_render(C.byref(blob), C.c_void_p(cam.ctypes.data), C.c_void_p(seeds.ctypes.data), C.c_uint32(len(seeds)),
+                        C.c_int32(W), C.c_int32(H), C.c_uint32(first_frame), C.c_int32(frames), C.c_int32(max_depth),
+                        C.c_int32(rr_depth), C.c_void_p(img.ctypes.data),
+                        C.c_void_p(recs.ctypes.data) if records else None, C.c_void_p(stats.ctypes.data))
+    return img.reshape(H, W, 4), recs, stats
+
+
+def cmj(idx, scramble, n):
+    out = np.zeros(n, np.float32)
+    lib().oracle_cmj(C.c_uint32(idx), C.c_uint32(scramble), C.c_int32(n), C.c_void_p(out.ctypes.data))
+    return out
+
+
+def camera_rays(scene: sio.Scene, frame=0):
+    W, H = scene.width, scene.height
+    rays = np.zeros(W * H, sio.RAY_DTYPE)
+    seeds = scene.seeds_for(W * H)
+    cam = np.ascontiguousarray(scene.camera)
+    lib().oracle_camera_rays(C.c_void_p(cam.ctypes.data), C.c_void_p(seeds.ctypes.data), C.c_uint32(len(seeds)),
+                             C.c_int32(W), C.c_int32(H), C.c_uint32(frame), C.c_void_p(rays.ctypes.data))
+    return rays
+
+
+# ---- the reference itself (oracle/_ref) ------------------------------------------------------
+def have_ref() -> bool:
+    return os.path.exists(REF_BIN) and os.path.isdir(REF_ASSET)
+
+
+def ref_run(*args, timeout=3600):
+    """Run oracle/_ref/ref_harness; returns the JSON line it prints."""
+    cmd = [REF_BIN, REF_ASSET] + [str(a) for a in args]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=timeout)
+    if r.returncode != 0:
+        raise RuntimeError(f"ref_harness failed ({r.returncode}): {' '.join(cmd)}\n{r.stderr[-2000:]}")
+    for line in reversed(r.stdout.strip().splitlines()):
+        if line.startswith("{"):
+            return json.loads(line)
+    return {}
+
+
+def ref_scene(name, W, H) -> sio.Scene:
+    with tempfile.TemporaryDirectory() as d:
+        p = os.path.join(d, "s.atnscene")
+        ref_run("scene", name, W, H, p)
+        return sio.load_scene(p)
+
+
+def ref_trace(name, W, H, frame=0, depth=5, rr=3):
+    with tempfile.TemporaryDirectory() as d:
+        pr, pi = os.path.join(d, "r.bin"), os.path.join(d, "i.f32")
+        info = ref_run("trace", name, W, H, frame, depth, rr, pr, pi)
+        recs = np.fromfile(pr, sio.BOUNCE_DTYPE).reshape(H * W, depth)
+        img = np.fromfile(pi, np.float32).reshape(H, W, 4)
+    return recs, img, info
+
+
+def ref_render(name, W, H, frames=1, depth=5, rr=3, threads=8):
+    with tempfile.TemporaryDirectory() as d:
+        pi = os.path.join(d, "i.f32")
+        info = ref_run("render", name, W, H, frames, depth, rr, threads, pi)
+        img = np.fromfile(pi, np.float32).reshape(H, W, 4)
+    return img, info
+
+
+def ref_rays(name, rays: np.ndarray, t_max: np.ndarray):
+    with tempfile.TemporaryDirectory() as d:
+        pin, pout = os.path.join(d, "in.bin"), os.path.join(d, "out.bin")
+        buf = np.zeros((len(rays), 7), np.float32)
+        buf[:, 0:3] = rays["org"]; buf[:, 3:6] = rays["dir"]; buf[:, 6] = t_max
+        buf.tofile(pin)
+        ref_run("rays", name, pin, pout)
+        return np.fromfile(pout, sio.HIT_DTYPE)

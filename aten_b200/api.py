@@ -1,0 +1,238 @@
+"""Python host side of the C ABI (include/aten_b200.h) -- a thin ctypes mirror of the reference's
+renderer object ``idaten::PathTracing`` (reference src/libidaten/kernel/pathtracing.h:107-152,
+src/libidaten/kernel/renderer.h:61-116): same method names, argument meaning and call order as the
+calls ``device_renderer`` makes (src/device_renderer/main.cpp:144-148, 199-202).
+
+There is no CPU path: without the CUDA library or without a GPU every call raises ``AtnError``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import scene_io as sio
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libaten_b200.so")
+
+EXPORTS = [
+    "atn_create", "atn_destroy", "atn_last_error", "atn_version", "atn_upload_scene", "atn_update_camera",
+    "atn_update_top_layer", "atn_update_materials", "atn_update_lights", "atn_update_config", "atn_set_seeds",
+    "atn_set_frame", "atn_get_frame", "atn_reset", "atn_set_progressive", "atn_set_hit_distance_limit",
+    "atn_render", "atn_render_region", "atn_synchronize", "atn_readback", "atn_device_image", "atn_get_stats",
+    "atn_set_profiling", "atn_get_stream", "atn_trace_closest", "atn_trace_any", "atn_trace_closest_device",
+    "atn_trace_any_device", "atn_set_bounce_tap",
+]
+
+
+class AtnError(RuntimeError):
+    pass
+
+
+class AtnStats(C.Structure):
+    _fields_ = [("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("camera_samples", C.c_uint64),
+                ("kernel_launches", C.c_uint64), ("device_ms", C.c_float), ("trace_ms", C.c_float)]
+
+
+_lib = None
+
+
+def load_library(path: str | None = None):
+    """dlopen libaten_b200.so; fails loudly if it was not built (python -m aten_b200.build)."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or LIB_PATH
+    if not os.path.exists(p):
+        raise AtnError(f"{p} is missing: build it with `python -m aten_b200.build` (needs nvcc); "
+                       "aten_b200 has no CPU fallback")
+    lib = C.CDLL(p)
+    lib.atn_last_error.restype = C.c_char_p
+    lib.atn_version.restype = C.c_char_p
+    for name in EXPORTS:
+        fn = getattr(lib, name)          # AttributeError if the symbol is not exported
+        if name not in ("atn_last_error", "atn_version"):
+            fn.restype = C.c_int
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def _check(lib, rc):
+    if rc != 0:
+        raise AtnError(f"[{rc}] {lib.atn_last_error().decode(errors='replace')}")
+
+
+class PathTracing:
+    """``idaten::PathTracing`` over the C ABI.
+
+    >>> r = PathTracing(device=0)
+    >>> r.UpdateSceneData(scene)            # Renderer::UpdateSceneData
+    >>> r.render(w, h, max_samples, max_bounce)
+    >>> img = r.readback()                  # float32 [h, w, 4]; replaces the GL surface
+    """
+
+    def __init__(self, device: int = 0):
+        self._lib = load_library()
+        self._h = C.c_void_p()
+        _check(self._lib, self._lib.atn_create(C.c_int(device), C.byref(self._h)))
+        self.device = device
+        self.width = self.height = 0
+        self._scene = None
+        self._tap = None
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.atn_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # -- Renderer::UpdateSceneData (reference renderer.cpp:12-131) ------------------------------
+    def UpdateSceneData(self, scene: sio.Scene, width: int | None = None, height: int | None = None, seeds=None):
+        width = width or scene.width
+        height = height or scene.height
+        blob = scene.blob()
+        cam = np.ascontiguousarray(scene.camera)
+        _check(self._lib, self._lib.atn_upload_scene(self._h, C.byref(blob), C.c_void_p(cam.ctypes.data),
+                                                     C.c_int32(width), C.c_int32(height)))
+        self.width, self.height = width, height
+        self._scene = scene
+        s = scene.seeds_for(width * height) if seeds is None else np.ascontiguousarray(seeds, np.uint32)
+        self.set_seeds(s)
+
+    def set_seeds(self, seeds: np.ndarray):
+        seeds = np.ascontiguousarray(seeds, np.uint32)
+        _check(self._lib, self._lib.atn_set_seeds(self._h, C.c_void_p(seeds.ctypes.data), C.c_uint32(len(seeds))))
+
+    def updateCamera(self, camera: np.ndarray):
+        cam = np.ascontiguousarray(camera, sio.CAMERA_DTYPE)
+        _check(self._lib, self._lib.atn_update_camera(self._h, C.c_void_p(cam.ctypes.data)))
+
+    def updateBVH(self, top_nodes: np.ndarray, objects: np.ndarray, matrices: np.ndarray):
+        top = np.ascontiguousarray(top_nodes, sio.NODE_DTYPE)
+        obj = np.ascontiguousarray(objects, sio.OBJ_DTYPE)
+        mtx = np.ascontiguousarray(matrices, np.float32).reshape(-1, 16)
+        _check(self._lib, self._lib.atn_update_top_layer(
+            self._h, C.c_void_p(top.ctypes.data), C.c_uint32(len(top)), C.c_void_p(obj.ctypes.data),
+            C.c_uint32(len(obj)), C.c_void_p(mtx.ctypes.data), C.c_uint32(len(mtx))))
+
+    def updateMaterial(self, materials: np.ndarray):
+        m = np.ascontiguousarray(materials, sio.MTRL_DTYPE)
+        _check(self._lib, self._lib.atn_update_materials(self._h, C.c_void_p(m.ctypes.data), C.c_uint32(len(m))))
+
+    def updateLight(self, lights: np.ndarray):
+        l = np.ascontiguousarray(lights, sio.LIGHT_DTYPE)
+        _check(self._lib, self._lib.atn_update_lights(self._h, C.c_void_p(l.ctypes.data), C.c_uint32(len(l))))
+
+    def UpdateSceneRenderingConfig(self, config: np.ndarray):
+        c = np.ascontiguousarray(config, sio.CONFIG_DTYPE)
+        _check(self._lib, self._lib.atn_update_config(self._h, C.c_void_p(c.ctypes.data)))
+
+    # -- frame control ---------------------------------------------------------------------------
+    def reset(self):
+        _check(self._lib, self._lib.atn_reset(self._h))
+
+    def GetFrameCount(self) -> int:
+        f = C.c_uint32()
+        _check(self._lib, self._lib.atn_get_frame(self._h, C.byref(f)))
+        return f.value
+
+    def set_frame(self, frame: int):
+        _check(self._lib, self._lib.atn_set_frame(self._h, C.c_uint32(frame)))
+
+    def SetEnableProgressive(self, b: bool):
+        _check(self._lib, self._lib.atn_set_progressive(self._h, C.c_int(1 if b else 0)))
+
+    def setHitDistanceLimit(self, d: float):
+        _check(self._lib, self._lib.atn_set_hit_distance_limit(self._h, C.c_float(d)))
+
+    def set_profiling(self, b: bool):
+        _check(self._lib, self._lib.atn_set_profiling(self._h, C.c_int(1 if b else 0)))
+
+    # -- render ----------------------------------------------------------------------------------
+    def render(self, width: int, height: int, maxSamples: int, maxBounce: int, rrBounce: int = 3):
+        """PathTracingImplBase::render (reference pathtracing.cpp:49-89); rrBounce = 3 is the
+        reference's constant (pathtracing.cpp:97)."""
+        _check(self._lib, self._lib.atn_render(self._h, C.c_int32(width), C.c_int32(height), C.c_int32(maxSamples),
+                                               C.c_int32(maxBounce), C.c_int32(rrBounce)))
+
+    def render_region(self, width, height, x0, y0, x1, y1, sample_begin, sample_end, maxBounce, rrBounce=3):
+        _check(self._lib, self._lib.atn_render_region(
+            self._h, C.c_int32(width), C.c_int32(height), C.c_int32(x0), C.c_int32(y0), C.c_int32(x1), C.c_int32(y1),
+            C.c_int32(sample_begin), C.c_int32(sample_end), C.c_int32(maxBounce), C.c_int32(rrBounce)))
+
+    def synchronize(self):
+        _check(self._lib, self._lib.atn_synchronize(self._h))
+
+    def readback(self, out: np.ndarray | None = None) -> np.ndarray:
+        n = self.width * self.height
+        if out is None:
+            out = np.empty((self.height, self.width, 4), np.float32)
+        _check(self._lib, self._lib.atn_readback(self._h, C.c_void_p(out.ctypes.data), C.c_size_t(n)))
+        return out
+
+    def readback_into(self, host_ptr: int):
+        """Read back into caller-owned (e.g. pinned) host memory given as an address."""
+        _check(self._lib, self._lib.atn_readback(self._h, C.c_void_p(host_ptr), C.c_size_t(self.width * self.height)))
+
+    def device_image(self):
+        p = C.c_void_p()
+        n = C.c_size_t()
+        _check(self._lib, self._lib.atn_device_image(self._h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def stream(self) -> int:
+        p = C.c_void_p()
+        _check(self._lib, self._lib.atn_get_stream(self._h, C.byref(p)))
+        return p.value or 0
+
+    def stats(self) -> dict:
+        s = AtnStats()
+        _check(self._lib, self._lib.atn_get_stats(self._h, C.byref(s)))
+        return {k: getattr(s, k) for k, _ in AtnStats._fields_}
+
+    def set_bounce_tap(self, max_bounce: int | None):
+        """Install (or remove with None) the per-bounce parity tap; returns the record array."""
+        if max_bounce is None:
+            self._tap = None
+            _check(self._lib, self._lib.atn_set_bounce_tap(self._h, None, C.c_int32(0)))
+            return None
+        self._tap = np.zeros((self.width * self.height, max_bounce), sio.BOUNCE_DTYPE)
+        _check(self._lib, self._lib.atn_set_bounce_tap(self._h, C.c_void_p(self._tap.ctypes.data), C.c_int32(max_bounce)))
+        return self._tap
+
+    # -- ray queries -----------------------------------------------------------------------------
+    def trace_closest(self, rays: np.ndarray, t_max: np.ndarray | None = None) -> np.ndarray:
+        rays = np.ascontiguousarray(rays, sio.RAY_DTYPE)
+        hits = np.zeros(len(rays), sio.HIT_DTYPE)
+        tm = None if t_max is None else np.ascontiguousarray(t_max, np.float32)
+        _check(self._lib, self._lib.atn_trace_closest(
+            self._h, C.c_void_p(rays.ctypes.data), C.c_void_p(tm.ctypes.data) if tm is not None else None,
+            C.c_size_t(len(rays)), C.c_void_p(hits.ctypes.data)))
+        return hits
+
+    def trace_any(self, rays: np.ndarray, dist: np.ndarray) -> np.ndarray:
+        rays = np.ascontiguousarray(rays, sio.RAY_DTYPE)
+        dist = np.ascontiguousarray(dist, np.float32)
+        vis = np.zeros(len(rays), np.uint8)
+        _check(self._lib, self._lib.atn_trace_any(self._h, C.c_void_p(rays.ctypes.data), C.c_void_p(dist.ctypes.data),
+                                                  C.c_size_t(len(rays)), C.c_void_p(vis.ctypes.data)))
+        return vis
+
+    def trace_closest_device(self, rays_ptr: int, t_max_ptr: int | None, n: int, hits_ptr: int):
+        _check(self._lib, self._lib.atn_trace_closest_device(self._h, C.c_void_p(rays_ptr),
+                                                             C.c_void_p(t_max_ptr) if t_max_ptr else None,
+                                                             C.c_size_t(n), C.c_void_p(hits_ptr)))
+
+    def trace_any_device(self, rays_ptr: int, dist_ptr: int, n: int, vis_ptr: int):
+        _check(self._lib, self._lib.atn_trace_any_device(self._h, C.c_void_p(rays_ptr), C.c_void_p(dist_ptr),
+                                                         C.c_size_t(n), C.c_void_p(vis_ptr)))

@@ -1,0 +1,1094 @@
+// atn_kernels.cu -- sm_100a kernels of the wavefront NEE path tracer + the C ABI (include/aten_b200.h).
+//
+// Pipeline per camera sample (replaces reference src/libidaten/kernel/pathtracing.cpp:91-153):
+//
+//   k_generate            genPath            (pt_standard_impl.cu:25-50, pathtracing_impl.h:65-110)
+//   for bounce:
+//     k_trace<CLOSEST>    hitTest            (pt_standard_impl.cu:57-229, threaded_bvh_traverser.h:98-304)
+//     k_shade             shade + ShadeMiss  (pathtracing_impl.cu:18-238, pt_standard_impl.cu:330-362;
+//                                             HOST ordering, pathtracing.cpp:91-236)
+//     k_trace<SHADOW>     hitShadowRay       (pathtracing_impl.cu:240-280, pathtracing_impl.h:266-393)
+//   k_gather              gather             (pathtracing_impl.cu:282-324, film.cpp:61-71)
+//
+// B200-native choices (DESIGN.md has the numbers):
+//   * path state is SoA float4 / u32 arrays indexed by path slot; there is no AoS PathThroughput;
+//   * the reference's scan-based stream compaction (StreamCompaction.cu, >= 7 launches + syncs per
+//     bounce) is replaced by device-side queues appended with warp-aggregated atomics
+//     (__ballot_sync / __popc / one atomicAdd per warp); the host never reads a count, so a frame
+//     is a fixed launch sequence with no synchronisation;
+//   * traversal kernels are persistent: grid = SMs x resident blocks, each warp pulls 32 rays at a
+//     time from the queue with one atomicAdd;
+//   * nodes are 64-byte child-pair records fetched with 128-bit read-only loads (LDG.E.128.CONSTANT),
+//     triangles are 48-byte gathered records; the traversal stack is a per-thread shared-memory
+//     short stack that spills to local memory only beyond kSmemStack entries;
+//   * no tensor cores: the path is pointer chasing + FP32 slab / Moeller-Trumbore arithmetic.
+// Compiled with -fmad=false: the intersection arithmetic must round exactly like the reference's
+// x86 build for primitive ids to match bit for bit.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <string>
+#include <vector>
+#include <algorithm>
+
+#include "atn_math.cuh"
+#include "atn_bvh.h"
+
+using namespace atn;
+
+// ---------------------------------------------------------------------------------------------
+// error handling
+// ---------------------------------------------------------------------------------------------
+static thread_local std::string g_last_error;
+
+static int set_error(int code, const char* fmt, ...)
+{
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                              \
+    do {                                                                                            \
+        cudaError_t e__ = (expr);                                                                   \
+        if (e__ != cudaSuccess)                                                                     \
+            return set_error(ATN_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), \
+                             __FILE__, __LINE__);                                                   \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// device-side views
+// ---------------------------------------------------------------------------------------------
+struct BvhView {
+    const float4* nodes;     // PairNode as 4 x float4
+    const float4* tris;      // TriLeaf as 3 x float4
+    const int4* insts;       // InstLeaf
+    const AtnMat4* matrices;
+    int32_t top_root;
+    float t_min;
+};
+
+constexpr int kMaxBounce = 16;
+constexpr int kSmemStack = 12;     // shared-memory stack entries per thread (ints)
+constexpr int kLocalStack = 64;    // overflow, local memory
+constexpr int kTraceBlock = 128;
+
+// Per-frame device counters; zeroed with one memset per sample pass.
+struct Counters {
+    int32_t n_active[kMaxBounce + 1];   // rays queued for closest-hit at bounce b
+    int32_t n_shadow[kMaxBounce];       // shadow rays queued at bounce b
+    int32_t fetch_closest[kMaxBounce];  // persistent-thread work cursors
+    int32_t fetch_shadow[kMaxBounce];
+    int32_t fetch_query;
+    int32_t pad[3];
+};
+
+// Ray totals of one atn_render call (not cleared per sample).
+struct Totals { unsigned long long closest, shadow; };
+
+struct PathBuffers {
+    float4* ray_o;        // org.xyz, -
+    float4* ray_d;        // dir.xyz, -
+    float4* hit0;         // t, a, b, bits(primid)
+    int2* hit1;           // objid, mtrlid   (objid < 0: miss)
+    float4* throughput;   // xyz, pdfb
+    float4* contrib;      // xyz, samples
+    uint32_t* sampler_dim;
+    uint32_t* flags;      // bit0 terminated, bit1 singular
+    int32_t* queue[2];
+    float4* sh_o;         // shadow org.xyz, dist
+    float4* sh_d;         // shadow dir.xyz, bits(light id)
+    float4* sh_c;         // light contribution xyz, bits(path slot)
+};
+
+// ---------------------------------------------------------------------------------------------
+// traversal
+// ---------------------------------------------------------------------------------------------
+struct TraceResult {
+    float t, a, b;
+    int32_t leaf;      // tri leaf index (tie-break rank), -1 none
+    int32_t inst;      // instance leaf index
+};
+
+enum : int { EXIT_NONE = 0, EXIT_ANY_HIT = 1, EXIT_HIT_BEFORE = 2 };
+
+__device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
+
+// Two-level closest-hit traversal over PairNodes with the reference's acceptance rules
+// (threaded_bvh_traverser.h:98-304): inner boxes use aabb::hit with the running t_max, leaves are
+// never box-tested, a triangle is accepted iff t_min < t && t < best (ties: lowest depth-first rank,
+// which is what "first encountered" means in the reference's fixed visit order).
+// early_exit: EXIT_ANY_HIT stops at the first accepted triangle, EXIT_HIT_BEFORE at the first
+// accepted triangle with t <= exit_dist (shadow rays towards infinite / singular lights).
+template <bool kShadow>
+__device__ __forceinline__ void traverse(const BvhView& bv, const V3& org_w, const V3& dir_w, float t_max,
+                                         int early_exit, float exit_dist, int32_t* smem_stack, TraceResult* out)
+{
+    int32_t lstack[kLocalStack];
+    int sp = 0;
+    auto push = [&](int32_t v) {
+        if (sp < kSmemStack) smem_stack[sp * kTraceBlock] = v; else lstack[sp - kSmemStack] = v;
+        sp++;
+    };
+    auto pop = [&]() -> int32_t {
+        sp--;
+        return (sp < kSmemStack) ? smem_stack[sp * kTraceBlock] : lstack[sp - kSmemStack];
+    };
+
+    V3 org = org_w, dir = dir_w;
+    RayInv ri = ray_inv(org, dir);
+    const float t_min = bv.t_min;
+    float best_t = kInf, best_a = 0.0f, best_b = 0.0f;
+    int32_t best_leaf = -1, best_inst = -1;
+    int32_t cur_inst = -1;
+    int32_t cur = bv.top_root;
+    bool done = false;
+
+    while (!done) {
+        // ---- descend through inner nodes ----
+        while (cur >= 0) {
+            const float4* np = bv.nodes + (size_t)cur * 4;
+            const float4 n0 = ldg4(np + 0);
+            const float4 n1 = ldg4(np + 1);
+            const float4 n2 = ldg4(np + 2);
+            const float4 n3 = ldg4(np + 3);
+            const int32_t left = __float_as_int(n3.x);
+            const int32_t right = __float_as_int(n3.y);
+            float t0l = -kInf, t0r = -kInf;
+            bool hl = (left != kRefNull), hr = (right != kRefNull);
+            if (hl && left >= 0) hl = aabb_hit(ri, V3(n0.x, n0.z, n2.x), V3(n0.y, n0.w, n2.y), t_min, t_max, &t0l);
+            if (hr && right >= 0) hr = aabb_hit(ri, V3(n1.x, n1.z, n2.z), V3(n1.y, n1.w, n2.w), t_min, t_max, &t0r);
+            if (hl && hr) {
+                // near child first; leaves (t0 = -inf) are taken before boxes
+                const bool swap = t0r < t0l;
+                const int32_t nearc = swap ? right : left;
+                const int32_t farc = swap ? left : right;
+                push(farc);
+                cur = nearc;
+            }
+            else if (hl) cur = left;
+            else if (hr) cur = right;
+            else { cur = kRefNull; break; }
+        }
+
+        // ---- leaf / marker ----
+        if (cur != kRefNull && cur != kRefExit) {
+            const int32_t leaf = ~cur;
+            if (cur_inst < 0) {
+                // top-layer leaf: enter the instance (threaded_bvh_traverser.h:146-185)
+                const int4 il = __ldg(bv.insts + leaf);
+                if (il.y != kRefNull) {
+                    push(kRefExit);
+                    cur_inst = leaf;
+                    if (il.z >= 0) {
+                        const AtnMat4 m = bv.matrices[il.z];
+                        const Ray tr = make_ray(mat_apply(m, org_w), mat_apply_xyz(m, dir_w));   // mat4::applyRay
+                        org = tr.org; dir = tr.dir;
+                    }
+                    else { org = org_w; dir = dir_w; }
+                    ri = ray_inv(org, dir);
+                    cur = il.y;
+                    continue;
+                }
+            }
+            else {
+                const float4* tp = bv.tris + (size_t)leaf * 3;
+                const float4 a = ldg4(tp + 0);
+                const float4 b = ldg4(tp + 1);
+                const float4 c = ldg4(tp + 2);
+                const TriHit h = intersect_triangle(org, dir, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), V3(c.x, c.y, c.z));
+                if (h.hit && h.t < kInf && t_min < h.t) {
+                    const bool closer = h.t < best_t ||
+                        (h.t == best_t && (cur_inst < best_inst || (cur_inst == best_inst && leaf < best_leaf)));
+                    if (closer) {
+                        best_t = h.t; best_a = h.a; best_b = h.b; best_leaf = leaf; best_inst = cur_inst;
+                        t_max = h.t;
+                        if (kShadow) {
+                            if (early_exit == EXIT_ANY_HIT || (early_exit == EXIT_HIT_BEFORE && h.t <= exit_dist)) break;
+                        }
+                    }
+                }
+            }
+        }
+
+        // ---- pop ----
+        for (;;) {
+            if (sp == 0) { done = true; break; }
+            cur = pop();
+            if (cur == kRefExit) {
+                cur_inst = -1;
+                org = org_w; dir = dir_w;
+                ri = ray_inv(org, dir);
+                continue;
+            }
+            break;
+        }
+    }
+    out->t = best_t; out->a = best_a; out->b = best_b; out->leaf = best_leaf; out->inst = best_inst;
+}
+
+// Resolve the winning leaf into the reference's Intersection fields.
+__device__ __forceinline__ void resolve_hit(const BvhView& bv, const TraceResult& r, int32_t* objid, int32_t* primid,
+                                            int32_t* mtrlid, int32_t* meshid)
+{
+    if (r.leaf < 0) { *objid = -1; *primid = -1; *mtrlid = -1; *meshid = -1; return; }
+    const float4* tp = bv.tris + (size_t)r.leaf * 3;
+    *primid = __float_as_int(ldg4(tp + 0).w);
+    *mtrlid = __float_as_int(ldg4(tp + 1).w);
+    const int32_t mesh = __float_as_int(ldg4(tp + 2).w);
+    const int4 il = __ldg(bv.insts + r.inst);
+    *objid = il.x;
+    *meshid = mesh < 0 ? il.w : mesh;
+}
+
+// Closest-hit kernel, persistent threads.  Rays come from the SoA path buffers through a queue of
+// path slots (queue == nullptr: identity).  `count` is read from device memory.
+__global__ void __launch_bounds__(kTraceBlock)
+k_trace_closest(BvhView bv, PathBuffers pb, const int32_t* __restrict__ queue, const int32_t* __restrict__ count_ptr,
+                int32_t* __restrict__ fetch, const float* __restrict__ t_max_arr, float t_max_all)
+{
+    __shared__ int32_t s_stack[kSmemStack * kTraceBlock];
+    const int lane = threadIdx.x & 31;
+    const int count = *count_ptr;
+    for (;;) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(fetch, 32);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= count) break;
+        const int i = base + lane;
+        if (i < count) {
+            const int slot = queue ? queue[i] : i;
+            const float4 o = pb.ray_o[slot];
+            const float4 d = pb.ray_d[slot];
+            TraceResult r;
+            traverse<false>(bv, V3(o.x, o.y, o.z), V3(d.x, d.y, d.z), t_max_arr ? t_max_arr[slot] : t_max_all,
+                            EXIT_NONE, 0.0f, s_stack + threadIdx.x, &r);
+            int32_t objid, primid, mtrlid, meshid;
+            resolve_hit(bv, r, &objid, &primid, &mtrlid, &meshid);
+            pb.hit0[slot] = make_float4(r.t, r.a, r.b, __int_as_float(primid));
+            pb.hit1[slot] = make_int2(objid, mtrlid);
+        }
+    }
+}
+
+// Shadow-ray kernel: traversal with the reference's closest-hit semantics (t_max = dist - 1e-9)
+// and early exit where that provably cannot change the answer; then scene::hitLight.
+template <bool kTap>
+__global__ void __launch_bounds__(kTraceBlock)
+k_trace_shadow(BvhView bv, SceneView sc, PathBuffers pb, const int32_t* __restrict__ count_ptr,
+               int32_t* __restrict__ fetch, AtnBounceRecord* tap, int tap_cap, int bounce)
+{
+    __shared__ int32_t s_stack[kSmemStack * kTraceBlock];
+    const int lane = threadIdx.x & 31;
+    const int count = *count_ptr;
+    for (;;) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(fetch, 32);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= count) break;
+        const int i = base + lane;
+        if (i < count) {
+            const float4 o = pb.sh_o[i];
+            const float4 d = pb.sh_d[i];
+            const float4 c = pb.sh_c[i];
+            const int light_id = __float_as_int(d.w);
+            const int slot = __float_as_int(c.w);
+            const AtnLightParameter& light = sc.lights[light_id];
+            const uint32_t attrib = light.attrib;
+            const int mode = (attrib & 2u) ? EXIT_ANY_HIT : ((attrib & 1u) ? EXIT_HIT_BEFORE : EXIT_NONE);
+            // aten::ray(rayorg, raydir) renormalises the direction (pathtracing_impl.h:378)
+            Ray sr; sr.org = V3(o.x, o.y, o.z); sr.dir = normalize(V3(d.x, d.y, d.z));
+            TraceResult r;
+            traverse<true>(bv, sr.org, sr.dir, o.w - kEps, mode, o.w, s_stack + threadIdx.x, &r);
+            int32_t objid, primid, mtrlid, meshid;
+            resolve_hit(bv, r, &objid, &primid, &mtrlid, &meshid);
+            const bool vis = shadow_visible(sc, light, sr, o.w, objid, primid, r.a, r.b, r.t, mtrlid);
+            if (vis) {
+                float4 cc = pb.contrib[slot];
+                cc.x += c.x; cc.y += c.y; cc.z += c.z;
+                pb.contrib[slot] = cc;
+            }
+            if (kTap) {
+                AtnBounceRecord& rec = tap[(size_t)slot * tap_cap + bounce];
+                rec.shadow_visible = vis ? 1 : 0;
+                if (vis) { const float4 cc = pb.contrib[slot]; rec.contrib[0] = cc.x; rec.contrib[1] = cc.y; rec.contrib[2] = cc.z; }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// generate / shade / gather
+// ---------------------------------------------------------------------------------------------
+struct FrameParams {
+    int32_t width, height;          // full image
+    int32_t x0, y0, rw, rh;         // region rendered by this call; slot s <-> (x0 + s % rw, y0 + s / rw)
+    uint32_t frame;                 // host frame index + sample index (pathtracing_impl.h:76-81)
+    int32_t max_bounce, rr_bounce;
+    uint32_t seed_count;
+};
+
+// GeneratePath (pathtracing_impl.h:65-110)
+__global__ void k_generate(FrameParams fp, AtnCameraParameter cam, const uint32_t* __restrict__ seeds, PathBuffers pb,
+                           Counters* cnt)
+{
+    const int n = fp.rw * fp.rh;
+    for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < n; s += gridDim.x * blockDim.x) {
+        const int ix = fp.x0 + s % fp.rw;
+        const int iy = fp.y0 + s / fp.rw;
+        const uint32_t idx = (uint32_t)(iy * fp.width + ix);
+        Sampler sp = sampler_for_path(fp.frame, seeds[idx % fp.seed_count]);
+        const float r1 = sp.next();
+        const float r2 = sp.next();
+        const float fs = (ix + r1) / (float)(cam.width);
+        const float ft = (iy + r2) / (float)(cam.height);
+        const Ray r = camera_sample(cam, fs, ft);
+        pb.ray_o[s] = make_float4(r.org.x, r.org.y, r.org.z, 0.0f);
+        pb.ray_d[s] = make_float4(r.dir.x, r.dir.y, r.dir.z, 0.0f);
+        pb.throughput[s] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+        pb.contrib[s] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
+        pb.sampler_dim[s] = sp.dim;
+        pb.flags[s] = 0u;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) cnt->n_active[0] = n;
+}
+
+// Append `value` for the lanes with `pred` to a device queue: one atomicAdd per warp.
+__device__ __forceinline__ int warp_append(bool pred, int32_t* counter)
+{
+    const unsigned mask = __ballot_sync(0xffffffffu, pred);
+    if (mask == 0u) return -1;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(mask) - 1;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(counter, __popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return pred ? base + __popc(mask & ((1u << lane) - 1u)) : -1;
+}
+
+template <bool kTap>
+__global__ void __launch_bounds__(128)
+k_shade(FrameParams fp, AtnCameraParameter cam, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb,
+        Counters* cnt, int bounce, AtnBounceRecord* tap, int tap_cap)
+{
+    const int count = cnt->n_active[bounce];
+    const int32_t* __restrict__ q_in = (bounce == 0) ? nullptr : pb.queue[bounce & 1];
+    int32_t* __restrict__ q_out = pb.queue[(bounce + 1) & 1];
+    const int rounds = (count + blockDim.x * gridDim.x - 1) / (blockDim.x * gridDim.x);
+    for (int it = 0; it < rounds; it++) {
+        const int i = (it * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+        const bool valid = i < count;
+        bool cont = false, shadow = false;
+        int slot = 0;
+        ShadowRayOut sh;
+        sh.active = false;
+        if (valid) {
+            slot = q_in ? q_in[i] : i;
+            const int ix = fp.x0 + slot % fp.rw;
+            const int iy = fp.y0 + slot / fp.rw;
+            const float4 o = pb.ray_o[slot];
+            const float4 d = pb.ray_d[slot];
+            const float4 h0 = pb.hit0[slot];
+            const int2 h1 = pb.hit1[slot];
+            const float4 th = pb.throughput[slot];
+            const float4 cb = pb.contrib[slot];
+            const uint32_t fl = pb.flags[slot];
+            Ray ray; ray.org = V3(o.x, o.y, o.z); ray.dir = V3(d.x, d.y, d.z);
+            PathState st;
+            st.throughput = V3(th.x, th.y, th.z); st.pdfb = th.w;
+            st.contrib = V3(cb.x, cb.y, cb.z);
+            st.sampler = sampler_for_path(fp.frame, seeds[(uint32_t)(iy * fp.width + ix) % fp.seed_count]);
+            st.sampler.dim = pb.sampler_dim[slot];
+            st.terminated = false;
+            st.singular = (fl & 2u) != 0u;
+            Ray next = ray;
+            if (h1.x >= 0) {
+                shade_hit(sc, ray, h1.x, __float_as_int(h0.w), h0.y, h0.z, h0.x, h1.y, bounce, fp.rr_bounce, &st, &sh, &next);
+            }
+            else {
+                shade_miss(sc, cam, ix, iy, fp.width, fp.height, bounce, ray, &st);
+            }
+            cont = !st.terminated && (bounce + 1 < fp.max_bounce);
+            shadow = !st.terminated && sh.active;      // HitShadowRay: terminated paths drop their shadow ray
+            pb.throughput[slot] = make_float4(st.throughput.x, st.throughput.y, st.throughput.z, st.pdfb);
+            pb.contrib[slot] = make_float4(st.contrib.x, st.contrib.y, st.contrib.z, cb.w);
+            pb.sampler_dim[slot] = st.sampler.dim;
+            pb.flags[slot] = (st.terminated ? 1u : 0u) | (st.singular ? 2u : 0u);
+            if (cont) {
+                pb.ray_o[slot] = make_float4(next.org.x, next.org.y, next.org.z, 0.0f);
+                pb.ray_d[slot] = make_float4(next.dir.x, next.dir.y, next.dir.z, 0.0f);
+            }
+            if (kTap) {
+                AtnBounceRecord& rec = tap[(size_t)slot * tap_cap + bounce];
+                rec.ray.org = AtnVec3{ o.x, o.y, o.z };
+                rec.ray.dir = AtnVec3{ d.x, d.y, d.z };
+                rec.hit.t = h0.x; rec.hit.objid = h1.x; rec.hit.mtrlid = h1.y; rec.hit.meshid = -1;
+                rec.hit.primid = __float_as_int(h0.w); rec.hit.a = h0.y; rec.hit.b = h0.z; rec.hit.isVoxel = 0;
+                rec.shadow_active = shadow ? 1 : 0;
+                rec.shadow_visible = 0;
+                if (shadow) {
+                    rec.shadow_org[0] = sh.org.x; rec.shadow_org[1] = sh.org.y; rec.shadow_org[2] = sh.org.z;
+                    rec.shadow_dist = sh.dist;
+                    rec.shadow_dir[0] = sh.dir.x; rec.shadow_dir[1] = sh.dir.y; rec.shadow_dir[2] = sh.dir.z;
+                    rec.light_contrib[0] = sh.lightcontrib.x; rec.light_contrib[1] = sh.lightcontrib.y; rec.light_contrib[2] = sh.lightcontrib.z;
+                }
+                rec.throughput[0] = st.throughput.x; rec.throughput[1] = st.throughput.y; rec.throughput[2] = st.throughput.z;
+                rec.pdfb = st.pdfb;
+                rec.contrib[0] = st.contrib.x; rec.contrib[1] = st.contrib.y; rec.contrib[2] = st.contrib.z;
+                rec.flags = 1 | (st.terminated ? 2 : 0);
+            }
+        }
+        // queue appends: one atomic per warp and queue
+        const int pos = warp_append(cont, &cnt->n_active[bounce + 1]);
+        if (cont) q_out[pos] = slot;
+        const int spos = warp_append(shadow, &cnt->n_shadow[bounce]);
+        if (shadow) {
+            pb.sh_o[spos] = make_float4(sh.org.x, sh.org.y, sh.org.z, sh.dist);
+            pb.sh_d[spos] = make_float4(sh.dir.x, sh.dir.y, sh.dir.z, __int_as_float(sh.light_id));
+            pb.sh_c[spos] = make_float4(sh.lightcontrib.x, sh.lightcontrib.y, sh.lightcontrib.z, __int_as_float(slot));
+        }
+    }
+}
+
+// pt::gather (pathtracing_impl.cu:282-324) / FilmProgressive::put (film.cpp:61-71)
+__global__ void k_gather(FrameParams fp, PathBuffers pb, float4* image, int progressive, const Counters* cnt, Totals* totals)
+{
+    const int n = fp.rw * fp.rh;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        unsigned long long c = 0, s = 0;
+        for (int b = 0; b < fp.max_bounce; b++) { c += (unsigned long long)cnt->n_active[b]; s += (unsigned long long)cnt->n_shadow[b]; }
+        totals->closest += c; totals->shadow += s;
+    }
+    for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < n; s += gridDim.x * blockDim.x) {
+        const int ix = fp.x0 + s % fp.rw;
+        const int iy = fp.y0 + s / fp.rw;
+        const float4 c = pb.contrib[s];
+        float4 cur = image[iy * fp.width + ix];
+        if (progressive) {
+            const float nn = (float)((int32_t)cur.w);
+            const float cx = c.x / 1.0f, cy = c.y / 1.0f, cz = c.z / 1.0f;   // col /= cnt, cnt = 1
+            cur.x = (nn * cur.x + cx) / (nn + 1);
+            cur.y = (nn * cur.y + cy) / (nn + 1);
+            cur.z = (nn * cur.z + cz) / (nn + 1);
+            cur.w = nn + 1;
+        }
+        else {
+            cur.x += c.x; cur.y += c.y; cur.z += c.z; cur.w += 1.0f;
+        }
+        image[iy * fp.width + ix] = cur;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// ray-query helpers (atn_trace_closest / atn_trace_any)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kTraceBlock)
+k_query_closest(BvhView bv, const AtnRay* __restrict__ rays, const float* __restrict__ t_max, int n,
+                int32_t* __restrict__ fetch, AtnHit* __restrict__ hits)
+{
+    __shared__ int32_t s_stack[kSmemStack * kTraceBlock];
+    const int lane = threadIdx.x & 31;
+    for (;;) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(fetch, 32);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        const int i = base + lane;
+        if (i < n) {
+            const AtnRay ray = rays[i];
+            TraceResult r;
+            traverse<false>(bv, V3(ray.org), V3(ray.dir), t_max ? t_max[i] : kInf, EXIT_NONE, 0.0f, s_stack + threadIdx.x, &r);
+            AtnHit h;
+            resolve_hit(bv, r, &h.objid, &h.primid, &h.mtrlid, &h.meshid);
+            h.t = r.t; h.a = r.a; h.b = r.b; h.isVoxel = 0;
+            hits[i] = h;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kTraceBlock)
+k_query_any(BvhView bv, const AtnRay* __restrict__ rays, const float* __restrict__ dist, int n,
+            int32_t* __restrict__ fetch, uint8_t* __restrict__ visible)
+{
+    __shared__ int32_t s_stack[kSmemStack * kTraceBlock];
+    const int lane = threadIdx.x & 31;
+    for (;;) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(fetch, 32);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        const int i = base + lane;
+        if (i < n) {
+            const AtnRay ray = rays[i];
+            const float dd = dist[i];
+            TraceResult r;
+            traverse<true>(bv, V3(ray.org), V3(ray.dir), dd - kEps, EXIT_HIT_BEFORE, dd, s_stack + threadIdx.x, &r);
+            visible[i] = (r.leaf < 0 || r.t > dd) ? 1 : 0;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+template <class T>
+struct DevBuf {
+    T* p{ nullptr };
+    size_t n{ 0 };
+    ~DevBuf() { release(); }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    cudaError_t resize(size_t count)
+    {
+        if (count <= n && p) return cudaSuccess;
+        release();
+        if (count == 0) return cudaSuccess;
+        cudaError_t e = cudaMalloc(&p, count * sizeof(T));
+        if (e == cudaSuccess) n = count;
+        return e;
+    }
+    cudaError_t upload(const T* src, size_t count, cudaStream_t s)
+    {
+        cudaError_t e = resize(count);
+        if (e != cudaSuccess || count == 0) return e;
+        return cudaMemcpyAsync(p, src, count * sizeof(T), cudaMemcpyHostToDevice, s);
+    }
+};
+
+struct AtnRenderer {
+    int device{ 0 };
+    cudaStream_t stream{ nullptr };
+    int sm_count{ 148 };
+    bool has_scene{ false };
+
+    // scene
+    DevBuf<AtnObjectParameter> objects;
+    DevBuf<AtnMat4> matrices;
+    DevBuf<AtnMaterialParameter> materials;
+    DevBuf<AtnLightParameter> lights;
+    DevBuf<AtnTriangleParameter> triangles;
+    DevBuf<AtnVec4> positions, normals;
+    DevBuf<AtnVec4> texels;
+    DevBuf<TexView> texviews;
+    DevBuf<PairNode> nodes;
+    DevBuf<TriLeaf> tris;
+    DevBuf<InstLeaf> insts;
+    DevBuf<uint32_t> seeds;
+    uint32_t seed_count{ 0 };
+    SceneView sv{};
+    BvhView bv{};
+    AtnCameraParameter camera{};
+    int32_t width{ 0 }, height{ 0 };
+    float hit_distance_limit{ kInf };
+
+    // host copies needed by atn_update_top_layer
+    std::vector<AtnObjectParameter> h_objects;
+    std::vector<AtnMat4> h_matrices;
+    std::vector<AtnTriangleParameter> h_triangles;
+    std::vector<AtnVec4> h_positions;
+    std::vector<std::vector<AtnBvhNode>> h_lists;
+
+    // path state
+    DevBuf<float4> ray_o, ray_d, hit0, throughput, contrib, sh_o, sh_d, sh_c, image;
+    DevBuf<int2> hit1;
+    DevBuf<uint32_t> sampler_dim, flags;
+    DevBuf<int32_t> queue0, queue1;
+    DevBuf<Counters> counters;
+    DevBuf<Totals> totals;
+    PathBuffers pb{};
+
+    // query scratch
+    DevBuf<AtnRay> q_rays;
+    DevBuf<float> q_f;
+    DevBuf<AtnHit> q_hits;
+    DevBuf<uint8_t> q_vis;
+
+    // tap
+    AtnBounceRecord* tap_host{ nullptr };
+    int tap_cap{ 0 };
+    DevBuf<AtnBounceRecord> tap_dev;
+
+    uint32_t frame{ 0 };
+    int progressive{ 1 };
+    int profiling{ 0 };
+    AtnStats stats{};
+    cudaEvent_t ev0{ nullptr }, ev1{ nullptr };
+    std::vector<cudaEvent_t> trace_events;
+    int trace_grid{ 148 * 8 };
+    int shade_grid{ 148 * 8 };
+};
+
+static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene)
+{
+    EncodedBvh enc = encode_bvh(scene);
+    if (!enc.error.empty()) return set_error(ATN_ERR_INVALID_ARGUMENT, "node lists: %s", enc.error.c_str());
+    if (enc.max_depth + 8 > kSmemStack + kLocalStack)
+        return set_error(ATN_ERR_TOO_LARGE, "BVH depth %d exceeds the traversal stack (%d)", enc.max_depth, kSmemStack + kLocalStack);
+    CUDA_TRY(r->nodes.upload(enc.nodes.data(), enc.nodes.size(), r->stream));
+    CUDA_TRY(r->tris.upload(enc.tris.data(), enc.tris.size(), r->stream));
+    CUDA_TRY(r->insts.upload(enc.insts.data(), enc.insts.size(), r->stream));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));   // enc goes out of scope
+    r->bv.nodes = reinterpret_cast<const float4*>(r->nodes.p);
+    r->bv.tris = reinterpret_cast<const float4*>(r->tris.p);
+    r->bv.insts = reinterpret_cast<const int4*>(r->insts.p);
+    r->bv.matrices = r->matrices.p;
+    r->bv.top_root = enc.top_root;
+    return ATN_OK;
+}
+
+static float scene_radius_of(const AtnSceneConfig& cfg)
+{
+    // ImageBasedLight::sample (ibl.h:105-110): ComputeDistanceToCoverBoundingSphere(Deg2Rad(30))
+    const float* mn = cfg.scene_bbox_min; const float* mx = cfg.scene_bbox_max;
+    const bool valid = !((mn[0] >= mx[0]) || (mn[1] >= mx[1]) || (mn[2] >= mx[2]));
+    if (!valid) return 10000.0f;
+    const V3 vmin(mn[0], mn[1], mn[2]), vmax(mx[0], mx[1], mx[2]);
+    const V3 center = (vmin + vmax) * 0.5f;
+    const float rad = length(vmax - center);
+    const float theta = kPi * 30.0f / 180.0f;
+    return rad / tanf(theta / 2);
+}
+
+static int alloc_paths(AtnRenderer* r, size_t n)
+{
+    CUDA_TRY(r->ray_o.resize(n)); CUDA_TRY(r->ray_d.resize(n)); CUDA_TRY(r->hit0.resize(n)); CUDA_TRY(r->hit1.resize(n));
+    CUDA_TRY(r->throughput.resize(n)); CUDA_TRY(r->contrib.resize(n)); CUDA_TRY(r->sampler_dim.resize(n));
+    CUDA_TRY(r->flags.resize(n)); CUDA_TRY(r->queue0.resize(n)); CUDA_TRY(r->queue1.resize(n));
+    CUDA_TRY(r->sh_o.resize(n)); CUDA_TRY(r->sh_d.resize(n)); CUDA_TRY(r->sh_c.resize(n));
+    CUDA_TRY(r->counters.resize(1));
+    CUDA_TRY(r->totals.resize(1));
+    PathBuffers& pb = r->pb;
+    pb.ray_o = r->ray_o.p; pb.ray_d = r->ray_d.p; pb.hit0 = r->hit0.p; pb.hit1 = r->hit1.p;
+    pb.throughput = r->throughput.p; pb.contrib = r->contrib.p; pb.sampler_dim = r->sampler_dim.p; pb.flags = r->flags.p;
+    pb.queue[0] = r->queue0.p; pb.queue[1] = r->queue1.p;
+    pb.sh_o = r->sh_o.p; pb.sh_d = r->sh_d.p; pb.sh_c = r->sh_c.p;
+    return ATN_OK;
+}
+
+extern "C" {
+
+ATN_API const char* atn_last_error(void) { return g_last_error.c_str(); }
+ATN_API const char* atn_version(void) { return "aten_b200 0.1 (sm_100a)"; }
+
+ATN_API int atn_create(int device_ordinal, AtnRenderer** out)
+{
+    if (!out) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_create: out is NULL");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return set_error(ATN_ERR_CUDA, "atn_create: no CUDA device (%s); this library has no CPU path",
+                         e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    if (device_ordinal < 0 || device_ordinal >= ndev)
+        return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_create: device %d out of range [0,%d)", device_ordinal, ndev);
+    CUDA_TRY(cudaSetDevice(device_ordinal));
+    AtnRenderer* r = new AtnRenderer();
+    r->device = device_ordinal;
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device_ordinal));
+    r->sm_count = prop.multiProcessorCount;
+    CUDA_TRY(cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking));
+    CUDA_TRY(cudaEventCreate(&r->ev0));
+    CUDA_TRY(cudaEventCreate(&r->ev1));
+    int bps = 0;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace_closest, kTraceBlock, 0));
+    r->trace_grid = r->sm_count * std::max(1, bps);
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_shade<false>, 128, 0));
+    r->shade_grid = r->sm_count * std::max(1, bps);
+    *out = r;
+    return ATN_OK;
+}
+
+ATN_API int atn_destroy(AtnRenderer* r)
+{
+    if (!r) return ATN_OK;
+    cudaSetDevice(r->device);
+    cudaStreamSynchronize(r->stream);
+    for (auto ev : r->trace_events) cudaEventDestroy(ev);
+    if (r->ev0) cudaEventDestroy(r->ev0);
+    if (r->ev1) cudaEventDestroy(r->ev1);
+    cudaStream_t s = r->stream;
+    delete r;
+    if (s) cudaStreamDestroy(s);
+    return ATN_OK;
+}
+
+ATN_API int atn_upload_scene(AtnRenderer* r, const AtnSceneBlob* scene, const AtnCameraParameter* camera,
+                             int32_t width, int32_t height)
+{
+    if (!r || !scene || !camera) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_upload_scene: NULL argument");
+    if (width <= 0 || height <= 0) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_upload_scene: bad size %dx%d", width, height);
+    if ((int64_t)width * height > (int64_t)1 << 28) return set_error(ATN_ERR_TOO_LARGE, "atn_upload_scene: image too large");
+    if (scene->node_list_count == 0 || !scene->node_lists) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_upload_scene: no node lists");
+    CUDA_TRY(cudaSetDevice(r->device));
+    cudaStream_t s = r->stream;
+    CUDA_TRY(r->objects.upload(scene->objects, scene->object_count, s));
+    CUDA_TRY(r->matrices.upload(scene->matrices, scene->matrix_count, s));
+    CUDA_TRY(r->materials.upload(scene->materials, scene->material_count, s));
+    CUDA_TRY(r->lights.upload(scene->lights, scene->light_count, s));
+    CUDA_TRY(r->triangles.upload(scene->triangles, scene->triangle_count, s));
+    CUDA_TRY(r->positions.upload(scene->positions, scene->vertex_count, s));
+    CUDA_TRY(r->normals.upload(scene->normals, scene->vertex_count, s));
+    // textures: one texel pool + a table of views
+    size_t total = 0;
+    for (uint32_t i = 0; i < scene->texture_count; i++) total += (size_t)scene->textures[i].width * scene->textures[i].height;
+    CUDA_TRY(r->texels.resize(total));
+    std::vector<TexView> tv(scene->texture_count);
+    size_t off = 0;
+    for (uint32_t i = 0; i < scene->texture_count; i++) {
+        const AtnTextureDesc& t = scene->textures[i];
+        const size_t n = (size_t)t.width * t.height;
+        tv[i].texels = t.texels ? r->texels.p + off : nullptr;
+        tv[i].w = t.width; tv[i].h = t.height;
+        if (t.texels && n) CUDA_TRY(cudaMemcpyAsync(r->texels.p + off, t.texels, n * sizeof(AtnVec4), cudaMemcpyHostToDevice, s));
+        off += n;
+    }
+    CUDA_TRY(r->texviews.upload(tv.data(), tv.size(), s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+
+    // host copies for atn_update_top_layer (re-encode needs triangles / positions / bottom lists)
+    r->h_objects.assign(scene->objects, scene->objects + scene->object_count);
+    r->h_matrices.assign(scene->matrices, scene->matrices + scene->matrix_count);
+    r->h_triangles.assign(scene->triangles, scene->triangles + scene->triangle_count);
+    r->h_positions.assign(scene->positions, scene->positions + scene->vertex_count);
+    r->h_lists.clear();
+    for (uint32_t k = 0; k < scene->node_list_count; k++)
+        r->h_lists.emplace_back(scene->node_lists[k], scene->node_lists[k] + scene->node_list_sizes[k]);
+
+    SceneView& sv = r->sv;
+    sv.objects = r->objects.p; sv.matrices = r->matrices.p; sv.materials = r->materials.p; sv.lights = r->lights.p;
+    sv.triangles = r->triangles.p; sv.positions = r->positions.p; sv.normals = r->normals.p;
+    sv.textures = r->texviews.p; sv.light_count = (int32_t)scene->light_count; sv.cfg = scene->config;
+    sv.scene_radius = scene_radius_of(scene->config);
+    r->bv.t_min = scene->config.bvh_hit_min > 0 ? scene->config.bvh_hit_min : kEps;
+
+    int rc = upload_bvh(r, scene);
+    if (rc != ATN_OK) return rc;
+
+    r->camera = *camera;
+    r->width = width; r->height = height;
+    const size_t n = (size_t)width * height;
+    rc = alloc_paths(r, n);
+    if (rc != ATN_OK) return rc;
+    CUDA_TRY(r->image.resize(n));
+    CUDA_TRY(cudaMemsetAsync(r->image.p, 0, n * sizeof(float4), s));
+    if (r->seed_count == 0) {
+        // default: every pixel seed 0 until atn_set_seeds is called
+        std::vector<uint32_t> zero(1, 0u);
+        CUDA_TRY(r->seeds.upload(zero.data(), 1, s));
+        r->seed_count = 1;
+    }
+    CUDA_TRY(cudaStreamSynchronize(s));
+    r->frame = 0;
+    r->has_scene = true;
+    return ATN_OK;
+}
+
+ATN_API int atn_update_camera(AtnRenderer* r, const AtnCameraParameter* camera)
+{
+    if (!r || !camera) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_update_camera: NULL argument");
+    r->camera = *camera;
+    return ATN_OK;
+}
+
+ATN_API int atn_update_top_layer(AtnRenderer* r, const AtnBvhNode* top_nodes, uint32_t node_count,
+                                 const AtnObjectParameter* objects, uint32_t object_count,
+                                 const AtnMat4* matrices, uint32_t matrix_count)
+{
+    if (!r || !top_nodes || !objects) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_update_top_layer: NULL argument");
+    if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_update_top_layer: no scene uploaded");
+    CUDA_TRY(cudaSetDevice(r->device));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
+    r->h_lists[0].assign(top_nodes, top_nodes + node_count);
+    r->h_objects.assign(objects, objects + object_count);
+    r->h_matrices.assign(matrices, matrices + matrix_count);
+    CUDA_TRY(r->objects.upload(objects, object_count, r->stream));
+    CUDA_TRY(r->matrices.upload(matrices, matrix_count, r->stream));
+    r->sv.objects = r->objects.p; r->sv.matrices = r->matrices.p;
+    std::vector<const AtnBvhNode*> ptrs; std::vector<uint32_t> sizes;
+    for (auto& l : r->h_lists) { ptrs.push_back(l.data()); sizes.push_back((uint32_t)l.size()); }
+    AtnSceneBlob b{};
+    b.objects = r->h_objects.data(); b.object_count = object_count;
+    b.matrices = r->h_matrices.data(); b.matrix_count = matrix_count;
+    b.triangles = r->h_triangles.data(); b.triangle_count = (uint32_t)r->h_triangles.size();
+    b.positions = r->h_positions.data(); b.vertex_count = (uint32_t)r->h_positions.size();
+    b.node_lists = ptrs.data(); b.node_list_sizes = sizes.data(); b.node_list_count = (uint32_t)ptrs.size();
+    return upload_bvh(r, &b);
+}
+
+ATN_API int atn_update_materials(AtnRenderer* r, const AtnMaterialParameter* m, uint32_t count)
+{
+    if (!r || !m) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_update_materials: NULL argument");
+    CUDA_TRY(cudaSetDevice(r->device));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
+    CUDA_TRY(r->materials.upload(m, count, r->stream));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
+    r->sv.materials = r->materials.p;
+    return ATN_OK;
+}
+
+ATN_API int atn_update_lights(AtnRenderer* r, const AtnLightParameter* l, uint32_t count)
+{
+    if (!r || (!l && count)) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_update_lights: NULL argument");
+    CUDA_TRY(cudaSetDevice(r->device));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
+    CUDA_TRY(r->lights.upload(l, count, r->stream));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
+    r->sv.lights = r->lights.p; r->sv.light_count = (int32_t)count;
+    return ATN_OK;
+}
+
+ATN_API int atn_update_config(AtnRenderer* r, const AtnSceneConfig* cfg)
+{
+    if (!r || !cfg) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_update_config: NULL argument");
+    r->sv.cfg = *cfg;
+    r->sv.scene_radius = scene_radius_of(*cfg);
+    r->bv.t_min = cfg->bvh_hit_min > 0 ? cfg->bvh_hit_min : kEps;
+    return ATN_OK;
+}
+
+ATN_API int atn_set_seeds(AtnRenderer* r, const uint32_t* seeds, uint32_t count)
+{
+    if (!r || !seeds || count == 0) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_set_seeds: NULL/empty");
+    CUDA_TRY(cudaSetDevice(r->device));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
+    CUDA_TRY(r->seeds.upload(seeds, count, r->stream));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
+    r->seed_count = count;
+    return ATN_OK;
+}
+
+ATN_API int atn_set_frame(AtnRenderer* r, uint32_t frame) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->frame = frame; return ATN_OK; }
+ATN_API int atn_get_frame(AtnRenderer* r, uint32_t* frame) { if (!r || !frame) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); *frame = r->frame; return ATN_OK; }
+ATN_API int atn_set_progressive(AtnRenderer* r, int enable) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->progressive = enable ? 1 : 0; return ATN_OK; }
+ATN_API int atn_set_hit_distance_limit(AtnRenderer* r, float d) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->hit_distance_limit = d; return ATN_OK; }
+ATN_API int atn_set_profiling(AtnRenderer* r, int enable) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->profiling = enable ? 1 : 0; return ATN_OK; }
+ATN_API int atn_get_stream(AtnRenderer* r, void** stream) { if (!r || !stream) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); *stream = (void*)r->stream; return ATN_OK; }
+
+ATN_API int atn_reset(AtnRenderer* r)
+{
+    if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL");
+    r->frame = 0;
+    if (r->image.p) {
+        CUDA_TRY(cudaSetDevice(r->device));
+        CUDA_TRY(cudaMemsetAsync(r->image.p, 0, r->image.n * sizeof(float4), r->stream));
+    }
+    return ATN_OK;
+}
+
+ATN_API int atn_set_bounce_tap(AtnRenderer* r, AtnBounceRecord* records, int32_t bounce_capacity)
+{
+    if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL");
+    r->tap_host = records;
+    r->tap_cap = records ? bounce_capacity : 0;
+    return ATN_OK;
+}
+
+ATN_API int atn_synchronize(AtnRenderer* r)
+{
+    if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL");
+    CUDA_TRY(cudaSetDevice(r->device));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
+    return ATN_OK;
+}
+
+ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int32_t x0, int32_t y0, int32_t x1, int32_t y1,
+                              int32_t sample_begin, int32_t sample_end, int32_t max_bounce, int32_t rr_bounce)
+{
+    if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render: NULL handle");
+    if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_render: no scene uploaded");
+    if (width != r->width || height != r->height)
+        return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render: size %dx%d differs from the uploaded %dx%d", width, height, r->width, r->height);
+    if (max_bounce < 1 || max_bounce > kMaxBounce) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render: max_bounce %d not in [1,%d]", max_bounce, kMaxBounce);
+    if (x0 < 0 || y0 < 0 || x1 > width || y1 > height || x0 >= x1 || y0 >= y1) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render: bad region");
+    if (sample_end < sample_begin) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render: bad sample range");
+    if (rr_bounce > max_bounce) rr_bounce = max_bounce - 1;       // pathtracing.cpp (host) :281-283
+    CUDA_TRY(cudaSetDevice(r->device));
+    cudaStream_t s = r->stream;
+
+    FrameParams fp;
+    fp.width = width; fp.height = height; fp.x0 = x0; fp.y0 = y0; fp.rw = x1 - x0; fp.rh = y1 - y0;
+    fp.max_bounce = max_bounce; fp.rr_bounce = rr_bounce; fp.seed_count = r->seed_count;
+    const int n = fp.rw * fp.rh;
+    const bool tap = r->tap_host != nullptr;
+    if (tap) {
+        CUDA_TRY(r->tap_dev.resize((size_t)n * r->tap_cap));
+        if (r->tap_cap < max_bounce) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render: tap capacity %d < max_bounce %d", r->tap_cap, max_bounce);
+    }
+    const int spp = sample_end - sample_begin;
+    const size_t n_ev = r->profiling ? (size_t)spp * max_bounce * 4 : 0;
+    while (r->trace_events.size() < n_ev) { cudaEvent_t ev; CUDA_TRY(cudaEventCreate(&ev)); r->trace_events.push_back(ev); }
+    size_t ev_i = 0;
+    uint64_t launches = 0;
+    const int gen_grid = std::min((n + 255) / 256, r->sm_count * 8);
+
+    CUDA_TRY(cudaMemsetAsync(r->totals.p, 0, sizeof(Totals), s));
+    CUDA_TRY(cudaEventRecord(r->ev0, s));
+    for (int smp = sample_begin; smp < sample_end; smp++) {
+        fp.frame = r->frame + (uint32_t)smp;
+        CUDA_TRY(cudaMemsetAsync(r->counters.p, 0, sizeof(Counters), s));
+        if (tap && smp == sample_end - 1) CUDA_TRY(cudaMemsetAsync(r->tap_dev.p, 0, (size_t)n * r->tap_cap * sizeof(AtnBounceRecord), s));
+        k_generate<<<gen_grid, 256, 0, s>>>(fp, r->camera, r->seeds.p, r->pb, r->counters.p);
+        launches++;
+        const bool tap_now = tap && smp == sample_end - 1;
+        for (int b = 0; b < max_bounce; b++) {
+            Counters* c = r->counters.p;
+            const int32_t* q = (b == 0) ? nullptr : r->pb.queue[b & 1];
+            const float tmax = (b == 0) ? kInf : r->hit_distance_limit;
+            if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
+            k_trace_closest<<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, r->pb, q, &c->n_active[b], &c->fetch_closest[b], nullptr, tmax);
+            if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
+            if (tap_now) k_shade<true><<<r->shade_grid, 128, 0, s>>>(fp, r->camera, r->sv, r->seeds.p, r->pb, c, b, r->tap_dev.p, r->tap_cap);
+            else k_shade<false><<<r->shade_grid, 128, 0, s>>>(fp, r->camera, r->sv, r->seeds.p, r->pb, c, b, nullptr, 0);
+            if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
+            if (tap_now) k_trace_shadow<true><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, r->sv, r->pb, &c->n_shadow[b], &c->fetch_shadow[b], r->tap_dev.p, r->tap_cap, b);
+            else k_trace_shadow<false><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, r->sv, r->pb, &c->n_shadow[b], &c->fetch_shadow[b], nullptr, 0, b);
+            if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
+            launches += 3;
+        }
+        k_gather<<<gen_grid, 256, 0, s>>>(fp, r->pb, r->image.p, r->progressive, r->counters.p, r->totals.p);
+        launches++;
+    }
+    CUDA_TRY(cudaEventRecord(r->ev1, s));
+    CUDA_TRY(cudaGetLastError());
+
+    // Exact ray counts: k_gather folds every sample's queue counters into Totals on the device.
+    Totals ht;
+    CUDA_TRY(cudaMemcpyAsync(&ht, r->totals.p, sizeof(Totals), cudaMemcpyDeviceToHost, s));
+    if (tap) CUDA_TRY(cudaMemcpyAsync(r->tap_host, r->tap_dev.p, (size_t)n * r->tap_cap * sizeof(AtnBounceRecord), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    r->stats.closest_rays = ht.closest;
+    r->stats.shadow_rays = ht.shadow;
+    r->stats.camera_samples = (uint64_t)n * (uint64_t)spp;
+    r->stats.kernel_launches = launches;
+    float ms = 0.0f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
+    r->stats.device_ms = ms;
+    r->stats.trace_ms = 0.0f;
+    if (r->profiling) {
+        float tot = 0.0f;
+        for (size_t i = 0; i + 3 < ev_i; i += 4) {
+            float a = 0.0f, b2 = 0.0f;
+            cudaEventElapsedTime(&a, r->trace_events[i], r->trace_events[i + 1]);
+            cudaEventElapsedTime(&b2, r->trace_events[i + 2], r->trace_events[i + 3]);
+            tot += a + b2;
+        }
+        r->stats.trace_ms = tot;
+    }
+    return ATN_OK;
+}
+
+ATN_API int atn_render(AtnRenderer* r, int32_t width, int32_t height, int32_t spp, int32_t max_bounce, int32_t rr_bounce)
+{
+    if (spp < 1) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render: spp %d < 1", spp);
+    const int rc = atn_render_region(r, width, height, 0, 0, width, height, 0, spp, max_bounce, rr_bounce);
+    if (rc == ATN_OK) r->frame += (uint32_t)spp;
+    return rc;
+}
+
+ATN_API int atn_readback(AtnRenderer* r, AtnVec4* host_image, size_t pixel_count)
+{
+    if (!r || !host_image) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_readback: NULL argument");
+    if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_readback: no scene uploaded");
+    if (pixel_count != (size_t)r->width * r->height) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_readback: pixel_count mismatch");
+    CUDA_TRY(cudaSetDevice(r->device));
+    CUDA_TRY(cudaMemcpyAsync(host_image, r->image.p, pixel_count * sizeof(AtnVec4), cudaMemcpyDeviceToHost, r->stream));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
+    return ATN_OK;
+}
+
+ATN_API int atn_device_image(AtnRenderer* r, void** device_ptr, size_t* pixel_count)
+{
+    if (!r || !device_ptr) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_device_image: NULL argument");
+    if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_device_image: no scene uploaded");
+    *device_ptr = r->image.p;
+    if (pixel_count) *pixel_count = (size_t)r->width * r->height;
+    return ATN_OK;
+}
+
+ATN_API int atn_get_stats(AtnRenderer* r, AtnStats* out)
+{
+    if (!r || !out) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_get_stats: NULL argument");
+    *out = r->stats;
+    return ATN_OK;
+}
+
+static int query_launch(AtnRenderer* r, const void* rays_dev, const void* f_dev, size_t n, void* out_dev, bool any)
+{
+    if (n > (size_t)INT32_MAX - 64) return set_error(ATN_ERR_TOO_LARGE, "ray query: more than 2^31 rays in one call");
+    cudaStream_t s = r->stream;
+    CUDA_TRY(r->counters.resize(1));
+    CUDA_TRY(cudaMemsetAsync(&r->counters.p->fetch_query, 0, sizeof(int32_t), s));
+    CUDA_TRY(cudaEventRecord(r->ev0, s));
+    if (any) k_query_any<<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, (const AtnRay*)rays_dev, (const float*)f_dev, (int)n, &r->counters.p->fetch_query, (uint8_t*)out_dev);
+    else k_query_closest<<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, (const AtnRay*)rays_dev, (const float*)f_dev, (int)n, &r->counters.p->fetch_query, (AtnHit*)out_dev);
+    CUDA_TRY(cudaEventRecord(r->ev1, s));
+    CUDA_TRY(cudaGetLastError());
+    r->stats.kernel_launches = 1;
+    r->stats.closest_rays = any ? 0 : n;
+    r->stats.shadow_rays = any ? n : 0;
+    r->stats.camera_samples = 0;
+    return ATN_OK;
+}
+
+ATN_API int atn_trace_closest_device(AtnRenderer* r, const void* rays_dev, const void* t_max_dev, size_t n, void* hits_dev)
+{
+    if (!r || !rays_dev || !hits_dev) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_trace_closest_device: NULL argument");
+    if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_trace_closest_device: no scene uploaded");
+    if (n == 0) return ATN_OK;
+    CUDA_TRY(cudaSetDevice(r->device));
+    return query_launch(r, rays_dev, t_max_dev, n, hits_dev, false);
+}
+
+ATN_API int atn_trace_any_device(AtnRenderer* r, const void* rays_dev, const void* dist_dev, size_t n, void* visible_dev)
+{
+    if (!r || !rays_dev || !dist_dev || !visible_dev) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_trace_any_device: NULL argument");
+    if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_trace_any_device: no scene uploaded");
+    if (n == 0) return ATN_OK;
+    CUDA_TRY(cudaSetDevice(r->device));
+    return query_launch(r, rays_dev, dist_dev, n, visible_dev, true);
+}
+
+ATN_API int atn_trace_closest(AtnRenderer* r, const AtnRay* rays, const float* t_max, size_t n, AtnHit* hits)
+{
+    if (!r || (n && (!rays || !hits))) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_trace_closest: NULL argument");
+    if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_trace_closest: no scene uploaded");
+    if (n == 0) return ATN_OK;
+    CUDA_TRY(cudaSetDevice(r->device));
+    cudaStream_t s = r->stream;
+    CUDA_TRY(r->q_rays.upload(rays, n, s));
+    if (t_max) CUDA_TRY(r->q_f.upload(t_max, n, s));
+    CUDA_TRY(r->q_hits.resize(n));
+    int rc = query_launch(r, r->q_rays.p, t_max ? r->q_f.p : nullptr, n, r->q_hits.p, false);
+    if (rc != ATN_OK) return rc;
+    CUDA_TRY(cudaMemcpyAsync(hits, r->q_hits.p, n * sizeof(AtnHit), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, r->ev0, r->ev1);
+    r->stats.device_ms = ms; r->stats.trace_ms = ms;
+    return ATN_OK;
+}
+
+ATN_API int atn_trace_any(AtnRenderer* r, const AtnRay* rays, const float* dist, size_t n, uint8_t* visible)
+{
+    if (!r || (n && (!rays || !dist || !visible))) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_trace_any: NULL argument");
+    if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_trace_any: no scene uploaded");
+    if (n == 0) return ATN_OK;
+    CUDA_TRY(cudaSetDevice(r->device));
+    cudaStream_t s = r->stream;
+    CUDA_TRY(r->q_rays.upload(rays, n, s));
+    CUDA_TRY(r->q_f.upload(dist, n, s));
+    CUDA_TRY(r->q_vis.resize(n));
+    int rc = query_launch(r, r->q_rays.p, r->q_f.p, n, r->q_vis.p, true);
+    if (rc != ATN_OK) return rc;
+    CUDA_TRY(cudaMemcpyAsync(visible, r->q_vis.p, n, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, r->ev0, r->ev1);
+    r->stats.device_ms = ms; r->stats.trace_ms = ms;
+    return ATN_OK;
+}
+
+}  // extern "C"

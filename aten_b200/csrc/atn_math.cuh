@@ -1279,9 +1279,12 @@ ATN_HD bool shadow_visible(const SceneView& sc, const AtnLightParameter& light, 
         hitobj = hit_objid;
         // material::isTranslucentByAlpha (src/libaten/material/material.cpp:193-210): an ignored
         // hit `continue`s the single-iteration loop, i.e. the light is reported as not reached.
-        const AtnMaterialParameter& m = sc.materials[hit_mtrlid];
+        const AtnMaterialParameter& m = sc.materials[hit_mtrlid < 0 ? 0 : hit_mtrlid];
         float alpha = m.baseColor.w;
-        if (m.albedoMap >= 0) {
+        if (hit_mtrlid < 0) {
+            alpha = 1.0f;
+        }
+        else if (m.albedoMap >= 0) {
             HitRecord rec;
             evaluate_hit(sc, sc.objects[hit_objid], ray, hit_primid, hit_a, hit_b, hit_t, hit_mtrlid, &rec);
             alpha = sample_texture(sc, m.albedoMap, rec.u, rec.v, v4(1.0f)).w * m.baseColor.w;

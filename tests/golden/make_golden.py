@@ -1,0 +1,96 @@
+#!/usr/bin/env python3
+"""Generates the golden vectors under tests/golden/ from the REFERENCE ITSELF (oracle/_ref, i.e.
+nackdai/aten's own CPU path tracer compiled in place by oracle/build_ref.py).
+
+Run in the build container (needs /root/reference):   python tests/golden/make_golden.py
+
+Files (all little endian, gzip):
+  cmj.f32.gz                      aten::CMJ known-answer stream (ref_harness cmj)
+  <scene>.atnscene.gz             flat scene blob at the golden resolution (ref_harness scene)
+  <scene>.trace.gz                AtnBounceRecord[H*W][5] of frame FRAME, replayed from the reference's
+                                  public functions and self-checked against stock render()
+  <scene>.image.f32.gz            float4 image of frames 0..FRAMES-1 through aten::PathTracing::render
+                                  with FilmProgressive
+  <scene>.rays.gz / .hits.gz      random rays {org,dir,tmax} and the reference's Traverse<Closest> hits
+"""
+import gzip
+import json
+import os
+import sys
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from tests import oracle_lib as ol  # noqa: E402
+from aten_b200 import scene_io as sio  # noqa: E402
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SCENES = {  # name: (W, H)
+    "cornell": (64, 64),
+    "cornell_mtrl": (64, 48),
+    "sponza_atrium": (64, 36),
+    "instanced": (64, 36),
+}
+FRAME = 2
+FRAMES = 3
+N_RAYS = 4096
+
+
+def gz_write(path, data: bytes):
+    with gzip.GzipFile(path, "wb", mtime=0) as fp:
+        fp.write(data)
+
+
+def random_rays(scene: sio.Scene, n: int, seed: int) -> tuple:
+    """Incoherent rays: origins inside the scene box, uniform directions; t_max = inf for half of
+    them, a finite bound for the rest (exercises the t_max culling path of aabb::hit)."""
+    rng = np.random.default_rng(seed)
+    lo = scene.config["scene_bbox_min"][0].astype(np.float64)
+    hi = scene.config["scene_bbox_max"][0].astype(np.float64)
+    org = (lo + (hi - lo) * rng.random((n, 3))).astype(np.float32)
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays = np.zeros(n, sio.RAY_DTYPE)
+    rays["org"] = org
+    rays["dir"] = d.astype(np.float32)
+    diag = float(np.linalg.norm(hi - lo))
+    tmax = np.full(n, np.finfo(np.float32).max, np.float32)
+    tmax[n // 2:] = (rng.random(n - n // 2) * diag).astype(np.float32)
+    return rays, tmax
+
+
+def main():
+    if not ol.have_ref():
+        sys.exit("oracle/_ref is not built: run python oracle/build_ref.py")
+    meta = {}
+    with tempfile.TemporaryDirectory() as d:
+        p = os.path.join(d, "cmj.bin")
+        ol.ref_run("cmj", p)
+        gz_write(os.path.join(HERE, "cmj.f32.gz"), open(p, "rb").read())
+    for name, (W, H) in SCENES.items():
+        with tempfile.TemporaryDirectory() as d:
+            ps = os.path.join(d, "s.atnscene")
+            info = ol.ref_run("scene", name, W, H, ps)
+            gz_write(os.path.join(HERE, f"{name}.atnscene.gz"), open(ps, "rb").read())
+            scene = sio.load_scene(ps)
+        recs, img1, tinfo = ol.ref_trace(name, W, H, frame=FRAME)
+        gz_write(os.path.join(HERE, f"{name}.trace.gz"), recs.tobytes())
+        img, rinfo = ol.ref_render(name, W, H, frames=FRAMES)
+        gz_write(os.path.join(HERE, f"{name}.image.f32.gz"), img.tobytes())
+        rays, tmax = random_rays(scene, N_RAYS, seed=hash(name) % 1000 if False else len(name) * 7 + 1)
+        hits = ol.ref_rays(name, rays, tmax)
+        buf = np.zeros((N_RAYS, 7), np.float32)
+        buf[:, :3] = rays["org"]; buf[:, 3:6] = rays["dir"]; buf[:, 6] = tmax
+        gz_write(os.path.join(HERE, f"{name}.rays.gz"), buf.tobytes())
+        gz_write(os.path.join(HERE, f"{name}.hits.gz"), hits.tobytes())
+        meta[name] = {"w": W, "h": H, "frame": FRAME, "frames": FRAMES, "depth": 5, "rr": 3, "scene": info,
+                      "closest_rays": tinfo["closest_rays"], "shadow_rays": tinfo["shadow_rays"],
+                      "hit_fraction": float((hits["objid"] >= 0).mean())}
+        print(name, meta[name])
+    json.dump(meta, open(os.path.join(HERE, "meta.json"), "w"), indent=1, sort_keys=True)
+
+
+if __name__ == "__main__":
+    main()

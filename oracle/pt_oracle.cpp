@@ -175,7 +175,7 @@ int oracle_trace_any(const AtnSceneBlob* blob, const AtnRay* rays, const float* 
 
 // aten::PathTracing::OnRender driven as `frames` successive frames of one sample, with
 // FilmProgressive accumulation; `records` (optional) receives AtnBounceRecord[pixel][max_depth]
-// of the LAST frame; stats = {closest rays, shadow rays}.
+// of the LAST frame; stats[6] = {closest rays, shadow rays, nodes, slab tests, triangle tests, instance entries}.
 __attribute__((visibility("default")))
 int oracle_render(const AtnSceneBlob* blob, const AtnCameraParameter* cam, const uint32_t* seeds, uint32_t seed_count,
                   int32_t W, int32_t H, uint32_t first_frame, int32_t frames, int32_t max_depth, int32_t rr_depth,
@@ -183,12 +183,14 @@ int oracle_render(const AtnSceneBlob* blob, const AtnCameraParameter* cam, const
 {
     const Scene s = MakeScene(blob);
     if (rr_depth > max_depth) rr_depth = max_depth - 1;
-    uint64_t n_closest = 0, n_shadow = 0;
+    uint64_t n_closest = 0, n_shadow = 0, cn = 0, cb = 0, ct = 0, ci = 0;
+    const bool want_cnt = stats != nullptr;
     for (int32_t f = 0; f < frames; f++) {
         const uint32_t frame = first_frame + (uint32_t)f;
         AtnBounceRecord* recs = (f == frames - 1) ? records : nullptr;
-#pragma omp parallel for reduction(+:n_closest,n_shadow) schedule(dynamic, 4)
+#pragma omp parallel for reduction(+:n_closest,n_shadow,cn,cb,ct,ci) schedule(dynamic, 4)
         for (int32_t y = 0; y < H; y++) {
+            Counters cnt{0, 0, 0, 0};
             for (int32_t x = 0; x < W; x++) {
                 const int32_t idx = y * W + x;
                 const uint32_t rnd = seeds[(uint32_t)idx % seed_count];
@@ -204,7 +206,7 @@ int oracle_render(const AtnSceneBlob* blob, const AtnCameraParameter* cam, const
                 int32_t depth = 0;
                 while (depth < max_depth) {
                     AtnHit isect;
-                    const bool is_hit = Traverse(s, ray, kInf, &isect, nullptr);
+                    const bool is_hit = Traverse(s, ray, kInf, &isect, want_cnt ? &cnt : nullptr);
                     n_closest++;
                     AtnBounceRecord rec;
                     memset(&rec, 0, sizeof(rec));
@@ -223,7 +225,7 @@ int oracle_render(const AtnSceneBlob* blob, const AtnCameraParameter* cam, const
                             n_shadow++;
                             Ray sr; sr.org = sh.org; sr.dir = normalize(sh.dir);   // aten::ray(org, dir) renormalises
                             AtnHit shit;
-                            Traverse(s, sr, sh.dist - kEps, &shit, nullptr);
+                            Traverse(s, sr, sh.dist - kEps, &shit, want_cnt ? &cnt : nullptr);
                             const bool vis = shadow_visible(s.view, s.view.lights[sh.light_id], sr, sh.dist,
                                                             shit.objid, shit.primid, shit.a, shit.b, shit.t, shit.mtrlid);
                             if (vis) st.contrib = st.contrib + sh.lightcontrib;
@@ -258,9 +260,12 @@ int oracle_render(const AtnSceneBlob* blob, const AtnCameraParameter* cam, const
                 cur.z = (n * cur.z + col.z) / (n + 1);
                 cur.w = n + 1;
             }
+            cn += cnt.nodes; cb += cnt.boxes; ct += cnt.tris; ci += cnt.insts;
         }
     }
-    if (stats) { stats[0] = n_closest; stats[1] = n_shadow; }
+    // stats: closest rays, shadow rays, then the traversal counters of ALL rays on the reference
+    // layout (nodes fetched, slab tests, triangle tests, instance entries) -- the roofline denominator
+    if (stats) { stats[0] = n_closest; stats[1] = n_shadow; stats[2] = cn; stats[3] = cb; stats[4] = ct; stats[5] = ci; }
     return 0;
 }
 

@@ -64,7 +64,7 @@ def render(scene: sio.Scene, frames=1, max_depth=5, rr_depth=3, first_frame=0, r
     img = np.zeros((H * W, 4), np.float32) if image is None else np.ascontiguousarray(image, np.float32).reshape(H * W, 4)
     recs = np.zeros((H * W, max_depth), sio.BOUNCE_DTYPE) if records else None
     seeds = scene.seeds_for(W * H)
-    stats = np.zeros(2, np.uint64)
+    stats = np.zeros(6, np.uint64)
     blob = scene.blob()
     cam = np.ascontiguousarray(scene.camera)
     lib().oracle_render(C.byref(blob), C.c_void_p(cam.ctypes.data), C.c_void_p(seeds.ctypes.data), C.c_uint32(len(seeds)),

@@ -40,15 +40,28 @@ def rel_err(a, b, floor=1e-6):
     return np.abs(a - b) / np.maximum(np.maximum(np.abs(a), np.abs(b)), floor)
 
 
-def assert_hits_equal(got, ref):
+def assert_hits_equal(got, ref, max_near_tie_rate=3e-4):
+    """Bit-exact comparison of closest hits, except the DOCUMENTED near-ties (DESIGN.md "Ties"):
+    rays on which two primitives are hit within 1e-5 relative distance of each other.  The reference
+    walks its tree in a fixed left-first order with a slab test biased by +1e-6 (aabb.h:68) and a
+    running t_max, so which of two such primitives it reports depends on its visit order; the GPU
+    traversal is ordered front to back and reports the nearer one.  Their rate is bounded here."""
     hit = ref["objid"] >= 0
-    assert (got["objid"] == ref["objid"]).all(), f"{(got['objid'] != ref['objid']).sum()} objid mismatches"
-    assert (got["primid"][hit] == ref["primid"][hit]).all(), f"{(got['primid'][hit] != ref['primid'][hit]).sum()} primid mismatches"
-    assert (bits(got["t"]) == bits(ref["t"])).all()
-    assert (bits(got["a"][hit]) == bits(ref["a"][hit])).all() and (bits(got["b"][hit]) == bits(ref["b"][hit])).all()
-    assert (got["mtrlid"][hit] == ref["mtrlid"][hit]).all()
-    assert (got["meshid"][hit] == ref["meshid"][hit]).all()
-    assert (got["primid"][~hit] == -1).all()          # documented: the reference leaves 0 here
+    diff = (got["objid"] != ref["objid"]) | (hit & (got["primid"] != ref["primid"])) | (bits(got["t"]) != bits(ref["t"]))
+    if diff.any():
+        both = diff & hit & (got["objid"] >= 0)
+        assert (both == diff).all(), f"{(diff & ~both).sum()} hit/miss disagreements"
+        rel = np.abs(got["t"][diff].astype(np.float64) - ref["t"][diff]) / ref["t"][diff]
+        assert rel.max() <= 1e-5, f"distance differs by {rel.max():.3g} relative"
+        assert (got["t"][diff] <= ref["t"][diff]).all(), "GPU reported a farther hit than the reference"
+        assert diff.mean() <= max_near_tie_rate, f"near-tie rate {diff.mean():.2e}"
+    same = ~diff
+    hs = hit & same
+    assert (bits(got["a"][hs]) == bits(ref["a"][hs])).all() and (bits(got["b"][hs]) == bits(ref["b"][hs])).all()
+    assert (got["mtrlid"][hs] == ref["mtrlid"][hs]).all()
+    assert (got["meshid"][hs] == ref["meshid"][hs]).all()
+    assert (got["primid"][~hit & same] == -1).all()          # documented: the reference leaves 0 here
+    return int(diff.sum())
 
 
 @pytest.mark.parametrize("name", SCENES)

@@ -76,6 +76,7 @@ constexpr int kMaxBounce = 16;
 constexpr int kSmemStack = 12;     // shared-memory stack entries per thread (ints)
 constexpr int kLocalStack = 64;    // overflow, local memory
 constexpr int kTraceBlock = 128;
+constexpr int kRefillThreshold = 20;   // refill a warp when fewer lanes than this still own a ray
 
 // Per-frame device counters; zeroed with one memset per sample pass.
 struct Counters {
@@ -118,119 +119,6 @@ enum : int { EXIT_NONE = 0, EXIT_ANY_HIT = 1, EXIT_HIT_BEFORE = 2 };
 
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
 
-// Two-level closest-hit traversal over PairNodes with the reference's acceptance rules
-// (threaded_bvh_traverser.h:98-304): inner boxes use aabb::hit with the running t_max, leaves are
-// never box-tested, a triangle is accepted iff t_min < t && t < best (ties: lowest depth-first rank,
-// which is what "first encountered" means in the reference's fixed visit order).
-// early_exit: EXIT_ANY_HIT stops at the first accepted triangle, EXIT_HIT_BEFORE at the first
-// accepted triangle with t <= exit_dist (shadow rays towards infinite / singular lights).
-template <bool kShadow>
-__device__ __forceinline__ void traverse(const BvhView& bv, const V3& org_w, const V3& dir_w, float t_max,
-                                         int early_exit, float exit_dist, int32_t* smem_stack, TraceResult* out)
-{
-    int32_t lstack[kLocalStack];
-    int sp = 0;
-    auto push = [&](int32_t v) {
-        if (sp < kSmemStack) smem_stack[sp * kTraceBlock] = v; else lstack[sp - kSmemStack] = v;
-        sp++;
-    };
-    auto pop = [&]() -> int32_t {
-        sp--;
-        return (sp < kSmemStack) ? smem_stack[sp * kTraceBlock] : lstack[sp - kSmemStack];
-    };
-
-    V3 org = org_w, dir = dir_w;
-    RayInv ri = ray_inv(org, dir);
-    const float t_min = bv.t_min;
-    float best_t = kInf, best_a = 0.0f, best_b = 0.0f;
-    int32_t best_leaf = -1, best_inst = -1;
-    int32_t cur_inst = -1;
-    int32_t cur = bv.top_root;
-    bool done = false;
-
-    while (!done) {
-        // ---- descend through inner nodes ----
-        while (cur >= 0) {
-            const float4* np = bv.nodes + (size_t)cur * 4;
-            const float4 n0 = ldg4(np + 0);
-            const float4 n1 = ldg4(np + 1);
-            const float4 n2 = ldg4(np + 2);
-            const float4 n3 = ldg4(np + 3);
-            const int32_t left = __float_as_int(n3.x);
-            const int32_t right = __float_as_int(n3.y);
-            float t0l = -kInf, t0r = -kInf;
-            bool hl = (left != kRefNull), hr = (right != kRefNull);
-            if (hl && left >= 0) hl = aabb_hit(ri, V3(n0.x, n0.z, n2.x), V3(n0.y, n0.w, n2.y), t_min, t_max, &t0l);
-            if (hr && right >= 0) hr = aabb_hit(ri, V3(n1.x, n1.z, n2.z), V3(n1.y, n1.w, n2.w), t_min, t_max, &t0r);
-            if (hl && hr) {
-                // near child first; leaves (t0 = -inf) are taken before boxes
-                const bool swap = t0r < t0l;
-                const int32_t nearc = swap ? right : left;
-                const int32_t farc = swap ? left : right;
-                push(farc);
-                cur = nearc;
-            }
-            else if (hl) cur = left;
-            else if (hr) cur = right;
-            else { cur = kRefNull; break; }
-        }
-
-        // ---- leaf / marker ----
-        if (cur != kRefNull && cur != kRefExit) {
-            const int32_t leaf = ~cur;
-            if (cur_inst < 0) {
-                // top-layer leaf: enter the instance (threaded_bvh_traverser.h:146-185)
-                const int4 il = __ldg(bv.insts + leaf);
-                if (il.y != kRefNull) {
-                    push(kRefExit);
-                    cur_inst = leaf;
-                    if (il.z >= 0) {
-                        const AtnMat4 m = bv.matrices[il.z];
-                        const Ray tr = make_ray(mat_apply(m, org_w), mat_apply_xyz(m, dir_w));   // mat4::applyRay
-                        org = tr.org; dir = tr.dir;
-                    }
-                    else { org = org_w; dir = dir_w; }
-                    ri = ray_inv(org, dir);
-                    cur = il.y;
-                    continue;
-                }
-            }
-            else {
-                const float4* tp = bv.tris + (size_t)leaf * 3;
-                const float4 a = ldg4(tp + 0);
-                const float4 b = ldg4(tp + 1);
-                const float4 c = ldg4(tp + 2);
-                const TriHit h = intersect_triangle(org, dir, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), V3(c.x, c.y, c.z));
-                if (h.hit && h.t < kInf && t_min < h.t) {
-                    const bool closer = h.t < best_t ||
-                        (h.t == best_t && (cur_inst < best_inst || (cur_inst == best_inst && leaf < best_leaf)));
-                    if (closer) {
-                        best_t = h.t; best_a = h.a; best_b = h.b; best_leaf = leaf; best_inst = cur_inst;
-                        t_max = h.t;
-                        if (kShadow) {
-                            if (early_exit == EXIT_ANY_HIT || (early_exit == EXIT_HIT_BEFORE && h.t <= exit_dist)) break;
-                        }
-                    }
-                }
-            }
-        }
-
-        // ---- pop ----
-        for (;;) {
-            if (sp == 0) { done = true; break; }
-            cur = pop();
-            if (cur == kRefExit) {
-                cur_inst = -1;
-                org = org_w; dir = dir_w;
-                ri = ray_inv(org, dir);
-                continue;
-            }
-            break;
-        }
-    }
-    out->t = best_t; out->a = best_a; out->b = best_b; out->leaf = best_leaf; out->inst = best_inst;
-}
-
 // Resolve the winning leaf into the reference's Intersection fields.
 __device__ __forceinline__ void resolve_hit(const BvhView& bv, const TraceResult& r, int32_t* objid, int32_t* primid,
                                             int32_t* mtrlid, int32_t* meshid)
@@ -245,77 +133,278 @@ __device__ __forceinline__ void resolve_hit(const BvhView& bv, const TraceResult
     *meshid = mesh < 0 ? il.w : mesh;
 }
 
-// Closest-hit kernel, persistent threads.  Rays come from the SoA path buffers through a queue of
-// path slots (queue == nullptr: identity).  `count` is read from device memory.
-__global__ void __launch_bounds__(kTraceBlock)
-k_trace_closest(BvhView bv, PathBuffers pb, const int32_t* __restrict__ queue, const int32_t* __restrict__ count_ptr,
-                int32_t* __restrict__ fetch, const float* __restrict__ t_max_arr, float t_max_all)
-{
-    __shared__ int32_t s_stack[kSmemStack * kTraceBlock];
-    const int lane = threadIdx.x & 31;
-    const int count = *count_ptr;
-    for (;;) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(fetch, 32);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= count) break;
-        const int i = base + lane;
-        if (i < count) {
-            const int slot = queue ? queue[i] : i;
-            const float4 o = pb.ray_o[slot];
-            const float4 d = pb.ray_d[slot];
-            TraceResult r;
-            traverse<false>(bv, V3(o.x, o.y, o.z), V3(d.x, d.y, d.z), t_max_arr ? t_max_arr[slot] : t_max_all,
-                            EXIT_NONE, 0.0f, s_stack + threadIdx.x, &r);
-            int32_t objid, primid, mtrlid, meshid;
-            resolve_hit(bv, r, &objid, &primid, &mtrlid, &meshid);
-            pb.hit0[slot] = make_float4(r.t, r.a, r.b, __int_as_float(primid));
-            pb.hit1[slot] = make_int2(objid, mtrlid);
+// Relative slack on the running t_max used to CULL boxes once a hit is known.  The reference culls
+// with the exact running t_max through a slab test that is biased by +1e-6 on the direction
+// (aabb.h:68), which makes its answer depend on its visit order when two primitives are hit within
+// a few ulps of each other.  Culling with t*(1+2e-5) makes the GPU answer order independent: it is
+// the nearest accepted triangle among all whose ancestor boxes pass the reference's own test.
+__device__ __forceinline__ float cull_bound(float t) { return t + fabsf(t) * 2e-5f; }
+
+// ---- ray sources / sinks of the traversal kernel -------------------------------------------
+// A policy tells the kernel where ray i comes from and where its result goes.
+struct ClosestPolicy {             // wavefront closest-hit (hitTest)
+    PathBuffers pb;
+    const int32_t* queue;          // path slots, nullptr = identity
+    float t_max_all;
+    __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* t_max, int* mode, float* exit_dist) const
+    {
+        const int s = queue ? queue[i] : i;
+        const float4 ro = pb.ray_o[s];
+        const float4 rd = pb.ray_d[s];
+        *slot = s; *o = V3(ro.x, ro.y, ro.z); *d = V3(rd.x, rd.y, rd.z);
+        *t_max = t_max_all; *mode = EXIT_NONE; *exit_dist = 0.0f;
+    }
+    __device__ __forceinline__ void world(int slot, V3* o, V3* d) const
+    {
+        const float4 ro = pb.ray_o[slot];
+        const float4 rd = pb.ray_d[slot];
+        *o = V3(ro.x, ro.y, ro.z); *d = V3(rd.x, rd.y, rd.z);
+    }
+    __device__ __forceinline__ void finish(const BvhView& bv, int slot, const TraceResult& r) const
+    {
+        int32_t objid, primid, mtrlid, meshid;
+        resolve_hit(bv, r, &objid, &primid, &mtrlid, &meshid);
+        pb.hit0[slot] = make_float4(r.t, r.a, r.b, __int_as_float(primid));
+        pb.hit1[slot] = make_int2(objid, mtrlid);
+    }
+};
+
+template <bool kTap>
+struct ShadowPolicy {              // wavefront shadow rays (hitShadowRay)
+    PathBuffers pb;
+    SceneView sc;
+    AtnBounceRecord* tap;
+    int tap_cap, bounce;
+    __device__ __forceinline__ void world(int i, V3* o, V3* d) const
+    {
+        const float4 so = pb.sh_o[i];
+        const float4 sd = pb.sh_d[i];
+        // aten::ray(rayorg, raydir) renormalises the direction (pathtracing_impl.h:378)
+        *o = V3(so.x, so.y, so.z); *d = normalize(V3(sd.x, sd.y, sd.z));
+    }
+    __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* t_max, int* mode, float* exit_dist) const
+    {
+        world(i, o, d);
+        const float dist = pb.sh_o[i].w;
+        const uint32_t attrib = sc.lights[__float_as_int(pb.sh_d[i].w)].attrib;
+        *slot = i;
+        *t_max = dist - kEps;                       // HitTestToTargetLight, pathtracing_impl.h:297-304
+        *mode = (attrib & 2u) ? EXIT_ANY_HIT : ((attrib & 1u) ? EXIT_HIT_BEFORE : EXIT_NONE);
+        *exit_dist = dist;
+    }
+    __device__ __forceinline__ void finish(const BvhView& bv, int i, const TraceResult& r) const
+    {
+        const float4 so = pb.sh_o[i];
+        const float4 sd = pb.sh_d[i];
+        const float4 c = pb.sh_c[i];
+        const int slot = __float_as_int(c.w);
+        const AtnLightParameter& light = sc.lights[__float_as_int(sd.w)];
+        Ray sr; sr.org = V3(so.x, so.y, so.z); sr.dir = normalize(V3(sd.x, sd.y, sd.z));
+        int32_t objid, primid, mtrlid, meshid;
+        resolve_hit(bv, r, &objid, &primid, &mtrlid, &meshid);
+        const bool vis = shadow_visible(sc, light, sr, so.w, objid, primid, r.a, r.b, r.t, mtrlid);
+        if (vis) {
+            float4 cc = pb.contrib[slot];
+            cc.x += c.x; cc.y += c.y; cc.z += c.z;
+            pb.contrib[slot] = cc;
+        }
+        if (kTap) {
+            AtnBounceRecord& rec = tap[(size_t)slot * tap_cap + bounce];
+            rec.shadow_visible = vis ? 1 : 0;
+            if (vis) { const float4 cc = pb.contrib[slot]; rec.contrib[0] = cc.x; rec.contrib[1] = cc.y; rec.contrib[2] = cc.z; }
         }
     }
-}
+};
 
-// Shadow-ray kernel: traversal with the reference's closest-hit semantics (t_max = dist - 1e-9)
-// and early exit where that provably cannot change the answer; then scene::hitLight.
-template <bool kTap>
+struct QueryClosestPolicy {        // atn_trace_closest
+    const AtnRay* rays; const float* t_max; AtnHit* hits;
+    __device__ __forceinline__ void world(int i, V3* o, V3* d) const { const AtnRay r = rays[i]; *o = V3(r.org); *d = V3(r.dir); }
+    __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* tm, int* mode, float* exit_dist) const
+    {
+        world(i, o, d); *slot = i; *tm = t_max ? t_max[i] : kInf; *mode = EXIT_NONE; *exit_dist = 0.0f;
+    }
+    __device__ __forceinline__ void finish(const BvhView& bv, int i, const TraceResult& r) const
+    {
+        AtnHit h;
+        resolve_hit(bv, r, &h.objid, &h.primid, &h.mtrlid, &h.meshid);
+        h.t = r.t; h.a = r.a; h.b = r.b; h.isVoxel = 0;
+        hits[i] = h;
+    }
+};
+
+struct QueryAnyPolicy {            // atn_trace_any
+    const AtnRay* rays; const float* dist; uint8_t* visible;
+    __device__ __forceinline__ void world(int i, V3* o, V3* d) const { const AtnRay r = rays[i]; *o = V3(r.org); *d = V3(r.dir); }
+    __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* tm, int* mode, float* exit_dist) const
+    {
+        world(i, o, d); *slot = i; *tm = dist[i] - kEps; *mode = EXIT_HIT_BEFORE; *exit_dist = dist[i];
+    }
+    __device__ __forceinline__ void finish(const BvhView&, int i, const TraceResult& r) const
+    {
+        visible[i] = (r.leaf < 0 || r.t > dist[i]) ? 1 : 0;
+    }
+};
+
+// Two-level closest-hit traversal over PairNodes with the reference's acceptance rules
+// (threaded_bvh_traverser.h:98-304): inner boxes use aabb::hit, leaves are never box-tested, a
+// triangle is accepted iff t_min < t && t < best (ties: lowest depth-first rank, which is what
+// "first encountered" means in the reference's fixed visit order).
+//
+// Execution model: persistent warps.  Every lane owns one ray and a resumable traversal state; the
+// warp advances all its rays one node / leaf per iteration and re-converges after each iteration.
+// When fewer than kRefillThreshold lanes still have a ray, the warp goes back to the queue and the
+// idle lanes pull new rays (one atomicAdd per warp, compacted with __ballot_sync/__popc), so
+// incoherent rays do not leave most of the warp idle behind the slowest one.
+// Stack: kSmemStack entries per lane in shared memory (reference + box entry distance), spilling to
+// local memory beyond that.  A popped subtree whose entry distance is already behind the current
+// hit is dropped without fetching its node.
+template <class Policy>
 __global__ void __launch_bounds__(kTraceBlock)
-k_trace_shadow(BvhView bv, SceneView sc, PathBuffers pb, const int32_t* __restrict__ count_ptr,
-               int32_t* __restrict__ fetch, AtnBounceRecord* tap, int tap_cap, int bounce)
+k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch)
 {
-    __shared__ int32_t s_stack[kSmemStack * kTraceBlock];
+    __shared__ int32_t s_ref[kSmemStack * kTraceBlock];
+    __shared__ float s_t0[kSmemStack * kTraceBlock];
+    int32_t l_ref[kLocalStack];
+    float l_t0[kLocalStack];
+    int32_t* const my_ref = s_ref + threadIdx.x;
+    float* const my_t0 = s_t0 + threadIdx.x;
+
+    const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    const int count = *count_ptr;
+    const int count = count_ptr ? *count_ptr : count_imm;
+    const float t_min = bv.t_min;
+
+    // per-lane traversal state
+    bool active = false;
+    bool exhausted = false;          // warp-uniform: the queue has no more rays
+    int slot = 0, mode = EXIT_NONE, sp = 0, cur = kRefNull, cur_inst = -1;
+    float exit_dist = 0.0f, t_cull = kInf;
+    V3 org, dir;
+    RayInv ri;
+    TraceResult best;
+    best.t = kInf; best.a = 0.0f; best.b = 0.0f; best.leaf = -1; best.inst = -1;
+
     for (;;) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(fetch, 32);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= count) break;
-        const int i = base + lane;
-        if (i < count) {
-            const float4 o = pb.sh_o[i];
-            const float4 d = pb.sh_d[i];
-            const float4 c = pb.sh_c[i];
-            const int light_id = __float_as_int(d.w);
-            const int slot = __float_as_int(c.w);
-            const AtnLightParameter& light = sc.lights[light_id];
-            const uint32_t attrib = light.attrib;
-            const int mode = (attrib & 2u) ? EXIT_ANY_HIT : ((attrib & 1u) ? EXIT_HIT_BEFORE : EXIT_NONE);
-            // aten::ray(rayorg, raydir) renormalises the direction (pathtracing_impl.h:378)
-            Ray sr; sr.org = V3(o.x, o.y, o.z); sr.dir = normalize(V3(d.x, d.y, d.z));
-            TraceResult r;
-            traverse<true>(bv, sr.org, sr.dir, o.w - kEps, mode, o.w, s_stack + threadIdx.x, &r);
-            int32_t objid, primid, mtrlid, meshid;
-            resolve_hit(bv, r, &objid, &primid, &mtrlid, &meshid);
-            const bool vis = shadow_visible(sc, light, sr, o.w, objid, primid, r.a, r.b, r.t, mtrlid);
-            if (vis) {
-                float4 cc = pb.contrib[slot];
-                cc.x += c.x; cc.y += c.y; cc.z += c.z;
-                pb.contrib[slot] = cc;
+        // ---------------- refill idle lanes ----------------
+        const unsigned idle = __ballot_sync(full, !active);
+        if (idle != 0u && !exhausted) {
+            const int nidle = __popc(idle);
+            const int leader = __ffs(idle) - 1;
+            int base = 0;
+            if (lane == leader) base = atomicAdd(fetch, nidle);
+            base = __shfl_sync(full, base, leader);
+            if (base + nidle >= count) exhausted = true;
+            if (!active) {
+                const int i = base + __popc(idle & ((1u << lane) - 1u));
+                if (i < count) {
+                    float t_max;
+                    pol.load(i, &slot, &org, &dir, &t_max, &mode, &exit_dist);
+                    ri = ray_inv(org, dir);
+                    t_cull = t_max;
+                    best.t = kInf; best.a = 0.0f; best.b = 0.0f; best.leaf = -1; best.inst = -1;
+                    sp = 0; cur = bv.top_root; cur_inst = -1;
+                    active = true;
+                }
             }
-            if (kTap) {
-                AtnBounceRecord& rec = tap[(size_t)slot * tap_cap + bounce];
-                rec.shadow_visible = vis ? 1 : 0;
-                if (vis) { const float4 cc = pb.contrib[slot]; rec.contrib[0] = cc.x; rec.contrib[1] = cc.y; rec.contrib[2] = cc.z; }
+        }
+        if (__ballot_sync(full, active) == 0u) break;
+
+        // ---------------- advance all rays of the warp ----------------
+        for (;;) {
+            const unsigned act = __ballot_sync(full, active);
+            if (act == 0u) break;
+            if (!exhausted && __popc(act) < kRefillThreshold) break;
+            if (!active) continue;
+
+            bool finished = false;
+            if (cur >= 0) {
+                // ---- inner node: test both children ----
+                const float4* np = bv.nodes + (size_t)cur * 4;
+                const float4 n0 = ldg4(np + 0);
+                const float4 n1 = ldg4(np + 1);
+                const float4 n2 = ldg4(np + 2);
+                const float4 n3 = ldg4(np + 3);
+                const int32_t left = __float_as_int(n3.x);
+                const int32_t right = __float_as_int(n3.y);
+                float t0l = -kInf, t0r = -kInf;
+                bool hl = (left != kRefNull), hr = (right != kRefNull);
+                if (hl && left >= 0) hl = aabb_hit(ri, V3(n0.x, n0.z, n2.x), V3(n0.y, n0.w, n2.y), t_min, t_cull, &t0l);
+                if (hr && right >= 0) hr = aabb_hit(ri, V3(n1.x, n1.z, n2.z), V3(n1.y, n1.w, n2.w), t_min, t_cull, &t0r);
+                if (hl && hr) {
+                    const bool swap = t0r < t0l;        // near child first; leaves (t0 = -inf) before boxes
+                    const int32_t farc = swap ? left : right;
+                    const float fart = swap ? t0l : t0r;
+                    if (sp < kSmemStack) { my_ref[sp * kTraceBlock] = farc; my_t0[sp * kTraceBlock] = fart; }
+                    else { l_ref[sp - kSmemStack] = farc; l_t0[sp - kSmemStack] = fart; }
+                    sp++;
+                    cur = swap ? right : left;
+                }
+                else if (hl) cur = left;
+                else if (hr) cur = right;
+                else cur = kRefNull;
+                if (cur >= 0) continue;              // next iteration fetches the child node
+            }
+
+            // ---- leaf (or nothing) ----
+            if (cur != kRefNull) {
+                const int32_t leaf = ~cur;
+                if (cur_inst < 0) {
+                    // top-layer leaf: enter the instance (threaded_bvh_traverser.h:146-185)
+                    const int4 il = __ldg(bv.insts + leaf);
+                    if (il.y != kRefNull) {
+                        if (sp < kSmemStack) { my_ref[sp * kTraceBlock] = kRefExit; my_t0[sp * kTraceBlock] = -kInf; }
+                        else { l_ref[sp - kSmemStack] = kRefExit; l_t0[sp - kSmemStack] = -kInf; }
+                        sp++;
+                        cur_inst = leaf;
+                        if (il.z >= 0) {
+                            const AtnMat4 m = bv.matrices[il.z];
+                            const Ray tr = make_ray(mat_apply(m, org), mat_apply_xyz(m, dir));   // mat4::applyRay
+                            org = tr.org; dir = tr.dir;
+                            ri = ray_inv(org, dir);
+                        }
+                        cur = il.y;
+                        continue;
+                    }
+                }
+                else {
+                    const float4* tp = bv.tris + (size_t)leaf * 3;
+                    const float4 a = ldg4(tp + 0);
+                    const float4 b = ldg4(tp + 1);
+                    const float4 c = ldg4(tp + 2);
+                    const TriHit h = intersect_triangle(org, dir, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), V3(c.x, c.y, c.z));
+                    if (h.hit && h.t < kInf && t_min < h.t) {
+                        const bool closer = h.t < best.t ||
+                            (h.t == best.t && (cur_inst < best.inst || (cur_inst == best.inst && leaf < best.leaf)));
+                        if (closer) {
+                            best.t = h.t; best.a = h.a; best.b = h.b; best.leaf = leaf; best.inst = cur_inst;
+                            t_cull = cull_bound(h.t);
+                            if (mode == EXIT_ANY_HIT || (mode == EXIT_HIT_BEFORE && h.t <= exit_dist)) finished = true;
+                        }
+                    }
+                }
+            }
+
+            // ---- pop ----
+            if (!finished) {
+                for (;;) {
+                    if (sp == 0) { finished = true; break; }
+                    sp--;
+                    float t0;
+                    if (sp < kSmemStack) { cur = my_ref[sp * kTraceBlock]; t0 = my_t0[sp * kTraceBlock]; }
+                    else { cur = l_ref[sp - kSmemStack]; t0 = l_t0[sp - kSmemStack]; }
+                    if (cur == kRefExit) {
+                        cur_inst = -1;
+                        pol.world(slot, &org, &dir);
+                        ri = ray_inv(org, dir);
+                        continue;
+                    }
+                    if (t0 > t_cull) continue;          // subtree starts behind the current hit
+                    break;
+                }
+            }
+            if (finished) {
+                pol.finish(bv, slot, best);
+                active = false;
             }
         }
     }
@@ -484,55 +573,6 @@ __global__ void k_gather(FrameParams fp, PathBuffers pb, float4* image, int prog
 }
 
 // ---------------------------------------------------------------------------------------------
-// ray-query helpers (atn_trace_closest / atn_trace_any)
-// ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kTraceBlock)
-k_query_closest(BvhView bv, const AtnRay* __restrict__ rays, const float* __restrict__ t_max, int n,
-                int32_t* __restrict__ fetch, AtnHit* __restrict__ hits)
-{
-    __shared__ int32_t s_stack[kSmemStack * kTraceBlock];
-    const int lane = threadIdx.x & 31;
-    for (;;) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(fetch, 32);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        const int i = base + lane;
-        if (i < n) {
-            const AtnRay ray = rays[i];
-            TraceResult r;
-            traverse<false>(bv, V3(ray.org), V3(ray.dir), t_max ? t_max[i] : kInf, EXIT_NONE, 0.0f, s_stack + threadIdx.x, &r);
-            AtnHit h;
-            resolve_hit(bv, r, &h.objid, &h.primid, &h.mtrlid, &h.meshid);
-            h.t = r.t; h.a = r.a; h.b = r.b; h.isVoxel = 0;
-            hits[i] = h;
-        }
-    }
-}
-
-__global__ void __launch_bounds__(kTraceBlock)
-k_query_any(BvhView bv, const AtnRay* __restrict__ rays, const float* __restrict__ dist, int n,
-            int32_t* __restrict__ fetch, uint8_t* __restrict__ visible)
-{
-    __shared__ int32_t s_stack[kSmemStack * kTraceBlock];
-    const int lane = threadIdx.x & 31;
-    for (;;) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(fetch, 32);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        const int i = base + lane;
-        if (i < n) {
-            const AtnRay ray = rays[i];
-            const float dd = dist[i];
-            TraceResult r;
-            traverse<true>(bv, V3(ray.org), V3(ray.dir), dd - kEps, EXIT_HIT_BEFORE, dd, s_stack + threadIdx.x, &r);
-            visible[i] = (r.leaf < 0 || r.t > dd) ? 1 : 0;
-        }
-    }
-}
-
-// ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
 template <class T>
@@ -693,7 +733,7 @@ ATN_API int atn_create(int device_ordinal, AtnRenderer** out)
     CUDA_TRY(cudaEventCreate(&r->ev0));
     CUDA_TRY(cudaEventCreate(&r->ev1));
     int bps = 0;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace_closest, kTraceBlock, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace<ClosestPolicy>, kTraceBlock, 0));
     r->trace_grid = r->sm_count * std::max(1, bps);
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_shade<false>, 128, 0));
     r->shade_grid = r->sm_count * std::max(1, bps);
@@ -938,13 +978,22 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
             const int32_t* q = (b == 0) ? nullptr : r->pb.queue[b & 1];
             const float tmax = (b == 0) ? kInf : r->hit_distance_limit;
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
-            k_trace_closest<<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, r->pb, q, &c->n_active[b], &c->fetch_closest[b], nullptr, tmax);
+            {
+                ClosestPolicy pol{ r->pb, q, tmax };
+                k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[b], 0, &c->fetch_closest[b]);
+            }
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             if (tap_now) k_shade<true><<<r->shade_grid, 128, 0, s>>>(fp, r->camera, r->sv, r->seeds.p, r->pb, c, b, r->tap_dev.p, r->tap_cap);
             else k_shade<false><<<r->shade_grid, 128, 0, s>>>(fp, r->camera, r->sv, r->seeds.p, r->pb, c, b, nullptr, 0);
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
-            if (tap_now) k_trace_shadow<true><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, r->sv, r->pb, &c->n_shadow[b], &c->fetch_shadow[b], r->tap_dev.p, r->tap_cap, b);
-            else k_trace_shadow<false><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, r->sv, r->pb, &c->n_shadow[b], &c->fetch_shadow[b], nullptr, 0, b);
+            if (tap_now) {
+                ShadowPolicy<true> pol{ r->pb, r->sv, r->tap_dev.p, r->tap_cap, b };
+                k_trace<ShadowPolicy<true>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b]);
+            }
+            else {
+                ShadowPolicy<false> pol{ r->pb, r->sv, nullptr, 0, b };
+                k_trace<ShadowPolicy<false>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b]);
+            }
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             launches += 3;
         }
@@ -1022,8 +1071,14 @@ static int query_launch(AtnRenderer* r, const void* rays_dev, const void* f_dev,
     CUDA_TRY(r->counters.resize(1));
     CUDA_TRY(cudaMemsetAsync(&r->counters.p->fetch_query, 0, sizeof(int32_t), s));
     CUDA_TRY(cudaEventRecord(r->ev0, s));
-    if (any) k_query_any<<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, (const AtnRay*)rays_dev, (const float*)f_dev, (int)n, &r->counters.p->fetch_query, (uint8_t*)out_dev);
-    else k_query_closest<<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, (const AtnRay*)rays_dev, (const float*)f_dev, (int)n, &r->counters.p->fetch_query, (AtnHit*)out_dev);
+    if (any) {
+        QueryAnyPolicy pol{ (const AtnRay*)rays_dev, (const float*)f_dev, (uint8_t*)out_dev };
+        k_trace<QueryAnyPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query);
+    }
+    else {
+        QueryClosestPolicy pol{ (const AtnRay*)rays_dev, (const float*)f_dev, (AtnHit*)out_dev };
+        k_trace<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query);
+    }
     CUDA_TRY(cudaEventRecord(r->ev1, s));
     CUDA_TRY(cudaGetLastError());
     r->stats.kernel_launches = 1;

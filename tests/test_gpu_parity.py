@@ -53,6 +53,7 @@ def assert_hits_equal(got, ref, max_near_tie_rate=3e-4):
         assert (both == diff).all(), f"{(diff & ~both).sum()} hit/miss disagreements"
         rel = np.abs(got["t"][diff].astype(np.float64) - ref["t"][diff]) / ref["t"][diff]
         assert rel.max() <= 1e-5, f"distance differs by {rel.max():.3g} relative"
+        # with the culling slack of the kernel the GPU never reports the farther of the two
         assert (got["t"][diff] <= ref["t"][diff]).all(), "GPU reported a farther hit than the reference"
         assert diff.mean() <= max_near_tie_rate, f"near-tie rate {diff.mean():.2e}"
     same = ~diff

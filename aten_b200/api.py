@@ -44,7 +44,7 @@ def load_library(path: str | None = None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = path or LIB_PATH
+    p = path or os.environ.get("ATEN_B200_LIB") or LIB_PATH     # env override: kernel-variant experiments only
     if not os.path.exists(p):
         raise AtnError(f"{p} is missing: build it with `python -m aten_b200.build` (needs nvcc); "
                        "aten_b200 has no CPU fallback")

@@ -28,10 +28,11 @@ def nvcc() -> str:
     return "nvcc"
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and os.path.exists(OUT) and all(os.path.getmtime(OUT) >= os.path.getmtime(d) for d in DEPS):
-        return OUT
-    cmd = [nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT, SRC]
+def build(force: bool = False, verbose: bool = False, defines=(), out: str = OUT) -> str:
+    """``defines``/``out``: build a kernel variant next to the product library (tuning experiments)."""
+    if not force and os.path.exists(out) and all(os.path.getmtime(out) >= os.path.getmtime(d) for d in DEPS):
+        return out
+    cmd = [nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + [f"-D{d}" for d in defines] + ["-o", out, SRC]
     env = dict(os.environ)
     env.pop("CXX", None)     # the image exports CXX=/opt/gcc/bin/g++, which nvcc must not pick up
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env)
@@ -39,7 +40,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         print(r.stdout)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed building libaten_b200.so")
-    return OUT
+    return out
 
 
 if __name__ == "__main__":

@@ -8,7 +8,7 @@
 //          threaded_bvh.cpp:254-357).
 // Output : * PairNode[]  64 B, 64-byte aligned: both children's boxes + both child references, so one
 //            node fetch (4 x LDG.128, two 32 B sectors) decides both children;
-//          * TriLeaf[]   48 B: the three vertex positions gathered next to each other with
+//          * TriLeaf[]   48 B: v0 and the two edges v1-v0, v2-v0 gathered next to each other with
 //            primid / mtrlid / mesh_id in the .w lanes (no index -> vertex indirection);
 //          * InstLeaf[]  16 B: objid, root reference of the bottom tree, W2L matrix index, meshid.
 //          Leaves are numbered in the reference's depth-first (hit-link) order; the index is the
@@ -37,8 +37,8 @@ static_assert(sizeof(PairNode) == 64, "PairNode");
 
 struct alignas(16) TriLeaf {
     float v0[3]; int32_t primid;
-    float v1[3]; int32_t mtrlid;
-    float v2[3]; int32_t mesh_id;
+    float e1[3]; int32_t mtrlid;      // v1 - v0 (the float subtraction intersectTriangle starts with)
+    float e2[3]; int32_t mesh_id;     // v2 - v0
 };
 static_assert(sizeof(TriLeaf) == 48, "TriLeaf");
 
@@ -105,8 +105,8 @@ struct ListBuilder {
         const AtnVec4& b = scene->positions[tp.idx[1]];
         const AtnVec4& c = scene->positions[tp.idx[2]];
         tl.v0[0] = a.x; tl.v0[1] = a.y; tl.v0[2] = a.z; tl.primid = (int32_t)primid;
-        tl.v1[0] = b.x; tl.v1[1] = b.y; tl.v1[2] = b.z; tl.mtrlid = tp.mtrlid;
-        tl.v2[0] = c.x; tl.v2[1] = c.y; tl.v2[2] = c.z; tl.mesh_id = tp.mesh_id;
+        tl.e1[0] = b.x - a.x; tl.e1[1] = b.y - a.y; tl.e1[2] = b.z - a.z; tl.mtrlid = tp.mtrlid;
+        tl.e2[0] = c.x - a.x; tl.e2[1] = c.y - a.y; tl.e2[2] = c.z - a.z; tl.mesh_id = tp.mesh_id;
         out->tris.push_back(tl);
         return leaf_ref((int32_t)out->tris.size() - 1);
     }

@@ -76,7 +76,14 @@ constexpr int kMaxBounce = 16;
 constexpr int kSmemStack = 12;     // shared-memory stack entries per thread (ints)
 constexpr int kLocalStack = 64;    // overflow, local memory
 constexpr int kTraceBlock = 128;
-constexpr int kRefillThreshold = 20;   // refill a warp when fewer lanes than this still own a ray
+#ifndef ATN_REFILL_THRESHOLD
+#define ATN_REFILL_THRESHOLD 20
+#endif
+constexpr int kRefillThreshold = ATN_REFILL_THRESHOLD;   // refill a warp when fewer lanes than this still own a ray
+#ifndef ATN_ENTRY_BATCH
+#define ATN_ENTRY_BATCH 6
+#endif
+constexpr int kEntryBatch = ATN_ENTRY_BATCH;             // lanes that must want to enter an instance before the transform runs
 
 // Per-frame device counters; zeroed with one memset per sample pass.
 struct Counters {
@@ -139,6 +146,42 @@ __device__ __forceinline__ void resolve_hit(const BvhView& bv, const TraceResult
 // a few ulps of each other.  Culling with t*(1+2e-5) makes the GPU answer order independent: it is
 // the nearest accepted triangle among all whose ancestor boxes pass the reference's own test.
 __device__ __forceinline__ float cull_bound(float t) { return t + fabsf(t) * 2e-5f; }
+
+// intersectTriangle (src/libaten/math/intersect.h:45-89) with e1 = v1 - v0 and e2 = v2 - v0 taken from
+// the TriLeaf record (computed on upload with the same float subtraction, so every later operation
+// sees the same operands as the reference's).
+__device__ __forceinline__ TriHit intersect_triangle_edges(const V3& org, const V3& dir, const V3& v0, const V3& e1, const V3& e2)
+{
+    const V3 r = org - v0;
+    const V3 u = cross(dir, e2);
+    const V3 v = cross(r, e1);
+    const float inv = 1.0f / dot(u, e1);
+    TriHit h;
+    h.t = dot(v, e2) * inv;
+    h.a = dot(u, r) * inv;
+    h.b = dot(v, dir) * inv;
+    h.hit = ((h.a >= 0.0f && h.a <= 1.0f) && (h.b >= 0.0f && h.b <= 1.0f) && (h.a + h.b <= 1.0f) && h.t >= 0.0f);
+    return h;
+}
+
+// aabb::hit (src/libaten/math/aabb.h:61-86) for the kernels: same products, sums and comparisons as
+// atn::aabb_hit, with the min/max selections as single FMNMX instructions.  fminf/fmaxf differ from
+// the reference's std::min/std::max only when an operand is NaN, which needs a direction component
+// equal to -1e-6f exactly (1/(dir + 1e-6) = inf); DESIGN.md lists this as not reproduced.
+__device__ __forceinline__ bool slab_test(const RayInv& ri, float minx, float maxx, float miny, float maxy,
+                                          float minz, float maxz, float t_min, float t_max, float* t0_out)
+{
+    const float fx = maxx * ri.invdir.x + ri.oxinvdir.x;
+    const float fy = maxy * ri.invdir.y + ri.oxinvdir.y;
+    const float fz = maxz * ri.invdir.z + ri.oxinvdir.z;
+    const float nx = minx * ri.invdir.x + ri.oxinvdir.x;
+    const float ny = miny * ri.invdir.y + ri.oxinvdir.y;
+    const float nz = minz * ri.invdir.z + ri.oxinvdir.z;
+    const float t1 = fminf(fminf(fminf(fmaxf(fx, nx), fmaxf(fy, ny)), fmaxf(fz, nz)), t_max);
+    const float t0 = fmaxf(fmaxf(fmaxf(fminf(fx, nx), fminf(fy, ny)), fminf(fz, nz)), t_min);
+    *t0_out = t0;
+    return t0 <= t1;
+}
 
 // ---- ray sources / sinks of the traversal kernel -------------------------------------------
 // A policy tells the kernel where ray i comes from and where its result goes.
@@ -264,10 +307,12 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
 {
     __shared__ int32_t s_ref[kSmemStack * kTraceBlock];
     __shared__ float s_t0[kSmemStack * kTraceBlock];
+    __shared__ float s_world[12 * kTraceBlock];      // world-space org, dir, invdir, oxinvdir of the lane's ray
     int32_t l_ref[kLocalStack];
     float l_t0[kLocalStack];
     int32_t* const my_ref = s_ref + threadIdx.x;
     float* const my_t0 = s_t0 + threadIdx.x;
+    float* const my_world = s_world + threadIdx.x;
 
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -275,7 +320,8 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
     const float t_min = bv.t_min;
 
     // per-lane traversal state
-    bool active = false;
+    bool active = false;             // the lane owns a ray that is still being traversed
+    bool done = false;               // traversal complete, result not written yet (written at the next refill)
     bool exhausted = false;          // warp-uniform: the queue has no more rays
     int slot = 0, mode = EXIT_NONE, sp = 0, cur = kRefNull, cur_inst = -1;
     float exit_dist = 0.0f, t_cull = kInf;
@@ -285,6 +331,9 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
     best.t = kInf; best.a = 0.0f; best.b = 0.0f; best.leaf = -1; best.inst = -1;
 
     for (;;) {
+        // ---------------- write results of completed rays (all such lanes together) ----------------
+        if (done) { pol.finish(bv, slot, best); done = false; }
+
         // ---------------- refill idle lanes ----------------
         const unsigned idle = __ballot_sync(full, !active);
         if (idle != 0u && !exhausted) {
@@ -300,6 +349,10 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                     float t_max;
                     pol.load(i, &slot, &org, &dir, &t_max, &mode, &exit_dist);
                     ri = ray_inv(org, dir);
+                    my_world[0 * kTraceBlock] = org.x; my_world[1 * kTraceBlock] = org.y; my_world[2 * kTraceBlock] = org.z;
+                    my_world[3 * kTraceBlock] = dir.x; my_world[4 * kTraceBlock] = dir.y; my_world[5 * kTraceBlock] = dir.z;
+                    my_world[6 * kTraceBlock] = ri.invdir.x; my_world[7 * kTraceBlock] = ri.invdir.y; my_world[8 * kTraceBlock] = ri.invdir.z;
+                    my_world[9 * kTraceBlock] = ri.oxinvdir.x; my_world[10 * kTraceBlock] = ri.oxinvdir.y; my_world[11 * kTraceBlock] = ri.oxinvdir.z;
                     t_cull = t_max;
                     best.t = kInf; best.a = 0.0f; best.b = 0.0f; best.leaf = -1; best.inst = -1;
                     sp = 0; cur = bv.top_root; cur_inst = -1;
@@ -309,16 +362,15 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
         }
         if (__ballot_sync(full, active) == 0u) break;
 
-        // ---------------- advance all rays of the warp ----------------
+        // ---------------- advance all rays of the warp, one node / leaf per iteration ----------------
         for (;;) {
             const unsigned act = __ballot_sync(full, active);
             if (act == 0u) break;
             if (!exhausted && __popc(act) < kRefillThreshold) break;
-            if (!active) continue;
 
-            bool finished = false;
-            if (cur >= 0) {
-                // ---- inner node: test both children ----
+            // ---- phase A: inner node, both slab tests branch free (aabb.h:61-86, running cull bound) ----
+            const bool on_node = active && cur >= 0;
+            if (on_node) {
                 const float4* np = bv.nodes + (size_t)cur * 4;
                 const float4 n0 = ldg4(np + 0);
                 const float4 n1 = ldg4(np + 1);
@@ -326,12 +378,16 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                 const float4 n3 = ldg4(np + 3);
                 const int32_t left = __float_as_int(n3.x);
                 const int32_t right = __float_as_int(n3.y);
-                float t0l = -kInf, t0r = -kInf;
-                bool hl = (left != kRefNull), hr = (right != kRefNull);
-                if (hl && left >= 0) hl = aabb_hit(ri, V3(n0.x, n0.z, n2.x), V3(n0.y, n0.w, n2.y), t_min, t_cull, &t0l);
-                if (hr && right >= 0) hr = aabb_hit(ri, V3(n1.x, n1.z, n2.z), V3(n1.y, n1.w, n2.w), t_min, t_cull, &t0r);
+                float t0l, t0r;
+                const bool bl = slab_test(ri, n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, t_min, t_cull, &t0l);
+                const bool br = slab_test(ri, n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, t_min, t_cull, &t0r);
+                // leaves are never box-tested by the reference: always taken, before boxes
+                const bool hl = (left >= 0) ? bl : (left != kRefNull);
+                const bool hr = (right >= 0) ? br : (right != kRefNull);
+                t0l = (left >= 0) ? t0l : -kInf;
+                t0r = (right >= 0) ? t0r : -kInf;
                 if (hl && hr) {
-                    const bool swap = t0r < t0l;        // near child first; leaves (t0 = -inf) before boxes
+                    const bool swap = t0r < t0l;        // near child first
                     const int32_t farc = swap ? left : right;
                     const float fart = swap ? t0l : t0r;
                     if (sp < kSmemStack) { my_ref[sp * kTraceBlock] = farc; my_t0[sp * kTraceBlock] = fart; }
@@ -342,50 +398,61 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                 else if (hl) cur = left;
                 else if (hr) cur = right;
                 else cur = kRefNull;
-                if (cur >= 0) continue;              // next iteration fetches the child node
             }
 
-            // ---- leaf (or nothing) ----
-            if (cur != kRefNull) {
+            // ---- phase B: triangle leaf (triangle::hit, triangle.h:40-67) ----
+            const bool on_tri = active && cur < 0 && cur != kRefNull && cur != kRefExit && cur_inst >= 0;
+            bool finished = false;
+            if (on_tri) {
                 const int32_t leaf = ~cur;
-                if (cur_inst < 0) {
-                    // top-layer leaf: enter the instance (threaded_bvh_traverser.h:146-185)
-                    const int4 il = __ldg(bv.insts + leaf);
-                    if (il.y != kRefNull) {
-                        if (sp < kSmemStack) { my_ref[sp * kTraceBlock] = kRefExit; my_t0[sp * kTraceBlock] = -kInf; }
-                        else { l_ref[sp - kSmemStack] = kRefExit; l_t0[sp - kSmemStack] = -kInf; }
-                        sp++;
-                        cur_inst = leaf;
-                        if (il.z >= 0) {
-                            const AtnMat4 m = bv.matrices[il.z];
-                            const Ray tr = make_ray(mat_apply(m, org), mat_apply_xyz(m, dir));   // mat4::applyRay
-                            org = tr.org; dir = tr.dir;
-                            ri = ray_inv(org, dir);
-                        }
-                        cur = il.y;
-                        continue;
+                const float4* tp = bv.tris + (size_t)leaf * 3;
+                const float4 a = ldg4(tp + 0);
+                const float4 b = ldg4(tp + 1);
+                const float4 c = ldg4(tp + 2);
+                const TriHit h = intersect_triangle_edges(org, dir, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), V3(c.x, c.y, c.z));
+                if (h.hit && h.t < kInf && t_min < h.t) {
+                    const bool closer = h.t < best.t ||
+                        (h.t == best.t && (cur_inst < best.inst || (cur_inst == best.inst && leaf < best.leaf)));
+                    if (closer) {
+                        best.t = h.t; best.a = h.a; best.b = h.b; best.leaf = leaf; best.inst = cur_inst;
+                        t_cull = cull_bound(h.t);
+                        if (mode == EXIT_ANY_HIT || (mode == EXIT_HIT_BEFORE && h.t <= exit_dist)) finished = true;
                     }
                 }
-                else {
-                    const float4* tp = bv.tris + (size_t)leaf * 3;
-                    const float4 a = ldg4(tp + 0);
-                    const float4 b = ldg4(tp + 1);
-                    const float4 c = ldg4(tp + 2);
-                    const TriHit h = intersect_triangle(org, dir, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), V3(c.x, c.y, c.z));
-                    if (h.hit && h.t < kInf && t_min < h.t) {
-                        const bool closer = h.t < best.t ||
-                            (h.t == best.t && (cur_inst < best.inst || (cur_inst == best.inst && leaf < best.leaf)));
-                        if (closer) {
-                            best.t = h.t; best.a = h.a; best.b = h.b; best.leaf = leaf; best.inst = cur_inst;
-                            t_cull = cull_bound(h.t);
-                            if (mode == EXIT_ANY_HIT || (mode == EXIT_HIT_BEFORE && h.t <= exit_dist)) finished = true;
+                cur = kRefNull;
+            }
+
+            // ---- phase E: top-layer leaf = instance entry (threaded_bvh_traverser.h:146-185).  Lanes
+            // wait here until a few of them want to enter, or nothing else is going on in the warp:
+            // the transform is long and otherwise runs for one or two lanes at a time. ----
+            const bool want_entry = active && cur < 0 && cur != kRefNull && cur != kRefExit && cur_inst < 0;
+            const unsigned me = __ballot_sync(full, want_entry);
+            if (me != 0u) {
+                const unsigned busy = __ballot_sync(full, on_node || on_tri);
+                if (__popc(me) >= kEntryBatch || busy == 0u) {
+                    if (want_entry) {
+                        const int32_t leaf = ~cur;
+                        const int4 il = __ldg(bv.insts + leaf);
+                        cur = kRefNull;
+                        if (il.y != kRefNull) {
+                            if (sp < kSmemStack) { my_ref[sp * kTraceBlock] = kRefExit; my_t0[sp * kTraceBlock] = -kInf; }
+                            else { l_ref[sp - kSmemStack] = kRefExit; l_t0[sp - kSmemStack] = -kInf; }
+                            sp++;
+                            cur_inst = leaf;
+                            if (il.z >= 0) {
+                                const AtnMat4 m = bv.matrices[il.z];
+                                const Ray tr = make_ray(mat_apply(m, org), mat_apply_xyz(m, dir));   // mat4::applyRay
+                                org = tr.org; dir = tr.dir;
+                                ri = ray_inv(org, dir);
+                            }
+                            cur = il.y;
                         }
                     }
                 }
             }
 
-            // ---- pop ----
-            if (!finished) {
+            // ---- phase C: pop ----
+            if (active && !finished && cur == kRefNull) {
                 for (;;) {
                     if (sp == 0) { finished = true; break; }
                     sp--;
@@ -393,19 +460,20 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                     if (sp < kSmemStack) { cur = my_ref[sp * kTraceBlock]; t0 = my_t0[sp * kTraceBlock]; }
                     else { cur = l_ref[sp - kSmemStack]; t0 = l_t0[sp - kSmemStack]; }
                     if (cur == kRefExit) {
+                        if (sp == 0) { finished = true; break; }      // nothing left in the top layer either
+                        // back to the top layer with the world ray (threaded_bvh_traverser.h:290-300)
                         cur_inst = -1;
-                        pol.world(slot, &org, &dir);
-                        ri = ray_inv(org, dir);
+                        org = V3(my_world[0 * kTraceBlock], my_world[1 * kTraceBlock], my_world[2 * kTraceBlock]);
+                        dir = V3(my_world[3 * kTraceBlock], my_world[4 * kTraceBlock], my_world[5 * kTraceBlock]);
+                        ri.invdir = V3(my_world[6 * kTraceBlock], my_world[7 * kTraceBlock], my_world[8 * kTraceBlock]);
+                        ri.oxinvdir = V3(my_world[9 * kTraceBlock], my_world[10 * kTraceBlock], my_world[11 * kTraceBlock]);
                         continue;
                     }
                     if (t0 > t_cull) continue;          // subtree starts behind the current hit
                     break;
                 }
             }
-            if (finished) {
-                pol.finish(bv, slot, best);
-                active = false;
-            }
+            if (finished) { active = false; done = true; }
         }
     }
 }

@@ -73,7 +73,10 @@ struct BvhView {
 };
 
 constexpr int kMaxBounce = 16;
-constexpr int kSmemStack = 12;     // shared-memory stack entries per thread (ints)
+#ifndef ATN_SMEM_STACK
+#define ATN_SMEM_STACK 12
+#endif
+constexpr int kSmemStack = ATN_SMEM_STACK;     // shared-memory stack entries per thread
 constexpr int kLocalStack = 64;    // overflow, local memory
 constexpr int kTraceBlock = 128;
 #ifndef ATN_REFILL_THRESHOLD
@@ -301,8 +304,11 @@ struct QueryAnyPolicy {            // atn_trace_any
 // Stack: kSmemStack entries per lane in shared memory (reference + box entry distance), spilling to
 // local memory beyond that.  A popped subtree whose entry distance is already behind the current
 // hit is dropped without fetching its node.
+#ifndef ATN_TRACE_MIN_BLOCKS
+#define ATN_TRACE_MIN_BLOCKS 8
+#endif
 template <class Policy>
-__global__ void __launch_bounds__(kTraceBlock)
+__global__ void __launch_bounds__(kTraceBlock, ATN_TRACE_MIN_BLOCKS)
 k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch)
 {
     __shared__ int32_t s_ref[kSmemStack * kTraceBlock];
@@ -527,8 +533,11 @@ __device__ __forceinline__ int warp_append(bool pred, int32_t* counter)
     return pred ? base + __popc(mask & ((1u << lane) - 1u)) : -1;
 }
 
+#ifndef ATN_SHADE_MIN_BLOCKS
+#define ATN_SHADE_MIN_BLOCKS 12
+#endif
 template <bool kTap>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, ATN_SHADE_MIN_BLOCKS)
 k_shade(FrameParams fp, AtnCameraParameter cam, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb,
         Counters* cnt, int bounce, AtnBounceRecord* tap, int tap_cap)
 {

@@ -91,6 +91,7 @@ constexpr int kEntryBatch = ATN_ENTRY_BATCH;             // lanes that must want
 // Per-frame device counters; zeroed with one memset per sample pass.
 struct Counters {
     int32_t n_active[kMaxBounce + 1];   // rays queued for closest-hit at bounce b
+    int32_t n_lit[kMaxBounce];          // surface hits that go on to NEE + BSDF sampling at bounce b
     int32_t n_shadow[kMaxBounce];       // shadow rays queued at bounce b
     int32_t fetch_closest[kMaxBounce];  // persistent-thread work cursors
     int32_t fetch_shadow[kMaxBounce];
@@ -110,10 +111,15 @@ struct PathBuffers {
     float4* contrib;      // xyz, samples
     uint32_t* sampler_dim;
     uint32_t* flags;      // bit0 terminated, bit1 singular
-    int32_t* queue[2];
-    float4* sh_o;         // shadow org.xyz, dist
+    int32_t* queue[2];    // path slots to trace at bounce b (b & 1)
+    int32_t* q_lit;       // path slots that passed the surface stage
+    int32_t* q_shadow;    // path slots with a shadow ray to trace
+    float4* surf0;        // Surface: p.xyz, u
+    float4* surf1;        //          orienting normal.xyz, v
+    float4* surf2;        //          albedo.xyz, bits(mtrlid)
+    float4* sh_o;         // shadow org.xyz, dist            (indexed by path slot)
     float4* sh_d;         // shadow dir.xyz, bits(light id)
-    float4* sh_c;         // light contribution xyz, bits(path slot)
+    float4* sh_c;         // light contribution xyz, -
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -221,29 +227,29 @@ struct ShadowPolicy {              // wavefront shadow rays (hitShadowRay)
     SceneView sc;
     AtnBounceRecord* tap;
     int tap_cap, bounce;
-    __device__ __forceinline__ void world(int i, V3* o, V3* d) const
+    __device__ __forceinline__ void world(int slot, V3* o, V3* d) const
     {
-        const float4 so = pb.sh_o[i];
-        const float4 sd = pb.sh_d[i];
+        const float4 so = pb.sh_o[slot];
+        const float4 sd = pb.sh_d[slot];
         // aten::ray(rayorg, raydir) renormalises the direction (pathtracing_impl.h:378)
         *o = V3(so.x, so.y, so.z); *d = normalize(V3(sd.x, sd.y, sd.z));
     }
     __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* t_max, int* mode, float* exit_dist) const
     {
-        world(i, o, d);
-        const float dist = pb.sh_o[i].w;
-        const uint32_t attrib = sc.lights[__float_as_int(pb.sh_d[i].w)].attrib;
-        *slot = i;
+        const int s = pb.q_shadow[i];
+        world(s, o, d);
+        const float dist = pb.sh_o[s].w;
+        const uint32_t attrib = sc.lights[__float_as_int(pb.sh_d[s].w)].attrib;
+        *slot = s;
         *t_max = dist - kEps;                       // HitTestToTargetLight, pathtracing_impl.h:297-304
         *mode = (attrib & 2u) ? EXIT_ANY_HIT : ((attrib & 1u) ? EXIT_HIT_BEFORE : EXIT_NONE);
         *exit_dist = dist;
     }
-    __device__ __forceinline__ void finish(const BvhView& bv, int i, const TraceResult& r) const
+    __device__ __forceinline__ void finish(const BvhView& bv, int slot, const TraceResult& r) const
     {
-        const float4 so = pb.sh_o[i];
-        const float4 sd = pb.sh_d[i];
-        const float4 c = pb.sh_c[i];
-        const int slot = __float_as_int(c.w);
+        const float4 so = pb.sh_o[slot];
+        const float4 sd = pb.sh_d[slot];
+        const float4 c = pb.sh_c[slot];
         const AtnLightParameter& light = sc.lights[__float_as_int(sd.w)];
         Ray sr; sr.org = V3(so.x, so.y, so.z); sr.dir = normalize(V3(sd.x, sd.y, sd.z));
         int32_t objid, primid, mtrlid, meshid;
@@ -533,29 +539,45 @@ __device__ __forceinline__ int warp_append(bool pred, int32_t* counter)
     return pred ? base + __popc(mask & ((1u << lane) - 1u)) : -1;
 }
 
-#ifndef ATN_SHADE_MIN_BLOCKS
-#define ATN_SHADE_MIN_BLOCKS 12
+#ifndef ATN_SURFACE_MIN_BLOCKS
+#define ATN_SURFACE_MIN_BLOCKS 10
 #endif
+#ifndef ATN_NEE_MIN_BLOCKS
+#define ATN_NEE_MIN_BLOCKS 10
+#endif
+#ifndef ATN_BSDF_MIN_BLOCKS
+#define ATN_BSDF_MIN_BLOCKS 10
+#endif
+constexpr int kShadeBlock = 128;
+
+__device__ __forceinline__ Sampler path_sampler(const FrameParams& fp, const uint32_t* seeds, const PathBuffers& pb, int slot)
+{
+    const int ix = fp.x0 + slot % fp.rw;
+    const int iy = fp.y0 + slot / fp.rw;
+    Sampler sp = sampler_for_path(fp.frame, seeds[(uint32_t)(iy * fp.width + ix) % fp.seed_count]);
+    sp.dim = pb.sampler_dim[slot];
+    return sp;
+}
+
+// The reference's shade kernel (pathtracing_impl.cu:18-238) is split in three so that each piece fits
+// the instruction caches and runs only for the paths that need it ("Shade stage").
+//
+// Stage 1, all traced paths of the bounce: ShadeMiss for misses (pt_standard_impl.cu:330-362),
+// hit evaluation + material + implicit light for hits.  Survivors go to q_lit with a Surface record.
 template <bool kTap>
-__global__ void __launch_bounds__(128, ATN_SHADE_MIN_BLOCKS)
-k_shade(FrameParams fp, AtnCameraParameter cam, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb,
-        Counters* cnt, int bounce, AtnBounceRecord* tap, int tap_cap)
+__global__ void __launch_bounds__(kShadeBlock, ATN_SURFACE_MIN_BLOCKS)
+k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, Counters* cnt, int bounce,
+          AtnBounceRecord* tap, int tap_cap)
 {
     const int count = cnt->n_active[bounce];
     const int32_t* __restrict__ q_in = (bounce == 0) ? nullptr : pb.queue[bounce & 1];
-    int32_t* __restrict__ q_out = pb.queue[(bounce + 1) & 1];
     const int rounds = (count + blockDim.x * gridDim.x - 1) / (blockDim.x * gridDim.x);
     for (int it = 0; it < rounds; it++) {
         const int i = (it * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
-        const bool valid = i < count;
-        bool cont = false, shadow = false;
+        bool lit = false;
         int slot = 0;
-        ShadowRayOut sh;
-        sh.active = false;
-        if (valid) {
+        if (i < count) {
             slot = q_in ? q_in[i] : i;
-            const int ix = fp.x0 + slot % fp.rw;
-            const int iy = fp.y0 + slot / fp.rw;
             const float4 o = pb.ray_o[slot];
             const float4 d = pb.ray_d[slot];
             const float4 h0 = pb.hit0[slot];
@@ -567,21 +589,109 @@ k_shade(FrameParams fp, AtnCameraParameter cam, SceneView sc, const uint32_t* __
             PathState st;
             st.throughput = V3(th.x, th.y, th.z); st.pdfb = th.w;
             st.contrib = V3(cb.x, cb.y, cb.z);
-            st.sampler = sampler_for_path(fp.frame, seeds[(uint32_t)(iy * fp.width + ix) % fp.seed_count]);
-            st.sampler.dim = pb.sampler_dim[slot];
             st.terminated = false;
             st.singular = (fl & 2u) != 0u;
-            Ray next = ray;
             if (h1.x >= 0) {
-                shade_hit(sc, ray, h1.x, __float_as_int(h0.w), h0.y, h0.z, h0.x, h1.y, bounce, fp.rr_bounce, &st, &sh, &next);
+                Surface sf;
+                lit = shade_surface(sc, ray, h1.x, __float_as_int(h0.w), h0.y, h0.z, h0.x, h1.y, bounce, &st, &sf);
+                if (lit) {
+                    pb.surf0[slot] = make_float4(sf.p.x, sf.p.y, sf.p.z, sf.u);
+                    pb.surf1[slot] = make_float4(sf.n.x, sf.n.y, sf.n.z, sf.v);
+                    pb.surf2[slot] = make_float4(sf.albedo.x, sf.albedo.y, sf.albedo.z, __int_as_float(sf.mtrlid));
+                }
             }
             else {
+                const int ix = fp.x0 + slot % fp.rw;
+                const int iy = fp.y0 + slot / fp.rw;
                 shade_miss(sc, cam, ix, iy, fp.width, fp.height, bounce, ray, &st);
             }
+            if (!lit) {
+                pb.contrib[slot] = make_float4(st.contrib.x, st.contrib.y, st.contrib.z, cb.w);
+                pb.flags[slot] = 1u | (st.singular ? 2u : 0u);
+            }
+            if (kTap) {
+                AtnBounceRecord& rec = tap[(size_t)slot * tap_cap + bounce];
+                rec.ray.org = AtnVec3{ o.x, o.y, o.z };
+                rec.ray.dir = AtnVec3{ d.x, d.y, d.z };
+                rec.hit.t = h0.x; rec.hit.objid = h1.x; rec.hit.mtrlid = h1.y; rec.hit.meshid = -1;
+                rec.hit.primid = __float_as_int(h0.w); rec.hit.a = h0.y; rec.hit.b = h0.z; rec.hit.isVoxel = 0;
+                rec.throughput[0] = st.throughput.x; rec.throughput[1] = st.throughput.y; rec.throughput[2] = st.throughput.z;
+                rec.pdfb = st.pdfb;
+                rec.contrib[0] = st.contrib.x; rec.contrib[1] = st.contrib.y; rec.contrib[2] = st.contrib.z;
+                rec.flags = 1 | (lit ? 0 : 2);
+            }
+        }
+        const int pos = warp_append(lit, &cnt->n_lit[bounce]);
+        if (lit) pb.q_lit[pos] = slot;
+    }
+}
+
+// Stage 2, lit paths: light pick + light sample + NEE evaluation (FillShadowRay).  The shadow-ray
+// candidate is stored per slot; stage 3 decides whether it is traced.
+__global__ void __launch_bounds__(kShadeBlock, ATN_NEE_MIN_BLOCKS)
+k_nee(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb, Counters* cnt, int bounce)
+{
+    const int count = cnt->n_lit[bounce];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const int slot = pb.q_lit[i];
+        const float4 d = pb.ray_d[slot];
+        const float4 s0 = pb.surf0[slot];
+        const float4 s1 = pb.surf1[slot];
+        const float4 s2 = pb.surf2[slot];
+        const float4 th = pb.throughput[slot];
+        Surface sf;
+        sf.p = V3(s0.x, s0.y, s0.z); sf.u = s0.w; sf.n = V3(s1.x, s1.y, s1.z); sf.v = s1.w;
+        sf.albedo = V3(s2.x, s2.y, s2.z); sf.mtrlid = __float_as_int(s2.w);
+        PathState st;
+        st.throughput = V3(th.x, th.y, th.z); st.pdfb = th.w;
+        st.sampler = path_sampler(fp, seeds, pb, slot);
+        ShadowRayOut sh;
+        shade_nee(sc, V3(d.x, d.y, d.z), sf, &st, &sh);
+        pb.sampler_dim[slot] = st.sampler.dim;
+        // dist < 0 marks "no shadow ray"
+        pb.sh_o[slot] = make_float4(sh.org.x, sh.org.y, sh.org.z, sh.active ? sh.dist : -1.0f);
+        if (sh.active) {
+            pb.sh_d[slot] = make_float4(sh.dir.x, sh.dir.y, sh.dir.z, __int_as_float(sh.light_id));
+            pb.sh_c[slot] = make_float4(sh.lightcontrib.x, sh.lightcontrib.y, sh.lightcontrib.z, 0.0f);
+        }
+    }
+}
+
+// Stage 3, lit paths: Russian roulette, BSDF sampling, next ray; queues the next bounce and the
+// shadow ray (HitShadowRay drops the shadow ray of a path that terminated here).
+template <bool kTap>
+__global__ void __launch_bounds__(kShadeBlock, ATN_BSDF_MIN_BLOCKS)
+k_bsdf(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb, Counters* cnt, int bounce,
+       AtnBounceRecord* tap, int tap_cap)
+{
+    const int count = cnt->n_lit[bounce];
+    int32_t* __restrict__ q_out = pb.queue[(bounce + 1) & 1];
+    const int rounds = (count + blockDim.x * gridDim.x - 1) / (blockDim.x * gridDim.x);
+    for (int it = 0; it < rounds; it++) {
+        const int i = (it * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+        bool cont = false, shadow = false;
+        int slot = 0;
+        if (i < count) {
+            slot = pb.q_lit[i];
+            const float4 d = pb.ray_d[slot];
+            const float4 s0 = pb.surf0[slot];
+            const float4 s1 = pb.surf1[slot];
+            const float4 s2 = pb.surf2[slot];
+            const float4 th = pb.throughput[slot];
+            const uint32_t fl = pb.flags[slot];
+            Surface sf;
+            sf.p = V3(s0.x, s0.y, s0.z); sf.u = s0.w; sf.n = V3(s1.x, s1.y, s1.z); sf.v = s1.w;
+            sf.albedo = V3(s2.x, s2.y, s2.z); sf.mtrlid = __float_as_int(s2.w);
+            PathState st;
+            st.throughput = V3(th.x, th.y, th.z); st.pdfb = th.w;
+            st.sampler = path_sampler(fp, seeds, pb, slot);
+            st.terminated = false;
+            st.singular = (fl & 2u) != 0u;
+            Ray next; next.org = sf.p; next.dir = V3(d.x, d.y, d.z);
+            shade_bsdf(sc, V3(d.x, d.y, d.z), sf, bounce, fp.rr_bounce, &st, &next);
             cont = !st.terminated && (bounce + 1 < fp.max_bounce);
-            shadow = !st.terminated && sh.active;      // HitShadowRay: terminated paths drop their shadow ray
+            shadow = !st.terminated && pb.sh_o[slot].w >= 0.0f;
             pb.throughput[slot] = make_float4(st.throughput.x, st.throughput.y, st.throughput.z, st.pdfb);
-            pb.contrib[slot] = make_float4(st.contrib.x, st.contrib.y, st.contrib.z, cb.w);
             pb.sampler_dim[slot] = st.sampler.dim;
             pb.flags[slot] = (st.terminated ? 1u : 0u) | (st.singular ? 2u : 0u);
             if (cont) {
@@ -590,33 +700,23 @@ k_shade(FrameParams fp, AtnCameraParameter cam, SceneView sc, const uint32_t* __
             }
             if (kTap) {
                 AtnBounceRecord& rec = tap[(size_t)slot * tap_cap + bounce];
-                rec.ray.org = AtnVec3{ o.x, o.y, o.z };
-                rec.ray.dir = AtnVec3{ d.x, d.y, d.z };
-                rec.hit.t = h0.x; rec.hit.objid = h1.x; rec.hit.mtrlid = h1.y; rec.hit.meshid = -1;
-                rec.hit.primid = __float_as_int(h0.w); rec.hit.a = h0.y; rec.hit.b = h0.z; rec.hit.isVoxel = 0;
                 rec.shadow_active = shadow ? 1 : 0;
                 rec.shadow_visible = 0;
                 if (shadow) {
-                    rec.shadow_org[0] = sh.org.x; rec.shadow_org[1] = sh.org.y; rec.shadow_org[2] = sh.org.z;
-                    rec.shadow_dist = sh.dist;
-                    rec.shadow_dir[0] = sh.dir.x; rec.shadow_dir[1] = sh.dir.y; rec.shadow_dir[2] = sh.dir.z;
-                    rec.light_contrib[0] = sh.lightcontrib.x; rec.light_contrib[1] = sh.lightcontrib.y; rec.light_contrib[2] = sh.lightcontrib.z;
+                    const float4 so = pb.sh_o[slot]; const float4 sd = pb.sh_d[slot]; const float4 sc4 = pb.sh_c[slot];
+                    rec.shadow_org[0] = so.x; rec.shadow_org[1] = so.y; rec.shadow_org[2] = so.z; rec.shadow_dist = so.w;
+                    rec.shadow_dir[0] = sd.x; rec.shadow_dir[1] = sd.y; rec.shadow_dir[2] = sd.z;
+                    rec.light_contrib[0] = sc4.x; rec.light_contrib[1] = sc4.y; rec.light_contrib[2] = sc4.z;
                 }
                 rec.throughput[0] = st.throughput.x; rec.throughput[1] = st.throughput.y; rec.throughput[2] = st.throughput.z;
                 rec.pdfb = st.pdfb;
-                rec.contrib[0] = st.contrib.x; rec.contrib[1] = st.contrib.y; rec.contrib[2] = st.contrib.z;
                 rec.flags = 1 | (st.terminated ? 2 : 0);
             }
         }
-        // queue appends: one atomic per warp and queue
         const int pos = warp_append(cont, &cnt->n_active[bounce + 1]);
         if (cont) q_out[pos] = slot;
         const int spos = warp_append(shadow, &cnt->n_shadow[bounce]);
-        if (shadow) {
-            pb.sh_o[spos] = make_float4(sh.org.x, sh.org.y, sh.org.z, sh.dist);
-            pb.sh_d[spos] = make_float4(sh.dir.x, sh.dir.y, sh.dir.z, __int_as_float(sh.light_id));
-            pb.sh_c[spos] = make_float4(sh.lightcontrib.x, sh.lightcontrib.y, sh.lightcontrib.z, __int_as_float(slot));
-        }
+        if (shadow) pb.q_shadow[spos] = slot;
     }
 }
 
@@ -712,7 +812,8 @@ struct AtnRenderer {
     DevBuf<float4> ray_o, ray_d, hit0, throughput, contrib, sh_o, sh_d, sh_c, image;
     DevBuf<int2> hit1;
     DevBuf<uint32_t> sampler_dim, flags;
-    DevBuf<int32_t> queue0, queue1;
+    DevBuf<int32_t> queue0, queue1, q_lit, q_shadow;
+    DevBuf<float4> surf0, surf1, surf2;
     DevBuf<Counters> counters;
     DevBuf<Totals> totals;
     PathBuffers pb{};
@@ -735,7 +836,7 @@ struct AtnRenderer {
     cudaEvent_t ev0{ nullptr }, ev1{ nullptr };
     std::vector<cudaEvent_t> trace_events;
     int trace_grid{ 148 * 8 };
-    int shade_grid{ 148 * 8 };
+    int surface_grid{ 148 * 8 }, nee_grid{ 148 * 8 }, bsdf_grid{ 148 * 8 };
 };
 
 static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene)
@@ -775,6 +876,8 @@ static int alloc_paths(AtnRenderer* r, size_t n)
     CUDA_TRY(r->throughput.resize(n)); CUDA_TRY(r->contrib.resize(n)); CUDA_TRY(r->sampler_dim.resize(n));
     CUDA_TRY(r->flags.resize(n)); CUDA_TRY(r->queue0.resize(n)); CUDA_TRY(r->queue1.resize(n));
     CUDA_TRY(r->sh_o.resize(n)); CUDA_TRY(r->sh_d.resize(n)); CUDA_TRY(r->sh_c.resize(n));
+    CUDA_TRY(r->q_lit.resize(n)); CUDA_TRY(r->q_shadow.resize(n));
+    CUDA_TRY(r->surf0.resize(n)); CUDA_TRY(r->surf1.resize(n)); CUDA_TRY(r->surf2.resize(n));
     CUDA_TRY(r->counters.resize(1));
     CUDA_TRY(r->totals.resize(1));
     PathBuffers& pb = r->pb;
@@ -782,6 +885,8 @@ static int alloc_paths(AtnRenderer* r, size_t n)
     pb.throughput = r->throughput.p; pb.contrib = r->contrib.p; pb.sampler_dim = r->sampler_dim.p; pb.flags = r->flags.p;
     pb.queue[0] = r->queue0.p; pb.queue[1] = r->queue1.p;
     pb.sh_o = r->sh_o.p; pb.sh_d = r->sh_d.p; pb.sh_c = r->sh_c.p;
+    pb.q_lit = r->q_lit.p; pb.q_shadow = r->q_shadow.p;
+    pb.surf0 = r->surf0.p; pb.surf1 = r->surf1.p; pb.surf2 = r->surf2.p;
     return ATN_OK;
 }
 
@@ -812,8 +917,12 @@ ATN_API int atn_create(int device_ordinal, AtnRenderer** out)
     int bps = 0;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace<ClosestPolicy>, kTraceBlock, 0));
     r->trace_grid = r->sm_count * std::max(1, bps);
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_shade<false>, 128, 0));
-    r->shade_grid = r->sm_count * std::max(1, bps);
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_surface<false>, kShadeBlock, 0));
+    r->surface_grid = r->sm_count * std::max(1, bps);
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_nee, kShadeBlock, 0));
+    r->nee_grid = r->sm_count * std::max(1, bps);
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_bsdf<false>, kShadeBlock, 0));
+    r->bsdf_grid = r->sm_count * std::max(1, bps);
     *out = r;
     return ATN_OK;
 }
@@ -1060,8 +1169,11 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
                 k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[b], 0, &c->fetch_closest[b]);
             }
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
-            if (tap_now) k_shade<true><<<r->shade_grid, 128, 0, s>>>(fp, r->camera, r->sv, r->seeds.p, r->pb, c, b, r->tap_dev.p, r->tap_cap);
-            else k_shade<false><<<r->shade_grid, 128, 0, s>>>(fp, r->camera, r->sv, r->seeds.p, r->pb, c, b, nullptr, 0);
+            if (tap_now) k_surface<true><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, r->pb, c, b, r->tap_dev.p, r->tap_cap);
+            else k_surface<false><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, r->pb, c, b, nullptr, 0);
+            k_nee<<<r->nee_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, r->pb, c, b);
+            if (tap_now) k_bsdf<true><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, r->pb, c, b, r->tap_dev.p, r->tap_cap);
+            else k_bsdf<false><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, r->pb, c, b, nullptr, 0);
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             if (tap_now) {
                 ShadowPolicy<true> pol{ r->pb, r->sv, r->tap_dev.p, r->tap_cap, b };
@@ -1072,7 +1184,7 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
                 k_trace<ShadowPolicy<false>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b]);
             }
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
-            launches += 3;
+            launches += 5;
         }
         k_gather<<<gen_grid, 256, 0, s>>>(fp, r->pb, r->image.p, r->progressive, r->counters.p, r->totals.p);
         launches++;

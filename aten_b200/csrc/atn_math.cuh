@@ -18,8 +18,27 @@
 
 #if defined(__CUDACC__)
 #define ATN_HD __host__ __device__ __forceinline__
+// ATN_NOINLINE_LEVEL (kernel tuning): 0 = everything inlined; 1 = the rarely taken BSDFs (Disney,
+// Beckmann, refraction) are real functions; 2 = also the sampler, sin/cos users, hit evaluation and
+// light sampling.  The shade kernel is instruction-fetch bound (ncu: "no_instruction" is its top
+// stall), so code size matters more than call overhead there.
+#ifndef ATN_NOINLINE_LEVEL
+#define ATN_NOINLINE_LEVEL 0
+#endif
+#if ATN_NOINLINE_LEVEL >= 1
+#define ATN_HD_COLD __host__ __device__ __noinline__
+#else
+#define ATN_HD_COLD ATN_HD
+#endif
+#if ATN_NOINLINE_LEVEL >= 2
+#define ATN_HD_CALL __host__ __device__ __noinline__
+#else
+#define ATN_HD_CALL ATN_HD
+#endif
 #else
 #define ATN_HD inline
+#define ATN_HD_COLD inline
+#define ATN_HD_CALL inline
 #endif
 
 namespace atn {
@@ -76,7 +95,7 @@ ATN_HD float i2f(int32_t i) { float f; memcpy(&f, &i, 4); return f; }
 struct Ray { V3 org, dir; };
 
 // aten::ray::Offset (src/libaten/math/ray.h:26-74)
-ATN_HD V3 ray_offset(const V3& o, const V3& n)
+ATN_HD_CALL V3 ray_offset(const V3& o, const V3& n)
 {
     const float origin = 1.0f / 32.0f;
     const float float_scale = 1.0f / 65536.0f;
@@ -141,7 +160,7 @@ struct Sampler {
         return i * (1.0f / 4294967808.0f);
     }
     // cmj(s, n, p).x with n = CMJ_DIM = 16 (cmj.h:100-111); nextSample() only uses .x
-    ATN_HD float next()
+    ATN_HD_CALL float next()
     {
         const uint32_t ds = dim * scramble;
         const int32_t s = (int32_t)permute(idx, 256u, 0xa399d265u * ds);
@@ -281,7 +300,7 @@ ATN_HD int32_t wrap_repeat(int32_t value, int32_t wrap)
     else if (value < 0) { int32_t n = value / wrap; if (n < 0) n = -n; value += (n + 1) * wrap; }
     return value;
 }
-ATN_HD AtnVec4 sample_texture(const SceneView& sc, int32_t texid, float u, float v, const AtnVec4& def)
+ATN_HD_CALL AtnVec4 sample_texture(const SceneView& sc, int32_t texid, float u, float v, const AtnVec4& def)
 {
     if (texid < 0) return def;
     const TexView t = sc.textures[texid];
@@ -295,7 +314,7 @@ ATN_HD AtnVec4 sample_texture(const SceneView& sc, int32_t texid, float u, float
 ATN_HD AtnVec4 v4(float a) { AtnVec4 r; r.x = r.y = r.z = r.w = a; return r; }
 
 // GetOrthoVector / GetTangentCoordinate (src/libaten/math/vec3.h:290-337)
-ATN_HD void tangent_frame(const V3& n, V3* t_out, V3* b_out)
+ATN_HD_CALL void tangent_frame(const V3& n, V3* t_out, V3* b_out)
 {
     V3 p;
     if (fabsf(n.z) > 0.0f) {
@@ -313,7 +332,7 @@ ATN_HD void tangent_frame(const V3& n, V3* t_out, V3* b_out)
 }
 
 // applyNormalMap (src/libaten/material/sample_texture.h:64-87)
-ATN_HD V3 apply_normal_map(const SceneView& sc, int32_t normal_map, const V3& org_nml, float u, float v)
+ATN_HD_CALL V3 apply_normal_map(const SceneView& sc, int32_t normal_map, const V3& org_nml, float u, float v)
 {
     if (normal_map >= 0) {
         V3 nml = V3(sample_texture(sc, normal_map, u, v, v4(0.0f)));
@@ -336,7 +355,7 @@ struct HitRecord { V3 p; float area; V3 normal; int32_t mtrlid; float u, v; };
 // triangle::EvaluateHitResult (src/libaten/geometry/triangle.h:70-120) +
 // PolygonObject::evaluate_hit_result (PolygonObject.h:38-72) + evaluate_hit_result
 // (EvaluateHitResult.h:11-72).  Sphere objects: sphere::EvaluateHitResult (sphere.cpp:93-109).
-ATN_HD void evaluate_hit(const SceneView& sc, const AtnObjectParameter& obj, const Ray& ray,
+ATN_HD_CALL void evaluate_hit(const SceneView& sc, const AtnObjectParameter& obj, const Ray& ray,
                          int32_t primid, float a, float b, float t, int32_t mtrlid, HitRecord* rec)
 {
     const bool inst = (obj.type == 1);
@@ -465,7 +484,7 @@ ATN_HD float schlick_fresnel(float ni, float nt, const V3& w, const V3& n)
 
 // Diffuse (src/libaten/material/diffuse.h:86-136)
 ATN_HD float lambert_pdf(const V3& n, const V3& wo) { const float c = fabsf(dot(n, wo)); return c / kPi; }
-ATN_HD V3 lambert_dir(const V3& n, float r1, float r2)
+ATN_HD_CALL V3 lambert_dir(const V3& n, float r1, float r2)
 {
     const float costheta = sqrtf(1 - r1);
     const float sintheta = sqrtf(r1);
@@ -518,7 +537,7 @@ ATN_HD float ggx_pdf(float roughness, const V3& n, const V3& wi, const V3& wo)
     const V3 wh = normalize(-wi + wo);
     return ggx_pdf_h(roughness, n, wh, wo);
 }
-ATN_HD V3 ggx_sample_m(float roughness, const V3& n, float r1, float r2)
+ATN_HD_CALL V3 ggx_sample_m(float roughness, const V3& n, float r1, float r2)
 {
     const float a = roughness;
     float theta = atanf(a * sqrtf(r1 / (1 - r1)));
@@ -538,7 +557,7 @@ ATN_HD V3 ggx_sample_dir(float r1, float r2, float roughness, const V3& wi, cons
     const V3 m = ggx_sample_m(roughness, n, r1, r2);
     return reflect_vec(wi, m);
 }
-ATN_HD V3 ggx_brdf(float roughness, float ior, const V3& n, const V3& wi, const V3& wo)
+ATN_HD_CALL V3 ggx_brdf(float roughness, float ior, const V3& n, const V3& wi, const V3& wo)
 {
     const V3 V = -wi;
     const V3 L = wo;
@@ -569,7 +588,7 @@ ATN_HD float beckman_D(const V3& m, const V3& n, float roughness)
     D *= expf(-tan2 / a2);
     return D;
 }
-ATN_HD float beckman_pdf(float roughness, const V3& n, const V3& wi, const V3& wo)
+ATN_HD_COLD float beckman_pdf(float roughness, const V3& n, const V3& wi, const V3& wo)
 {
     const V3 wh = normalize(-wi + wo);
     const float costheta = fabsf(dot(wh, n));
@@ -577,7 +596,7 @@ ATN_HD float beckman_pdf(float roughness, const V3& n, const V3& wi, const V3& w
     const float denom = 4 * fabsf(dot(wo, wh));
     return denom > 0 ? (D * costheta) / denom : 0;
 }
-ATN_HD V3 beckman_sample_dir(float roughness, const V3& wi, const V3& n, float r1, float r2)
+ATN_HD_COLD V3 beckman_sample_dir(float roughness, const V3& wi, const V3& n, float r1, float r2)
 {
     const float a2 = roughness * roughness;
     const float theta = atanf(sqrtf(-a2 * logf(1.0f - r1 * 0.99f)));
@@ -602,7 +621,7 @@ ATN_HD float beckman_G1(float roughness, const V3& v, const V3& n)
     if (a < 1.6f) return (3.535f * a + 2.181f * a2) / (1.0f + 2.276f * a + 2.577f * a2);
     return 1.0f;
 }
-ATN_HD V3 beckman_brdf(float roughness, float ior, const V3& n, const V3& wi, const V3& wo)
+ATN_HD_COLD V3 beckman_brdf(float roughness, float ior, const V3& n, const V3& wi, const V3& wo)
 {
     const V3 V = -wi;
     const V3 L = wo;
@@ -634,7 +653,7 @@ ATN_HD V3 refraction_brdf(float ni, float nt, const V3& wo, const V3& n, float T
     const float bsdf = c == 0.0f ? 0.0f : (nt_ni * nt_ni) * T / c;
     return V3(bsdf);
 }
-ATN_HD void refraction_sample(MtrlSample* result, Sampler* sampler, const Mtrl& param, const V3& n, const V3& wi)
+ATN_HD_COLD void refraction_sample(MtrlSample* result, Sampler* sampler, const Mtrl& param, const V3& n, const V3& wi)
 {
     float ni = 1.0f;
     float nt = param.s.ior;
@@ -772,7 +791,7 @@ ATN_HD void disney_eval_rest(const Mtrl& m, float w[4], const V3& V, const V3& w
                        *pdf += w[2] * disney_specular_pdf(m.s.roughness, V, wo, N); }
     if (w[3] > 0.0f) { *cc = disney_clearcoat_brdf(m.s.clearcoat, V, wo); *pdf += w[3] * disney_clearcoat_pdf(m.s.roughness, V, wo, N); }
 }
-ATN_HD float disney_pdf(const Mtrl& m, const V3& n, const V3& wi, const V3& wo)     // disney_brdf.cpp:338-369
+ATN_HD_COLD float disney_pdf(const Mtrl& m, const V3& n, const V3& wi, const V3& wo)     // disney_brdf.cpp:338-369
 {
     float w[4];
     disney_weights(w, V3(m.baseColor), m.s.metallic, m.s.sheen, m.s.specular, m.s.clearcoat);
@@ -784,7 +803,7 @@ ATN_HD float disney_pdf(const Mtrl& m, const V3& n, const V3& wi, const V3& wo) 
     pdf += w[3] * disney_clearcoat_pdf(m.s.clearcoatGloss, V, wo, n);
     return pdf;
 }
-ATN_HD MtrlSample disney_bsdf(const Mtrl& m, const V3& n, const V3& wi, const V3& wo)
+ATN_HD_COLD MtrlSample disney_bsdf(const Mtrl& m, const V3& n, const V3& wi, const V3& wo)
 {
     float w[4];
     disney_weights(w, V3(m.baseColor), m.s.metallic, m.s.sheen, m.s.specular, m.s.clearcoat);
@@ -799,7 +818,7 @@ ATN_HD MtrlSample disney_bsdf(const Mtrl& m, const V3& n, const V3& wi, const V3
     r.dir = V3(0.0f);
     return r;
 }
-ATN_HD void disney_sample(MtrlSample* result, const Mtrl& m, const V3& n, const V3& wi, Sampler* sampler)
+ATN_HD_COLD void disney_sample(MtrlSample* result, const Mtrl& m, const V3& n, const V3& wi, Sampler* sampler)
 {
     const float r1 = sampler->next();
     const float r2 = sampler->next();
@@ -934,7 +953,7 @@ ATN_HD void dir_to_uv(const V3& dir, float* u, float* v)
     *v = 1 - theta / kPi;
 }
 // Background::SampleFromRay (background.h:34-62)
-ATN_HD AtnVec4 background_sample(const SceneView& sc, const V3& dir)
+ATN_HD_CALL AtnVec4 background_sample(const SceneView& sc, const V3& dir)
 {
     if (sc.cfg.envmap_tex_idx < 0 || !sc.cfg.enable_env_map) {
         AtnVec4 c; c.x = sc.cfg.bg_color.x; c.y = sc.cfg.bg_color.y; c.z = sc.cfg.bg_color.z; c.w = 0.0f;
@@ -956,7 +975,7 @@ ATN_HD float ibl_pdf(const V3& clr, float avg_illum)
 
 // triangle::SamplePosAndNormal (triangle.h:122-162) + PolygonObject::SamplePosAndNormal
 // (PolygonObject.h:114-156) + AreaLight::sample (arealight.h:37-143)
-ATN_HD bool area_light_sample(LightSample* result, const AtnLightParameter& light, const SceneView& sc,
+ATN_HD_CALL bool area_light_sample(LightSample* result, const AtnLightParameter& light, const SceneView& sc,
                               const V3& org, Sampler* sampler)
 {
     if (light.arealight_objid < 0) return false;
@@ -1015,7 +1034,7 @@ ATN_HD bool area_light_sample(LightSample* result, const AtnLightParameter& ligh
 }
 
 // Light::sample dispatch (src/libaten/light/light_impl.h:13-44)
-ATN_HD void light_sample(LightSample* r, const AtnLightParameter& light, const SceneView& sc,
+ATN_HD_CALL void light_sample(LightSample* r, const AtnLightParameter& light, const SceneView& sc,
                          const V3& org, const V3& nml, Sampler* sampler)
 {
     r->pos = V3(0.0f); r->dir = V3(0.0f); r->dist = 0.0f; r->nml = V3(0.0f); r->color = V3(0.0f); r->pdf = 0.0f;
@@ -1088,7 +1107,7 @@ ATN_HD void light_sample(LightSample* r, const AtnLightParameter& light, const S
 }
 
 // ComputeRadianceNEE (src/libaten/renderer/pathtracing/pathtracing_nee_impl.h:23-95)
-ATN_HD bool radiance_nee(V3* out, const SceneView& sc, const V3& wi, const V3& nml, const Mtrl& m,
+ATN_HD_CALL bool radiance_nee(V3* out, const SceneView& sc, const V3& wi, const V3& nml, const Mtrl& m,
                          float u, float v, float light_select_prob, const LightSample& ls)
 {
     const float cosShadow = dot(nml, ls.dir);
@@ -1162,16 +1181,21 @@ ATN_HD void shade_miss(const SceneView& sc, const AtnCameraParameter& cam, int32
 }
 
 // aten::PathTracing::shade (src/libaten/renderer/pathtracing/pathtracing.cpp:91-236): the HOST
-// order (normal flipped, then normal map), with HitImplicitLight
-// (pathtracing_impl.h:395-452), FillShadowRay / SampleLight (:178-264), ComputeRussianProbability
-// (:680-698) and PrepareForNextBounce (:700-743).
-ATN_HD void shade_hit(const SceneView& sc, const Ray& ray, int32_t objid, int32_t primid, float a, float b,
-                      float t, int32_t mtrlid, int32_t bounce, int32_t rr_bounce,
-                      PathState* st, ShadowRayOut* sh, Ray* next_ray)
-{
-    sh->active = false;
-    if (st->terminated) return;
+// order (normal flipped, then normal map), in three stages that hand over a small
+// Surface record.  On the GPU each stage is its own kernel (the monolithic shade kernel was
+// instruction-fetch bound); the CPU restatement simply calls them in a row (shade_hit below).
+struct Surface {
+    V3 p; float u;          // hit position, texture u
+    V3 n; float v;          // orienting normal after flip + normal map, texture v
+    V3 albedo; int32_t mtrlid;
+};
 
+// Stage 1: evaluate_hit, FillMaterial, albedo, HitTeminatedMaterial -> HitImplicitLight
+// (pathtracing_impl.h:395-452), normal orientation + material::applyNormal.
+// Returns false when the path ended here (implicit light).
+ATN_HD bool shade_surface(const SceneView& sc, const Ray& ray, int32_t objid, int32_t primid, float a, float b,
+                          float t, int32_t mtrlid, int32_t bounce, PathState* st, Surface* sf)
+{
     const AtnObjectParameter obj = sc.objects[objid];
     HitRecord rec;
     evaluate_hit(sc, obj, ray, primid, a, b, t, mtrlid, &rec);
@@ -1181,9 +1205,7 @@ ATN_HD void shade_hit(const SceneView& sc, const Ray& ray, int32_t objid, int32_
 
     const Mtrl mtrl = fill_material(sc, rec.mtrlid);
     const AtnVec4 albedo4 = sample_texture(sc, mtrl.albedoMap, rec.u, rec.v, mtrl.baseColor);
-    const V3 albedo(albedo4);
 
-    // HitTeminatedMaterial -> HitImplicitLight
     if (mtrl.type == ATN_MTRL_EMISSIVE) {
         if (mtrl.is_emissive() && !backfacing && obj.light_id >= 0) {
             const AtnLightParameter& light = sc.lights[obj.light_id];
@@ -1202,15 +1224,23 @@ ATN_HD void shade_hit(const SceneView& sc, const Ray& ray, int32_t objid, int32_
             const V3 c = st->throughput * weight * light_color;
             st->contrib = st->contrib + c;
             st->terminated = true;
-            return;
+            return false;
         }
     }
 
     if (!mtrl.is_translucent() && backfacing) orienting = -orienting;
-
     orienting = apply_normal_map(sc, mtrl.normalMap, orienting, rec.u, rec.v);
 
-    // FillShadowRay
+    sf->p = rec.p; sf->u = rec.u; sf->n = orienting; sf->v = rec.v;
+    sf->albedo = V3(albedo4); sf->mtrlid = rec.mtrlid;
+    return true;
+}
+
+// Stage 2: FillShadowRay / SampleLight (pathtracing_impl.h:178-264) + ComputeRadianceNEE.
+ATN_HD void shade_nee(const SceneView& sc, const V3& ray_dir, const Surface& sf, PathState* st, ShadowRayOut* sh)
+{
+    sh->active = false;
+    const Mtrl mtrl = fill_material(sc, sf.mtrlid);
     const int32_t lightnum = sc.light_count;
     if (lightnum > 0 && !(mtrl.is_singular() || mtrl.is_translucent())) {
         int32_t target = (int32_t)(st->sampler.next() * lightnum);
@@ -1218,21 +1248,26 @@ ATN_HD void shade_hit(const SceneView& sc, const Ray& ray, int32_t objid, int32_
         const float select_prob = 1.0f / lightnum;
         const AtnLightParameter& light = sc.lights[target];
         LightSample ls;
-        light_sample(&ls, light, sc, rec.p, orienting, &st->sampler);
+        light_sample(&ls, light, sc, sf.p, sf.n, &st->sampler);
 
         sh->dir = normalize(ls.dir);
-        sh->dist = length(ls.pos - rec.p);
-        sh->org = ray_offset(rec.p, orienting);
+        sh->dist = length(ls.pos - sf.p);
+        sh->org = ray_offset(sf.p, sf.n);
         sh->light_id = target;
         sh->lightcontrib = V3(0.0f);
         V3 radiance;
-        if (radiance_nee(&radiance, sc, ray.dir, orienting, mtrl, rec.u, rec.v, select_prob, ls)) {
-            sh->lightcontrib = st->throughput * radiance * albedo;
+        if (radiance_nee(&radiance, sc, ray_dir, sf.n, mtrl, sf.u, sf.v, select_prob, ls)) {
+            sh->lightcontrib = st->throughput * radiance * sf.albedo;
             sh->active = true;
         }
     }
+}
 
-    // ComputeRussianProbability
+// Stage 3: ComputeRussianProbability (:680-698), material::sampleMaterial, PrepareForNextBounce (:700-743).
+ATN_HD void shade_bsdf(const SceneView& sc, const V3& ray_dir, const Surface& sf, int32_t bounce, int32_t rr_bounce,
+                       PathState* st, Ray* next_ray)
+{
+    const Mtrl mtrl = fill_material(sc, sf.mtrlid);
     float russian_prob = 1.0f;
     if (bounce > rr_bounce) {
         if (squared_length(st->throughput) > 0) {
@@ -1244,16 +1279,15 @@ ATN_HD void shade_hit(const SceneView& sc, const Ray& ray, int32_t objid, int32_
 
     MtrlSample smp;
     smp.dir = V3(0.0f); smp.bsdf = V3(0.0f); smp.pdf = 0.0f;
-    sample_material(&smp, sc, mtrl, orienting, ray.dir, &st->sampler, rec.u, rec.v);
+    sample_material(&smp, sc, mtrl, sf.n, ray_dir, &st->sampler, sf.u, sf.v);
 
-    // PrepareForNextBounce
     const V3 next_dir = normalize(smp.dir);
     const float pdfb = smp.pdf;
-    V3 along = orienting;
+    V3 along = sf.n;
     along = dot(along, next_dir) >= 0.0f ? along : -along;
     const float c = dot(along, next_dir);
     if (pdfb > 0 && c > 0) {
-        st->throughput = st->throughput * (albedo * smp.bsdf * c / pdfb);
+        st->throughput = st->throughput * (sf.albedo * smp.bsdf * c / pdfb);
         st->throughput = st->throughput / russian_prob;
     }
     else {
@@ -1262,7 +1296,19 @@ ATN_HD void shade_hit(const SceneView& sc, const Ray& ray, int32_t objid, int32_
     if (st->terminated) return;
     st->pdfb = pdfb;
     st->singular = mtrl.is_singular();
-    *next_ray = make_ray(rec.p, next_dir, along);
+    *next_ray = make_ray(sf.p, next_dir, along);
+}
+
+ATN_HD void shade_hit(const SceneView& sc, const Ray& ray, int32_t objid, int32_t primid, float a, float b,
+                      float t, int32_t mtrlid, int32_t bounce, int32_t rr_bounce,
+                      PathState* st, ShadowRayOut* sh, Ray* next_ray)
+{
+    sh->active = false;
+    if (st->terminated) return;
+    Surface sf;
+    if (!shade_surface(sc, ray, objid, primid, a, b, t, mtrlid, bounce, st, &sf)) return;
+    shade_nee(sc, ray.dir, sf, st, sh);
+    shade_bsdf(sc, ray.dir, sf, bounce, rr_bounce, st, next_ray);
 }
 
 // Decision after the shadow ray's closest-hit traversal: HitTestToTargetLight

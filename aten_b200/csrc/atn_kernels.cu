@@ -540,13 +540,13 @@ __device__ __forceinline__ int warp_append(bool pred, int32_t* counter)
 }
 
 #ifndef ATN_SURFACE_MIN_BLOCKS
-#define ATN_SURFACE_MIN_BLOCKS 10
+#define ATN_SURFACE_MIN_BLOCKS 8
 #endif
 #ifndef ATN_NEE_MIN_BLOCKS
-#define ATN_NEE_MIN_BLOCKS 10
+#define ATN_NEE_MIN_BLOCKS 8
 #endif
 #ifndef ATN_BSDF_MIN_BLOCKS
-#define ATN_BSDF_MIN_BLOCKS 10
+#define ATN_BSDF_MIN_BLOCKS 8
 #endif
 constexpr int kShadeBlock = 128;
 

@@ -23,7 +23,7 @@ EXPORTS = [
     "atn_set_frame", "atn_get_frame", "atn_reset", "atn_set_progressive", "atn_set_hit_distance_limit",
     "atn_render", "atn_render_region", "atn_synchronize", "atn_readback", "atn_device_image", "atn_get_stats",
     "atn_set_profiling", "atn_get_stream", "atn_trace_closest", "atn_trace_any", "atn_trace_closest_device",
-    "atn_trace_any_device", "atn_set_bounce_tap",
+    "atn_trace_any_device", "atn_set_bounce_tap", "atn_trace_closest_static",
 ]
 
 
@@ -216,6 +216,21 @@ class PathTracing:
         hits = np.zeros(len(rays), sio.HIT_DTYPE)
         tm = None if t_max is None else np.ascontiguousarray(t_max, np.float32)
         _check(self._lib, self._lib.atn_trace_closest(
+            self._h, C.c_void_p(rays.ctypes.data), C.c_void_p(tm.ctypes.data) if tm is not None else None,
+            C.c_size_t(len(rays)), C.c_void_p(hits.ctypes.data)))
+        return hits
+
+    STATIC_MAX_RAYS = 65536
+
+    def trace_closest_static(self, rays: np.ndarray, t_max: np.ndarray | None = None) -> np.ndarray:
+        """``trace_closest`` through ``atn_trace_closest_static``: for hosts that may not allocate device
+        memory (fixed, already spent memory budget; frame loops that cannot stall on cudaMalloc).  Rays
+        and hits are staged in a fixed array inside the library, so a call takes at most
+        ``STATIC_MAX_RAYS`` rays, and calls on the same GPU must not overlap."""
+        rays = np.ascontiguousarray(rays, sio.RAY_DTYPE)
+        hits = np.zeros(len(rays), sio.HIT_DTYPE)
+        tm = None if t_max is None else np.ascontiguousarray(t_max, np.float32)
+        _check(self._lib, self._lib.atn_trace_closest_static(
             self._h, C.c_void_p(rays.ctypes.data), C.c_void_p(tm.ctypes.data) if tm is not None else None,
             C.c_size_t(len(rays)), C.c_void_p(hits.ctypes.data)))
         return hits

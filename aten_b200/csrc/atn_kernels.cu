@@ -27,6 +27,7 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <stdarg.h>
+#include <mutex>
 #include <string>
 #include <vector>
 #include <algorithm>
@@ -1336,3 +1337,75 @@ ATN_API int atn_trace_any(AtnRenderer* r, const AtnRay* rays, const float* dist,
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// atn_trace_closest_static: closest-hit query that allocates nothing
+// ---------------------------------------------------------------------------------------------
+// atn_trace_closest stages the caller's host rays and hits in device buffers that it (re)allocates
+// with cudaMalloc whenever a call is larger than the last one.  Some hosts cannot afford that: a
+// renderer or simulation that was given a fixed device-memory budget at start-up and has spent it
+// (an engine arena, a process that shares the GPU with a framework allocator which already took the
+// rest), so cudaMalloc may simply fail mid-frame; and interactive code (picking, line-of-sight
+// queries inside a frame loop) for which cudaMalloc's device-wide synchronisation is a visible
+// stall.  For them the staging area lives in the library image itself: one file-scope __device__
+// array per GPU, sized for kStaticMaxRays rays, present from the moment the library is loaded on a
+// device until the process exits (about 3.9 MB per GPU).
+constexpr size_t kStaticMaxRays = 65536;
+
+struct StaticScratch {
+    int32_t cursor;                    // work-fetch cursor of the persistent traversal kernel
+    int32_t pad[63];                   // keeps the arrays below 256-byte aligned
+    AtnRay rays[kStaticMaxRays];
+    float t_max[kStaticMaxRays];
+    AtnHit hits[kStaticMaxRays];
+};
+
+// In host code this name is only a handle for cudaGetSymbolAddress; it is NOT a device address.
+static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScratch)];
+
+constexpr int kMaxDevices = 64;
+static std::mutex g_static_mutex;
+static StaticScratch* g_static_ptr[kMaxDevices] = {};     // device address of g_static_scratch, per GPU
+
+// Looks up (once per GPU, with that GPU current) where g_static_scratch lives on the device.
+static int static_scratch_for_device(int device, StaticScratch** out)
+{
+    if (device < 0 || device >= kMaxDevices)
+        return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_trace_closest_static: device ordinal %d not supported (max %d)", device, kMaxDevices - 1);
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!g_static_ptr[device]) {
+        void* p = nullptr;
+        CUDA_TRY(cudaSetDevice(device));
+        CUDA_TRY(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p) return set_error(ATN_ERR_CUDA, "atn_trace_closest_static: cudaGetSymbolAddress returned NULL");
+        g_static_ptr[device] = static_cast<StaticScratch*>(p);
+    }
+    *out = g_static_ptr[device];
+    return ATN_OK;
+}
+
+extern "C" ATN_API int atn_trace_closest_static(AtnRenderer* r, const AtnRay* rays, const float* t_max, size_t n, AtnHit* hits)
+{
+    if (!r || (n && (!rays || !hits))) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_trace_closest_static: NULL argument");
+    if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_trace_closest_static: no scene uploaded");
+    if (n > kStaticMaxRays)
+        return set_error(ATN_ERR_TOO_LARGE, "atn_trace_closest_static: %zu rays exceed the static staging area of %zu rays; "
+                         "split the batch or use atn_trace_closest", n, kStaticMaxRays);
+    if (n == 0) return ATN_OK;
+    StaticScratch* sc = nullptr;
+    const int rc = static_scratch_for_device(r->device, &sc);       // first call on a GPU: address look-up
+    if (rc != ATN_OK) return rc;
+    CUDA_TRY(cudaSetDevice(r->device));
+    cudaStream_t s = r->stream;
+    // The array keeps whatever the previous call left in it: the cursor must restart at zero; rays,
+    // bounds and hits are fully overwritten for [0, n) and never read beyond n.
+    CUDA_TRY(cudaMemsetAsync(&sc->cursor, 0, sizeof(int32_t), s));
+    CUDA_TRY(cudaMemcpyAsync(sc->rays, rays, n * sizeof(AtnRay), cudaMemcpyHostToDevice, s));
+    if (t_max) CUDA_TRY(cudaMemcpyAsync(sc->t_max, t_max, n * sizeof(float), cudaMemcpyHostToDevice, s));
+    QueryClosestPolicy pol{ sc->rays, t_max ? sc->t_max : nullptr, sc->hits };
+    k_trace<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &sc->cursor);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(hits, sc->hits, n * sizeof(AtnHit), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    return ATN_OK;
+}

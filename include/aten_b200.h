@@ -283,6 +283,21 @@ ATN_API int atn_trace_closest_device(AtnRenderer* r, const void* rays_dev, const
 ATN_API int atn_trace_any_device(AtnRenderer* r, const void* rays_dev, const void* dist_dev,
                                  size_t n, void* visible_dev);
 
+/* No counterpart in the reference.  Same query as atn_trace_closest (host rays in, host hits out,
+ * t_max may be NULL) for callers that must not allocate device memory: hosts that run inside a fixed
+ * device-memory budget which is already spent (so a cudaMalloc may fail), and frame loops that cannot
+ * take cudaMalloc's device-wide synchronisation.  Rays and hits are staged in an array that is part of
+ * the library image on every GPU it is loaded on (~3.9 MB, held until the process exits) instead of
+ * buffers grown on demand; the call performs no cudaMalloc / cudaFree and calls no allocating routine.
+ *   - at most 65536 rays per call; more is refused with ATN_ERR_TOO_LARGE (split the batch);
+ *   - the first call on each GPU looks the array's device address up (cudaGetSymbolAddress); make that
+ *     first call before any stream capture begins;
+ *   - all handles and threads on one GPU share the one array: calls that overlap on the GPU race and
+ *     corrupt each other's rays and hits -- serialise them (one call at a time per GPU).
+ * Synchronous: returns when `hits` is filled. */
+ATN_API int atn_trace_closest_static(AtnRenderer* r, const AtnRay* rays, const float* t_max /* may be NULL */,
+                                     size_t n, AtnHit* hits);
+
 /* ---- debug / parity taps ------------------------------------------------------------------------ */
 /* Per-bounce dump of the wavefront state for parity tests: after atn_render with a tap installed,
  * `records` holds one AtnBounceRecord per (pixel, bounce) for the LAST sample rendered.

@@ -45,7 +45,8 @@ def assert_hits_equal(got, ref, max_near_tie_rate=3e-4):
     rays on which two primitives are hit within 1e-5 relative distance of each other.  The reference
     walks its tree in a fixed left-first order with a slab test biased by +1e-6 (aabb.h:68) and a
     running t_max, so which of two such primitives it reports depends on its visit order; the GPU
-    traversal is ordered front to back and reports the nearer one.  Their rate is bounded here."""
+    traversal is ordered front to back and may report the other one of the pair (either way round:
+    the bias error of a box entry distance can exceed the gap).  Their rate is bounded here."""
     hit = ref["objid"] >= 0
     diff = (got["objid"] != ref["objid"]) | (hit & (got["primid"] != ref["primid"])) | (bits(got["t"]) != bits(ref["t"]))
     if diff.any():
@@ -53,8 +54,6 @@ def assert_hits_equal(got, ref, max_near_tie_rate=3e-4):
         assert (both == diff).all(), f"{(diff & ~both).sum()} hit/miss disagreements"
         rel = np.abs(got["t"][diff].astype(np.float64) - ref["t"][diff]) / ref["t"][diff]
         assert rel.max() <= 1e-5, f"distance differs by {rel.max():.3g} relative"
-        # with the culling slack of the kernel the GPU never reports the farther of the two
-        assert (got["t"][diff] <= ref["t"][diff]).all(), "GPU reported a farther hit than the reference"
         assert diff.mean() <= max_near_tie_rate, f"near-tie rate {diff.mean():.2e}"
     same = ~diff
     hs = hit & same
@@ -271,3 +270,46 @@ def test_full_size_properties(golden):
     a, b = float(prog[..., :3].mean()), float(ref[..., :3].mean())
     assert abs(a - b) / b < 0.05, (a, b)
     r.close()
+
+
+# ---- live checks against the reference binary (oracle/_ref travels with the repo) ---------------
+needs_ref = pytest.mark.skipif(not ol.have_ref(), reason="oracle/_ref (reference compiled in place) not present")
+
+
+@needs_ref
+@pytest.mark.parametrize("name,W,H", [("sponza_tex", 96, 54), ("instanced_dragon", 80, 45)])
+def test_live_reference_textured_and_large_scene(name, W, H):
+    """Configs C3/C4 stand-ins, produced live by the reference on this box: Sponza with the .mtl's
+    albedo + normal maps (host point sampling, texture.cpp:64-75), and the instanced scene with the
+    100k-triangle dragon (SBVH built by the reference's own builder).  Primary hits bit-exact, every
+    ray the reference traced re-traced on the GPU, image within tolerance."""
+    scene = ol.ref_scene(name, W, H)
+    ref, img_ref, info = ol.ref_trace(name, W, H, frame=1)
+    r = PathTracing(0)
+    r.UpdateSceneData(scene)
+    try:
+        valid = (ref["flags"] & 1) != 0
+        rays = np.ascontiguousarray(ref["ray"][valid])
+        want = np.ascontiguousarray(ref["hit"][valid]).copy()
+        want["primid"][want["objid"] < 0] = -1
+        got = r.trace_closest(rays)
+        want["meshid"] = got["meshid"]
+        assert_hits_equal(got, want, max_near_tie_rate=1e-3)
+        r.set_frame(1)
+        tap = r.set_bounce_tap(5)
+        r.render(W, H, 1, 5, 3)
+        r.set_bounce_tap(None)
+        img = r.readback()
+        hit0 = ref[:, 0]["hit"]["objid"] >= 0
+        assert (tap[:, 0]["hit"]["primid"][hit0] == ref[:, 0]["hit"]["primid"][hit0]).all()
+        assert (bits(tap[:, 0]["hit"]["t"]) == bits(ref[:, 0]["hit"]["t"])).all()
+        a = img[..., :3].reshape(-1, 3); b = img_ref[..., :3].reshape(-1, 3)
+        rmse = np.sqrt(np.mean((a - b) ** 2)); scale = np.sqrt(np.mean(b ** 2))
+        assert rmse <= 5e-3 * scale, (rmse, scale)
+        close = (np.abs(a - b) <= 1e-3 * np.maximum(np.abs(b), 1e-3)).all(axis=1).mean()
+        assert close > 0.97, close
+        st = r.stats()
+        assert abs(st["closest_rays"] - info["closest_rays"]) <= 0.01 * info["closest_rays"]
+        assert abs(st["shadow_rays"] - info["shadow_rays"]) <= 0.02 * info["shadow_rays"] + 5
+    finally:
+        r.close()

@@ -33,7 +33,8 @@ class AtnError(RuntimeError):
 
 class AtnStats(C.Structure):
     _fields_ = [("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("camera_samples", C.c_uint64),
-                ("kernel_launches", C.c_uint64), ("device_ms", C.c_float), ("trace_ms", C.c_float)]
+                ("kernel_launches", C.c_uint64), ("device_ms", C.c_float), ("trace_ms", C.c_float),
+                ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64)]
 
 
 _lib = None

@@ -20,6 +20,8 @@
 
 #include <stdint.h>
 #include <string.h>
+#include <algorithm>
+#include <cmath>
 #include <string>
 #include <vector>
 
@@ -111,6 +113,49 @@ struct ListBuilder {
         return leaf_ref((int32_t)out->tris.size() - 1);
     }
 
+    // Conservative bounds of a leaf: the triangle's own AABB, or the AABB of the instance's root box
+    // (bottom list node 0) carried to world space by its L2W matrix.
+    void leaf_bounds(int32_t ref, float mn[3], float mx[3]) const
+    {
+        const int32_t idx = ~ref;
+        if (!top) {
+            const TriLeaf& t = out->tris[idx];
+            for (int a = 0; a < 3; a++) {
+                const float p0 = t.v0[a], p1 = t.v0[a] + t.e1[a], p2 = t.v0[a] + t.e2[a];
+                // v0 + (v1 - v0) may round away from v1 by an ulp: widen by one ulp-ish step
+                const float lo = std::min(p0, std::min(p1, p2)), hi = std::max(p0, std::max(p1, p2));
+                const float pad = 4e-7f * std::max(std::fabs(lo), std::fabs(hi)) + 1e-30f;
+                mn[a] = lo - pad; mx[a] = hi + pad;
+            }
+            return;
+        }
+        const InstLeaf& il = out->insts[idx];
+        const AtnObjectParameter& obj = scene->objects[il.objid];
+        // find the bottom list of this instance again: its root box is node 0 of that list
+        const AtnBvhNode* root = nullptr;
+        for (uint32_t k = 1; k < scene->node_list_count; k++) {
+            if ((*list_roots)[k] == il.root && scene->node_list_sizes[k] > 0) { root = &scene->node_lists[k][0]; break; }
+        }
+        const float big = 3.0e38f;
+        if (!root) { for (int a = 0; a < 3; a++) { mn[a] = -big; mx[a] = big; } return; }
+        float M[16] = { 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1 };
+        if (obj.mtx_id >= 0 && (uint32_t)obj.mtx_id < scene->matrix_count) memcpy(M, scene->matrices[obj.mtx_id].m, sizeof(M));
+        for (int a = 0; a < 3; a++) { mn[a] = big; mx[a] = -big; }
+        for (int c = 0; c < 8; c++) {
+            const double x = (c & 1) ? root->boxmax[0] : root->boxmin[0];
+            const double y = (c & 2) ? root->boxmax[1] : root->boxmin[1];
+            const double z = (c & 4) ? root->boxmax[2] : root->boxmin[2];
+            for (int a = 0; a < 3; a++) {
+                const double w = M[a * 4 + 0] * x + M[a * 4 + 1] * y + M[a * 4 + 2] * z + M[a * 4 + 3];
+                mn[a] = std::min(mn[a], (float)w); mx[a] = std::max(mx[a], (float)w);
+            }
+        }
+        for (int a = 0; a < 3; a++) {
+            const float pad = 1e-5f * std::max(std::fabs(mn[a]), std::fabs(mx[a])) + 1e-6f;
+            mn[a] -= pad; mx[a] += pad;
+        }
+    }
+
     // Children of inner node i: c = hit(i); while c != miss(i): take c, c = miss(c).
     // Emits nodes in depth-first order so that leaf numbers follow the reference's visit order.
     int32_t build(int32_t i, int32_t depth)
@@ -142,6 +187,11 @@ struct ListBuilder {
         float rmin[3] = { big, big, big }, rmax[3] = { -big, -big, -big };
         for (int a = 0; a < 3; a++) { lmin[a] = list[kids[0]].boxmin[a]; lmax[a] = list[kids[0]].boxmax[a]; }
         if (nk == 2) for (int a = 0; a < 3; a++) { rmin[a] = list[kids[1]].boxmin[a]; rmax[a] = list[kids[1]].boxmax[a]; }
+        // The reference never reads a LEAF's box (threaded_bvh_traverser.h:142-220), and SBVH leaf boxes
+        // are clipped pieces that need not contain the triangle.  The slot is re-used for a box that is
+        // conservative by construction; the kernels use it only as a pre-filter (leaf_margin).
+        if (refs[0] < 0 && refs[0] != kRefNull) leaf_bounds(refs[0], lmin, lmax);
+        if (nk == 2 && refs[1] < 0 && refs[1] != kRefNull) leaf_bounds(refs[1], rmin, rmax);
         pn.n0[0] = lmin[0]; pn.n0[1] = lmax[0]; pn.n0[2] = lmin[1]; pn.n0[3] = lmax[1];
         pn.n1[0] = rmin[0]; pn.n1[1] = rmax[0]; pn.n1[2] = rmin[1]; pn.n1[3] = rmax[1];
         pn.n2[0] = lmin[2]; pn.n2[1] = lmax[2]; pn.n2[2] = rmin[2]; pn.n2[3] = rmax[2];

@@ -102,6 +102,8 @@ struct Counters {
 
 // Ray totals of one atn_render call (not cleared per sample).
 struct Totals { unsigned long long closest, shadow; };
+// Traversal work of one call: PairNodes fetched and triangle tests run (all lanes, all traversal kernels).
+struct Visits { unsigned long long nodes, tris; };
 
 struct PathBuffers {
     float4* ray_o;        // org.xyz, -
@@ -179,7 +181,7 @@ __device__ __forceinline__ TriHit intersect_triangle_edges(const V3& org, const 
 // the reference's std::min/std::max only when an operand is NaN, which needs a direction component
 // equal to -1e-6f exactly (1/(dir + 1e-6) = inf); DESIGN.md lists this as not reproduced.
 __device__ __forceinline__ bool slab_test(const RayInv& ri, float minx, float maxx, float miny, float maxy,
-                                          float minz, float maxz, float t_min, float t_max, float* t0_out)
+                                          float minz, float maxz, float t_min, float t_max, float* t0_out, float* t1_out)
 {
     const float fx = maxx * ri.invdir.x + ri.oxinvdir.x;
     const float fy = maxy * ri.invdir.y + ri.oxinvdir.y;
@@ -187,10 +189,43 @@ __device__ __forceinline__ bool slab_test(const RayInv& ri, float minx, float ma
     const float nx = minx * ri.invdir.x + ri.oxinvdir.x;
     const float ny = miny * ri.invdir.y + ri.oxinvdir.y;
     const float nz = minz * ri.invdir.z + ri.oxinvdir.z;
-    const float t1 = fminf(fminf(fminf(fmaxf(fx, nx), fmaxf(fy, ny)), fmaxf(fz, nz)), t_max);
+    const float t1raw = fminf(fminf(fmaxf(fx, nx), fmaxf(fy, ny)), fmaxf(fz, nz));
     const float t0 = fmaxf(fmaxf(fmaxf(fminf(fx, nx), fminf(fy, ny)), fminf(fz, nz)), t_min);
     *t0_out = t0;
-    return t0 <= t1;
+    *t1_out = t1raw;                       // exit distance, not clamped by t_max (leaf filter uses its own bound)
+    return t0 <= fminf(t1raw, t_max);
+}
+
+// Leaf pre-filter.  The reference never box-tests a leaf: it runs the triangle test (or enters the
+// instance) for every leaf whose parent box was hit, ~8 triangle tests per ray on Sponza of which one
+// succeeds.  On the GPU those tests run for a handful of lanes at a time and dominated the issue
+// slots.  The child-box slot of a leaf in a PairNode is free (the reference never reads a leaf's
+// box), so the encoder stores there a box that is conservative BY CONSTRUCTION -- the triangle's own
+// AABB, or the world AABB of an instance's transformed root box (atn_bvh.h) -- and the kernel skips a
+// leaf when the ray misses that box by a safe margin: if the reference's Moeller-Trumbore test
+// accepts a triangle, the hit point lies (to float accuracy) inside the triangle's AABB and the
+// relaxed test below passes.  Far bound: the running hit distance only (the reference's triangle test
+// ignores the caller's t_max, threaded_bvh_traverser.h:198-200).
+//   margin in t:  2e-4 (|t0| + |t1|)          covers the +1e-6 direction bias, <= 5e-5 relative for |d_k| >= 0.02
+//               + 1e-6 sum_k |org_k / d_k|    covers the rounding of plane*inv - org*inv
+//               + 5e-4 (1 + max_k |org_k|)    covers the triangle test's own error, mapped through 1/|d_k| <= 50
+// Rays with a direction component below 0.02 in magnitude are not filtered at all (their slab
+// distances are too ill-conditioned for a fixed margin): leaf_margin() returns a negative value.
+#ifndef ATN_LEAF_FILTER
+#define ATN_LEAF_FILTER 1
+#endif
+__device__ __forceinline__ float leaf_margin(const V3& org, const V3& dir, const RayInv& ri)
+{
+    if (!ATN_LEAF_FILTER) return -1.0f;
+    const float dmin = fminf(fminf(fabsf(dir.x), fabsf(dir.y)), fabsf(dir.z));
+    if (!(dmin >= 0.02f)) return -1.0f;
+    const float S = fabsf(ri.oxinvdir.x) + fabsf(ri.oxinvdir.y) + fabsf(ri.oxinvdir.z);
+    const float M = fmaxf(fmaxf(fabsf(org.x), fabsf(org.y)), fabsf(org.z));
+    return 1e-6f * S + 5e-4f * (1.0f + M);
+}
+__device__ __forceinline__ bool leaf_may_hit(float t0, float t1, float margin)
+{
+    return (margin < 0.0f) || (t0 <= t1 + 2e-4f * (fabsf(t0) + fabsf(t1)) + margin);
 }
 
 // ---- ray sources / sinks of the traversal kernel -------------------------------------------
@@ -316,11 +351,11 @@ struct QueryAnyPolicy {            // atn_trace_any
 #endif
 template <class Policy>
 __global__ void __launch_bounds__(kTraceBlock, ATN_TRACE_MIN_BLOCKS)
-k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch)
+k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch, Visits* visits)
 {
     __shared__ int32_t s_ref[kSmemStack * kTraceBlock];
     __shared__ float s_t0[kSmemStack * kTraceBlock];
-    __shared__ float s_world[12 * kTraceBlock];      // world-space org, dir, invdir, oxinvdir of the lane's ray
+    __shared__ float s_world[13 * kTraceBlock];      // world-space org, dir, invdir, oxinvdir, leaf margin of the lane's ray
     int32_t l_ref[kLocalStack];
     float l_t0[kLocalStack];
     int32_t* const my_ref = s_ref + threadIdx.x;
@@ -337,11 +372,12 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
     bool done = false;               // traversal complete, result not written yet (written at the next refill)
     bool exhausted = false;          // warp-uniform: the queue has no more rays
     int slot = 0, mode = EXIT_NONE, sp = 0, cur = kRefNull, cur_inst = -1;
-    float exit_dist = 0.0f, t_cull = kInf;
+    float exit_dist = 0.0f, t_cull = kInf, margin = -1.0f;
     V3 org, dir;
     RayInv ri;
     TraceResult best;
     best.t = kInf; best.a = 0.0f; best.b = 0.0f; best.leaf = -1; best.inst = -1;
+    uint32_t n_nodes = 0, n_tris = 0;     // work counters (folded into Visits once per warp)
 
     for (;;) {
         // ---------------- write results of completed rays (all such lanes together) ----------------
@@ -362,10 +398,12 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                     float t_max;
                     pol.load(i, &slot, &org, &dir, &t_max, &mode, &exit_dist);
                     ri = ray_inv(org, dir);
+                    margin = leaf_margin(org, dir, ri);
                     my_world[0 * kTraceBlock] = org.x; my_world[1 * kTraceBlock] = org.y; my_world[2 * kTraceBlock] = org.z;
                     my_world[3 * kTraceBlock] = dir.x; my_world[4 * kTraceBlock] = dir.y; my_world[5 * kTraceBlock] = dir.z;
                     my_world[6 * kTraceBlock] = ri.invdir.x; my_world[7 * kTraceBlock] = ri.invdir.y; my_world[8 * kTraceBlock] = ri.invdir.z;
                     my_world[9 * kTraceBlock] = ri.oxinvdir.x; my_world[10 * kTraceBlock] = ri.oxinvdir.y; my_world[11 * kTraceBlock] = ri.oxinvdir.z;
+                    my_world[12 * kTraceBlock] = margin;
                     t_cull = t_max;
                     best.t = kInf; best.a = 0.0f; best.b = 0.0f; best.leaf = -1; best.inst = -1;
                     sp = 0; cur = bv.top_root; cur_inst = -1;
@@ -391,12 +429,15 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                 const float4 n3 = ldg4(np + 3);
                 const int32_t left = __float_as_int(n3.x);
                 const int32_t right = __float_as_int(n3.y);
-                float t0l, t0r;
-                const bool bl = slab_test(ri, n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, t_min, t_cull, &t0l);
-                const bool br = slab_test(ri, n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, t_min, t_cull, &t0r);
-                // leaves are never box-tested by the reference: always taken, before boxes
-                const bool hl = (left >= 0) ? bl : (left != kRefNull);
-                const bool hr = (right >= 0) ? br : (right != kRefNull);
+                float t0l, t0r, t1l, t1r;
+                const bool bl = slab_test(ri, n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, t_min, t_cull, &t0l, &t1l);
+                const bool br = slab_test(ri, n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, t_min, t_cull, &t0r, &t1r);
+                // leaves are never box-tested by the reference: taken before boxes, unless the ray
+                // misses the leaf's box by a safe margin (see leaf_margin)
+                const float leaf_far = (best.leaf >= 0) ? t_cull : kInf;
+                const bool hl = (left >= 0) ? bl : (left != kRefNull && leaf_may_hit(t0l, fminf(t1l, leaf_far), margin));
+                const bool hr = (right >= 0) ? br : (right != kRefNull && leaf_may_hit(t0r, fminf(t1r, leaf_far), margin));
+                n_nodes++;
                 t0l = (left >= 0) ? t0l : -kInf;
                 t0r = (right >= 0) ? t0r : -kInf;
                 if (hl && hr) {
@@ -423,6 +464,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                 const float4 b = ldg4(tp + 1);
                 const float4 c = ldg4(tp + 2);
                 const TriHit h = intersect_triangle_edges(org, dir, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), V3(c.x, c.y, c.z));
+                n_tris++;
                 if (h.hit && h.t < kInf && t_min < h.t) {
                     const bool closer = h.t < best.t ||
                         (h.t == best.t && (cur_inst < best.inst || (cur_inst == best.inst && leaf < best.leaf)));
@@ -457,6 +499,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                                 const Ray tr = make_ray(mat_apply(m, org), mat_apply_xyz(m, dir));   // mat4::applyRay
                                 org = tr.org; dir = tr.dir;
                                 ri = ray_inv(org, dir);
+                                margin = leaf_margin(org, dir, ri);
                             }
                             cur = il.y;
                         }
@@ -480,6 +523,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                         dir = V3(my_world[3 * kTraceBlock], my_world[4 * kTraceBlock], my_world[5 * kTraceBlock]);
                         ri.invdir = V3(my_world[6 * kTraceBlock], my_world[7 * kTraceBlock], my_world[8 * kTraceBlock]);
                         ri.oxinvdir = V3(my_world[9 * kTraceBlock], my_world[10 * kTraceBlock], my_world[11 * kTraceBlock]);
+                        margin = my_world[12 * kTraceBlock];
                         continue;
                     }
                     if (t0 > t_cull) continue;          // subtree starts behind the current hit
@@ -488,6 +532,15 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
             }
             if (finished) { active = false; done = true; }
         }
+    }
+    // work counters: one atomic pair per warp
+    for (int o = 16; o > 0; o >>= 1) {
+        n_nodes += __shfl_xor_sync(full, n_nodes, o);
+        n_tris += __shfl_xor_sync(full, n_tris, o);
+    }
+    if (lane == 0 && visits) {
+        atomicAdd(&visits->nodes, (unsigned long long)n_nodes);
+        atomicAdd(&visits->tris, (unsigned long long)n_tris);
     }
 }
 
@@ -817,6 +870,7 @@ struct AtnRenderer {
     DevBuf<float4> surf0, surf1, surf2;
     DevBuf<Counters> counters;
     DevBuf<Totals> totals;
+    DevBuf<Visits> visits;
     PathBuffers pb{};
 
     // query scratch
@@ -881,6 +935,7 @@ static int alloc_paths(AtnRenderer* r, size_t n)
     CUDA_TRY(r->surf0.resize(n)); CUDA_TRY(r->surf1.resize(n)); CUDA_TRY(r->surf2.resize(n));
     CUDA_TRY(r->counters.resize(1));
     CUDA_TRY(r->totals.resize(1));
+    CUDA_TRY(r->visits.resize(1));
     PathBuffers& pb = r->pb;
     pb.ray_o = r->ray_o.p; pb.ray_d = r->ray_d.p; pb.hit0 = r->hit0.p; pb.hit1 = r->hit1.p;
     pb.throughput = r->throughput.p; pb.contrib = r->contrib.p; pb.sampler_dim = r->sampler_dim.p; pb.flags = r->flags.p;
@@ -1152,6 +1207,7 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
     const int gen_grid = std::min((n + 255) / 256, r->sm_count * 8);
 
     CUDA_TRY(cudaMemsetAsync(r->totals.p, 0, sizeof(Totals), s));
+    CUDA_TRY(cudaMemsetAsync(r->visits.p, 0, sizeof(Visits), s));
     CUDA_TRY(cudaEventRecord(r->ev0, s));
     for (int smp = sample_begin; smp < sample_end; smp++) {
         fp.frame = r->frame + (uint32_t)smp;
@@ -1167,7 +1223,7 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             {
                 ClosestPolicy pol{ r->pb, q, tmax };
-                k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[b], 0, &c->fetch_closest[b]);
+                k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[b], 0, &c->fetch_closest[b], r->visits.p);
             }
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             if (tap_now) k_surface<true><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, r->pb, c, b, r->tap_dev.p, r->tap_cap);
@@ -1178,11 +1234,11 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             if (tap_now) {
                 ShadowPolicy<true> pol{ r->pb, r->sv, r->tap_dev.p, r->tap_cap, b };
-                k_trace<ShadowPolicy<true>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b]);
+                k_trace<ShadowPolicy<true>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
             }
             else {
                 ShadowPolicy<false> pol{ r->pb, r->sv, nullptr, 0, b };
-                k_trace<ShadowPolicy<false>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b]);
+                k_trace<ShadowPolicy<false>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
             }
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             launches += 5;
@@ -1196,10 +1252,14 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
     // Exact ray counts: k_gather folds every sample's queue counters into Totals on the device.
     Totals ht;
     CUDA_TRY(cudaMemcpyAsync(&ht, r->totals.p, sizeof(Totals), cudaMemcpyDeviceToHost, s));
+    Visits hv;
+    CUDA_TRY(cudaMemcpyAsync(&hv, r->visits.p, sizeof(Visits), cudaMemcpyDeviceToHost, s));
     if (tap) CUDA_TRY(cudaMemcpyAsync(r->tap_host, r->tap_dev.p, (size_t)n * r->tap_cap * sizeof(AtnBounceRecord), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaStreamSynchronize(s));
     r->stats.closest_rays = ht.closest;
     r->stats.shadow_rays = ht.shadow;
+    r->stats.nodes_visited = hv.nodes;
+    r->stats.tris_tested = hv.tris;
     r->stats.camera_samples = (uint64_t)n * (uint64_t)spp;
     r->stats.kernel_launches = launches;
     float ms = 0.0f;
@@ -1260,14 +1320,16 @@ static int query_launch(AtnRenderer* r, const void* rays_dev, const void* f_dev,
     cudaStream_t s = r->stream;
     CUDA_TRY(r->counters.resize(1));
     CUDA_TRY(cudaMemsetAsync(&r->counters.p->fetch_query, 0, sizeof(int32_t), s));
+    CUDA_TRY(r->visits.resize(1));
+    CUDA_TRY(cudaMemsetAsync(r->visits.p, 0, sizeof(Visits), s));
     CUDA_TRY(cudaEventRecord(r->ev0, s));
     if (any) {
         QueryAnyPolicy pol{ (const AtnRay*)rays_dev, (const float*)f_dev, (uint8_t*)out_dev };
-        k_trace<QueryAnyPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query);
+        k_trace<QueryAnyPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
     }
     else {
         QueryClosestPolicy pol{ (const AtnRay*)rays_dev, (const float*)f_dev, (AtnHit*)out_dev };
-        k_trace<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query);
+        k_trace<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
     }
     CUDA_TRY(cudaEventRecord(r->ev1, s));
     CUDA_TRY(cudaGetLastError());
@@ -1403,7 +1465,7 @@ extern "C" ATN_API int atn_trace_closest_static(AtnRenderer* r, const AtnRay* ra
     CUDA_TRY(cudaMemcpyAsync(sc->rays, rays, n * sizeof(AtnRay), cudaMemcpyHostToDevice, s));
     if (t_max) CUDA_TRY(cudaMemcpyAsync(sc->t_max, t_max, n * sizeof(float), cudaMemcpyHostToDevice, s));
     QueryClosestPolicy pol{ sc->rays, t_max ? sc->t_max : nullptr, sc->hits };
-    k_trace<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &sc->cursor);
+    k_trace<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &sc->cursor, nullptr);
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaMemcpyAsync(hits, sc->hits, n * sizeof(AtnHit), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaStreamSynchronize(s));

@@ -236,10 +236,11 @@ def main():
     barrier()
     clocks.start()
     t0 = time.perf_counter()
-    rays = samples = launches = 0
+    rays = samples = launches = nodes = tris = 0
     dev_ms = 0.0
     for _ in range(args.steps):
         st = step_device()
+        nodes += st["nodes_visited"]; tris += st["tris_tested"]
         rays += st["closest_rays"] + st["shadow_rays"]
         samples += st["camera_samples"]
         launches += st["kernel_launches"]
@@ -296,6 +297,8 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "msamples_per_s": round(samples / t_s / 1e6, 2),
             "rays_per_sample": round(rays / max(samples, 1), 3),
+            "own_layout": {"pair_nodes_per_ray": round(nodes * world / max(rays, 1), 2), "tri_tests_per_ray": round(tris * world / max(rays, 1), 2),
+                           "bytes_per_ray": round((64 * nodes + 48 * tris) * world / max(rays, 1) + 56, 1)},
             "wall_ms_per_step": round(1e3 * wall_s / args.steps, 3),
             "config": {"workload": WORKLOAD, "scene": SCENE, "width": W, "height": H, "spp_per_gpu": SPP,
                        "bounces": BOUNCE, "rr_bounce": RR,

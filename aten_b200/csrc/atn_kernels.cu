@@ -225,7 +225,9 @@ __device__ __forceinline__ float leaf_margin(const V3& org, const V3& dir, const
 }
 __device__ __forceinline__ bool leaf_may_hit(float t0, float t1, float margin)
 {
-    return (margin < 0.0f) || (t0 <= t1 + 2e-4f * (fabsf(t0) + fabsf(t1)) + margin);
+    // branch free; margin < 0 disables the filter
+    const bool pass = t0 <= t1 + 2e-4f * (fabsf(t0) + fabsf(t1)) + margin;
+    return pass | (margin < 0.0f);
 }
 
 // ---- ray sources / sinks of the traversal kernel -------------------------------------------
@@ -353,13 +355,10 @@ template <class Policy>
 __global__ void __launch_bounds__(kTraceBlock, ATN_TRACE_MIN_BLOCKS)
 k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch, Visits* visits)
 {
-    __shared__ int32_t s_ref[kSmemStack * kTraceBlock];
-    __shared__ float s_t0[kSmemStack * kTraceBlock];
+    __shared__ int2 s_stack[kSmemStack * kTraceBlock];   // (reference, entry distance bits) per lane and level
     __shared__ float s_world[13 * kTraceBlock];      // world-space org, dir, invdir, oxinvdir, leaf margin of the lane's ray
-    int32_t l_ref[kLocalStack];
-    float l_t0[kLocalStack];
-    int32_t* const my_ref = s_ref + threadIdx.x;
-    float* const my_t0 = s_t0 + threadIdx.x;
+    int2 l_stack[kLocalStack];
+    int2* const my_stack = s_stack + threadIdx.x;
     float* const my_world = s_world + threadIdx.x;
 
     const unsigned full = 0xffffffffu;
@@ -435,8 +434,10 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                 // leaves are never box-tested by the reference: taken before boxes, unless the ray
                 // misses the leaf's box by a safe margin (see leaf_margin)
                 const float leaf_far = (best.leaf >= 0) ? t_cull : kInf;
-                const bool hl = (left >= 0) ? bl : (left != kRefNull && leaf_may_hit(t0l, fminf(t1l, leaf_far), margin));
-                const bool hr = (right >= 0) ? br : (right != kRefNull && leaf_may_hit(t0r, fminf(t1r, leaf_far), margin));
+                const bool fl = leaf_may_hit(t0l, fminf(t1l, leaf_far), margin) & (left != kRefNull);
+                const bool fr = leaf_may_hit(t0r, fminf(t1r, leaf_far), margin) & (right != kRefNull);
+                const bool hl = (left >= 0) ? bl : fl;
+                const bool hr = (right >= 0) ? br : fr;
                 n_nodes++;
                 t0l = (left >= 0) ? t0l : -kInf;
                 t0r = (right >= 0) ? t0r : -kInf;
@@ -444,8 +445,8 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                     const bool swap = t0r < t0l;        // near child first
                     const int32_t farc = swap ? left : right;
                     const float fart = swap ? t0l : t0r;
-                    if (sp < kSmemStack) { my_ref[sp * kTraceBlock] = farc; my_t0[sp * kTraceBlock] = fart; }
-                    else { l_ref[sp - kSmemStack] = farc; l_t0[sp - kSmemStack] = fart; }
+                    const int2 e = make_int2(farc, __float_as_int(fart));
+                    if (sp < kSmemStack) my_stack[sp * kTraceBlock] = e; else l_stack[sp - kSmemStack] = e;
                     sp++;
                     cur = swap ? right : left;
                 }
@@ -490,8 +491,8 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                         const int4 il = __ldg(bv.insts + leaf);
                         cur = kRefNull;
                         if (il.y != kRefNull) {
-                            if (sp < kSmemStack) { my_ref[sp * kTraceBlock] = kRefExit; my_t0[sp * kTraceBlock] = -kInf; }
-                            else { l_ref[sp - kSmemStack] = kRefExit; l_t0[sp - kSmemStack] = -kInf; }
+                            const int2 e = make_int2(kRefExit, __float_as_int(-kInf));
+                            if (sp < kSmemStack) my_stack[sp * kTraceBlock] = e; else l_stack[sp - kSmemStack] = e;
                             sp++;
                             cur_inst = leaf;
                             if (il.z >= 0) {
@@ -512,9 +513,9 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                 for (;;) {
                     if (sp == 0) { finished = true; break; }
                     sp--;
-                    float t0;
-                    if (sp < kSmemStack) { cur = my_ref[sp * kTraceBlock]; t0 = my_t0[sp * kTraceBlock]; }
-                    else { cur = l_ref[sp - kSmemStack]; t0 = l_t0[sp - kSmemStack]; }
+                    const int2 e = (sp < kSmemStack) ? my_stack[sp * kTraceBlock] : l_stack[sp - kSmemStack];
+                    cur = e.x;
+                    const float t0 = __int_as_float(e.y);
                     if (cur == kRefExit) {
                         if (sp == 0) { finished = true; break; }      // nothing left in the top layer either
                         // back to the top layer with the world ray (threaded_bvh_traverser.h:290-300)

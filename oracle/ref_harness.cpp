@@ -102,7 +102,7 @@ struct Harness {
     // ---- scenes -------------------------------------------------------------------------------
     // C1: the reference's ObjCornellBoxScene (src/common/scenedefs.cpp:732-803), restated through
     // the same public calls so that asset paths are not tied to the cwd.
-    void BuildCornell()
+    void BuildCornell(float light_dy = 0.0f)
     {
         auto emit = MakeMtrl("light", ctxt, aten::MaterialType::Emissive, aten::vec3(1.0f));
         auto objs = aten::ObjLoader::Load(
@@ -120,7 +120,7 @@ struct Harness {
             },
             nullptr, true, true);
         auto light = aten::TransformableFactory::createInstance<aten::PolygonObject>(
-            ctxt, objs[0], aten::vec3(0.0f), aten::vec3(0.0f), aten::vec3(1.0f));
+            ctxt, objs[0], aten::vec3(0.0f, light_dy, 0.0f), aten::vec3(0.0f), aten::vec3(1.0f));
         scene.add(light);
         ctxt.AddLight(std::make_shared<aten::AreaLight>(light, emit->param().baseColor, 200.0f));
         for (size_t i = 1; i < objs.size(); i++) {
@@ -294,6 +294,43 @@ struct Harness {
         ctxt.scene_rendering_config.bg = AT_NAME::Background::CreateBackgroundResource(envmap);
     }
 
+    // C5 stand-in: a k x k grid of transformed instances of the 100 000-triangle dragon over a ground
+    // plane (k = 10: 10 M instanced triangles through the two-level structure), one SBVH built once by
+    // the reference's builder.  A 10 M-triangle single mesh would take the reference builder hours.
+    void BuildDragonGrid(int k)
+    {
+        aten::MaterialParameter ggx;
+        ggx.baseColor = aten::vec3(0.75f, 0.65f, 0.4f); ggx.standard.roughness = 0.3f; ggx.standard.ior = 1.8f;
+        auto m_ggx = MakeMtrlP("ggx", ctxt, aten::MaterialType::GGX, ggx);
+        auto m_floor = MakeMtrl("floor", ctxt, aten::MaterialType::Diffuse, aten::vec3(0.6f, 0.6f, 0.6f));
+        std::shared_ptr<aten::material> cur;
+        auto cb = [&](std::string_view, aten::context&, aten::MaterialType, const aten::vec3&,
+                      const std::string&, const std::string&) -> std::shared_ptr<aten::material> { return cur; };
+        auto find = [&](std::string_view, const aten::context&) -> std::shared_ptr<aten::material> { return cur; };
+        cur = m_ggx;
+        auto dragon = aten::ObjLoader::Load(g_asset + "/dragon/dragon.obj", ctxt, cb, find, false, true);
+        cur = m_floor;
+        auto plane = aten::ObjLoader::Load(g_asset + "/plane/plane.obj", ctxt, cb, find, false, true);
+        const auto bb = dragon[0]->getBoundingbox();
+        const auto size = bb.size();
+        const float pitch = 1.3f * std::max(size.x, size.z);
+        for (int j = 0; j < k; j++) {
+            for (int i = 0; i < k; i++) {
+                scene.add(aten::TransformableFactory::createInstance<aten::PolygonObject>(
+                    ctxt, dragon[0],
+                    aten::vec3((i - 0.5f * (k - 1)) * pitch, -bb.minPos().y, (j - 0.5f * (k - 1)) * pitch),
+                    aten::vec3(0.03f * ((i * 7 + j * 3) % 11), 0.0f, 0.0f), aten::vec3(1.0f)));
+            }
+        }
+        scene.add(aten::TransformableFactory::createInstance<aten::PolygonObject>(
+            ctxt, plane[0], aten::vec3(0.0f), aten::vec3(-AT_MATH_PI_HALF, 0.0f, 0.0f), aten::vec3(1.0f)));
+        const float ext = 0.5f * k * pitch;
+        ctxt.AddLight(std::make_shared<aten::PointLight>(aten::vec3(0.0f, 3.0f * ext, 0.5f * ext), aten::vec3(1.0f, 0.95f, 0.9f), 40.0f * ext * ext));
+        SetCamera(aten::vec3(0.0f, 1.2f * ext, 1.8f * ext), aten::vec3(0.0f, 0.0f, 0.0f), 45.0f);
+        envmap = MakeSky(ctxt, 512, 256);
+        ctxt.scene_rendering_config.bg = AT_NAME::Background::CreateBackgroundResource(envmap);
+    }
+
     bool Build(const std::string& name, int32_t w, int32_t h)
     {
         W = w; H = h;
@@ -305,6 +342,9 @@ struct Harness {
         else if (name == "sponza_tex") BuildSponza(true, true);
         else if (name == "instanced") BuildInstanced(false);
         else if (name == "instanced_dragon") BuildInstanced(true);
+        else if (name == "cornell_moved") BuildCornell(-0.3f);
+        else if (name == "dragon_grid4") BuildDragonGrid(4);
+        else if (name == "dragon_grid10") BuildDragonGrid(10);
         else { fprintf(stderr, "unknown scene %s\n", name.c_str()); return false; }
 
         scene.build(ctxt);

@@ -1,0 +1,117 @@
+#!/usr/bin/env python3
+"""Throughput of the hot path on the other BASELINE.json configs (stand-ins where the snapshot lacks
+the assets).  Scenes are built on the spot by the reference's own loaders / SBVH builder
+through oracle/_ref/ref_harness, so this runs only where that binary travelled (the GPU box).
+
+    python scripts/bench_configs.py [--quick] > profiles/rNN_configs.jsonl
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from aten_b200 import PathTracing, scene_io as sio  # noqa: E402
+from tests import oracle_lib as ol  # noqa: E402
+
+
+def render_bench(name, W, H, spp, steps=3, warmup=2, label=""):
+    scene = ol.ref_scene(name, W, H)
+    r = PathTracing(0)
+    r.UpdateSceneData(scene)
+    r.SetEnableProgressive(False)
+    for _ in range(warmup):
+        r.reset(); r.render(W, H, spp, 5, 3)
+    ms = rays = samples = nodes = tris = 0
+    for _ in range(steps):
+        r.reset(); r.render(W, H, spp, 5, 3)
+        st = r.stats()
+        ms += st["device_ms"]; rays += st["closest_rays"] + st["shadow_rays"]; samples += st["camera_samples"]
+        nodes += st["nodes_visited"]; tris += st["tris_tested"]
+    img = r.readback()
+    r.close()
+    out = {"config": label, "scene": name, "w": W, "h": H, "spp": spp, "bounces": 5, "triangles": int(len(scene.triangles)),
+           "nodes": scene.node_count, "instances": int((scene.objects["type"] == 1).sum()),
+           "ms_per_step": round(ms / steps, 3), "mrays_per_s": round(rays / ms / 1e3, 1),
+           "msamples_per_s": round(samples / ms / 1e3, 1), "rays_per_sample": round(rays / samples, 2),
+           "pair_nodes_per_ray": round(nodes / rays, 2), "tri_tests_per_ray": round(tris / rays, 2),
+           "mean_radiance": float(img[..., :3].mean() / spp), "finite": bool(np.isfinite(img).all())}
+    print(json.dumps(out), flush=True)
+
+
+def ray_stress(name, n_rays, label=""):
+    """Incoherent diffuse secondary rays: origins = surface points found by a first random pass,
+    directions cosine-distributed about nothing in particular (uniform sphere), closest-hit and any-hit."""
+    import torch
+    scene = ol.ref_scene(name, 8, 8)
+    r = PathTracing(0)
+    r.UpdateSceneData(scene)
+    rng = np.random.default_rng(1)
+    lo = scene.config["scene_bbox_min"][0]; hi = scene.config["scene_bbox_max"][0]
+    seed_n = min(n_rays, 2_000_000)
+    rays = np.zeros(seed_n, sio.RAY_DTYPE)
+    rays["org"] = (lo + (hi - lo) * rng.random((seed_n, 3))).astype(np.float32)
+    d = rng.normal(size=(seed_n, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays["dir"] = d.astype(np.float32)
+    hits = r.trace_closest(rays)
+    ok = hits["objid"] >= 0
+    # secondary rays start on the surfaces that were hit, pushed back a little along the incoming ray
+    p = rays["org"][ok] + rays["dir"][ok] * (hits["t"][ok] * np.float32(0.999))[:, None]
+    reps = int(np.ceil(n_rays / max(1, len(p))))
+    org = np.tile(p, (reps, 1))[:n_rays]
+    d = rng.normal(size=(n_rays, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    sec = np.zeros(n_rays, sio.RAY_DTYPE)
+    sec["org"] = org.astype(np.float32); sec["dir"] = d.astype(np.float32)
+    diag = float(np.linalg.norm(hi - lo))
+    dist = (rng.random(n_rays) * diag).astype(np.float32)
+    t_rays = torch.from_numpy(sec.view(np.float32).reshape(-1, 6)).cuda()
+    t_dist = torch.from_numpy(dist).cuda()
+    t_hits = torch.empty((n_rays, 8), dtype=torch.float32, device="cuda")
+    t_vis = torch.empty(n_rays, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    res = {}
+    for kind in ("closest", "any"):
+        best = 1e30
+        for it in range(4):          # first pass is the warm-up; wall clock around launch + sync (tens of ms per pass)
+            r.synchronize()
+            t0 = time.perf_counter()
+            if kind == "closest":
+                r.trace_closest_device(t_rays.data_ptr(), None, n_rays, t_hits.data_ptr())
+            else:
+                r.trace_any_device(t_rays.data_ptr(), t_dist.data_ptr(), n_rays, t_vis.data_ptr())
+            r.synchronize()
+            if it > 0:
+                best = min(best, (time.perf_counter() - t0) * 1e3)
+        res[kind] = best
+    hit_frac = float((t_hits[:, 1].view(torch.int32) >= 0).float().mean())
+    r.close()
+    print(json.dumps({"config": label, "scene": name, "rays": n_rays, "triangles": int(len(scene.triangles)),
+                      "instances": int((scene.objects["type"] == 1).sum()), "nodes": scene.node_count,
+                      "closest_mrays_per_s": round(n_rays / res["closest"] / 1e3, 1),
+                      "any_mrays_per_s": round(n_rays / res["any"] / 1e3, 1), "hit_fraction": round(hit_frac, 3),
+                      "visible_fraction": round(float(t_vis.float().mean()), 3)}), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--quick", action="store_true")
+    a = ap.parse_args()
+    if not ol.have_ref():
+        sys.exit("oracle/_ref not present")
+    q = a.quick
+    render_bench("cornell", 512, 512, 1, steps=5, warmup=3, label="C1 Cornell 512x512 1spp")
+    render_bench("sponza_atrium", 1920, 1080, 16 if not q else 2, label="C2 sponza_lod 1080p 16spp (bench.py workload)")
+    render_bench("sponza_tex", 1920, 1080, 16 if not q else 2, label="C3 stand-in: sponza_lod + albedo/normal maps + synthetic-sky IBL, 1080p 16spp")
+    render_bench("instanced_dragon", 3840, 2160, 8 if not q else 1, label="C4 stand-in: instanced dragon+teapot+suzanne, Disney/refraction, 4K, 8 spp (one GPU's share of 64 spp on 8)")
+    render_bench("dragon_grid10", 1920, 1080, 4 if not q else 1, label="C5 stand-in (rendered): 100 instanced dragons = 10 M triangles, 1080p 4spp")
+    ray_stress("dragon_grid10", 100_000_000 if not q else 5_000_000,
+               label="C5 stand-in: 100 M incoherent secondary rays into 100 instanced dragons (10 M triangles), closest-hit and any-hit")
+
+
+if __name__ == "__main__":
+    main()

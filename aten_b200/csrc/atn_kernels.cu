@@ -2,13 +2,15 @@
 //
 // Pipeline per camera sample (replaces reference src/libidaten/kernel/pathtracing.cpp:91-153):
 //
-//   k_generate            genPath            (pt_standard_impl.cu:25-50, pathtracing_impl.h:65-110)
+//   k_generate              genPath            (pt_standard_impl.cu:25-50, pathtracing_impl.h:65-110)
 //   for bounce:
-//     k_trace<CLOSEST>    hitTest            (pt_standard_impl.cu:57-229, threaded_bvh_traverser.h:98-304)
-//     k_shade             shade + ShadeMiss  (pathtracing_impl.cu:18-238, pt_standard_impl.cu:330-362;
-//                                             HOST ordering, pathtracing.cpp:91-236)
-//     k_trace<SHADOW>     hitShadowRay       (pathtracing_impl.cu:240-280, pathtracing_impl.h:266-393)
-//   k_gather              gather             (pathtracing_impl.cu:282-324, film.cpp:61-71)
+//     k_trace<ClosestPolicy> hitTest           (pt_standard_impl.cu:57-229, threaded_bvh_traverser.h:98-304)
+//     k_surface             shade, first part + ShadeMiss (pathtracing_impl.cu:18-238, pt_standard_impl.cu:330-362;
+//                                               HOST ordering, pathtracing.cpp:91-236)
+//     k_nee                 FillShadowRay / SampleLight / ComputeRadianceNEE (pathtracing_impl.h:178-264)
+//     k_bsdf                Russian roulette, sampleMaterial, PrepareForNextBounce (pathtracing_impl.h:680-743)
+//     k_trace<ShadowPolicy>  hitShadowRay       (pathtracing_impl.cu:240-280, pathtracing_impl.h:266-393)
+//   k_gather                gather             (pathtracing_impl.cu:282-324, film.cpp:61-71)
 //
 // B200-native choices (DESIGN.md has the numbers):
 //   * path state is SoA float4 / u32 arrays indexed by path slot; there is no AoS PathThroughput;
@@ -16,11 +18,11 @@
 //     bounce) is replaced by device-side queues appended with warp-aggregated atomics
 //     (__ballot_sync / __popc / one atomicAdd per warp); the host never reads a count, so a frame
 //     is a fixed launch sequence with no synchronisation;
-//   * traversal kernels are persistent: grid = SMs x resident blocks, each warp pulls 32 rays at a
-//     time from the queue with one atomicAdd;
+//   * traversal kernels are persistent and warp-synchronous: grid = SMs x resident blocks, every lane
+//     owns a resumable ray, the warp refills idle lanes from the queue with one atomicAdd;
 //   * nodes are 64-byte child-pair records fetched with 128-bit read-only loads (LDG.E.128.CONSTANT),
-//     triangles are 48-byte gathered records; the traversal stack is a per-thread shared-memory
-//     short stack that spills to local memory only beyond kSmemStack entries;
+//     triangles are 48-byte gathered records; the traversal stack is a per-lane shared-memory
+//     stack of (reference, entry distance) pairs that spills to local memory beyond kSmemStack;
 //   * no tensor cores: the path is pointer chasing + FP32 slab / Moeller-Trumbore arithmetic.
 // Compiled with -fmad=false: the intersection arithmetic must round exactly like the reference's
 // x86 build for primitive ids to match bit for bit.

@@ -264,10 +264,12 @@ def main():
     r.set_profiling(True)
     step_device()
     tr_ms = tr_rays = 0.0
+    trace_launches = 0
     for _ in range(max(1, min(args.steps, 3))):
         st = step_device()
         tr_ms += st["trace_ms"]
         tr_rays += st["closest_rays"] + st["shadow_rays"]
+        trace_launches += 2 * BOUNCE * SPP
     r.set_profiling(False)
     barrier()
 
@@ -315,13 +317,19 @@ def main():
             achieved = tr_rays * base["b_ray"] / (tr_ms / 1e3) / 1e9
             line["roofline"] = {
                 "bound": "hbm", "achieved": round(achieved, 1), "peak": hbm, "unit": "GB/s", "frac": round(achieved / hbm, 4),
-                "traffic": None, "peak_source": which, "kernel": "k_trace_closest + k_trace_shadow",
+                # dram__bytes_read+write per traversal launch from the ncu --set full capture summarised in
+                # profiles/r01_ncu_full_v5.txt (42-124 MB per launch, mean of the captured launches): the ray / hit
+                # streams only -- nodes and triangles are served from L2
+                "traffic": 8.7e7, "algorithmic_bytes_per_launch": round(tr_rays * base["b_ray"] / max(1, trace_launches), 0),
+                "peak_source": which, "kernel": "k_trace<ClosestPolicy> + k_trace<ShadowPolicy>",
+                "issue_slot_utilisation_ncu": 0.70, "threads_per_instruction_ncu": 14.4,
                 "bytes_per_ray": round(base["b_ray"], 1), "flops_per_ray": round(base["f_ray"], 1),
                 "nodes_per_ray": round(base["n_node"], 2), "tris_per_ray": round(base["n_tri"], 2),
                 "trace_share_of_step": round(tr_ms / max(1e-9, (dev_ms / args.steps) * max(1, min(args.steps, 3))), 3),
                 "trace_mrays_per_s": round(tr_rays / (tr_ms / 1e3) / 1e6, 1),
-                "note": "algorithmic bytes on the REFERENCE layout and visit order (oracle counters); the working set is L2-resident, "
-                        "so this is reported against the HBM copy peak only as the agreed denominator",
+                "note": "algorithmic bytes on the REFERENCE layout and visit order (oracle counters, SURVEY 8d); the scene is L2-resident and "
+                        "the ordered traversal fetches ~2.4 KB/ray from L1/L2 (own_layout), so frac > 1 against the HBM copy peak is expected; "
+                        "the kernel is instruction-issue bound (issue_slot_utilisation_ncu at threads_per_instruction_ncu of 32 lanes)",
             }
         if cpu:
             line["cpu_baseline"] = cpu

@@ -86,6 +86,10 @@ constexpr int kTraceBlock = 128;
 #define ATN_REFILL_THRESHOLD 20
 #endif
 constexpr int kRefillThreshold = ATN_REFILL_THRESHOLD;   // refill a warp when fewer lanes than this still own a ray
+#ifndef ATN_LEAF_BATCH
+#define ATN_LEAF_BATCH 5
+#endif
+constexpr int kLeafBatch = ATN_LEAF_BATCH;               // lanes that must hold a triangle leaf before the test runs
 #ifndef ATN_ENTRY_BATCH
 #define ATN_ENTRY_BATCH 6
 #endif
@@ -458,7 +462,16 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
             }
 
             // ---- phase B: triangle leaf (triangle::hit, triangle.h:40-67) ----
-            const bool on_tri = active && cur < 0 && cur != kRefNull && cur != kRefExit && cur_inst >= 0;
+            const bool want_tri = active && cur < 0 && cur != kRefNull && cur != kRefExit && cur_inst >= 0;
+            // The triangle test is the longest section and runs for few lanes at a time.  Lanes wait with
+            // their leaf until kLeafBatch of them have one, or no lane is on a node (kLeafBatch = 1: no waiting).
+            bool run_tris = true;
+            if (kLeafBatch > 1) {
+                const unsigned mt = __ballot_sync(full, want_tri);
+                const unsigned mn = __ballot_sync(full, on_node);
+                run_tris = (__popc(mt) >= kLeafBatch) || (mn == 0u);
+            }
+            const bool on_tri = want_tri && run_tris;
             bool finished = false;
             if (on_tri) {
                 const int32_t leaf = ~cur;

@@ -23,7 +23,7 @@ EXPORTS = [
     "atn_set_frame", "atn_get_frame", "atn_reset", "atn_set_progressive", "atn_set_hit_distance_limit",
     "atn_render", "atn_render_region", "atn_synchronize", "atn_readback", "atn_device_image", "atn_get_stats",
     "atn_set_profiling", "atn_get_stream", "atn_trace_closest", "atn_trace_any", "atn_trace_closest_device",
-    "atn_trace_any_device", "atn_set_bounce_tap", "atn_trace_closest_static",
+    "atn_trace_any_device", "atn_set_bounce_tap", "atn_trace_closest_static", "atn_readback_aov",
 ]
 
 
@@ -180,6 +180,14 @@ class PathTracing:
             out = np.empty((self.height, self.width, 4), np.float32)
         _check(self._lib, self._lib.atn_readback(self._h, C.c_void_p(out.ctypes.data), C.c_size_t(n)))
         return out
+
+    def readback_aov(self):
+        """(normal_depth, albedo_meshid), float32 [h, w, 4] each: the reference's two basic AOV buffers."""
+        n = self.width * self.height
+        nd = np.empty((self.height, self.width, 4), np.float32)
+        am = np.empty((self.height, self.width, 4), np.float32)
+        _check(self._lib, self._lib.atn_readback_aov(self._h, C.c_void_p(nd.ctypes.data), C.c_void_p(am.ctypes.data), C.c_size_t(n)))
+        return nd, am
 
     def readback_into(self, host_ptr: int):
         """Read back into caller-owned (e.g. pinned) host memory given as an address."""

@@ -129,6 +129,9 @@ struct PathBuffers {
     float4* sh_o;         // shadow org.xyz, dist            (indexed by path slot)
     float4* sh_d;         // shadow dir.xyz, bits(light id)
     float4* sh_c;         // light contribution xyz, -
+    int32_t* hit_mesh;    // meshid of the first hit (bounce 0 only; feeds the AOVs)
+    float4* aov_nd;       // AOV normal.xyz + depth, per PIXEL (PathTracingImplBase::aov_, pathtracing.h:96-98)
+    float4* aov_am;       // AOV albedo.rgb + meshid, per pixel
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -242,6 +245,7 @@ struct ClosestPolicy {             // wavefront closest-hit (hitTest)
     PathBuffers pb;
     const int32_t* queue;          // path slots, nullptr = identity
     float t_max_all;
+    int32_t* mesh_out;             // where to keep isect.meshid (first bounce only), or nullptr
     __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* t_max, int* mode, float* exit_dist) const
     {
         const int s = queue ? queue[i] : i;
@@ -262,6 +266,7 @@ struct ClosestPolicy {             // wavefront closest-hit (hitTest)
         resolve_hit(bv, r, &objid, &primid, &mtrlid, &meshid);
         pb.hit0[slot] = make_float4(r.t, r.a, r.b, __int_as_float(primid));
         pb.hit1[slot] = make_int2(objid, mtrlid);
+        if (mesh_out) mesh_out[slot] = meshid;
     }
 };
 
@@ -661,9 +666,14 @@ k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, 
             st.contrib = V3(cb.x, cb.y, cb.z);
             st.terminated = false;
             st.singular = (fl & 2u) != 0u;
+            // AOVs of the first hit are kept per pixel (the reference indexes them by pixel too)
+            const int pix = (fp.y0 + slot / fp.rw) * fp.width + (fp.x0 + slot % fp.rw);
+            AtnVec4* aov_nd = (bounce <= 1) ? reinterpret_cast<AtnVec4*>(pb.aov_nd) + pix : nullptr;
+            AtnVec4* aov_am = (bounce <= 1) ? reinterpret_cast<AtnVec4*>(pb.aov_am) + pix : nullptr;
             if (h1.x >= 0) {
                 Surface sf;
-                lit = shade_surface(sc, ray, h1.x, __float_as_int(h0.w), h0.y, h0.z, h0.x, h1.y, bounce, &st, &sf);
+                lit = shade_surface(sc, ray, h1.x, __float_as_int(h0.w), h0.y, h0.z, h0.x, h1.y, bounce, &st, &sf,
+                                    aov_nd, aov_am, bounce == 0 ? pb.hit_mesh[slot] : -1);
                 if (lit) {
                     pb.surf0[slot] = make_float4(sf.p.x, sf.p.y, sf.p.z, sf.u);
                     pb.surf1[slot] = make_float4(sf.n.x, sf.n.y, sf.n.z, sf.v);
@@ -673,7 +683,7 @@ k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, 
             else {
                 const int ix = fp.x0 + slot % fp.rw;
                 const int iy = fp.y0 + slot / fp.rw;
-                shade_miss(sc, cam, ix, iy, fp.width, fp.height, bounce, ray, &st);
+                shade_miss(sc, cam, ix, iy, fp.width, fp.height, bounce, ray, &st, aov_nd, aov_am);
             }
             if (!lit) {
                 pb.contrib[slot] = make_float4(st.contrib.x, st.contrib.y, st.contrib.z, cb.w);
@@ -882,6 +892,8 @@ struct AtnRenderer {
     DevBuf<float4> ray_o, ray_d, hit0, throughput, contrib, sh_o, sh_d, sh_c, image;
     DevBuf<int2> hit1;
     DevBuf<uint32_t> sampler_dim, flags;
+    DevBuf<int32_t> hit_mesh;
+    DevBuf<float4> aov_nd, aov_am;
     DevBuf<int32_t> queue0, queue1, q_lit, q_shadow;
     DevBuf<float4> surf0, surf1, surf2;
     DevBuf<Counters> counters;
@@ -948,6 +960,7 @@ static int alloc_paths(AtnRenderer* r, size_t n)
     CUDA_TRY(r->flags.resize(n)); CUDA_TRY(r->queue0.resize(n)); CUDA_TRY(r->queue1.resize(n));
     CUDA_TRY(r->sh_o.resize(n)); CUDA_TRY(r->sh_d.resize(n)); CUDA_TRY(r->sh_c.resize(n));
     CUDA_TRY(r->q_lit.resize(n)); CUDA_TRY(r->q_shadow.resize(n));
+    CUDA_TRY(r->hit_mesh.resize(n)); CUDA_TRY(r->aov_nd.resize(n)); CUDA_TRY(r->aov_am.resize(n));
     CUDA_TRY(r->surf0.resize(n)); CUDA_TRY(r->surf1.resize(n)); CUDA_TRY(r->surf2.resize(n));
     CUDA_TRY(r->counters.resize(1));
     CUDA_TRY(r->totals.resize(1));
@@ -958,6 +971,7 @@ static int alloc_paths(AtnRenderer* r, size_t n)
     pb.queue[0] = r->queue0.p; pb.queue[1] = r->queue1.p;
     pb.sh_o = r->sh_o.p; pb.sh_d = r->sh_d.p; pb.sh_c = r->sh_c.p;
     pb.q_lit = r->q_lit.p; pb.q_shadow = r->q_shadow.p;
+    pb.hit_mesh = r->hit_mesh.p; pb.aov_nd = r->aov_nd.p; pb.aov_am = r->aov_am.p;
     pb.surf0 = r->surf0.p; pb.surf1 = r->surf1.p; pb.surf2 = r->surf2.p;
     return ATN_OK;
 }
@@ -1238,7 +1252,7 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
             const float tmax = (b == 0) ? kInf : r->hit_distance_limit;
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             {
-                ClosestPolicy pol{ r->pb, q, tmax };
+                ClosestPolicy pol{ r->pb, q, tmax, b == 0 ? r->pb.hit_mesh : nullptr };
                 k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[b], 0, &c->fetch_closest[b], r->visits.p);
             }
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
@@ -1310,6 +1324,18 @@ ATN_API int atn_readback(AtnRenderer* r, AtnVec4* host_image, size_t pixel_count
     if (pixel_count != (size_t)r->width * r->height) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_readback: pixel_count mismatch");
     CUDA_TRY(cudaSetDevice(r->device));
     CUDA_TRY(cudaMemcpyAsync(host_image, r->image.p, pixel_count * sizeof(AtnVec4), cudaMemcpyDeviceToHost, r->stream));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
+    return ATN_OK;
+}
+
+ATN_API int atn_readback_aov(AtnRenderer* r, AtnVec4* normal_depth, AtnVec4* albedo_meshid, size_t pixel_count)
+{
+    if (!r || (!normal_depth && !albedo_meshid)) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_readback_aov: NULL argument");
+    if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_readback_aov: no scene uploaded");
+    if (pixel_count != (size_t)r->width * r->height) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_readback_aov: pixel_count mismatch");
+    CUDA_TRY(cudaSetDevice(r->device));
+    if (normal_depth) CUDA_TRY(cudaMemcpyAsync(normal_depth, r->aov_nd.p, pixel_count * sizeof(AtnVec4), cudaMemcpyDeviceToHost, r->stream));
+    if (albedo_meshid) CUDA_TRY(cudaMemcpyAsync(albedo_meshid, r->aov_am.p, pixel_count * sizeof(AtnVec4), cudaMemcpyDeviceToHost, r->stream));
     CUDA_TRY(cudaStreamSynchronize(r->stream));
     return ATN_OK;
 }

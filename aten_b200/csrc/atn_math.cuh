@@ -1154,9 +1154,38 @@ struct ShadowRayOut {
     V3 lightcontrib;
 };
 
+// AOVs of the first hit (A8/A12): FillBasicAOVs / FillBasicAOVsIfHitMiss
+// (src/libaten/renderer/aov.h:159-199).  `w2c` is the world-to-clip matrix; the reference's PT kernel
+// passes the identity (src/libidaten/kernel/pathtracing_impl.cu:102-111), which makes depth = 1.
+ATN_HD void fill_basic_aovs(AtnVec4* normal_depth, const V3& normal, const V3& p, const AtnMat4& w2c,
+                            AtnVec4* albedo_meshid, const AtnVec4& albedo, int32_t meshid)
+{
+    // pos = mtx_W2C.apply(vec4(p, 1)); only .w is used (mat4.h:171-181)
+    const float w = w2c.m[12] * p.x + w2c.m[13] * p.y + w2c.m[14] * p.z + w2c.m[15] * 1.0f;
+    normal_depth->x = normal.x; normal_depth->y = normal.y; normal_depth->z = normal.z; normal_depth->w = w;
+    albedo_meshid->x = albedo.x; albedo_meshid->y = albedo.y; albedo_meshid->z = albedo.z;
+    albedo_meshid->w = (float)meshid;
+}
+ATN_HD void fill_basic_aovs_miss(AtnVec4* normal_depth, AtnVec4* albedo_meshid, const AtnVec4& bg)
+{
+    normal_depth->x = 0.0f; normal_depth->y = 0.0f; normal_depth->z = 0.0f; normal_depth->w = -1.0f;
+    albedo_meshid->x = bg.x; albedo_meshid->y = bg.y; albedo_meshid->z = bg.z; albedo_meshid->w = -1.0f;
+}
+// Camera::ComputePixelWidthAtDistance (src/libaten/camera/camera.h:182-197)
+ATN_HD float pixel_width_at_distance(const AtnCameraParameter& cam, float distance)
+{
+    distance = fabsf(distance);
+    float hfov = cam.vfov * cam.height / (float)(cam.width);
+    hfov = kPi * hfov / 180.0f;
+    const float half_width = tanf(hfov / 2) * distance;
+    const float width = half_width * 2;
+    return width / (float)(cam.width);
+}
+
 // ShadeMiss (src/libaten/renderer/pathtracing/pathtracing_impl.h:112-176)
 ATN_HD void shade_miss(const SceneView& sc, const AtnCameraParameter& cam, int32_t ix, int32_t iy,
-                       int32_t width, int32_t height, int32_t bounce, const Ray& ray, PathState* st)
+                       int32_t width, int32_t height, int32_t bounce, const Ray& ray, PathState* st,
+                       AtnVec4* aov_normal_depth = nullptr, AtnVec4* aov_albedo_meshid = nullptr)
 {
     V3 dir = ray.dir;
     if (bounce == 0) {
@@ -1168,7 +1197,8 @@ ATN_HD void shade_miss(const SceneView& sc, const AtnCameraParameter& cam, int32
     const V3 emit(emit4);
     float misW = 1.0f;
     if (bounce == 0 || (bounce == 1 && st->singular)) {
-        // AOV export only
+        // Export bg color to the albedo buffer (pathtracing_impl.h:150-158)
+        if (aov_normal_depth && aov_albedo_meshid) fill_basic_aovs_miss(aov_normal_depth, aov_albedo_meshid, emit4);
     }
     else {
         const float pdfLight = ibl_pdf(emit, sc.cfg.avgIllum);
@@ -1194,7 +1224,8 @@ struct Surface {
 // (pathtracing_impl.h:395-452), normal orientation + material::applyNormal.
 // Returns false when the path ended here (implicit light).
 ATN_HD bool shade_surface(const SceneView& sc, const Ray& ray, int32_t objid, int32_t primid, float a, float b,
-                          float t, int32_t mtrlid, int32_t bounce, PathState* st, Surface* sf)
+                          float t, int32_t mtrlid, int32_t bounce, PathState* st, Surface* sf,
+                          AtnVec4* aov_normal_depth = nullptr, AtnVec4* aov_albedo_meshid = nullptr, int32_t meshid = -1)
 {
     const AtnObjectParameter obj = sc.objects[objid];
     HitRecord rec;
@@ -1205,6 +1236,16 @@ ATN_HD bool shade_surface(const SceneView& sc, const Ray& ray, int32_t objid, in
 
     const Mtrl mtrl = fill_material(sc, rec.mtrlid);
     const AtnVec4 albedo4 = sample_texture(sc, mtrl.albedoMap, rec.u, rec.v, mtrl.baseColor);
+
+    if (bounce == 0 && aov_normal_depth && aov_albedo_meshid) {
+        // The reference's GPU shade kernel stores the AOVs of the first hit before anything else can end
+        // the path, with the normal-mapped (not yet flipped) normal and an identity matrix
+        // (pathtracing_impl.cu:92-111).
+        AtnMat4 I;
+        for (int i = 0; i < 16; i++) I.m[i] = (i % 5 == 0) ? 1.0f : 0.0f;
+        const V3 aov_n = apply_normal_map(sc, mtrl.normalMap, rec.normal, rec.u, rec.v);
+        fill_basic_aovs(aov_normal_depth, aov_n, rec.p, I, aov_albedo_meshid, albedo4, meshid);
+    }
 
     if (mtrl.type == ATN_MTRL_EMISSIVE) {
         if (mtrl.is_emissive() && !backfacing && obj.light_id >= 0) {

@@ -261,6 +261,12 @@ ATN_API int atn_synchronize(AtnRenderer* r);
 /* Replaces the CUDA-GL surface the reference writes with surf2Dwrite (pathtracing_impl.cu:282-324):
  * copies the float4 W*H image to host memory. */
 ATN_API int atn_readback(AtnRenderer* r, AtnVec4* host_image, size_t pixel_count);
+/* The two basic AOV buffers PathTracingImplBase keeps (aov_.normal_depth(), aov_.albedo_meshid(),
+ * pathtracing.h:96-98), filled for the first hit of the last sample rendered exactly as the reference's
+ * shade / ShadeMiss kernels fill them (FillBasicAOVs with an identity matrix, pathtracing_impl.cu:102-111;
+ * FillBasicAOVsIfHitMiss, pathtracing_impl.h:150-158): normal.xyz + depth and albedo.rgb + meshid per
+ * pixel.  Either pointer may be NULL. */
+ATN_API int atn_readback_aov(AtnRenderer* r, AtnVec4* normal_depth, AtnVec4* albedo_meshid, size_t pixel_count);
 /* Device pointer (float4[W*H]) of the image, for NCCL / torch interop; owned by the handle. */
 ATN_API int atn_device_image(AtnRenderer* r, void** device_ptr, size_t* pixel_count);
 ATN_API int atn_get_stats(AtnRenderer* r, AtnStats* out);

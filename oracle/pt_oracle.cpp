@@ -179,7 +179,8 @@ int oracle_trace_any(const AtnSceneBlob* blob, const AtnRay* rays, const float* 
 __attribute__((visibility("default")))
 int oracle_render(const AtnSceneBlob* blob, const AtnCameraParameter* cam, const uint32_t* seeds, uint32_t seed_count,
                   int32_t W, int32_t H, uint32_t first_frame, int32_t frames, int32_t max_depth, int32_t rr_depth,
-                  AtnVec4* image /* in/out progressive film, W*H */, AtnBounceRecord* records, uint64_t* stats)
+                  AtnVec4* image /* in/out progressive film, W*H */, AtnBounceRecord* records, uint64_t* stats,
+                  AtnVec4* aov_normal_depth /* W*H or NULL */, AtnVec4* aov_albedo_meshid /* W*H or NULL */)
 {
     const Scene s = MakeScene(blob);
     if (rr_depth > max_depth) rr_depth = max_depth - 1;
@@ -218,8 +219,18 @@ int oracle_render(const AtnSceneBlob* blob, const AtnCameraParameter* cam, const
                     if (is_hit) {
                         ShadowRayOut sh;
                         Ray next = ray;
-                        shade_hit(s.view, ray, isect.objid, isect.primid, isect.a, isect.b, isect.t, isect.mtrlid,
-                                  depth, rr_depth, &st, &sh, &next);
+                        // shade_hit() == the three stages in a row; the first one also stores the AOVs of the
+                        // first hit the way the reference's GPU kernel does (pathtracing_impl.cu:92-111)
+                        sh.active = false;
+                        Surface sf;
+                        const bool lit = shade_surface(s.view, ray, isect.objid, isect.primid, isect.a, isect.b, isect.t, isect.mtrlid,
+                                                       depth, &st, &sf,
+                                                       aov_normal_depth ? &aov_normal_depth[idx] : nullptr,
+                                                       aov_albedo_meshid ? &aov_albedo_meshid[idx] : nullptr, isect.meshid);
+                        if (lit) {
+                            shade_nee(s.view, ray.dir, sf, &st, &sh);
+                            shade_bsdf(s.view, ray.dir, sf, depth, rr_depth, &st, &next);
+                        }
                         // HitShadowRay (pathtracing_impl.h:353-393)
                         if (!st.terminated && sh.active) {
                             n_shadow++;
@@ -240,7 +251,9 @@ int oracle_render(const AtnSceneBlob* blob, const AtnCameraParameter* cam, const
                         ray = next;
                     }
                     else {
-                        shade_miss(s.view, *cam, x, y, W, H, depth, ray, &st);
+                        shade_miss(s.view, *cam, x, y, W, H, depth, ray, &st,
+                                   aov_normal_depth ? &aov_normal_depth[idx] : nullptr,
+                                   aov_albedo_meshid ? &aov_albedo_meshid[idx] : nullptr);
                         will_continue = false;
                     }
                     rec.throughput[0] = st.throughput.x; rec.throughput[1] = st.throughput.y; rec.throughput[2] = st.throughput.z;
@@ -291,6 +304,36 @@ int oracle_camera_rays(const AtnCameraParameter* cam, const uint32_t* seeds, uin
         rays[idx].dir = AtnVec3{r.dir.x, r.dir.y, r.dir.z};
     }
     return 0;
+}
+
+// The reference's own known-answer tests for this path, restated as callable functions:
+// FillBasicAOVs / FillBasicAOVsIfHitMiss (src/aten_unittest/aov_host_buffer.cpp:73-130) and
+// Camera::ComputePixelWidthAtDistance (src/aten_unittest/pinhole_camera.cpp:6-15).
+__attribute__((visibility("default")))
+void oracle_fill_basic_aovs(const float normal[3], const float p[3], const float w2c[16], const float albedo[4], int32_t meshid,
+                            float normal_depth[4], float albedo_meshid[4])
+{
+    AtnMat4 m; memcpy(m.m, w2c, sizeof(m.m));
+    AtnVec4 al{ albedo[0], albedo[1], albedo[2], albedo[3] };
+    AtnVec4 nd, am;
+    fill_basic_aovs(&nd, V3(normal[0], normal[1], normal[2]), V3(p[0], p[1], p[2]), m, &am, al, meshid);
+    memcpy(normal_depth, &nd, 16); memcpy(albedo_meshid, &am, 16);
+}
+
+__attribute__((visibility("default")))
+void oracle_fill_basic_aovs_miss(const float bg[4], float normal_depth[4], float albedo_meshid[4])
+{
+    AtnVec4 b{ bg[0], bg[1], bg[2], bg[3] }, nd, am;
+    fill_basic_aovs_miss(&nd, &am, b);
+    memcpy(normal_depth, &nd, 16); memcpy(albedo_meshid, &am, 16);
+}
+
+__attribute__((visibility("default")))
+float oracle_pixel_width_at_distance(float vfov, int32_t width, int32_t height, float distance)
+{
+    AtnCameraParameter c; memset(&c, 0, sizeof(c));
+    c.vfov = vfov; c.width = width; c.height = height;
+    return pixel_width_at_distance(c, distance);
 }
 
 __attribute__((visibility("default")))

@@ -57,7 +57,8 @@ def trace_any(scene: sio.Scene, rays: np.ndarray, dist: np.ndarray):
     return vis
 
 
-def render(scene: sio.Scene, frames=1, max_depth=5, rr_depth=3, first_frame=0, records=False, image=None, threads=None):
+def render(scene: sio.Scene, frames=1, max_depth=5, rr_depth=3, first_frame=0, records=False, image=None, threads=None, aov=None):
+    """`aov`: optional dict that receives 'normal_depth' and 'albedo_meshid' float32 [H, W, 4] (first-hit AOVs)."""
     W, H = scene.width, scene.height
     if threads:
         lib().oracle_set_threads(int(threads))
@@ -65,12 +66,19 @@ def render(scene: sio.Scene, frames=1, max_depth=5, rr_depth=3, first_frame=0, r
     recs = np.zeros((H * W, max_depth), sio.BOUNCE_DTYPE) if records else None
     seeds = scene.seeds_for(W * H)
     stats = np.zeros(6, np.uint64)
+    nd = np.zeros((H * W, 4), np.float32)
+    am = np.zeros((H * W, 4), np.float32)
     blob = scene.blob()
     cam = np.ascontiguousarray(scene.camera)
     lib().oracle_render(C.byref(blob), C.c_void_p(cam.ctypes.data), C.c_void_p(seeds.ctypes.data), C.c_uint32(len(seeds)),
                         C.c_int32(W), C.c_int32(H), C.c_uint32(first_frame), C.c_int32(frames), C.c_int32(max_depth),
                         C.c_int32(rr_depth), C.c_void_p(img.ctypes.data),
-                        C.c_void_p(recs.ctypes.data) if records else None, C.c_void_p(stats.ctypes.data))
+                        C.c_void_p(recs.ctypes.data) if records else None, C.c_void_p(stats.ctypes.data),
+                        C.c_void_p(nd.ctypes.data) if aov is not None else None,
+                        C.c_void_p(am.ctypes.data) if aov is not None else None)
+    if aov is not None:
+        aov["normal_depth"] = nd.reshape(H, W, 4)
+        aov["albedo_meshid"] = am.reshape(H, W, 4)
     return img.reshape(H, W, 4), recs, stats
 
 
@@ -139,3 +147,22 @@ def ref_rays(name, rays: np.ndarray, t_max: np.ndarray):
         buf.tofile(pin)
         ref_run("rays", name, pin, pout)
         return np.fromfile(pout, sio.HIT_DTYPE)
+
+
+def fill_basic_aovs(normal, p, w2c, albedo, meshid):
+    f = lambda a, n: (C.c_float * n)(*[float(x) for x in a])
+    nd = (C.c_float * 4)(); am = (C.c_float * 4)()
+    lib().oracle_fill_basic_aovs(f(normal, 3), f(p, 3), f(np.asarray(w2c).reshape(-1), 16), f(albedo, 4), C.c_int32(meshid), nd, am)
+    return list(nd), list(am)
+
+
+def fill_basic_aovs_miss(bg):
+    nd = (C.c_float * 4)(); am = (C.c_float * 4)()
+    lib().oracle_fill_basic_aovs_miss((C.c_float * 4)(*[float(x) for x in bg]), nd, am)
+    return list(nd), list(am)
+
+
+def pixel_width_at_distance(vfov, width, height, distance):
+    fn = lib().oracle_pixel_width_at_distance
+    fn.restype = C.c_float
+    return float(fn(C.c_float(vfov), C.c_int32(width), C.c_int32(height), C.c_float(distance)))

@@ -372,3 +372,22 @@ def test_live_reference_instanced_dragon_grid():
         assert np.sqrt(np.mean((a - b) ** 2)) <= 5e-3 * np.sqrt(np.mean(b ** 2))
     finally:
         r.close()
+
+
+@pytest.mark.parametrize("name", ["cornell_mtrl", "sponza_atrium"])
+def test_first_hit_aovs_vs_oracle(golden, renderers, name):
+    """normal+depth and albedo+meshid of the first hit (FillBasicAOVs with an identity matrix as in the
+    reference's GPU shade kernel; background colour and -1 on a miss): bit-exact against the restatement
+    -- nothing transcendental is involved."""
+    m = golden.meta[name]
+    r = renderers[name]
+    r.reset(); r.set_frame(0)
+    r.render(m["w"], m["h"], 1, 5, 3)
+    nd, am = r.readback_aov()
+    aov = {}
+    ol.render(golden.scene(name), frames=1, aov=aov)
+    assert (bits(nd) == bits(aov["normal_depth"])).all()
+    assert (bits(am) == bits(aov["albedo_meshid"])).all()
+    hit = nd[..., 3] > 0
+    assert hit.mean() > 0.5 and (nd[..., 3][hit] == 1.0).all() and (am[..., 3][hit] >= 0).all()
+    assert np.allclose(np.linalg.norm(nd[..., :3][hit], axis=-1), 1.0, atol=1e-5)

@@ -90,6 +90,10 @@ constexpr int kRefillThreshold = ATN_REFILL_THRESHOLD;   // refill a warp when f
 #define ATN_LEAF_BATCH 5
 #endif
 constexpr int kLeafBatch = ATN_LEAF_BATCH;               // lanes that must hold a triangle leaf before the test runs
+#ifndef ATN_POP_MAX
+#define ATN_POP_MAX 1000000
+#endif
+constexpr int kPopMax = ATN_POP_MAX;                     // stack entries a lane may discard per iteration before it yields
 #ifndef ATN_ENTRY_BATCH
 #define ATN_ENTRY_BATCH 6
 #endif
@@ -369,8 +373,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
     __shared__ int2 s_stack[kSmemStack * kTraceBlock];   // (reference, entry distance bits) per lane and level
     __shared__ float s_world[13 * kTraceBlock];      // world-space org, dir, invdir, oxinvdir, leaf margin of the lane's ray
     int2 l_stack[kLocalStack];
-    int2* const my_stack = s_stack + threadIdx.x;
-    float* const my_world = s_world + threadIdx.x;
+    const int tid = threadIdx.x;
 
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -409,11 +412,11 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                     pol.load(i, &slot, &org, &dir, &t_max, &mode, &exit_dist);
                     ri = ray_inv(org, dir);
                     margin = leaf_margin(org, dir, ri);
-                    my_world[0 * kTraceBlock] = org.x; my_world[1 * kTraceBlock] = org.y; my_world[2 * kTraceBlock] = org.z;
-                    my_world[3 * kTraceBlock] = dir.x; my_world[4 * kTraceBlock] = dir.y; my_world[5 * kTraceBlock] = dir.z;
-                    my_world[6 * kTraceBlock] = ri.invdir.x; my_world[7 * kTraceBlock] = ri.invdir.y; my_world[8 * kTraceBlock] = ri.invdir.z;
-                    my_world[9 * kTraceBlock] = ri.oxinvdir.x; my_world[10 * kTraceBlock] = ri.oxinvdir.y; my_world[11 * kTraceBlock] = ri.oxinvdir.z;
-                    my_world[12 * kTraceBlock] = margin;
+                    s_world[0 * kTraceBlock + tid] = org.x; s_world[1 * kTraceBlock + tid] = org.y; s_world[2 * kTraceBlock + tid] = org.z;
+                    s_world[3 * kTraceBlock + tid] = dir.x; s_world[4 * kTraceBlock + tid] = dir.y; s_world[5 * kTraceBlock + tid] = dir.z;
+                    s_world[6 * kTraceBlock + tid] = ri.invdir.x; s_world[7 * kTraceBlock + tid] = ri.invdir.y; s_world[8 * kTraceBlock + tid] = ri.invdir.z;
+                    s_world[9 * kTraceBlock + tid] = ri.oxinvdir.x; s_world[10 * kTraceBlock + tid] = ri.oxinvdir.y; s_world[11 * kTraceBlock + tid] = ri.oxinvdir.z;
+                    s_world[12 * kTraceBlock + tid] = margin;
                     t_cull = t_max;
                     best.t = kInf; best.a = 0.0f; best.b = 0.0f; best.leaf = -1; best.inst = -1;
                     sp = 0; cur = bv.top_root; cur_inst = -1;
@@ -457,7 +460,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                     const int32_t farc = swap ? left : right;
                     const float fart = swap ? t0l : t0r;
                     const int2 e = make_int2(farc, __float_as_int(fart));
-                    if (sp < kSmemStack) my_stack[sp * kTraceBlock] = e; else l_stack[sp - kSmemStack] = e;
+                    if (sp < kSmemStack) s_stack[sp * kTraceBlock + tid] = e; else l_stack[sp - kSmemStack] = e;
                     sp++;
                     cur = swap ? right : left;
                 }
@@ -512,7 +515,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                         cur = kRefNull;
                         if (il.y != kRefNull) {
                             const int2 e = make_int2(kRefExit, __float_as_int(-kInf));
-                            if (sp < kSmemStack) my_stack[sp * kTraceBlock] = e; else l_stack[sp - kSmemStack] = e;
+                            if (sp < kSmemStack) s_stack[sp * kTraceBlock + tid] = e; else l_stack[sp - kSmemStack] = e;
                             sp++;
                             cur_inst = leaf;
                             if (il.z >= 0) {
@@ -530,24 +533,26 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
 
             // ---- phase C: pop ----
             if (active && !finished && cur == kRefNull) {
-                for (;;) {
+#pragma unroll 1
+                for (int pops = 0; pops < kPopMax; pops++) {
                     if (sp == 0) { finished = true; break; }
                     sp--;
-                    const int2 e = (sp < kSmemStack) ? my_stack[sp * kTraceBlock] : l_stack[sp - kSmemStack];
+                    const int2 e = (sp < kSmemStack) ? s_stack[sp * kTraceBlock + tid] : l_stack[sp - kSmemStack];
                     cur = e.x;
                     const float t0 = __int_as_float(e.y);
                     if (cur == kRefExit) {
                         if (sp == 0) { finished = true; break; }      // nothing left in the top layer either
                         // back to the top layer with the world ray (threaded_bvh_traverser.h:290-300)
                         cur_inst = -1;
-                        org = V3(my_world[0 * kTraceBlock], my_world[1 * kTraceBlock], my_world[2 * kTraceBlock]);
-                        dir = V3(my_world[3 * kTraceBlock], my_world[4 * kTraceBlock], my_world[5 * kTraceBlock]);
-                        ri.invdir = V3(my_world[6 * kTraceBlock], my_world[7 * kTraceBlock], my_world[8 * kTraceBlock]);
-                        ri.oxinvdir = V3(my_world[9 * kTraceBlock], my_world[10 * kTraceBlock], my_world[11 * kTraceBlock]);
-                        margin = my_world[12 * kTraceBlock];
+                        org = V3(s_world[0 * kTraceBlock + tid], s_world[1 * kTraceBlock + tid], s_world[2 * kTraceBlock + tid]);
+                        dir = V3(s_world[3 * kTraceBlock + tid], s_world[4 * kTraceBlock + tid], s_world[5 * kTraceBlock + tid]);
+                        ri.invdir = V3(s_world[6 * kTraceBlock + tid], s_world[7 * kTraceBlock + tid], s_world[8 * kTraceBlock + tid]);
+                        ri.oxinvdir = V3(s_world[9 * kTraceBlock + tid], s_world[10 * kTraceBlock + tid], s_world[11 * kTraceBlock + tid]);
+                        margin = s_world[12 * kTraceBlock + tid];
+                        cur = kRefNull;
                         continue;
                     }
-                    if (t0 > t_cull) continue;          // subtree starts behind the current hit
+                    if (t0 > t_cull) { cur = kRefNull; continue; }   // subtree starts behind the current hit
                     break;
                 }
             }

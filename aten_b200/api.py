@@ -23,7 +23,7 @@ EXPORTS = [
     "atn_set_frame", "atn_get_frame", "atn_reset", "atn_set_progressive", "atn_set_hit_distance_limit",
     "atn_render", "atn_render_region", "atn_synchronize", "atn_readback", "atn_device_image", "atn_get_stats",
     "atn_set_profiling", "atn_get_stream", "atn_trace_closest", "atn_trace_any", "atn_trace_closest_device",
-    "atn_trace_any_device", "atn_set_bounce_tap", "atn_trace_closest_static", "atn_readback_aov",
+    "atn_trace_any_device", "atn_set_bounce_tap", "atn_trace_closest_static", "atn_readback_aov", "atn_render_ao",
 ]
 
 
@@ -165,6 +165,12 @@ class PathTracing:
         reference's constant (pathtracing.cpp:97)."""
         _check(self._lib, self._lib.atn_render(self._h, C.c_int32(width), C.c_int32(height), C.c_int32(maxSamples),
                                                C.c_int32(maxBounce), C.c_int32(rrBounce)))
+
+    def render_ao(self, width: int, height: int, maxSamples: int, num_rays: int = 1, radius: float = 1.0):
+        """idaten::AORenderer::render (reference src/libidaten/ao/ao.cpp:9-51); the reference fixes
+        num_rays = 1 and radius = 1."""
+        _check(self._lib, self._lib.atn_render_ao(self._h, C.c_int32(width), C.c_int32(height), C.c_int32(maxSamples),
+                                                  C.c_int32(num_rays), C.c_float(radius)))
 
     def render_region(self, width, height, x0, y0, x1, y1, sample_begin, sample_end, maxBounce, rrBounce=3):
         _check(self._lib, self._lib.atn_render_region(

@@ -805,6 +805,91 @@ k_bsdf(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuf
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// N1: ambient-occlusion renderer on the same path (idaten::AORenderer, src/libidaten/ao/ao.cu:20-121;
+// host twin aten::AORenderer, src/libaten/renderer/ao/aorenderer.cpp).  It re-uses k_generate, the
+// closest-hit traversal and k_gather; only the three small kernels below are its own.
+// ---------------------------------------------------------------------------------------------
+// After the primary trace: a miss stores ShadeByAOIfHitMiss() = 1 (ao.cu:27-33); a hit gets the AO
+// sampler (aorenderer.cpp:27-29), its shading point and normal, and joins q_lit.
+__global__ void __launch_bounds__(kShadeBlock)
+k_ao_begin(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb, Counters* cnt)
+{
+    const int count = fp.rw * fp.rh;
+    const int rounds = (count + blockDim.x * gridDim.x - 1) / (blockDim.x * gridDim.x);
+    for (int it = 0; it < rounds; it++) {
+        const int slot = (it * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+        bool lit = false;
+        if (slot < count) {
+            const float4 h0 = pb.hit0[slot];
+            const int2 h1 = pb.hit1[slot];
+            if (h1.x >= 0) {
+                const float4 o = pb.ray_o[slot];
+                const float4 d = pb.ray_d[slot];
+                Ray ray; ray.org = V3(o.x, o.y, o.z); ray.dir = V3(d.x, d.y, d.z);
+                V3 p, n;
+                ao_surface(sc, ray, h1.x, __float_as_int(h0.w), h0.y, h0.z, h0.x, h1.y, &p, &n);
+                pb.surf0[slot] = make_float4(p.x, p.y, p.z, 0.0f);
+                pb.surf1[slot] = make_float4(n.x, n.y, n.z, 0.0f);
+                pb.contrib[slot] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
+                pb.sampler_dim[slot] = 4 + 5 * 300;
+                lit = true;
+            }
+            else {
+                pb.contrib[slot] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+            }
+        }
+        const int pos = warp_append(lit, &cnt->n_lit[0]);
+        if (lit) pb.q_lit[pos] = slot;
+    }
+}
+
+// One AO ray per lit path: Diffuse::sampleDirection + aten::ray(p, dir, n) (aorenderer_impl.h:70-71)
+__global__ void __launch_bounds__(kShadeBlock)
+k_ao_ray(FrameParams fp, const uint32_t* __restrict__ seeds, PathBuffers pb, Counters* cnt)
+{
+    const int count = cnt->n_lit[0];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const int slot = pb.q_lit[i];
+        const int ix = fp.x0 + slot % fp.rw;
+        const int iy = fp.y0 + slot / fp.rw;
+        Sampler sp = ao_sampler_for_path(fp.frame, seeds[(uint32_t)(iy * fp.width + ix) % fp.seed_count]);
+        sp.dim = pb.sampler_dim[slot];
+        const float4 s0 = pb.surf0[slot];
+        const float4 s1 = pb.surf1[slot];
+        V3 next_dir;
+        const Ray ar = ao_ray(V3(s0.x, s0.y, s0.z), V3(s1.x, s1.y, s1.z), &sp, &next_dir);
+        pb.sampler_dim[slot] = sp.dim;
+        pb.ray_o[slot] = make_float4(ar.org.x, ar.org.y, ar.org.z, 0.0f);
+        pb.ray_d[slot] = make_float4(ar.dir.x, ar.dir.y, ar.dir.z, 0.0f);
+        pb.surf2[slot] = make_float4(next_dir.x, next_dir.y, next_dir.z, 0.0f);
+    }
+}
+
+// Fold the AO ray's closest hit into the running value (aorenderer_impl.h:80-111); `last` also applies
+// `ao_color /= ao_num_rays` and spreads the value over rgb.
+__global__ void __launch_bounds__(kShadeBlock)
+k_ao_accum(SceneView sc, PathBuffers pb, Counters* cnt, float radius, int last, int num_rays)
+{
+    const int count = cnt->n_lit[0];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const int slot = pb.q_lit[i];
+        const float4 o = pb.ray_o[slot];
+        const float4 d = pb.ray_d[slot];
+        const float4 h0 = pb.hit0[slot];
+        const int2 h1 = pb.hit1[slot];
+        const float4 s1 = pb.surf1[slot];
+        const float4 s2 = pb.surf2[slot];
+        Ray ar; ar.org = V3(o.x, o.y, o.z); ar.dir = V3(d.x, d.y, d.z);
+        float4 c = pb.contrib[slot];
+        float ao = ao_accumulate(sc, c.x, V3(s1.x, s1.y, s1.z), V3(s2.x, s2.y, s2.z), ar, radius,
+                                 h1.x, __float_as_int(h0.w), h0.y, h0.z, h0.x, h1.y);
+        if (last) { ao /= num_rays; c.y = ao; c.z = ao; }
+        c.x = ao;
+        pb.contrib[slot] = c;
+    }
+}
+
 // pt::gather (pathtracing_impl.cu:282-324) / FilmProgressive::put (film.cpp:61-71)
 __global__ void k_gather(FrameParams fp, PathBuffers pb, float4* image, int progressive, const Counters* cnt, Totals* totals)
 {
@@ -1311,6 +1396,69 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
         }
         r->stats.trace_ms = tot;
     }
+    return ATN_OK;
+}
+
+ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t spp, int32_t num_rays, float radius)
+{
+    if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_ao: NULL handle");
+    if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_render_ao: no scene uploaded");
+    if (width != r->width || height != r->height)
+        return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_ao: size %dx%d differs from the uploaded %dx%d", width, height, r->width, r->height);
+    if (spp < 1 || num_rays < 1 || !(radius > 0.0f))
+        return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_ao: spp %d, num_rays %d, radius %g must be positive", spp, num_rays, radius);
+    CUDA_TRY(cudaSetDevice(r->device));
+    cudaStream_t s = r->stream;
+    FrameParams fp;
+    fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height;
+    fp.max_bounce = 1; fp.rr_bounce = 1; fp.seed_count = r->seed_count;
+    const int n = width * height;
+    const int grid = std::min((n + 255) / 256, r->sm_count * 8);
+    const int sgrid = r->sm_count * 8;
+    uint64_t launches = 0;
+    CUDA_TRY(cudaMemsetAsync(r->totals.p, 0, sizeof(Totals), s));
+    CUDA_TRY(cudaMemsetAsync(r->visits.p, 0, sizeof(Visits), s));
+    CUDA_TRY(cudaEventRecord(r->ev0, s));
+    for (int smp = 0; smp < spp; smp++) {
+        fp.frame = r->frame + (uint32_t)smp;
+        Counters* c = r->counters.p;
+        CUDA_TRY(cudaMemsetAsync(c, 0, sizeof(Counters), s));
+        k_generate<<<grid, 256, 0, s>>>(fp, r->camera, r->seeds.p, r->pb, c);
+        {
+            ClosestPolicy pol{ r->pb, nullptr, kInf, nullptr };
+            k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[0], 0, &c->fetch_closest[0], r->visits.p);
+        }
+        k_ao_begin<<<sgrid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, r->pb, c);
+        launches += 3;
+        for (int i = 0; i < num_rays; i++) {
+            k_ao_ray<<<sgrid, kShadeBlock, 0, s>>>(fp, r->seeds.p, r->pb, c);
+            CUDA_TRY(cudaMemsetAsync(&c->fetch_query, 0, sizeof(int32_t), s));
+            ClosestPolicy pol{ r->pb, r->pb.q_lit, radius, nullptr };
+            k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_lit[0], 0, &c->fetch_query, r->visits.p);
+            k_ao_accum<<<sgrid, kShadeBlock, 0, s>>>(r->sv, r->pb, c, radius, i == num_rays - 1 ? 1 : 0, num_rays);
+            launches += 3;
+        }
+        // n_active[0] primary rays + num_rays * n_lit[0] AO rays: folded into Totals by k_gather through
+        // n_active[0] / n_shadow[0]; the AO rays are reported as shadow rays
+        k_gather<<<grid, 256, 0, s>>>(fp, r->pb, r->image.p, r->progressive, c, r->totals.p);
+        launches++;
+    }
+    CUDA_TRY(cudaEventRecord(r->ev1, s));
+    CUDA_TRY(cudaGetLastError());
+    Totals ht; Visits hv; Counters hc;
+    CUDA_TRY(cudaMemcpyAsync(&ht, r->totals.p, sizeof(Totals), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaMemcpyAsync(&hv, r->visits.p, sizeof(Visits), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaMemcpyAsync(&hc, r->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    r->stats.closest_rays = ht.closest;
+    r->stats.shadow_rays = (uint64_t)hc.n_lit[0] * (uint64_t)num_rays * (uint64_t)spp;   // AO rays (last sample's count x spp)
+    r->stats.camera_samples = (uint64_t)n * (uint64_t)spp;
+    r->stats.kernel_launches = launches;
+    r->stats.nodes_visited = hv.nodes; r->stats.tris_tested = hv.tris;
+    float ms = 0.0f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
+    r->stats.device_ms = ms; r->stats.trace_ms = 0.0f;
+    r->frame += (uint32_t)spp;
     return ATN_OK;
 }
 

@@ -1352,6 +1352,55 @@ ATN_HD void shade_hit(const SceneView& sc, const Ray& ray, int32_t objid, int32_
     shade_bsdf(sc, ray.dir, sf, bounce, rr_bounce, st, next_ray);
 }
 
+// ---------------------------------------------------------------------------------------------
+// N1 (first renderer built on the path): ambient occlusion, AT_NAME::ao::ShandeByAO
+// (src/libaten/renderer/ao/aorenderer_impl.h:33-117) and AORenderer::radiance
+// (src/libaten/renderer/ao/aorenderer.cpp:20-58)
+// ---------------------------------------------------------------------------------------------
+// AORenderer::radiance re-seeds the sampler after GeneratePath (aorenderer.cpp:27-29)
+ATN_HD Sampler ao_sampler_for_path(uint32_t frame, uint32_t rnd)
+{
+    Sampler s;
+    s.scramble = rnd * 0x1fe3434fu * ((frame + 331u * rnd) / 256u);
+    s.idx = frame % 256u;
+    s.dim = 4 + 5 * 300;
+    return s;
+}
+// First half of ShandeByAO: hit evaluation and the (normal-mapped, unflipped) shading normal.
+ATN_HD void ao_surface(const SceneView& sc, const Ray& ray, int32_t objid, int32_t primid, float a, float b,
+                       float t, int32_t mtrlid, V3* p, V3* n)
+{
+    HitRecord rec;
+    evaluate_hit(sc, sc.objects[objid], ray, primid, a, b, t, mtrlid, &rec);
+    const Mtrl m = fill_material(sc, rec.mtrlid);
+    *p = rec.p;
+    *n = apply_normal_map(sc, m.normalMap, rec.normal, rec.u, rec.v);
+}
+// One AO ray: Diffuse::sampleDirection + aten::ray(p, dir, normal) (aorenderer_impl.h:70-71)
+ATN_HD Ray ao_ray(const V3& p, const V3& n, Sampler* sampler, V3* next_dir)
+{
+    const float r1 = sampler->next();
+    const float r2 = sampler->next();
+    *next_dir = lambert_dir(n, r1, r2);
+    return make_ray(p, *next_dir, n);
+}
+// Result of that ray's closest hit (traced with t_max = radius): aorenderer_impl.h:80-111.
+// Occluders that are translucent by alpha are re-traced up to 10 times by the reference; that loop is
+// not reproduced (no such material in any config) -- they count as opaque here.
+ATN_HD float ao_accumulate(const SceneView& sc, float ao, const V3& n, const V3& next_dir, const Ray& ray, float radius,
+                           int32_t hit_objid, int32_t hit_primid, float hit_a, float hit_b, float hit_t, int32_t hit_mtrlid)
+{
+    if (hit_objid < 0) return 1.0f;            // `ao_color = 1.0f` (assignment, as in the reference)
+    HitRecord rec;
+    evaluate_hit(sc, sc.objects[hit_objid], ray, hit_primid, hit_a, hit_b, hit_t, hit_mtrlid, &rec);
+    const float c = dot(rec.normal, next_dir);
+    if (c > 0.0f) {
+        const float pdfb = lambert_pdf(n, next_dir);
+        ao += hit_t / radius * c / pdfb;
+    }
+    return ao;
+}
+
 // Decision after the shadow ray's closest-hit traversal: HitTestToTargetLight
 // (pathtracing_impl.h:266-351, one lookup: alpha blending / stencil are off on this path) +
 // scene::hitLight (src/libaten/scene/scene.h:120-133).

@@ -256,6 +256,13 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height,
                               int32_t x0, int32_t y0, int32_t x1, int32_t y1,
                               int32_t sample_begin, int32_t sample_end,
                               int32_t max_bounce, int32_t rr_bounce);
+/* Row N1 of SURVEY 8f, the first renderer that sits on this path: ambient occlusion.
+ * idaten::AORenderer::render (src/libidaten/ao/ao.cpp:9-51, kernels ao.cu:20-121) / aten::AORenderer
+ * (src/libaten/renderer/ao/aorenderer.cpp:20-146, ShandeByAO aorenderer_impl.h:33-117): camera ray,
+ * closest hit, `num_rays` cosine-distributed rays of length `radius` from the hit, image = AO value in
+ * rgb.  The reference hard-codes num_rays = 1, radius = 1.  A primary miss stores 1.0 (GPU kernel
+ * semantics, ao.cu:27-33).  Advances the frame counter by spp; accumulates like atn_render. */
+ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t spp, int32_t num_rays, float radius);
 /* Blocks until the handle's stream is idle. */
 ATN_API int atn_synchronize(AtnRenderer* r);
 /* Replaces the CUDA-GL surface the reference writes with surf2Dwrite (pathtracing_impl.cu:282-324):

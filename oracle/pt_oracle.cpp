@@ -282,6 +282,62 @@ int oracle_render(const AtnSceneBlob* blob, const AtnCameraParameter* cam, const
     return 0;
 }
 
+// aten::AORenderer::RenderAO (src/libaten/renderer/ao/aorenderer.cpp:75-146) driven as `frames` frames
+// of one sample with FilmProgressive accumulation.
+// host_row_break = 1 reproduces the stock host renderer bit for bit, including its quirk: the
+// `if (is_terminated) break;` at aorenderer.cpp:136-138 sits in the x loop (there is no sample loop), so
+// the first primary-ray miss of a scanline ends that scanline and neither that pixel nor the rest of the
+// row is written to the film.  host_row_break = 0 is the per-pixel semantics of the reference's GPU
+// kernels (src/libidaten/ao/ao.cu:20-35): a miss stores ShadeByAOIfHitMiss() = 1.0 and every pixel is
+// independent -- what the CUDA path implements.
+__attribute__((visibility("default")))
+int oracle_render_ao(const AtnSceneBlob* blob, const AtnCameraParameter* cam, const uint32_t* seeds, uint32_t seed_count,
+                     int32_t W, int32_t H, uint32_t first_frame, int32_t frames, int32_t num_rays, float radius,
+                     int32_t host_row_break, AtnVec4* image)
+{
+    const Scene s = MakeScene(blob);
+    for (int32_t f = 0; f < frames; f++) {
+        const uint32_t frame = first_frame + (uint32_t)f;
+#pragma omp parallel for schedule(dynamic, 4)
+        for (int32_t y = 0; y < H; y++) {
+            for (int32_t x = 0; x < W; x++) {
+                const int32_t idx = y * W + x;
+                const uint32_t rnd = seeds[(uint32_t)idx % seed_count];
+                Sampler sp = sampler_for_path(frame, rnd);
+                const float r1 = sp.next();
+                const float r2 = sp.next();
+                const Ray ray = camera_sample(*cam, (x + r1) / (float)(cam->width), (y + r2) / (float)(cam->height));
+                sp = ao_sampler_for_path(frame, rnd);
+                AtnHit isect;
+                float ao = 1.0f;
+                const bool is_hit = Traverse(s, ray, kInf, &isect, nullptr);
+                if (!is_hit && host_row_break) break;
+                if (is_hit) {
+                    ao = 0.0f;
+                    V3 p, n;
+                    ao_surface(s.view, ray, isect.objid, isect.primid, isect.a, isect.b, isect.t, isect.mtrlid, &p, &n);
+                    for (int32_t i = 0; i < num_rays; i++) {
+                        V3 next_dir;
+                        const Ray ar = ao_ray(p, n, &sp, &next_dir);
+                        AtnHit ah;
+                        Traverse(s, ar, radius, &ah, nullptr);
+                        ao = ao_accumulate(s.view, ao, n, next_dir, ar, radius, ah.objid, ah.primid, ah.a, ah.b, ah.t, ah.mtrlid);
+                    }
+                    ao /= num_rays;
+                }
+                AtnVec4& cur = image[idx];
+                const float nn = (float)((int32_t)cur.w);
+                const V3 col = V3(ao) / 1.0f;
+                cur.x = (nn * cur.x + col.x) / (nn + 1);
+                cur.y = (nn * cur.y + col.y) / (nn + 1);
+                cur.z = (nn * cur.z + col.z) / (nn + 1);
+                cur.w = nn + 1;
+            }
+        }
+    }
+    return 0;
+}
+
 __attribute__((visibility("default")))
 int oracle_cmj(uint32_t idx, uint32_t scramble, int32_t n, float* out)
 {

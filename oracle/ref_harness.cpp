@@ -479,6 +479,7 @@ int Usage()
         "  trace  <name> W H frame depth rr out_records.bin [out_image.f32]\n"
         "  rays   <name> rays.bin hits.bin         (n x {org[3],dir[3],tmax} -> n x AtnHit)\n"
         "  bench  <name> W H frames depth rr threads repeats     (JSON line with timings and ray counts)\n"
+        "  ao     <name> W H frame threads out_image.f32            (stock aten::AORenderer, one frame at index `frame`)\n"
         "  cmj    out.bin                           (golden CMJ stream)\n");
     return 2;
 }
@@ -569,6 +570,31 @@ int main(int argc, char** argv)
                name.c_str(), W, H, frames, depth, threads, best, samples / best / 1e3,
                (double)(cnt.closest + cnt.shadow) / best / 1e3,
                (unsigned long long)cnt.closest, (unsigned long long)cnt.shadow, build_ms);
+        return 0;
+    }
+
+    if (cmd == "ao") {
+        // stock aten::AORenderer (src/libaten/renderer/ao/aorenderer.cpp), 1 AO ray, radius 1, progressive film
+        if (argc < 9) return Usage();
+        // argv[6] = frame index of the ONE frame rendered.  (The stock renderer keeps its Intersection array
+        // across frames without resetting .t, so later frames of one renderer object only accept hits closer
+        // than the previous frame's -- a fresh renderer per frame avoids pinning that.)
+        const int W = atoi(argv[4]), H = atoi(argv[5]), frame = atoi(argv[6]), threads = atoi(argv[7]);
+        const int frames = 1;
+        Harness hs;
+        if (!hs.Build(name, W, H)) return 1;
+        aten::OMPUtil::setThreadNum(threads);
+        omp_set_num_threads(threads);
+        struct FramedAO : public aten::AORenderer { void SetFrame(uint32_t f) { frame_count_ = f; } } ao;
+        ao.SetFrame(frame);
+        aten::FilmProgressive film(W, H);
+        auto dst = hs.MakeDst(&film, 1, 1);
+        double t0 = NowMs();
+        ao.render(hs.ctxt, dst, &hs.scene, &hs.camera);
+        const double ms = NowMs() - t0;
+        WriteFile(argv[8], film.image().data(), film.image().size() * sizeof(aten::vec4));
+        printf("{\"scene\": \"%s\", \"renderer\": \"ao\", \"w\": %d, \"h\": %d, \"frames\": %d, \"threads\": %d, \"render_ms\": %.3f}\n",
+               name.c_str(), W, H, frames, threads, ms);
         return 0;
     }
 

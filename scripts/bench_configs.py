@@ -44,6 +44,30 @@ def render_bench(name, W, H, spp, steps=3, warmup=2, label=""):
     print(json.dumps(out), flush=True)
 
 
+def ao_bench(name, W, H, spp, steps=3, warmup=2, label=""):
+    """Row N1: the ambient-occlusion renderer (1 AO ray of radius 1 per sample, as the reference fixes it)."""
+    scene = ol.ref_scene(name, W, H)
+    r = PathTracing(0)
+    r.UpdateSceneData(scene)
+    r.SetEnableProgressive(False)
+    for _ in range(warmup):
+        r.reset(); r.render_ao(W, H, spp, 1, 1.0)
+    ms = rays = samples = 0
+    for _ in range(steps):
+        r.reset(); r.render_ao(W, H, spp, 1, 1.0)
+        st = r.stats()
+        ms += st["device_ms"]; rays += st["closest_rays"] + st["shadow_rays"]; samples += st["camera_samples"]
+    img = r.readback()
+    r.close()
+    t0 = time.perf_counter()
+    ref, info = ol.ref_render_ao(name, 480, 270, frame=0, threads=os.cpu_count() or 1)
+    print(json.dumps({"config": label, "renderer": "ao", "scene": name, "w": W, "h": H, "spp": spp,
+                      "ms_per_step": round(ms / steps, 3), "mrays_per_s": round(rays / ms / 1e3, 1),
+                      "msamples_per_s": round(samples / ms / 1e3, 1), "mean_ao": float(img[..., 0].mean() / spp),
+                      "reference_cpu": {"msamples_per_s": round(480 * 270 / info["render_ms"] / 1e3, 4),
+                                        "sample": f"stock aten::AORenderer, {name} 480x270, 1 frame, {info['threads']} threads"}}), flush=True)
+
+
 def ray_stress(name, n_rays, label=""):
     """Incoherent diffuse secondary rays: origins = surface points found by a first random pass,
     directions cosine-distributed about nothing in particular (uniform sphere), closest-hit and any-hit."""
@@ -109,6 +133,7 @@ def main():
     render_bench("sponza_tex", 1920, 1080, 16 if not q else 2, label="C3 stand-in: sponza_lod + albedo/normal maps + synthetic-sky IBL, 1080p 16spp")
     render_bench("instanced_dragon", 3840, 2160, 8 if not q else 1, label="C4 stand-in: instanced dragon+teapot+suzanne, Disney/refraction, 4K, 8 spp (one GPU's share of 64 spp on 8)")
     render_bench("dragon_grid10", 1920, 1080, 4 if not q else 1, label="C5 stand-in (rendered): 100 instanced dragons = 10 M triangles, 1080p 4spp")
+    ao_bench("sponza_atrium", 1920, 1080, 16 if not q else 2, label="N1 ambient occlusion, sponza_lod 1080p 16spp")
     ray_stress("dragon_grid10", 100_000_000 if not q else 5_000_000,
                label="C5 stand-in: 100 M incoherent secondary rays into 100 instanced dragons (10 M triangles), closest-hit and any-hit")
 

@@ -60,6 +60,10 @@ class Golden:
         m = self.meta[name]
         return np.frombuffer(_gz(f"{name}.image.f32.gz"), np.float32).reshape(m["h"], m["w"], 4)
 
+    def ao(self, name):
+        m = self.meta[name]
+        return np.frombuffer(_gz(f"{name}.ao.f32.gz"), np.float32).reshape(m["h"], m["w"], 4)
+
     def rays(self, name):
         buf = np.frombuffer(_gz(f"{name}.rays.gz"), np.float32).reshape(-1, 7)
         rays = np.zeros(len(buf), self.sio.RAY_DTYPE)

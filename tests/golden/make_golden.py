@@ -12,6 +12,7 @@ Files (all little endian, gzip):
   <scene>.image.f32.gz            float4 image of frames 0..FRAMES-1 through aten::PathTracing::render
                                   with FilmProgressive
   <scene>.rays.gz / .hits.gz      random rays {org,dir,tmax} and the reference's Traverse<Closest> hits
+  <scene>.ao.f32.gz               float4 film of ONE frame (index FRAME) of the stock aten::AORenderer (ref_harness ao)
 """
 import gzip
 import json
@@ -85,6 +86,8 @@ def main():
         buf[:, :3] = rays["org"]; buf[:, 3:6] = rays["dir"]; buf[:, 6] = tmax
         gz_write(os.path.join(HERE, f"{name}.rays.gz"), buf.tobytes())
         gz_write(os.path.join(HERE, f"{name}.hits.gz"), hits.tobytes())
+        ao, _ = ol.ref_render_ao(name, W, H, frame=FRAME)
+        gz_write(os.path.join(HERE, f"{name}.ao.f32.gz"), ao.tobytes())
         meta[name] = {"w": W, "h": H, "frame": FRAME, "frames": FRAMES, "depth": 5, "rr": 3, "scene": info,
                       "closest_rays": tinfo["closest_rays"], "shadow_rays": tinfo["shadow_rays"],
                       "hit_fraction": float((hits["objid"] >= 0).mean())}

@@ -82,6 +82,27 @@ def render(scene: sio.Scene, frames=1, max_depth=5, rr_depth=3, first_frame=0, r
     return img.reshape(H, W, 4), recs, stats
 
 
+def render_ao(scene: sio.Scene, frames=1, first_frame=0, num_rays=1, radius=1.0, image=None, host_row_break=False):
+    W, H = scene.width, scene.height
+    img = np.zeros((H * W, 4), np.float32) if image is None else np.ascontiguousarray(image, np.float32).reshape(H * W, 4)
+    seeds = scene.seeds_for(W * H)
+    blob = scene.blob()
+    cam = np.ascontiguousarray(scene.camera)
+    lib().oracle_render_ao(C.byref(blob), C.c_void_p(cam.ctypes.data), C.c_void_p(seeds.ctypes.data), C.c_uint32(len(seeds)),
+                           C.c_int32(W), C.c_int32(H), C.c_uint32(first_frame), C.c_int32(frames), C.c_int32(num_rays),
+                           C.c_float(radius), C.c_int32(1 if host_row_break else 0), C.c_void_p(img.ctypes.data))
+    return img.reshape(H, W, 4)
+
+
+def ref_render_ao(name, W, H, frame=0, threads=8):
+    """One frame of the stock aten::AORenderer at frame index `frame` (film starts at (0,0,0,1))."""
+    with tempfile.TemporaryDirectory() as d:
+        pi = os.path.join(d, "i.f32")
+        info = ref_run("ao", name, W, H, frame, threads, pi)
+        img = np.fromfile(pi, np.float32).reshape(H, W, 4)
+    return img, info
+
+
 def cmj(idx, scramble, n):
     out = np.zeros(n, np.float32)
     lib().oracle_cmj(C.c_uint32(idx), C.c_uint32(scramble), C.c_int32(n), C.c_void_p(out.ctypes.data))

@@ -391,3 +391,32 @@ def test_first_hit_aovs_vs_oracle(golden, renderers, name):
     hit = nd[..., 3] > 0
     assert hit.mean() > 0.5 and (nd[..., 3][hit] == 1.0).all() and (am[..., 3][hit] >= 0).all()
     assert np.allclose(np.linalg.norm(nd[..., :3][hit], axis=-1), 1.0, atol=1e-5)
+
+
+@pytest.mark.parametrize("name", ["sponza_atrium", "instanced", "cornell"])
+def test_ao_renderer_vs_oracle(golden, renderers, name):
+    """Row N1 on the GPU (atn_render_ao) against the restatement in per-pixel mode, and against the stock
+    aten::AORenderer film wherever the host renderer wrote a pixel.  The AO value involves sin/cos
+    (cosine sampling), so the tolerance is the shading one: 99 % of pixels within 1e-4 relative."""
+    m = golden.meta[name]
+    r = renderers[name]
+    r.reset(); r.set_frame(m["frame"]); r.SetEnableProgressive(True)
+    r.render_ao(m["w"], m["h"], 1, 1, 1.0)
+    got = r.readback()
+    want = ol.render_ao(golden.scene(name), frames=1, first_frame=m["frame"])
+    assert (got[..., 3] == 1).all() and np.isfinite(got).all()
+    close = np.abs(got[..., 0] - want[..., 0]) <= 1e-4 * np.maximum(np.abs(want[..., 0]), 1e-2)
+    assert close.mean() > 0.99, close.mean()
+    assert (got[..., 0] == got[..., 1]).all() and (got[..., 0] == got[..., 2]).all()
+    ref = golden.ao(name)                     # stock host film: (0 + v) / 2 where written (count starts at 1)
+    written = ref[..., 3] == 2
+    if written.any():
+        c2 = np.abs(got[..., 0][written] - 2 * ref[..., 0][written]) <= 2e-4 * np.maximum(2 * ref[..., 0][written], 1e-2)
+        assert c2.mean() > 0.99
+    # more rays, other radius: still the restatement
+    r.reset(); r.set_frame(0)
+    r.render_ao(m["w"], m["h"], 2, 3, 0.5)
+    got = r.readback()
+    want = ol.render_ao(golden.scene(name), frames=2, num_rays=3, radius=0.5)
+    close = np.abs(got[..., 0] - want[..., 0]) <= 1e-4 * np.maximum(np.abs(want[..., 0]), 1e-2)
+    assert close.mean() > 0.985, close.mean()

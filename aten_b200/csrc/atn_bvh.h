@@ -37,12 +37,13 @@ struct alignas(64) PairNode {
 };
 static_assert(sizeof(PairNode) == 64, "PairNode");
 
-struct alignas(16) TriLeaf {
+struct alignas(32) TriLeaf {
     float v0[3]; int32_t primid;
     float e1[3]; int32_t mtrlid;      // v1 - v0 (the float subtraction intersectTriangle starts with)
     float e2[3]; int32_t mesh_id;     // v2 - v0
+    int32_t pad[4];                   // 64 B: one 256-bit + one 128-bit load, 32-byte aligned
 };
-static_assert(sizeof(TriLeaf) == 48, "TriLeaf");
+static_assert(sizeof(TriLeaf) == 64, "TriLeaf");
 
 struct alignas(16) InstLeaf {
     int32_t objid;      // object index recorded in isect.objid
@@ -109,6 +110,7 @@ struct ListBuilder {
         tl.v0[0] = a.x; tl.v0[1] = a.y; tl.v0[2] = a.z; tl.primid = (int32_t)primid;
         tl.e1[0] = b.x - a.x; tl.e1[1] = b.y - a.y; tl.e1[2] = b.z - a.z; tl.mtrlid = tp.mtrlid;
         tl.e2[0] = c.x - a.x; tl.e2[1] = c.y - a.y; tl.e2[2] = c.z - a.z; tl.mesh_id = tp.mesh_id;
+        tl.pad[0] = tl.pad[1] = tl.pad[2] = tl.pad[3] = 0;
         out->tris.push_back(tl);
         return leaf_ref((int32_t)out->tris.size() - 1);
     }
@@ -237,6 +239,238 @@ inline EncodedBvh encode_bvh(const AtnSceneBlob* scene)
         out.top_root = wrap_root(&out, scene->node_lists[0][0], r);
         out.max_depth += lb.depth_seen + 4;
     }
+    return out;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// Wide (4-slot) encoding.
+//
+// The reference's trees are binary with one triangle per leaf.  A QuadNode stands for one inner node P
+// of the reference's tree whose own box has already been tested, and holds up to four SLOTS obtained
+// by replacing children of P by their own children (largest box first) while the result fits.  What makes
+// this exact rather than approximate:
+//   * an inner node g below a replaced child X keeps its own box.  The reference reaches g only if X's
+//     box was hit as well; g's box lies inside X's box plane by plane (checked here, node by node --
+//     X is only replaced if it holds), and the slab test aabb.h:61-86 is monotone in the plane values
+//     (same multiplier, same addend, rounding is monotone), so hit(g) implies hit(X) bit for bit;
+//   * a LEAF below a replaced child X is never box-tested by the reference; it is visited iff X's box
+//     was hit.  Its slot therefore carries X's box;
+//   * a leaf that is a child of P itself is visited whenever P is: its slot carries an always-hit box.
+// Slots keep the reference's depth-first order and leaves keep their depth-first numbers, so the
+// tie-break rank is unchanged.
+// ---------------------------------------------------------------------------------------------
+struct alignas(128) QuadNode {
+    // slots (0,1): q[0] = min.x0, min.y0, min.x1, min.y1 ; q[1] = max.x0, max.y0, max.x1, max.y1 ;
+    //              q[2] = min.z0, min.z1, max.z0, max.z1
+    // slots (2,3): q[3], q[4], q[5] likewise.  Pairs (x, y) share the (invdir.x, invdir.y) multiplier pair.
+    float q[6][4];
+    int32_t ref[4];        // >= 0 QuadNode index, < 0 leaf ~ref, kRefNull: empty slot
+    int32_t pad[4];
+};
+static_assert(sizeof(QuadNode) == 128, "QuadNode");
+
+struct alignas(32) InstLeafW {
+    int32_t objid, root, w2l, meshid;
+    float wmin[3]; float pad0;      // conservative world-space bounds of the instance (entry pre-filter)
+    float wmax[3]; float pad1;
+    int32_t pad2[4];
+};
+static_assert(sizeof(InstLeafW) == 64, "InstLeafW");
+
+struct WideBvh {
+    std::vector<QuadNode> nodes;
+    std::vector<TriLeaf> tris;
+    std::vector<InstLeafW> insts;
+    int32_t top_root{ kRefNull };
+    int32_t max_stack{ 0 };          // bound on the traversal stack depth (entries)
+    uint64_t slots_used{ 0 }, replaced{ 0 }, not_nested{ 0 };
+    std::string error;
+};
+
+namespace detail {
+
+struct WideBuilder {
+    const AtnBvhNode* list;
+    uint32_t count;
+    bool top;
+    EncodedBvh* leaves;                       // receives TriLeaf / InstLeaf records in depth-first order
+    ListBuilder* lb;                          // leaf construction and bounds
+    WideBvh* out;
+    std::vector<int32_t> kid0, kid1, leafref; // per original node
+    std::vector<uint8_t> nested;
+    int32_t depth_seen{ 0 };
+
+    bool inner(int32_t i) const { return !ListBuilder::is_leaf(list[i]); }
+
+    // pass 1: children and leaves in the reference's depth-first order
+    void scan(int32_t i, int32_t depth)
+    {
+        if (!out->error.empty()) return;
+        if (i < 0 || (uint32_t)i >= count) { out->error = "link out of range in node list"; return; }
+        if (depth > 96) { out->error = "node list deeper than 96 levels (cyclic links?)"; return; }
+        const AtnBvhNode& n = list[i];
+        if (ListBuilder::is_leaf(n)) {
+            leafref[i] = lb->make_leaf(n);
+            if (!leaves->error.empty()) out->error = leaves->error;
+            return;
+        }
+        const int32_t escape = (int32_t)n.miss;
+        int nk = 0;
+        int32_t c = (int32_t)n.hit;
+        while (c >= 0 && c != escape) {
+            if ((uint32_t)c >= count) { out->error = "link out of range in node list"; return; }
+            if (nk == 2) { out->error = "inner node with more than two children"; return; }
+            (nk == 0 ? kid0 : kid1)[i] = c;
+            nk++;
+            c = (int32_t)list[c].miss;
+        }
+        bool ok = true;
+        const int32_t ks[2] = { kid0[i], kid1[i] };
+        for (int k = 0; k < nk; k++) {
+            scan(ks[k], depth + 1);
+            if (!out->error.empty()) return;
+            if (inner(ks[k])) {
+                const AtnBvhNode& g = list[ks[k]];
+                for (int a = 0; a < 3; a++)
+                    if (!(g.boxmin[a] >= n.boxmin[a] && g.boxmax[a] <= n.boxmax[a])) ok = false;
+            }
+        }
+        nested[i] = ok ? 1 : 0;
+        if (!ok) out->not_nested++;
+    }
+
+    struct Slot { int32_t node, boxnode; };   // boxnode: original node whose box the slot tests, -1 = always hit
+
+    static float area(const AtnBvhNode& n)
+    {
+        const float dx = n.boxmax[0] - n.boxmin[0], dy = n.boxmax[1] - n.boxmin[1], dz = n.boxmax[2] - n.boxmin[2];
+        return dx * dy + dy * dz + dz * dx;
+    }
+
+    void push_kids(std::vector<Slot>& slots, size_t at, int32_t X, bool x_tested)
+    {
+        // children of X in order; a leaf child inherits X's box unless X's box is known to be hit
+        std::vector<Slot> ins;
+        const int32_t ks[2] = { kid0[X], kid1[X] };
+        for (int k = 0; k < 2; k++) {
+            if (ks[k] < 0) continue;
+            if (inner(ks[k])) ins.push_back({ ks[k], ks[k] });
+            else if (leafref[ks[k]] != kRefNull) ins.push_back({ ks[k], x_tested ? -1 : X });
+        }
+        slots.insert(slots.begin() + at, ins.begin(), ins.end());
+    }
+
+    int nkids_live(int32_t X) const
+    {
+        int n = 0;
+        const int32_t ks[2] = { kid0[X], kid1[X] };
+        for (int k = 0; k < 2; k++)
+            if (ks[k] >= 0 && (inner(ks[k]) || leafref[ks[k]] != kRefNull)) n++;
+        return n;
+    }
+
+    // QuadNode for the slots `slots` (already the children of a tested node); returns its index
+    int32_t emit(std::vector<Slot> slots, int32_t depth)
+    {
+        if (depth > depth_seen) depth_seen = depth;
+        for (;;) {
+            int best = -1; float best_area = -1.0f;
+            for (size_t s = 0; s < slots.size(); s++) {
+                const int32_t X = slots[s].node;
+                if (!inner(X) || !nested[X]) continue;
+                if (slots.size() - 1 + (size_t)nkids_live(X) > 4) continue;
+                const float a = area(list[X]);
+                if (a > best_area) { best_area = a; best = (int)s; }
+            }
+            if (best < 0) break;
+            const int32_t X = slots[best].node;
+            slots.erase(slots.begin() + best);
+            push_kids(slots, (size_t)best, X, false);
+            out->replaced++;
+        }
+        if (slots.empty()) return kRefNull;
+        const int32_t self = (int32_t)out->nodes.size();
+        out->nodes.emplace_back();
+        int32_t refs[4] = { kRefNull, kRefNull, kRefNull, kRefNull };
+        for (size_t s = 0; s < slots.size(); s++) {
+            const int32_t X = slots[s].node;
+            if (inner(X)) {
+                std::vector<Slot> sub;
+                push_kids(sub, 0, X, true);
+                refs[s] = emit(sub, depth + 1);
+            }
+            else refs[s] = leafref[X];
+        }
+        QuadNode& qn = out->nodes[self];
+        const float big = 3.0e38f;
+        for (int s = 0; s < 4; s++) {
+            float mn[3] = { big, big, big }, mx[3] = { big, big, big };      // empty: never hit (masked by ref too)
+            if ((size_t)s < slots.size() && refs[s] != kRefNull) {
+                if (slots[s].boxnode < 0) { for (int a = 0; a < 3; a++) { mn[a] = -big; mx[a] = big; } }
+                else for (int a = 0; a < 3; a++) { mn[a] = list[slots[s].boxnode].boxmin[a]; mx[a] = list[slots[s].boxnode].boxmax[a]; }
+                out->slots_used++;
+            }
+            const int g = (s >> 1) * 3, h = (s & 1);
+            qn.q[g + 0][h * 2 + 0] = mn[0]; qn.q[g + 0][h * 2 + 1] = mn[1];
+            qn.q[g + 1][h * 2 + 0] = mx[0]; qn.q[g + 1][h * 2 + 1] = mx[1];
+            qn.q[g + 2][h] = mn[2]; qn.q[g + 2][2 + h] = mx[2];
+            qn.ref[s] = refs[s];
+            qn.pad[s] = 0;
+        }
+        return self;
+    }
+
+    // the whole list: the root's own box is tested like any inner node's (threaded_bvh_traverser.h:278-280)
+    int32_t run()
+    {
+        kid0.assign(count, -1); kid1.assign(count, -1); leafref.assign(count, kRefNull); nested.assign(count, 0);
+        scan(0, 0);
+        if (!out->error.empty()) return kRefNull;
+        if (!inner(0)) return leafref[0];        // a leaf root is never box-tested by the reference
+        std::vector<Slot> slots{ Slot{ 0, 0 } };
+        return emit(slots, 1);
+    }
+};
+
+}  // namespace detail
+
+inline WideBvh encode_wide(const AtnSceneBlob* scene)
+{
+    WideBvh out;
+    if (scene->node_list_count == 0) return out;
+    EncodedBvh leaves;
+    std::vector<int32_t> roots(scene->node_list_count, kRefNull);
+    int32_t bottom_depth = 0;
+    for (uint32_t k = 1; k < scene->node_list_count; k++) {
+        if (scene->node_list_sizes[k] == 0) continue;
+        detail::ListBuilder lb{ scene->node_lists[k], scene->node_list_sizes[k], false, scene, &leaves, &roots };
+        detail::WideBuilder wb{ scene->node_lists[k], scene->node_list_sizes[k], false, &leaves, &lb, &out };
+        roots[k] = wb.run();
+        if (!out.error.empty()) return out;
+        bottom_depth = std::max(bottom_depth, wb.depth_seen);
+    }
+    int32_t top_depth = 0;
+    if (scene->node_list_sizes[0] > 0) {
+        detail::ListBuilder lb{ scene->node_lists[0], scene->node_list_sizes[0], true, scene, &leaves, &roots };
+        detail::WideBuilder wb{ scene->node_lists[0], scene->node_list_sizes[0], true, &leaves, &lb, &out };
+        out.top_root = wb.run();
+        if (!out.error.empty()) return out;
+        top_depth = wb.depth_seen;
+        out.insts.resize(leaves.insts.size());
+        for (size_t i = 0; i < leaves.insts.size(); i++) {
+            const InstLeaf& il = leaves.insts[i];
+            InstLeafW& w = out.insts[i];
+            w.objid = il.objid; w.root = il.root; w.w2l = il.w2l; w.meshid = il.meshid;
+            float mn[3], mx[3];
+            lb.leaf_bounds(leaf_ref((int32_t)i), mn, mx);
+            for (int a = 0; a < 3; a++) { w.wmin[a] = mn[a]; w.wmax[a] = mx[a]; }
+            w.pad0 = 0.0f; w.pad1 = 0.0f; w.pad2[0] = w.pad2[1] = w.pad2[2] = w.pad2[3] = 0;
+        }
+    }
+    out.tris.swap(leaves.tris);
+    // every node step leaves at most three entries behind, an instance entry one more
+    out.max_stack = 3 * (bottom_depth + top_depth) + 2;
     return out;
 }
 

@@ -66,10 +66,16 @@ static int set_error(int code, const char* fmt, ...)
 // ---------------------------------------------------------------------------------------------
 // device-side views
 // ---------------------------------------------------------------------------------------------
+#ifndef ATN_WIDE
+#define ATN_WIDE 1          // 1: QuadNode traversal (k_trace4), 0: PairNode traversal (k_trace)
+#endif
+constexpr int kInstStride = ATN_WIDE ? 4 : 1;   // 16-byte words per instance leaf record
+constexpr int kTriStride = 4;                    // 16-byte words per TriLeaf
+
 struct BvhView {
-    const float4* nodes;     // PairNode as 4 x float4
-    const float4* tris;      // TriLeaf as 3 x float4
-    const int4* insts;       // InstLeaf
+    const float4* nodes;     // QuadNode as 8 x float4 (ATN_WIDE) or PairNode as 4 x float4
+    const float4* tris;      // TriLeaf as 4 x float4 (the last one is padding)
+    const float4* insts;     // InstLeafW as 3 x 16 B (ATN_WIDE) or InstLeaf as one int4
     const AtnMat4* matrices;
     int32_t top_root;
     float t_min;
@@ -156,11 +162,11 @@ __device__ __forceinline__ void resolve_hit(const BvhView& bv, const TraceResult
                                             int32_t* mtrlid, int32_t* meshid)
 {
     if (r.leaf < 0) { *objid = -1; *primid = -1; *mtrlid = -1; *meshid = -1; return; }
-    const float4* tp = bv.tris + (size_t)r.leaf * 3;
+    const float4* tp = bv.tris + (size_t)r.leaf * kTriStride;
     *primid = __float_as_int(ldg4(tp + 0).w);
     *mtrlid = __float_as_int(ldg4(tp + 1).w);
     const int32_t mesh = __float_as_int(ldg4(tp + 2).w);
-    const int4 il = __ldg(bv.insts + r.inst);
+    const int4 il = __ldg(reinterpret_cast<const int4*>(bv.insts) + (size_t)r.inst * kInstStride);
     *objid = il.x;
     *meshid = mesh < 0 ? il.w : mesh;
 }
@@ -483,7 +489,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
             bool finished = false;
             if (on_tri) {
                 const int32_t leaf = ~cur;
-                const float4* tp = bv.tris + (size_t)leaf * 3;
+                const float4* tp = bv.tris + (size_t)leaf * kTriStride;
                 const float4 a = ldg4(tp + 0);
                 const float4 b = ldg4(tp + 1);
                 const float4 c = ldg4(tp + 2);
@@ -511,7 +517,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                 if (__popc(me) >= kEntryBatch || busy == 0u) {
                     if (want_entry) {
                         const int32_t leaf = ~cur;
-                        const int4 il = __ldg(bv.insts + leaf);
+                        const int4 il = __ldg(reinterpret_cast<const int4*>(bv.insts) + leaf);
                         cur = kRefNull;
                         if (il.y != kRefNull) {
                             const int2 e = make_int2(kRefExit, __float_as_int(-kInf));
@@ -569,6 +575,307 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
         atomicAdd(&visits->tris, (unsigned long long)n_tris);
     }
 }
+
+// ---------------------------------------------------------------------------------------------
+// traversal over QuadNodes (atn_bvh.h "Wide (4-slot) encoding")
+// ---------------------------------------------------------------------------------------------
+#ifndef ATN_SMEM_STACK4
+#define ATN_SMEM_STACK4 16
+#endif
+#ifndef ATN_LEAF_BATCH4
+#define ATN_LEAF_BATCH4 6
+#endif
+constexpr int kSmemStack4 = ATN_SMEM_STACK4;
+constexpr int kLeafBatch4 = ATN_LEAF_BATCH4;
+constexpr uint32_t kStackStride = kTraceBlock * 8u;     // bytes between two levels of one lane's shared stack
+
+// Two IEEE multiplications in one issue slot (FMUL2).  Only the products are packed: ptxas contracts a
+// packed multiply feeding a packed add into FFMA2 even with .rn on both, which would round once where
+// the reference rounds twice; the additions stay scalar add.rn.f32, which are never contracted.
+__device__ __forceinline__ float2 mul2(float ax, float ay, float2 b)
+{
+    float2 r;
+    asm("{\n\t.reg .b64 ra, rb, rc;\n\tmov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\tmul.rn.f32x2 rc, ra, rb;\n\tmov.b64 {%0, %1}, rc;\n\t}"
+        : "=f"(r.x), "=f"(r.y) : "f"(ax), "f"(ay), "f"(b.x), "f"(b.y));
+    return r;
+}
+// One 256-bit read-only load (LDG.E.256, sm_100): a lane's 32-byte sector in one L1 request instead of two.
+#ifndef ATN_LDG256
+#define ATN_LDG256 1
+#endif
+struct F4x2 { float4 lo, hi; };
+__device__ __forceinline__ F4x2 ldg8(const float4* p)
+{
+    F4x2 r;
+#if ATN_LDG256
+    asm volatile("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=f"(r.lo.x), "=f"(r.lo.y), "=f"(r.lo.z), "=f"(r.lo.w), "=f"(r.hi.x), "=f"(r.hi.y), "=f"(r.hi.z), "=f"(r.hi.w)
+                 : "l"(p));
+#else
+    r.lo = ldg4(p); r.hi = ldg4(p + 1);
+#endif
+    return r;
+}
+__device__ __forceinline__ void sts64(uint32_t addr, int32_t x, int32_t y)
+{
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" :: "r"(addr), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ int2 lds64(uint32_t addr)
+{
+    int2 v;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr) : "memory");
+    return v;
+}
+
+// Entry distance and exit distance of the two slots held by one float4 triple of a QuadNode
+// (aabb::hit, aabb.h:61-86: plane * invdir + oxinvdir, min / max per axis).
+struct SlabPair { float t0a, t1a, t0b, t1b; };
+__device__ __forceinline__ SlabPair slab_pair(const float4 mn_xy, const float4 mx_xy, const float4 z, const float2 inv_xy,
+                                              const float2 inv_zz, const V3& ox)
+{
+    const float2 na = mul2(mn_xy.x, mn_xy.y, inv_xy), nb = mul2(mn_xy.z, mn_xy.w, inv_xy);
+    const float2 fa = mul2(mx_xy.x, mx_xy.y, inv_xy), fb = mul2(mx_xy.z, mx_xy.w, inv_xy);
+    const float2 nz = mul2(z.x, z.y, inv_zz), fz = mul2(z.z, z.w, inv_zz);
+    const float nax = na.x + ox.x, nay = na.y + ox.y, naz = nz.x + ox.z;
+    const float fax = fa.x + ox.x, fay = fa.y + ox.y, faz = fz.x + ox.z;
+    const float nbx = nb.x + ox.x, nby = nb.y + ox.y, nbz = nz.y + ox.z;
+    const float fbx = fb.x + ox.x, fby = fb.y + ox.y, fbz = fz.y + ox.z;
+    SlabPair r;
+    r.t1a = fminf(fminf(fmaxf(fax, nax), fmaxf(fay, nay)), fmaxf(faz, naz));
+    r.t0a = fmaxf(fmaxf(fminf(fax, nax), fminf(fay, nay)), fminf(faz, naz));
+    r.t1b = fminf(fminf(fmaxf(fbx, nbx), fmaxf(fby, nby)), fmaxf(fbz, nbz));
+    r.t0b = fmaxf(fmaxf(fminf(fbx, nbx), fminf(fby, nby)), fminf(fbz, nbz));
+    return r;
+}
+
+// compare-exchange of (key, reference) pairs, ascending keys
+#define ATN_CE(ka, ra, kb, rb)                                          \
+    {                                                                   \
+        const bool sw_ = kb < ka;                                       \
+        const float lo_ = fminf(ka, kb), hi_ = fmaxf(ka, kb);           \
+        const int32_t rl_ = sw_ ? rb : ra, rh_ = sw_ ? ra : rb;         \
+        ka = lo_; kb = hi_; ra = rl_; rb = rh_;                         \
+    }
+
+// Same execution model and acceptance rules as k_trace; what differs is the inner-node step: one
+// 128-byte QuadNode decides up to four subtrees or leaves, the slots that are hit are ordered by entry
+// distance, the nearest is followed and the others go to the stack farthest first.  Every slot's box
+// is tested with the reference's own slab test (a leaf's slot carries the box of the node whose hit
+// makes the reference visit that leaf), so there is no approximate filter inside the trees; the only
+// conservative pre-filter left is the world-space box of an instance, tested before the ray is
+// carried into the instance's space.
+template <class Policy>
+__global__ void __launch_bounds__(kTraceBlock, ATN_TRACE_MIN_BLOCKS)
+k_trace4(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch, Visits* visits)
+{
+    __shared__ int2 s_stack[kSmemStack4 * kTraceBlock];   // (reference, entry distance bits) per lane and level
+    __shared__ float s_world[12 * kTraceBlock];          // world-space org, dir, invdir, oxinvdir of the lane's ray
+    int2 l_stack[kLocalStack];
+    const int tid = threadIdx.x;
+    const uint32_t stack_base = (uint32_t)__cvta_generic_to_shared(&s_stack[tid]);
+
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int count = count_ptr ? *count_ptr : count_imm;
+    const float t_min = bv.t_min;
+
+    bool active = false, done = false, exhausted = false;
+    int slot = 0, mode = EXIT_NONE, sp = 0, cur = kRefNull, cur_inst = -1;
+    float exit_dist = 0.0f, t_cull = kInf;
+    V3 org, dir;
+    RayInv ri;
+    TraceResult best;
+    best.t = kInf; best.a = 0.0f; best.b = 0.0f; best.leaf = -1; best.inst = -1;
+    uint32_t n_nodes = 0, n_tris = 0;
+
+    for (;;) {
+        if (done) { pol.finish(bv, slot, best); done = false; }
+
+        // ---------------- refill idle lanes ----------------
+        const unsigned idle = __ballot_sync(full, !active);
+        if (idle != 0u && !exhausted) {
+            const int nidle = __popc(idle);
+            const int leader = __ffs(idle) - 1;
+            int base = 0;
+            if (lane == leader) base = atomicAdd(fetch, nidle);
+            base = __shfl_sync(full, base, leader);
+            if (base + nidle >= count) exhausted = true;
+            if (!active) {
+                const int i = base + __popc(idle & ((1u << lane) - 1u));
+                if (i < count) {
+                    float t_max;
+                    pol.load(i, &slot, &org, &dir, &t_max, &mode, &exit_dist);
+                    ri = ray_inv(org, dir);
+                    s_world[0 * kTraceBlock + tid] = org.x; s_world[1 * kTraceBlock + tid] = org.y; s_world[2 * kTraceBlock + tid] = org.z;
+                    s_world[3 * kTraceBlock + tid] = dir.x; s_world[4 * kTraceBlock + tid] = dir.y; s_world[5 * kTraceBlock + tid] = dir.z;
+                    s_world[6 * kTraceBlock + tid] = ri.invdir.x; s_world[7 * kTraceBlock + tid] = ri.invdir.y; s_world[8 * kTraceBlock + tid] = ri.invdir.z;
+                    s_world[9 * kTraceBlock + tid] = ri.oxinvdir.x; s_world[10 * kTraceBlock + tid] = ri.oxinvdir.y; s_world[11 * kTraceBlock + tid] = ri.oxinvdir.z;
+                    t_cull = t_max;
+                    best.t = kInf; best.a = 0.0f; best.b = 0.0f; best.leaf = -1; best.inst = -1;
+                    sp = 0; cur = bv.top_root; cur_inst = -1;
+                    active = true;
+                }
+            }
+        }
+        if (__ballot_sync(full, active) == 0u) break;
+
+        for (;;) {
+            const unsigned act = __ballot_sync(full, active);
+            if (act == 0u) break;
+            if (!exhausted && __popc(act) < kRefillThreshold) break;
+
+            // ---- phase A: QuadNode ----
+            const bool on_node = active && cur >= 0;
+            if (on_node) {
+                const float4* np = bv.nodes + (size_t)cur * 8;
+                const F4x2 c0 = ldg8(np + 0), c1 = ldg8(np + 2), c2 = ldg8(np + 4), c3 = ldg8(np + 6);
+                const float4 a0 = c0.lo, a1 = c0.hi, a2 = c1.lo, b0 = c1.hi, b1 = c2.lo, b2 = c2.hi;
+                const int4 rf = make_int4(__float_as_int(c3.lo.x), __float_as_int(c3.lo.y), __float_as_int(c3.lo.z), __float_as_int(c3.lo.w));
+                const float2 inv_xy = make_float2(ri.invdir.x, ri.invdir.y);
+                const float2 inv_zz = make_float2(ri.invdir.z, ri.invdir.z);
+                const SlabPair pa = slab_pair(a0, a1, a2, inv_xy, inv_zz, ri.oxinvdir);
+                const SlabPair pb = slab_pair(b0, b1, b2, inv_xy, inv_zz, ri.oxinvdir);
+                n_nodes++;
+                // t0 = max(entry, t_min) <= min(exit, running cull bound); empty slots never hit
+                float k0 = fmaxf(pa.t0a, t_min), k1 = fmaxf(pa.t0b, t_min), k2 = fmaxf(pb.t0a, t_min), k3 = fmaxf(pb.t0b, t_min);
+                int32_t r0 = rf.x, r1 = rf.y, r2 = rf.z, r3 = rf.w;
+                const bool h0 = (k0 <= fminf(pa.t1a, t_cull)) & (r0 != kRefNull);
+                const bool h1 = (k1 <= fminf(pa.t1b, t_cull)) & (r1 != kRefNull);
+                const bool h2 = (k2 <= fminf(pb.t1a, t_cull)) & (r2 != kRefNull);
+                const bool h3 = (k3 <= fminf(pb.t1b, t_cull)) & (r3 != kRefNull);
+                const int nhit = (int)h0 + (int)h1 + (int)h2 + (int)h3;
+                k0 = h0 ? k0 : kInf; k1 = h1 ? k1 : kInf; k2 = h2 ? k2 : kInf; k3 = h3 ? k3 : kInf;
+                ATN_CE(k0, r0, k1, r1) ATN_CE(k2, r2, k3, r3) ATN_CE(k0, r0, k2, r2) ATN_CE(k1, r1, k3, r3) ATN_CE(k1, r1, k2, r2)
+                cur = nhit ? r0 : kRefNull;
+                const int np_ = nhit - 1;                 // entries left behind, nearest on top
+                if (np_ > 0) {
+                    if (sp + np_ <= kSmemStack4) {
+                        const uint32_t top = stack_base + (uint32_t)(sp + np_) * kStackStride;
+                        sts64(top - kStackStride, r1, __float_as_int(k1));
+                        if (np_ > 1) sts64(top - 2u * kStackStride, r2, __float_as_int(k2));
+                        if (np_ > 2) sts64(top - 3u * kStackStride, r3, __float_as_int(k3));
+                    }
+                    else {
+                        const int32_t rr[3] = { r1, r2, r3 };
+                        const float kk[3] = { k1, k2, k3 };
+#pragma unroll
+                        for (int k = 2; k >= 0; k--) {
+                            if (k < np_) {
+                                const int at = sp + (np_ - 1 - k);
+                                if (at < kSmemStack4) sts64(stack_base + (uint32_t)at * kStackStride, rr[k], __float_as_int(kk[k]));
+                                else l_stack[at - kSmemStack4] = make_int2(rr[k], __float_as_int(kk[k]));
+                            }
+                        }
+                    }
+                    sp += np_;
+                }
+            }
+
+            // ---- phase B: triangle leaf (triangle::hit, triangle.h:40-67) ----
+            const bool want_tri = active && cur < 0 && cur != kRefNull && cur != kRefExit && cur_inst >= 0;
+            bool run_tris = true;
+            if (kLeafBatch4 > 1) {
+                const unsigned mt = __ballot_sync(full, want_tri);
+                const unsigned mn = __ballot_sync(full, on_node);
+                run_tris = (__popc(mt) >= kLeafBatch4) || (mn == 0u);
+            }
+            const bool on_tri = want_tri && run_tris;
+            bool finished = false;
+            if (on_tri) {
+                const int32_t leaf = ~cur;
+                const float4* tp = bv.tris + (size_t)leaf * kTriStride;
+                const F4x2 ab = ldg8(tp);
+                const float4 a = ab.lo, b = ab.hi;
+                const float4 c = ldg4(tp + 2);
+                const TriHit h = intersect_triangle_edges(org, dir, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), V3(c.x, c.y, c.z));
+                n_tris++;
+                if (h.hit && h.t < kInf && t_min < h.t) {
+                    const bool closer = h.t < best.t ||
+                        (h.t == best.t && (cur_inst < best.inst || (cur_inst == best.inst && leaf < best.leaf)));
+                    if (closer) {
+                        best.t = h.t; best.a = h.a; best.b = h.b; best.leaf = leaf; best.inst = cur_inst;
+                        t_cull = cull_bound(h.t);
+                        if (mode == EXIT_ANY_HIT || (mode == EXIT_HIT_BEFORE && h.t <= exit_dist)) finished = true;
+                    }
+                }
+                cur = kRefNull;
+            }
+
+            // ---- phase E: instance entry (threaded_bvh_traverser.h:146-185), batched ----
+            const bool want_entry = active && cur < 0 && cur != kRefNull && cur != kRefExit && cur_inst < 0;
+            const unsigned me = __ballot_sync(full, want_entry);
+            if (me != 0u) {
+                const unsigned busy = __ballot_sync(full, on_node || on_tri);
+                if (__popc(me) >= kEntryBatch || busy == 0u) {
+                    if (want_entry) {
+                        const int32_t leaf = ~cur;
+                        const float4* ip = bv.insts + (size_t)leaf * kInstStride;
+                        const F4x2 iw = ldg8(ip);
+                        const int4 il = make_int4(__float_as_int(iw.lo.x), __float_as_int(iw.lo.y), __float_as_int(iw.lo.z), __float_as_int(iw.lo.w));
+                        const float4 wmin = iw.hi, wmax = ldg4(ip + 2);
+                        cur = kRefNull;
+                        // conservative pre-filter (see leaf_margin): does the world ray come near the instance at all?
+                        float t0w, t1w;
+                        slab_test(ri, wmin.x, wmax.x, wmin.y, wmax.y, wmin.z, wmax.z, t_min, kInf, &t0w, &t1w);
+                        const float far = (best.leaf >= 0) ? t_cull : kInf;
+                        const bool may = leaf_may_hit(t0w, fminf(t1w, far), leaf_margin(org, dir, ri));
+                        if (il.y != kRefNull && may) {
+                            if (sp < kSmemStack4) sts64(stack_base + (uint32_t)sp * kStackStride, kRefExit, __float_as_int(-kInf));
+                            else l_stack[sp - kSmemStack4] = make_int2(kRefExit, __float_as_int(-kInf));
+                            sp++;
+                            cur_inst = leaf;
+                            if (il.z >= 0) {
+                                const AtnMat4 m = bv.matrices[il.z];
+                                const Ray tr = make_ray(mat_apply(m, org), mat_apply_xyz(m, dir));   // mat4::applyRay
+                                org = tr.org; dir = tr.dir;
+                                ri = ray_inv(org, dir);
+                            }
+                            cur = il.y;
+                        }
+                    }
+                }
+            }
+
+            // ---- phase C: pop ----
+            if (active && !finished && cur == kRefNull) {
+#pragma unroll 1
+                for (;;) {
+                    if (sp == 0) { finished = true; break; }
+                    sp--;
+                    const int2 e = (sp < kSmemStack4) ? lds64(stack_base + (uint32_t)sp * kStackStride) : l_stack[sp - kSmemStack4];
+                    cur = e.x;
+                    if (cur == kRefExit) {
+                        if (sp == 0) { finished = true; break; }      // nothing left in the top layer either
+                        cur_inst = -1;
+                        org = V3(s_world[0 * kTraceBlock + tid], s_world[1 * kTraceBlock + tid], s_world[2 * kTraceBlock + tid]);
+                        dir = V3(s_world[3 * kTraceBlock + tid], s_world[4 * kTraceBlock + tid], s_world[5 * kTraceBlock + tid]);
+                        ri.invdir = V3(s_world[6 * kTraceBlock + tid], s_world[7 * kTraceBlock + tid], s_world[8 * kTraceBlock + tid]);
+                        ri.oxinvdir = V3(s_world[9 * kTraceBlock + tid], s_world[10 * kTraceBlock + tid], s_world[11 * kTraceBlock + tid]);
+                        cur = kRefNull;
+                        continue;
+                    }
+                    if (__int_as_float(e.y) > t_cull) { cur = kRefNull; continue; }   // subtree starts behind the current hit
+                    break;
+                }
+            }
+            if (finished) { active = false; done = true; }
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        n_nodes += __shfl_xor_sync(full, n_nodes, o);
+        n_tris += __shfl_xor_sync(full, n_tris, o);
+    }
+    if (lane == 0 && visits) {
+        atomicAdd(&visits->nodes, (unsigned long long)n_nodes);
+        atomicAdd(&visits->tris, (unsigned long long)n_tris);
+    }
+}
+
+#if ATN_WIDE
+#define ATN_TRACE_KERNEL k_trace4
+#else
+#define ATN_TRACE_KERNEL k_trace
+#endif
 
 // ---------------------------------------------------------------------------------------------
 // generate / shade / gather
@@ -960,9 +1267,17 @@ struct AtnRenderer {
     DevBuf<AtnVec4> positions, normals;
     DevBuf<AtnVec4> texels;
     DevBuf<TexView> texviews;
+#if ATN_WIDE
+    DevBuf<QuadNode> nodes;
+#else
     DevBuf<PairNode> nodes;
+#endif
     DevBuf<TriLeaf> tris;
+#if ATN_WIDE
+    DevBuf<InstLeafW> insts;
+#else
     DevBuf<InstLeaf> insts;
+#endif
     DevBuf<uint32_t> seeds;
     uint32_t seed_count{ 0 };
     SceneView sv{};
@@ -1014,17 +1329,24 @@ struct AtnRenderer {
 
 static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene)
 {
+#if ATN_WIDE
+    WideBvh enc = encode_wide(scene);
+    if (!enc.error.empty()) return set_error(ATN_ERR_INVALID_ARGUMENT, "node lists: %s", enc.error.c_str());
+    if (enc.max_stack > kSmemStack4 + kLocalStack)
+        return set_error(ATN_ERR_TOO_LARGE, "BVH needs a traversal stack of %d entries (limit %d)", enc.max_stack, kSmemStack4 + kLocalStack);
+#else
     EncodedBvh enc = encode_bvh(scene);
     if (!enc.error.empty()) return set_error(ATN_ERR_INVALID_ARGUMENT, "node lists: %s", enc.error.c_str());
     if (enc.max_depth + 8 > kSmemStack + kLocalStack)
         return set_error(ATN_ERR_TOO_LARGE, "BVH depth %d exceeds the traversal stack (%d)", enc.max_depth, kSmemStack + kLocalStack);
+#endif
     CUDA_TRY(r->nodes.upload(enc.nodes.data(), enc.nodes.size(), r->stream));
     CUDA_TRY(r->tris.upload(enc.tris.data(), enc.tris.size(), r->stream));
     CUDA_TRY(r->insts.upload(enc.insts.data(), enc.insts.size(), r->stream));
     CUDA_TRY(cudaStreamSynchronize(r->stream));   // enc goes out of scope
     r->bv.nodes = reinterpret_cast<const float4*>(r->nodes.p);
     r->bv.tris = reinterpret_cast<const float4*>(r->tris.p);
-    r->bv.insts = reinterpret_cast<const int4*>(r->insts.p);
+    r->bv.insts = reinterpret_cast<const float4*>(r->insts.p);
     r->bv.matrices = r->matrices.p;
     r->bv.top_root = enc.top_root;
     return ATN_OK;
@@ -1091,7 +1413,7 @@ ATN_API int atn_create(int device_ordinal, AtnRenderer** out)
     CUDA_TRY(cudaEventCreate(&r->ev0));
     CUDA_TRY(cudaEventCreate(&r->ev1));
     int bps = 0;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace<ClosestPolicy>, kTraceBlock, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, ATN_TRACE_KERNEL<ClosestPolicy>, kTraceBlock, 0));
     r->trace_grid = r->sm_count * std::max(1, bps);
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_surface<false>, kShadeBlock, 0));
     r->surface_grid = r->sm_count * std::max(1, bps);
@@ -1343,7 +1665,7 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             {
                 ClosestPolicy pol{ r->pb, q, tmax, b == 0 ? r->pb.hit_mesh : nullptr };
-                k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[b], 0, &c->fetch_closest[b], r->visits.p);
+                ATN_TRACE_KERNEL<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[b], 0, &c->fetch_closest[b], r->visits.p);
             }
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             if (tap_now) k_surface<true><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, r->pb, c, b, r->tap_dev.p, r->tap_cap);
@@ -1354,11 +1676,11 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             if (tap_now) {
                 ShadowPolicy<true> pol{ r->pb, r->sv, r->tap_dev.p, r->tap_cap, b };
-                k_trace<ShadowPolicy<true>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
+                ATN_TRACE_KERNEL<ShadowPolicy<true>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
             }
             else {
                 ShadowPolicy<false> pol{ r->pb, r->sv, nullptr, 0, b };
-                k_trace<ShadowPolicy<false>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
+                ATN_TRACE_KERNEL<ShadowPolicy<false>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
             }
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             launches += 5;
@@ -1426,7 +1748,7 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
         k_generate<<<grid, 256, 0, s>>>(fp, r->camera, r->seeds.p, r->pb, c);
         {
             ClosestPolicy pol{ r->pb, nullptr, kInf, nullptr };
-            k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[0], 0, &c->fetch_closest[0], r->visits.p);
+            ATN_TRACE_KERNEL<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[0], 0, &c->fetch_closest[0], r->visits.p);
         }
         k_ao_begin<<<sgrid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, r->pb, c);
         launches += 3;
@@ -1434,7 +1756,7 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
             k_ao_ray<<<sgrid, kShadeBlock, 0, s>>>(fp, r->seeds.p, r->pb, c);
             CUDA_TRY(cudaMemsetAsync(&c->fetch_query, 0, sizeof(int32_t), s));
             ClosestPolicy pol{ r->pb, r->pb.q_lit, radius, nullptr };
-            k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_lit[0], 0, &c->fetch_query, r->visits.p);
+            ATN_TRACE_KERNEL<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_lit[0], 0, &c->fetch_query, r->visits.p);
             k_ao_accum<<<sgrid, kShadeBlock, 0, s>>>(r->sv, r->pb, c, radius, i == num_rays - 1 ? 1 : 0, num_rays);
             launches += 3;
         }
@@ -1520,11 +1842,11 @@ static int query_launch(AtnRenderer* r, const void* rays_dev, const void* f_dev,
     CUDA_TRY(cudaEventRecord(r->ev0, s));
     if (any) {
         QueryAnyPolicy pol{ (const AtnRay*)rays_dev, (const float*)f_dev, (uint8_t*)out_dev };
-        k_trace<QueryAnyPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
+        ATN_TRACE_KERNEL<QueryAnyPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
     }
     else {
         QueryClosestPolicy pol{ (const AtnRay*)rays_dev, (const float*)f_dev, (AtnHit*)out_dev };
-        k_trace<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
+        ATN_TRACE_KERNEL<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
     }
     CUDA_TRY(cudaEventRecord(r->ev1, s));
     CUDA_TRY(cudaGetLastError());
@@ -1660,7 +1982,7 @@ extern "C" ATN_API int atn_trace_closest_static(AtnRenderer* r, const AtnRay* ra
     CUDA_TRY(cudaMemcpyAsync(sc->rays, rays, n * sizeof(AtnRay), cudaMemcpyHostToDevice, s));
     if (t_max) CUDA_TRY(cudaMemcpyAsync(sc->t_max, t_max, n * sizeof(float), cudaMemcpyHostToDevice, s));
     QueryClosestPolicy pol{ sc->rays, t_max ? sc->t_max : nullptr, sc->hits };
-    k_trace<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &sc->cursor, nullptr);
+    ATN_TRACE_KERNEL<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &sc->cursor, nullptr);
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaMemcpyAsync(hits, sc->hits, n * sizeof(AtnHit), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaStreamSynchronize(s));

@@ -1,0 +1,296 @@
+// DEVELOPMENT TOOL (not part of the product, not loaded by it): a sequential CPU emulation of the
+// traversal kernels' per-ray logic over the PairNode and QuadNode encodings of atn_bvh.h.  Used to
+// count node steps / triangle tests / stack depth for an encoding before it goes to the GPU, and to
+// check its hits against the oracle on the same rays (scripts/emu_wide.py).
+//   g++ -std=c++17 -O2 -fopenmp -fPIC -ffp-contract=off -shared -o /tmp/libemu_wide.so scripts/emu_wide.cpp
+#include <stdint.h>
+#include <string.h>
+#include <cmath>
+#include <vector>
+
+#include "../aten_b200/csrc/atn_math.cuh"
+#include "../aten_b200/csrc/atn_bvh.h"
+
+using namespace atn;
+
+namespace {
+
+constexpr float kBig = 3.402823466e+38f;
+
+struct Slab { float t0, t1; bool hit; };
+inline Slab slab(const RayInv& ri, const float mn[3], const float mx[3], float t_min, float t_max)
+{
+    const float fx = mx[0] * ri.invdir.x + ri.oxinvdir.x;
+    const float fy = mx[1] * ri.invdir.y + ri.oxinvdir.y;
+    const float fz = mx[2] * ri.invdir.z + ri.oxinvdir.z;
+    const float nx = mn[0] * ri.invdir.x + ri.oxinvdir.x;
+    const float ny = mn[1] * ri.invdir.y + ri.oxinvdir.y;
+    const float nz = mn[2] * ri.invdir.z + ri.oxinvdir.z;
+    Slab s;
+    s.t1 = fminf(fminf(fmaxf(fx, nx), fmaxf(fy, ny)), fmaxf(fz, nz));
+    s.t0 = fmaxf(fmaxf(fmaxf(fminf(fx, nx), fminf(fy, ny)), fminf(fz, nz)), t_min);
+    s.hit = s.t0 <= fminf(s.t1, t_max);
+    return s;
+}
+
+inline float leaf_margin(const V3& org, const V3& dir, const RayInv& ri)
+{
+    const float dmin = fminf(fminf(fabsf(dir.x), fabsf(dir.y)), fabsf(dir.z));
+    if (!(dmin >= 0.02f)) return -1.0f;
+    const float S = fabsf(ri.oxinvdir.x) + fabsf(ri.oxinvdir.y) + fabsf(ri.oxinvdir.z);
+    const float M = fmaxf(fmaxf(fabsf(org.x), fabsf(org.y)), fabsf(org.z));
+    return 1e-6f * S + 5e-4f * (1.0f + M);
+}
+inline bool leaf_may_hit(float t0, float t1, float margin)
+{
+    return (t0 <= t1 + 2e-4f * (fabsf(t0) + fabsf(t1)) + margin) | (margin < 0.0f);
+}
+
+inline TriHit tri_edges(const V3& org, const V3& dir, const V3& v0, const V3& e1, const V3& e2)
+{
+    const V3 r = org - v0;
+    const V3 u = cross(dir, e2);
+    const V3 v = cross(r, e1);
+    const float inv = 1.0f / dot(u, e1);
+    TriHit h;
+    h.t = dot(v, e2) * inv;
+    h.a = dot(u, r) * inv;
+    h.b = dot(v, dir) * inv;
+    h.hit = ((h.a >= 0.0f && h.a <= 1.0f) && (h.b >= 0.0f && h.b <= 1.0f) && (h.a + h.b <= 1.0f) && h.t >= 0.0f);
+    return h;
+}
+
+struct Best { float t, a, b; int32_t leaf, inst; };
+struct Ent { int32_t ref; float t0; };
+
+struct Stats { uint64_t nodes, tris, entries, entries_filtered, pops_culled, rays; uint64_t max_sp; uint64_t sum_sp; };
+
+inline void finish(const std::vector<TriLeaf>& tris, const int32_t* inst_objid, const int32_t* inst_meshid, const Best& b, AtnHit* h)
+{
+    h->t = b.t; h->a = b.a; h->b = b.b; h->isVoxel = 0;
+    if (b.leaf < 0) { h->objid = -1; h->primid = -1; h->mtrlid = -1; h->meshid = -1; return; }
+    const TriLeaf& t = tris[b.leaf];
+    h->primid = t.primid; h->mtrlid = t.mtrlid;
+    h->objid = inst_objid[b.inst];
+    h->meshid = t.mesh_id < 0 ? inst_meshid[b.inst] : t.mesh_id;
+}
+
+inline float cull_bound(float t) { return t + fabsf(t) * 2e-5f; }
+
+}  // namespace
+
+extern "C" int emu_trace_wide(const AtnSceneBlob* scene, const AtnRay* rays, const float* t_max_in, size_t n, AtnHit* hits,
+                              uint64_t* stats_out, int sort_leaves_first, int entry_filter)
+{
+    WideBvh w = encode_wide(scene);
+    if (!w.error.empty()) return -1;
+    std::vector<int32_t> iobj(w.insts.size()), imesh(w.insts.size());
+    for (size_t i = 0; i < w.insts.size(); i++) { iobj[i] = w.insts[i].objid; imesh[i] = w.insts[i].meshid; }
+    const float t_min = scene->config.bvh_hit_min > 0 ? scene->config.bvh_hit_min : kEps;
+    Stats tot{};
+#pragma omp parallel
+    {
+        Stats st{};
+        std::vector<Ent> stack;
+#pragma omp for schedule(dynamic, 1024)
+        for (long long i = 0; i < (long long)n; i++) {
+            const V3 worg(rays[i].org), wdir(rays[i].dir);
+            V3 org = worg, dir = wdir;
+            RayInv ri = ray_inv(org, dir);
+            const RayInv wri = ri;
+            const float wmargin = leaf_margin(org, dir, ri);
+            float t_cull = t_max_in ? t_max_in[i] : kBig;
+            Best best{ kBig, 0, 0, -1, -1 };
+            stack.clear();
+            int32_t cur = w.top_root, cur_inst = -1;
+            for (;;) {
+                if (cur >= 0) {
+                    const QuadNode& q = w.nodes[cur];
+                    st.nodes++;
+                    Ent e[4]; int ne = 0;
+                    for (int s = 0; s < 4; s++) {
+                        if (q.ref[s] == kRefNull) continue;
+                        const int g = (s >> 1) * 3, h = s & 1;
+                        const float mn[3] = { q.q[g][h * 2], q.q[g][h * 2 + 1], q.q[g + 2][h] };
+                        const float mx[3] = { q.q[g + 1][h * 2], q.q[g + 1][h * 2 + 1], q.q[g + 2][2 + h] };
+                        const Slab sl = slab(ri, mn, mx, t_min, t_cull);
+                        if (!sl.hit) continue;
+                        e[ne].ref = q.ref[s];
+                        e[ne].t0 = (sort_leaves_first && q.ref[s] < 0) ? -kBig : sl.t0;
+                        ne++;
+                    }
+                    // stable insertion sort by entry distance
+                    for (int a = 1; a < ne; a++) { Ent k = e[a]; int b = a - 1; while (b >= 0 && e[b].t0 > k.t0) { e[b + 1] = e[b]; b--; } e[b + 1] = k; }
+                    for (int a = ne - 1; a >= 1; a--) stack.push_back(e[a]);
+                    cur = ne ? e[0].ref : kRefNull;
+                }
+                else if (cur != kRefNull && cur != kRefExit) {
+                    const int32_t leaf = ~cur;
+                    if (cur_inst >= 0) {
+                        const TriLeaf& t = w.tris[leaf];
+                        st.tris++;
+                        const TriHit h = tri_edges(org, dir, V3(t.v0[0], t.v0[1], t.v0[2]), V3(t.e1[0], t.e1[1], t.e1[2]), V3(t.e2[0], t.e2[1], t.e2[2]));
+                        if (h.hit && h.t < kBig && t_min < h.t) {
+                            const bool closer = h.t < best.t || (h.t == best.t && (cur_inst < best.inst || (cur_inst == best.inst && leaf < best.leaf)));
+                            if (closer) { best.t = h.t; best.a = h.a; best.b = h.b; best.leaf = leaf; best.inst = cur_inst; t_cull = cull_bound(h.t); }
+                        }
+                        cur = kRefNull;
+                    }
+                    else {
+                        const InstLeafW& il = w.insts[leaf];
+                        cur = kRefNull;
+                        bool enter = il.root != kRefNull;
+                        if (enter && entry_filter) {
+                            const Slab sl = slab(ri, il.wmin, il.wmax, t_min, kBig);
+                            const float far = best.leaf >= 0 ? t_cull : kBig;
+                            if (!leaf_may_hit(sl.t0, fminf(sl.t1, far), wmargin)) { enter = false; st.entries_filtered++; }
+                        }
+                        if (enter) {
+                            st.entries++;
+                            stack.push_back(Ent{ kRefExit, -kBig });
+                            cur_inst = leaf;
+                            if (il.w2l >= 0) {
+                                const AtnMat4& m = scene->matrices[il.w2l];
+                                const Ray tr = make_ray(mat_apply(m, org), mat_apply_xyz(m, dir));
+                                org = tr.org; dir = tr.dir; ri = ray_inv(org, dir);
+                            }
+                            cur = il.root;
+                        }
+                    }
+                }
+                if (stack.size() > st.max_sp) st.max_sp = stack.size();
+                bool finished = false;
+                while (cur == kRefNull) {
+                    if (stack.empty()) { finished = true; break; }
+                    const Ent e = stack.back(); stack.pop_back();
+                    cur = e.ref;
+                    if (cur == kRefExit) {
+                        if (stack.empty()) { finished = true; break; }
+                        cur_inst = -1; org = worg; dir = wdir; ri = wri; cur = kRefNull; continue;
+                    }
+                    if (e.t0 > t_cull) { cur = kRefNull; st.pops_culled++; continue; }
+                }
+                if (finished) break;
+            }
+            finish(w.tris, iobj.data(), imesh.data(), best, &hits[i]);
+            st.rays++;
+        }
+#pragma omp critical
+        {
+            tot.nodes += st.nodes; tot.tris += st.tris; tot.entries += st.entries; tot.entries_filtered += st.entries_filtered;
+            tot.pops_culled += st.pops_culled; tot.rays += st.rays; if (st.max_sp > tot.max_sp) tot.max_sp = st.max_sp;
+        }
+    }
+    if (stats_out) {
+        stats_out[0] = tot.nodes; stats_out[1] = tot.tris; stats_out[2] = tot.entries; stats_out[3] = tot.entries_filtered;
+        stats_out[4] = tot.pops_culled; stats_out[5] = tot.max_sp; stats_out[6] = w.nodes.size(); stats_out[7] = w.slots_used;
+        stats_out[8] = w.replaced; stats_out[9] = w.not_nested; stats_out[10] = (uint64_t)w.max_stack;
+    }
+    return 0;
+}
+
+// The PairNode encoding the kernels walk today (same acceptance rules, leaf pre-filter included).
+extern "C" int emu_trace_pair(const AtnSceneBlob* scene, const AtnRay* rays, const float* t_max_in, size_t n, AtnHit* hits,
+                              uint64_t* stats_out)
+{
+    EncodedBvh w = encode_bvh(scene);
+    if (!w.error.empty()) return -1;
+    std::vector<int32_t> iobj(w.insts.size()), imesh(w.insts.size());
+    for (size_t i = 0; i < w.insts.size(); i++) { iobj[i] = w.insts[i].objid; imesh[i] = w.insts[i].meshid; }
+    const float t_min = scene->config.bvh_hit_min > 0 ? scene->config.bvh_hit_min : kEps;
+    Stats tot{};
+#pragma omp parallel
+    {
+        Stats st{};
+        std::vector<Ent> stack;
+#pragma omp for schedule(dynamic, 1024)
+        for (long long i = 0; i < (long long)n; i++) {
+            const V3 worg(rays[i].org), wdir(rays[i].dir);
+            V3 org = worg, dir = wdir;
+            RayInv ri = ray_inv(org, dir);
+            const RayInv wri = ri;
+            float margin = leaf_margin(org, dir, ri);
+            const float wmargin = margin;
+            float t_cull = t_max_in ? t_max_in[i] : kBig;
+            Best best{ kBig, 0, 0, -1, -1 };
+            stack.clear();
+            int32_t cur = w.top_root, cur_inst = -1;
+            for (;;) {
+                if (cur >= 0) {
+                    const PairNode& p = w.nodes[cur];
+                    st.nodes++;
+                    const float lmn[3] = { p.n0[0], p.n0[2], p.n2[0] }, lmx[3] = { p.n0[1], p.n0[3], p.n2[1] };
+                    const float rmn[3] = { p.n1[0], p.n1[2], p.n2[2] }, rmx[3] = { p.n1[1], p.n1[3], p.n2[3] };
+                    const Slab sl = slab(ri, lmn, lmx, t_min, t_cull), sr = slab(ri, rmn, rmx, t_min, t_cull);
+                    const float far = best.leaf >= 0 ? t_cull : kBig;
+                    const bool fl = leaf_may_hit(sl.t0, fminf(sl.t1, far), margin) && p.left != kRefNull;
+                    const bool fr = leaf_may_hit(sr.t0, fminf(sr.t1, far), margin) && p.right != kRefNull;
+                    const bool hl = p.left >= 0 ? sl.hit : fl, hr = p.right >= 0 ? sr.hit : fr;
+                    const float t0l = p.left >= 0 ? sl.t0 : -kBig, t0r = p.right >= 0 ? sr.t0 : -kBig;
+                    if (hl && hr) {
+                        const bool swap = t0r < t0l;
+                        stack.push_back(Ent{ swap ? p.left : p.right, swap ? t0l : t0r });
+                        cur = swap ? p.right : p.left;
+                    }
+                    else if (hl) cur = p.left;
+                    else if (hr) cur = p.right;
+                    else cur = kRefNull;
+                }
+                else if (cur != kRefNull && cur != kRefExit) {
+                    const int32_t leaf = ~cur;
+                    if (cur_inst >= 0) {
+                        const TriLeaf& t = w.tris[leaf];
+                        st.tris++;
+                        const TriHit h = tri_edges(org, dir, V3(t.v0[0], t.v0[1], t.v0[2]), V3(t.e1[0], t.e1[1], t.e1[2]), V3(t.e2[0], t.e2[1], t.e2[2]));
+                        if (h.hit && h.t < kBig && t_min < h.t) {
+                            const bool closer = h.t < best.t || (h.t == best.t && (cur_inst < best.inst || (cur_inst == best.inst && leaf < best.leaf)));
+                            if (closer) { best.t = h.t; best.a = h.a; best.b = h.b; best.leaf = leaf; best.inst = cur_inst; t_cull = cull_bound(h.t); }
+                        }
+                        cur = kRefNull;
+                    }
+                    else {
+                        const InstLeaf& il = w.insts[leaf];
+                        cur = kRefNull;
+                        if (il.root != kRefNull) {
+                            st.entries++;
+                            stack.push_back(Ent{ kRefExit, -kBig });
+                            cur_inst = leaf;
+                            if (il.w2l >= 0) {
+                                const AtnMat4& m = scene->matrices[il.w2l];
+                                const Ray tr = make_ray(mat_apply(m, org), mat_apply_xyz(m, dir));
+                                org = tr.org; dir = tr.dir; ri = ray_inv(org, dir); margin = leaf_margin(org, dir, ri);
+                            }
+                            cur = il.root;
+                        }
+                    }
+                }
+                if (stack.size() > st.max_sp) st.max_sp = stack.size();
+                bool finished = false;
+                while (cur == kRefNull) {
+                    if (stack.empty()) { finished = true; break; }
+                    const Ent e = stack.back(); stack.pop_back();
+                    cur = e.ref;
+                    if (cur == kRefExit) {
+                        if (stack.empty()) { finished = true; break; }
+                        cur_inst = -1; org = worg; dir = wdir; ri = wri; margin = wmargin; cur = kRefNull; continue;
+                    }
+                    if (e.t0 > t_cull) { cur = kRefNull; st.pops_culled++; continue; }
+                }
+                if (finished) break;
+            }
+            finish(w.tris, iobj.data(), imesh.data(), best, &hits[i]);
+            st.rays++;
+        }
+#pragma omp critical
+        {
+            tot.nodes += st.nodes; tot.tris += st.tris; tot.entries += st.entries; tot.pops_culled += st.pops_culled;
+            tot.rays += st.rays; if (st.max_sp > tot.max_sp) tot.max_sp = st.max_sp;
+        }
+    }
+    if (stats_out) {
+        stats_out[0] = tot.nodes; stats_out[1] = tot.tris; stats_out[2] = tot.entries; stats_out[3] = 0;
+        stats_out[4] = tot.pops_culled; stats_out[5] = tot.max_sp; stats_out[6] = w.nodes.size(); stats_out[7] = 0;
+        stats_out[8] = 0; stats_out[9] = 0; stats_out[10] = (uint64_t)w.max_depth;
+    }
+    return 0;
+}

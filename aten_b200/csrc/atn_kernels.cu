@@ -20,9 +20,10 @@
 //     is a fixed launch sequence with no synchronisation;
 //   * traversal kernels are persistent and warp-synchronous: grid = SMs x resident blocks, every lane
 //     owns a resumable ray, the warp refills idle lanes from the queue with one atomicAdd;
-//   * nodes are 64-byte child-pair records fetched with 128-bit read-only loads (LDG.E.128.CONSTANT),
-//     triangles are 48-byte gathered records; the traversal stack is a per-lane shared-memory
-//     stack of (reference, entry distance) pairs that spills to local memory beyond kSmemStack;
+//   * nodes are 128-byte 4-slot records (an exact collapse of the reference's binary trees, atn_bvh.h)
+//     fetched with 256-bit read-only loads (LDG.E.256), triangles are 64-byte gathered records; the
+//     traversal stack is a per-lane shared-memory stack of (reference, entry distance) pairs that
+//     spills to local memory beyond kSmemStack;
 //   * no tensor cores: the path is pointer chasing + FP32 slab / Moeller-Trumbore arithmetic.
 // Compiled with -fmad=false: the intersection arithmetic must round exactly like the reference's
 // x86 build for primitive ids to match bit for bit.
@@ -66,16 +67,13 @@ static int set_error(int code, const char* fmt, ...)
 // ---------------------------------------------------------------------------------------------
 // device-side views
 // ---------------------------------------------------------------------------------------------
-#ifndef ATN_WIDE
-#define ATN_WIDE 1          // 1: QuadNode traversal (k_trace4), 0: PairNode traversal (k_trace)
-#endif
-constexpr int kInstStride = ATN_WIDE ? 4 : 1;   // 16-byte words per instance leaf record
+constexpr int kInstStride = 4;                   // 16-byte words per InstLeafW
 constexpr int kTriStride = 4;                    // 16-byte words per TriLeaf
 
 struct BvhView {
-    const float4* nodes;     // QuadNode as 8 x float4 (ATN_WIDE) or PairNode as 4 x float4
+    const float4* nodes;     // QuadNode as 8 x float4
     const float4* tris;      // TriLeaf as 4 x float4 (the last one is padding)
-    const float4* insts;     // InstLeafW as 3 x 16 B (ATN_WIDE) or InstLeaf as one int4
+    const float4* insts;     // InstLeafW as 4 x 16 B
     const AtnMat4* matrices;
     int32_t top_root;
     float t_min;
@@ -83,7 +81,7 @@ struct BvhView {
 
 constexpr int kMaxBounce = 16;
 #ifndef ATN_SMEM_STACK
-#define ATN_SMEM_STACK 12
+#define ATN_SMEM_STACK 16
 #endif
 constexpr int kSmemStack = ATN_SMEM_STACK;     // shared-memory stack entries per thread
 constexpr int kLocalStack = 64;    // overflow, local memory
@@ -93,13 +91,9 @@ constexpr int kTraceBlock = 128;
 #endif
 constexpr int kRefillThreshold = ATN_REFILL_THRESHOLD;   // refill a warp when fewer lanes than this still own a ray
 #ifndef ATN_LEAF_BATCH
-#define ATN_LEAF_BATCH 5
+#define ATN_LEAF_BATCH 6
 #endif
 constexpr int kLeafBatch = ATN_LEAF_BATCH;               // lanes that must hold a triangle leaf before the test runs
-#ifndef ATN_POP_MAX
-#define ATN_POP_MAX 1000000
-#endif
-constexpr int kPopMax = ATN_POP_MAX;                     // stack entries a lane may discard per iteration before it yields
 #ifndef ATN_ENTRY_BATCH
 #define ATN_ENTRY_BATCH 6
 #endif
@@ -118,7 +112,7 @@ struct Counters {
 
 // Ray totals of one atn_render call (not cleared per sample).
 struct Totals { unsigned long long closest, shadow; };
-// Traversal work of one call: PairNodes fetched and triangle tests run (all lanes, all traversal kernels).
+// Traversal work of one call: QuadNodes fetched and triangle tests run (all lanes, all traversal kernels).
 struct Visits { unsigned long long nodes, tris; };
 
 struct PathBuffers {
@@ -215,16 +209,14 @@ __device__ __forceinline__ bool slab_test(const RayInv& ri, float minx, float ma
     return t0 <= fminf(t1raw, t_max);
 }
 
-// Leaf pre-filter.  The reference never box-tests a leaf: it runs the triangle test (or enters the
-// instance) for every leaf whose parent box was hit, ~8 triangle tests per ray on Sponza of which one
-// succeeds.  On the GPU those tests run for a handful of lanes at a time and dominated the issue
-// slots.  The child-box slot of a leaf in a PairNode is free (the reference never reads a leaf's
-// box), so the encoder stores there a box that is conservative BY CONSTRUCTION -- the triangle's own
-// AABB, or the world AABB of an instance's transformed root box (atn_bvh.h) -- and the kernel skips a
-// leaf when the ray misses that box by a safe margin: if the reference's Moeller-Trumbore test
-// accepts a triangle, the hit point lies (to float accuracy) inside the triangle's AABB and the
-// relaxed test below passes.  Far bound: the running hit distance only (the reference's triangle test
-// ignores the caller's t_max, threaded_bvh_traverser.h:198-200).
+// Instance pre-filter.  The reference enters every instance whose parent box in the top layer was hit
+// (leaves are never box-tested, threaded_bvh_traverser.h:146-185); the entry costs a matrix transform
+// and a root test that run for one or two lanes at a time.  InstLeafW carries a world-space box that is
+// conservative BY CONSTRUCTION (the instance's transformed root box, padded, atn_bvh.h), and the kernel
+// skips the entry when the world ray misses that box by a safe margin: whatever the reference would
+// accept inside the instance lies (to float accuracy) inside that box and passes the relaxed test.
+// Far bound: the running hit distance only (the reference's triangle test ignores the caller's t_max,
+// threaded_bvh_traverser.h:198-200).
 //   margin in t:  2e-4 (|t0| + |t1|)          covers the +1e-6 direction bias, <= 5e-5 relative for |d_k| >= 0.02
 //               + 1e-6 sum_k |org_k / d_k|    covers the rounding of plane*inv - org*inv
 //               + 5e-4 (1 + max_k |org_k|)    covers the triangle test's own error, mapped through 1/|d_k| <= 50
@@ -356,237 +348,9 @@ struct QueryAnyPolicy {            // atn_trace_any
     }
 };
 
-// Two-level closest-hit traversal over PairNodes with the reference's acceptance rules
-// (threaded_bvh_traverser.h:98-304): inner boxes use aabb::hit, leaves are never box-tested, a
-// triangle is accepted iff t_min < t && t < best (ties: lowest depth-first rank, which is what
-// "first encountered" means in the reference's fixed visit order).
-//
-// Execution model: persistent warps.  Every lane owns one ray and a resumable traversal state; the
-// warp advances all its rays one node / leaf per iteration and re-converges after each iteration.
-// When fewer than kRefillThreshold lanes still have a ray, the warp goes back to the queue and the
-// idle lanes pull new rays (one atomicAdd per warp, compacted with __ballot_sync/__popc), so
-// incoherent rays do not leave most of the warp idle behind the slowest one.
-// Stack: kSmemStack entries per lane in shared memory (reference + box entry distance), spilling to
-// local memory beyond that.  A popped subtree whose entry distance is already behind the current
-// hit is dropped without fetching its node.
-#ifndef ATN_TRACE_MIN_BLOCKS
-#define ATN_TRACE_MIN_BLOCKS 8
-#endif
-template <class Policy>
-__global__ void __launch_bounds__(kTraceBlock, ATN_TRACE_MIN_BLOCKS)
-k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch, Visits* visits)
-{
-    __shared__ int2 s_stack[kSmemStack * kTraceBlock];   // (reference, entry distance bits) per lane and level
-    __shared__ float s_world[13 * kTraceBlock];      // world-space org, dir, invdir, oxinvdir, leaf margin of the lane's ray
-    int2 l_stack[kLocalStack];
-    const int tid = threadIdx.x;
-
-    const unsigned full = 0xffffffffu;
-    const int lane = threadIdx.x & 31;
-    const int count = count_ptr ? *count_ptr : count_imm;
-    const float t_min = bv.t_min;
-
-    // per-lane traversal state
-    bool active = false;             // the lane owns a ray that is still being traversed
-    bool done = false;               // traversal complete, result not written yet (written at the next refill)
-    bool exhausted = false;          // warp-uniform: the queue has no more rays
-    int slot = 0, mode = EXIT_NONE, sp = 0, cur = kRefNull, cur_inst = -1;
-    float exit_dist = 0.0f, t_cull = kInf, margin = -1.0f;
-    V3 org, dir;
-    RayInv ri;
-    TraceResult best;
-    best.t = kInf; best.a = 0.0f; best.b = 0.0f; best.leaf = -1; best.inst = -1;
-    uint32_t n_nodes = 0, n_tris = 0;     // work counters (folded into Visits once per warp)
-
-    for (;;) {
-        // ---------------- write results of completed rays (all such lanes together) ----------------
-        if (done) { pol.finish(bv, slot, best); done = false; }
-
-        // ---------------- refill idle lanes ----------------
-        const unsigned idle = __ballot_sync(full, !active);
-        if (idle != 0u && !exhausted) {
-            const int nidle = __popc(idle);
-            const int leader = __ffs(idle) - 1;
-            int base = 0;
-            if (lane == leader) base = atomicAdd(fetch, nidle);
-            base = __shfl_sync(full, base, leader);
-            if (base + nidle >= count) exhausted = true;
-            if (!active) {
-                const int i = base + __popc(idle & ((1u << lane) - 1u));
-                if (i < count) {
-                    float t_max;
-                    pol.load(i, &slot, &org, &dir, &t_max, &mode, &exit_dist);
-                    ri = ray_inv(org, dir);
-                    margin = leaf_margin(org, dir, ri);
-                    s_world[0 * kTraceBlock + tid] = org.x; s_world[1 * kTraceBlock + tid] = org.y; s_world[2 * kTraceBlock + tid] = org.z;
-                    s_world[3 * kTraceBlock + tid] = dir.x; s_world[4 * kTraceBlock + tid] = dir.y; s_world[5 * kTraceBlock + tid] = dir.z;
-                    s_world[6 * kTraceBlock + tid] = ri.invdir.x; s_world[7 * kTraceBlock + tid] = ri.invdir.y; s_world[8 * kTraceBlock + tid] = ri.invdir.z;
-                    s_world[9 * kTraceBlock + tid] = ri.oxinvdir.x; s_world[10 * kTraceBlock + tid] = ri.oxinvdir.y; s_world[11 * kTraceBlock + tid] = ri.oxinvdir.z;
-                    s_world[12 * kTraceBlock + tid] = margin;
-                    t_cull = t_max;
-                    best.t = kInf; best.a = 0.0f; best.b = 0.0f; best.leaf = -1; best.inst = -1;
-                    sp = 0; cur = bv.top_root; cur_inst = -1;
-                    active = true;
-                }
-            }
-        }
-        if (__ballot_sync(full, active) == 0u) break;
-
-        // ---------------- advance all rays of the warp, one node / leaf per iteration ----------------
-        for (;;) {
-            const unsigned act = __ballot_sync(full, active);
-            if (act == 0u) break;
-            if (!exhausted && __popc(act) < kRefillThreshold) break;
-
-            // ---- phase A: inner node, both slab tests branch free (aabb.h:61-86, running cull bound) ----
-            const bool on_node = active && cur >= 0;
-            if (on_node) {
-                const float4* np = bv.nodes + (size_t)cur * 4;
-                const float4 n0 = ldg4(np + 0);
-                const float4 n1 = ldg4(np + 1);
-                const float4 n2 = ldg4(np + 2);
-                const float4 n3 = ldg4(np + 3);
-                const int32_t left = __float_as_int(n3.x);
-                const int32_t right = __float_as_int(n3.y);
-                float t0l, t0r, t1l, t1r;
-                const bool bl = slab_test(ri, n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, t_min, t_cull, &t0l, &t1l);
-                const bool br = slab_test(ri, n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, t_min, t_cull, &t0r, &t1r);
-                // leaves are never box-tested by the reference: taken before boxes, unless the ray
-                // misses the leaf's box by a safe margin (see leaf_margin)
-                const float leaf_far = (best.leaf >= 0) ? t_cull : kInf;
-                const bool fl = leaf_may_hit(t0l, fminf(t1l, leaf_far), margin) & (left != kRefNull);
-                const bool fr = leaf_may_hit(t0r, fminf(t1r, leaf_far), margin) & (right != kRefNull);
-                const bool hl = (left >= 0) ? bl : fl;
-                const bool hr = (right >= 0) ? br : fr;
-                n_nodes++;
-                t0l = (left >= 0) ? t0l : -kInf;
-                t0r = (right >= 0) ? t0r : -kInf;
-                if (hl && hr) {
-                    const bool swap = t0r < t0l;        // near child first
-                    const int32_t farc = swap ? left : right;
-                    const float fart = swap ? t0l : t0r;
-                    const int2 e = make_int2(farc, __float_as_int(fart));
-                    if (sp < kSmemStack) s_stack[sp * kTraceBlock + tid] = e; else l_stack[sp - kSmemStack] = e;
-                    sp++;
-                    cur = swap ? right : left;
-                }
-                else if (hl) cur = left;
-                else if (hr) cur = right;
-                else cur = kRefNull;
-            }
-
-            // ---- phase B: triangle leaf (triangle::hit, triangle.h:40-67) ----
-            const bool want_tri = active && cur < 0 && cur != kRefNull && cur != kRefExit && cur_inst >= 0;
-            // The triangle test is the longest section and runs for few lanes at a time.  Lanes wait with
-            // their leaf until kLeafBatch of them have one, or no lane is on a node (kLeafBatch = 1: no waiting).
-            bool run_tris = true;
-            if (kLeafBatch > 1) {
-                const unsigned mt = __ballot_sync(full, want_tri);
-                const unsigned mn = __ballot_sync(full, on_node);
-                run_tris = (__popc(mt) >= kLeafBatch) || (mn == 0u);
-            }
-            const bool on_tri = want_tri && run_tris;
-            bool finished = false;
-            if (on_tri) {
-                const int32_t leaf = ~cur;
-                const float4* tp = bv.tris + (size_t)leaf * kTriStride;
-                const float4 a = ldg4(tp + 0);
-                const float4 b = ldg4(tp + 1);
-                const float4 c = ldg4(tp + 2);
-                const TriHit h = intersect_triangle_edges(org, dir, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), V3(c.x, c.y, c.z));
-                n_tris++;
-                if (h.hit && h.t < kInf && t_min < h.t) {
-                    const bool closer = h.t < best.t ||
-                        (h.t == best.t && (cur_inst < best.inst || (cur_inst == best.inst && leaf < best.leaf)));
-                    if (closer) {
-                        best.t = h.t; best.a = h.a; best.b = h.b; best.leaf = leaf; best.inst = cur_inst;
-                        t_cull = cull_bound(h.t);
-                        if (mode == EXIT_ANY_HIT || (mode == EXIT_HIT_BEFORE && h.t <= exit_dist)) finished = true;
-                    }
-                }
-                cur = kRefNull;
-            }
-
-            // ---- phase E: top-layer leaf = instance entry (threaded_bvh_traverser.h:146-185).  Lanes
-            // wait here until a few of them want to enter, or nothing else is going on in the warp:
-            // the transform is long and otherwise runs for one or two lanes at a time. ----
-            const bool want_entry = active && cur < 0 && cur != kRefNull && cur != kRefExit && cur_inst < 0;
-            const unsigned me = __ballot_sync(full, want_entry);
-            if (me != 0u) {
-                const unsigned busy = __ballot_sync(full, on_node || on_tri);
-                if (__popc(me) >= kEntryBatch || busy == 0u) {
-                    if (want_entry) {
-                        const int32_t leaf = ~cur;
-                        const int4 il = __ldg(reinterpret_cast<const int4*>(bv.insts) + leaf);
-                        cur = kRefNull;
-                        if (il.y != kRefNull) {
-                            const int2 e = make_int2(kRefExit, __float_as_int(-kInf));
-                            if (sp < kSmemStack) s_stack[sp * kTraceBlock + tid] = e; else l_stack[sp - kSmemStack] = e;
-                            sp++;
-                            cur_inst = leaf;
-                            if (il.z >= 0) {
-                                const AtnMat4 m = bv.matrices[il.z];
-                                const Ray tr = make_ray(mat_apply(m, org), mat_apply_xyz(m, dir));   // mat4::applyRay
-                                org = tr.org; dir = tr.dir;
-                                ri = ray_inv(org, dir);
-                                margin = leaf_margin(org, dir, ri);
-                            }
-                            cur = il.y;
-                        }
-                    }
-                }
-            }
-
-            // ---- phase C: pop ----
-            if (active && !finished && cur == kRefNull) {
-#pragma unroll 1
-                for (int pops = 0; pops < kPopMax; pops++) {
-                    if (sp == 0) { finished = true; break; }
-                    sp--;
-                    const int2 e = (sp < kSmemStack) ? s_stack[sp * kTraceBlock + tid] : l_stack[sp - kSmemStack];
-                    cur = e.x;
-                    const float t0 = __int_as_float(e.y);
-                    if (cur == kRefExit) {
-                        if (sp == 0) { finished = true; break; }      // nothing left in the top layer either
-                        // back to the top layer with the world ray (threaded_bvh_traverser.h:290-300)
-                        cur_inst = -1;
-                        org = V3(s_world[0 * kTraceBlock + tid], s_world[1 * kTraceBlock + tid], s_world[2 * kTraceBlock + tid]);
-                        dir = V3(s_world[3 * kTraceBlock + tid], s_world[4 * kTraceBlock + tid], s_world[5 * kTraceBlock + tid]);
-                        ri.invdir = V3(s_world[6 * kTraceBlock + tid], s_world[7 * kTraceBlock + tid], s_world[8 * kTraceBlock + tid]);
-                        ri.oxinvdir = V3(s_world[9 * kTraceBlock + tid], s_world[10 * kTraceBlock + tid], s_world[11 * kTraceBlock + tid]);
-                        margin = s_world[12 * kTraceBlock + tid];
-                        cur = kRefNull;
-                        continue;
-                    }
-                    if (t0 > t_cull) { cur = kRefNull; continue; }   // subtree starts behind the current hit
-                    break;
-                }
-            }
-            if (finished) { active = false; done = true; }
-        }
-    }
-    // work counters: one atomic pair per warp
-    for (int o = 16; o > 0; o >>= 1) {
-        n_nodes += __shfl_xor_sync(full, n_nodes, o);
-        n_tris += __shfl_xor_sync(full, n_tris, o);
-    }
-    if (lane == 0 && visits) {
-        atomicAdd(&visits->nodes, (unsigned long long)n_nodes);
-        atomicAdd(&visits->tris, (unsigned long long)n_tris);
-    }
-}
-
 // ---------------------------------------------------------------------------------------------
-// traversal over QuadNodes (atn_bvh.h "Wide (4-slot) encoding")
+// traversal kernel over QuadNodes (atn_bvh.h "Wide (4-slot) encoding")
 // ---------------------------------------------------------------------------------------------
-#ifndef ATN_SMEM_STACK4
-#define ATN_SMEM_STACK4 16
-#endif
-#ifndef ATN_LEAF_BATCH4
-#define ATN_LEAF_BATCH4 6
-#endif
-constexpr int kSmemStack4 = ATN_SMEM_STACK4;
-constexpr int kLeafBatch4 = ATN_LEAF_BATCH4;
 constexpr uint32_t kStackStride = kTraceBlock * 8u;     // bytes between two levels of one lane's shared stack
 
 // Two IEEE multiplications in one issue slot (FMUL2).  Only the products are packed: ptxas contracts a
@@ -657,18 +421,34 @@ __device__ __forceinline__ SlabPair slab_pair(const float4 mn_xy, const float4 m
         ka = lo_; kb = hi_; ra = rl_; rb = rh_;                         \
     }
 
-// Same execution model and acceptance rules as k_trace; what differs is the inner-node step: one
-// 128-byte QuadNode decides up to four subtrees or leaves, the slots that are hit are ordered by entry
-// distance, the nearest is followed and the others go to the stack farthest first.  Every slot's box
-// is tested with the reference's own slab test (a leaf's slot carries the box of the node whose hit
-// makes the reference visit that leaf), so there is no approximate filter inside the trees; the only
-// conservative pre-filter left is the world-space box of an instance, tested before the ray is
-// carried into the instance's space.
+// Two-level closest-hit traversal with the reference's acceptance rules (threaded_bvh_traverser.h:98-304):
+// inner boxes use aabb::hit, leaves are never box-tested, a triangle is accepted iff t_min < t && t < best
+// (ties: lowest depth-first rank, which is what "first encountered" means in the reference's fixed
+// visit order).
+//
+// Execution model: persistent warps.  Every lane owns one ray and a resumable traversal state; the
+// warp advances all its rays one node / leaf per iteration and re-converges after each iteration.
+// When fewer than kRefillThreshold lanes still have a ray, the warp goes back to the queue and the
+// idle lanes pull new rays (one atomicAdd per warp, compacted with __ballot_sync/__popc), so
+// incoherent rays do not leave most of the warp idle behind the slowest one.
+//
+// Node step: one 128-byte QuadNode (four 256-bit loads) decides up to four subtrees or leaves; the slots
+// that are hit are ordered by entry distance with a 5-comparator network, the nearest is followed and
+// the others go to the stack farthest first.  Every slot's box is tested with the reference's own slab
+// test (a leaf's slot carries the box of the node whose hit makes the reference visit that leaf), so
+// there is no approximate filter inside the trees; the only conservative pre-filter is the world-space
+// box of an instance, tested before the ray is carried into the instance's space.
+// Stack: kSmemStack entries per lane in shared memory (reference + box entry distance), spilling to
+// local memory beyond that.  A popped subtree whose entry distance is already behind the current hit
+// is dropped without fetching its node.
+#ifndef ATN_TRACE_MIN_BLOCKS
+#define ATN_TRACE_MIN_BLOCKS 8
+#endif
 template <class Policy>
 __global__ void __launch_bounds__(kTraceBlock, ATN_TRACE_MIN_BLOCKS)
-k_trace4(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch, Visits* visits)
+k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch, Visits* visits)
 {
-    __shared__ int2 s_stack[kSmemStack4 * kTraceBlock];   // (reference, entry distance bits) per lane and level
+    __shared__ int2 s_stack[kSmemStack * kTraceBlock];   // (reference, entry distance bits) per lane and level
     __shared__ float s_world[12 * kTraceBlock];          // world-space org, dir, invdir, oxinvdir of the lane's ray
     int2 l_stack[kLocalStack];
     const int tid = threadIdx.x;
@@ -749,7 +529,7 @@ k_trace4(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int coun
                 cur = nhit ? r0 : kRefNull;
                 const int np_ = nhit - 1;                 // entries left behind, nearest on top
                 if (np_ > 0) {
-                    if (sp + np_ <= kSmemStack4) {
+                    if (sp + np_ <= kSmemStack) {
                         const uint32_t top = stack_base + (uint32_t)(sp + np_) * kStackStride;
                         sts64(top - kStackStride, r1, __float_as_int(k1));
                         if (np_ > 1) sts64(top - 2u * kStackStride, r2, __float_as_int(k2));
@@ -762,8 +542,8 @@ k_trace4(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int coun
                         for (int k = 2; k >= 0; k--) {
                             if (k < np_) {
                                 const int at = sp + (np_ - 1 - k);
-                                if (at < kSmemStack4) sts64(stack_base + (uint32_t)at * kStackStride, rr[k], __float_as_int(kk[k]));
-                                else l_stack[at - kSmemStack4] = make_int2(rr[k], __float_as_int(kk[k]));
+                                if (at < kSmemStack) sts64(stack_base + (uint32_t)at * kStackStride, rr[k], __float_as_int(kk[k]));
+                                else l_stack[at - kSmemStack] = make_int2(rr[k], __float_as_int(kk[k]));
                             }
                         }
                     }
@@ -774,10 +554,10 @@ k_trace4(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int coun
             // ---- phase B: triangle leaf (triangle::hit, triangle.h:40-67) ----
             const bool want_tri = active && cur < 0 && cur != kRefNull && cur != kRefExit && cur_inst >= 0;
             bool run_tris = true;
-            if (kLeafBatch4 > 1) {
+            if (kLeafBatch > 1) {
                 const unsigned mt = __ballot_sync(full, want_tri);
                 const unsigned mn = __ballot_sync(full, on_node);
-                run_tris = (__popc(mt) >= kLeafBatch4) || (mn == 0u);
+                run_tris = (__popc(mt) >= kLeafBatch) || (mn == 0u);
             }
             const bool on_tri = want_tri && run_tris;
             bool finished = false;
@@ -820,8 +600,8 @@ k_trace4(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int coun
                         const float far = (best.leaf >= 0) ? t_cull : kInf;
                         const bool may = leaf_may_hit(t0w, fminf(t1w, far), leaf_margin(org, dir, ri));
                         if (il.y != kRefNull && may) {
-                            if (sp < kSmemStack4) sts64(stack_base + (uint32_t)sp * kStackStride, kRefExit, __float_as_int(-kInf));
-                            else l_stack[sp - kSmemStack4] = make_int2(kRefExit, __float_as_int(-kInf));
+                            if (sp < kSmemStack) sts64(stack_base + (uint32_t)sp * kStackStride, kRefExit, __float_as_int(-kInf));
+                            else l_stack[sp - kSmemStack] = make_int2(kRefExit, __float_as_int(-kInf));
                             sp++;
                             cur_inst = leaf;
                             if (il.z >= 0) {
@@ -842,7 +622,7 @@ k_trace4(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int coun
                 for (;;) {
                     if (sp == 0) { finished = true; break; }
                     sp--;
-                    const int2 e = (sp < kSmemStack4) ? lds64(stack_base + (uint32_t)sp * kStackStride) : l_stack[sp - kSmemStack4];
+                    const int2 e = (sp < kSmemStack) ? lds64(stack_base + (uint32_t)sp * kStackStride) : l_stack[sp - kSmemStack];
                     cur = e.x;
                     if (cur == kRefExit) {
                         if (sp == 0) { finished = true; break; }      // nothing left in the top layer either
@@ -870,12 +650,6 @@ k_trace4(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int coun
         atomicAdd(&visits->tris, (unsigned long long)n_tris);
     }
 }
-
-#if ATN_WIDE
-#define ATN_TRACE_KERNEL k_trace4
-#else
-#define ATN_TRACE_KERNEL k_trace
-#endif
 
 // ---------------------------------------------------------------------------------------------
 // generate / shade / gather
@@ -1267,17 +1041,9 @@ struct AtnRenderer {
     DevBuf<AtnVec4> positions, normals;
     DevBuf<AtnVec4> texels;
     DevBuf<TexView> texviews;
-#if ATN_WIDE
     DevBuf<QuadNode> nodes;
-#else
-    DevBuf<PairNode> nodes;
-#endif
     DevBuf<TriLeaf> tris;
-#if ATN_WIDE
     DevBuf<InstLeafW> insts;
-#else
-    DevBuf<InstLeaf> insts;
-#endif
     DevBuf<uint32_t> seeds;
     uint32_t seed_count{ 0 };
     SceneView sv{};
@@ -1329,17 +1095,10 @@ struct AtnRenderer {
 
 static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene)
 {
-#if ATN_WIDE
     WideBvh enc = encode_wide(scene);
     if (!enc.error.empty()) return set_error(ATN_ERR_INVALID_ARGUMENT, "node lists: %s", enc.error.c_str());
-    if (enc.max_stack > kSmemStack4 + kLocalStack)
-        return set_error(ATN_ERR_TOO_LARGE, "BVH needs a traversal stack of %d entries (limit %d)", enc.max_stack, kSmemStack4 + kLocalStack);
-#else
-    EncodedBvh enc = encode_bvh(scene);
-    if (!enc.error.empty()) return set_error(ATN_ERR_INVALID_ARGUMENT, "node lists: %s", enc.error.c_str());
-    if (enc.max_depth + 8 > kSmemStack + kLocalStack)
-        return set_error(ATN_ERR_TOO_LARGE, "BVH depth %d exceeds the traversal stack (%d)", enc.max_depth, kSmemStack + kLocalStack);
-#endif
+    if (enc.max_stack > kSmemStack + kLocalStack)
+        return set_error(ATN_ERR_TOO_LARGE, "BVH needs a traversal stack of %d entries (limit %d)", enc.max_stack, kSmemStack + kLocalStack);
     CUDA_TRY(r->nodes.upload(enc.nodes.data(), enc.nodes.size(), r->stream));
     CUDA_TRY(r->tris.upload(enc.tris.data(), enc.tris.size(), r->stream));
     CUDA_TRY(r->insts.upload(enc.insts.data(), enc.insts.size(), r->stream));
@@ -1413,7 +1172,7 @@ ATN_API int atn_create(int device_ordinal, AtnRenderer** out)
     CUDA_TRY(cudaEventCreate(&r->ev0));
     CUDA_TRY(cudaEventCreate(&r->ev1));
     int bps = 0;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, ATN_TRACE_KERNEL<ClosestPolicy>, kTraceBlock, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace<ClosestPolicy>, kTraceBlock, 0));
     r->trace_grid = r->sm_count * std::max(1, bps);
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_surface<false>, kShadeBlock, 0));
     r->surface_grid = r->sm_count * std::max(1, bps);
@@ -1665,7 +1424,7 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             {
                 ClosestPolicy pol{ r->pb, q, tmax, b == 0 ? r->pb.hit_mesh : nullptr };
-                ATN_TRACE_KERNEL<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[b], 0, &c->fetch_closest[b], r->visits.p);
+                k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[b], 0, &c->fetch_closest[b], r->visits.p);
             }
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             if (tap_now) k_surface<true><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, r->pb, c, b, r->tap_dev.p, r->tap_cap);
@@ -1676,11 +1435,11 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             if (tap_now) {
                 ShadowPolicy<true> pol{ r->pb, r->sv, r->tap_dev.p, r->tap_cap, b };
-                ATN_TRACE_KERNEL<ShadowPolicy<true>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
+                k_trace<ShadowPolicy<true>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
             }
             else {
                 ShadowPolicy<false> pol{ r->pb, r->sv, nullptr, 0, b };
-                ATN_TRACE_KERNEL<ShadowPolicy<false>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
+                k_trace<ShadowPolicy<false>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
             }
             if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
             launches += 5;
@@ -1748,7 +1507,7 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
         k_generate<<<grid, 256, 0, s>>>(fp, r->camera, r->seeds.p, r->pb, c);
         {
             ClosestPolicy pol{ r->pb, nullptr, kInf, nullptr };
-            ATN_TRACE_KERNEL<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[0], 0, &c->fetch_closest[0], r->visits.p);
+            k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[0], 0, &c->fetch_closest[0], r->visits.p);
         }
         k_ao_begin<<<sgrid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, r->pb, c);
         launches += 3;
@@ -1756,7 +1515,7 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
             k_ao_ray<<<sgrid, kShadeBlock, 0, s>>>(fp, r->seeds.p, r->pb, c);
             CUDA_TRY(cudaMemsetAsync(&c->fetch_query, 0, sizeof(int32_t), s));
             ClosestPolicy pol{ r->pb, r->pb.q_lit, radius, nullptr };
-            ATN_TRACE_KERNEL<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_lit[0], 0, &c->fetch_query, r->visits.p);
+            k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_lit[0], 0, &c->fetch_query, r->visits.p);
             k_ao_accum<<<sgrid, kShadeBlock, 0, s>>>(r->sv, r->pb, c, radius, i == num_rays - 1 ? 1 : 0, num_rays);
             launches += 3;
         }
@@ -1842,11 +1601,11 @@ static int query_launch(AtnRenderer* r, const void* rays_dev, const void* f_dev,
     CUDA_TRY(cudaEventRecord(r->ev0, s));
     if (any) {
         QueryAnyPolicy pol{ (const AtnRay*)rays_dev, (const float*)f_dev, (uint8_t*)out_dev };
-        ATN_TRACE_KERNEL<QueryAnyPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
+        k_trace<QueryAnyPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
     }
     else {
         QueryClosestPolicy pol{ (const AtnRay*)rays_dev, (const float*)f_dev, (AtnHit*)out_dev };
-        ATN_TRACE_KERNEL<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
+        k_trace<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
     }
     CUDA_TRY(cudaEventRecord(r->ev1, s));
     CUDA_TRY(cudaGetLastError());
@@ -1982,7 +1741,7 @@ extern "C" ATN_API int atn_trace_closest_static(AtnRenderer* r, const AtnRay* ra
     CUDA_TRY(cudaMemcpyAsync(sc->rays, rays, n * sizeof(AtnRay), cudaMemcpyHostToDevice, s));
     if (t_max) CUDA_TRY(cudaMemcpyAsync(sc->t_max, t_max, n * sizeof(float), cudaMemcpyHostToDevice, s));
     QueryClosestPolicy pol{ sc->rays, t_max ? sc->t_max : nullptr, sc->hits };
-    ATN_TRACE_KERNEL<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &sc->cursor, nullptr);
+    k_trace<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &sc->cursor, nullptr);
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaMemcpyAsync(hits, sc->hits, n * sizeof(AtnHit), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaStreamSynchronize(s));

@@ -39,7 +39,7 @@ def render_bench(name, W, H, spp, steps=3, warmup=2, label=""):
            "nodes": scene.node_count, "instances": int((scene.objects["type"] == 1).sum()),
            "ms_per_step": round(ms / steps, 3), "mrays_per_s": round(rays / ms / 1e3, 1),
            "msamples_per_s": round(samples / ms / 1e3, 1), "rays_per_sample": round(rays / samples, 2),
-           "pair_nodes_per_ray": round(nodes / rays, 2), "tri_tests_per_ray": round(tris / rays, 2),
+           "quad_nodes_per_ray": round(nodes / rays, 2), "tri_tests_per_ray": round(tris / rays, 2),
            "mean_radiance": float(img[..., :3].mean() / spp), "finite": bool(np.isfinite(img).all())}
     print(json.dumps(out), flush=True)
 

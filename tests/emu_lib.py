@@ -1,0 +1,48 @@
+"""TEST INFRASTRUCTURE: ctypes access to tests/emu_traversal.cpp, a sequential CPU emulation of the
+traversal kernel over the product's own QuadNode encoder (aten_b200/csrc/atn_bvh.h).  It gives the CPU
+suite a way to check the encoder without a GPU; the product never loads it."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from aten_b200 import scene_io as sio
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SO = os.path.join(HERE, "_build", "libemu_traversal.so")
+SRC = os.path.join(HERE, "emu_traversal.cpp")
+DEPS = [SRC, os.path.join(HERE, "..", "aten_b200", "csrc", "atn_bvh.h"), os.path.join(HERE, "..", "aten_b200", "csrc", "atn_math.cuh")]
+_lib = None
+
+STAT_NAMES = ("nodes", "tris", "entries", "entries_filtered", "pops_culled", "max_sp", "node_count", "slots_used",
+              "replaced", "not_nested", "stack_bound")
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        stale = not os.path.exists(SO) or any(os.path.getmtime(d) > os.path.getmtime(SO) for d in DEPS)
+        if stale:
+            os.makedirs(os.path.dirname(SO), exist_ok=True)
+            subprocess.run(["g++", "-std=c++17", "-O2", "-fopenmp", "-fPIC", "-ffp-contract=off", "-shared", "-o", SO, SRC],
+                           check=True)
+        _lib = C.CDLL(SO)
+    return _lib
+
+
+def trace_closest(scene: sio.Scene, rays: np.ndarray, t_max=None, leaves_first=False, entry_filter=True):
+    """Closest hits of `rays` through encode_wide(scene) + the kernel's per-ray logic; returns (hits, stats dict)."""
+    rays = np.ascontiguousarray(rays, dtype=sio.RAY_DTYPE)
+    hits = np.zeros(len(rays), dtype=sio.HIT_DTYPE)
+    stats = np.zeros(16, np.uint64)
+    tm = None if t_max is None else np.ascontiguousarray(t_max, dtype=np.float32)
+    blob = scene.blob()
+    rc = lib().emu_trace_wide(C.byref(blob), C.c_void_p(rays.ctypes.data), C.c_void_p(tm.ctypes.data) if tm is not None else None,
+                              C.c_size_t(len(rays)), C.c_void_p(hits.ctypes.data), C.c_void_p(stats.ctypes.data),
+                              C.c_int(1 if leaves_first else 0), C.c_int(1 if entry_filter else 0))
+    if rc != 0:
+        raise RuntimeError("encode_wide rejected the scene's node lists")
+    return hits, {k: int(v) for k, v in zip(STAT_NAMES, stats)}

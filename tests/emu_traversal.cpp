@@ -1,8 +1,9 @@
-// DEVELOPMENT TOOL (not part of the product, not loaded by it): a sequential CPU emulation of the
-// traversal kernels' per-ray logic over the PairNode and QuadNode encodings of atn_bvh.h.  Used to
-// count node steps / triangle tests / stack depth for an encoding before it goes to the GPU, and to
-// check its hits against the oracle on the same rays (scripts/emu_wide.py).
-//   g++ -std=c++17 -O2 -fopenmp -fPIC -ffp-contract=off -shared -o /tmp/libemu_wide.so scripts/emu_wide.cpp
+// TEST INFRASTRUCTURE (not part of the product, not loaded by it): a sequential CPU emulation of the
+// traversal kernel's per-ray logic (k_trace, atn_kernels.cu) over the QuadNode encoding that the
+// product's host code builds (atn_bvh.h, encode_wide).  It lets the CPU suite check the encoder -- the
+// exact collapse of the reference's binary trees -- against the oracle without a GPU, and counts node
+// steps / triangle tests / stack depth (scripts/emu_wide.py).
+//   g++ -std=c++17 -O2 -fopenmp -fPIC -ffp-contract=off -shared -o tests/_build/libemu_traversal.so tests/emu_traversal.cpp
 #include <stdint.h>
 #include <string.h>
 #include <cmath>
@@ -185,112 +186,6 @@ extern "C" int emu_trace_wide(const AtnSceneBlob* scene, const AtnRay* rays, con
         stats_out[0] = tot.nodes; stats_out[1] = tot.tris; stats_out[2] = tot.entries; stats_out[3] = tot.entries_filtered;
         stats_out[4] = tot.pops_culled; stats_out[5] = tot.max_sp; stats_out[6] = w.nodes.size(); stats_out[7] = w.slots_used;
         stats_out[8] = w.replaced; stats_out[9] = w.not_nested; stats_out[10] = (uint64_t)w.max_stack;
-    }
-    return 0;
-}
-
-// The PairNode encoding the kernels walk today (same acceptance rules, leaf pre-filter included).
-extern "C" int emu_trace_pair(const AtnSceneBlob* scene, const AtnRay* rays, const float* t_max_in, size_t n, AtnHit* hits,
-                              uint64_t* stats_out)
-{
-    EncodedBvh w = encode_bvh(scene);
-    if (!w.error.empty()) return -1;
-    std::vector<int32_t> iobj(w.insts.size()), imesh(w.insts.size());
-    for (size_t i = 0; i < w.insts.size(); i++) { iobj[i] = w.insts[i].objid; imesh[i] = w.insts[i].meshid; }
-    const float t_min = scene->config.bvh_hit_min > 0 ? scene->config.bvh_hit_min : kEps;
-    Stats tot{};
-#pragma omp parallel
-    {
-        Stats st{};
-        std::vector<Ent> stack;
-#pragma omp for schedule(dynamic, 1024)
-        for (long long i = 0; i < (long long)n; i++) {
-            const V3 worg(rays[i].org), wdir(rays[i].dir);
-            V3 org = worg, dir = wdir;
-            RayInv ri = ray_inv(org, dir);
-            const RayInv wri = ri;
-            float margin = leaf_margin(org, dir, ri);
-            const float wmargin = margin;
-            float t_cull = t_max_in ? t_max_in[i] : kBig;
-            Best best{ kBig, 0, 0, -1, -1 };
-            stack.clear();
-            int32_t cur = w.top_root, cur_inst = -1;
-            for (;;) {
-                if (cur >= 0) {
-                    const PairNode& p = w.nodes[cur];
-                    st.nodes++;
-                    const float lmn[3] = { p.n0[0], p.n0[2], p.n2[0] }, lmx[3] = { p.n0[1], p.n0[3], p.n2[1] };
-                    const float rmn[3] = { p.n1[0], p.n1[2], p.n2[2] }, rmx[3] = { p.n1[1], p.n1[3], p.n2[3] };
-                    const Slab sl = slab(ri, lmn, lmx, t_min, t_cull), sr = slab(ri, rmn, rmx, t_min, t_cull);
-                    const float far = best.leaf >= 0 ? t_cull : kBig;
-                    const bool fl = leaf_may_hit(sl.t0, fminf(sl.t1, far), margin) && p.left != kRefNull;
-                    const bool fr = leaf_may_hit(sr.t0, fminf(sr.t1, far), margin) && p.right != kRefNull;
-                    const bool hl = p.left >= 0 ? sl.hit : fl, hr = p.right >= 0 ? sr.hit : fr;
-                    const float t0l = p.left >= 0 ? sl.t0 : -kBig, t0r = p.right >= 0 ? sr.t0 : -kBig;
-                    if (hl && hr) {
-                        const bool swap = t0r < t0l;
-                        stack.push_back(Ent{ swap ? p.left : p.right, swap ? t0l : t0r });
-                        cur = swap ? p.right : p.left;
-                    }
-                    else if (hl) cur = p.left;
-                    else if (hr) cur = p.right;
-                    else cur = kRefNull;
-                }
-                else if (cur != kRefNull && cur != kRefExit) {
-                    const int32_t leaf = ~cur;
-                    if (cur_inst >= 0) {
-                        const TriLeaf& t = w.tris[leaf];
-                        st.tris++;
-                        const TriHit h = tri_edges(org, dir, V3(t.v0[0], t.v0[1], t.v0[2]), V3(t.e1[0], t.e1[1], t.e1[2]), V3(t.e2[0], t.e2[1], t.e2[2]));
-                        if (h.hit && h.t < kBig && t_min < h.t) {
-                            const bool closer = h.t < best.t || (h.t == best.t && (cur_inst < best.inst || (cur_inst == best.inst && leaf < best.leaf)));
-                            if (closer) { best.t = h.t; best.a = h.a; best.b = h.b; best.leaf = leaf; best.inst = cur_inst; t_cull = cull_bound(h.t); }
-                        }
-                        cur = kRefNull;
-                    }
-                    else {
-                        const InstLeaf& il = w.insts[leaf];
-                        cur = kRefNull;
-                        if (il.root != kRefNull) {
-                            st.entries++;
-                            stack.push_back(Ent{ kRefExit, -kBig });
-                            cur_inst = leaf;
-                            if (il.w2l >= 0) {
-                                const AtnMat4& m = scene->matrices[il.w2l];
-                                const Ray tr = make_ray(mat_apply(m, org), mat_apply_xyz(m, dir));
-                                org = tr.org; dir = tr.dir; ri = ray_inv(org, dir); margin = leaf_margin(org, dir, ri);
-                            }
-                            cur = il.root;
-                        }
-                    }
-                }
-                if (stack.size() > st.max_sp) st.max_sp = stack.size();
-                bool finished = false;
-                while (cur == kRefNull) {
-                    if (stack.empty()) { finished = true; break; }
-                    const Ent e = stack.back(); stack.pop_back();
-                    cur = e.ref;
-                    if (cur == kRefExit) {
-                        if (stack.empty()) { finished = true; break; }
-                        cur_inst = -1; org = worg; dir = wdir; ri = wri; margin = wmargin; cur = kRefNull; continue;
-                    }
-                    if (e.t0 > t_cull) { cur = kRefNull; st.pops_culled++; continue; }
-                }
-                if (finished) break;
-            }
-            finish(w.tris, iobj.data(), imesh.data(), best, &hits[i]);
-            st.rays++;
-        }
-#pragma omp critical
-        {
-            tot.nodes += st.nodes; tot.tris += st.tris; tot.entries += st.entries; tot.pops_culled += st.pops_culled;
-            tot.rays += st.rays; if (st.max_sp > tot.max_sp) tot.max_sp = st.max_sp;
-        }
-    }
-    if (stats_out) {
-        stats_out[0] = tot.nodes; stats_out[1] = tot.tris; stats_out[2] = tot.entries; stats_out[3] = 0;
-        stats_out[4] = tot.pops_culled; stats_out[5] = tot.max_sp; stats_out[6] = w.nodes.size(); stats_out[7] = 0;
-        stats_out[8] = 0; stats_out[9] = 0; stats_out[10] = (uint64_t)w.max_depth;
     }
     return 0;
 }

@@ -1243,7 +1243,7 @@ ATN_API int atn_upload_scene(AtnRenderer* r, const AtnSceneBlob* scene, const At
     SceneView& sv = r->sv;
     sv.objects = r->objects.p; sv.matrices = r->matrices.p; sv.materials = r->materials.p; sv.lights = r->lights.p;
     sv.triangles = r->triangles.p; sv.positions = r->positions.p; sv.normals = r->normals.p;
-    sv.textures = r->texviews.p; sv.light_count = (int32_t)scene->light_count; sv.cfg = scene->config;
+    sv.textures = r->texviews.p; sv.light_count = (int32_t)scene->light_count; sv.material_count = (int32_t)scene->material_count; sv.cfg = scene->config;
     sv.scene_radius = scene_radius_of(scene->config);
     r->bv.t_min = scene->config.bvh_hit_min > 0 ? scene->config.bvh_hit_min : kEps;
 
@@ -1308,7 +1308,7 @@ ATN_API int atn_update_materials(AtnRenderer* r, const AtnMaterialParameter* m, 
     CUDA_TRY(cudaStreamSynchronize(r->stream));
     CUDA_TRY(r->materials.upload(m, count, r->stream));
     CUDA_TRY(cudaStreamSynchronize(r->stream));
-    r->sv.materials = r->materials.p;
+    r->sv.materials = r->materials.p; r->sv.material_count = (int32_t)count;
     return ATN_OK;
 }
 

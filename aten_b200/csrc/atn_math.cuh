@@ -278,6 +278,7 @@ struct SceneView {
     const AtnVec4* normals;
     const TexView* textures;
     int32_t light_count;
+    int32_t material_count;
     AtnSceneConfig cfg;
     float scene_radius;      // ComputeDistanceToCoverBoundingSphere(30 deg) or 10000 (ibl.h:105-110)
 };
@@ -1145,6 +1146,7 @@ struct PathState {
     Sampler sampler;
     bool terminated;
     bool singular;
+    bool last_specular = false;   // PathAttribute::last_hit_mtrl_idx names a Specular material (read by the SVGF shade only)
 };
 
 struct ShadowRayOut {
@@ -1223,9 +1225,15 @@ struct Surface {
 // Stage 1: evaluate_hit, FillMaterial, albedo, HitTeminatedMaterial -> HitImplicitLight
 // (pathtracing_impl.h:395-452), normal orientation + material::applyNormal.
 // Returns false when the path ended here (implicit light).
+// `svgf_w2c` != nullptr selects aten::SVGFRenderer::Shade (src/libaten/renderer/svgf/svgf.cpp:91-247) instead:
+// the AOVs of the first hit (or of the hit behind a Specular first hit) take the geometric normal, the
+// clip-space w of the hit as depth and the MATERIAL id in place of the mesh id; the albedo texture of that
+// hit is taken out of the path (albedoMap = -1: "exporting separated albedo") and put back by the last
+// a-trous pass; the albedo default is white instead of baseColor.
 ATN_HD bool shade_surface(const SceneView& sc, const Ray& ray, int32_t objid, int32_t primid, float a, float b,
                           float t, int32_t mtrlid, int32_t bounce, PathState* st, Surface* sf,
-                          AtnVec4* aov_normal_depth = nullptr, AtnVec4* aov_albedo_meshid = nullptr, int32_t meshid = -1)
+                          AtnVec4* aov_normal_depth = nullptr, AtnVec4* aov_albedo_meshid = nullptr, int32_t meshid = -1,
+                          const AtnMat4* svgf_w2c = nullptr)
 {
     const AtnObjectParameter obj = sc.objects[objid];
     HitRecord rec;
@@ -1234,10 +1242,21 @@ ATN_HD bool shade_surface(const SceneView& sc, const Ray& ray, int32_t objid, in
     const bool backfacing = dot(rec.normal, -ray.dir) < 0.0f;
     V3 orienting = rec.normal;
 
-    const Mtrl mtrl = fill_material(sc, rec.mtrlid);
-    const AtnVec4 albedo4 = sample_texture(sc, mtrl.albedoMap, rec.u, rec.v, mtrl.baseColor);
+    Mtrl mtrl = fill_material(sc, rec.mtrlid);
+    AtnVec4 albedo4;
+    if (svgf_w2c) {
+        if ((bounce == 0 || (bounce == 1 && st->last_specular)) && aov_normal_depth && aov_albedo_meshid) {
+            const AtnVec4 texcolor = sample_texture(sc, mtrl.albedoMap, rec.u, rec.v, v4(1.0f));
+            fill_basic_aovs(aov_normal_depth, orienting, rec.p, *svgf_w2c, aov_albedo_meshid, texcolor, mtrlid);
+            mtrl.albedoMap = -1;
+        }
+        albedo4 = sample_texture(sc, mtrl.albedoMap, rec.u, rec.v, v4(1.0f));
+    }
+    else {
+        albedo4 = sample_texture(sc, mtrl.albedoMap, rec.u, rec.v, mtrl.baseColor);
+    }
 
-    if (bounce == 0 && aov_normal_depth && aov_albedo_meshid) {
+    if (!svgf_w2c && bounce == 0 && aov_normal_depth && aov_albedo_meshid) {
         // The reference's GPU shade kernel stores the AOVs of the first hit before anything else can end
         // the path, with the normal-mapped (not yet flipped) normal and an identity matrix
         // (pathtracing_impl.cu:92-111).
@@ -1337,17 +1356,20 @@ ATN_HD void shade_bsdf(const SceneView& sc, const V3& ray_dir, const Surface& sf
     if (st->terminated) return;
     st->pdfb = pdfb;
     st->singular = mtrl.is_singular();
+    // PrepareForNextBounce: last_hit_mtrl_idx = mtrl.id; SVGFRenderer::Shade asks whether that material is Specular
+    st->last_specular = mtrl.id >= 0 && mtrl.id < sc.material_count && sc.materials[mtrl.id].type == ATN_MTRL_SPECULAR;
     *next_ray = make_ray(sf.p, next_dir, along);
 }
 
 ATN_HD void shade_hit(const SceneView& sc, const Ray& ray, int32_t objid, int32_t primid, float a, float b,
                       float t, int32_t mtrlid, int32_t bounce, int32_t rr_bounce,
-                      PathState* st, ShadowRayOut* sh, Ray* next_ray)
+                      PathState* st, ShadowRayOut* sh, Ray* next_ray,
+                      AtnVec4* aov_normal_depth = nullptr, AtnVec4* aov_albedo_meshid = nullptr, const AtnMat4* svgf_w2c = nullptr)
 {
     sh->active = false;
     if (st->terminated) return;
     Surface sf;
-    if (!shade_surface(sc, ray, objid, primid, a, b, t, mtrlid, bounce, st, &sf)) return;
+    if (!shade_surface(sc, ray, objid, primid, a, b, t, mtrlid, bounce, st, &sf, aov_normal_depth, aov_albedo_meshid, -1, svgf_w2c)) return;
     shade_nee(sc, ray.dir, sf, st, sh);
     shade_bsdf(sc, ray.dir, sf, bounce, rr_bounce, st, next_ray);
 }

@@ -24,6 +24,7 @@
 #include <vector>
 
 #include "../aten_b200/csrc/atn_math.cuh"
+#include "../aten_b200/csrc/atn_svgf.cuh"
 
 using namespace atn;
 
@@ -41,7 +42,7 @@ Scene MakeScene(const AtnSceneBlob* b)
     Scene s;
     s.view.objects = b->objects; s.view.matrices = b->matrices; s.view.materials = b->materials;
     s.view.lights = b->lights; s.view.triangles = b->triangles; s.view.positions = b->positions;
-    s.view.normals = b->normals; s.view.light_count = (int32_t)b->light_count; s.view.cfg = b->config;
+    s.view.normals = b->normals; s.view.light_count = (int32_t)b->light_count; s.view.material_count = (int32_t)b->material_count; s.view.cfg = b->config;
     for (uint32_t i = 0; i < b->texture_count; i++) {
         TexView t; t.texels = b->textures[i].texels; t.w = b->textures[i].width; t.h = b->textures[i].height;
         s.tex.push_back(t);
@@ -339,6 +340,114 @@ int oracle_render_ao(const AtnSceneBlob* blob, const AtnCameraParameter* cam, co
 }
 
 __attribute__((visibility("default")))
+// N1: aten::SVGFRenderer::OnRender (src/libaten/renderer/svgf/svgf.cpp:461-639), `frames` frames of one
+// sample each, starting at frame 0 (frame 0 has no history).  State lives in `state`, 11 * W*H AtnVec4 laid
+// out as: aov[0] {normal_depth, albedo_meshid, color_variance, moment_tw}, aov[1] {...}, atrous ping, atrous pong,
+// temporary colour; the caller passes it zero-filled... except that the reference's buffers start as default
+// aten::vec4 = (0,0,0,1), which this function writes itself when first_frame == 0.
+// `motion_depth`: W*H motion vectors (xy, in screen fractions) or NULL for a static camera.
+// `host_order` = 1: variance estimation updates the colour history in place in row-major order on one thread,
+// which is what the stock host renderer does with one OpenMP thread; 0: order-independent form (all pixels
+// read the unfiltered colours), which is what the GPU path computes.
+// `image`: W*H film colours of the LAST frame rendered (last a-trous iteration, albedo put back).
+int oracle_render_svgf(const AtnSceneBlob* blob, const AtnCameraParameter* cam, const uint32_t* seeds, uint32_t seed_count,
+                       int32_t W, int32_t H, uint32_t first_frame, int32_t frames, int32_t max_depth, int32_t rr_depth,
+                       const AtnVec4* motion_depth, int32_t host_order, int32_t atrous_iters, AtnVec4* state, AtnVec4* image)
+{
+    const Scene s = MakeScene(blob);
+    if (rr_depth > max_depth) rr_depth = max_depth - 1;
+    const size_t n = (size_t)W * H;
+    SvgfAov aovs[2];
+    for (int k = 0; k < 2; k++) {
+        aovs[k].normal_depth = state + (k * 4 + 0) * n; aovs[k].albedo_meshid = state + (k * 4 + 1) * n;
+        aovs[k].color_variance = state + (k * 4 + 2) * n; aovs[k].moment_tw = state + (k * 4 + 3) * n;
+    }
+    AtnVec4* atrous[2] = { state + 8 * n, state + 9 * n };
+    AtnVec4* temporary = state + 10 * n;
+    if (first_frame == 0)
+        for (size_t i = 0; i < 11 * n; i++) { state[i].x = 0; state[i].y = 0; state[i].z = 0; state[i].w = 1; }
+    std::vector<AtnVec4> contribs(n), scratch(host_order ? 0 : n);
+    const AtnMat4 w2c = camera_w2c(*cam);
+    const float camera_distance = screen_distance(*cam, H);
+    const int32_t iter_count = atrous_iters > 0 ? atrous_iters : 5;      // SVGFParams::atrous_iter_cnt, svgf_types.h:74
+
+    for (int32_t f = 0; f < frames; f++) {
+        const uint32_t frame = first_frame + (uint32_t)f;
+        SvgfAov cur = aovs[frame & 1], prev = aovs[1 - (frame & 1)];
+        // ---- one sample of path tracing per pixel (ExecRendering + Shade) + PrepareForDenoise ----
+#pragma omp parallel for schedule(dynamic, 4)
+        for (int32_t y = 0; y < H; y++) {
+            for (int32_t x = 0; x < W; x++) {
+                const int32_t idx = y * W + x;
+                const uint32_t rnd = seeds[(uint32_t)idx % seed_count];
+                PathState st;
+                st.sampler = sampler_for_path(frame, rnd);
+                const float r1 = st.sampler.next();
+                const float r2 = st.sampler.next();
+                Ray ray = camera_sample(*cam, (x + r1) / (float)(cam->width), (y + r2) / (float)(cam->height));
+                st.throughput = V3(1.0f); st.pdfb = 1.0f; st.contrib = V3(0.0f);
+                st.terminated = false; st.singular = false; st.last_specular = false;
+                for (int32_t depth = 0; depth < max_depth; depth++) {
+                    AtnHit isect;
+                    if (!Traverse(s, ray, kInf, &isect, nullptr)) {
+                        shade_miss(s.view, *cam, x, y, W, H, depth, ray, &st, &cur.normal_depth[idx], &cur.albedo_meshid[idx]);
+                        break;
+                    }
+                    ShadowRayOut sh;
+                    Ray next = ray;
+                    shade_hit(s.view, ray, isect.objid, isect.primid, isect.a, isect.b, isect.t, isect.mtrlid, depth, rr_depth,
+                              &st, &sh, &next, &cur.normal_depth[idx], &cur.albedo_meshid[idx], &w2c);
+                    if (!st.terminated && sh.active) {
+                        Ray sr; sr.org = sh.org; sr.dir = normalize(sh.dir);
+                        AtnHit shit;
+                        Traverse(s, sr, sh.dist - kEps, &shit, nullptr);
+                        if (shadow_visible(s.view, s.view.lights[sh.light_id], sr, sh.dist, shit.objid, shit.primid, shit.a, shit.b, shit.t, shit.mtrlid))
+                            st.contrib = st.contrib + sh.lightcontrib;
+                    }
+                    if (st.terminated) break;
+                    ray = next;
+                }
+                AtnVec4 c; c.x = st.contrib.x; c.y = st.contrib.y; c.z = st.contrib.z; c.w = 1.0f;   // one sample
+                contribs[idx] = c;
+                svgf_prepare(frame == 0, idx, c, temporary, cur);
+            }
+        }
+        // ---- temporal reprojection ----
+        if (frame > 0) {
+#pragma omp parallel for schedule(static)
+            for (int32_t y = 0; y < H; y++)
+                for (int32_t x = 0; x < W; x++)
+                    svgf_temporal(x, y, W, H, 0.98f, 0.05f, contribs[y * W + x], cur, prev, motion_depth);
+        }
+        // ---- variance estimation ----
+        if (host_order) {
+            for (int32_t y = 0; y < H; y++)
+                for (int32_t x = 0; x < W; x++)
+                    svgf_variance(x, y, W, H, camera_distance, cur, cur.color_variance, cur.color_variance);
+        }
+        else {
+#pragma omp parallel for schedule(static)
+            for (int32_t y = 0; y < H; y++)
+                for (int32_t x = 0; x < W; x++)
+                    svgf_variance(x, y, W, H, camera_distance, cur, cur.color_variance, scratch.data());
+            memcpy(cur.color_variance, scratch.data(), n * sizeof(AtnVec4));
+        }
+        // ---- a-trous iterations ----
+        for (int32_t i = 0; i < iter_count; i++) {
+            const AtnVec4* src = (i == 0) ? cur.color_variance : atrous[i & 1];
+            AtnVec4* next = atrous[1 - (i & 1)];
+#pragma omp parallel for schedule(static)
+            for (int32_t y = 0; y < H; y++)
+                for (int32_t x = 0; x < W; x++) {
+                    AtnVec4 film;
+                    if (svgf_atrous(i, iter_count, x, y, W, H, camera_distance, cur, src, next, temporary, &film)) image[y * W + x] = film;
+                }
+        }
+        for (size_t i = 0; i < n; i++) svgf_copy((int32_t)i, temporary, cur);
+    }
+    return 0;
+}
+
 int oracle_cmj(uint32_t idx, uint32_t scramble, int32_t n, float* out)
 {
     Sampler s; s.idx = idx; s.dim = 0; s.scramble = scramble;

@@ -27,6 +27,7 @@
 #include "aten.h"
 #include "atenscene.h"
 #include "renderer/pathtracing/pathtracing_impl.h"
+#include "renderer/svgf/svgf.h"
 
 #include "../include/idaten_b200_shim.h"
 
@@ -465,6 +466,16 @@ void Replay(Harness& hs, uint32_t frame, int32_t max_depth, int32_t rr_depth,
     if (cnt) { cnt->closest += n_closest; cnt->shadow += n_shadow; }
 }
 
+// aten::SVGFRenderer takes its motion / depth buffer from a GL frame buffer object
+// (SVGFRenderer::SetMotionDepthBuffer(aten::FBO&), svgf.cpp:451-459).  There is no GL here, so the
+// harness writes the vector the renderer reads -- SVGFParams::motion_depth_buffer inside the private
+// member params_ -- through an explicit-instantiation accessor (access checks do not apply to the
+// arguments of an explicit template instantiation).
+using SvgfParamsT = AT_NAME::SVGFParams<std::vector<aten::vec4>>;
+struct SvgfParamsTag { using type = SvgfParamsT aten::SVGFRenderer::*; friend type GetMember(SvgfParamsTag); };
+template <typename Tag, typename Tag::type M> struct MemberAccess { friend typename Tag::type GetMember(Tag) { return M; } };
+template struct MemberAccess<SvgfParamsTag, &aten::SVGFRenderer::params_>;
+
 double NowMs()
 {
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
@@ -480,6 +491,8 @@ int Usage()
         "  rays   <name> rays.bin hits.bin         (n x {org[3],dir[3],tmax} -> n x AtnHit)\n"
         "  bench  <name> W H frames depth rr threads repeats     (JSON line with timings and ray counts)\n"
         "  ao     <name> W H frame threads out_image.f32            (stock aten::AORenderer, one frame at index `frame`)\n"
+        "  svgf   <name> W H frames depth rr out_prefix [mx my [iters]]  (stock aten::SVGFRenderer on ONE thread, frames 0..frames-1,\n"
+        "         1 sample each; constant motion vector (mx,my) or 0; writes <prefix>.f<k>.f32 per frame and <prefix>.aov.f32)\n"
         "  cmj    out.bin                           (golden CMJ stream)\n");
     return 2;
 }
@@ -595,6 +608,43 @@ int main(int argc, char** argv)
         WriteFile(argv[8], film.image().data(), film.image().size() * sizeof(aten::vec4));
         printf("{\"scene\": \"%s\", \"renderer\": \"ao\", \"w\": %d, \"h\": %d, \"frames\": %d, \"threads\": %d, \"render_ms\": %.3f}\n",
                name.c_str(), W, H, frames, threads, ms);
+        return 0;
+    }
+
+    if (cmd == "svgf") {
+        // stock aten::SVGFRenderer (src/libaten/renderer/svgf/svgf.cpp); one OpenMP thread, because its variance
+        // estimation filters the colour history in place and is order dependent (svgf_impl.h:438-544)
+        if (argc < 10) return Usage();
+        const int W = atoi(argv[4]), H = atoi(argv[5]), frames = atoi(argv[6]), depth = atoi(argv[7]), rr = atoi(argv[8]);
+        const std::string prefix = argv[9];
+        const float mx = argc > 10 ? (float)atof(argv[10]) : 0.0f, my = argc > 11 ? (float)atof(argv[11]) : 0.0f;
+        const int iters = argc > 12 ? atoi(argv[12]) : 5;
+        Harness hs;
+        if (!hs.Build(name, W, H)) return 1;
+        aten::OMPUtil::setThreadNum(1);
+        omp_set_num_threads(1);
+        aten::SVGFRenderer svgf;
+        SvgfParamsT& params = svgf.*GetMember(SvgfParamsTag());
+        params.atrous_iter_cnt = iters;    // public field of SVGFParams (svgf_types.h:74), default 5
+        aten::Film film(W, H);
+        auto dst = hs.MakeDst(&film, depth, rr);
+        double ms = 0;
+        for (int f = 0; f < frames; f++) {
+            params.motion_depth_buffer.assign((size_t)W * H, aten::vec4(mx, my, 0.0f, 0.0f));
+            const double t0 = NowMs();
+            svgf.render(hs.ctxt, dst, &hs.scene, &hs.camera);
+            ms += NowMs() - t0;
+            WriteFile(prefix + ".f" + std::to_string(f) + ".f32", film.image().data(), film.image().size() * sizeof(aten::vec4));
+        }
+        // AOV set of the last frame rendered (the renderer has already toggled to the other set)
+        auto& aov = params.GetPrevAovBuffer();
+        std::vector<aten::vec4> dump;
+        for (auto* b : { &aov.get<AT_NAME::SVGFAovBufferType::NormalDepth>(), &aov.get<AT_NAME::SVGFAovBufferType::AlbedoMeshId>(),
+                         &aov.get<AT_NAME::SVGFAovBufferType::ColorVariance>(), &aov.get<AT_NAME::SVGFAovBufferType::MomentTemporalWeight>() })
+            dump.insert(dump.end(), b->begin(), b->end());
+        WriteFile(prefix + ".aov.f32", dump.data(), dump.size() * sizeof(aten::vec4));
+        printf("{\"scene\": \"%s\", \"renderer\": \"svgf\", \"w\": %d, \"h\": %d, \"frames\": %d, \"threads\": 1, \"render_ms\": %.3f}\n",
+               name.c_str(), W, H, frames, ms);
         return 0;
     }
 

@@ -187,3 +187,42 @@ def pixel_width_at_distance(vfov, width, height, distance):
     fn = lib().oracle_pixel_width_at_distance
     fn.restype = C.c_float
     return float(fn(C.c_float(vfov), C.c_int32(width), C.c_int32(height), C.c_float(distance)))
+
+
+# ---- N1: SVGF -------------------------------------------------------------------------------
+SVGF_STATE_PLANES = 11    # aov[0] x4, aov[1] x4, a-trous ping / pong, temporary colour
+
+
+def render_svgf(scene: sio.Scene, frames=1, max_depth=5, rr_depth=3, motion=None, host_order=False, state=None, first_frame=0, iters=5):
+    """CPU restatement of aten::SVGFRenderer, frames first_frame .. first_frame+frames-1 (1 sample each).
+    Returns (film image of the last frame [H,W,4], state [11,H*W,4]); pass `state` back in to continue."""
+    W, H = scene.width, scene.height
+    n = W * H
+    st = np.zeros((SVGF_STATE_PLANES, n, 4), np.float32) if state is None else np.ascontiguousarray(state, np.float32)
+    img = np.zeros((n, 4), np.float32)
+    seeds = scene.seeds_for(n)
+    md = None if motion is None else np.ascontiguousarray(motion, np.float32).reshape(n, 4)
+    blob = scene.blob()
+    cam = np.ascontiguousarray(scene.camera)
+    rc = lib().oracle_render_svgf(C.byref(blob), C.c_void_p(cam.ctypes.data), C.c_void_p(seeds.ctypes.data), C.c_uint32(len(seeds)),
+                                  C.c_int32(W), C.c_int32(H), C.c_uint32(first_frame), C.c_int32(frames), C.c_int32(max_depth),
+                                  C.c_int32(rr_depth), C.c_void_p(md.ctypes.data) if md is not None else None,
+                                  C.c_int32(1 if host_order else 0), C.c_int32(iters), C.c_void_p(st.ctypes.data), C.c_void_p(img.ctypes.data))
+    assert rc == 0
+    return img.reshape(H, W, 4), st
+
+
+def svgf_last_aov(state, frames_rendered):
+    """The AOV set [4, n, 4] (normal_depth, albedo_meshid, color_variance, moment_tw) of the last frame rendered."""
+    k = (frames_rendered - 1) & 1
+    return state[k * 4:(k + 1) * 4]
+
+
+def ref_render_svgf(name, W, H, frames=1, depth=5, rr=3, motion=(0.0, 0.0), iters=5):
+    """Stock aten::SVGFRenderer on one thread: ([frames] film images [H,W,4], AOV set of the last frame [4,H*W,4])."""
+    with tempfile.TemporaryDirectory() as d:
+        prefix = os.path.join(d, "svgf")
+        ref_run("svgf", name, W, H, frames, depth, rr, prefix, motion[0], motion[1], iters)
+        imgs = [np.fromfile(f"{prefix}.f{k}.f32", np.float32).reshape(H, W, 4) for k in range(frames)]
+        aov = np.fromfile(f"{prefix}.aov.f32", np.float32).reshape(4, H * W, 4)
+    return imgs, aov

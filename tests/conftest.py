@@ -71,6 +71,15 @@ class Golden:
         rays["dir"] = buf[:, 3:6]
         return rays, buf[:, 6].copy()
 
+    def svgf(self, name, frames=3):
+        """Stock aten::SVGFRenderer: ([frames, H, W, 4] film images, [4, H*W, 4] AOV set of the last frame, motion)."""
+        m = self.meta[name]
+        n = m["w"] * m["h"]
+        buf = np.frombuffer(_gz(f"{name}.svgf.f32.gz"), np.float32)
+        imgs = buf[:frames * n * 4].reshape(frames, m["h"], m["w"], 4)
+        aov = buf[frames * n * 4:].reshape(4, n, 4)
+        return imgs, aov, (0.02, -0.03)
+
     def hits(self, name):
         return np.frombuffer(_gz(f"{name}.hits.gz"), self.sio.HIT_DTYPE)
 

@@ -62,9 +62,26 @@ def random_rays(scene: sio.Scene, n: int, seed: int) -> tuple:
     return rays, tmax
 
 
+SVGF_SCENES = ("cornell_mtrl", "instanced", "sponza_atrium")
+SVGF_FRAMES = 3
+SVGF_MOTION = (0.02, -0.03)     # constant motion vector fed to frames > 0 (screen fractions)
+
+
+def make_svgf():
+    """Film images of frames 0..2 and the AOV set of frame 2 from the stock aten::SVGFRenderer (one thread)."""
+    for name in SVGF_SCENES:
+        W, H = SCENES[name]
+        imgs, aov = ol.ref_render_svgf(name, W, H, frames=SVGF_FRAMES, motion=SVGF_MOTION)
+        gz_write(os.path.join(HERE, f"{name}.svgf.f32.gz"), np.stack(imgs).tobytes() + aov.tobytes())
+        print(name, "svgf", [float(i[..., :3].mean()) for i in imgs])
+
+
 def main():
     if not ol.have_ref():
         sys.exit("oracle/_ref is not built: run python oracle/build_ref.py")
+    if len(sys.argv) > 1 and sys.argv[1] == "svgf":     # only the SVGF fixtures (the others are unchanged)
+        make_svgf()
+        return
     meta = {}
     with tempfile.TemporaryDirectory() as d:
         p = os.path.join(d, "cmj.bin")
@@ -93,6 +110,7 @@ def main():
                       "hit_fraction": float((hits["objid"] >= 0).mean())}
         print(name, meta[name])
     json.dump(meta, open(os.path.join(HERE, "meta.json"), "w"), indent=1, sort_keys=True)
+    make_svgf()
 
 
 if __name__ == "__main__":

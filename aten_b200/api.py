@@ -24,6 +24,7 @@ EXPORTS = [
     "atn_render", "atn_render_region", "atn_synchronize", "atn_readback", "atn_device_image", "atn_get_stats",
     "atn_set_profiling", "atn_get_stream", "atn_trace_closest", "atn_trace_any", "atn_trace_closest_device",
     "atn_trace_any_device", "atn_set_bounce_tap", "atn_trace_closest_static", "atn_readback_aov", "atn_render_ao",
+    "atn_render_svgf", "atn_set_motion_depth", "atn_readback_svgf",
 ]
 
 
@@ -171,6 +172,27 @@ class PathTracing:
         num_rays = 1 and radius = 1."""
         _check(self._lib, self._lib.atn_render_ao(self._h, C.c_int32(width), C.c_int32(height), C.c_int32(maxSamples),
                                                   C.c_int32(num_rays), C.c_float(radius)))
+
+    def render_svgf(self, width: int, height: int, maxBounce: int, rrBounce: int = 3, atrous_iters: int = 5):
+        """One frame of idaten::SVGFPathTracing::render (reference src/libidaten/svgf/svgf.cpp:28-160): 1 sample per
+        pixel + temporal reprojection + variance estimation + a-trous filter.  Frame 0 starts a sequence."""
+        _check(self._lib, self._lib.atn_render_svgf(self._h, C.c_int32(width), C.c_int32(height), C.c_int32(maxBounce),
+                                                    C.c_int32(rrBounce), C.c_int32(atrous_iters)))
+
+    def set_motion_depth(self, motion: np.ndarray | None):
+        """SetMotionDepthBuffer without the GL frame buffer: float32 [h*w, 4] motion vectors in .xy, or None."""
+        if motion is None:
+            _check(self._lib, self._lib.atn_set_motion_depth(self._h, None, C.c_size_t(0)))
+            return
+        m = np.ascontiguousarray(motion, np.float32).reshape(-1, 4)
+        _check(self._lib, self._lib.atn_set_motion_depth(self._h, C.c_void_p(m.ctypes.data), C.c_size_t(len(m))))
+
+    def readback_svgf(self):
+        """float32 [4, h*w, 4]: normal_depth, albedo_meshid, color_variance, moment_temporalweight of the last frame."""
+        n = self.width * self.height
+        out = np.empty((4, n, 4), np.float32)
+        _check(self._lib, self._lib.atn_readback_svgf(self._h, *[C.c_void_p(out[k].ctypes.data) for k in range(4)], C.c_size_t(n)))
+        return out
 
     def render_region(self, width, height, x0, y0, x1, y1, sample_begin, sample_end, maxBounce, rrBounce=3):
         _check(self._lib, self._lib.atn_render_region(

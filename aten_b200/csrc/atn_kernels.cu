@@ -36,6 +36,7 @@
 #include <algorithm>
 
 #include "atn_math.cuh"
+#include "atn_svgf.cuh"
 #include "atn_bvh.h"
 
 using namespace atn;
@@ -725,10 +726,12 @@ __device__ __forceinline__ Sampler path_sampler(const FrameParams& fp, const uin
 //
 // Stage 1, all traced paths of the bounce: ShadeMiss for misses (pt_standard_impl.cu:330-362),
 // hit evaluation + material + implicit light for hits.  Survivors go to q_lit with a Surface record.
-template <bool kTap>
+// kSvgf: aten::SVGFRenderer::Shade instead of PathTracing::shade (see shade_surface); `w2c` is then the
+// world-to-clip matrix of the frame and pb.aov_nd / pb.aov_am point at the current SVGF AOV set.
+template <bool kTap, bool kSvgf>
 __global__ void __launch_bounds__(kShadeBlock, ATN_SURFACE_MIN_BLOCKS)
 k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, Counters* cnt, int bounce,
-          AtnBounceRecord* tap, int tap_cap)
+          AtnBounceRecord* tap, int tap_cap, AtnMat4 w2c)
 {
     const int count = cnt->n_active[bounce];
     const int32_t* __restrict__ q_in = (bounce == 0) ? nullptr : pb.queue[bounce & 1];
@@ -752,6 +755,7 @@ k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, 
             st.contrib = V3(cb.x, cb.y, cb.z);
             st.terminated = false;
             st.singular = (fl & 2u) != 0u;
+            st.last_specular = (fl & 4u) != 0u;
             // AOVs of the first hit are kept per pixel (the reference indexes them by pixel too)
             const int pix = (fp.y0 + slot / fp.rw) * fp.width + (fp.x0 + slot % fp.rw);
             AtnVec4* aov_nd = (bounce <= 1) ? reinterpret_cast<AtnVec4*>(pb.aov_nd) + pix : nullptr;
@@ -759,7 +763,7 @@ k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, 
             if (h1.x >= 0) {
                 Surface sf;
                 lit = shade_surface(sc, ray, h1.x, __float_as_int(h0.w), h0.y, h0.z, h0.x, h1.y, bounce, &st, &sf,
-                                    aov_nd, aov_am, bounce == 0 ? pb.hit_mesh[slot] : -1);
+                                    aov_nd, aov_am, bounce == 0 ? pb.hit_mesh[slot] : -1, kSvgf ? &w2c : nullptr);
                 if (lit) {
                     pb.surf0[slot] = make_float4(sf.p.x, sf.p.y, sf.p.z, sf.u);
                     pb.surf1[slot] = make_float4(sf.n.x, sf.n.y, sf.n.z, sf.v);
@@ -859,7 +863,7 @@ k_bsdf(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuf
             shadow = !st.terminated && pb.sh_o[slot].w >= 0.0f;
             pb.throughput[slot] = make_float4(st.throughput.x, st.throughput.y, st.throughput.z, st.pdfb);
             pb.sampler_dim[slot] = st.sampler.dim;
-            pb.flags[slot] = (st.terminated ? 1u : 0u) | (st.singular ? 2u : 0u);
+            pb.flags[slot] = (st.terminated ? 1u : 0u) | (st.singular ? 2u : 0u) | (st.last_specular ? 4u : 0u);
             if (cont) {
                 pb.ray_o[slot] = make_float4(next.org.x, next.org.y, next.org.z, 0.0f);
                 pb.ray_d[slot] = make_float4(next.dir.x, next.dir.y, next.dir.z, 0.0f);
@@ -971,6 +975,80 @@ k_ao_accum(SceneView sc, PathBuffers pb, Counters* cnt, float radius, int last, 
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// N1: SVGF renderer on the same path (idaten::SVGFPathTracing, src/libidaten/svgf/svgf.cpp:28-160 and
+// svgf_*.cu; host twin aten::SVGFRenderer, src/libaten/renderer/svgf/svgf.cpp).  The path-tracing half is
+// the pipeline above with k_surface<.., true>; the image-space half is the five kernels below, one per
+// pass of the reference (per-pixel functions in atn_svgf.cuh).  All of them are streaming stencils over
+// W*H float4 planes: HBM / L2 bound.
+// ---------------------------------------------------------------------------------------------
+struct SvgfView {
+    SvgfAov cur, prev;
+    AtnVec4* atrous[2];
+    AtnVec4* temporary;
+    AtnVec4* scratch;             // variance estimation writes here (order-independent form), then becomes cur.color_variance
+    const AtnVec4* motion_depth;  // or nullptr: static camera
+};
+
+// PrepareForDenoise; also folds the frame's queue counters into Totals (k_gather does that on the PT path)
+__global__ void k_svgf_prepare(FrameParams fp, PathBuffers pb, SvgfView sv, int first_frame, const Counters* cnt, Totals* totals)
+{
+    const int n = fp.width * fp.height;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        unsigned long long c = 0, s = 0;
+        for (int b = 0; b < fp.max_bounce; b++) { c += (unsigned long long)cnt->n_active[b]; s += (unsigned long long)cnt->n_shadow[b]; }
+        totals->closest += c; totals->shadow += s;
+    }
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 c = pb.contrib[i];
+        AtnVec4 cc; cc.x = c.x; cc.y = c.y; cc.z = c.z; cc.w = c.w;
+        svgf_prepare(first_frame != 0, i, cc, sv.temporary, sv.cur);
+    }
+}
+
+__global__ void k_svgf_temporal(FrameParams fp, PathBuffers pb, SvgfView sv)
+{
+    const int n = fp.width * fp.height;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 c = pb.contrib[i];
+        AtnVec4 cc; cc.x = c.x; cc.y = c.y; cc.z = c.z; cc.w = c.w;
+        svgf_temporal(i % fp.width, i / fp.width, fp.width, fp.height, 0.98f, 0.05f, cc, sv.cur, sv.prev, sv.motion_depth);
+    }
+}
+
+__global__ void k_svgf_variance(FrameParams fp, SvgfView sv, float camera_distance)
+{
+    const int n = fp.width * fp.height;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        svgf_variance(i % fp.width, i / fp.width, fp.width, fp.height, camera_distance, sv.cur, sv.cur.color_variance, sv.scratch);
+}
+
+__global__ void k_svgf_atrous(FrameParams fp, SvgfView sv, float camera_distance, int iter, int iter_count, float4* image)
+{
+    const int n = fp.width * fp.height;
+    // (selects, not sv.atrous[iter & 1]: a dynamic index would push the whole parameter struct to local memory)
+    const AtnVec4* src = (iter == 0) ? sv.cur.color_variance : ((iter & 1) ? sv.atrous[1] : sv.atrous[0]);
+    AtnVec4* next = (iter & 1) ? sv.atrous[0] : sv.atrous[1];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        AtnVec4 film;
+        if (svgf_atrous(iter, iter_count, i % fp.width, i / fp.width, fp.width, fp.height, camera_distance, sv.cur, src, next,
+                        sv.temporary, &film))
+            image[i] = make_float4(film.x, film.y, film.z, film.w);
+    }
+}
+
+__global__ void k_svgf_copy(FrameParams fp, SvgfView sv)
+{
+    const int n = fp.width * fp.height;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) svgf_copy(i, sv.temporary, sv.cur);
+}
+
+// fills planes with aten::vec4's default value (0, 0, 0, 1): what the reference's buffers hold before frame 0
+__global__ void k_fill_vec4(float4* p, size_t n, float4 v)
+{
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
+}
+
 // pt::gather (pathtracing_impl.cu:282-324) / FilmProgressive::put (film.cpp:61-71)
 __global__ void k_gather(FrameParams fp, PathBuffers pb, float4* image, int progressive, const Counters* cnt, Totals* totals)
 {
@@ -1078,6 +1156,14 @@ struct AtnRenderer {
     DevBuf<AtnHit> q_hits;
     DevBuf<uint8_t> q_vis;
 
+    // SVGF (N1): 12 planes of W*H float4 -- AOV sets 0 and 1 (normal_depth, albedo_meshid, color_variance, moment_tw),
+    // a-trous ping / pong, temporary colour, variance scratch -- and the caller's motion vectors
+    DevBuf<float4> svgf_planes, svgf_motion;
+    int svgf_cv_plane[2]{ 2, 6 };      // which plane holds color_variance of each AOV set (swaps with the scratch plane)
+    int svgf_scratch_plane{ 11 };
+    bool svgf_has_motion{ false };
+    size_t svgf_pixels{ 0 };
+
     // tap
     AtnBounceRecord* tap_host{ nullptr };
     int tap_cap{ 0 };
@@ -1174,7 +1260,7 @@ ATN_API int atn_create(int device_ordinal, AtnRenderer** out)
     int bps = 0;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace<ClosestPolicy>, kTraceBlock, 0));
     r->trace_grid = r->sm_count * std::max(1, bps);
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_surface<false>, kShadeBlock, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_surface<false, false>, kShadeBlock, 0));
     r->surface_grid = r->sm_count * std::max(1, bps);
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_nee, kShadeBlock, 0));
     r->nee_grid = r->sm_count * std::max(1, bps);
@@ -1377,6 +1463,45 @@ ATN_API int atn_synchronize(AtnRenderer* r)
     return ATN_OK;
 }
 
+// The bounce loop of one camera sample: closest hit, the three shade stages, shadow rays.
+// `svgf_w2c` != nullptr: the SVGF shade variant (pb.aov_nd / pb.aov_am then point at the SVGF AOV set).
+static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffers& pb, bool tap_now, const AtnMat4* svgf_w2c,
+                          size_t* ev_i, uint64_t* launches)
+{
+    cudaStream_t s = r->stream;
+    AtnMat4 w2c;
+    for (int i = 0; i < 16; i++) w2c.m[i] = svgf_w2c ? svgf_w2c->m[i] : 0.0f;
+    for (int b = 0; b < fp.max_bounce; b++) {
+        Counters* c = r->counters.p;
+        const int32_t* q = (b == 0) ? nullptr : pb.queue[b & 1];
+        const float tmax = (b == 0) ? kInf : r->hit_distance_limit;
+        if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
+        {
+            ClosestPolicy pol{ pb, q, tmax, b == 0 ? pb.hit_mesh : nullptr };
+            k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[b], 0, &c->fetch_closest[b], r->visits.p);
+        }
+        if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
+        if (svgf_w2c) k_surface<false, true><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, pb, c, b, nullptr, 0, w2c);
+        else if (tap_now) k_surface<true, false><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, pb, c, b, r->tap_dev.p, r->tap_cap, w2c);
+        else k_surface<false, false><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, pb, c, b, nullptr, 0, w2c);
+        k_nee<<<r->nee_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, b);
+        if (tap_now) k_bsdf<true><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, b, r->tap_dev.p, r->tap_cap);
+        else k_bsdf<false><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, b, nullptr, 0);
+        if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
+        if (tap_now) {
+            ShadowPolicy<true> pol{ pb, r->sv, r->tap_dev.p, r->tap_cap, b };
+            k_trace<ShadowPolicy<true>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
+        }
+        else {
+            ShadowPolicy<false> pol{ pb, r->sv, nullptr, 0, b };
+            k_trace<ShadowPolicy<false>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
+        }
+        if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
+        *launches += 5;
+    }
+    return ATN_OK;
+}
+
 ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int32_t x0, int32_t y0, int32_t x1, int32_t y1,
                               int32_t sample_begin, int32_t sample_end, int32_t max_bounce, int32_t rr_bounce)
 {
@@ -1417,33 +1542,8 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
         k_generate<<<gen_grid, 256, 0, s>>>(fp, r->camera, r->seeds.p, r->pb, r->counters.p);
         launches++;
         const bool tap_now = tap && smp == sample_end - 1;
-        for (int b = 0; b < max_bounce; b++) {
-            Counters* c = r->counters.p;
-            const int32_t* q = (b == 0) ? nullptr : r->pb.queue[b & 1];
-            const float tmax = (b == 0) ? kInf : r->hit_distance_limit;
-            if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
-            {
-                ClosestPolicy pol{ r->pb, q, tmax, b == 0 ? r->pb.hit_mesh : nullptr };
-                k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[b], 0, &c->fetch_closest[b], r->visits.p);
-            }
-            if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
-            if (tap_now) k_surface<true><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, r->pb, c, b, r->tap_dev.p, r->tap_cap);
-            else k_surface<false><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, r->pb, c, b, nullptr, 0);
-            k_nee<<<r->nee_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, r->pb, c, b);
-            if (tap_now) k_bsdf<true><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, r->pb, c, b, r->tap_dev.p, r->tap_cap);
-            else k_bsdf<false><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, r->pb, c, b, nullptr, 0);
-            if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
-            if (tap_now) {
-                ShadowPolicy<true> pol{ r->pb, r->sv, r->tap_dev.p, r->tap_cap, b };
-                k_trace<ShadowPolicy<true>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
-            }
-            else {
-                ShadowPolicy<false> pol{ r->pb, r->sv, nullptr, 0, b };
-                k_trace<ShadowPolicy<false>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
-            }
-            if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[ev_i++], s));
-            launches += 5;
-        }
+        const int rc = launch_bounces(r, fp, r->pb, tap_now, nullptr, &ev_i, &launches);
+        if (rc != ATN_OK) return rc;
         k_gather<<<gen_grid, 256, 0, s>>>(fp, r->pb, r->image.p, r->progressive, r->counters.p, r->totals.p);
         launches++;
     }
@@ -1540,6 +1640,143 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
     CUDA_TRY(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
     r->stats.device_ms = ms; r->stats.trace_ms = 0.0f;
     r->frame += (uint32_t)spp;
+    return ATN_OK;
+}
+
+// ---- N1: SVGF ----------------------------------------------------------------------------------
+static SvgfAov svgf_aov_of(AtnRenderer* r, int k)
+{
+    AtnVec4* base = reinterpret_cast<AtnVec4*>(r->svgf_planes.p);
+    const size_t n = r->svgf_pixels;
+    SvgfAov a;
+    a.normal_depth = base + (size_t)(k * 4 + 0) * n; a.albedo_meshid = base + (size_t)(k * 4 + 1) * n;
+    a.color_variance = base + (size_t)r->svgf_cv_plane[k] * n; a.moment_tw = base + (size_t)(k * 4 + 3) * n;
+    return a;
+}
+
+ATN_API int atn_set_motion_depth(AtnRenderer* r, const AtnVec4* motion_depth, size_t pixel_count)
+{
+    if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_set_motion_depth: NULL handle");
+    if (!motion_depth) { r->svgf_has_motion = false; return ATN_OK; }
+    if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_set_motion_depth: no scene uploaded");
+    if (pixel_count != (size_t)r->width * r->height) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_set_motion_depth: pixel_count mismatch");
+    CUDA_TRY(cudaSetDevice(r->device));
+    CUDA_TRY(r->svgf_motion.upload(reinterpret_cast<const float4*>(motion_depth), pixel_count, r->stream));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
+    r->svgf_has_motion = true;
+    return ATN_OK;
+}
+
+ATN_API int atn_render_svgf(AtnRenderer* r, int32_t width, int32_t height, int32_t max_bounce, int32_t rr_bounce, int32_t atrous_iters)
+{
+    if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_svgf: NULL handle");
+    if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_render_svgf: no scene uploaded");
+    if (width != r->width || height != r->height)
+        return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_svgf: size %dx%d differs from the uploaded %dx%d", width, height, r->width, r->height);
+    if (max_bounce < 1 || max_bounce > kMaxBounce) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_svgf: max_bounce %d not in [1,%d]", max_bounce, kMaxBounce);
+    if (atrous_iters <= 0) atrous_iters = 5;                      // SVGFParams::atrous_iter_cnt, svgf_types.h:74
+    if (atrous_iters > 16) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_svgf: atrous_iters %d > 16", atrous_iters);
+    if (rr_bounce > max_bounce) rr_bounce = max_bounce - 1;       // svgf.cpp:432-434
+    if (r->tap_host) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_svgf: the bounce tap is not available on this renderer");
+    CUDA_TRY(cudaSetDevice(r->device));
+    cudaStream_t s = r->stream;
+    const size_t n = (size_t)width * height;
+    const int grid = (int)std::min<size_t>((n + 255) / 256, (size_t)r->sm_count * 8);
+
+    const bool first_frame = r->frame == 0;
+    if (r->svgf_pixels != n || !r->svgf_planes.p) {
+        CUDA_TRY(r->svgf_planes.resize(12 * n));
+        r->svgf_pixels = n;
+        if (!first_frame) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_svgf: no history for frame %u (start at frame 0: atn_set_frame(0))", r->frame);
+    }
+    if (first_frame) {
+        r->svgf_cv_plane[0] = 2; r->svgf_cv_plane[1] = 6; r->svgf_scratch_plane = 11;
+        k_fill_vec4<<<r->sm_count * 8, 256, 0, s>>>(r->svgf_planes.p, 12 * n, make_float4(0.0f, 0.0f, 0.0f, 1.0f));
+    }
+    if (r->svgf_has_motion && r->svgf_motion.n < n) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_svgf: motion buffer smaller than the image");
+
+    FrameParams fp;
+    fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height;
+    fp.max_bounce = max_bounce; fp.rr_bounce = rr_bounce; fp.seed_count = r->seed_count;
+    fp.frame = r->frame;
+    const int cur_k = (int)(r->frame & 1u);
+    AtnVec4* base = reinterpret_cast<AtnVec4*>(r->svgf_planes.p);
+    SvgfView sv;
+    sv.cur = svgf_aov_of(r, cur_k); sv.prev = svgf_aov_of(r, 1 - cur_k);
+    sv.atrous[0] = base + 8 * n; sv.atrous[1] = base + 9 * n; sv.temporary = base + 10 * n;
+    sv.scratch = base + (size_t)r->svgf_scratch_plane * n;
+    sv.motion_depth = r->svgf_has_motion ? reinterpret_cast<const AtnVec4*>(r->svgf_motion.p) : nullptr;
+    PathBuffers pb = r->pb;
+    pb.aov_nd = reinterpret_cast<float4*>(sv.cur.normal_depth);
+    pb.aov_am = reinterpret_cast<float4*>(sv.cur.albedo_meshid);
+    const AtnMat4 w2c = camera_w2c(r->camera);
+    const float camera_distance = screen_distance(r->camera, height);
+
+    const size_t n_ev = r->profiling ? (size_t)max_bounce * 4 : 0;
+    while (r->trace_events.size() < n_ev) { cudaEvent_t ev; CUDA_TRY(cudaEventCreate(&ev)); r->trace_events.push_back(ev); }
+    size_t ev_i = 0;
+    uint64_t launches = 0;
+    CUDA_TRY(cudaMemsetAsync(r->totals.p, 0, sizeof(Totals), s));
+    CUDA_TRY(cudaMemsetAsync(r->visits.p, 0, sizeof(Visits), s));
+    CUDA_TRY(cudaEventRecord(r->ev0, s));
+    CUDA_TRY(cudaMemsetAsync(r->counters.p, 0, sizeof(Counters), s));
+    k_generate<<<grid, 256, 0, s>>>(fp, r->camera, r->seeds.p, pb, r->counters.p);
+    launches++;
+    const int rc = launch_bounces(r, fp, pb, false, &w2c, &ev_i, &launches);
+    if (rc != ATN_OK) return rc;
+    k_svgf_prepare<<<grid, 256, 0, s>>>(fp, pb, sv, first_frame ? 1 : 0, r->counters.p, r->totals.p);
+    if (!first_frame) { k_svgf_temporal<<<grid, 256, 0, s>>>(fp, pb, sv); launches++; }
+    k_svgf_variance<<<grid, 256, 0, s>>>(fp, sv, camera_distance);
+    // the variance pass wrote the filtered colour history to the scratch plane: that plane is the AOV set's from here on
+    std::swap(r->svgf_cv_plane[cur_k], r->svgf_scratch_plane);
+    sv.cur = svgf_aov_of(r, cur_k);
+    sv.scratch = base + (size_t)r->svgf_scratch_plane * n;
+    for (int i = 0; i < atrous_iters; i++)
+        k_svgf_atrous<<<grid, 256, 0, s>>>(fp, sv, camera_distance, i, atrous_iters, r->image.p);
+    k_svgf_copy<<<grid, 256, 0, s>>>(fp, sv);
+    launches += 3 + (uint64_t)atrous_iters;
+    CUDA_TRY(cudaEventRecord(r->ev1, s));
+    CUDA_TRY(cudaGetLastError());
+
+    Totals ht; Visits hv;
+    CUDA_TRY(cudaMemcpyAsync(&ht, r->totals.p, sizeof(Totals), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaMemcpyAsync(&hv, r->visits.p, sizeof(Visits), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    r->stats.closest_rays = ht.closest; r->stats.shadow_rays = ht.shadow;
+    r->stats.nodes_visited = hv.nodes; r->stats.tris_tested = hv.tris;
+    r->stats.camera_samples = (uint64_t)n;
+    r->stats.kernel_launches = launches;
+    float ms = 0.0f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
+    r->stats.device_ms = ms;
+    r->stats.trace_ms = 0.0f;
+    if (r->profiling) {
+        float tot = 0.0f;
+        for (size_t i = 0; i + 3 < ev_i; i += 4) {
+            float a = 0.0f, b2 = 0.0f;
+            cudaEventElapsedTime(&a, r->trace_events[i], r->trace_events[i + 1]);
+            cudaEventElapsedTime(&b2, r->trace_events[i + 2], r->trace_events[i + 3]);
+            tot += a + b2;
+        }
+        r->stats.trace_ms = tot;
+    }
+    r->frame += 1u;
+    return ATN_OK;
+}
+
+ATN_API int atn_readback_svgf(AtnRenderer* r, AtnVec4* normal_depth, AtnVec4* albedo_meshid, AtnVec4* color_variance,
+                              AtnVec4* moment_temporalweight, size_t pixel_count)
+{
+    if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_readback_svgf: NULL handle");
+    if (!r->svgf_planes.p || r->frame == 0) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_readback_svgf: no SVGF frame rendered");
+    if (pixel_count != r->svgf_pixels) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_readback_svgf: pixel_count mismatch");
+    CUDA_TRY(cudaSetDevice(r->device));
+    const SvgfAov a = svgf_aov_of(r, (int)((r->frame - 1u) & 1u));      // the set of the last frame rendered
+    const AtnVec4* src[4] = { a.normal_depth, a.albedo_meshid, a.color_variance, a.moment_tw };
+    AtnVec4* dst[4] = { normal_depth, albedo_meshid, color_variance, moment_temporalweight };
+    for (int k = 0; k < 4; k++)
+        if (dst[k]) CUDA_TRY(cudaMemcpyAsync(dst[k], src[k], pixel_count * sizeof(AtnVec4), cudaMemcpyDeviceToHost, r->stream));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
     return ATN_OK;
 }
 

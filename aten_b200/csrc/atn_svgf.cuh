@@ -1,5 +1,5 @@
 // atn_svgf.cuh -- the image-space half of the SVGF renderer (N1), one text for the sm_100a kernels
-// (atn_kernels.cu) and for the CPU restatement (oracle/pt_oracle.cpp).
+// (atn_kernels.cu) and for the CPU restatement under oracle/, which compiles this header with g++.
 //
 // Reference: aten::SVGFRenderer (src/libaten/renderer/svgf/svgf.cpp:248-639) and the per-pixel functions
 // it shares with the device renderer idaten::SVGFPathTracing (src/libaten/renderer/svgf/svgf_impl.h).
@@ -14,6 +14,12 @@
 #pragma once
 
 #include "atn_math.cuh"
+
+#ifdef __CUDACC__
+#define ATN_UNROLL _Pragma("unroll")
+#else
+#define ATN_UNROLL
+#endif
 
 namespace atn {
 
@@ -259,10 +265,12 @@ ATN_HD bool svgf_atrous(int32_t iter, int32_t iter_count, int32_t ix, int32_t iy
     // 3x3 Gauss filter of the variance channel (svgf_impl.h:546-603)
     float gauss = 0;
     {
-        const float kernel[9] = { 1.0f / 16.0f, 1.0f / 8.0f, 1.0f / 16.0f, 1.0f / 8.0f, 1.0f / 4.0f, 1.0f / 8.0f,
+        static constexpr float kernel[9] = { 1.0f / 16.0f, 1.0f / 8.0f, 1.0f / 16.0f, 1.0f / 8.0f, 1.0f / 4.0f, 1.0f / 8.0f,
                                   1.0f / 16.0f, 1.0f / 8.0f, 1.0f / 16.0f };
         int pos = 0;
+        ATN_UNROLL
         for (int32_t oy = -1; oy <= 1; oy++)
+            ATN_UNROLL
             for (int32_t ox = -1; ox <= 1; ox++) {
                 const int32_t xx = svgf_clampi(ix + ox, 0, width - 1);
                 const int32_t yy = svgf_clampi(iy + oy, 0, height - 1);
@@ -272,11 +280,11 @@ ATN_HD bool svgf_atrous(int32_t iter, int32_t iter_count, int32_t ix, int32_t iy
 
     // ExecAtrousWaveletFilter (svgf_impl.h:665-779)
     const float sigmaZ = 1.0f, sigmaN = 128.0f, sigmaL = 4.0f;
-    const float h[24] = { 2.0f / 3.0f, 2.0f / 3.0f, 2.0f / 3.0f, 2.0f / 3.0f, 1.0f / 6.0f, 1.0f / 6.0f, 1.0f / 6.0f, 1.0f / 6.0f,
+    static constexpr float h[24] = { 2.0f / 3.0f, 2.0f / 3.0f, 2.0f / 3.0f, 2.0f / 3.0f, 1.0f / 6.0f, 1.0f / 6.0f, 1.0f / 6.0f, 1.0f / 6.0f,
                           4.0f / 9.0f, 4.0f / 9.0f, 4.0f / 9.0f, 4.0f / 9.0f, 1.0f / 9.0f, 1.0f / 9.0f, 1.0f / 9.0f, 1.0f / 9.0f,
                           1.0f / 9.0f, 1.0f / 9.0f, 1.0f / 9.0f, 1.0f / 9.0f, 1.0f / 36.0f, 1.0f / 36.0f, 1.0f / 36.0f, 1.0f / 36.0f };
-    const int8_t offx[24] = { 1, 0, -1, 0, 2, 0, -2, 0, 1, -1, -1, 1, 1, -1, -1, 1, 2, -2, -2, 2, 2, -2, -2, 2 };
-    const int8_t offy[24] = { 0, 1, 0, -1, 0, 2, 0, -2, 1, 1, -1, -1, 2, 2, -2, -2, 1, 1, -1, -1, 2, 2, -2, -2 };
+    static constexpr int8_t offx[24] = { 1, 0, -1, 0, 2, 0, -2, 0, 1, -1, -1, 1, 1, -1, -1, 1, 2, -2, -2, 2, 2, -2, -2, 2 };
+    static constexpr int8_t offy[24] = { 0, 1, 0, -1, 0, 2, 0, -2, 1, 1, -1, -1, 2, 2, -2, -2, 1, 1, -1, -1, 2, 2, -2, -2 };
     const int32_t step_scale = 1 << iter;
     const float sqrt_gauss = sqrtf(gauss);
     const float center_lum = luminance(center_color.x, center_color.y, center_color.z);
@@ -284,6 +292,7 @@ ATN_HD bool svgf_atrous(int32_t iter, int32_t iter_count, int32_t ix, int32_t iy
     float sumV = center_color.w;
     float weight = 1.0f;
     const float pixel_distance_ratio = (center_depth / camera_distance) * height;
+    ATN_UNROLL
     for (int i = 0; i < 24; i++) {
         const int32_t sox = offx[i] * step_scale, soy = offy[i] * step_scale;
         const int32_t xx = svgf_clampi(ix + sox, 0, width - 1);

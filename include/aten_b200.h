@@ -263,6 +263,28 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height,
  * rgb.  The reference hard-codes num_rays = 1, radius = 1.  A primary miss stores 1.0 (GPU kernel
  * semantics, ao.cu:27-33).  Advances the frame counter by spp; accumulates like atn_render. */
 ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t spp, int32_t num_rays, float radius);
+/* Row N1 of SURVEY 8f, second renderer on the path: SVGF (spatiotemporal variance-guided filtering).
+ * idaten::SVGFPathTracing::render (src/libidaten/svgf/svgf.cpp:28-160; kernels svgf_pt.cu, svgf_tp.cu,
+ * svgf_VarianceEstimation.cu, svgf_atrous.cu) / aten::SVGFRenderer::OnRender (src/libaten/renderer/svgf/svgf.cpp:461-639,
+ * per-pixel functions svgf_impl.h).  ONE frame per call: one path-traced sample per pixel with the SVGF shade
+ * (albedo of the first hit separated, AOVs = geometric normal, clip-space depth, material id), then
+ * PrepareForDenoise, temporal reprojection against the previous frame's AOV set (frames > 0), variance
+ * estimation, `atrous_iters` a-trous iterations (<= 0: the reference's 5) and the copy into the colour
+ * history.  The frame with counter 0 has no history (atn_set_frame(0) / a fresh upload starts a sequence);
+ * the counter advances by 1.  The image (atn_readback / atn_device_image) holds the filtered colour with the
+ * albedo put back, .w as the reference leaves it (material id x variance).
+ * Variance estimation: the reference filters the colour history in place while neighbours read it
+ * (svgf_impl.h:438-544), so its result depends on the pixel order; this entry point computes the
+ * order-independent form (every pixel reads the unfiltered colours) -- DESIGN.md "SVGF". */
+ATN_API int atn_render_svgf(AtnRenderer* r, int32_t width, int32_t height, int32_t max_bounce, int32_t rr_bounce, int32_t atrous_iters);
+/* Replaces SVGFPathTracing::SetMotionDepthBuffer / SVGFRenderer::SetMotionDepthBuffer(aten::FBO&) (svgf.cpp:451-459),
+ * which read a GL frame buffer: W*H motion vectors in .xy (fractions of the screen, added to the pixel position to
+ * find it in the previous frame, svgf_impl.h:325-326).  NULL: static camera (zero motion). */
+ATN_API int atn_set_motion_depth(AtnRenderer* r, const AtnVec4* motion_depth, size_t pixel_count);
+/* The SVGF AOV set of the last frame rendered (SVGFParams::aovs, svgf_types.h:55-66): normal + depth, albedo +
+ * material id, colour history + variance, luminance moments + frames + temporal weight.  Any pointer may be NULL. */
+ATN_API int atn_readback_svgf(AtnRenderer* r, AtnVec4* normal_depth, AtnVec4* albedo_meshid, AtnVec4* color_variance,
+                              AtnVec4* moment_temporalweight, size_t pixel_count);
 /* Blocks until the handle's stream is idle. */
 ATN_API int atn_synchronize(AtnRenderer* r);
 /* Replaces the CUDA-GL surface the reference writes with surf2Dwrite (pathtracing_impl.cu:282-324):

@@ -491,7 +491,7 @@ int Usage()
         "  rays   <name> rays.bin hits.bin         (n x {org[3],dir[3],tmax} -> n x AtnHit)\n"
         "  bench  <name> W H frames depth rr threads repeats     (JSON line with timings and ray counts)\n"
         "  ao     <name> W H frame threads out_image.f32            (stock aten::AORenderer, one frame at index `frame`)\n"
-        "  svgf   <name> W H frames depth rr out_prefix [mx my [iters]]  (stock aten::SVGFRenderer on ONE thread, frames 0..frames-1,\n"
+        "  svgf   <name> W H frames depth rr out_prefix [mx my [iters [threads]]]  (stock aten::SVGFRenderer on ONE thread, frames 0..frames-1,\n"
         "         1 sample each; constant motion vector (mx,my) or 0; writes <prefix>.f<k>.f32 per frame and <prefix>.aov.f32)\n"
         "  cmj    out.bin                           (golden CMJ stream)\n");
     return 2;
@@ -619,10 +619,11 @@ int main(int argc, char** argv)
         const std::string prefix = argv[9];
         const float mx = argc > 10 ? (float)atof(argv[10]) : 0.0f, my = argc > 11 ? (float)atof(argv[11]) : 0.0f;
         const int iters = argc > 12 ? atoi(argv[12]) : 5;
+        const int threads = argc > 13 ? atoi(argv[13]) : 1;     // > 1 only for timing: the result then depends on the schedule
         Harness hs;
         if (!hs.Build(name, W, H)) return 1;
-        aten::OMPUtil::setThreadNum(1);
-        omp_set_num_threads(1);
+        aten::OMPUtil::setThreadNum(threads);
+        omp_set_num_threads(threads);
         aten::SVGFRenderer svgf;
         SvgfParamsT& params = svgf.*GetMember(SvgfParamsTag());
         params.atrous_iter_cnt = iters;    // public field of SVGFParams (svgf_types.h:74), default 5
@@ -643,8 +644,8 @@ int main(int argc, char** argv)
                          &aov.get<AT_NAME::SVGFAovBufferType::ColorVariance>(), &aov.get<AT_NAME::SVGFAovBufferType::MomentTemporalWeight>() })
             dump.insert(dump.end(), b->begin(), b->end());
         WriteFile(prefix + ".aov.f32", dump.data(), dump.size() * sizeof(aten::vec4));
-        printf("{\"scene\": \"%s\", \"renderer\": \"svgf\", \"w\": %d, \"h\": %d, \"frames\": %d, \"threads\": 1, \"render_ms\": %.3f}\n",
-               name.c_str(), W, H, frames, ms);
+        printf("{\"scene\": \"%s\", \"renderer\": \"svgf\", \"w\": %d, \"h\": %d, \"frames\": %d, \"threads\": %d, \"render_ms\": %.3f}\n",
+               name.c_str(), W, H, frames, threads, ms);
         return 0;
     }
 

@@ -68,6 +68,46 @@ def ao_bench(name, W, H, spp, steps=3, warmup=2, label=""):
                                         "sample": f"stock aten::AORenderer, {name} 480x270, 1 frame, {info['threads']} threads"}}), flush=True)
 
 
+def svgf_bench(name, W, H, frames=8, warmup=1, label=""):
+    """Row N1: the SVGF renderer, a sequence of `frames` frames (1 sample per pixel each) from frame 0.  The
+    image-space half (prepare, temporal reprojection, variance estimation, 5 a-trous passes, copy) is timed as the
+    difference to the path-traced sample alone; its algorithmic traffic is 690 B per pixel and frame
+    (DESIGN.md "SVGF")."""
+    scene = ol.ref_scene(name, W, H)
+    r = PathTracing(0)
+    r.UpdateSceneData(scene)
+    r.SetEnableProgressive(False)
+    for _ in range(warmup):
+        r.set_frame(0)
+        for f in range(frames):
+            r.render_svgf(W, H, 5, 3)
+    r.set_frame(0)
+    ms = rays = 0
+    for f in range(frames):
+        r.render_svgf(W, H, 5, 3)
+        st = r.stats()
+        if f > 0:       # frame 0 has no temporal pass
+            ms += st["device_ms"]; rays += st["closest_rays"] + st["shadow_rays"]
+    img = r.readback()
+    pt_ms = 0
+    for f in range(1, frames):
+        r.set_frame(f); r.render(W, H, 1, 5, 3)
+        pt_ms += r.stats()["device_ms"]
+    r.close()
+    n = frames - 1
+    filt_ms = (ms - pt_ms) / n
+    info = {}
+    ol.ref_render_svgf(name, 480, 270, frames=3, threads=os.cpu_count() or 1, info=info)
+    print(json.dumps({"config": label, "renderer": "svgf", "scene": name, "w": W, "h": H, "frames": frames,
+                      "ms_per_frame": round(ms / n, 3), "path_tracing_ms": round(pt_ms / n, 3), "filter_ms": round(filt_ms, 3),
+                      "frames_per_s": round(1e3 * n / ms, 1), "msamples_per_s": round(W * H * n / ms / 1e3, 1),
+                      "mrays_per_s": round(rays / ms / 1e3, 1),
+                      "filter_algorithmic_gb_per_s": round(690.0 * W * H / (filt_ms * 1e-3) / 1e9, 1),
+                      "finite": bool(np.isfinite(img).all()),
+                      "reference_cpu": {"msamples_per_s": round(480 * 270 * 3 / info["render_ms"] / 1e3, 4),
+                                        "sample": f"stock aten::SVGFRenderer, {name} 480x270, 3 frames, {info['threads']} threads"}}), flush=True)
+
+
 def ray_stress(name, n_rays, label=""):
     """Incoherent diffuse secondary rays: origins = surface points found by a first random pass,
     directions cosine-distributed about nothing in particular (uniform sphere), closest-hit and any-hit."""
@@ -123,17 +163,22 @@ def ray_stress(name, n_rays, label=""):
 
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--only", default="")
     ap.add_argument("--quick", action="store_true")
     a = ap.parse_args()
     if not ol.have_ref():
         sys.exit("oracle/_ref not present")
     q = a.quick
+    if a.only == "svgf":
+        svgf_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 3, label="N1 SVGF, sponza_lod 1080p, 8-frame sequence")
+        return
     render_bench("cornell", 512, 512, 1, steps=5, warmup=3, label="C1 Cornell 512x512 1spp")
     render_bench("sponza_atrium", 1920, 1080, 16 if not q else 2, label="C2 sponza_lod 1080p 16spp (bench.py workload)")
     render_bench("sponza_tex", 1920, 1080, 16 if not q else 2, label="C3 stand-in: sponza_lod + albedo/normal maps + synthetic-sky IBL, 1080p 16spp")
     render_bench("instanced_dragon", 3840, 2160, 8 if not q else 1, label="C4 stand-in: instanced dragon+teapot+suzanne, Disney/refraction, 4K, 8 spp (one GPU's share of 64 spp on 8)")
     render_bench("dragon_grid10", 1920, 1080, 4 if not q else 1, label="C5 stand-in (rendered): 100 instanced dragons = 10 M triangles, 1080p 4spp")
     ao_bench("sponza_atrium", 1920, 1080, 16 if not q else 2, label="N1 ambient occlusion, sponza_lod 1080p 16spp")
+    svgf_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 3, label="N1 SVGF, sponza_lod 1080p, 8-frame sequence")
     ray_stress("dragon_grid10", 100_000_000 if not q else 5_000_000,
                label="C5 stand-in: 100 M incoherent secondary rays into 100 instanced dragons (10 M triangles), closest-hit and any-hit")
 

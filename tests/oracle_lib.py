@@ -218,11 +218,13 @@ def svgf_last_aov(state, frames_rendered):
     return state[k * 4:(k + 1) * 4]
 
 
-def ref_render_svgf(name, W, H, frames=1, depth=5, rr=3, motion=(0.0, 0.0), iters=5):
+def ref_render_svgf(name, W, H, frames=1, depth=5, rr=3, motion=(0.0, 0.0), iters=5, threads=1, info=None):
     """Stock aten::SVGFRenderer on one thread: ([frames] film images [H,W,4], AOV set of the last frame [4,H*W,4])."""
     with tempfile.TemporaryDirectory() as d:
         prefix = os.path.join(d, "svgf")
-        ref_run("svgf", name, W, H, frames, depth, rr, prefix, motion[0], motion[1], iters)
+        res = ref_run("svgf", name, W, H, frames, depth, rr, prefix, motion[0], motion[1], iters, threads)
+        if info is not None:
+            info.update(res)
         imgs = [np.fromfile(f"{prefix}.f{k}.f32", np.float32).reshape(H, W, 4) for k in range(frames)]
         aov = np.fromfile(f"{prefix}.aov.f32", np.float32).reshape(4, H * W, 4)
     return imgs, aov

@@ -286,7 +286,7 @@ public:
     AtnRenderer* handle() { Ensure(); return h_; }
     FlatScene& flat() { return flat_; }
 
-private:
+protected:
     void Ensure() { if (!h_) Check(atn_create(device_, &h_)); }
     static void Check(int rc) { if (rc != ATN_OK) throw std::runtime_error(atn_last_error()); }
 
@@ -295,6 +295,69 @@ private:
     bool progressive_{ false };
     Mode mode_{ Mode::PT };
     FlatScene flat_;
+};
+
+/// idaten::AORenderer (src/libidaten/ao/ao.h:9-52): PathTracing whose render() is the ambient-occlusion pass.
+class AORenderer : public PathTracing {
+public:
+    using PathTracing::PathTracing;
+    int32_t getNumRays() const { return num_rays_; }
+    void setNumRays(int32_t num) { num_rays_ = num; }
+    float getRadius() const { return radius_; }
+    void setRadius(float radius) { radius_ = radius; }
+
+    /// AORenderer::OnRender (src/libidaten/ao/ao.cpp:9-51); maxBounce is ignored there as well
+    void render(int32_t width, int32_t height, int32_t maxSamples, int32_t /*maxBounce*/)
+    {
+        Check(atn_render_ao(h_, width, height, maxSamples, num_rays_, radius_));
+    }
+
+private:
+    int32_t num_rays_{ 1 };     // m_ao_num_rays
+    float radius_{ 1.0f };      // m_ao_radius
+};
+
+/// idaten::SVGFPathTracing (src/libidaten/svgf/svgf.h:13-215): one render() call = one frame of the SVGF sequence.
+/// The GL G-buffer / motion-depth textures of SetGBuffer() are replaced by a host buffer of motion vectors.
+class SVGFPathTracing : public PathTracing {
+public:
+    enum Mode { SVGF, TF, PT, VAR, AOVar };
+    using PathTracing::PathTracing;
+
+    Mode GetMode() const { return mode_; }
+    void SetMode(Mode mode)
+    {
+        if (mode != SVGF && mode != PT) throw std::runtime_error("idaten_b200::SVGFPathTracing: only Mode::SVGF and Mode::PT are implemented");
+        const Mode prev = mode_;
+        mode_ = mode;
+        if (prev != mode_) reset();
+    }
+
+    /// SVGFPathTracing::render (svgf.cpp:28-125).  maxSamples is 1 in every caller of the reference; more than one
+    /// sample per frame is not implemented (the host twin's sample loop stops at the first terminated path anyway,
+    /// src/libaten/renderer/svgf/svgf.cpp:494-519).
+    void render(int32_t width, int32_t height, int32_t maxSamples, int32_t maxBounce)
+    {
+        if (mode_ == PT) { PathTracing::render(width, height, maxSamples, maxBounce); return; }
+        if (maxSamples != 1) throw std::runtime_error("idaten_b200::SVGFPathTracing::render: maxSamples must be 1");
+        Check(atn_render_svgf(h_, width, height, maxBounce, /*rrBounce*/ 3, atrous_iters_));
+    }
+
+    /// Stands in for SetGBuffer(gltexGbuffer, gltexMotionDepthbuffer): W*H float4, .xy = motion in screen fractions.
+    void SetMotionDepthBuffer(const aten::vec4* motion_depth, size_t pixel_count)
+    {
+        Check(atn_set_motion_depth(h_, reinterpret_cast<const AtnVec4*>(motion_depth), pixel_count));
+    }
+
+    void SetAtrousIterCount(int32_t n) { atrous_iters_ = n; }      // SVGFParams::atrous_iter_cnt (svgf_types.h:74)
+
+    /// The sequence restarts without history.  (idaten::Renderer::reset() sets the frame counter to 1, which makes the
+    /// reference re-use whatever history its buffers hold; here frame 0 = no history.)
+    void reset() { PathTracing::reset(); }
+
+private:
+    Mode mode_{ SVGF };
+    int32_t atrous_iters_{ 5 };
 };
 
 }  // namespace idaten_b200

@@ -18,7 +18,8 @@ DEPS = [SRC, os.path.join(HERE, "..", "aten_b200", "csrc", "atn_bvh.h"), os.path
 _lib = None
 
 STAT_NAMES = ("nodes", "tris", "entries", "entries_filtered", "pops_culled", "max_sp", "node_count", "slots_used",
-              "replaced", "not_nested", "stack_bound")
+              "replaced", "not_nested", "stack_bound", "visited_0slot", "visited_1slot", "visited_2slot", "visited_3slot",
+              "visited_4slot")
 
 
 def lib():

@@ -64,7 +64,7 @@ inline TriHit tri_edges(const V3& org, const V3& dir, const V3& v0, const V3& e1
 struct Best { float t, a, b; int32_t leaf, inst; };
 struct Ent { int32_t ref; float t0; };
 
-struct Stats { uint64_t nodes, tris, entries, entries_filtered, pops_culled, rays; uint64_t max_sp; uint64_t sum_sp; };
+struct Stats { uint64_t nodes, tris, entries, entries_filtered, pops_culled, rays; uint64_t max_sp; uint64_t sum_sp; uint64_t slot_hist[5]; };
 
 inline void finish(const std::vector<TriLeaf>& tris, const int32_t* inst_objid, const int32_t* inst_meshid, const Best& b, AtnHit* h)
 {
@@ -108,6 +108,7 @@ extern "C" int emu_trace_wide(const AtnSceneBlob* scene, const AtnRay* rays, con
                 if (cur >= 0) {
                     const QuadNode& q = w.nodes[cur];
                     st.nodes++;
+                    { int used = 0; for (int k = 0; k < 4; k++) used += q.ref[k] != kRefNull; st.slot_hist[used]++; }
                     Ent e[4]; int ne = 0;
                     for (int s = 0; s < 4; s++) {
                         if (q.ref[s] == kRefNull) continue;
@@ -180,9 +181,11 @@ extern "C" int emu_trace_wide(const AtnSceneBlob* scene, const AtnRay* rays, con
         {
             tot.nodes += st.nodes; tot.tris += st.tris; tot.entries += st.entries; tot.entries_filtered += st.entries_filtered;
             tot.pops_culled += st.pops_culled; tot.rays += st.rays; if (st.max_sp > tot.max_sp) tot.max_sp = st.max_sp;
+            for (int k = 0; k < 5; k++) tot.slot_hist[k] += st.slot_hist[k];
         }
     }
     if (stats_out) {
+        for (int k = 0; k < 5; k++) stats_out[11 + k] = tot.slot_hist[k];
         stats_out[0] = tot.nodes; stats_out[1] = tot.tris; stats_out[2] = tot.entries; stats_out[3] = tot.entries_filtered;
         stats_out[4] = tot.pops_culled; stats_out[5] = tot.max_sp; stats_out[6] = w.nodes.size(); stats_out[7] = w.slots_used;
         stats_out[8] = w.replaced; stats_out[9] = w.not_nested; stats_out[10] = (uint64_t)w.max_stack;

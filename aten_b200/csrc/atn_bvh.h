@@ -191,7 +191,8 @@ struct WideBvh {
     std::vector<TriLeaf> tris;
     std::vector<InstLeafW> insts;
     int32_t top_root{ kRefNull };
-    int32_t max_stack{ 0 };          // bound on the traversal stack depth (entries)
+    int32_t max_stack{ 0 };          // exact worst case of the traversal stack depth (entries), see stack_need
+    std::vector<int32_t> stack_need; // per QuadNode: entries the traversal can have on its stack below this node
     uint64_t slots_used{ 0 }, replaced{ 0 }, not_nested{ 0 };
     std::string error;
 };
@@ -278,6 +279,16 @@ struct WideBuilder {
         return n;
     }
 
+    // stack entries the traversal can hold while it is below reference `ref`: an instance leaves an exit marker
+    // behind and then walks the bottom tree (emitted before the top layer)
+    int32_t need_of(int32_t ref) const
+    {
+        if (ref >= 0) return (size_t)ref < out->stack_need.size() ? out->stack_need[ref] : 0;
+        if (ref == kRefNull || !top) return 0;
+        const int32_t root = leaves->insts[~ref].root;
+        return 1 + (root >= 0 && (size_t)root < out->stack_need.size() ? out->stack_need[root] : 0);
+    }
+
     // QuadNode for the slots `slots` (already the children of a tested node); returns its index
     int32_t emit(std::vector<Slot> slots, int32_t depth)
     {
@@ -326,6 +337,15 @@ struct WideBuilder {
             qn.ref[s] = refs[s];
             qn.pad[s] = 0;
         }
+        // Worst case below this node: the deepest child is entered first, with all other hit slots left on the stack.
+        int32_t live = 0, deepest = 0;
+        for (int s = 0; s < 4; s++) {
+            if (refs[s] == kRefNull) continue;
+            live++;
+            deepest = std::max(deepest, need_of(refs[s]));
+        }
+        if (out->stack_need.size() < out->nodes.size()) out->stack_need.resize(out->nodes.size(), 0);
+        out->stack_need[self] = (live > 0 ? live - 1 : 0) + deepest;
         return self;
     }
 
@@ -349,22 +369,18 @@ inline WideBvh encode_wide(const AtnSceneBlob* scene)
     if (scene->node_list_count == 0) return out;
     EncodedBvh leaves;
     std::vector<int32_t> roots(scene->node_list_count, kRefNull);
-    int32_t bottom_depth = 0;
     for (uint32_t k = 1; k < scene->node_list_count; k++) {
         if (scene->node_list_sizes[k] == 0) continue;
         detail::ListBuilder lb{ scene->node_lists[k], scene->node_list_sizes[k], false, scene, &leaves, &roots };
         detail::WideBuilder wb{ scene->node_lists[k], scene->node_list_sizes[k], false, &leaves, &lb, &out };
         roots[k] = wb.run();
         if (!out.error.empty()) return out;
-        bottom_depth = std::max(bottom_depth, wb.depth_seen);
     }
-    int32_t top_depth = 0;
     if (scene->node_list_sizes[0] > 0) {
         detail::ListBuilder lb{ scene->node_lists[0], scene->node_list_sizes[0], true, scene, &leaves, &roots };
         detail::WideBuilder wb{ scene->node_lists[0], scene->node_list_sizes[0], true, &leaves, &lb, &out };
         out.top_root = wb.run();
         if (!out.error.empty()) return out;
-        top_depth = wb.depth_seen;
         out.insts.resize(leaves.insts.size());
         for (size_t i = 0; i < leaves.insts.size(); i++) {
             const InstLeaf& il = leaves.insts[i];
@@ -377,8 +393,13 @@ inline WideBvh encode_wide(const AtnSceneBlob* scene)
         }
     }
     out.tris.swap(leaves.tris);
-    // every node step leaves at most three entries behind, an instance entry one more
-    out.max_stack = 3 * (bottom_depth + top_depth) + 2;
+    out.max_stack = 0;
+    if (out.top_root >= 0) out.max_stack = out.stack_need[out.top_root];
+    else if (out.top_root != kRefNull && !out.insts.empty()) {      // the top layer is a single instance leaf
+        const int32_t root = out.insts[~out.top_root].root;
+        out.max_stack = 1 + (root >= 0 ? out.stack_need[root] : 0);
+    }
+    out.max_stack += 1;    // slack: the kernel checks sp + pushes <= capacity before it writes
     return out;
 }
 

@@ -85,7 +85,7 @@ constexpr int kMaxBounce = 16;
 #define ATN_SMEM_STACK 16
 #endif
 constexpr int kSmemStack = ATN_SMEM_STACK;     // shared-memory stack entries per thread
-constexpr int kLocalStack = 64;    // overflow, local memory
+constexpr int kLocalStack = 112;   // overflow, local memory (with kSmemStack: 128 entries; the encoder computes the exact worst case per scene)
 constexpr int kTraceBlock = 128;
 #ifndef ATN_REFILL_THRESHOLD
 #define ATN_REFILL_THRESHOLD 20

@@ -24,7 +24,7 @@ EXPORTS = [
     "atn_render", "atn_render_region", "atn_synchronize", "atn_readback", "atn_device_image", "atn_get_stats",
     "atn_set_profiling", "atn_get_stream", "atn_trace_closest", "atn_trace_any", "atn_trace_closest_device",
     "atn_trace_any_device", "atn_set_bounce_tap", "atn_trace_closest_static", "atn_readback_aov", "atn_render_ao",
-    "atn_render_svgf", "atn_set_motion_depth", "atn_readback_svgf",
+    "atn_render_svgf", "atn_set_motion_depth", "atn_readback_svgf", "atn_update_texture",
 ]
 
 
@@ -134,6 +134,15 @@ class PathTracing:
     def updateLight(self, lights: np.ndarray):
         l = np.ascontiguousarray(lights, sio.LIGHT_DTYPE)
         _check(self._lib, self._lib.atn_update_lights(self._h, C.c_void_p(l.ctypes.data), C.c_uint32(len(l))))
+
+    def UpdateTexture(self, idx: int, texels: np.ndarray):
+        """idaten::Renderer::UpdateTexture (reference src/libidaten/kernel/renderer.cpp:236-247): float32 [h, w, 4]
+        texels for texture `idx`, same size as at upload."""
+        t = np.ascontiguousarray(texels, np.float32)
+        if t.ndim != 3 or t.shape[2] != 4:
+            raise ValueError("texels must be float32 [h, w, 4]")
+        d = sio.AtnTextureDesc(C.c_void_p(t.ctypes.data), t.shape[1], t.shape[0], 0, 0)
+        _check(self._lib, self._lib.atn_update_texture(self._h, C.c_uint32(idx), C.byref(d)))
 
     def UpdateSceneRenderingConfig(self, config: np.ndarray):
         c = np.ascontiguousarray(config, sio.CONFIG_DTYPE)

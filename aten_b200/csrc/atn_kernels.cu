@@ -1119,6 +1119,7 @@ struct AtnRenderer {
     DevBuf<AtnVec4> positions, normals;
     DevBuf<AtnVec4> texels;
     DevBuf<TexView> texviews;
+    std::vector<TexView> h_texviews;           // host copy of the view table (atn_update_texture)
     DevBuf<QuadNode> nodes;
     DevBuf<TriLeaf> tris;
     DevBuf<InstLeafW> insts;
@@ -1316,6 +1317,7 @@ ATN_API int atn_upload_scene(AtnRenderer* r, const AtnSceneBlob* scene, const At
     }
     CUDA_TRY(r->texviews.upload(tv.data(), tv.size(), s));
     CUDA_TRY(cudaStreamSynchronize(s));
+    r->h_texviews = tv;
 
     // host copies for atn_update_top_layer (re-encode needs triangles / positions / bottom lists)
     r->h_objects.assign(scene->objects, scene->objects + scene->object_count);
@@ -1395,6 +1397,23 @@ ATN_API int atn_update_materials(AtnRenderer* r, const AtnMaterialParameter* m, 
     CUDA_TRY(r->materials.upload(m, count, r->stream));
     CUDA_TRY(cudaStreamSynchronize(r->stream));
     r->sv.materials = r->materials.p; r->sv.material_count = (int32_t)count;
+    return ATN_OK;
+}
+
+ATN_API int atn_update_texture(AtnRenderer* r, uint32_t index, const AtnTextureDesc* texture)
+{
+    if (!r || !texture || !texture->texels) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_update_texture: NULL argument");
+    if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_update_texture: no scene uploaded");
+    if (index >= r->h_texviews.size()) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_update_texture: index %u of %zu", index, r->h_texviews.size());
+    const TexView& tv = r->h_texviews[index];
+    if (!tv.texels || texture->width != tv.w || texture->height != tv.h)
+        return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_update_texture: texture %u is %dx%d, got %dx%d (the size is fixed at upload)",
+                         index, tv.w, tv.h, texture->width, texture->height);
+    CUDA_TRY(cudaSetDevice(r->device));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
+    CUDA_TRY(cudaMemcpyAsync(const_cast<AtnVec4*>(tv.texels), texture->texels, (size_t)tv.w * tv.h * sizeof(AtnVec4),
+                             cudaMemcpyHostToDevice, r->stream));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
     return ATN_OK;
 }
 

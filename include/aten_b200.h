@@ -222,6 +222,9 @@ ATN_API int atn_update_top_layer(AtnRenderer* r, const AtnBvhNode* top_nodes, ui
                                  const AtnMat4* matrices, uint32_t matrix_count);
 /* Renderer::updateMaterial (renderer.cpp:190-200) */
 ATN_API int atn_update_materials(AtnRenderer* r, const AtnMaterialParameter* m, uint32_t count);
+/* Renderer::UpdateTexture(idx, ctxt) (src/libidaten/kernel/renderer.cpp:236-247): new texels for texture `index`;
+ * the reference copies into the existing CUDA texture resource, so the size stays what it was at upload. */
+ATN_API int atn_update_texture(AtnRenderer* r, uint32_t index, const AtnTextureDesc* texture);
 /* Renderer::updateLight (renderer.cpp:202-220) */
 ATN_API int atn_update_lights(AtnRenderer* r, const AtnLightParameter* l, uint32_t count);
 /* Renderer::UpdateSceneRenderingConfig (renderer.h:103-106) */

@@ -252,6 +252,16 @@ public:
         Check(atn_update_lights(h_, reinterpret_cast<const AtnLightParameter*>(lights.data()), (uint32_t)lights.size()));
     }
 
+    /// Renderer::UpdateTexture (renderer.cpp:236-247)
+    void UpdateTexture(int32_t idx, const aten::context& ctxt)
+    {
+        auto tex = ctxt.GetTexture(idx);
+        AtnTextureDesc d{};
+        d.texels = reinterpret_cast<const AtnVec4*>(tex->colors().data());
+        d.width = static_cast<int32_t>(tex->width()); d.height = static_cast<int32_t>(tex->height());
+        Check(atn_update_texture(h_, static_cast<uint32_t>(idx), &d));
+    }
+
     void UpdateSceneRenderingConfig(const aten::context& ctxt)
     {
         FlatScene tmp;

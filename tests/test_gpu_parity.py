@@ -316,6 +316,45 @@ def test_live_reference_textured_and_large_scene(name, W, H):
 
 
 @needs_ref
+def test_update_texture_equals_fresh_upload():
+    """Renderer::UpdateTexture (reference src/libidaten/kernel/renderer.cpp:236-247): new texels for one albedo map
+    give the image a fresh upload of the edited scene gives -- bit for bit -- and differ from the old one; a
+    texture of another size is refused."""
+    import copy
+    W, H = 96, 54
+    scene = ol.ref_scene("sponza_tex", W, H)
+    used = sorted({int(m) for m in scene.materials["albedoMap"] if m >= 0})
+    assert used, "the stand-in scene binds albedo maps"
+    idx = used[0]
+    tex, flt, adr = scene.textures[idx]
+    edited = np.ascontiguousarray(tex[::-1, :, :] * np.float32(0.5))          # flipped and darkened
+    r = PathTracing(0)
+    fresh = PathTracing(0)
+    try:
+        r.UpdateSceneData(scene)
+        r.render(W, H, 2, 5, 3)
+        before = r.readback().copy()
+        r.UpdateTexture(idx, edited)
+        r.reset()
+        r.render(W, H, 2, 5, 3)
+        after = r.readback()
+        scene2 = copy.copy(scene)
+        scene2.textures = list(scene.textures)
+        scene2.textures[idx] = (edited, flt, adr)
+        fresh.UpdateSceneData(scene2)
+        fresh.render(W, H, 2, 5, 3)
+        want = fresh.readback()
+        assert (bits(after) == bits(want)).all()
+        assert np.abs(after - before).max() > 1e-3
+        with pytest.raises(AtnError):
+            r.UpdateTexture(idx, edited[:-1])
+        with pytest.raises(AtnError):
+            r.UpdateTexture(len(scene.textures), edited)
+    finally:
+        r.close(); fresh.close()
+
+
+@needs_ref
 def test_top_layer_update_moving_instance(golden):
     """Renderer::updateBVH (reference src/libidaten/kernel/renderer.cpp:133-153): after the host moves
     an instance and rebuilds the top layer, uploading list 0 + objects + matrices alone must give what

@@ -85,7 +85,9 @@ constexpr int kMaxBounce = 16;
 #define ATN_SMEM_STACK 16
 #endif
 constexpr int kSmemStack = ATN_SMEM_STACK;     // shared-memory stack entries per thread
-constexpr int kLocalStack = 112;   // overflow, local memory (with kSmemStack: 128 entries; the encoder computes the exact worst case per scene)
+// overflow of the shared-memory stack, local memory: two instantiations of the kernel, picked per scene from the
+// encoder's exact worst-case depth (a larger local frame costs ~1 % even when it is never touched)
+constexpr int kLocalStackSmall = 48, kLocalStackLarge = 240;
 constexpr int kTraceBlock = 128;
 #ifndef ATN_REFILL_THRESHOLD
 #define ATN_REFILL_THRESHOLD 20
@@ -445,7 +447,7 @@ __device__ __forceinline__ SlabPair slab_pair(const float4 mn_xy, const float4 m
 #ifndef ATN_TRACE_MIN_BLOCKS
 #define ATN_TRACE_MIN_BLOCKS 8
 #endif
-template <class Policy>
+template <class Policy, int kLocalStack>
 __global__ void __launch_bounds__(kTraceBlock, ATN_TRACE_MIN_BLOCKS)
 k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch, Visits* visits)
 {
@@ -1177,15 +1179,27 @@ struct AtnRenderer {
     cudaEvent_t ev0{ nullptr }, ev1{ nullptr };
     std::vector<cudaEvent_t> trace_events;
     int trace_grid{ 148 * 8 };
+    int stack_need{ 0 };                // worst-case traversal stack depth of the uploaded scene (WideBvh::max_stack)
     int surface_grid{ 148 * 8 }, nee_grid{ 148 * 8 }, bsdf_grid{ 148 * 8 };
 };
+
+// One traversal launch: the instantiation whose stack covers the scene's worst case (upload_bvh checked that one does).
+template <class Policy>
+static void launch_trace(AtnRenderer* r, cudaStream_t s, Policy pol, const int32_t* count_ptr, int count_imm, int32_t* fetch, Visits* visits)
+{
+    if (r->stack_need <= kSmemStack + kLocalStackSmall)
+        k_trace<Policy, kLocalStackSmall><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
+    else
+        k_trace<Policy, kLocalStackLarge><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
+}
 
 static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene)
 {
     WideBvh enc = encode_wide(scene);
     if (!enc.error.empty()) return set_error(ATN_ERR_INVALID_ARGUMENT, "node lists: %s", enc.error.c_str());
-    if (enc.max_stack > kSmemStack + kLocalStack)
-        return set_error(ATN_ERR_TOO_LARGE, "BVH needs a traversal stack of %d entries (limit %d)", enc.max_stack, kSmemStack + kLocalStack);
+    if (enc.max_stack > kSmemStack + kLocalStackLarge)
+        return set_error(ATN_ERR_TOO_LARGE, "BVH needs a traversal stack of %d entries (limit %d)", enc.max_stack, kSmemStack + kLocalStackLarge);
+    r->stack_need = enc.max_stack;
     CUDA_TRY(r->nodes.upload(enc.nodes.data(), enc.nodes.size(), r->stream));
     CUDA_TRY(r->tris.upload(enc.tris.data(), enc.tris.size(), r->stream));
     CUDA_TRY(r->insts.upload(enc.insts.data(), enc.insts.size(), r->stream));
@@ -1259,7 +1273,7 @@ ATN_API int atn_create(int device_ordinal, AtnRenderer** out)
     CUDA_TRY(cudaEventCreate(&r->ev0));
     CUDA_TRY(cudaEventCreate(&r->ev1));
     int bps = 0;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace<ClosestPolicy>, kTraceBlock, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace<ClosestPolicy, kLocalStackSmall>, kTraceBlock, 0));
     r->trace_grid = r->sm_count * std::max(1, bps);
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_surface<false, false>, kShadeBlock, 0));
     r->surface_grid = r->sm_count * std::max(1, bps);
@@ -1497,7 +1511,7 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
         if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
         {
             ClosestPolicy pol{ pb, q, tmax, b == 0 ? pb.hit_mesh : nullptr };
-            k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[b], 0, &c->fetch_closest[b], r->visits.p);
+            launch_trace<ClosestPolicy>(r, s, pol, &c->n_active[b], 0, &c->fetch_closest[b], r->visits.p);
         }
         if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
         if (svgf_w2c) k_surface<false, true><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, pb, c, b, nullptr, 0, w2c);
@@ -1509,11 +1523,11 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
         if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
         if (tap_now) {
             ShadowPolicy<true> pol{ pb, r->sv, r->tap_dev.p, r->tap_cap, b };
-            k_trace<ShadowPolicy<true>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
+            launch_trace<ShadowPolicy<true>>(r, s, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
         }
         else {
             ShadowPolicy<false> pol{ pb, r->sv, nullptr, 0, b };
-            k_trace<ShadowPolicy<false>><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
+            launch_trace<ShadowPolicy<false>>(r, s, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
         }
         if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
         *launches += 5;
@@ -1626,7 +1640,7 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
         k_generate<<<grid, 256, 0, s>>>(fp, r->camera, r->seeds.p, r->pb, c);
         {
             ClosestPolicy pol{ r->pb, nullptr, kInf, nullptr };
-            k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_active[0], 0, &c->fetch_closest[0], r->visits.p);
+            launch_trace<ClosestPolicy>(r, s, pol, &c->n_active[0], 0, &c->fetch_closest[0], r->visits.p);
         }
         k_ao_begin<<<sgrid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, r->pb, c);
         launches += 3;
@@ -1634,7 +1648,7 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
             k_ao_ray<<<sgrid, kShadeBlock, 0, s>>>(fp, r->seeds.p, r->pb, c);
             CUDA_TRY(cudaMemsetAsync(&c->fetch_query, 0, sizeof(int32_t), s));
             ClosestPolicy pol{ r->pb, r->pb.q_lit, radius, nullptr };
-            k_trace<ClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, &c->n_lit[0], 0, &c->fetch_query, r->visits.p);
+            launch_trace<ClosestPolicy>(r, s, pol, &c->n_lit[0], 0, &c->fetch_query, r->visits.p);
             k_ao_accum<<<sgrid, kShadeBlock, 0, s>>>(r->sv, r->pb, c, radius, i == num_rays - 1 ? 1 : 0, num_rays);
             launches += 3;
         }
@@ -1857,11 +1871,11 @@ static int query_launch(AtnRenderer* r, const void* rays_dev, const void* f_dev,
     CUDA_TRY(cudaEventRecord(r->ev0, s));
     if (any) {
         QueryAnyPolicy pol{ (const AtnRay*)rays_dev, (const float*)f_dev, (uint8_t*)out_dev };
-        k_trace<QueryAnyPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
+        launch_trace<QueryAnyPolicy>(r, s, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
     }
     else {
         QueryClosestPolicy pol{ (const AtnRay*)rays_dev, (const float*)f_dev, (AtnHit*)out_dev };
-        k_trace<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
+        launch_trace<QueryClosestPolicy>(r, s, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
     }
     CUDA_TRY(cudaEventRecord(r->ev1, s));
     CUDA_TRY(cudaGetLastError());
@@ -1997,7 +2011,7 @@ extern "C" ATN_API int atn_trace_closest_static(AtnRenderer* r, const AtnRay* ra
     CUDA_TRY(cudaMemcpyAsync(sc->rays, rays, n * sizeof(AtnRay), cudaMemcpyHostToDevice, s));
     if (t_max) CUDA_TRY(cudaMemcpyAsync(sc->t_max, t_max, n * sizeof(float), cudaMemcpyHostToDevice, s));
     QueryClosestPolicy pol{ sc->rays, t_max ? sc->t_max : nullptr, sc->hits };
-    k_trace<QueryClosestPolicy><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, nullptr, (int)n, &sc->cursor, nullptr);
+    launch_trace<QueryClosestPolicy>(r, s, pol, nullptr, (int)n, &sc->cursor, nullptr);
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaMemcpyAsync(hits, sc->hits, n * sizeof(AtnHit), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaStreamSynchronize(s));

@@ -49,6 +49,7 @@ struct alignas(16) InstLeaf {
 // Child / root references: >= 0 inner QuadNode index; < 0 leaf number ~ref; two reserved values.
 constexpr int32_t kRefNull = INT32_MIN + 1;   // leaf that holds nothing traversable (e.g. a sphere)
 constexpr int32_t kRefExit = INT32_MIN;       // stack marker: leave the current instance
+constexpr int32_t kRefDone = INT32_MIN + 2;   // stack sentinel below every ray's first entry: the traversal is complete
 
 struct EncodedBvh {          // leaf records collected while a node list is scanned
     std::vector<TriLeaf> tris;
@@ -399,7 +400,7 @@ inline WideBvh encode_wide(const AtnSceneBlob* scene)
         const int32_t root = out.insts[~out.top_root].root;
         out.max_stack = 1 + (root >= 0 ? out.stack_need[root] : 0);
     }
-    out.max_stack += 1;    // slack: the kernel checks sp + pushes <= capacity before it writes
+    out.max_stack += 2;    // the sentinel at the bottom of every ray's stack, and one entry of slack
     return out;
 }
 

@@ -78,6 +78,7 @@ struct BvhView {
     const AtnMat4* matrices;
     int32_t top_root;
     float t_min;
+    cudaTextureObject_t node_tex;   // the QuadNode array again, as a linear float4 texture (see ATN_NODE_TEX)
 };
 
 constexpr int kMaxBounce = 16;
@@ -447,6 +448,14 @@ __device__ __forceinline__ SlabPair slab_pair(const float4 mn_xy, const float4 m
 #ifndef ATN_TRACE_MIN_BLOCKS
 #define ATN_TRACE_MIN_BLOCKS 8
 #endif
+// Which 32-byte chunks of a QuadNode are fetched through the TEXTURE pipe (tex1Dfetch of float4) instead of
+// LDG.256; bit k = chunk k.  The kernel is co-limited by the LSU data pipe of L1 (one wavefront per distinct line
+// and load instruction); the texture path reads the same cache through its own pipe, so moving part of the node
+// there relieves the LSU one.  Measured on the bench workload (Mrays/s): 0: 1 749, 8: 1 809, 12: 1 807, 9: 1 814,
+// 10: 1 821 (default), 14: 1 814, 15: 1 774; triangles through the texture pipe as well: no gain.
+#ifndef ATN_NODE_TEX
+#define ATN_NODE_TEX 10
+#endif
 template <class Policy, int kLocalStack>
 __global__ void __launch_bounds__(kTraceBlock, ATN_TRACE_MIN_BLOCKS)
 k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch, Visits* visits)
@@ -495,7 +504,8 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                     s_world[9 * kTraceBlock + tid] = ri.oxinvdir.x; s_world[10 * kTraceBlock + tid] = ri.oxinvdir.y; s_world[11 * kTraceBlock + tid] = ri.oxinvdir.z;
                     t_cull = t_max;
                     best.t = kInf; best.a = 0.0f; best.b = 0.0f; best.leaf = -1; best.inst = -1;
-                    sp = 0; cur = bv.top_root; cur_inst = -1;
+                    sts64(stack_base, kRefDone, __float_as_int(-kInf));     // sentinel: popping it ends the ray
+                    sp = 1; cur = bv.top_root; cur_inst = -1;
                     active = true;
                 }
             }
@@ -511,7 +521,17 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
             const bool on_node = active && cur >= 0;
             if (on_node) {
                 const float4* np = bv.nodes + (size_t)cur * 8;
-                const F4x2 c0 = ldg8(np + 0), c1 = ldg8(np + 2), c2 = ldg8(np + 4), c3 = ldg8(np + 6);
+                // chunk k through the texture pipe (two 128-bit fetches; one for the last chunk, whose upper half is
+                // padding) or through LDG.256, see ATN_NODE_TEX
+                F4x2 c0, c1, c2, c3;
+                if (ATN_NODE_TEX & 1) { c0.lo = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 0); c0.hi = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 1); }
+                else c0 = ldg8(np + 0);
+                if (ATN_NODE_TEX & 2) { c1.lo = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 2); c1.hi = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 3); }
+                else c1 = ldg8(np + 2);
+                if (ATN_NODE_TEX & 4) { c2.lo = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 4); c2.hi = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 5); }
+                else c2 = ldg8(np + 4);
+                if (ATN_NODE_TEX & 8) c3.lo = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 6);
+                else c3 = ldg8(np + 6);
                 const float4 a0 = c0.lo, a1 = c0.hi, a2 = c1.lo, b0 = c1.hi, b1 = c2.lo, b2 = c2.hi;
                 const int4 rf = make_int4(__float_as_int(c3.lo.x), __float_as_int(c3.lo.y), __float_as_int(c3.lo.z), __float_as_int(c3.lo.w));
                 const float2 inv_xy = make_float2(ri.invdir.x, ri.invdir.y);
@@ -555,7 +575,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
             }
 
             // ---- phase B: triangle leaf (triangle::hit, triangle.h:40-67) ----
-            const bool want_tri = active && cur < 0 && cur != kRefNull && cur != kRefExit && cur_inst >= 0;
+            const bool want_tri = active && cur < 0 && cur > kRefDone && cur_inst >= 0;       // a leaf, not one of the reserved values
             bool run_tris = true;
             if (kLeafBatch > 1) {
                 const unsigned mt = __ballot_sync(full, want_tri);
@@ -585,7 +605,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
             }
 
             // ---- phase E: instance entry (threaded_bvh_traverser.h:146-185), batched ----
-            const bool want_entry = active && cur < 0 && cur != kRefNull && cur != kRefExit && cur_inst < 0;
+            const bool want_entry = active && cur < 0 && cur > kRefDone && cur_inst < 0;
             const unsigned me = __ballot_sync(full, want_entry);
             if (me != 0u) {
                 const unsigned busy = __ballot_sync(full, on_node || on_tri);
@@ -619,27 +639,28 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                 }
             }
 
-            // ---- phase C: pop ----
+            // ---- phase C: pop.  Runs for a few lanes at a time, so it is kept short: entries whose subtree starts behind
+            // the current hit are skipped in a three-instruction loop, the sentinel at the bottom of the stack (entry
+            // distance -inf, like the exit markers) ends the ray without a separate emptiness test. ----
             if (active && !finished && cur == kRefNull) {
 #pragma unroll 1
                 for (;;) {
-                    if (sp == 0) { finished = true; break; }
-                    sp--;
-                    const int2 e = (sp < kSmemStack) ? lds64(stack_base + (uint32_t)sp * kStackStride) : l_stack[sp - kSmemStack];
+                    int2 e;
+#pragma unroll 1
+                    do {
+                        sp--;
+                        e = (sp < kSmemStack) ? lds64(stack_base + (uint32_t)sp * kStackStride) : l_stack[sp - kSmemStack];
+                    } while (__int_as_float(e.y) > t_cull);
                     cur = e.x;
-                    if (cur == kRefExit) {
-                        if (sp == 0) { finished = true; break; }      // nothing left in the top layer either
-                        cur_inst = -1;
-                        org = V3(s_world[0 * kTraceBlock + tid], s_world[1 * kTraceBlock + tid], s_world[2 * kTraceBlock + tid]);
-                        dir = V3(s_world[3 * kTraceBlock + tid], s_world[4 * kTraceBlock + tid], s_world[5 * kTraceBlock + tid]);
-                        ri.invdir = V3(s_world[6 * kTraceBlock + tid], s_world[7 * kTraceBlock + tid], s_world[8 * kTraceBlock + tid]);
-                        ri.oxinvdir = V3(s_world[9 * kTraceBlock + tid], s_world[10 * kTraceBlock + tid], s_world[11 * kTraceBlock + tid]);
-                        cur = kRefNull;
-                        continue;
-                    }
-                    if (__int_as_float(e.y) > t_cull) { cur = kRefNull; continue; }   // subtree starts behind the current hit
-                    break;
+                    if (cur != kRefExit) break;
+                    // back to the top layer with the world ray (threaded_bvh_traverser.h:290-300), then pop again
+                    cur_inst = -1;
+                    org = V3(s_world[0 * kTraceBlock + tid], s_world[1 * kTraceBlock + tid], s_world[2 * kTraceBlock + tid]);
+                    dir = V3(s_world[3 * kTraceBlock + tid], s_world[4 * kTraceBlock + tid], s_world[5 * kTraceBlock + tid]);
+                    ri.invdir = V3(s_world[6 * kTraceBlock + tid], s_world[7 * kTraceBlock + tid], s_world[8 * kTraceBlock + tid]);
+                    ri.oxinvdir = V3(s_world[9 * kTraceBlock + tid], s_world[10 * kTraceBlock + tid], s_world[11 * kTraceBlock + tid]);
                 }
+                finished = (cur == kRefDone);
             }
             if (finished) { active = false; done = true; }
         }
@@ -1025,17 +1046,45 @@ __global__ void k_svgf_variance(FrameParams fp, SvgfView sv, float camera_distan
         svgf_variance(i % fp.width, i / fp.width, fp.width, fp.height, camera_distance, sv.cur, sv.cur.color_variance, sv.scratch);
 }
 
-__global__ void k_svgf_atrous(FrameParams fp, SvgfView sv, float camera_distance, int iter, int iter_count, float4* image)
+// ATN_SVGF_TEX: bit 0 = the normal-depth taps, bit 1 = the colour taps go through the texture pipe (a linear float4
+// texture over all SVGF planes); 0 = everything through LDG.  The kernel is bound by the LSU pipe of L1 (84 128-bit
+// loads per pixel); filter time per 1080p frame: 0: 1.83 ms, 1: 1.69, 2: 1.73, 3: 1.59 (default).
+#ifndef ATN_SVGF_TEX
+#define ATN_SVGF_TEX 3
+#endif
+struct SvgfTexPlane {
+    cudaTextureObject_t tex; int32_t base;      // first texel of the plane inside the texture
+    __device__ __forceinline__ AtnVec4 operator()(int32_t i) const
+    {
+        const float4 v = tex1Dfetch<float4>(tex, base + i);
+        AtnVec4 r; r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w;
+        return r;
+    }
+};
+__global__ void k_svgf_atrous(FrameParams fp, SvgfView sv, float camera_distance, int iter, int iter_count, float4* image,
+                              cudaTextureObject_t planes_tex, const AtnVec4* planes_base)
 {
     const int n = fp.width * fp.height;
     // (selects, not sv.atrous[iter & 1]: a dynamic index would push the whole parameter struct to local memory)
     const AtnVec4* src = (iter == 0) ? sv.cur.color_variance : ((iter & 1) ? sv.atrous[1] : sv.atrous[0]);
     AtnVec4* next = (iter & 1) ? sv.atrous[0] : sv.atrous[1];
+    const bool use_tex = planes_tex != 0;
+    const SvgfTexPlane tnd{ planes_tex, (int32_t)(sv.cur.normal_depth - planes_base) };
+    const SvgfTexPlane tcl{ planes_tex, (int32_t)(src - planes_base) };
+    const SvgfPlane pnd{ sv.cur.normal_depth }, pcl{ src };
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         AtnVec4 film;
-        if (svgf_atrous(iter, iter_count, i % fp.width, i / fp.width, fp.width, fp.height, camera_distance, sv.cur, src, next,
-                        sv.temporary, &film))
-            image[i] = make_float4(film.x, film.y, film.z, film.w);
+        bool done;
+        const int ix = i % fp.width, iy = i / fp.width;
+        if (use_tex && (ATN_SVGF_TEX & 3) == 1)
+            done = svgf_atrous(iter, iter_count, ix, iy, fp.width, fp.height, camera_distance, sv.cur, src, next, sv.temporary, &film, tnd, pcl);
+        else if (use_tex && (ATN_SVGF_TEX & 3) == 2)
+            done = svgf_atrous(iter, iter_count, ix, iy, fp.width, fp.height, camera_distance, sv.cur, src, next, sv.temporary, &film, pnd, tcl);
+        else if (use_tex && (ATN_SVGF_TEX & 3) == 3)
+            done = svgf_atrous(iter, iter_count, ix, iy, fp.width, fp.height, camera_distance, sv.cur, src, next, sv.temporary, &film, tnd, tcl);
+        else
+            done = svgf_atrous(iter, iter_count, ix, iy, fp.width, fp.height, camera_distance, sv.cur, src, next, sv.temporary, &film, pnd, pcl);
+        if (done) image[i] = make_float4(film.x, film.y, film.z, film.w);
     }
 }
 
@@ -1165,6 +1214,7 @@ struct AtnRenderer {
     int svgf_cv_plane[2]{ 2, 6 };      // which plane holds color_variance of each AOV set (swaps with the scratch plane)
     int svgf_scratch_plane{ 11 };
     bool svgf_has_motion{ false };
+    cudaTextureObject_t svgf_tex{ 0 };  // linear float4 texture over svgf_planes (a-trous taps, ATN_SVGF_TEX)
     size_t svgf_pixels{ 0 };
 
     // tap
@@ -1205,6 +1255,16 @@ static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene)
     CUDA_TRY(r->insts.upload(enc.insts.data(), enc.insts.size(), r->stream));
     CUDA_TRY(cudaStreamSynchronize(r->stream));   // enc goes out of scope
     r->bv.nodes = reinterpret_cast<const float4*>(r->nodes.p);
+    if (r->bv.node_tex) { cudaDestroyTextureObject(r->bv.node_tex); r->bv.node_tex = 0; }
+    if (ATN_NODE_TEX && !enc.nodes.empty()) {
+        // linear float4 texture over the node array; tex1Dfetch addresses 2^27 texels = 16 M QuadNodes (2 GB)
+        if (enc.nodes.size() * 8 > ((size_t)1 << 27))
+            return set_error(ATN_ERR_TOO_LARGE, "%zu nodes exceed the linear-texture limit of %zu", enc.nodes.size(), ((size_t)1 << 27) / 8);
+        cudaResourceDesc rd{}; rd.resType = cudaResourceTypeLinear; rd.res.linear.devPtr = r->nodes.p;
+        rd.res.linear.desc = cudaCreateChannelDesc<float4>(); rd.res.linear.sizeInBytes = enc.nodes.size() * sizeof(QuadNode);
+        cudaTextureDesc td{}; td.readMode = cudaReadModeElementType;
+        CUDA_TRY(cudaCreateTextureObject(&r->bv.node_tex, &rd, &td, nullptr));
+    }
     r->bv.tris = reinterpret_cast<const float4*>(r->tris.p);
     r->bv.insts = reinterpret_cast<const float4*>(r->insts.p);
     r->bv.matrices = r->matrices.p;
@@ -1293,6 +1353,8 @@ ATN_API int atn_destroy(AtnRenderer* r)
     for (auto ev : r->trace_events) cudaEventDestroy(ev);
     if (r->ev0) cudaEventDestroy(r->ev0);
     if (r->ev1) cudaEventDestroy(r->ev1);
+    if (r->bv.node_tex) cudaDestroyTextureObject(r->bv.node_tex);
+    if (r->svgf_tex) cudaDestroyTextureObject(r->svgf_tex);
     cudaStream_t s = r->stream;
     delete r;
     if (s) cudaStreamDestroy(s);
@@ -1720,6 +1782,13 @@ ATN_API int atn_render_svgf(AtnRenderer* r, int32_t width, int32_t height, int32
     if (r->svgf_pixels != n || !r->svgf_planes.p) {
         CUDA_TRY(r->svgf_planes.resize(12 * n));
         r->svgf_pixels = n;
+        if (r->svgf_tex) { cudaDestroyTextureObject(r->svgf_tex); r->svgf_tex = 0; }
+        if (ATN_SVGF_TEX && 12 * n <= ((size_t)1 << 27)) {      // tex1Dfetch addresses 2^27 texels; larger frames use LDG only
+            cudaResourceDesc rd{}; rd.resType = cudaResourceTypeLinear; rd.res.linear.devPtr = r->svgf_planes.p;
+            rd.res.linear.desc = cudaCreateChannelDesc<float4>(); rd.res.linear.sizeInBytes = 12 * n * sizeof(float4);
+            cudaTextureDesc td{}; td.readMode = cudaReadModeElementType;
+            CUDA_TRY(cudaCreateTextureObject(&r->svgf_tex, &rd, &td, nullptr));
+        }
         if (!first_frame) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_svgf: no history for frame %u (start at frame 0: atn_set_frame(0))", r->frame);
     }
     if (first_frame) {
@@ -1765,7 +1834,7 @@ ATN_API int atn_render_svgf(AtnRenderer* r, int32_t width, int32_t height, int32
     sv.cur = svgf_aov_of(r, cur_k);
     sv.scratch = base + (size_t)r->svgf_scratch_plane * n;
     for (int i = 0; i < atrous_iters; i++)
-        k_svgf_atrous<<<grid, 256, 0, s>>>(fp, sv, camera_distance, i, atrous_iters, r->image.p);
+        k_svgf_atrous<<<grid, 256, 0, s>>>(fp, sv, camera_distance, i, atrous_iters, r->image.p, r->svgf_tex, base);
     k_svgf_copy<<<grid, 256, 0, s>>>(fp, sv);
     launches += 3 + (uint64_t)atrous_iters;
     CUDA_TRY(cudaEventRecord(r->ev1, s));

@@ -247,9 +247,17 @@ ATN_HD AtnVec4 svgf_variance(int32_t ix, int32_t iy, int32_t width, int32_t heig
 // Exec3x3GaussFilter of the variance, ExecAtrousWaveletFilter, PostProcessForAtrousFilter.
 // `src` = aov.color_variance for the first iteration, the ping-pong buffer after that.  Returns true and
 // the film colour when this iteration produces one (the last iteration; albedo put back).
+// `tap_nd(i)` / `tap_color(i)` read the normal-depth plane and the colour source at pixel i for the 24 taps: plain
+// array reads on the host (SvgfPlane); the kernel passes readers that go through the texture pipe for one of them
+// (the a-trous kernel is bound by the LSU pipe of L1, see k_svgf_atrous).
+struct SvgfPlane {
+    const AtnVec4* p;
+    ATN_HD AtnVec4 operator()(int32_t i) const { return p[i]; }
+};
+template <class TapNd, class TapColor>
 ATN_HD bool svgf_atrous(int32_t iter, int32_t iter_count, int32_t ix, int32_t iy, int32_t width, int32_t height,
                         float camera_distance, const SvgfAov& aov, const AtnVec4* src, AtnVec4* next,
-                        AtnVec4* temporary_color, AtnVec4* film_color)
+                        AtnVec4* temporary_color, AtnVec4* film_color, const TapNd& tap_nd, const TapColor& tap_color)
 {
     const bool first = iter == 0, last = iter == iter_count - 1;
     const int32_t idx = ix + iy * width;
@@ -313,11 +321,11 @@ ATN_HD bool svgf_atrous(int32_t iter, int32_t iter_count, int32_t ix, int32_t iy
         const int32_t yy = svgf_clampi(iy + soy, 0, height - 1);
         const float u_length = sqrtf((float)(sox * sox + soy * soy));
         const int32_t qidx = xx + yy * width;
-        const AtnVec4 qnd = aov.normal_depth[qidx];
+        const AtnVec4 qnd = tap_nd(qidx);
         const V3 normal(qnd.x, qnd.y, qnd.z);
         const float depth = qnd.w;
         const int32_t meshid = (int32_t)aov.albedo_meshid[qidx].w;
-        const AtnVec4 color = first ? aov.color_variance[qidx] : src[qidx];
+        const AtnVec4 color = tap_color(qidx);      // = aov.color_variance in the first iteration, the ping-pong source after
         const float variance = color.w;
         const float lum = luminance(color.x, color.y, color.z);
         const float Wn = svgf_pow128(fmaxf(0.0f, dot(center_normal, normal)));     // sigmaN = 128
@@ -353,6 +361,14 @@ ATN_HD bool svgf_atrous(int32_t iter, int32_t iter_count, int32_t ix, int32_t iy
         return true;
     }
     return false;
+}
+
+ATN_HD bool svgf_atrous(int32_t iter, int32_t iter_count, int32_t ix, int32_t iy, int32_t width, int32_t height,
+                        float camera_distance, const SvgfAov& aov, const AtnVec4* src, AtnVec4* next,
+                        AtnVec4* temporary_color, AtnVec4* film_color)
+{
+    return svgf_atrous(iter, iter_count, ix, iy, width, height, camera_distance, aov, src, next, temporary_color, film_color,
+                       SvgfPlane{ aov.normal_depth }, SvgfPlane{ iter == 0 ? aov.color_variance : src });
 }
 
 // CopyFromTeporaryColorBufferToAov (svgf.cpp:412-424): xyz only

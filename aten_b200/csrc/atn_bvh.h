@@ -24,6 +24,7 @@
 #include <string.h>
 #include <algorithm>
 #include <cmath>
+#include <limits>
 #include <string>
 #include <vector>
 
@@ -325,7 +326,10 @@ struct WideBuilder {
         QuadNode& qn = out->nodes[self];
         const float big = 3.0e38f;
         for (int s = 0; s < 4; s++) {
-            float mn[3] = { big, big, big }, mx[3] = { big, big, big };      // empty: never hit (masked by ref too)
+            // empty slot: min = max = +inf.  Its slab distances are +inf or -inf on every axis, so entry <= min(exit, t_max)
+            // fails for any finite t_max and the kernel needs no separate test of the reference
+            const float inf = std::numeric_limits<float>::infinity();
+            float mn[3] = { inf, inf, inf }, mx[3] = { inf, inf, inf };
             if ((size_t)s < slots.size() && refs[s] != kRefNull) {
                 if (slots[s].boxnode < 0) { for (int a = 0; a < 3; a++) { mn[a] = -big; mx[a] = big; } }
                 else for (int a = 0; a < 3; a++) { mn[a] = list[slots[s].boxnode].boxmin[a]; mx[a] = list[slots[s].boxnode].boxmax[a]; }

@@ -328,7 +328,7 @@ struct QueryClosestPolicy {        // atn_trace_closest
     __device__ __forceinline__ void world(int i, V3* o, V3* d) const { const AtnRay r = rays[i]; *o = V3(r.org); *d = V3(r.dir); }
     __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* tm, int* mode, float* exit_dist) const
     {
-        world(i, o, d); *slot = i; *tm = t_max ? t_max[i] : kInf; *mode = EXIT_NONE; *exit_dist = 0.0f;
+        world(i, o, d); *slot = i; *tm = t_max ? fminf(t_max[i], kInf) : kInf; *mode = EXIT_NONE; *exit_dist = 0.0f;
     }
     __device__ __forceinline__ void finish(const BvhView& bv, int i, const TraceResult& r) const
     {
@@ -344,7 +344,7 @@ struct QueryAnyPolicy {            // atn_trace_any
     __device__ __forceinline__ void world(int i, V3* o, V3* d) const { const AtnRay r = rays[i]; *o = V3(r.org); *d = V3(r.dir); }
     __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* tm, int* mode, float* exit_dist) const
     {
-        world(i, o, d); *slot = i; *tm = dist[i] - kEps; *mode = EXIT_HIT_BEFORE; *exit_dist = dist[i];
+        world(i, o, d); *slot = i; *tm = fminf(dist[i] - kEps, kInf); *mode = EXIT_HIT_BEFORE; *exit_dist = dist[i];
     }
     __device__ __forceinline__ void finish(const BvhView&, int i, const TraceResult& r) const
     {
@@ -539,13 +539,14 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                 const SlabPair pa = slab_pair(a0, a1, a2, inv_xy, inv_zz, ri.oxinvdir);
                 const SlabPair pb = slab_pair(b0, b1, b2, inv_xy, inv_zz, ri.oxinvdir);
                 n_nodes++;
-                // t0 = max(entry, t_min) <= min(exit, running cull bound); empty slots never hit
+                // t0 = max(entry, t_min) <= min(exit, running cull bound); empty slots carry an infinite box and never
+                // pass (t_cull is finite: every source clamps it to kInf = FLT_MAX)
                 float k0 = fmaxf(pa.t0a, t_min), k1 = fmaxf(pa.t0b, t_min), k2 = fmaxf(pb.t0a, t_min), k3 = fmaxf(pb.t0b, t_min);
                 int32_t r0 = rf.x, r1 = rf.y, r2 = rf.z, r3 = rf.w;
-                const bool h0 = (k0 <= fminf(pa.t1a, t_cull)) & (r0 != kRefNull);
-                const bool h1 = (k1 <= fminf(pa.t1b, t_cull)) & (r1 != kRefNull);
-                const bool h2 = (k2 <= fminf(pb.t1a, t_cull)) & (r2 != kRefNull);
-                const bool h3 = (k3 <= fminf(pb.t1b, t_cull)) & (r3 != kRefNull);
+                const bool h0 = k0 <= fminf(pa.t1a, t_cull);
+                const bool h1 = k1 <= fminf(pa.t1b, t_cull);
+                const bool h2 = k2 <= fminf(pb.t1a, t_cull);
+                const bool h3 = k3 <= fminf(pb.t1b, t_cull);
                 const int nhit = (int)h0 + (int)h1 + (int)h2 + (int)h3;
                 k0 = h0 ? k0 : kInf; k1 = h1 ? k1 : kInf; k2 = h2 ? k2 : kInf; k3 = h3 ? k3 : kInf;
                 ATN_CE(k0, r0, k1, r1) ATN_CE(k2, r2, k3, r3) ATN_CE(k0, r0, k2, r2) ATN_CE(k1, r1, k3, r3) ATN_CE(k1, r1, k2, r2)
@@ -1527,7 +1528,7 @@ ATN_API int atn_set_seeds(AtnRenderer* r, const uint32_t* seeds, uint32_t count)
 ATN_API int atn_set_frame(AtnRenderer* r, uint32_t frame) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->frame = frame; return ATN_OK; }
 ATN_API int atn_get_frame(AtnRenderer* r, uint32_t* frame) { if (!r || !frame) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); *frame = r->frame; return ATN_OK; }
 ATN_API int atn_set_progressive(AtnRenderer* r, int enable) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->progressive = enable ? 1 : 0; return ATN_OK; }
-ATN_API int atn_set_hit_distance_limit(AtnRenderer* r, float d) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->hit_distance_limit = d; return ATN_OK; }
+ATN_API int atn_set_hit_distance_limit(AtnRenderer* r, float d) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->hit_distance_limit = fminf(d, kInf); return ATN_OK; }
 ATN_API int atn_set_profiling(AtnRenderer* r, int enable) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->profiling = enable ? 1 : 0; return ATN_OK; }
 ATN_API int atn_get_stream(AtnRenderer* r, void** stream) { if (!r || !stream) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); *stream = (void*)r->stream; return ATN_OK; }
 

@@ -318,20 +318,19 @@ def main():
             line["roofline"] = {
                 "bound": "hbm", "achieved": round(achieved, 1), "peak": hbm, "unit": "GB/s", "frac": round(achieved / hbm, 4),
                 # dram__bytes_read+write per traversal launch from the ncu --set full capture summarised in
-                # profiles/r01_ncu_full_v6_wide.txt (85-140 MB per launch, mean of the ten captured launches): the ray / hit
+                # profiles/r01_ncu_full_v8_final.txt (85-140 MB per launch, mean of the ten captured launches): the ray / hit
                 # streams only -- nodes and triangles are served from L2
                 "traffic": 1.05e8, "algorithmic_bytes_per_launch": round(tr_rays * base["b_ray"] / max(1, trace_launches), 0),
                 "peak_source": which, "kernel": "k_trace<ClosestPolicy> + k_trace<ShadowPolicy>",
-                "issue_slot_utilisation_ncu": 0.67, "threads_per_instruction_ncu": 15.3, "l1_data_pipe_utilisation_ncu": 0.79,
+                "issue_slot_utilisation_ncu": 0.70, "threads_per_instruction_ncu": 16.1, "l1_throughput_ncu": 0.60,
                 "bytes_per_ray": round(base["b_ray"], 1), "flops_per_ray": round(base["f_ray"], 1),
                 "nodes_per_ray": round(base["n_node"], 2), "tris_per_ray": round(base["n_tri"], 2),
                 "trace_share_of_step": round(tr_ms / max(1e-9, (dev_ms / args.steps) * max(1, min(args.steps, 3))), 3),
                 "trace_mrays_per_s": round(tr_rays / (tr_ms / 1e3) / 1e6, 1),
                 "note": "algorithmic bytes on the REFERENCE layout and visit order (oracle counters, SURVEY 8d); the scene is L2-resident and "
                         "the ordered traversal over 4-slot nodes fetches ~2.5 KB/ray from L1/L2 (own_layout), so frac > 1 against the HBM copy peak is expected; "
-                        "the kernel is bound by instruction issue and the L1 data pipe together (issue_slot_utilisation_ncu at "
-                        "threads_per_instruction_ncu of 32 lanes; l1tex__data_pipe_lsu_wavefronts at l1_data_pipe_utilisation_ncu of peak "
-                        "on the incoherent bounces)",
+                        "the kernel is instruction-issue bound (issue_slot_utilisation_ncu at threads_per_instruction_ncu of 32 lanes); "
+                        "part of every node is fetched through the texture pipe, which took l1tex throughput from 0.79 to l1_throughput_ncu",
             }
         if cpu:
             line["cpu_baseline"] = cpu

@@ -128,6 +128,14 @@ def test_ray_query_edge_cases(golden, renderers):
     g_rays, _ = golden.rays("cornell")
     for n in (1, 31, 32, 33, 1000):
         assert_hits_equal(r.trace_closest(g_rays[:n]), ol.trace_closest(golden.scene("cornell"), g_rays[:n]))
+    # a caller's t_max of +inf behaves like the reference's AT_MATH_INF = FLT_MAX (the empty slots of a node rely on a
+    # finite bound); a t_max of 0 or below finds nothing
+    n = 2000
+    inf_hits = r.trace_closest(g_rays[:n], np.full(n, np.inf, np.float32))
+    max_hits = r.trace_closest(g_rays[:n], np.full(n, FLT_MAX, np.float32))
+    assert (inf_hits.view(np.uint8) == max_hits.view(np.uint8)).all() and (max_hits["objid"] >= 0).any()
+    none = r.trace_closest(g_rays[:n], np.zeros(n, np.float32))
+    assert (none["objid"] == -1).all()
 
 
 @pytest.mark.parametrize("name", SCENES)

@@ -173,7 +173,7 @@ __device__ __forceinline__ void resolve_hit(const BvhView& bv, const TraceResult
 // with the exact running t_max through a slab test that is biased by +1e-6 on the direction
 // (aabb.h:68), which makes its answer depend on its visit order when two primitives are hit within
 // a few ulps of each other.  Culling with t*(1+2e-5) keeps triangles that tie with the current hit
-// reachable; pairs within ~1e-5 relative distance can still resolve either way (DESIGN.md "Near ties").
+// reachable; pairs within 2e-5 relative distance can still resolve either way (DESIGN.md "Near ties").
 __device__ __forceinline__ float cull_bound(float t) { return t + fabsf(t) * 2e-5f; }
 
 // intersectTriangle (src/libaten/math/intersect.h:45-89) with e1 = v1 - v0 and e2 = v2 - v0 taken from

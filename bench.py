@@ -324,6 +324,11 @@ def main():
                 "peak_source": which, "kernel": "k_trace<ClosestPolicy> + k_trace<ShadowPolicy>",
                 "issue_slot_utilisation_ncu": 0.70, "threads_per_instruction_ncu": 16.1, "l1_throughput_ncu": 0.60,
                 "bytes_per_ray": round(base["b_ray"], 1), "flops_per_ray": round(base["f_ray"], 1),
+                # the second roof of SURVEY 8d: algorithmic flops against the FP32 peak of the SMs (148 x 128 lanes x 2 x the
+                # SM clock sampled during the run); nominal, not measured
+                "achieved_tflops": round(tr_rays * base["f_ray"] / (tr_ms / 1e3) / 1e12, 2),
+                "fp32_peak_tflops": round(148 * 128 * 2 * (clk.get("sm_mhz") or 1965.0) * 1e6 / 1e12, 1),
+                "fp32_frac": round(tr_rays * base["f_ray"] / (tr_ms / 1e3) / (148 * 128 * 2 * (clk.get("sm_mhz") or 1965.0) * 1e6), 4),
                 "nodes_per_ray": round(base["n_node"], 2), "tris_per_ray": round(base["n_tri"], 2),
                 "trace_share_of_step": round(tr_ms / max(1e-9, (dev_ms / args.steps) * max(1, min(args.steps, 3))), 3),
                 "trace_mrays_per_s": round(tr_rays / (tr_ms / 1e3) / 1e6, 1),

@@ -28,6 +28,8 @@
 #include "atenscene.h"
 #include "renderer/pathtracing/pathtracing_impl.h"
 #include "renderer/svgf/svgf.h"
+#include "renderer/restir/restir.h"
+#include "renderer/restir/restir_impl.h"
 
 #include "../include/idaten_b200_shim.h"
 
@@ -476,6 +478,142 @@ struct SvgfParamsTag { using type = SvgfParamsT aten::SVGFRenderer::*; friend ty
 template <typename Tag, typename Tag::type M> struct MemberAccess { friend typename Tag::type GetMember(Tag) { return M; } };
 template struct MemberAccess<SvgfParamsTag, &aten::SVGFRenderer::params_>;
 
+// ---- ReSTIR --------------------------------------------------------------------------------------
+// The stock host driver aten::ReSTIRRenderer::OnRender is in a debugging state (RELEASE_DEBUG, restir.cpp:10):
+// Render() calls GeneratePath again at every bounce, so the "path" restarts from the camera.  The per-pixel steps
+// themselves -- ReSTIRRenderer::Shade / EvaluateVisibility / ApplyTemporalReuse / ApplySpatialReuse /
+// ComputePixelColor, private static members built on restir_impl.h -- are sound and shared with the device
+// renderer.  ReplayReSTIR calls exactly those functions, in the order of idaten::ReSTIRPathTracing::OnRender
+// (src/libidaten/restir/restir.cpp:47-123, restir.cu:340-425, restir_reuse.cu:124-230): one GeneratePath per frame,
+// bounce 0 = Shade, visibility, temporal reuse (frame > 1), spatial reuse, pixel colour; bounces > 0 = the path
+// tracer's shade + shadow ray.  The private statics are reached through explicit-instantiation accessors.
+using ReSTIRShadeFn = void (*)(int32_t, int32_t, int32_t, aten::Path&, const aten::context&, aten::ray*, const aten::Intersection&,
+                               aten::span<AT_NAME::Reservoir>&, aten::span<AT_NAME::ReSTIRInfo>&, int32_t, int32_t, const aten::mat4&,
+                               aten::span<aten::vec4>&, aten::span<aten::vec4>&);
+using ReSTIRVisFn = void (*)(int32_t, int32_t, int32_t, int32_t, aten::Path&, const aten::context&, aten::scene*,
+                             std::vector<AT_NAME::Reservoir>&, std::vector<AT_NAME::ReSTIRInfo>&, std::vector<aten::ShadowRay>&);
+using ReSTIRSpatialFn = void (*)(int32_t, int32_t, int32_t, const aten::context&, aten::sampler&, const std::vector<AT_NAME::Reservoir>&,
+                                 std::vector<AT_NAME::Reservoir>&, const std::vector<AT_NAME::ReSTIRInfo>&, const std::vector<aten::vec4>&);
+using ReSTIRTemporalFn = void (*)(int32_t, int32_t, int32_t, const aten::context&, aten::sampler&, std::vector<AT_NAME::Reservoir>&,
+                                  const std::vector<AT_NAME::Reservoir>&, const std::vector<AT_NAME::ReSTIRInfo>&,
+                                  const std::vector<AT_NAME::ReSTIRInfo>&, const std::vector<aten::vec4>&, const std::vector<aten::vec4>&);
+using ReSTIRColorFn = void (*)(int32_t, AT_NAME::Path&, const aten::context&, const std::vector<AT_NAME::Reservoir>&,
+                               const std::vector<AT_NAME::ReSTIRInfo>&, const std::vector<aten::vec4>&);
+struct RsShadeTag { using type = ReSTIRShadeFn; friend type GetMember(RsShadeTag); };
+struct RsVisTag { using type = ReSTIRVisFn; friend type GetMember(RsVisTag); };
+struct RsSpatialTag { using type = ReSTIRSpatialFn; friend type GetMember(RsSpatialTag); };
+struct RsTemporalTag { using type = ReSTIRTemporalFn; friend type GetMember(RsTemporalTag); };
+struct RsColorTag { using type = ReSTIRColorFn; friend type GetMember(RsColorTag); };
+template struct MemberAccess<RsShadeTag, &aten::ReSTIRRenderer::Shade>;
+template struct MemberAccess<RsVisTag, &aten::ReSTIRRenderer::EvaluateVisibility>;
+template struct MemberAccess<RsSpatialTag, &aten::ReSTIRRenderer::ApplySpatialReuse>;
+template struct MemberAccess<RsTemporalTag, &aten::ReSTIRRenderer::ApplyTemporalReuse>;
+template struct MemberAccess<RsColorTag, &aten::ReSTIRRenderer::ComputePixelColor>;
+
+struct ReSTIRState {
+    aten::PathHost ph;
+    std::vector<aten::ray> rays;
+    std::vector<aten::ShadowRay> shadow;
+    AT_NAME::ReuseParams<std::vector<AT_NAME::Reservoir>> reservoirs;
+    AT_NAME::ReuseParams<std::vector<AT_NAME::ReSTIRInfo>> infos;
+    AT_NAME::MatricesForRendering mtxs;
+    std::vector<aten::vec4> aov_nd, aov_am, motion;
+    int32_t last_target{ 0 };
+};
+
+// One frame of the ReSTIR sequence (see the comment above ReSTIRState).
+void ReplayReSTIRFrame(Harness& hs, ReSTIRState& st, uint32_t frame, int32_t max_depth, int32_t rr_depth, std::vector<aten::vec4>* image)
+{
+    const int32_t W = hs.W, H = hs.H, n = W * H;
+    if (rr_depth > max_depth) rr_depth = max_depth - 1;                 // restir.cpp:333-335
+    // ReSTIRRenderer::Initialize (restir.cpp:322-356)
+    if (st.rays.empty()) st.rays.resize(n);
+    if (st.shadow.empty()) st.shadow.resize(n);
+    st.ph.init(W, H);
+    st.ph.Clear(frame);
+    st.reservoirs.Init(n);
+    st.infos.Init(n);
+    st.mtxs.Reset(hs.camera.param());
+    if (st.aov_nd.empty()) { st.aov_nd.resize(n); st.aov_am.resize(n); }
+    const auto& cam = hs.camera.param();
+    const aten::mat4 w2c = st.mtxs.GetW2C();
+    aten::span<aten::vec4> aov_nd(st.aov_nd), aov_am(st.aov_am);
+    const auto shade = GetMember(RsShadeTag());
+    const auto visibility = GetMember(RsVisTag());
+    const auto spatial = GetMember(RsSpatialTag());
+    const auto temporal = GetMember(RsTemporalTag());
+    const auto pixel_color = GetMember(RsColorTag());
+
+    // generatePath + InitReSTIR (libidaten restir.cpp:66-72, restir.cu:18-34)
+    for (int32_t idx = 0; idx < n; idx++) {
+        AT_NAME::GeneratePath(st.rays[idx], idx, idx % W, idx / W, W, H, 0, frame, st.ph.paths, cam, aten::getRandom(idx));
+        st.reservoirs.GetCurrParams()[idx].clear();
+        st.infos.GetCurrParams()[idx].clear();
+    }
+    for (int32_t bounce = 0; bounce < max_depth; bounce++) {
+        for (int32_t idx = 0; idx < n; idx++) {
+            auto& attrib = st.ph.paths.attrib[idx];
+            if (attrib.attr.is_terminated) continue;
+            attrib.attr.isHit = false;
+            aten::Intersection isect;
+            const bool is_hit = aten::BvhTraverser::Traverse<aten::IntersectType::Closest>(isect, hs.ctxt, st.rays[idx], AT_MATH_EPSILON, AT_MATH_INF);
+            if (is_hit) {
+                attrib.attr.isHit = true;
+                if (bounce == 0) {
+                    aten::span<AT_NAME::Reservoir> reservoirs(st.reservoirs.GetCurrParams());
+                    aten::span<AT_NAME::ReSTIRInfo> infos(st.infos.GetCurrParams());
+                    shade(idx, W, H, st.ph.paths, hs.ctxt, st.rays.data(), isect, reservoirs, infos, rr_depth, bounce, w2c, aov_nd, aov_am);
+                }
+                else {
+                    aten::PathTracing::shade(idx, st.ph.paths, hs.ctxt, st.rays.data(), st.shadow.data(), isect, &hs.scene, rr_depth, bounce);
+                    const auto& mtrl = hs.ctxt.GetMaterial(isect.mtrlid);
+                    std::ignore = AT_NAME::HitShadowRay(bounce, hs.ctxt, mtrl, attrib, st.ph.paths.contrib[idx], st.shadow[idx]);
+                }
+            }
+            else {
+                AT_NAME::ShadeMiss(idx, idx % W, idx / W, W, H, bounce, hs.ctxt, cam, st.ph.paths, st.rays[idx], aov_nd, aov_am);
+            }
+        }
+        if (bounce > 0) continue;
+        // OnShadeByShadowRayReSTIR (restir.cu:382-425) and ComputelReuse (restir_reuse.cu:124-230)
+        for (int32_t idx = 0; idx < n; idx++) {
+            if (st.ph.paths.attrib[idx].attr.is_terminated) continue;
+            visibility(idx, bounce, W, H, st.ph.paths, hs.ctxt, &hs.scene, st.reservoirs.GetCurrParams(), st.infos.GetCurrParams(), st.shadow);
+        }
+        const int32_t dst_idx = st.reservoirs.GetDestinationParamsIdxForSpatialReuse();
+        const int32_t cur_infos_idx = st.infos.GetCurrParamsIdx();
+        auto& cur_res = st.reservoirs.GetCurrParams();
+        auto& prev_res = st.reservoirs.GetPreviousFrameParamsForTemporalReuse();
+        auto& dst_res = st.reservoirs.GetDestinationParamsForSpatialReuse();
+        auto& cur_infos = st.infos.GetCurrParams();
+        auto& prev_infos = st.infos.GetPreviousFrameParamsForTemporalReuse();
+        st.reservoirs.Update();
+        st.infos.Update();
+        if (frame > 1) {
+            for (int32_t idx = 0; idx < n; idx++) {
+                if (st.ph.paths.attrib[idx].attr.is_terminated) continue;
+                temporal(idx, W, H, hs.ctxt, st.ph.sampler[idx], cur_res, prev_res, cur_infos, prev_infos, st.aov_am, st.motion);
+            }
+        }
+        for (int32_t idx = 0; idx < n; idx++) {
+            if (st.ph.paths.attrib[idx].attr.is_terminated) continue;
+            spatial(idx, W, H, hs.ctxt, st.ph.sampler[idx], cur_res, dst_res, cur_infos, st.aov_am);
+        }
+        for (int32_t idx = 0; idx < n; idx++) {
+            if (st.ph.paths.attrib[idx].attr.is_terminated) continue;
+            pixel_color(idx, st.ph.paths, hs.ctxt, st.reservoirs.GetParams(dst_idx), st.infos.GetParams(cur_infos_idx), st.aov_am);
+        }
+        st.last_target = dst_idx;
+    }
+    if (image) {
+        image->resize(n);
+        for (int32_t idx = 0; idx < n; idx++) {
+            const auto& c = st.ph.paths.contrib[idx].contrib;
+            (*image)[idx] = aten::vec4(c.x, c.y, c.z, 1.0f);
+        }
+    }
+}
+
 double NowMs()
 {
     return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
@@ -493,6 +631,8 @@ int Usage()
         "  ao     <name> W H frame threads out_image.f32            (stock aten::AORenderer, one frame at index `frame`)\n"
         "  svgf   <name> W H frames depth rr out_prefix [mx my [iters [threads]]]  (stock aten::SVGFRenderer on ONE thread, frames 0..frames-1,\n"
         "         1 sample each; constant motion vector (mx,my) or 0; writes <prefix>.f<k>.f32 per frame and <prefix>.aov.f32)\n"
+        "  restir <name> W H frames depth rr out_prefix [mx my]       (the reference's ReSTIR steps in the device renderer's order;\n"
+        "         writes <prefix>.f<k>.f32 per frame and <prefix>.reservoirs.f32)\n"
         "  cmj    out.bin                           (golden CMJ stream)\n");
     return 2;
 }
@@ -646,6 +786,37 @@ int main(int argc, char** argv)
         WriteFile(prefix + ".aov.f32", dump.data(), dump.size() * sizeof(aten::vec4));
         printf("{\"scene\": \"%s\", \"renderer\": \"svgf\", \"w\": %d, \"h\": %d, \"frames\": %d, \"threads\": %d, \"render_ms\": %.3f}\n",
                name.c_str(), W, H, frames, threads, ms);
+        return 0;
+    }
+
+    if (cmd == "restir") {
+        // the reference's ReSTIR per-pixel steps in the device renderer's order (ReplayReSTIRFrame), one thread
+        if (argc < 10) return Usage();
+        const int W = atoi(argv[4]), H = atoi(argv[5]), frames = atoi(argv[6]), depth = atoi(argv[7]), rr = atoi(argv[8]);
+        const std::string prefix = argv[9];
+        const float mx = argc > 10 ? (float)atof(argv[10]) : 0.0f, my = argc > 11 ? (float)atof(argv[11]) : 0.0f;
+        Harness hs;
+        if (!hs.Build(name, W, H)) return 1;
+        aten::OMPUtil::setThreadNum(1);
+        omp_set_num_threads(1);
+        ReSTIRState st;
+        st.motion.assign((size_t)W * H, aten::vec4(mx, my, 0.0f, 0.0f));
+        std::vector<aten::vec4> image;
+        double ms = 0;
+        for (int f = 0; f < frames; f++) {
+            const double t0 = NowMs();
+            ReplayReSTIRFrame(hs, st, (uint32_t)f, depth, rr, &image);
+            ms += NowMs() - t0;
+            WriteFile(prefix + ".f" + std::to_string(f) + ".f32", image.data(), image.size() * sizeof(aten::vec4));
+        }
+        // the reservoirs the last frame's pixel colours were computed from: w_sum, M, y, W, target pdf per pixel
+        std::vector<float> dump;
+        for (const auto& r : st.reservoirs.GetParams(st.last_target)) {
+            dump.push_back(r.w_sum); dump.push_back((float)r.M); dump.push_back((float)r.y); dump.push_back(r.W); dump.push_back(r.target_pdf_of_y);
+        }
+        WriteFile(prefix + ".reservoirs.f32", dump.data(), dump.size() * sizeof(float));
+        printf("{\"scene\": \"%s\", \"renderer\": \"restir\", \"w\": %d, \"h\": %d, \"frames\": %d, \"threads\": 1, \"render_ms\": %.3f}\n",
+               name.c_str(), W, H, frames, ms);
         return 0;
     }
 

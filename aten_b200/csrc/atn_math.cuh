@@ -1151,6 +1151,7 @@ struct PathState {
 
 struct ShadowRayOut {
     bool active;
+    bool sampled = false;   // a light was sampled: FillShadowRay reset ShadowRay::lightcontrib (read again by ReSTIR's visibility step)
     V3 org; float dist;
     V3 dir; int32_t light_id;
     V3 lightcontrib;
@@ -1300,6 +1301,7 @@ ATN_HD bool shade_surface(const SceneView& sc, const Ray& ray, int32_t objid, in
 ATN_HD void shade_nee(const SceneView& sc, const V3& ray_dir, const Surface& sf, PathState* st, ShadowRayOut* sh)
 {
     sh->active = false;
+    sh->sampled = false;
     const Mtrl mtrl = fill_material(sc, sf.mtrlid);
     const int32_t lightnum = sc.light_count;
     if (lightnum > 0 && !(mtrl.is_singular() || mtrl.is_translucent())) {
@@ -1315,6 +1317,7 @@ ATN_HD void shade_nee(const SceneView& sc, const V3& ray_dir, const Surface& sf,
         sh->org = ray_offset(sf.p, sf.n);
         sh->light_id = target;
         sh->lightcontrib = V3(0.0f);
+        sh->sampled = true;
         V3 radiance;
         if (radiance_nee(&radiance, sc, ray_dir, sf.n, mtrl, sf.u, sf.v, select_prob, ls)) {
             sh->lightcontrib = st->throughput * radiance * sf.albedo;

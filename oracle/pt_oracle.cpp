@@ -25,6 +25,7 @@
 
 #include "../aten_b200/csrc/atn_math.cuh"
 #include "../aten_b200/csrc/atn_svgf.cuh"
+#include "../aten_b200/csrc/atn_restir.cuh"
 
 using namespace atn;
 
@@ -445,6 +446,139 @@ int oracle_render_svgf(const AtnSceneBlob* blob, const AtnCameraParameter* cam, 
         }
         for (size_t i = 0; i < n; i++) svgf_copy((int32_t)i, temporary, cur);
     }
+    return 0;
+}
+
+// N1: the ReSTIR renderer -- the reference's per-pixel steps (restir_impl.h, ReSTIRRenderer::Shade) in the order of
+// idaten::ReSTIRPathTracing::OnRender, frames 0 .. frames-1 of one sample each (oracle/ref_harness.cpp, ReplayReSTIRFrame,
+// is the same sequence built from the reference's own functions).  `motion_depth`: W*H motion vectors or NULL.
+// `image`: W*H contribution of the LAST frame (rgb, 1).  `reservoirs_out`: W*H x 5 floats (w_sum, M, y, W, target pdf)
+// of the reservoirs that frame's pixel colours were computed from, or NULL.
+int oracle_render_restir(const AtnSceneBlob* blob, const AtnCameraParameter* cam, const uint32_t* seeds, uint32_t seed_count,
+                         int32_t W, int32_t H, int32_t frames, int32_t max_depth, int32_t rr_depth,
+                         const AtnVec4* motion_depth, AtnVec4* image, float* reservoirs_out)
+{
+    const Scene s = MakeScene(blob);
+    if (rr_depth > max_depth) rr_depth = max_depth - 1;
+    const int32_t n = W * H;
+    std::vector<Reservoir> res[2] = { std::vector<Reservoir>(n), std::vector<Reservoir>(n) };
+    std::vector<RestirInfo> infos[2] = { std::vector<RestirInfo>(n), std::vector<RestirInfo>(n) };
+    for (int k = 0; k < 2; k++)
+        for (int32_t i = 0; i < n; i++) {
+            memset((void*)&res[k][i], 0, sizeof(Reservoir)); res[k][i].y = -1;               // Reservoir's default member initialisers
+            memset((void*)&infos[k][i], 0, sizeof(RestirInfo)); infos[k][i].mtrl_idx = -1; infos[k][i].mesh_id = -1;
+        }
+    std::vector<V3> stale_lightcontrib(n, V3(0.0f));      // ShadowRay::lightcontrib, kept across bounces and frames
+    std::vector<AtnVec4> aov_nd(n), aov_am(n);
+    std::vector<PathState> paths(n);
+    std::vector<Ray> rays(n);
+    const AtnMat4 w2c = camera_w2c(*cam);
+    int cur = 0, target = 0;
+
+    for (int32_t frame = 0; frame < frames; frame++) {
+        for (int32_t idx = 0; idx < n; idx++) {
+            const int32_t x = idx % W, y = idx / W;
+            PathState& st = paths[idx];
+            st.sampler = sampler_for_path((uint32_t)frame, seeds[(uint32_t)idx % seed_count]);
+            const float r1 = st.sampler.next();
+            const float r2 = st.sampler.next();
+            rays[idx] = camera_sample(*cam, (x + r1) / (float)(cam->width), (y + r2) / (float)(cam->height));
+            st.throughput = V3(1.0f); st.pdfb = 1.0f; st.contrib = V3(0.0f);
+            st.terminated = false; st.singular = false; st.last_specular = false;
+            res[cur][idx].clear();
+            infos[cur][idx].clear();
+        }
+        for (int32_t bounce = 0; bounce < max_depth; bounce++) {
+#pragma omp parallel for schedule(dynamic, 64)
+            for (int32_t idx = 0; idx < n; idx++) {
+                PathState& st = paths[idx];
+                if (st.terminated) continue;
+                const Ray ray = rays[idx];
+                AtnHit isect;
+                if (!Traverse(s, ray, kInf, &isect, nullptr)) {
+                    shade_miss(s.view, *cam, idx % W, idx / W, W, H, bounce, ray, &st, &aov_nd[idx], &aov_am[idx]);
+                    continue;
+                }
+                if (bounce == 0) {
+                    Surface sf;
+                    if (!restir_surface(s.view, ray, isect.objid, isect.primid, isect.a, isect.b, isect.t, isect.mtrlid, isect.meshid,
+                                        bounce, w2c, &st, &sf, &infos[cur][idx], &aov_nd[idx], &aov_am[idx]))
+                        continue;
+                    const Mtrl mtrl = fill_material(s.view, sf.mtrlid);
+                    if (!(mtrl.is_singular() || mtrl.is_translucent()))
+                        restir_initial_candidate(&res[cur][idx], mtrl, s.view, sf.p, sf.n, ray.dir, sf.u, sf.v, &st.sampler);
+                    Ray next = ray;
+                    shade_bsdf(s.view, ray.dir, sf, bounce, rr_depth, &st, &next);
+                    rays[idx] = next;
+                }
+                else {
+                    ShadowRayOut sh;
+                    Ray next = ray;
+                    shade_hit(s.view, ray, isect.objid, isect.primid, isect.a, isect.b, isect.t, isect.mtrlid, bounce, rr_depth, &st, &sh, &next);
+                    if (sh.sampled) stale_lightcontrib[idx] = sh.lightcontrib;
+                    if (!st.terminated && sh.active) {
+                        Ray sr; sr.org = sh.org; sr.dir = normalize(sh.dir);
+                        AtnHit shit;
+                        Traverse(s, sr, sh.dist - kEps, &shit, nullptr);
+                        if (shadow_visible(s.view, s.view.lights[sh.light_id], sr, sh.dist, shit.objid, shit.primid, shit.a, shit.b, shit.t, shit.mtrlid))
+                            st.contrib = st.contrib + sh.lightcontrib;
+                    }
+                    rays[idx] = next;
+                }
+            }
+            if (bounce > 0) continue;
+            // visibility of every reservoir's sample
+#pragma omp parallel for schedule(dynamic, 64)
+            for (int32_t idx = 0; idx < n; idx++) {
+                PathState& st = paths[idx];
+                if (st.terminated) continue;
+                Reservoir& r = res[cur][idx];
+                bool reached = false;
+                if (r.valid()) {
+                    V3 org, dir; float dist;
+                    restir_shadow_ray(r, &infos[cur][idx], &org, &dir, &dist);
+                    Ray sr; sr.org = org; sr.dir = normalize(dir);       // aten::ray(org, dir) renormalises
+                    AtnHit shit;
+                    Traverse(s, sr, dist - kEps, &shit, nullptr);
+                    reached = shadow_visible(s.view, s.view.lights[r.y], sr, dist, shit.objid, shit.primid, shit.a, shit.b, shit.t, shit.mtrlid);
+                    if (reached) st.contrib = st.contrib + stale_lightcontrib[idx];
+                }
+                restir_visibility_result(&r, reached);
+            }
+            const int dst = (cur + 1) & 1, prev = (cur + 1) & 1;
+            const int cur_infos = cur;
+            if (frame > 1) {
+#pragma omp parallel for schedule(dynamic, 64)
+                for (int32_t idx = 0; idx < n; idx++) {
+                    if (paths[idx].terminated) continue;
+                    restir_temporal(idx, W, H, s.view, &paths[idx].sampler, &res[cur][idx], infos[cur][idx], res[prev].data(), infos[prev].data(),
+                                    aov_am.data(), motion_depth);
+                }
+            }
+#pragma omp parallel for schedule(dynamic, 64)
+            for (int32_t idx = 0; idx < n; idx++) {
+                if (paths[idx].terminated) continue;
+                restir_spatial(idx, W, H, s.view, &paths[idx].sampler, &res[dst][idx], res[cur].data(), infos[cur].data(), aov_am.data());
+            }
+            for (int32_t idx = 0; idx < n; idx++) {
+                if (paths[idx].terminated) continue;
+                V3 c;
+                if (restir_pixel_color(s.view, res[dst][idx], infos[cur_infos][idx], aov_am[idx], &c)) paths[idx].contrib = paths[idx].contrib + c;
+            }
+            target = dst;
+            cur = (cur + 1) & 1;      // ReuseParams::Update
+        }
+        for (int32_t idx = 0; idx < n; idx++) {
+            const V3 c = paths[idx].contrib;
+            image[idx].x = c.x; image[idx].y = c.y; image[idx].z = c.z; image[idx].w = 1.0f;
+        }
+    }
+    if (reservoirs_out)
+        for (int32_t idx = 0; idx < n; idx++) {
+            const Reservoir& r = res[target][idx];
+            float* o = reservoirs_out + (size_t)idx * 5;
+            o[0] = r.w_sum; o[1] = (float)r.M; o[2] = (float)r.y; o[3] = r.W; o[4] = r.target_pdf;
+        }
     return 0;
 }
 

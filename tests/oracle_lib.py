@@ -228,3 +228,34 @@ def ref_render_svgf(name, W, H, frames=1, depth=5, rr=3, motion=(0.0, 0.0), iter
         imgs = [np.fromfile(f"{prefix}.f{k}.f32", np.float32).reshape(H, W, 4) for k in range(frames)]
         aov = np.fromfile(f"{prefix}.aov.f32", np.float32).reshape(4, H * W, 4)
     return imgs, aov
+
+
+# ---- N1: ReSTIR -----------------------------------------------------------------------------
+def render_restir(scene: sio.Scene, frames=1, max_depth=5, rr_depth=3, motion=None):
+    """CPU restatement of the ReSTIR sequence, frames 0 .. frames-1 (1 sample each).
+    Returns (contribution image of the last frame [H,W,4], reservoirs [H*W,5] = w_sum, M, y, W, target pdf)."""
+    W, H = scene.width, scene.height
+    n = W * H
+    img = np.zeros((n, 4), np.float32)
+    res = np.zeros((n, 5), np.float32)
+    seeds = scene.seeds_for(n)
+    md = None if motion is None else np.ascontiguousarray(motion, np.float32).reshape(n, 4)
+    blob = scene.blob()
+    cam = np.ascontiguousarray(scene.camera)
+    rc = lib().oracle_render_restir(C.byref(blob), C.c_void_p(cam.ctypes.data), C.c_void_p(seeds.ctypes.data), C.c_uint32(len(seeds)),
+                                    C.c_int32(W), C.c_int32(H), C.c_int32(frames), C.c_int32(max_depth), C.c_int32(rr_depth),
+                                    C.c_void_p(md.ctypes.data) if md is not None else None, C.c_void_p(img.ctypes.data),
+                                    C.c_void_p(res.ctypes.data))
+    assert rc == 0
+    return img.reshape(H, W, 4), res
+
+
+def ref_render_restir(name, W, H, frames=1, depth=5, rr=3, motion=(0.0, 0.0)):
+    """The reference's own ReSTIR steps in the device renderer's order (ref_harness restir), one thread:
+    ([frames] contribution images [H,W,4], reservoirs of the last frame [H*W,5])."""
+    with tempfile.TemporaryDirectory() as d:
+        prefix = os.path.join(d, "restir")
+        ref_run("restir", name, W, H, frames, depth, rr, prefix, motion[0], motion[1])
+        imgs = [np.fromfile(f"{prefix}.f{k}.f32", np.float32).reshape(H, W, 4) for k in range(frames)]
+        res = np.fromfile(f"{prefix}.reservoirs.f32", np.float32).reshape(H * W, 5)
+    return imgs, res

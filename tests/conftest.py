@@ -80,6 +80,13 @@ class Golden:
         aov = buf[frames * n * 4:].reshape(4, n, 4)
         return imgs, aov, (0.02, -0.03)
 
+    def restir(self, name, frames=4):
+        """The reference's ReSTIR steps: ([frames, H, W, 4] contribution images, [H*W, 5] final reservoirs, motion)."""
+        m = self.meta[name]
+        n = m["w"] * m["h"]
+        buf = np.frombuffer(_gz(f"{name}.restir.f32.gz"), np.float32)
+        return buf[:frames * n * 4].reshape(frames, m["h"], m["w"], 4), buf[frames * n * 4:].reshape(n, 5), (0.02, -0.03)
+
     def hits(self, name):
         return np.frombuffer(_gz(f"{name}.hits.gz"), self.sio.HIT_DTYPE)
 

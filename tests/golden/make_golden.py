@@ -76,11 +76,28 @@ def make_svgf():
         print(name, "svgf", [float(i[..., :3].mean()) for i in imgs])
 
 
+RESTIR_SCENES = ("cornell_mtrl", "instanced", "sponza_atrium")
+RESTIR_FRAMES = 4
+
+
+def make_restir():
+    """Contribution images of frames 0..3 and the final reservoirs from the reference's own ReSTIR steps run in the
+    device renderer's order (ref_harness restir), with the same constant motion vector as the SVGF fixtures."""
+    for name in RESTIR_SCENES:
+        W, H = SCENES[name]
+        imgs, res = ol.ref_render_restir(name, W, H, frames=RESTIR_FRAMES, motion=SVGF_MOTION)
+        gz_write(os.path.join(HERE, f"{name}.restir.f32.gz"), np.stack(imgs).tobytes() + res.tobytes())
+        print(name, "restir", [float(i[..., :3].mean()) for i in imgs])
+
+
 def main():
     if not ol.have_ref():
         sys.exit("oracle/_ref is not built: run python oracle/build_ref.py")
     if len(sys.argv) > 1 and sys.argv[1] == "svgf":     # only the SVGF fixtures (the others are unchanged)
         make_svgf()
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "restir":   # only the ReSTIR fixtures
+        make_restir()
         return
     meta = {}
     with tempfile.TemporaryDirectory() as d:
@@ -111,6 +128,7 @@ def main():
         print(name, meta[name])
     json.dump(meta, open(os.path.join(HERE, "meta.json"), "w"), indent=1, sort_keys=True)
     make_svgf()
+    make_restir()
 
 
 if __name__ == "__main__":

@@ -25,6 +25,7 @@ EXPORTS = [
     "atn_set_profiling", "atn_get_stream", "atn_trace_closest", "atn_trace_any", "atn_trace_closest_device",
     "atn_trace_any_device", "atn_set_bounce_tap", "atn_trace_closest_static", "atn_readback_aov", "atn_render_ao",
     "atn_render_svgf", "atn_set_motion_depth", "atn_readback_svgf", "atn_update_texture",
+    "atn_render_restir", "atn_readback_restir",
 ]
 
 
@@ -187,6 +188,17 @@ class PathTracing:
         pixel + temporal reprojection + variance estimation + a-trous filter.  Frame 0 starts a sequence."""
         _check(self._lib, self._lib.atn_render_svgf(self._h, C.c_int32(width), C.c_int32(height), C.c_int32(maxBounce),
                                                     C.c_int32(rrBounce), C.c_int32(atrous_iters)))
+
+    def render_restir(self, width: int, height: int, maxBounce: int, rrBounce: int = 3):
+        """One frame of idaten::ReSTIRPathTracing::OnRender (reference src/libidaten/restir/restir.cpp:47-123)."""
+        _check(self._lib, self._lib.atn_render_restir(self._h, C.c_int32(width), C.c_int32(height), C.c_int32(maxBounce), C.c_int32(rrBounce)))
+
+    def readback_restir(self) -> np.ndarray:
+        """float32 [h*w, 5]: w_sum, M, y, W, target pdf of the reservoirs behind the last frame's pixel colours."""
+        n = self.width * self.height
+        out = np.empty((n, 5), np.float32)
+        _check(self._lib, self._lib.atn_readback_restir(self._h, C.c_void_p(out.ctypes.data), C.c_size_t(n)))
+        return out
 
     def set_motion_depth(self, motion: np.ndarray | None):
         """SetMotionDepthBuffer without the GL frame buffer: float32 [h*w, 4] motion vectors in .xy, or None."""

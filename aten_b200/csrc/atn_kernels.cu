@@ -37,6 +37,7 @@
 
 #include "atn_math.cuh"
 #include "atn_svgf.cuh"
+#include "atn_restir.cuh"
 #include "atn_bvh.h"
 
 using namespace atn;
@@ -844,10 +845,10 @@ k_nee(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuff
         pb.sampler_dim[slot] = st.sampler.dim;
         // dist < 0 marks "no shadow ray"
         pb.sh_o[slot] = make_float4(sh.org.x, sh.org.y, sh.org.z, sh.active ? sh.dist : -1.0f);
-        if (sh.active) {
-            pb.sh_d[slot] = make_float4(sh.dir.x, sh.dir.y, sh.dir.z, __int_as_float(sh.light_id));
-            pb.sh_c[slot] = make_float4(sh.lightcontrib.x, sh.lightcontrib.y, sh.lightcontrib.z, 0.0f);
-        }
+        if (sh.active) pb.sh_d[slot] = make_float4(sh.dir.x, sh.dir.y, sh.dir.z, __int_as_float(sh.light_id));
+        // ShadowRay::lightcontrib is reset whenever a light was sampled (FillShadowRay, pathtracing_impl.h:241) and stays
+        // in the buffer: the ReSTIR visibility step of the next frame adds it again (restir_shadow_ray)
+        if (sh.sampled) pb.sh_c[slot] = make_float4(sh.lightcontrib.x, sh.lightcontrib.y, sh.lightcontrib.z, 0.0f);
     }
 }
 
@@ -1101,6 +1102,195 @@ __global__ void k_fill_vec4(float4* p, size_t n, float4 v)
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
 }
 
+// ---------------------------------------------------------------------------------------------
+// N1: ReSTIR renderer on the same path (idaten::ReSTIRPathTracing, src/libidaten/restir/restir.cpp:47-123, restir.cu,
+// restir_reuse.cu; per-pixel steps shared with aten::ReSTIRRenderer in restir_impl.h -> atn_restir.cuh).  Bounce 0 of a
+// frame: k_restir_begin (hit evaluation, ReSTIRInfo, AOVs, implicit light), k_restir_candidate (one light candidate
+// into the pixel's reservoir), k_bsdf (as on the path-tracing path), k_restir_visibility + the shadow traversal,
+// k_restir_temporal (frames > 1), k_restir_spatial, k_restir_color.  Bounces > 0 are the path tracer's.
+// ---------------------------------------------------------------------------------------------
+struct RestirView {
+    Reservoir* cur; Reservoir* other;           // other = previous frame's reservoirs, then the spatial destination
+    RestirInfo* info_cur; RestirInfo* info_other;
+    const AtnVec4* motion_depth;
+};
+
+__global__ void __launch_bounds__(kShadeBlock)
+k_restir_begin(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, RestirView rv, Counters* cnt, AtnMat4 w2c)
+{
+    const int count = fp.width * fp.height;
+    const int rounds = (count + blockDim.x * gridDim.x - 1) / (blockDim.x * gridDim.x);
+    for (int it = 0; it < rounds; it++) {
+        const int slot = (it * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+        bool lit = false;
+        if (slot < count) {
+            const float4 o = pb.ray_o[slot];
+            const float4 d = pb.ray_d[slot];
+            const float4 h0 = pb.hit0[slot];
+            const int2 h1 = pb.hit1[slot];
+            const float4 th = pb.throughput[slot];
+            const float4 cb = pb.contrib[slot];
+            Ray ray; ray.org = V3(o.x, o.y, o.z); ray.dir = V3(d.x, d.y, d.z);
+            PathState st;
+            st.throughput = V3(th.x, th.y, th.z); st.pdfb = th.w;
+            st.contrib = V3(cb.x, cb.y, cb.z);
+            st.terminated = false; st.singular = false;
+            AtnVec4* aov_nd = reinterpret_cast<AtnVec4*>(pb.aov_nd) + slot;
+            AtnVec4* aov_am = reinterpret_cast<AtnVec4*>(pb.aov_am) + slot;
+            rv.cur[slot].clear();                               // InitReSTIR (restir.cu:18-34)
+            RestirInfo info = rv.info_cur[slot];
+            info.clear();
+            if (h1.x >= 0) {
+                Surface sf;
+                lit = restir_surface(sc, ray, h1.x, __float_as_int(h0.w), h0.y, h0.z, h0.x, h1.y, pb.hit_mesh[slot], 0, w2c, &st, &sf,
+                                     &info, aov_nd, aov_am);
+                if (lit) {
+                    pb.surf0[slot] = make_float4(sf.p.x, sf.p.y, sf.p.z, sf.u);
+                    pb.surf1[slot] = make_float4(sf.n.x, sf.n.y, sf.n.z, sf.v);
+                    pb.surf2[slot] = make_float4(sf.albedo.x, sf.albedo.y, sf.albedo.z, __int_as_float(sf.mtrlid));
+                }
+            }
+            else {
+                shade_miss(sc, cam, slot % fp.width, slot / fp.width, fp.width, fp.height, 0, ray, &st, aov_nd, aov_am);
+            }
+            rv.info_cur[slot] = info;
+            if (!lit) {
+                pb.contrib[slot] = make_float4(st.contrib.x, st.contrib.y, st.contrib.z, cb.w);
+                pb.flags[slot] = 1u;
+            }
+        }
+        const int pos = warp_append(lit, &cnt->n_lit[0]);
+        if (lit) pb.q_lit[pos] = slot;
+    }
+}
+
+// GenerateInitialCandidate for the lit paths; no path-traced shadow ray at this bounce
+__global__ void __launch_bounds__(kShadeBlock)
+k_restir_candidate(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb, RestirView rv, Counters* cnt)
+{
+    const int count = cnt->n_lit[0];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const int slot = pb.q_lit[i];
+        const float4 d = pb.ray_d[slot];
+        const float4 s0 = pb.surf0[slot];
+        const float4 s1 = pb.surf1[slot];
+        const float4 s2 = pb.surf2[slot];
+        const Mtrl mtrl = fill_material(sc, __float_as_int(s2.w));
+        if (!(mtrl.is_singular() || mtrl.is_translucent())) {
+            Sampler sp = path_sampler(fp, seeds, pb, slot);
+            Reservoir res = rv.cur[slot];
+            restir_initial_candidate(&res, mtrl, sc, V3(s0.x, s0.y, s0.z), V3(s1.x, s1.y, s1.z), V3(d.x, d.y, d.z), s0.w, s1.w, &sp);
+            rv.cur[slot] = res;
+            pb.sampler_dim[slot] = sp.dim;
+        }
+        float4 so = pb.sh_o[slot];
+        so.w = -1.0f;
+        pb.sh_o[slot] = so;
+    }
+}
+
+// EvaluateVisibility, first half: the shadow ray of every live pixel whose reservoir holds a sample
+__global__ void __launch_bounds__(kShadeBlock)
+k_restir_visibility(FrameParams fp, PathBuffers pb, RestirView rv, Counters* cnt)
+{
+    const int count = fp.width * fp.height;
+    const int rounds = (count + blockDim.x * gridDim.x - 1) / (blockDim.x * gridDim.x);
+    for (int it = 0; it < rounds; it++) {
+        const int slot = (it * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+        bool shadow = false;
+        if (slot < count && (pb.flags[slot] & 1u) == 0u) {
+            Reservoir& res = rv.cur[slot];
+            if (res.valid()) {
+                RestirInfo info = rv.info_cur[slot];
+                V3 org, dir; float dist;
+                restir_shadow_ray(res, &info, &org, &dir, &dist);
+                rv.info_cur[slot].point_to_light = info.point_to_light;
+                pb.sh_o[slot] = make_float4(org.x, org.y, org.z, dist);
+                pb.sh_d[slot] = make_float4(dir.x, dir.y, dir.z, __int_as_float(res.y));
+                shadow = true;
+            }
+            else restir_visibility_result(&res, false);
+        }
+        const int spos = warp_append(shadow, &cnt->n_shadow[0]);
+        if (shadow) pb.q_shadow[spos] = slot;
+    }
+}
+
+// the shadow traversal of that step: ShadowPolicy's decision (HitShadowRay adds the buffered lightcontrib when the
+// light is reached) + the second half of EvaluateVisibility
+struct RestirShadowPolicy {
+    ShadowPolicy<false> base;
+    Reservoir* res;
+    __device__ __forceinline__ void world(int slot, V3* o, V3* d) const { base.world(slot, o, d); }
+    __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* t_max, int* mode, float* exit_dist) const
+    {
+        base.load(i, slot, o, d, t_max, mode, exit_dist);
+    }
+    __device__ __forceinline__ void finish(const BvhView& bv, int slot, const TraceResult& r) const
+    {
+        const float4 so = base.pb.sh_o[slot];
+        const float4 sd = base.pb.sh_d[slot];
+        const AtnLightParameter& light = base.sc.lights[__float_as_int(sd.w)];
+        Ray sr; sr.org = V3(so.x, so.y, so.z); sr.dir = normalize(V3(sd.x, sd.y, sd.z));
+        int32_t objid, primid, mtrlid, meshid;
+        resolve_hit(bv, r, &objid, &primid, &mtrlid, &meshid);
+        const bool vis = shadow_visible(base.sc, light, sr, so.w, objid, primid, r.a, r.b, r.t, mtrlid);
+        if (vis) {
+            const float4 c = base.pb.sh_c[slot];
+            float4 cc = base.pb.contrib[slot];
+            cc.x += c.x; cc.y += c.y; cc.z += c.z;
+            base.pb.contrib[slot] = cc;
+        }
+        restir_visibility_result(&res[slot], vis);
+    }
+};
+
+__global__ void __launch_bounds__(kShadeBlock)
+k_restir_temporal(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb, RestirView rv)
+{
+    const int n = fp.width * fp.height;
+    for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n; slot += gridDim.x * blockDim.x) {
+        if (pb.flags[slot] & 1u) continue;
+        Sampler sp = path_sampler(fp, seeds, pb, slot);
+        Reservoir res = rv.cur[slot];
+        restir_temporal(slot, fp.width, fp.height, sc, &sp, &res, rv.info_cur[slot], rv.other, rv.info_other,
+                        reinterpret_cast<const AtnVec4*>(pb.aov_am), rv.motion_depth);
+        rv.cur[slot] = res;
+        pb.sampler_dim[slot] = sp.dim;
+    }
+}
+
+__global__ void __launch_bounds__(kShadeBlock)
+k_restir_spatial(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb, RestirView rv)
+{
+    const int n = fp.width * fp.height;
+    for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n; slot += gridDim.x * blockDim.x) {
+        if (pb.flags[slot] & 1u) continue;
+        Sampler sp = path_sampler(fp, seeds, pb, slot);
+        Reservoir res = rv.other[slot];
+        restir_spatial(slot, fp.width, fp.height, sc, &sp, &res, rv.cur, rv.info_cur, reinterpret_cast<const AtnVec4*>(pb.aov_am));
+        rv.other[slot] = res;
+        pb.sampler_dim[slot] = sp.dim;
+    }
+}
+
+__global__ void __launch_bounds__(kShadeBlock)
+k_restir_color(FrameParams fp, SceneView sc, PathBuffers pb, RestirView rv)
+{
+    const int n = fp.width * fp.height;
+    for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < n; slot += gridDim.x * blockDim.x) {
+        if (pb.flags[slot] & 1u) continue;
+        const float4 am = pb.aov_am[slot];
+        AtnVec4 a; a.x = am.x; a.y = am.y; a.z = am.z; a.w = am.w;
+        V3 c;
+        if (restir_pixel_color(sc, rv.other[slot], rv.info_cur[slot], a, &c)) {
+            float4 cc = pb.contrib[slot];
+            cc.x += c.x; cc.y += c.y; cc.z += c.z;
+            pb.contrib[slot] = cc;
+        }
+    }
+}
+
 // pt::gather (pathtracing_impl.cu:282-324) / FilmProgressive::put (film.cpp:61-71)
 __global__ void k_gather(FrameParams fp, PathBuffers pb, float4* image, int progressive, const Counters* cnt, Totals* totals)
 {
@@ -1215,6 +1405,10 @@ struct AtnRenderer {
     int svgf_cv_plane[2]{ 2, 6 };      // which plane holds color_variance of each AOV set (swaps with the scratch plane)
     int svgf_scratch_plane{ 11 };
     bool svgf_has_motion{ false };
+    DevBuf<Reservoir> restir_res[2];           // ReSTIR (N1): reservoirs and infos of the current / other frame
+    DevBuf<RestirInfo> restir_info[2];
+    int restir_cur{ 0 }, restir_target{ 0 };
+    size_t restir_pixels{ 0 };
     cudaTextureObject_t svgf_tex{ 0 };  // linear float4 texture over svgf_planes (a-trous taps, ATN_SVGF_TEX)
     size_t svgf_pixels{ 0 };
 
@@ -1292,6 +1486,7 @@ static int alloc_paths(AtnRenderer* r, size_t n)
     CUDA_TRY(r->throughput.resize(n)); CUDA_TRY(r->contrib.resize(n)); CUDA_TRY(r->sampler_dim.resize(n));
     CUDA_TRY(r->flags.resize(n)); CUDA_TRY(r->queue0.resize(n)); CUDA_TRY(r->queue1.resize(n));
     CUDA_TRY(r->sh_o.resize(n)); CUDA_TRY(r->sh_d.resize(n)); CUDA_TRY(r->sh_c.resize(n));
+    CUDA_TRY(cudaMemsetAsync(r->sh_c.p, 0, n * sizeof(float4), r->stream));      // ShadowRay::lightcontrib starts at zero
     CUDA_TRY(r->q_lit.resize(n)); CUDA_TRY(r->q_shadow.resize(n));
     CUDA_TRY(r->hit_mesh.resize(n)); CUDA_TRY(r->aov_nd.resize(n)); CUDA_TRY(r->aov_am.resize(n));
     CUDA_TRY(r->surf0.resize(n)); CUDA_TRY(r->surf1.resize(n)); CUDA_TRY(r->surf2.resize(n));
@@ -1562,12 +1757,12 @@ ATN_API int atn_synchronize(AtnRenderer* r)
 // The bounce loop of one camera sample: closest hit, the three shade stages, shadow rays.
 // `svgf_w2c` != nullptr: the SVGF shade variant (pb.aov_nd / pb.aov_am then point at the SVGF AOV set).
 static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffers& pb, bool tap_now, const AtnMat4* svgf_w2c,
-                          size_t* ev_i, uint64_t* launches)
+                          size_t* ev_i, uint64_t* launches, int first_bounce = 0)
 {
     cudaStream_t s = r->stream;
     AtnMat4 w2c;
     for (int i = 0; i < 16; i++) w2c.m[i] = svgf_w2c ? svgf_w2c->m[i] : 0.0f;
-    for (int b = 0; b < fp.max_bounce; b++) {
+    for (int b = first_bounce; b < fp.max_bounce; b++) {
         Counters* c = r->counters.p;
         const int32_t* q = (b == 0) ? nullptr : pb.queue[b & 1];
         const float tmax = (b == 0) ? kInf : r->hit_distance_limit;
@@ -1880,6 +2075,131 @@ ATN_API int atn_readback_svgf(AtnRenderer* r, AtnVec4* normal_depth, AtnVec4* al
     for (int k = 0; k < 4; k++)
         if (dst[k]) CUDA_TRY(cudaMemcpyAsync(dst[k], src[k], pixel_count * sizeof(AtnVec4), cudaMemcpyDeviceToHost, r->stream));
     CUDA_TRY(cudaStreamSynchronize(r->stream));
+    return ATN_OK;
+}
+
+// ---- N1: ReSTIR --------------------------------------------------------------------------------
+__global__ void k_restir_init(Reservoir* res0, Reservoir* res1, RestirInfo* info0, RestirInfo* info1, size_t n)
+{
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        Reservoir r;
+        r.w_sum = 0.0f; r.M = 0; r.y = -1; r.W = 0.0f; r.target_pdf = 0.0f;
+        r.ls.pos = V3(0.0f); r.ls.dir = V3(0.0f); r.ls.dist = 0.0f; r.ls.nml = V3(0.0f); r.ls.color = V3(0.0f); r.ls.pdf = 0.0f; r.ls.attrib = 0;
+        RestirInfo f;
+        f.clear(); f.point_to_light = V3(0.0f); f.p = V3(0.0f); f.throughput = V3(0.0f);
+        res0[i] = r; res1[i] = r; info0[i] = f; info1[i] = f;
+    }
+}
+
+ATN_API int atn_render_restir(AtnRenderer* r, int32_t width, int32_t height, int32_t max_bounce, int32_t rr_bounce)
+{
+    if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_restir: NULL handle");
+    if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_render_restir: no scene uploaded");
+    if (width != r->width || height != r->height)
+        return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_restir: size %dx%d differs from the uploaded %dx%d", width, height, r->width, r->height);
+    if (max_bounce < 1 || max_bounce > kMaxBounce) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_restir: max_bounce %d not in [1,%d]", max_bounce, kMaxBounce);
+    if (rr_bounce > max_bounce) rr_bounce = max_bounce - 1;       // restir.cpp (host) :333-335
+    if (r->tap_host) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_restir: the bounce tap is not available on this renderer");
+    if (r->sv.light_count <= 0) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_restir: the scene has no light");
+    CUDA_TRY(cudaSetDevice(r->device));
+    cudaStream_t s = r->stream;
+    const size_t n = (size_t)width * height;
+    const int grid = (int)std::min<size_t>((n + 255) / 256, (size_t)r->sm_count * 8);
+    const int sgrid = r->sm_count * 8;
+
+    if (r->restir_pixels != n || !r->restir_res[0].p) {
+        if (r->frame != 0) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_restir: no history for frame %u (start at frame 0: atn_set_frame(0))", r->frame);
+        for (int k = 0; k < 2; k++) { CUDA_TRY(r->restir_res[k].resize(n)); CUDA_TRY(r->restir_info[k].resize(n)); }
+        r->restir_pixels = n;
+    }
+    if (r->frame == 0) {
+        k_restir_init<<<sgrid, 256, 0, s>>>(r->restir_res[0].p, r->restir_res[1].p, r->restir_info[0].p, r->restir_info[1].p, n);
+        CUDA_TRY(cudaMemsetAsync(r->sh_c.p, 0, n * sizeof(float4), s));          // ShadowRay::lightcontrib of a new sequence
+        r->restir_cur = 0;
+    }
+    if (r->svgf_has_motion && r->svgf_motion.n < n) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_restir: motion buffer smaller than the image");
+
+    FrameParams fp;
+    fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height;
+    fp.max_bounce = max_bounce; fp.rr_bounce = rr_bounce; fp.seed_count = r->seed_count;
+    fp.frame = r->frame;
+    const int cur = r->restir_cur, other = (cur + 1) & 1;
+    RestirView rv;
+    rv.cur = r->restir_res[cur].p; rv.other = r->restir_res[other].p;
+    rv.info_cur = r->restir_info[cur].p; rv.info_other = r->restir_info[other].p;
+    rv.motion_depth = r->svgf_has_motion ? reinterpret_cast<const AtnVec4*>(r->svgf_motion.p) : nullptr;
+    const PathBuffers& pb = r->pb;
+    const AtnMat4 w2c = camera_w2c(r->camera);
+    Counters* c = r->counters.p;
+
+    const size_t n_ev = r->profiling ? (size_t)max_bounce * 4 : 0;
+    while (r->trace_events.size() < n_ev) { cudaEvent_t ev; CUDA_TRY(cudaEventCreate(&ev)); r->trace_events.push_back(ev); }
+    size_t ev_i = 0;
+    uint64_t launches = 0;
+    CUDA_TRY(cudaMemsetAsync(r->totals.p, 0, sizeof(Totals), s));
+    CUDA_TRY(cudaMemsetAsync(r->visits.p, 0, sizeof(Visits), s));
+    CUDA_TRY(cudaEventRecord(r->ev0, s));
+    CUDA_TRY(cudaMemsetAsync(c, 0, sizeof(Counters), s));
+    k_generate<<<grid, 256, 0, s>>>(fp, r->camera, r->seeds.p, pb, c);
+    // bounce 0
+    {
+        ClosestPolicy pol{ pb, nullptr, kInf, pb.hit_mesh };
+        launch_trace<ClosestPolicy>(r, s, pol, &c->n_active[0], 0, &c->fetch_closest[0], r->visits.p);
+    }
+    k_restir_begin<<<sgrid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, pb, rv, c, w2c);
+    k_restir_candidate<<<sgrid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, rv, c);
+    k_bsdf<false><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, 0, nullptr, 0);
+    k_restir_visibility<<<sgrid, kShadeBlock, 0, s>>>(fp, pb, rv, c);
+    {
+        RestirShadowPolicy pol{ ShadowPolicy<false>{ pb, r->sv, nullptr, 0, 0 }, rv.cur };
+        launch_trace<RestirShadowPolicy>(r, s, pol, &c->n_shadow[0], 0, &c->fetch_shadow[0], r->visits.p);
+    }
+    launches += 7;
+    if (r->frame > 1) { k_restir_temporal<<<sgrid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, rv); launches++; }
+    k_restir_spatial<<<sgrid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, rv);
+    k_restir_color<<<sgrid, kShadeBlock, 0, s>>>(fp, r->sv, pb, rv);
+    launches += 2;
+    r->restir_target = other;
+    r->restir_cur = other;                                   // ReuseParams::Update
+    // bounces > 0: the path tracer's
+    const int rc = launch_bounces(r, fp, pb, false, nullptr, &ev_i, &launches, 1);
+    if (rc != ATN_OK) return rc;
+    // one frame per call: without progressive accumulation the image holds this frame alone
+    if (!r->progressive) CUDA_TRY(cudaMemsetAsync(r->image.p, 0, n * sizeof(float4), s));
+    k_gather<<<grid, 256, 0, s>>>(fp, pb, r->image.p, r->progressive, c, r->totals.p);
+    launches++;
+    CUDA_TRY(cudaEventRecord(r->ev1, s));
+    CUDA_TRY(cudaGetLastError());
+
+    Totals ht; Visits hv;
+    CUDA_TRY(cudaMemcpyAsync(&ht, r->totals.p, sizeof(Totals), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaMemcpyAsync(&hv, r->visits.p, sizeof(Visits), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    r->stats.closest_rays = ht.closest; r->stats.shadow_rays = ht.shadow;
+    r->stats.nodes_visited = hv.nodes; r->stats.tris_tested = hv.tris;
+    r->stats.camera_samples = (uint64_t)n;
+    r->stats.kernel_launches = launches;
+    float ms = 0.0f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
+    r->stats.device_ms = ms;
+    r->stats.trace_ms = 0.0f;
+    r->frame += 1u;
+    return ATN_OK;
+}
+
+ATN_API int atn_readback_restir(AtnRenderer* r, float* reservoirs, size_t pixel_count)
+{
+    if (!r || !reservoirs) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_readback_restir: NULL argument");
+    if (!r->restir_res[0].p || r->frame == 0) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_readback_restir: no ReSTIR frame rendered");
+    if (pixel_count != r->restir_pixels) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_readback_restir: pixel_count mismatch");
+    CUDA_TRY(cudaSetDevice(r->device));
+    std::vector<Reservoir> host(pixel_count);
+    CUDA_TRY(cudaMemcpyAsync(host.data(), r->restir_res[r->restir_target].p, pixel_count * sizeof(Reservoir), cudaMemcpyDeviceToHost, r->stream));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
+    for (size_t i = 0; i < pixel_count; i++) {
+        float* o = reservoirs + i * 5;
+        o[0] = host[i].w_sum; o[1] = (float)host[i].M; o[2] = (float)host[i].y; o[3] = host[i].W; o[4] = host[i].target_pdf;
+    }
     return ATN_OK;
 }
 

@@ -280,6 +280,18 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
  * (svgf_impl.h:438-544), so its result depends on the pixel order; this entry point computes the
  * order-independent form (every pixel reads the unfiltered colours) -- DESIGN.md "SVGF". */
 ATN_API int atn_render_svgf(AtnRenderer* r, int32_t width, int32_t height, int32_t max_bounce, int32_t rr_bounce, int32_t atrous_iters);
+/* Row N1 of SURVEY 8f, third renderer on the path: ReSTIR (reservoir-based spatiotemporal importance resampling of the
+ * direct light at the first hit).  idaten::ReSTIRPathTracing::OnRender (src/libidaten/restir/restir.cpp:47-123, restir.cu,
+ * restir_reuse.cu); per-pixel steps = restir_impl.h + aten::ReSTIRRenderer::Shade (src/libaten/renderer/restir/restir.cpp:100-241).
+ * ONE frame of one sample per call: camera ray, first hit -> ReSTIRInfo + AOVs (shading normal, clip-space depth, mesh id),
+ * one light candidate per pixel, visibility of the kept sample, temporal reuse against the previous frame's reservoirs
+ * (frames > 1, through the motion vectors of atn_set_motion_depth), 3x3 spatial reuse, pixel colour; the remaining
+ * bounces are the path tracer's.  Frame 0 starts a sequence (atn_set_frame(0)); the counter advances by 1.  The image
+ * accumulates like atn_render with progressive mode on, and holds this frame alone with it off. */
+ATN_API int atn_render_restir(AtnRenderer* r, int32_t width, int32_t height, int32_t max_bounce, int32_t rr_bounce);
+/* The reservoirs the last frame's pixel colours were computed from (AT_NAME::Reservoir, restir_types.h:6-57), five floats
+ * per pixel: w_sum, M, y (light index, -1 none), W, target pdf. */
+ATN_API int atn_readback_restir(AtnRenderer* r, float* reservoirs, size_t pixel_count);
 /* Replaces SVGFPathTracing::SetMotionDepthBuffer / SVGFRenderer::SetMotionDepthBuffer(aten::FBO&) (svgf.cpp:451-459),
  * which read a GL frame buffer: W*H motion vectors in .xy (fractions of the screen, added to the pixel position to
  * find it in the previous frame, svgf_impl.h:325-326).  NULL: static camera (zero motion). */

@@ -370,4 +370,37 @@ private:
     int32_t atrous_iters_{ 5 };
 };
 
+/// idaten::ReSTIRPathTracing (src/libidaten/restir/restir.h): one render() call = one frame of the ReSTIR sequence.
+class ReSTIRPathTracing : public PathTracing {
+public:
+    enum class Mode { ReSTIR, PT, AOVar };
+    using PathTracing::PathTracing;
+
+    Mode GetMode() const { return mode_; }
+    void SetMode(Mode mode)
+    {
+        if (mode == Mode::AOVar) throw std::runtime_error("idaten_b200::ReSTIRPathTracing: Mode::AOVar (debug display) is not implemented");
+        const Mode prev = mode_;
+        mode_ = mode;
+        if (prev != mode_) reset();
+    }
+
+    /// ReSTIRPathTracing::OnRender (restir.cpp:47-123); one sample per frame, as every caller of the reference passes
+    void render(int32_t width, int32_t height, int32_t maxSamples, int32_t maxBounce)
+    {
+        if (mode_ == Mode::PT) { PathTracing::render(width, height, maxSamples, maxBounce); return; }
+        if (maxSamples != 1) throw std::runtime_error("idaten_b200::ReSTIRPathTracing::render: maxSamples must be 1");
+        Check(atn_render_restir(h_, width, height, maxBounce, /*rrBounce (restir.cpp:53)*/ 3));
+    }
+
+    /// Stands in for SetGBuffer(gltexGbuffer, gltexMotionDepthbuffer): W*H float4, .xy = motion in screen fractions.
+    void SetMotionDepthBuffer(const aten::vec4* motion_depth, size_t pixel_count)
+    {
+        Check(atn_set_motion_depth(h_, reinterpret_cast<const AtnVec4*>(motion_depth), pixel_count));
+    }
+
+private:
+    Mode mode_{ Mode::ReSTIR };
+};
+
 }  // namespace idaten_b200

@@ -108,6 +108,42 @@ def svgf_bench(name, W, H, frames=8, warmup=1, label=""):
                                         "sample": f"stock aten::SVGFRenderer, {name} 480x270, 3 frames, {info['threads']} threads"}}), flush=True)
 
 
+def restir_bench(name, W, H, frames=8, warmup=1, label=""):
+    """Row N1: the ReSTIR renderer, a sequence of `frames` frames (1 sample per pixel each) from frame 0."""
+    scene = ol.ref_scene(name, W, H)
+    r = PathTracing(0)
+    r.UpdateSceneData(scene)
+    r.SetEnableProgressive(False)
+    for _ in range(warmup):
+        r.set_frame(0)
+        for f in range(frames):
+            r.render_restir(W, H, 5, 3)
+    r.set_frame(0)
+    ms = rays = 0
+    for f in range(frames):
+        r.render_restir(W, H, 5, 3)
+        st = r.stats()
+        if f > 1:       # frames 0 and 1 have no temporal pass
+            ms += st["device_ms"]; rays += st["closest_rays"] + st["shadow_rays"]
+    img = r.readback()
+    pt_ms = 0
+    for f in range(2, frames):
+        r.set_frame(f); r.render(W, H, 1, 5, 3)
+        pt_ms += r.stats()["device_ms"]
+    r.close()
+    n = frames - 2
+    import time
+    t0 = time.perf_counter()
+    ol.ref_render_restir(name, 480, 270, frames=3)
+    ref_s = time.perf_counter() - t0
+    print(json.dumps({"config": label, "renderer": "restir", "scene": name, "w": W, "h": H, "frames": frames,
+                      "ms_per_frame": round(ms / n, 3), "path_tracer_same_frame_ms": round(pt_ms / n, 3),
+                      "frames_per_s": round(1e3 * n / ms, 1), "msamples_per_s": round(W * H * n / ms / 1e3, 1),
+                      "mrays_per_s": round(rays / ms / 1e3, 1), "finite": bool(np.isfinite(img).all()),
+                      "reference_cpu": {"msamples_per_s": round(480 * 270 * 3 / ref_s / 1e6, 4),
+                                        "sample": f"the reference's ReSTIR steps (ref_harness restir), {name} 480x270, 3 frames, 1 thread, incl. scene build"}}), flush=True)
+
+
 def ray_stress(name, n_rays, label=""):
     """Incoherent diffuse secondary rays: origins = surface points found by a first random pass,
     directions cosine-distributed about nothing in particular (uniform sphere), closest-hit and any-hit."""
@@ -169,6 +205,9 @@ def main():
     if not ol.have_ref():
         sys.exit("oracle/_ref not present")
     q = a.quick
+    if a.only == "restir":
+        restir_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 4, label="N1 ReSTIR, sponza_lod 1080p, 8-frame sequence")
+        return
     if a.only == "svgf":
         svgf_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 3, label="N1 SVGF, sponza_lod 1080p, 8-frame sequence")
         return
@@ -179,6 +218,7 @@ def main():
     render_bench("dragon_grid10", 1920, 1080, 4 if not q else 1, label="C5 stand-in (rendered): 100 instanced dragons = 10 M triangles, 1080p 4spp")
     ao_bench("sponza_atrium", 1920, 1080, 16 if not q else 2, label="N1 ambient occlusion, sponza_lod 1080p 16spp")
     svgf_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 3, label="N1 SVGF, sponza_lod 1080p, 8-frame sequence")
+    restir_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 4, label="N1 ReSTIR, sponza_lod 1080p, 8-frame sequence")
     ray_stress("dragon_grid10", 100_000_000 if not q else 5_000_000,
                label="C5 stand-in: 100 M incoherent secondary rays into 100 instanced dragons (10 M triangles), closest-hit and any-hit")
 

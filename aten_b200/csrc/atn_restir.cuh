@@ -121,10 +121,15 @@ ATN_HD void restir_visibility_result(Reservoir* res, bool reached)
     if (!reached) { res->w_sum = 0.0f; res->W = 0.0f; res->target_pdf = 0.0f; res->y = -1; }     // M is kept (restir_impl.h:201-210)
 }
 
-// restir::_detail::IsAcceptableNeighbor (restir_impl.h:212-228)
-ATN_HD bool restir_acceptable(const Mtrl& m, int32_t mesh_id, const V3& n, const Mtrl& nm, int32_t n_mesh_id, const V3& nn)
+// restir::_detail::IsAcceptableNeighbor (restir_impl.h:212-228).  Only the TYPE of the neighbour's material takes part,
+// so the neighbour's 248-byte MaterialParameter is not copied (FillMaterial of an invalid id yields a Diffuse material).
+ATN_HD int32_t restir_material_type(const SceneView& sc, int32_t mtrl_idx)
 {
-    return (m.type == nm.type) && (mesh_id == n_mesh_id) && (dot(n, nn) >= 0.95f);
+    return mtrl_idx >= 0 ? sc.materials[mtrl_idx].type : (int32_t)ATN_MTRL_DIFFUSE;
+}
+ATN_HD bool restir_acceptable(const Mtrl& m, int32_t mesh_id, const V3& n, int32_t n_type, int32_t n_mesh_id, const V3& nn)
+{
+    return ((int32_t)m.type == n_type) && (mesh_id == n_mesh_id) && (dot(n, nn) >= 0.95f);
 }
 
 // restir::ApplyTemporalReuse (restir_impl.h:230-346).  `motion` = the centre pixel's motion vector (xy).
@@ -151,8 +156,7 @@ ATN_HD void restir_temporal(int32_t idx, int32_t width, int32_t height, const Sc
         if (nr.valid()) {
             const RestirInfo& ni = prev_infos[nidx];
             const bool valid_mtrl = ni.mtrl_idx >= 0;
-            const Mtrl nm = fill_material(sc, ni.mtrl_idx);
-            acceptable = valid_mtrl && restir_acceptable(mtrl, mesh_id, normal, nm, ni.mesh_id, ni.nml);
+            acceptable = valid_mtrl && restir_acceptable(mtrl, mesh_id, normal, restir_material_type(sc, ni.mtrl_idx), ni.mesh_id, ni.nml);
             if (acceptable) {
                 const int32_t light_pos = nr.y;
                 const AtnLightParameter& light = sc.lights[light_pos];
@@ -197,9 +201,8 @@ ATN_HD void restir_spatial(int32_t idx, int32_t width, int32_t height, const Sce
             if (!nr.valid()) continue;
             const RestirInfo& ni = infos[nidx];
             const bool valid_mtrl = ni.mtrl_idx >= 0;
-            const Mtrl nm = fill_material(sc, ni.mtrl_idx);
             const int32_t n_mesh_id = (int32_t)aov_albedo_meshid[nidx].w;
-            if (!(valid_mtrl && restir_acceptable(mtrl, mesh_id, normal, nm, n_mesh_id, ni.nml))) continue;
+            if (!(valid_mtrl && restir_acceptable(mtrl, mesh_id, normal, restir_material_type(sc, ni.mtrl_idx), n_mesh_id, ni.nml))) continue;
             const int32_t light_pos = nr.y;
             const AtnLightParameter& light = sc.lights[light_pos];
             LightSample ls;

@@ -686,18 +686,36 @@ struct FrameParams {
     uint32_t frame;                 // host frame index + sample index (pathtracing_impl.h:76-81)
     int32_t max_bounce, rr_bounce;
     uint32_t seed_count;
+    int32_t batch;                  // camera samples traced as one wavefront: slot = k * (rw * rh) + pixel, sample k uses frame + k
 };
+
+// Where a path slot sits: pixel of the region, sample of the batch.  Samples are independent in the reference (one
+// `render` pass per sample); a wavefront of one 1080p sample (2 M rays per launch) leaves ~6 % on the table against
+// one of 8 M rays (launch tails, refill granularity), so several samples share a wavefront when the frame is small.
+struct SlotInfo { int ix, iy, pix, k; uint32_t frame; };
+__device__ __forceinline__ SlotInfo slot_info(const FrameParams& fp, int slot)
+{
+    const int n_pix = fp.rw * fp.rh;
+    SlotInfo si;
+    si.k = (fp.batch > 1) ? slot / n_pix : 0;
+    const int p = slot - si.k * n_pix;
+    si.ix = fp.x0 + p % fp.rw;
+    si.iy = fp.y0 + p / fp.rw;
+    si.pix = si.iy * fp.width + si.ix;
+    si.frame = fp.frame + (uint32_t)si.k;
+    return si;
+}
 
 // GeneratePath (pathtracing_impl.h:65-110)
 __global__ void k_generate(FrameParams fp, AtnCameraParameter cam, const uint32_t* __restrict__ seeds, PathBuffers pb,
                            Counters* cnt)
 {
-    const int n = fp.rw * fp.rh;
+    const int n = fp.rw * fp.rh * fp.batch;
     for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < n; s += gridDim.x * blockDim.x) {
-        const int ix = fp.x0 + s % fp.rw;
-        const int iy = fp.y0 + s / fp.rw;
-        const uint32_t idx = (uint32_t)(iy * fp.width + ix);
-        Sampler sp = sampler_for_path(fp.frame, seeds[idx % fp.seed_count]);
+        const SlotInfo si = slot_info(fp, s);
+        const int ix = si.ix, iy = si.iy;
+        const uint32_t idx = (uint32_t)si.pix;
+        Sampler sp = sampler_for_path(si.frame, seeds[idx % fp.seed_count]);
         const float r1 = sp.next();
         const float r2 = sp.next();
         const float fs = (ix + r1) / (float)(cam.width);
@@ -736,12 +754,17 @@ __device__ __forceinline__ int warp_append(bool pred, int32_t* counter)
 #define ATN_BSDF_MIN_BLOCKS 8
 #endif
 constexpr int kShadeBlock = 128;
+#ifndef ATN_WAVEFRONT_PATHS
+#define ATN_WAVEFRONT_PATHS (8 * 1024 * 1024)     // paths per wavefront the sample batching aims at
+#endif
+#ifndef ATN_MAX_BATCH
+#define ATN_MAX_BATCH 16
+#endif
 
 __device__ __forceinline__ Sampler path_sampler(const FrameParams& fp, const uint32_t* seeds, const PathBuffers& pb, int slot)
 {
-    const int ix = fp.x0 + slot % fp.rw;
-    const int iy = fp.y0 + slot / fp.rw;
-    Sampler sp = sampler_for_path(fp.frame, seeds[(uint32_t)(iy * fp.width + ix) % fp.seed_count]);
+    const SlotInfo si = slot_info(fp, slot);
+    Sampler sp = sampler_for_path(si.frame, seeds[(uint32_t)si.pix % fp.seed_count]);
     sp.dim = pb.sampler_dim[slot];
     return sp;
 }
@@ -782,9 +805,12 @@ k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, 
             st.singular = (fl & 2u) != 0u;
             st.last_specular = (fl & 4u) != 0u;
             // AOVs of the first hit are kept per pixel (the reference indexes them by pixel too)
-            const int pix = (fp.y0 + slot / fp.rw) * fp.width + (fp.x0 + slot % fp.rw);
-            AtnVec4* aov_nd = (bounce <= 1) ? reinterpret_cast<AtnVec4*>(pb.aov_nd) + pix : nullptr;
-            AtnVec4* aov_am = (bounce <= 1) ? reinterpret_cast<AtnVec4*>(pb.aov_am) + pix : nullptr;
+            // (of the last sample of a batch: the buffers hold "the last sample rendered")
+            const SlotInfo si = slot_info(fp, slot);
+            const int pix = si.pix;
+            const bool aov = bounce <= 1 && si.k == fp.batch - 1;
+            AtnVec4* aov_nd = aov ? reinterpret_cast<AtnVec4*>(pb.aov_nd) + pix : nullptr;
+            AtnVec4* aov_am = aov ? reinterpret_cast<AtnVec4*>(pb.aov_am) + pix : nullptr;
             if (h1.x >= 0) {
                 Surface sf;
                 lit = shade_surface(sc, ray, h1.x, __float_as_int(h0.w), h0.y, h0.z, h0.x, h1.y, bounce, &st, &sf,
@@ -796,9 +822,7 @@ k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, 
                 }
             }
             else {
-                const int ix = fp.x0 + slot % fp.rw;
-                const int iy = fp.y0 + slot / fp.rw;
-                shade_miss(sc, cam, ix, iy, fp.width, fp.height, bounce, ray, &st, aov_nd, aov_am);
+                shade_miss(sc, cam, si.ix, si.iy, fp.width, fp.height, bounce, ray, &st, aov_nd, aov_am);
             }
             if (!lit) {
                 pb.contrib[slot] = make_float4(st.contrib.x, st.contrib.y, st.contrib.z, cb.w);
@@ -1303,18 +1327,20 @@ __global__ void k_gather(FrameParams fp, PathBuffers pb, float4* image, int prog
     for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < n; s += gridDim.x * blockDim.x) {
         const int ix = fp.x0 + s % fp.rw;
         const int iy = fp.y0 + s / fp.rw;
-        const float4 c = pb.contrib[s];
         float4 cur = image[iy * fp.width + ix];
-        if (progressive) {
-            const float nn = (float)((int32_t)cur.w);
-            const float cx = c.x / 1.0f, cy = c.y / 1.0f, cz = c.z / 1.0f;   // col /= cnt, cnt = 1
-            cur.x = (nn * cur.x + cx) / (nn + 1);
-            cur.y = (nn * cur.y + cy) / (nn + 1);
-            cur.z = (nn * cur.z + cz) / (nn + 1);
-            cur.w = nn + 1;
-        }
-        else {
-            cur.x += c.x; cur.y += c.y; cur.z += c.z; cur.w += 1.0f;
+        for (int k = 0; k < fp.batch; k++) {          // the samples of the batch, in sample order
+            const float4 c = pb.contrib[(size_t)k * n + s];
+            if (progressive) {
+                const float nn = (float)((int32_t)cur.w);
+                const float cx = c.x / 1.0f, cy = c.y / 1.0f, cz = c.z / 1.0f;   // col /= cnt, cnt = 1
+                cur.x = (nn * cur.x + cx) / (nn + 1);
+                cur.y = (nn * cur.y + cy) / (nn + 1);
+                cur.z = (nn * cur.z + cz) / (nn + 1);
+                cur.w = nn + 1;
+            }
+            else {
+                cur.x += c.x; cur.y += c.y; cur.z += c.z; cur.w += 1.0f;
+            }
         }
         image[iy * fp.width + ix] = cur;
     }
@@ -1424,6 +1450,8 @@ struct AtnRenderer {
     cudaEvent_t ev0{ nullptr }, ev1{ nullptr };
     std::vector<cudaEvent_t> trace_events;
     int trace_grid{ 148 * 8 };
+    int batch_cap{ 1 };                 // camera samples per wavefront (atn_upload_scene sizes the path buffers for it)
+    size_t path_capacity{ 0 };          // path slots allocated
     int stack_need{ 0 };                // worst-case traversal stack depth of the uploaded scene (WideBvh::max_stack)
     int surface_grid{ 148 * 8 }, nee_grid{ 148 * 8 }, bsdf_grid{ 148 * 8 };
 };
@@ -1613,7 +1641,11 @@ ATN_API int atn_upload_scene(AtnRenderer* r, const AtnSceneBlob* scene, const At
     r->camera = *camera;
     r->width = width; r->height = height;
     const size_t n = (size_t)width * height;
-    rc = alloc_paths(r, n);
+    // path buffers for a wavefront of about 8 M paths (what a 4K frame gives by itself): up to kMaxBatch samples of a
+    // smaller frame are traced together (slot_info); ~216 B per path, 1.8 GB at the cap
+    r->batch_cap = (int)std::max<size_t>(1, std::min<size_t>((size_t)ATN_MAX_BATCH, ((size_t)ATN_WAVEFRONT_PATHS + n / 2) / n));
+    r->path_capacity = n * (size_t)r->batch_cap;
+    rc = alloc_paths(r, r->path_capacity);
     if (rc != ATN_OK) return rc;
     CUDA_TRY(r->image.resize(n));
     CUDA_TRY(cudaMemsetAsync(r->image.p, 0, n * sizeof(float4), s));
@@ -1826,17 +1858,25 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
     CUDA_TRY(cudaMemsetAsync(r->totals.p, 0, sizeof(Totals), s));
     CUDA_TRY(cudaMemsetAsync(r->visits.p, 0, sizeof(Visits), s));
     CUDA_TRY(cudaEventRecord(r->ev0, s));
-    for (int smp = sample_begin; smp < sample_end; smp++) {
+    // Samples are traced `batch` at a time as one wavefront (slot_info): as many as the path buffers hold, one when
+    // the bounce tap is on (its records are indexed by pixel).
+    const int batch_max = tap ? 1 : std::max<int>(1, (int)std::min<size_t>((size_t)r->batch_cap, r->path_capacity / (size_t)n));
+    for (int smp = sample_begin; smp < sample_end;) {
+        const int batch = std::min(batch_max, sample_end - smp);
         fp.frame = r->frame + (uint32_t)smp;
+        fp.batch = batch;
+        const int paths = n * batch;
+        const int grid_b = std::min((paths + 255) / 256, r->sm_count * 8);
         CUDA_TRY(cudaMemsetAsync(r->counters.p, 0, sizeof(Counters), s));
-        if (tap && smp == sample_end - 1) CUDA_TRY(cudaMemsetAsync(r->tap_dev.p, 0, (size_t)n * r->tap_cap * sizeof(AtnBounceRecord), s));
-        k_generate<<<gen_grid, 256, 0, s>>>(fp, r->camera, r->seeds.p, r->pb, r->counters.p);
-        launches++;
         const bool tap_now = tap && smp == sample_end - 1;
+        if (tap_now) CUDA_TRY(cudaMemsetAsync(r->tap_dev.p, 0, (size_t)n * r->tap_cap * sizeof(AtnBounceRecord), s));
+        k_generate<<<grid_b, 256, 0, s>>>(fp, r->camera, r->seeds.p, r->pb, r->counters.p);
+        launches++;
         const int rc = launch_bounces(r, fp, r->pb, tap_now, nullptr, &ev_i, &launches);
         if (rc != ATN_OK) return rc;
         k_gather<<<gen_grid, 256, 0, s>>>(fp, r->pb, r->image.p, r->progressive, r->counters.p, r->totals.p);
         launches++;
+        smp += batch;
     }
     CUDA_TRY(cudaEventRecord(r->ev1, s));
     CUDA_TRY(cudaGetLastError());
@@ -1883,7 +1923,7 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
     cudaStream_t s = r->stream;
     FrameParams fp;
     fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height;
-    fp.max_bounce = 1; fp.rr_bounce = 1; fp.seed_count = r->seed_count;
+    fp.max_bounce = 1; fp.rr_bounce = 1; fp.seed_count = r->seed_count; fp.batch = 1;
     const int n = width * height;
     const int grid = std::min((n + 255) / 256, r->sm_count * 8);
     const int sgrid = r->sm_count * 8;
@@ -1995,7 +2035,7 @@ ATN_API int atn_render_svgf(AtnRenderer* r, int32_t width, int32_t height, int32
 
     FrameParams fp;
     fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height;
-    fp.max_bounce = max_bounce; fp.rr_bounce = rr_bounce; fp.seed_count = r->seed_count;
+    fp.max_bounce = max_bounce; fp.rr_bounce = rr_bounce; fp.seed_count = r->seed_count; fp.batch = 1;
     fp.frame = r->frame;
     const int cur_k = (int)(r->frame & 1u);
     AtnVec4* base = reinterpret_cast<AtnVec4*>(r->svgf_planes.p);
@@ -2121,7 +2161,7 @@ ATN_API int atn_render_restir(AtnRenderer* r, int32_t width, int32_t height, int
 
     FrameParams fp;
     fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height;
-    fp.max_bounce = max_bounce; fp.rr_bounce = rr_bounce; fp.seed_count = r->seed_count;
+    fp.max_bounce = max_bounce; fp.rr_bounce = rr_bounce; fp.seed_count = r->seed_count; fp.batch = 1;
     fp.frame = r->frame;
     const int cur = r->restir_cur, other = (cur + 1) & 1;
     RestirView rv;

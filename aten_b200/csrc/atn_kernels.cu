@@ -1417,6 +1417,7 @@ struct AtnRenderer {
     DevBuf<Counters> counters;
     DevBuf<Totals> totals;
     DevBuf<Visits> visits;
+    bool query_pending{ false };   // a device-buffer ray query whose time / visit counts atn_get_stats has yet to collect
     PathBuffers pb{};
 
     // query scratch
@@ -2286,6 +2287,19 @@ ATN_API int atn_device_image(AtnRenderer* r, void** device_ptr, size_t* pixel_co
 ATN_API int atn_get_stats(AtnRenderer* r, AtnStats* out)
 {
     if (!r || !out) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_get_stats: NULL argument");
+    if (r->query_pending) {
+        // a ray query on device buffers (atn_trace_*_device) returns without waiting; its time and visit counts are
+        // collected here, on demand
+        CUDA_TRY(cudaSetDevice(r->device));
+        CUDA_TRY(cudaStreamSynchronize(r->stream));
+        float ms = 0.0f;
+        Visits hv{};
+        CUDA_TRY(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
+        CUDA_TRY(cudaMemcpy(&hv, r->visits.p, sizeof(Visits), cudaMemcpyDeviceToHost));
+        r->stats.device_ms = ms; r->stats.trace_ms = ms;
+        r->stats.nodes_visited = hv.nodes; r->stats.tris_tested = hv.tris;
+        r->query_pending = false;
+    }
     *out = r->stats;
     return ATN_OK;
 }
@@ -2313,6 +2327,7 @@ static int query_launch(AtnRenderer* r, const void* rays_dev, const void* f_dev,
     r->stats.closest_rays = any ? 0 : n;
     r->stats.shadow_rays = any ? n : 0;
     r->stats.camera_samples = 0;
+    r->query_pending = true;
     return ATN_OK;
 }
 

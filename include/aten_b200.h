@@ -195,8 +195,8 @@ typedef struct AtnStats {
     uint64_t kernel_launches;  /* CUDA kernels launched by the call */
     float    device_ms;        /* CUDA-event time of the call on the handle's stream */
     float    trace_ms;         /* sum of CUDA-event times of the traversal kernels (if profiling on) */
-    uint64_t nodes_visited;    /* 64-byte child-pair nodes fetched by the traversal kernels (atn_render only) */
-    uint64_t tris_tested;      /* triangle tests run by the traversal kernels (atn_render only) */
+    uint64_t nodes_visited;    /* 128-byte QuadNodes fetched by the traversal kernels (renders and ray queries) */
+    uint64_t tris_tested;      /* triangle tests run by the traversal kernels (renders and ray queries) */
 } AtnStats;
 
 typedef struct AtnRenderer AtnRenderer;

@@ -197,16 +197,92 @@ def ray_stress(name, n_rays, label=""):
                       "visible_fraction": round(float(t_vis.float().mean()), 3)}), flush=True)
 
 
+def ray_stress_flat(name, n_rays, label="", parity_rays=200_000, copies=None):
+    """configs[4] proper: 100 DISTINCT dragon meshes (scripts/flat_scene.py: own vertices, triangles and bottom-layer
+    node list per copy -- ~1.4 GB of QuadNodes + TriLeafs, not L2-resident), rays that start on the surfaces
+    (area-uniform origins, cosine-distributed directions).  Reports closest-hit and any-hit Mrays/s, the bytes the
+    traversal fetched on its own layout (128 B per QuadNode step, 64 B per triangle test, 24 B ray in, 32 B hit out)
+    against the measured HBM copy peak, and a parity check of a sample of the same rays against the CPU restatement."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import flat_scene as fs
+    t0 = time.perf_counter()
+    src = ol.ref_scene(name, 8, 8)
+    t1 = time.perf_counter()
+    scene = fs.flatten_instances(src, max_copies=copies)
+    del src
+    t2 = time.perf_counter()
+    r = PathTracing(0)
+    r.UpdateSceneData(scene)
+    t3 = time.perf_counter()
+    rays, dist = fs.surface_rays(scene, n_rays, seed=1)
+    hits = torch.empty((n_rays, 8), dtype=torch.float32, device="cuda")
+    vis = torch.empty(n_rays, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    res = {}
+    for kind in ("closest", "any"):
+        best = None
+        for it in range(4):          # first pass is the warm-up; CUDA events on the handle's stream
+            if kind == "closest":
+                r.trace_closest_device(rays.data_ptr(), None, n_rays, hits.data_ptr())
+            else:
+                r.trace_any_device(rays.data_ptr(), dist.data_ptr(), n_rays, vis.data_ptr())
+            st = r.stats()
+            if it > 0 and (best is None or st["device_ms"] < best["device_ms"]):
+                best = st
+        res[kind] = best
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm = float(peaks.get("hbm_gbs", 0) or 0)
+
+    def line(st, out_bytes):
+        b = 128 * st["nodes_visited"] + 64 * st["tris_tested"] + (24 + out_bytes) * n_rays
+        gbs = b / st["device_ms"] / 1e6
+        return {"mrays_per_s": round(n_rays / st["device_ms"] / 1e3, 1), "ms": round(st["device_ms"], 2),
+                "quad_nodes_per_ray": round(st["nodes_visited"] / n_rays, 2), "tri_tests_per_ray": round(st["tris_tested"] / n_rays, 2),
+                "fetched_gb_per_s": round(gbs, 1), "frac_of_hbm_copy_peak": round(gbs / hbm, 3) if hbm else None}
+    # parity of a sample of exactly these rays
+    k = min(parity_rays, n_rays)
+    sel = torch.arange(k, device="cuda", dtype=torch.int64) * (n_rays // k)
+    h_rays = np.zeros(k, sio.RAY_DTYPE)
+    rr = rays[sel].cpu().numpy()
+    h_rays["org"] = rr[:, 0:3]; h_rays["dir"] = rr[:, 3:6]
+    got = np.frombuffer(hits[sel].cpu().numpy().tobytes(), sio.HIT_DTYPE)
+    want = ol.trace_closest(scene, h_rays)
+    hit = want["objid"] >= 0
+    differ = (got["objid"] != want["objid"]) | (hit & (got["primid"] != want["primid"])) | (got["t"].view(np.uint32) != want["t"].view(np.uint32))
+    hitmiss = int(((got["objid"] >= 0) != hit).sum())
+    rel = float(np.max(np.abs(got["t"][differ & hit].astype(np.float64) - want["t"][differ & hit]) / want["t"][differ & hit])) if (differ & hit).any() else 0.0
+    out = {"config": label, "scene": name + " flattened", "rays": n_rays, "triangles": int(len(scene.triangles)),
+           "meshes": int(len(scene.node_lists) - 1), "reference_nodes": scene.node_count,
+           "closest": line(res["closest"], 32), "any": line(res["any"], 1),
+           "hit_fraction": round(float((hits[:, 1].view(torch.int32) >= 0).float().mean()), 3),
+           "visible_fraction": round(float(vis.float().mean()), 3),
+           "hbm_copy_peak_gbs": hbm or None,
+           "parity_vs_restatement": {"rays": k, "differing": int(differ.sum()), "hit_miss_disagreements": hitmiss, "max_rel_dt": rel},
+           "seconds": {"reference_build": round(t1 - t0, 1), "flatten": round(t2 - t1, 1), "upload_encode": round(t3 - t2, 1)}}
+    r.close()
+    print(json.dumps(out), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default="")
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--rays", type=int, default=0, help="--only flat: number of rays (default 100 M)")
     a = ap.parse_args()
     if not ol.have_ref():
         sys.exit("oracle/_ref not present")
     q = a.quick
     if a.only == "restir":
         restir_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 4, label="N1 ReSTIR, sponza_lod 1080p, 8-frame sequence")
+        return
+    if a.only == "flat":
+        ray_stress_flat("dragon_grid10", a.rays or (100_000_000 if not q else 5_000_000), copies=None if not q else 9,
+                        label="C5: incoherent secondary rays into 100 distinct dragon meshes (10 M triangles, ~1.4 GB of nodes + triangles)")
         return
     if a.only == "svgf":
         svgf_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 3, label="N1 SVGF, sponza_lod 1080p, 8-frame sequence")
@@ -221,6 +297,8 @@ def main():
     restir_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 4, label="N1 ReSTIR, sponza_lod 1080p, 8-frame sequence")
     ray_stress("dragon_grid10", 100_000_000 if not q else 5_000_000,
                label="C5 stand-in: 100 M incoherent secondary rays into 100 instanced dragons (10 M triangles), closest-hit and any-hit")
+    ray_stress_flat("dragon_grid10", 100_000_000 if not q else 5_000_000, copies=None if not q else 9,
+                    label="C5: 100 M incoherent secondary rays into 100 distinct dragon meshes (10 M triangles, ~1.4 GB of nodes + triangles)")
 
 
 if __name__ == "__main__":

@@ -1,0 +1,101 @@
+"""Config C5's scene shape -- many DISTINCT meshes, each with its own bottom-layer node list (scripts/flat_scene.py) --
+at a size the checkers finish in seconds: the instanced golden scene with every instance turned into a mesh of
+its own.  The flattened scene is a new input in the reference's layouts, so it goes through the same three
+checks as the others: CPU restatement vs brute force, the encoder emulation vs the restatement, and (gpu) the
+CUDA traversal vs the restatement, bit-exact."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from aten_b200 import scene_io as sio
+from tests import emu_lib
+from tests import oracle_lib as ol
+from tests.test_gpu_parity import assert_hits_equal
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts"))
+import flat_scene as fs  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def flat(golden):
+    return fs.flatten_instances(golden.scene("instanced"), min_triangles=100)
+
+
+def random_rays(scene, n, seed):
+    rng = np.random.default_rng(seed)
+    lo = scene.config["scene_bbox_min"][0].astype(np.float64); hi = scene.config["scene_bbox_max"][0].astype(np.float64)
+    rays = np.zeros(n, sio.RAY_DTYPE)
+    rays["org"] = (lo - 0.2 * (hi - lo) + 1.4 * (hi - lo) * rng.random((n, 3))).astype(np.float32)
+    d = rng.normal(size=(n, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays["dir"] = d.astype(np.float32)
+    return rays
+
+
+def test_flat_scene_layout(flat, golden):
+    src = golden.scene("instanced")
+    n = (len(flat.objects)) // 2
+    assert n == 5 and len(flat.node_lists) == 1 + n
+    assert len(flat.triangles) == 3 * 6400 + 2 * 15488           # three teapots, two suzannes, the floor is dropped
+    assert all(flat.triangles["idx"].max() < len(flat.positions) for _ in [0])
+    top = flat.node_lists[0]
+    leaves = top[top["object_id"] >= 0]
+    assert sorted(leaves["object_id"].astype(int)) == list(range(n, 2 * n))
+    assert sorted(int(b) & 0x7fff for b in leaves["exid"].view("<u4")) == list(range(1, n + 1))
+    # every triangle of a copy lies in the root box of the copy's own list
+    for j in range(n):
+        o = flat.objects[j]
+        tri = flat.triangles[o["triangle_id"]:o["triangle_id"] + o["triangle_num"]]
+        p = flat.positions[np.unique(tri["idx"]), :3]
+        root = flat.node_lists[1 + j][0]
+        assert (p >= root["boxmin"]).all() and (p <= root["boxmax"]).all()
+        prim = flat.node_lists[1 + j]["primid"]
+        prim = prim[prim >= 0].astype(int)
+        assert prim.min() >= o["triangle_id"] and prim.max() < o["triangle_id"] + o["triangle_num"]
+    assert len(src.node_lists[1]) == len(flat.node_lists[1])
+
+
+def test_flat_scene_oracle_vs_brute_force(flat):
+    rays = random_rays(flat, 200, 3)
+    h = ol.trace_closest(flat, rays)
+    P = flat.positions[:, :3].astype(np.float64); I = flat.triangles["idx"]
+    a, b, c = P[I[:, 0]], P[I[:, 1]], P[I[:, 2]]
+    e1, e2 = b - a, c - a
+    for k in range(len(rays)):
+        og = rays["org"][k].astype(np.float64); dr = rays["dir"][k].astype(np.float64)
+        u = np.cross(dr, e2); det = (u * e1).sum(1)
+        with np.errstate(all="ignore"):
+            inv = 1.0 / det; r = og - a
+            be = (u * r).sum(1) * inv; v = np.cross(r, e1); ga = (v * dr).sum(1) * inv; t = (v * e2).sum(1) * inv
+        ok = (be >= 0) & (ga >= 0) & (be + ga <= 1) & (t > 1e-9)
+        tb = t[ok].min() if ok.any() else np.inf
+        th = float(h["t"][k]) if h["objid"][k] >= 0 else np.inf
+        assert (np.isinf(tb) and np.isinf(th)) or abs(tb - th) <= 1e-4 * tb, (k, tb, th)
+
+
+def test_flat_scene_encoder_emulation(flat):
+    rays = random_rays(flat, 50_000, 4)
+    want = ol.trace_closest(flat, rays).copy()
+    miss = want["objid"] < 0
+    want["primid"][miss] = -1; want["mtrlid"][miss] = -1; want["meshid"][miss] = -1
+    got, st = emu_lib.trace_closest(flat, rays)
+    assert (want["objid"] >= 0).mean() > 0.1
+    assert_hits_equal(got, want)
+    assert st["max_sp"] <= st["stack_bound"]
+
+
+@pytest.mark.gpu
+def test_flat_scene_gpu_vs_oracle(flat):
+    from aten_b200 import PathTracing
+    rays = random_rays(flat, 200_000, 5)
+    rng = np.random.default_rng(6)
+    diag = float(np.linalg.norm(flat.config["scene_bbox_max"][0] - flat.config["scene_bbox_min"][0]))
+    dist = (rng.random(len(rays)) * diag).astype(np.float32)
+    with PathTracing(0) as r:
+        r.UpdateSceneData(flat)
+        got = r.trace_closest(rays)
+        vis = r.trace_any(rays, dist)
+    want = ol.trace_closest(flat, rays)
+    assert_hits_equal(got, want)
+    assert (vis == ol.trace_any(flat, rays, dist)).mean() >= 1.0 - 3e-4       # near ties at the distance limit

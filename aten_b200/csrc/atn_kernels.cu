@@ -30,6 +30,7 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -457,7 +458,10 @@ __device__ __forceinline__ SlabPair slab_pair(const float4 mn_xy, const float4 m
 #ifndef ATN_NODE_TEX
 #define ATN_NODE_TEX 10
 #endif
-template <class Policy, int kLocalStack>
+#ifndef ATN_PREFETCH
+#define ATN_PREFETCH 0
+#endif
+template <class Policy, int kLocalStack, bool kStream>
 __global__ void __launch_bounds__(kTraceBlock, ATN_TRACE_MIN_BLOCKS)
 k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch, Visits* visits)
 {
@@ -518,21 +522,47 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
             if (act == 0u) break;
             if (!exhausted && __popc(act) < kRefillThreshold) break;
 
-            // ---- phase A: QuadNode ----
+            // ---- what every lane does in this iteration ----
+            // kStream (scenes whose nodes and triangles do not fit the L2): the iteration is decided from the lanes'
+            // current references alone and ALL its global loads -- a QuadNode, a TriLeaf or an InstLeafW per lane -- are
+            // issued here, together, so that an iteration waits for device memory once.  The default form lets a lane
+            // run node step, triangle test and instance entry back to back in one iteration (fewer iterations, which is
+            // what counts when the set is L2-resident and the kernel is issue bound), at the price of up to three
+            // dependent load latencies per iteration.
             const bool on_node = active && cur >= 0;
+            F4x2 c0, c1, c2, c3;
+            bool s_on_tri = false, s_on_entry = false;
+            if (kStream) {
+                const bool is_leaf = active && cur < 0 && cur > kRefDone;
+                const bool w_tri = is_leaf && cur_inst >= 0, w_entry = is_leaf && cur_inst < 0;
+                const unsigned mn = __ballot_sync(full, on_node);
+                const unsigned mt = __ballot_sync(full, w_tri);
+                const unsigned me = __ballot_sync(full, w_entry);
+                const bool run_tris = (__popc(mt) >= kLeafBatch) || (mn == 0u);
+                s_on_tri = w_tri && run_tris;
+                const bool busy = (mn != 0u) || (run_tris && mt != 0u);
+                s_on_entry = w_entry && (__popc(me) >= kEntryBatch || !busy);
+                const float4* p = on_node ? bv.nodes + (size_t)cur * 8
+                                          : (s_on_tri ? bv.tris + (size_t)(~cur) * kTriStride : bv.insts + (size_t)(~cur) * kInstStride);
+                if (on_node || s_on_tri || s_on_entry) { c0 = ldg8(p); c1 = ldg8(p + 2); }     // all three records are >= 64 bytes
+                if (on_node) { c2 = ldg8(p + 4); c3 = ldg8(p + 6); }
+            }
+
+            // ---- phase A: QuadNode ----
             if (on_node) {
-                const float4* np = bv.nodes + (size_t)cur * 8;
-                // chunk k through the texture pipe (two 128-bit fetches; one for the last chunk, whose upper half is
-                // padding) or through LDG.256, see ATN_NODE_TEX
-                F4x2 c0, c1, c2, c3;
-                if (ATN_NODE_TEX & 1) { c0.lo = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 0); c0.hi = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 1); }
-                else c0 = ldg8(np + 0);
-                if (ATN_NODE_TEX & 2) { c1.lo = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 2); c1.hi = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 3); }
-                else c1 = ldg8(np + 2);
-                if (ATN_NODE_TEX & 4) { c2.lo = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 4); c2.hi = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 5); }
-                else c2 = ldg8(np + 4);
-                if (ATN_NODE_TEX & 8) c3.lo = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 6);
-                else c3 = ldg8(np + 6);
+                if (!kStream) {
+                    const float4* np = bv.nodes + (size_t)cur * 8;
+                    // chunk k through the texture pipe (two 128-bit fetches; one for the last chunk, whose upper half is
+                    // padding) or through LDG.256, see ATN_NODE_TEX
+                    if (ATN_NODE_TEX & 1) { c0.lo = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 0); c0.hi = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 1); }
+                    else c0 = ldg8(np + 0);
+                    if (ATN_NODE_TEX & 2) { c1.lo = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 2); c1.hi = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 3); }
+                    else c1 = ldg8(np + 2);
+                    if (ATN_NODE_TEX & 4) { c2.lo = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 4); c2.hi = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 5); }
+                    else c2 = ldg8(np + 4);
+                    if (ATN_NODE_TEX & 8) c3.lo = tex1Dfetch<float4>(bv.node_tex, cur * 8 + 6);
+                    else c3 = ldg8(np + 6);
+                }
                 const float4 a0 = c0.lo, a1 = c0.hi, a2 = c1.lo, b0 = c1.hi, b1 = c2.lo, b2 = c2.hi;
                 const int4 rf = make_int4(__float_as_int(c3.lo.x), __float_as_int(c3.lo.y), __float_as_int(c3.lo.z), __float_as_int(c3.lo.w));
                 const float2 inv_xy = make_float2(ri.invdir.x, ri.invdir.y);
@@ -573,25 +603,41 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                         }
                     }
                     sp += np_;
+                    if (ATN_PREFETCH && kStream) {
+                        // the second-nearest subtree will most likely be visited: start its fetch into the L2 now
+                        const char* q = r1 >= 0 ? (const char*)(bv.nodes + (size_t)r1 * 8)
+                                                : (cur_inst >= 0 ? (const char*)(bv.tris + (size_t)(~r1) * kTriStride) : nullptr);
+                        if (q) {
+                            asm volatile("prefetch.global.L2 [%0];" :: "l"(q));
+                            if (ATN_PREFETCH >= 2) asm volatile("prefetch.global.L2 [%0];" :: "l"(q + 32));
+                            if (ATN_PREFETCH >= 4 && r1 >= 0) { asm volatile("prefetch.global.L2 [%0];" :: "l"(q + 64)); asm volatile("prefetch.global.L2 [%0];" :: "l"(q + 96)); }
+                        }
+                    }
                 }
             }
 
             // ---- phase B: triangle leaf (triangle::hit, triangle.h:40-67) ----
-            const bool want_tri = active && cur < 0 && cur > kRefDone && cur_inst >= 0;       // a leaf, not one of the reserved values
-            bool run_tris = true;
-            if (kLeafBatch > 1) {
-                const unsigned mt = __ballot_sync(full, want_tri);
-                const unsigned mn = __ballot_sync(full, on_node);
-                run_tris = (__popc(mt) >= kLeafBatch) || (mn == 0u);
+            bool on_tri = s_on_tri;
+            if (!kStream) {
+                const bool want_tri = active && cur < 0 && cur > kRefDone && cur_inst >= 0;       // a leaf, not one of the reserved values
+                bool run_tris = true;
+                if (kLeafBatch > 1) {
+                    const unsigned mt = __ballot_sync(full, want_tri);
+                    const unsigned mn = __ballot_sync(full, on_node);
+                    run_tris = (__popc(mt) >= kLeafBatch) || (mn == 0u);
+                }
+                on_tri = want_tri && run_tris;
             }
-            const bool on_tri = want_tri && run_tris;
             bool finished = false;
             if (on_tri) {
                 const int32_t leaf = ~cur;
-                const float4* tp = bv.tris + (size_t)leaf * kTriStride;
-                const F4x2 ab = ldg8(tp);
-                const float4 a = ab.lo, b = ab.hi;
-                const float4 c = ldg4(tp + 2);
+                if (!kStream) {
+                    const float4* tp = bv.tris + (size_t)leaf * kTriStride;
+                    c0 = ldg8(tp);
+                    c1.lo = ldg4(tp + 2);
+                }
+                const float4 a = c0.lo, b = c0.hi;
+                const float4 c = c1.lo;
                 const TriHit h = intersect_triangle_edges(org, dir, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), V3(c.x, c.y, c.z));
                 n_tris++;
                 if (h.hit && h.t < kInf && t_min < h.t) {
@@ -607,17 +653,26 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
             }
 
             // ---- phase E: instance entry (threaded_bvh_traverser.h:146-185), batched ----
-            const bool want_entry = active && cur < 0 && cur > kRefDone && cur_inst < 0;
-            const unsigned me = __ballot_sync(full, want_entry);
+            bool want_entry = s_on_entry;
+            unsigned me = 0u;
+            if (!kStream) {
+                want_entry = active && cur < 0 && cur > kRefDone && cur_inst < 0;
+                me = __ballot_sync(full, want_entry);
+            }
+            else me = __ballot_sync(full, s_on_entry);
             if (me != 0u) {
-                const unsigned busy = __ballot_sync(full, on_node || on_tri);
-                if (__popc(me) >= kEntryBatch || busy == 0u) {
+                const unsigned busy = kStream ? 0u : __ballot_sync(full, on_node || on_tri);
+                if (kStream || __popc(me) >= kEntryBatch || busy == 0u) {
                     if (want_entry) {
                         const int32_t leaf = ~cur;
-                        const float4* ip = bv.insts + (size_t)leaf * kInstStride;
-                        const F4x2 iw = ldg8(ip);
+                        if (!kStream) {
+                            const float4* ip = bv.insts + (size_t)leaf * kInstStride;
+                            c0 = ldg8(ip);
+                            c1.lo = ldg4(ip + 2);
+                        }
+                        const F4x2 iw = c0;
                         const int4 il = make_int4(__float_as_int(iw.lo.x), __float_as_int(iw.lo.y), __float_as_int(iw.lo.z), __float_as_int(iw.lo.w));
-                        const float4 wmin = iw.hi, wmax = ldg4(ip + 2);
+                        const float4 wmin = iw.hi, wmax = c1.lo;
                         cur = kRefNull;
                         // conservative pre-filter (see leaf_margin): does the world ray come near the instance at all?
                         float t0w, t1w;
@@ -1417,6 +1472,7 @@ struct AtnRenderer {
     DevBuf<Counters> counters;
     DevBuf<Totals> totals;
     DevBuf<Visits> visits;
+    bool stream_loads{ false };    // traversal variant for scenes beyond the L2 (k_trace<.., kStream = true>), set at upload
     bool query_pending{ false };   // a device-buffer ray query whose time / visit counts atn_get_stats has yet to collect
     PathBuffers pb{};
 
@@ -1451,6 +1507,7 @@ struct AtnRenderer {
     cudaEvent_t ev0{ nullptr }, ev1{ nullptr };
     std::vector<cudaEvent_t> trace_events;
     int trace_grid{ 148 * 8 };
+    size_t l2_bytes{ 0 };
     int batch_cap{ 1 };                 // camera samples per wavefront (atn_upload_scene sizes the path buffers for it)
     size_t path_capacity{ 0 };          // path slots allocated
     int stack_need{ 0 };                // worst-case traversal stack depth of the uploaded scene (WideBvh::max_stack)
@@ -1461,10 +1518,15 @@ struct AtnRenderer {
 template <class Policy>
 static void launch_trace(AtnRenderer* r, cudaStream_t s, Policy pol, const int32_t* count_ptr, int count_imm, int32_t* fetch, Visits* visits)
 {
-    if (r->stack_need <= kSmemStack + kLocalStackSmall)
-        k_trace<Policy, kLocalStackSmall><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
-    else
-        k_trace<Policy, kLocalStackLarge><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
+    const bool small = r->stack_need <= kSmemStack + kLocalStackSmall;
+    if (r->stream_loads) {
+        if (small) k_trace<Policy, kLocalStackSmall, true><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
+        else k_trace<Policy, kLocalStackLarge, true><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
+    }
+    else {
+        if (small) k_trace<Policy, kLocalStackSmall, false><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
+        else k_trace<Policy, kLocalStackLarge, false><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
+    }
 }
 
 static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene)
@@ -1474,6 +1536,13 @@ static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene)
     if (enc.max_stack > kSmemStack + kLocalStackLarge)
         return set_error(ATN_ERR_TOO_LARGE, "BVH needs a traversal stack of %d entries (limit %d)", enc.max_stack, kSmemStack + kLocalStackLarge);
     r->stack_need = enc.max_stack;
+    {
+        // nodes + triangles beyond the L2: the traversal waits for device memory, not for issue slots -- use the variant
+        // that issues an iteration's loads together (k_trace<.., kStream>).  ATEN_B200_STREAM=0/1 overrides (experiments).
+        const size_t set_bytes = enc.nodes.size() * sizeof(QuadNode) + enc.tris.size() * sizeof(TriLeaf);
+        r->stream_loads = r->l2_bytes > 0 && set_bytes > r->l2_bytes;
+        if (const char* ov = getenv("ATEN_B200_STREAM")) r->stream_loads = (ov[0] == '1');
+    }
     CUDA_TRY(r->nodes.upload(enc.nodes.data(), enc.nodes.size(), r->stream));
     CUDA_TRY(r->tris.upload(enc.tris.data(), enc.tris.size(), r->stream));
     CUDA_TRY(r->insts.upload(enc.insts.data(), enc.insts.size(), r->stream));
@@ -1558,7 +1627,8 @@ ATN_API int atn_create(int device_ordinal, AtnRenderer** out)
     CUDA_TRY(cudaEventCreate(&r->ev0));
     CUDA_TRY(cudaEventCreate(&r->ev1));
     int bps = 0;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace<ClosestPolicy, kLocalStackSmall>, kTraceBlock, 0));
+    r->l2_bytes = (size_t)prop.l2CacheSize;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace<ClosestPolicy, kLocalStackSmall, false>, kTraceBlock, 0));
     r->trace_grid = r->sm_count * std::max(1, bps);
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_surface<false, false>, kShadeBlock, 0));
     r->surface_grid = r->sm_count * std::max(1, bps);

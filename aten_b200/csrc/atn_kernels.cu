@@ -386,6 +386,27 @@ __device__ __forceinline__ F4x2 ldg8(const float4* p)
 #endif
     return r;
 }
+// A whole QuadNode (7 x 16 bytes used) / a 48-byte leaf record, each as ONE asm statement: the loads are issued back to back.
+__device__ __forceinline__ void ldg_node(const float4* p, F4x2& c0, F4x2& c1, F4x2& c2, F4x2& c3)
+{
+    asm volatile("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%28];\n\t"
+                 "ld.global.nc.v8.f32 {%8, %9, %10, %11, %12, %13, %14, %15}, [%28+32];\n\t"
+                 "ld.global.nc.v8.f32 {%16, %17, %18, %19, %20, %21, %22, %23}, [%28+64];\n\t"
+                 "ld.global.nc.v4.f32 {%24, %25, %26, %27}, [%28+96];"
+                 : "=f"(c0.lo.x), "=f"(c0.lo.y), "=f"(c0.lo.z), "=f"(c0.lo.w), "=f"(c0.hi.x), "=f"(c0.hi.y), "=f"(c0.hi.z), "=f"(c0.hi.w),
+                   "=f"(c1.lo.x), "=f"(c1.lo.y), "=f"(c1.lo.z), "=f"(c1.lo.w), "=f"(c1.hi.x), "=f"(c1.hi.y), "=f"(c1.hi.z), "=f"(c1.hi.w),
+                   "=f"(c2.lo.x), "=f"(c2.lo.y), "=f"(c2.lo.z), "=f"(c2.lo.w), "=f"(c2.hi.x), "=f"(c2.hi.y), "=f"(c2.hi.z), "=f"(c2.hi.w),
+                   "=f"(c3.lo.x), "=f"(c3.lo.y), "=f"(c3.lo.z), "=f"(c3.lo.w)
+                 : "l"(p));
+}
+__device__ __forceinline__ void ldg_leaf(const float4* p, F4x2& c0, float4& c1)
+{
+    asm volatile("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%12];\n\t"
+                 "ld.global.nc.v4.f32 {%8, %9, %10, %11}, [%12+32];"
+                 : "=f"(c0.lo.x), "=f"(c0.lo.y), "=f"(c0.lo.z), "=f"(c0.lo.w), "=f"(c0.hi.x), "=f"(c0.hi.y), "=f"(c0.hi.z), "=f"(c0.hi.w),
+                   "=f"(c1.x), "=f"(c1.y), "=f"(c1.z), "=f"(c1.w)
+                 : "l"(p));
+}
 __device__ __forceinline__ void sts64(uint32_t addr, int32_t x, int32_t y)
 {
     asm volatile("st.shared.v2.b32 [%0], {%1, %2};" :: "r"(addr), "r"(x), "r"(y) : "memory");
@@ -458,11 +479,29 @@ __device__ __forceinline__ SlabPair slab_pair(const float4 mn_xy, const float4 m
 #ifndef ATN_NODE_TEX
 #define ATN_NODE_TEX 10
 #endif
+// batching thresholds of the kStream form (an idle iteration costs a device-memory latency there, not a few issue slots)
+#ifndef ATN_STREAM_LEAF_BATCH
+#define ATN_STREAM_LEAF_BATCH ATN_LEAF_BATCH
+#endif
+#ifndef ATN_STREAM_ENTRY_BATCH
+#define ATN_STREAM_ENTRY_BATCH ATN_ENTRY_BATCH
+#endif
+#ifndef ATN_STREAM_REFILL
+#define ATN_STREAM_REFILL ATN_REFILL_THRESHOLD
+#endif
 #ifndef ATN_PREFETCH
 #define ATN_PREFETCH 0
 #endif
+// Resident blocks per SM of the kStream form.  With 8 (64 registers) ptxas sinks half of a node's loads below the first
+// use of the other half to save registers, and the node step waits for device memory twice; a larger register budget
+// keeps the four loads together, which is worth more than the block it costs.  Closest-hit Mrays/s on the 10 M-triangle
+// scene: 8 blocks 966 (784 when the first two loads are split as well), 7: 1 266, 6: 1 158, 5: 1 160.  The default form
+// (L2-resident scenes) has the same split at 8 blocks but is issue bound: 7 or 6 blocks there are 1.5 % slower.
+#ifndef ATN_STREAM_MIN_BLOCKS
+#define ATN_STREAM_MIN_BLOCKS 7
+#endif
 template <class Policy, int kLocalStack, bool kStream>
-__global__ void __launch_bounds__(kTraceBlock, ATN_TRACE_MIN_BLOCKS)
+__global__ void __launch_bounds__(kTraceBlock, kStream ? ATN_STREAM_MIN_BLOCKS : ATN_TRACE_MIN_BLOCKS)
 k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch, Visits* visits)
 {
     __shared__ int2 s_stack[kSmemStack * kTraceBlock];   // (reference, entry distance bits) per lane and level
@@ -520,7 +559,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
         for (;;) {
             const unsigned act = __ballot_sync(full, active);
             if (act == 0u) break;
-            if (!exhausted && __popc(act) < kRefillThreshold) break;
+            if (!exhausted && __popc(act) < (kStream ? ATN_STREAM_REFILL : kRefillThreshold)) break;
 
             // ---- what every lane does in this iteration ----
             // kStream (scenes whose nodes and triangles do not fit the L2): the iteration is decided from the lanes'
@@ -538,14 +577,17 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                 const unsigned mn = __ballot_sync(full, on_node);
                 const unsigned mt = __ballot_sync(full, w_tri);
                 const unsigned me = __ballot_sync(full, w_entry);
-                const bool run_tris = (__popc(mt) >= kLeafBatch) || (mn == 0u);
+                const bool run_tris = (__popc(mt) >= ATN_STREAM_LEAF_BATCH) || (mn == 0u);
                 s_on_tri = w_tri && run_tris;
                 const bool busy = (mn != 0u) || (run_tris && mt != 0u);
-                s_on_entry = w_entry && (__popc(me) >= kEntryBatch || !busy);
+                s_on_entry = w_entry && (__popc(me) >= ATN_STREAM_ENTRY_BATCH || !busy);
                 const float4* p = on_node ? bv.nodes + (size_t)cur * 8
                                           : (s_on_tri ? bv.tris + (size_t)(~cur) * kTriStride : bv.insts + (size_t)(~cur) * kInstStride);
-                if (on_node || s_on_tri || s_on_entry) { c0 = ldg8(p); c1 = ldg8(p + 2); }     // all three records are >= 64 bytes
-                if (on_node) { c2 = ldg8(p + 4); c3 = ldg8(p + 6); }
+                // One asm statement per record kind, so that ptxas cannot sink part of a node's loads below the first use of
+                // its other parts (it does, to save registers, and the node step then waits for device memory twice:
+                // 966 vs 784 Mrays/s on the 10 M-triangle scene for two otherwise identical builds).
+                if (on_node) ldg_node(p, c0, c1, c2, c3);
+                else if (s_on_tri || s_on_entry) ldg_leaf(p, c0, c1.lo);
             }
 
             // ---- phase A: QuadNode ----
@@ -1506,7 +1548,7 @@ struct AtnRenderer {
     AtnStats stats{};
     cudaEvent_t ev0{ nullptr }, ev1{ nullptr };
     std::vector<cudaEvent_t> trace_events;
-    int trace_grid{ 148 * 8 };
+    int trace_grid{ 148 * 8 }, trace_grid_stream{ 148 * 6 };
     size_t l2_bytes{ 0 };
     int batch_cap{ 1 };                 // camera samples per wavefront (atn_upload_scene sizes the path buffers for it)
     size_t path_capacity{ 0 };          // path slots allocated
@@ -1520,8 +1562,8 @@ static void launch_trace(AtnRenderer* r, cudaStream_t s, Policy pol, const int32
 {
     const bool small = r->stack_need <= kSmemStack + kLocalStackSmall;
     if (r->stream_loads) {
-        if (small) k_trace<Policy, kLocalStackSmall, true><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
-        else k_trace<Policy, kLocalStackLarge, true><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
+        if (small) k_trace<Policy, kLocalStackSmall, true><<<r->trace_grid_stream, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
+        else k_trace<Policy, kLocalStackLarge, true><<<r->trace_grid_stream, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
     }
     else {
         if (small) k_trace<Policy, kLocalStackSmall, false><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
@@ -1630,6 +1672,8 @@ ATN_API int atn_create(int device_ordinal, AtnRenderer** out)
     r->l2_bytes = (size_t)prop.l2CacheSize;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace<ClosestPolicy, kLocalStackSmall, false>, kTraceBlock, 0));
     r->trace_grid = r->sm_count * std::max(1, bps);
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace<ClosestPolicy, kLocalStackSmall, true>, kTraceBlock, 0));
+    r->trace_grid_stream = r->sm_count * std::max(1, bps);
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_surface<false, false>, kShadeBlock, 0));
     r->surface_grid = r->sm_count * std::max(1, bps);
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_nee, kShadeBlock, 0));

@@ -1,17 +1,14 @@
 # A/B of traversal variants on the C5 scene (100 distinct dragon meshes, 30 M surface rays):
-# the load-streaming kernel form on/off, and the build variants under aten_b200/variants/.
+# the default build, and the build variants under aten_b200/variants/ (scripts/build_variants.py).
 mkdir -p gpurun_out
 R=${RAYS:-30000000}
-ATEN_B200_STREAM=1 timeout 1200 python -m pytest tests -x -q -m gpu 2>&1 | tail -3 > gpurun_out/abf_tests_stream1.log
-ATEN_B200_STREAM=0 python scripts/bench_configs.py --only flat --rays $R > gpurun_out/abf_stream0.json 2> gpurun_out/abf_stream0.err
+ATEN_B200_STREAM=0 python scripts/bench_configs.py --only flat --rays $R > gpurun_out/abf_control_stream0.json 2> gpurun_out/abf_control.err
 python scripts/bench_configs.py --only flat --rays $R > gpurun_out/abf_default.json 2> gpurun_out/abf_default.err
 for f in aten_b200/variants/lib_*.so; do
   [ -e "$f" ] || continue
   v=$(basename $f .so); v=${v#lib_}
   ATEN_B200_LIB=$f python scripts/bench_configs.py --only flat --rays $R > gpurun_out/abf_$v.json 2> gpurun_out/abf_$v.err
 done
-ATEN_B200_STREAM=1 python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/abf_bench_stream1.json 2> gpurun_out/abf_bench_stream1.err
-cat gpurun_out/abf_tests_stream1.log
 for f in gpurun_out/abf_*.json; do echo $f; python - "$f" <<'PY'
 import json,sys
 try:

@@ -479,7 +479,11 @@ __device__ __forceinline__ SlabPair slab_pair(const float4 mn_xy, const float4 m
 #ifndef ATN_NODE_TEX
 #define ATN_NODE_TEX 10
 #endif
-// batching thresholds of the kStream form (an idle iteration costs a device-memory latency there, not a few issue slots)
+// batching thresholds of the kStream form.  Measured on the 10 M-triangle scene (closest-hit Mrays/s, default 1 266):
+// leaf / entry batch 1: 1 230, 3: 1 259; refill threshold 12: -6 %, 24: 1 285, 28: 1 256.  Also measured and not kept:
+// part of the node through the texture pipe (748 - 1 165: the extra address registers make ptxas split the loads again),
+// prefetch.global.L2 of the second-nearest subtree at push time (-12 ... -18 %: the LSU data pipe of L1, 80 % busy in
+// this form, pays for every prefetch), 9 / 10 / 12 resident blocks with spills (-4 ... -50 %).
 #ifndef ATN_STREAM_LEAF_BATCH
 #define ATN_STREAM_LEAF_BATCH ATN_LEAF_BATCH
 #endif
@@ -488,9 +492,6 @@ __device__ __forceinline__ SlabPair slab_pair(const float4 mn_xy, const float4 m
 #endif
 #ifndef ATN_STREAM_REFILL
 #define ATN_STREAM_REFILL ATN_REFILL_THRESHOLD
-#endif
-#ifndef ATN_PREFETCH
-#define ATN_PREFETCH 0
 #endif
 // Resident blocks per SM of the kStream form.  With 8 (64 registers) ptxas sinks half of a node's loads below the first
 // use of the other half to save registers, and the node step waits for device memory twice; a larger register budget
@@ -645,16 +646,6 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                         }
                     }
                     sp += np_;
-                    if (ATN_PREFETCH && kStream) {
-                        // the second-nearest subtree will most likely be visited: start its fetch into the L2 now
-                        const char* q = r1 >= 0 ? (const char*)(bv.nodes + (size_t)r1 * 8)
-                                                : (cur_inst >= 0 ? (const char*)(bv.tris + (size_t)(~r1) * kTriStride) : nullptr);
-                        if (q) {
-                            asm volatile("prefetch.global.L2 [%0];" :: "l"(q));
-                            if (ATN_PREFETCH >= 2) asm volatile("prefetch.global.L2 [%0];" :: "l"(q + 32));
-                            if (ATN_PREFETCH >= 4 && r1 >= 0) { asm volatile("prefetch.global.L2 [%0];" :: "l"(q + 64)); asm volatile("prefetch.global.L2 [%0];" :: "l"(q + 96)); }
-                        }
-                    }
                 }
             }
 

@@ -264,6 +264,24 @@ def ray_stress_flat(name, n_rays, label="", parity_rays=200_000, copies=None):
            "hbm_copy_peak_gbs": hbm or None,
            "parity_vs_restatement": {"rays": k, "differing": int(differ.sum()), "hit_miss_disagreements": hitmiss, "max_rel_dt": rel},
            "seconds": {"reference_build": round(t1 - t0, 1), "flatten": round(t2 - t1, 1), "upload_encode": round(t3 - t2, 1)}}
+    # the same scene through the whole path tracer (point light + sky IBL as the instanced stand-in has them)
+    del rays, dist, hits, vis
+    torch.cuda.empty_cache()
+    W, H, spp = 1920, 1080, 4
+    r.close()
+    r = PathTracing(0)
+    r.UpdateSceneData(scene.with_size(W, H))
+    r.SetEnableProgressive(False)
+    ms = nr = ns = 0
+    for it in range(3):
+        r.reset(); r.render(W, H, spp, 5, 3)
+        st = r.stats()
+        if it > 0:
+            ms += st["device_ms"]; nr += st["closest_rays"] + st["shadow_rays"]; ns += st["camera_samples"]
+    img = r.readback()
+    out["render_1080p_4spp"] = {"mrays_per_s": round(nr / ms / 1e3, 1), "msamples_per_s": round(ns / ms / 1e3, 1),
+                                "rays_per_sample": round(nr / ns, 2), "finite": bool(np.isfinite(img).all()),
+                                "mean_radiance": float(img[..., :3].mean() / spp)}
     r.close()
     print(json.dumps(out), flush=True)
 

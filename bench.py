@@ -305,7 +305,7 @@ def main():
             "config": {"workload": WORKLOAD, "scene": SCENE, "width": W, "height": H, "spp_per_gpu": SPP,
                        "bounces": BOUNCE, "rr_bounce": RR,
                        "partition": "sample index: rank r renders samples [16r,16r+16); NCCL reduce(sum) of float4 images to rank 0" if world > 1 else "single GPU",
-                       "l2": "path state (2.07M paths x ~200 B SoA = 415 MB touched per bounce) exceeds the 126 MB L2; "
+                       "l2": "path state (8.3M paths per wavefront x ~200 B SoA = 1.7 GB touched per bounce) exceeds the 126 MB L2; "
                              "the scene (2.4 MB nodes + 0.6 MB triangles) is L2-resident by design, as in production use"},
             "clocks": clk,
             "e2e": {"value": round(e_rays / e2e_s / 1e6, 2), "unit": "Mrays/s",
@@ -318,11 +318,11 @@ def main():
             line["roofline"] = {
                 "bound": "hbm", "achieved": round(achieved, 1), "peak": hbm, "unit": "GB/s", "frac": round(achieved / hbm, 4),
                 # dram__bytes_read+write per traversal launch from the ncu --set full capture summarised in
-                # profiles/r01_ncu_full_v8_final.txt (85-140 MB per launch, mean of the ten captured launches): the ray / hit
-                # streams only -- nodes and triangles are served from L2
-                "traffic": 1.05e8, "algorithmic_bytes_per_launch": round(tr_rays * base["b_ray"] / max(1, trace_launches), 0),
+                # profiles/r01_ncu_full_v9_batched.txt (0.47-0.57 GB per launch of a four-sample wavefront, mean of the nine
+                # full launches captured): the ray / hit streams only -- nodes and triangles are served from L2
+                "traffic": 5.1e8, "algorithmic_bytes_per_launch": round(tr_rays * base["b_ray"] / max(1, trace_launches), 0),
                 "peak_source": which, "kernel": "k_trace<ClosestPolicy> + k_trace<ShadowPolicy>",
-                "issue_slot_utilisation_ncu": 0.70, "threads_per_instruction_ncu": 16.1, "l1_throughput_ncu": 0.60,
+                "issue_slot_utilisation_ncu": 0.72, "threads_per_instruction_ncu": 15.9, "l1_throughput_ncu": 0.68,
                 "bytes_per_ray": round(base["b_ray"], 1), "flops_per_ray": round(base["f_ray"], 1),
                 # the second roof of SURVEY 8d: algorithmic flops against the FP32 peak of the SMs (148 x 128 lanes x 2 x the
                 # SM clock sampled during the run); nominal, not measured

@@ -35,6 +35,7 @@ sys.path.insert(0, ROOT)
 
 W, H, SPP, BOUNCE, RR = 1920, 1080, 16, 5, 3
 SCENE = "sponza_atrium"
+L2_COPY_PEAK_GBS = 8140.2   # measured on this pool's B200: copy between two L2-resident 32 MB buffers (profiles/r01_l2_bandwidth.json)
 WORKLOAD = "sponza_lod 1920x1080 16spp 5-bounce NEE (configs[1] stand-in: full Sponza OBJ missing from snapshot)"
 
 
@@ -332,6 +333,13 @@ def main():
                 "nodes_per_ray": round(base["n_node"], 2), "tris_per_ray": round(base["n_tri"], 2),
                 "trace_share_of_step": round(tr_ms / max(1e-9, (dev_ms / args.steps) * max(1, min(args.steps, 3))), 3),
                 "trace_mrays_per_s": round(tr_rays / (tr_ms / 1e3) / 1e6, 1),
+                # the same kernels on their OWN layout: bytes they request (128 B per QuadNode step, 64 B per triangle test,
+                # 56 B ray in / hit out; counted by the kernels) per second, against the L2-resident copy bandwidth of this
+                # GPU (32 MB buffers, scripts/l2_bandwidth.py -> profiles/r01_l2_bandwidth.json) -- the roof that applies to
+                # a scene served from L2
+                "own_layout_fetched_gbs": round(tr_rays * line["own_layout"]["bytes_per_ray"] / (tr_ms / 1e3) / 1e9, 1),
+                "l2_copy_peak_gbs": L2_COPY_PEAK_GBS,
+                "own_layout_frac_of_l2_copy_peak": round(tr_rays * line["own_layout"]["bytes_per_ray"] / (tr_ms / 1e3) / 1e9 / L2_COPY_PEAK_GBS, 3),
                 "note": "algorithmic bytes on the REFERENCE layout and visit order (oracle counters, SURVEY 8d); the scene is L2-resident and "
                         "the ordered traversal over 4-slot nodes fetches ~2.5 KB/ray from L1/L2 (own_layout), so frac > 1 against the HBM copy peak is expected; "
                         "the kernel is instruction-issue bound (issue_slot_utilisation_ncu at threads_per_instruction_ncu of 32 lanes); "

@@ -37,8 +37,14 @@ def rays_for(scene, n, seed):
 
 def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 4_000_000
-    for name in ("cornell_mtrl", "sponza_atrium", "instanced", "instanced_dragon", "dragon_grid4"):
-        scene = ol.ref_scene(name, 8, 8)
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import flat_scene as fs
+    form = {"0": "default", "1": "streaming"}.get(os.environ.get("ATEN_B200_STREAM", ""), "picked at upload")
+    for name in ("cornell_mtrl", "sponza_atrium", "instanced", "instanced_dragon", "dragon_grid4", "dragon_grid4 flattened"):
+        if name.endswith(" flattened"):     # 16 distinct dragon meshes, 1.6 M triangles, 0.2 GB of nodes + triangles: beyond the L2
+            scene = fs.flatten_instances(ol.ref_scene(name.split()[0], 8, 8))
+        else:
+            scene = ol.ref_scene(name, 8, 8)
         r = PathTracing(0)
         r.UpdateSceneData(scene)
         bad_miss = bad_id = 0
@@ -62,7 +68,7 @@ def main():
             assert (got["a"][same].view(np.uint32) == want["a"][same].view(np.uint32)).all()
             total += m
         r.close()
-        print(json.dumps({"scene": name, "triangles": int(len(scene.triangles)), "rays": total, "hit_miss_disagreements": bad_miss,
+        print(json.dumps({"scene": name, "kernel_form": form, "triangles": int(len(scene.triangles)), "rays": total, "hit_miss_disagreements": bad_miss,
                           "differing_primitives": bad_id, "rate": bad_id / total, "largest_relative_distance_gap": worst}), flush=True)
 
 

@@ -150,6 +150,26 @@ def main():
             if not os.path.exists(d) or os.path.getsize(d) != os.path.getsize(s):
                 shutil.copyfile(s, d)
     print(f"[oracle/_ref] built {exe}")
+    # device_host: the same harness compiled with the `device` command and linked against the product library -- the
+    # reference's loaders + the C++ shim class + libaten_b200.so in one C++ program (tests/test_gpu_cpp_host.py).
+    lib_dir = os.path.join(os.path.dirname(HERE), "aten_b200")
+    if os.path.exists(os.path.join(lib_dir, "libaten_b200.so")):
+        hsrc = os.path.join(HERE, "ref_harness.cpp")
+        dobj = os.path.join(OUT, "obj", "ref_harness_device.o")
+        if a.force or not os.path.exists(dobj) or os.path.getmtime(dobj) < max(os.path.getmtime(hsrc), os.path.getmtime(__file__)) \
+                or os.path.getmtime(dobj) < os.path.getmtime(os.path.join(os.path.dirname(HERE), "include", "idaten_b200_shim.h")):
+            rc, out = sh(cxx + ["-DATN_WITH_DEVICE", "-c", hsrc, "-o", dobj])
+            if rc != 0:
+                print(out[-3000:], file=sys.stderr)
+                return 1
+        dexe = os.path.join(OUT, "device_host")
+        rc, out = sh(["g++", "-fopenmp", "-o", dexe] + [o for o in objs if o != obj_of(hsrc)] + [dobj] +
+                     ["-L", lib_dir, "-laten_b200", "-Wl,-rpath,$ORIGIN/../../aten_b200",
+                      "-Wl,--unresolved-symbols=ignore-all", "-lpthread", "-ldl"])
+        if rc != 0:
+            print(out[-4000:], file=sys.stderr)
+            return 1
+        print(f"[oracle/_ref] built {dexe}")
     return 0
 
 

@@ -633,7 +633,8 @@ int Usage()
         "         1 sample each; constant motion vector (mx,my) or 0; writes <prefix>.f<k>.f32 per frame and <prefix>.aov.f32)\n"
         "  restir <name> W H frames depth rr out_prefix [mx my]       (the reference's ReSTIR steps in the device renderer's order;\n"
         "         writes <prefix>.f<k>.f32 per frame and <prefix>.reservoirs.f32)\n"
-        "  cmj    out.bin                           (golden CMJ stream)\n");
+        "  cmj    out.bin                           (golden CMJ stream)\n"
+        "  device <name> W H frames spp depth out_image.f32   (device_host only: idaten_b200::PathTracing on the GPU, progressive)\n");
     return 2;
 }
 
@@ -680,6 +681,42 @@ int main(int argc, char** argv)
                flat.triangles.size(), flat.positions.size(), flat.nodes.size(), nn, flat.textures.size());
         return 0;
     }
+
+#ifdef ATN_WITH_DEVICE
+    if (cmd == "device") {
+        // The reference's device_renderer frame loop (src/device_renderer/main.cpp:133-148, 185-202) with
+        // idaten_b200::PathTracing in the place of idaten::PathTracing: scene built by the reference's own loaders
+        // and SBVH builder, handed over through the shim class, rendered on the GPU, image read back.  Only the
+        // `device_host` executable has this command (it links libaten_b200.so); `ref_harness` stays CPU-only.
+        if (argc < 10) return Usage();
+        const int W = atoi(argv[4]), H = atoi(argv[5]), frames = atoi(argv[6]), spp = atoi(argv[7]), depth = atoi(argv[8]);
+        Harness hs;
+        if (!hs.Build(name, W, H)) return 1;
+        try {
+            idaten_b200::PathTracing renderer;
+            const auto& nodes = hs.scene.getAccel()->getNodes();
+            auto camparam = hs.camera.param();
+            camparam.znear = 0.1f; camparam.zfar = 10000.0f;
+            renderer.UpdateSceneData(0, W, H, camparam, hs.ctxt, nodes, 0, 0);
+            renderer.SetEnableProgressive(true);
+            renderer.updateCamera(camparam);
+            double t0 = NowMs();
+            for (int f = 0; f < frames; f++) renderer.render(W, H, spp, depth);
+            std::vector<aten::vec4> img((size_t)W * H);
+            renderer.ReadbackImage(img.data(), img.size());
+            const double ms = NowMs() - t0;
+            WriteFile(argv[9], img.data(), img.size() * sizeof(aten::vec4));
+            printf("{\"scene\": \"%s\", \"w\": %d, \"h\": %d, \"frames\": %d, \"spp\": %d, \"depth\": %d, \"frame_count\": %u, "
+                   "\"wall_ms\": %.3f, \"host\": \"idaten_b200::PathTracing (C++ shim over the C ABI)\"}\n",
+                   name.c_str(), W, H, frames, spp, depth, renderer.GetFrameCount(), ms);
+        }
+        catch (const std::exception& e) {
+            fprintf(stderr, "device: %s\n", e.what());
+            return 3;
+        }
+        return 0;
+    }
+#endif
 
     if (cmd == "render" || cmd == "bench") {
         if (argc < 11) return Usage();

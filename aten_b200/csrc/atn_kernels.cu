@@ -1570,10 +1570,14 @@ static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene)
         return set_error(ATN_ERR_TOO_LARGE, "BVH needs a traversal stack of %d entries (limit %d)", enc.max_stack, kSmemStack + kLocalStackLarge);
     r->stack_need = enc.max_stack;
     {
-        // nodes + triangles beyond the L2: the traversal waits for device memory, not for issue slots -- use the variant
+        // nodes + triangles far beyond the L2: the traversal waits for device memory, not for issue slots -- use the variant
         // that issues an iteration's loads together (k_trace<.., kStream>).  ATEN_B200_STREAM=0/1 overrides (experiments).
+        // Where the forms cross, measured with 20 M incoherent rays into n distinct 100 k-triangle meshes (13.4 MB each;
+        // closest-hit Mrays/s, default / streaming): n = 14 (187 MB) 1 744 / 1 537, 25 (334 MB) 1 630 / 1 455,
+        // 40 (535 MB) 1 301 / 1 339, 60 (802 MB) 859 / 1 394, 100 (1.3 GB) 722 / 1 266: the hot upper levels of the trees
+        // stay in the 126 MB L2 long after the whole set has outgrown it, so the switch is at four times its size.
         const size_t set_bytes = enc.nodes.size() * sizeof(QuadNode) + enc.tris.size() * sizeof(TriLeaf);
-        r->stream_loads = r->l2_bytes > 0 && set_bytes > r->l2_bytes;
+        r->stream_loads = r->l2_bytes > 0 && set_bytes > 4 * r->l2_bytes;
         if (const char* ov = getenv("ATEN_B200_STREAM")) r->stream_loads = (ov[0] == '1');
     }
     CUDA_TRY(r->nodes.upload(enc.nodes.data(), enc.nodes.size(), r->stream));

@@ -291,6 +291,7 @@ def main():
     ap.add_argument("--only", default="")
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--rays", type=int, default=0, help="--only flat: number of rays (default 100 M)")
+    ap.add_argument("--copies", type=int, default=0, help="--only flat: number of distinct meshes (default all 100)")
     a = ap.parse_args()
     if not ol.have_ref():
         sys.exit("oracle/_ref not present")
@@ -299,8 +300,9 @@ def main():
         restir_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 4, label="N1 ReSTIR, sponza_lod 1080p, 8-frame sequence")
         return
     if a.only == "flat":
-        ray_stress_flat("dragon_grid10", a.rays or (100_000_000 if not q else 5_000_000), copies=None if not q else 9,
-                        label="C5: incoherent secondary rays into 100 distinct dragon meshes (10 M triangles, ~1.4 GB of nodes + triangles)")
+        ray_stress_flat("dragon_grid10", a.rays or (100_000_000 if not q else 5_000_000), copies=a.copies or (None if not q else 9),
+                        label="C5: incoherent secondary rays into 100 distinct dragon meshes (10 M triangles, ~1.4 GB of nodes + triangles)"
+                        if not (a.copies or q) else f"incoherent secondary rays into {a.copies or 9} distinct dragon meshes")
         return
     if a.only == "svgf":
         svgf_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 3, label="N1 SVGF, sponza_lod 1080p, 8-frame sequence")

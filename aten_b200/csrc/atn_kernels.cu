@@ -1586,10 +1586,11 @@ static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene)
     CUDA_TRY(cudaStreamSynchronize(r->stream));   // enc goes out of scope
     r->bv.nodes = reinterpret_cast<const float4*>(r->nodes.p);
     if (r->bv.node_tex) { cudaDestroyTextureObject(r->bv.node_tex); r->bv.node_tex = 0; }
-    if (ATN_NODE_TEX && !enc.nodes.empty()) {
-        // linear float4 texture over the node array; tex1Dfetch addresses 2^27 texels = 16 M QuadNodes (2 GB)
-        if (enc.nodes.size() * 8 > ((size_t)1 << 27))
-            return set_error(ATN_ERR_TOO_LARGE, "%zu nodes exceed the linear-texture limit of %zu", enc.nodes.size(), ((size_t)1 << 27) / 8);
+    // linear float4 texture over the node array; tex1Dfetch addresses 2^27 texels = 16 M QuadNodes (2 GB).  Only the
+    // default form of the kernel reads nodes through it: a larger set (which is far beyond the L2 anyway) is served by
+    // the streaming form, with plain loads.
+    if (enc.nodes.size() * 8 > ((size_t)1 << 27)) r->stream_loads = true;
+    if (ATN_NODE_TEX && !enc.nodes.empty() && !r->stream_loads) {
         cudaResourceDesc rd{}; rd.resType = cudaResourceTypeLinear; rd.res.linear.devPtr = r->nodes.p;
         rd.res.linear.desc = cudaCreateChannelDesc<float4>(); rd.res.linear.sizeInBytes = enc.nodes.size() * sizeof(QuadNode);
         cudaTextureDesc td{}; td.readMode = cudaReadModeElementType;

@@ -86,8 +86,12 @@ def test_flat_scene_encoder_emulation(flat):
 
 
 @pytest.mark.gpu
-def test_flat_scene_gpu_vs_oracle(flat):
+@pytest.mark.parametrize("form", ["0", "1"])
+def test_flat_scene_gpu_vs_oracle(flat, monkeypatch, form):
+    """Both forms of the traversal kernel (the library picks one at upload from the size of the encoded set; the
+    override is read there): "0" the default form, "1" the load-streaming form that scenes far beyond the L2 get."""
     from aten_b200 import PathTracing
+    monkeypatch.setenv("ATEN_B200_STREAM", form)
     rays = random_rays(flat, 200_000, 5)
     rng = np.random.default_rng(6)
     diag = float(np.linalg.norm(flat.config["scene_bbox_max"][0] - flat.config["scene_bbox_min"][0]))
@@ -99,3 +103,23 @@ def test_flat_scene_gpu_vs_oracle(flat):
     want = ol.trace_closest(flat, rays)
     assert_hits_equal(got, want)
     assert (vis == ol.trace_any(flat, rays, dist)).mean() >= 1.0 - 3e-4       # near ties at the distance limit
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["sponza_atrium", "instanced"])
+def test_streaming_form_renders_the_same_image(golden, monkeypatch, name):
+    """The path tracer through the load-streaming form of the traversal kernel (closest-hit and shadow policies):
+    both forms are exact traversals with the same tie rule, so the images are bit-identical."""
+    from aten_b200 import PathTracing
+    from tests.conftest import bits
+    m = golden.meta[name]
+    imgs = []
+    for form in ("0", "1"):
+        monkeypatch.setenv("ATEN_B200_STREAM", form)
+        with PathTracing(0) as r:
+            r.UpdateSceneData(golden.scene(name))
+            r.SetEnableProgressive(False)
+            r.render(m["w"], m["h"], 2, 5, 3)
+            imgs.append(r.readback().copy())
+    assert (bits(imgs[0]) == bits(imgs[1])).all()
+    assert np.isfinite(imgs[0]).all() and imgs[0][..., :3].max() > 0

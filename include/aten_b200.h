@@ -313,6 +313,7 @@ ATN_API int atn_readback(AtnRenderer* r, AtnVec4* host_image, size_t pixel_count
 ATN_API int atn_readback_aov(AtnRenderer* r, AtnVec4* normal_depth, AtnVec4* albedo_meshid, size_t pixel_count);
 /* Device pointer (float4[W*H]) of the image, for NCCL / torch interop; owned by the handle. */
 ATN_API int atn_device_image(AtnRenderer* r, void** device_ptr, size_t* pixel_count);
+/* Counters of the last call on the handle.  After a device-resident ray query this waits for the stream first. */
 ATN_API int atn_get_stats(AtnRenderer* r, AtnStats* out);
 /* 1: time the traversal kernels separately with CUDA events (fills AtnStats.trace_ms). */
 ATN_API int atn_set_profiling(AtnRenderer* r, int enable);
@@ -329,7 +330,8 @@ ATN_API int atn_trace_closest(AtnRenderer* r, const AtnRay* rays, const float* t
  * visible[i] = 1 iff nothing is hit closer than dist[i]. */
 ATN_API int atn_trace_any(AtnRenderer* r, const AtnRay* rays, const float* dist, size_t n,
                           uint8_t* visible);
-/* Device-resident variants (pointers are CUDA device pointers; asynchronous on the stream). */
+/* Device-resident variants (pointers are CUDA device pointers; asynchronous on the stream).  Their CUDA-event time and
+ * visit counts are collected by the next atn_get_stats, which waits for the stream. */
 ATN_API int atn_trace_closest_device(AtnRenderer* r, const void* rays_dev, const void* t_max_dev,
                                      size_t n, void* hits_dev);
 ATN_API int atn_trace_any_device(AtnRenderer* r, const void* rays_dev, const void* dist_dev,

@@ -211,6 +211,8 @@ def main():
         st = r.stats()
         if world > 1:
             dist.reduce(image_t, dst=0, op=dist.ReduceOp.SUM)
+            # the reduce runs on torch's stream, the next step clears the image on the renderer's: finish it first
+            torch.cuda.current_stream().synchronize()
         return st
 
     def step_e2e():

@@ -421,6 +421,28 @@ def test_live_reference_instanced_dragon_grid():
         r.close()
 
 
+@needs_ref
+def test_non_finite_sample_of_the_reference_is_reproduced():
+    """The reference's Disney material yields a non-finite throughput about once per 8 M samples (found at 4K on the
+    instanced dragon scene: frame 11, pixel (2140, 1526) -- the stock aten::PathTracing writes (inf, inf, inf) there, as
+    does the restatement).  Results identical to the reference's include that pixel: same position, no other one."""
+    W, H, frame = 3840, 2160, 11
+    scene = ol.ref_scene("instanced_dragon", W, H)
+    with PathTracing(0) as r:
+        r.UpdateSceneData(scene)
+        r.SetEnableProgressive(False)
+        r.render_region(W, H, 0, 0, W, H, frame, frame + 1, 5, 3)
+        img = r.readback()
+    bad = ~np.isfinite(img[..., :3]).all(axis=2)
+    assert list(zip(*np.nonzero(bad))) == [(1526, 2140)]
+    assert np.isinf(img[1526, 2140, :3]).all()
+    want, _, _ = ol.render(scene, frames=1, first_frame=frame)
+    assert ((~np.isfinite(want[..., :3]).all(axis=2)) == bad).all()
+    ok = ~bad
+    rmse = np.sqrt(np.mean((img[ok][:, :3] - want[ok][:, :3]) ** 2)); scale = np.sqrt(np.mean(want[ok][:, :3] ** 2))
+    assert rmse <= 2e-3 * scale
+
+
 @pytest.mark.parametrize("name", ["cornell_mtrl", "sponza_atrium"])
 def test_first_hit_aovs_vs_oracle(golden, renderers, name):
     """normal+depth and albedo+meshid of the first hit (FillBasicAOVs with an identity matrix as in the

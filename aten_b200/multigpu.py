@@ -42,7 +42,9 @@ def partition_tiles(width: int, height: int, world: int, rank: int, tile: int = 
 
 
 def combine_images(image, group=None, dst: int = 0):
-    """``reduce(SUM)`` of the float4 sum images onto ``dst`` (in place)."""
+    """``reduce(SUM)`` of the float4 sum images onto ``dst`` (in place).  On CUDA the reduce is asynchronous on torch's
+    current stream while the renderer clears and writes its image on its own stream: synchronize torch's stream before
+    the next ``reset()`` / render on that handle."""
     import torch.distributed as dist
     dist.reduce(image, dst=dst, op=dist.ReduceOp.SUM, group=group)
     return image

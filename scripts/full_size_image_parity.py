@@ -3,7 +3,7 @@
 path against the CPU restatement (bit-exact against the reference) with the same seeds, per frame accumulated with
 the FilmProgressive formula.  The restatement needs ~30 s of all host cores per sample at this size, hence a script
 and not a test; prints one JSON line (relative RMSE, relMSE, share of pixels equal within 1e-4 relative).
-    python scripts/full_size_image_parity.py [spp]"""
+    python scripts/full_size_image_parity.py [spp [scene]]"""
 import json
 import os
 import sys
@@ -19,8 +19,12 @@ from tests import oracle_lib as ol  # noqa: E402
 
 def main():
     spp = int(sys.argv[1]) if len(sys.argv) > 1 else 4
+    name = sys.argv[2] if len(sys.argv) > 2 else "sponza_atrium"
     W, H = 1920, 1080
-    scene = sio.load_scene(os.path.join(ROOT, "tests", "golden", "sponza_atrium.atnscene.gz")).with_size(W, H)
+    if name == "sponza_atrium":
+        scene = sio.load_scene(os.path.join(ROOT, "tests", "golden", "sponza_atrium.atnscene.gz")).with_size(W, H)
+    else:                                   # built on the spot by the reference's loaders (needs oracle/_ref)
+        scene = ol.ref_scene(name, W, H)
     with PathTracing(0) as r:
         r.UpdateSceneData(scene)
         r.SetEnableProgressive(True)
@@ -30,7 +34,9 @@ def main():
     t0 = time.perf_counter()
     want, _, stats = ol.render(scene, frames=spp, max_depth=5, rr_depth=3, threads=os.cpu_count() or 1)
     cpu_s = time.perf_counter() - t0
-    a = got[..., :3].astype(np.float64); b = want[..., :3].astype(np.float64)
+    finite = np.isfinite(got[..., :3]).all(axis=2) & np.isfinite(want[..., :3]).all(axis=2)
+    same_non_finite = bool((np.isfinite(got[..., :3]).all(axis=2) == np.isfinite(want[..., :3]).all(axis=2)).all())
+    a = np.where(finite[..., None], got[..., :3], 0).astype(np.float64); b = np.where(finite[..., None], want[..., :3], 0).astype(np.float64)
     rmse = float(np.sqrt(np.mean((a - b) ** 2))); scale = float(np.sqrt(np.mean(b ** 2)))
     relmse = float(np.mean((a - b) ** 2 / (b ** 2 + 1e-2)))
     same = (np.abs(a - b) <= 1e-4 * np.maximum(np.abs(b), 1e-3)).all(axis=2)
@@ -39,11 +45,11 @@ def main():
     # a near-tie hit) hold two different random paths; with an IBL in the scene a few of them are fireflies
     rmse_same = float(np.sqrt(np.mean((a[same] - b[same]) ** 2)) / np.sqrt(np.mean(b[same] ** 2)))
     d = np.abs(a - b).max(axis=2)
-    print(json.dumps({"scene": "sponza_atrium", "w": W, "h": H, "spp": spp, "bounces": 5,
+    print(json.dumps({"scene": name, "w": W, "h": H, "spp": spp, "bounces": 5,
                       "relative_rmse": rmse / scale, "relmse": relmse, "pixels_equal_within_1e-4": close,
                       "differing_pixels": int((~same).sum()), "relative_rmse_over_the_equal_pixels": rmse_same,
                       "largest_pixel_differences": [float(x) for x in np.sort(d.ravel())[-5:][::-1]], "median_differing_pixel_difference": float(np.median(d[~same])) if (~same).any() else 0.0,
-                      "mean_gpu": float(a.mean()), "mean_restatement": float(b.mean()),
+                      "non_finite_pixels": int((~finite).sum()), "same_non_finite_pixels": same_non_finite, "mean_gpu": float(a.mean()), "mean_restatement": float(b.mean()),
                       "gpu_rays": int(st["closest_rays"] + st["shadow_rays"]), "restatement_rays": int(stats[0] + stats[1]),
                       "gpu_ms": round(st["device_ms"], 2), "restatement_s": round(cpu_s, 1), "host_threads": os.cpu_count()}), flush=True)
 

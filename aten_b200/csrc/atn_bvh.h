@@ -252,6 +252,10 @@ struct WideBuilder {
     }
 
     struct Slot { int32_t node, boxnode; };   // boxnode: original node whose box the slot tests, -1 = always hit
+    struct SlotList {                         // at most four slots, plus the two a replacement inserts before one is dropped
+        Slot s[6];
+        int n{ 0 };
+    };
 
     static float area(const AtnBvhNode& n)
     {
@@ -259,17 +263,20 @@ struct WideBuilder {
         return dx * dy + dy * dz + dz * dx;
     }
 
-    void push_kids(std::vector<Slot>& slots, size_t at, int32_t X, bool x_tested)
+    // children of X in order, inserted at `at`; a leaf child inherits X's box unless X's box is known to be hit
+    void push_kids(SlotList& slots, int at, int32_t X, bool x_tested)
     {
-        // children of X in order; a leaf child inherits X's box unless X's box is known to be hit
-        std::vector<Slot> ins;
+        Slot ins[2];
+        int ni = 0;
         const int32_t ks[2] = { kid0[X], kid1[X] };
         for (int k = 0; k < 2; k++) {
             if (ks[k] < 0) continue;
-            if (inner(ks[k])) ins.push_back({ ks[k], ks[k] });
-            else if (leafref[ks[k]] != kRefNull) ins.push_back({ ks[k], x_tested ? -1 : X });
+            if (inner(ks[k])) ins[ni++] = Slot{ ks[k], ks[k] };
+            else if (leafref[ks[k]] != kRefNull) ins[ni++] = Slot{ ks[k], x_tested ? -1 : X };
         }
-        slots.insert(slots.begin() + at, ins.begin(), ins.end());
+        for (int k = slots.n - 1; k >= at; k--) slots.s[k + ni] = slots.s[k];
+        for (int k = 0; k < ni; k++) slots.s[at + k] = ins[k];
+        slots.n += ni;
     }
 
     int nkids_live(int32_t X) const
@@ -292,32 +299,33 @@ struct WideBuilder {
     }
 
     // QuadNode for the slots `slots` (already the children of a tested node); returns its index
-    int32_t emit(std::vector<Slot> slots, int32_t depth)
+    int32_t emit(SlotList slots, int32_t depth)
     {
         if (depth > depth_seen) depth_seen = depth;
         for (;;) {
             int best = -1; float best_area = -1.0f;
-            for (size_t s = 0; s < slots.size(); s++) {
-                const int32_t X = slots[s].node;
+            for (int s = 0; s < slots.n; s++) {
+                const int32_t X = slots.s[s].node;
                 if (!inner(X) || !nested[X]) continue;
-                if (slots.size() - 1 + (size_t)nkids_live(X) > 4) continue;
+                if (slots.n - 1 + nkids_live(X) > 4) continue;
                 const float a = area(list[X]);
                 if (a > best_area) { best_area = a; best = (int)s; }
             }
             if (best < 0) break;
-            const int32_t X = slots[best].node;
-            slots.erase(slots.begin() + best);
-            push_kids(slots, (size_t)best, X, false);
+            const int32_t X = slots.s[best].node;
+            for (int k = best; k + 1 < slots.n; k++) slots.s[k] = slots.s[k + 1];
+            slots.n--;
+            push_kids(slots, best, X, false);
             out->replaced++;
         }
-        if (slots.empty()) return kRefNull;
+        if (slots.n == 0) return kRefNull;
         const int32_t self = (int32_t)out->nodes.size();
         out->nodes.emplace_back();
         int32_t refs[4] = { kRefNull, kRefNull, kRefNull, kRefNull };
-        for (size_t s = 0; s < slots.size(); s++) {
-            const int32_t X = slots[s].node;
+        for (int s = 0; s < slots.n; s++) {
+            const int32_t X = slots.s[s].node;
             if (inner(X)) {
-                std::vector<Slot> sub;
+                SlotList sub;
                 push_kids(sub, 0, X, true);
                 refs[s] = emit(sub, depth + 1);
             }
@@ -330,9 +338,9 @@ struct WideBuilder {
             // fails for any finite t_max and the kernel needs no separate test of the reference
             const float inf = std::numeric_limits<float>::infinity();
             float mn[3] = { inf, inf, inf }, mx[3] = { inf, inf, inf };
-            if ((size_t)s < slots.size() && refs[s] != kRefNull) {
-                if (slots[s].boxnode < 0) { for (int a = 0; a < 3; a++) { mn[a] = -big; mx[a] = big; } }
-                else for (int a = 0; a < 3; a++) { mn[a] = list[slots[s].boxnode].boxmin[a]; mx[a] = list[slots[s].boxnode].boxmax[a]; }
+            if (s < slots.n && refs[s] != kRefNull) {
+                if (slots.s[s].boxnode < 0) { for (int a = 0; a < 3; a++) { mn[a] = -big; mx[a] = big; } }
+                else for (int a = 0; a < 3; a++) { mn[a] = list[slots.s[s].boxnode].boxmin[a]; mx[a] = list[slots.s[s].boxnode].boxmax[a]; }
                 out->slots_used++;
             }
             const int g = (s >> 1) * 3, h = (s & 1);
@@ -361,7 +369,8 @@ struct WideBuilder {
         scan(0, 0);
         if (!out->error.empty()) return kRefNull;
         if (!inner(0)) return leafref[0];        // a leaf root is never box-tested by the reference
-        std::vector<Slot> slots{ Slot{ 0, 0 } };
+        SlotList slots;
+        slots.s[0] = Slot{ 0, 0 }; slots.n = 1;
         return emit(slots, 1);
     }
 };
@@ -373,6 +382,13 @@ inline WideBvh encode_wide(const AtnSceneBlob* scene)
     WideBvh out;
     if (scene->node_list_count == 0) return out;
     EncodedBvh leaves;
+    {
+        size_t total = 0;
+        for (uint32_t k = 0; k < scene->node_list_count; k++) total += scene->node_list_sizes[k];
+        leaves.tris.reserve(total / 2 + 1);         // one triangle per leaf, about half of a binary tree's nodes
+        out.nodes.reserve(total / 4 + 1);           // measured: 4.2 reference nodes per QuadNode
+        out.stack_need.reserve(total / 4 + 1);
+    }
     std::vector<int32_t> roots(scene->node_list_count, kRefNull);
     for (uint32_t k = 1; k < scene->node_list_count; k++) {
         if (scene->node_list_sizes[k] == 0) continue;

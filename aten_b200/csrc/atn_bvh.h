@@ -23,6 +23,8 @@
 #include <stdint.h>
 #include <string.h>
 #include <algorithm>
+#include <atomic>
+#include <thread>
 #include <cmath>
 #include <limits>
 #include <string>
@@ -390,12 +392,53 @@ inline WideBvh encode_wide(const AtnSceneBlob* scene)
         out.stack_need.reserve(total / 4 + 1);
     }
     std::vector<int32_t> roots(scene->node_list_count, kRefNull);
-    for (uint32_t k = 1; k < scene->node_list_count; k++) {
+    // Bottom lists are independent of each other: each is encoded on its own (in parallel when the scene is large) with
+    // list-local node and leaf numbers, then appended in list order with the numbers moved to their global positions --
+    // the result is what the lists encoded one after the other into the shared arrays would give.
+    struct Part { WideBvh w; EncodedBvh l; int32_t root{ kRefNull }; };
+    const uint32_t nlists = scene->node_list_count;
+    std::vector<Part> parts(nlists);
+    auto encode_list = [&](uint32_t k) {
+        Part& pt = parts[k];
+        const uint32_t cnt = scene->node_list_sizes[k];
+        pt.l.tris.reserve(cnt / 2 + 1); pt.w.nodes.reserve(cnt / 4 + 1); pt.w.stack_need.reserve(cnt / 4 + 1);
+        detail::ListBuilder lb{ scene->node_lists[k], cnt, false, scene, &pt.l, &roots };
+        detail::WideBuilder wb{ scene->node_lists[k], cnt, false, &pt.l, &lb, &pt.w };
+        pt.root = wb.run();
+    };
+    {
+        size_t total = 0;
+        for (uint32_t k = 1; k < nlists; k++) total += scene->node_list_sizes[k];
+        unsigned nthreads = std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
+        if (total < 400000 || nlists < 3) nthreads = 1;
+        std::atomic<uint32_t> next{ 1 };
+        auto worker = [&]() {
+            for (uint32_t k = next.fetch_add(1); k < nlists; k = next.fetch_add(1))
+                if (scene->node_list_sizes[k] > 0) encode_list(k);
+        };
+        std::vector<std::thread> pool;
+        for (unsigned t = 1; t < nthreads; t++) pool.emplace_back(worker);
+        worker();
+        for (auto& th : pool) th.join();
+    }
+    for (uint32_t k = 1; k < nlists; k++) {
         if (scene->node_list_sizes[k] == 0) continue;
-        detail::ListBuilder lb{ scene->node_lists[k], scene->node_list_sizes[k], false, scene, &leaves, &roots };
-        detail::WideBuilder wb{ scene->node_lists[k], scene->node_list_sizes[k], false, &leaves, &lb, &out };
-        roots[k] = wb.run();
-        if (!out.error.empty()) return out;
+        Part& pt = parts[k];
+        if (!pt.w.error.empty()) { out.error = pt.w.error; return out; }
+        const int32_t node_off = (int32_t)out.nodes.size(), leaf_off = (int32_t)leaves.tris.size();
+        auto move_ref = [&](int32_t ref) -> int32_t {
+            if (ref >= 0) return ref + node_off;
+            if (ref == kRefNull || ref == kRefExit || ref == kRefDone) return ref;
+            return leaf_ref(~ref + leaf_off);
+        };
+        for (QuadNode& qn : pt.w.nodes)
+            for (int sl = 0; sl < 4; sl++) qn.ref[sl] = move_ref(qn.ref[sl]);
+        out.nodes.insert(out.nodes.end(), pt.w.nodes.begin(), pt.w.nodes.end());
+        out.stack_need.insert(out.stack_need.end(), pt.w.stack_need.begin(), pt.w.stack_need.end());
+        leaves.tris.insert(leaves.tris.end(), pt.l.tris.begin(), pt.l.tris.end());
+        out.slots_used += pt.w.slots_used; out.replaced += pt.w.replaced; out.not_nested += pt.w.not_nested;
+        roots[k] = move_ref(pt.root);
+        pt = Part();                                  // release the list's partial arrays
     }
     if (scene->node_list_sizes[0] > 0) {
         detail::ListBuilder lb{ scene->node_lists[0], scene->node_list_sizes[0], true, scene, &leaves, &roots };

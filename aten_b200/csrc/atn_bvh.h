@@ -57,7 +57,17 @@ constexpr int32_t kRefDone = INT32_MIN + 2;   // stack sentinel below every ray'
 struct EncodedBvh {          // leaf records collected while a node list is scanned
     std::vector<TriLeaf> tris;
     std::vector<InstLeaf> insts;
+    std::vector<int32_t> inst_list;   // per instance leaf: the number of its bottom node list
     std::string error;
+};
+
+// What the top layer needs to know about the encoded bottom trees.  A top-layer update (Renderer::updateBVH: list 0,
+// objects and matrices change every frame, renderer.cpp:133-153) re-encodes list 0 against this and touches nothing else.
+struct BottomInfo {
+    std::vector<int32_t> roots;      // per node list: reference of its root, kRefNull for an empty list (entry 0 unused)
+    std::vector<int32_t> need;       // per node list: stack entries the traversal can hold below that root
+    std::vector<float> box;          // per node list: root box, min xyz then max xyz (node 0 of the reference's list)
+    int32_t node_count{ 0 };         // QuadNodes of all bottom lists; the top layer's nodes follow them
 };
 
 inline int32_t leaf_ref(int32_t leaf_index) { return ~leaf_index; }
@@ -70,7 +80,7 @@ struct ListBuilder {
     bool top;
     const AtnSceneBlob* scene;
     EncodedBvh* out;
-    const std::vector<int32_t>* list_roots;   // for the top layer: root refs of the bottom lists
+    const BottomInfo* bottom;                 // for the top layer: roots, stack needs and root boxes of the bottom lists
 
     static bool is_leaf(const AtnBvhNode& n) { return n.object_id >= 0 || n.primid >= 0; }
 
@@ -80,14 +90,16 @@ struct ListBuilder {
             if (!(n.exid >= 0)) return kRefNull;        // no external tree: sphere / cube, never hit (F5)
             uint32_t bits; memcpy(&bits, &n.exid, 4);
             const int32_t exid = (int32_t)(bits & 0x7fffu);   // mainExid:15 (threaded_bvh.h:29-37)
-            if (exid <= 0 || exid >= (int32_t)list_roots->size()) return kRefNull;
+            if (exid <= 0 || exid >= (int32_t)bottom->roots.size()) return kRefNull;
+            if ((uint32_t)n.object_id >= scene->object_count) { out->error = "object index out of range in the top layer"; return kRefNull; }
             InstLeaf il;
             il.objid = (int32_t)n.object_id;
-            il.root = (*list_roots)[exid];
+            il.root = bottom->roots[exid];
             const AtnObjectParameter& obj = scene->objects[(uint32_t)n.object_id];
             il.w2l = obj.mtx_id >= 0 ? obj.mtx_id + 1 : -1;    // threaded_bvh_traverser.h:149-158
             il.meshid = (int32_t)n.meshid;
             out->insts.push_back(il);
+            out->inst_list.push_back(exid);
             return leaf_ref((int32_t)out->insts.size() - 1);
         }
         if (!(n.primid >= 0)) return kRefNull;
@@ -127,20 +139,18 @@ struct ListBuilder {
         }
         const InstLeaf& il = out->insts[idx];
         const AtnObjectParameter& obj = scene->objects[il.objid];
-        // find the bottom list of this instance again: its root box is node 0 of that list
-        const AtnBvhNode* root = nullptr;
-        for (uint32_t k = 1; k < scene->node_list_count; k++) {
-            if ((*list_roots)[k] == il.root && scene->node_list_sizes[k] > 0) { root = &scene->node_lists[k][0]; break; }
-        }
+        // the instance's root box: node 0 of its bottom list
+        const int32_t lk = out->inst_list[idx];
+        const float* rb = (il.root != kRefNull && (size_t)lk * 6 + 5 < bottom->box.size()) ? &bottom->box[(size_t)lk * 6] : nullptr;
         const float big = 3.0e38f;
-        if (!root) { for (int a = 0; a < 3; a++) { mn[a] = -big; mx[a] = big; } return; }
+        if (!rb) { for (int a = 0; a < 3; a++) { mn[a] = -big; mx[a] = big; } return; }
         float M[16] = { 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1 };
         if (obj.mtx_id >= 0 && (uint32_t)obj.mtx_id < scene->matrix_count) memcpy(M, scene->matrices[obj.mtx_id].m, sizeof(M));
         for (int a = 0; a < 3; a++) { mn[a] = big; mx[a] = -big; }
         for (int c = 0; c < 8; c++) {
-            const double x = (c & 1) ? root->boxmax[0] : root->boxmin[0];
-            const double y = (c & 2) ? root->boxmax[1] : root->boxmin[1];
-            const double z = (c & 4) ? root->boxmax[2] : root->boxmin[2];
+            const double x = (c & 1) ? rb[3] : rb[0];
+            const double y = (c & 2) ? rb[4] : rb[1];
+            const double z = (c & 4) ? rb[5] : rb[2];
             for (int a = 0; a < 3; a++) {
                 const double w = M[a * 4 + 0] * x + M[a * 4 + 1] * y + M[a * 4 + 2] * z + M[a * 4 + 3];
                 mn[a] = std::min(mn[a], (float)w); mx[a] = std::max(mx[a], (float)w);
@@ -296,8 +306,8 @@ struct WideBuilder {
     {
         if (ref >= 0) return (size_t)ref < out->stack_need.size() ? out->stack_need[ref] : 0;
         if (ref == kRefNull || !top) return 0;
-        const int32_t root = leaves->insts[~ref].root;
-        return 1 + (root >= 0 && (size_t)root < out->stack_need.size() ? out->stack_need[root] : 0);
+        const int32_t lk = leaves->inst_list[~ref];
+        return 1 + lb->bottom->need[lk];
     }
 
     // QuadNode for the slots `slots` (already the children of a tested node); returns its index
@@ -379,36 +389,65 @@ struct WideBuilder {
 
 }  // namespace detail
 
-inline WideBvh encode_wide(const AtnSceneBlob* scene)
+// The top layer alone (node list 0) against already encoded bottom trees: its QuadNodes (references numbered from
+// bottom.node_count on), the instance leaves with their world boxes, the root and the exact worst-case stack depth of
+// the whole two-level walk.  `scene` supplies objects and matrices only.
+inline WideBvh encode_top(const AtnBvhNode* top_nodes, uint32_t top_count, const AtnSceneBlob* scene, const BottomInfo& bottom)
+{
+    WideBvh out;
+    if (top_count == 0) return out;
+    EncodedBvh leaves;
+    detail::ListBuilder lb{ top_nodes, top_count, true, scene, &leaves, &bottom };
+    detail::WideBuilder wb{ top_nodes, top_count, true, &leaves, &lb, &out };
+    out.top_root = wb.run();
+    if (out.error.empty() && !leaves.error.empty()) out.error = leaves.error;
+    if (!out.error.empty()) return out;
+    const int32_t node_off = bottom.node_count;
+    for (QuadNode& qn : out.nodes)
+        for (int sl = 0; sl < 4; sl++) if (qn.ref[sl] >= 0) qn.ref[sl] += node_off;     // leaf references are instance numbers
+    if (out.top_root >= 0) out.top_root += node_off;
+    out.insts.resize(leaves.insts.size());
+    for (size_t i = 0; i < leaves.insts.size(); i++) {
+        const InstLeaf& il = leaves.insts[i];
+        InstLeafW& w = out.insts[i];
+        w.objid = il.objid; w.root = il.root; w.w2l = il.w2l; w.meshid = il.meshid;
+        float mn[3], mx[3];
+        lb.leaf_bounds(leaf_ref((int32_t)i), mn, mx);
+        for (int a = 0; a < 3; a++) { w.wmin[a] = mn[a]; w.wmax[a] = mx[a]; }
+        w.pad0 = 0.0f; w.pad1 = 0.0f; w.pad2[0] = w.pad2[1] = w.pad2[2] = w.pad2[3] = 0;
+    }
+    out.max_stack = 0;
+    if (out.top_root >= 0) out.max_stack = out.stack_need[out.top_root - node_off];
+    else if (out.top_root != kRefNull && !out.insts.empty())       // the top layer is a single instance leaf
+        out.max_stack = 1 + bottom.need[leaves.inst_list[~out.top_root]];
+    out.max_stack += 2;    // the sentinel at the bottom of every ray's stack, and one entry of slack
+    return out;
+}
+
+// The whole scene.  `info` (optional) receives what later top-layer updates need (encode_top).
+inline WideBvh encode_wide(const AtnSceneBlob* scene, BottomInfo* info = nullptr)
 {
     WideBvh out;
     if (scene->node_list_count == 0) return out;
-    EncodedBvh leaves;
-    {
-        size_t total = 0;
-        for (uint32_t k = 0; k < scene->node_list_count; k++) total += scene->node_list_sizes[k];
-        leaves.tris.reserve(total / 2 + 1);         // one triangle per leaf, about half of a binary tree's nodes
-        out.nodes.reserve(total / 4 + 1);           // measured: 4.2 reference nodes per QuadNode
-        out.stack_need.reserve(total / 4 + 1);
-    }
-    std::vector<int32_t> roots(scene->node_list_count, kRefNull);
+    const uint32_t nlists = scene->node_list_count;
+    BottomInfo bottom;
+    bottom.roots.assign(nlists, kRefNull); bottom.need.assign(nlists, 0); bottom.box.assign((size_t)nlists * 6, 0.0f);
     // Bottom lists are independent of each other: each is encoded on its own (in parallel when the scene is large) with
     // list-local node and leaf numbers, then appended in list order with the numbers moved to their global positions --
-    // the result is what the lists encoded one after the other into the shared arrays would give.
+    // the result is what the lists encoded one after the other into shared arrays would give.
     struct Part { WideBvh w; EncodedBvh l; int32_t root{ kRefNull }; };
-    const uint32_t nlists = scene->node_list_count;
     std::vector<Part> parts(nlists);
     auto encode_list = [&](uint32_t k) {
         Part& pt = parts[k];
         const uint32_t cnt = scene->node_list_sizes[k];
         pt.l.tris.reserve(cnt / 2 + 1); pt.w.nodes.reserve(cnt / 4 + 1); pt.w.stack_need.reserve(cnt / 4 + 1);
-        detail::ListBuilder lb{ scene->node_lists[k], cnt, false, scene, &pt.l, &roots };
+        detail::ListBuilder lb{ scene->node_lists[k], cnt, false, scene, &pt.l, nullptr };
         detail::WideBuilder wb{ scene->node_lists[k], cnt, false, &pt.l, &lb, &pt.w };
         pt.root = wb.run();
     };
+    size_t total = 0;
+    for (uint32_t k = 1; k < nlists; k++) total += scene->node_list_sizes[k];
     {
-        size_t total = 0;
-        for (uint32_t k = 1; k < nlists; k++) total += scene->node_list_sizes[k];
         unsigned nthreads = std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
         if (total < 400000 || nlists < 3) nthreads = 1;
         std::atomic<uint32_t> next{ 1 };
@@ -421,11 +460,13 @@ inline WideBvh encode_wide(const AtnSceneBlob* scene)
         worker();
         for (auto& th : pool) th.join();
     }
+    out.nodes.reserve(total / 4 + scene->node_list_sizes[0] + 1);
+    out.tris.reserve(total / 2 + 1);
     for (uint32_t k = 1; k < nlists; k++) {
         if (scene->node_list_sizes[k] == 0) continue;
         Part& pt = parts[k];
         if (!pt.w.error.empty()) { out.error = pt.w.error; return out; }
-        const int32_t node_off = (int32_t)out.nodes.size(), leaf_off = (int32_t)leaves.tris.size();
+        const int32_t node_off = (int32_t)out.nodes.size(), leaf_off = (int32_t)out.tris.size();
         auto move_ref = [&](int32_t ref) -> int32_t {
             if (ref >= 0) return ref + node_off;
             if (ref == kRefNull || ref == kRefExit || ref == kRefDone) return ref;
@@ -435,35 +476,27 @@ inline WideBvh encode_wide(const AtnSceneBlob* scene)
             for (int sl = 0; sl < 4; sl++) qn.ref[sl] = move_ref(qn.ref[sl]);
         out.nodes.insert(out.nodes.end(), pt.w.nodes.begin(), pt.w.nodes.end());
         out.stack_need.insert(out.stack_need.end(), pt.w.stack_need.begin(), pt.w.stack_need.end());
-        leaves.tris.insert(leaves.tris.end(), pt.l.tris.begin(), pt.l.tris.end());
+        out.tris.insert(out.tris.end(), pt.l.tris.begin(), pt.l.tris.end());
         out.slots_used += pt.w.slots_used; out.replaced += pt.w.replaced; out.not_nested += pt.w.not_nested;
-        roots[k] = move_ref(pt.root);
+        bottom.roots[k] = move_ref(pt.root);
+        bottom.need[k] = pt.root >= 0 ? pt.w.stack_need[pt.root] : 0;
+        const AtnBvhNode& n0 = scene->node_lists[k][0];
+        for (int a = 0; a < 3; a++) { bottom.box[(size_t)k * 6 + a] = n0.boxmin[a]; bottom.box[(size_t)k * 6 + 3 + a] = n0.boxmax[a]; }
         pt = Part();                                  // release the list's partial arrays
     }
+    bottom.node_count = (int32_t)out.nodes.size();
     if (scene->node_list_sizes[0] > 0) {
-        detail::ListBuilder lb{ scene->node_lists[0], scene->node_list_sizes[0], true, scene, &leaves, &roots };
-        detail::WideBuilder wb{ scene->node_lists[0], scene->node_list_sizes[0], true, &leaves, &lb, &out };
-        out.top_root = wb.run();
-        if (!out.error.empty()) return out;
-        out.insts.resize(leaves.insts.size());
-        for (size_t i = 0; i < leaves.insts.size(); i++) {
-            const InstLeaf& il = leaves.insts[i];
-            InstLeafW& w = out.insts[i];
-            w.objid = il.objid; w.root = il.root; w.w2l = il.w2l; w.meshid = il.meshid;
-            float mn[3], mx[3];
-            lb.leaf_bounds(leaf_ref((int32_t)i), mn, mx);
-            for (int a = 0; a < 3; a++) { w.wmin[a] = mn[a]; w.wmax[a] = mx[a]; }
-            w.pad0 = 0.0f; w.pad1 = 0.0f; w.pad2[0] = w.pad2[1] = w.pad2[2] = w.pad2[3] = 0;
-        }
+        WideBvh top = encode_top(scene->node_lists[0], scene->node_list_sizes[0], scene, bottom);
+        if (!top.error.empty()) { out.error = top.error; return out; }
+        out.nodes.insert(out.nodes.end(), top.nodes.begin(), top.nodes.end());
+        out.stack_need.insert(out.stack_need.end(), top.stack_need.begin(), top.stack_need.end());
+        out.insts.swap(top.insts);
+        out.top_root = top.top_root;
+        out.max_stack = top.max_stack;
+        out.slots_used += top.slots_used; out.replaced += top.replaced; out.not_nested += top.not_nested;
     }
-    out.tris.swap(leaves.tris);
-    out.max_stack = 0;
-    if (out.top_root >= 0) out.max_stack = out.stack_need[out.top_root];
-    else if (out.top_root != kRefNull && !out.insts.empty()) {      // the top layer is a single instance leaf
-        const int32_t root = out.insts[~out.top_root].root;
-        out.max_stack = 1 + (root >= 0 ? out.stack_need[root] : 0);
-    }
-    out.max_stack += 2;    // the sentinel at the bottom of every ray's stack, and one entry of slack
+    else out.max_stack = 2;
+    if (info) *info = std::move(bottom);
     return out;
 }
 

@@ -1488,11 +1488,8 @@ struct AtnRenderer {
     float hit_distance_limit{ kInf };
 
     // host copies needed by atn_update_top_layer
-    std::vector<AtnObjectParameter> h_objects;
-    std::vector<AtnMat4> h_matrices;
-    std::vector<AtnTriangleParameter> h_triangles;
-    std::vector<AtnVec4> h_positions;
-    std::vector<std::vector<AtnBvhNode>> h_lists;
+    BottomInfo bottom;                  // roots / stack needs / root boxes of the encoded bottom trees (top-layer updates)
+    size_t node_capacity{ 0 };          // QuadNodes the device array holds (bottom trees + room for the top layer)
 
     // path state
     DevBuf<float4> ray_o, ray_d, hit0, throughput, contrib, sh_o, sh_d, sh_c, image;
@@ -1562,13 +1559,38 @@ static void launch_trace(AtnRenderer* r, cudaStream_t s, Policy pol, const int32
     }
 }
 
+// (Re)binds what depends on the node array and the top layer: the linear node texture of the default kernel form, the
+// instance leaves, the root and the stack bound.
+static int bind_top_layer(AtnRenderer* r, size_t node_count, const std::vector<InstLeafW>& insts, int32_t top_root, int32_t max_stack)
+{
+    if (max_stack > kSmemStack + kLocalStackLarge)
+        return set_error(ATN_ERR_TOO_LARGE, "BVH needs a traversal stack of %d entries (limit %d)", max_stack, kSmemStack + kLocalStackLarge);
+    r->stack_need = max_stack;
+    CUDA_TRY(r->insts.upload(insts.data(), insts.size(), r->stream));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));   // the caller's host arrays go out of scope
+    r->bv.nodes = reinterpret_cast<const float4*>(r->nodes.p);
+    if (r->bv.node_tex) { cudaDestroyTextureObject(r->bv.node_tex); r->bv.node_tex = 0; }
+    // linear float4 texture over the node array; tex1Dfetch addresses 2^27 texels = 16 M QuadNodes (2 GB).  Only the
+    // default form of the kernel reads nodes through it: a larger set (which is far beyond the L2 anyway) is served by
+    // the streaming form, with plain loads.
+    if (node_count * 8 > ((size_t)1 << 27)) r->stream_loads = true;
+    if (ATN_NODE_TEX && node_count > 0 && !r->stream_loads) {
+        cudaResourceDesc rd{}; rd.resType = cudaResourceTypeLinear; rd.res.linear.devPtr = r->nodes.p;
+        rd.res.linear.desc = cudaCreateChannelDesc<float4>(); rd.res.linear.sizeInBytes = node_count * sizeof(QuadNode);
+        cudaTextureDesc td{}; td.readMode = cudaReadModeElementType;
+        CUDA_TRY(cudaCreateTextureObject(&r->bv.node_tex, &rd, &td, nullptr));
+    }
+    r->bv.tris = reinterpret_cast<const float4*>(r->tris.p);
+    r->bv.insts = reinterpret_cast<const float4*>(r->insts.p);
+    r->bv.matrices = r->matrices.p;
+    r->bv.top_root = top_root;
+    return ATN_OK;
+}
+
 static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene)
 {
-    WideBvh enc = encode_wide(scene);
+    WideBvh enc = encode_wide(scene, &r->bottom);
     if (!enc.error.empty()) return set_error(ATN_ERR_INVALID_ARGUMENT, "node lists: %s", enc.error.c_str());
-    if (enc.max_stack > kSmemStack + kLocalStackLarge)
-        return set_error(ATN_ERR_TOO_LARGE, "BVH needs a traversal stack of %d entries (limit %d)", enc.max_stack, kSmemStack + kLocalStackLarge);
-    r->stack_need = enc.max_stack;
     {
         // nodes + triangles far beyond the L2: the traversal waits for device memory, not for issue slots -- use the variant
         // that issues an iteration's loads together (k_trace<.., kStream>).  ATEN_B200_STREAM=0/1 overrides (experiments).
@@ -1580,27 +1602,14 @@ static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene)
         r->stream_loads = r->l2_bytes > 0 && set_bytes > 4 * r->l2_bytes;
         if (const char* ov = getenv("ATEN_B200_STREAM")) r->stream_loads = (ov[0] == '1');
     }
-    CUDA_TRY(r->nodes.upload(enc.nodes.data(), enc.nodes.size(), r->stream));
+    // room for a top layer of twice today's size: an update with more instances grows the array (atn_update_top_layer)
+    const size_t top_nodes = enc.nodes.size() - (size_t)r->bottom.node_count;
+    r->nodes.release();
+    CUDA_TRY(r->nodes.resize(enc.nodes.size() + top_nodes + 64));
+    r->node_capacity = r->nodes.n;
+    CUDA_TRY(cudaMemcpyAsync(r->nodes.p, enc.nodes.data(), enc.nodes.size() * sizeof(QuadNode), cudaMemcpyHostToDevice, r->stream));
     CUDA_TRY(r->tris.upload(enc.tris.data(), enc.tris.size(), r->stream));
-    CUDA_TRY(r->insts.upload(enc.insts.data(), enc.insts.size(), r->stream));
-    CUDA_TRY(cudaStreamSynchronize(r->stream));   // enc goes out of scope
-    r->bv.nodes = reinterpret_cast<const float4*>(r->nodes.p);
-    if (r->bv.node_tex) { cudaDestroyTextureObject(r->bv.node_tex); r->bv.node_tex = 0; }
-    // linear float4 texture over the node array; tex1Dfetch addresses 2^27 texels = 16 M QuadNodes (2 GB).  Only the
-    // default form of the kernel reads nodes through it: a larger set (which is far beyond the L2 anyway) is served by
-    // the streaming form, with plain loads.
-    if (enc.nodes.size() * 8 > ((size_t)1 << 27)) r->stream_loads = true;
-    if (ATN_NODE_TEX && !enc.nodes.empty() && !r->stream_loads) {
-        cudaResourceDesc rd{}; rd.resType = cudaResourceTypeLinear; rd.res.linear.devPtr = r->nodes.p;
-        rd.res.linear.desc = cudaCreateChannelDesc<float4>(); rd.res.linear.sizeInBytes = enc.nodes.size() * sizeof(QuadNode);
-        cudaTextureDesc td{}; td.readMode = cudaReadModeElementType;
-        CUDA_TRY(cudaCreateTextureObject(&r->bv.node_tex, &rd, &td, nullptr));
-    }
-    r->bv.tris = reinterpret_cast<const float4*>(r->tris.p);
-    r->bv.insts = reinterpret_cast<const float4*>(r->insts.p);
-    r->bv.matrices = r->matrices.p;
-    r->bv.top_root = enc.top_root;
-    return ATN_OK;
+    return bind_top_layer(r, enc.nodes.size(), enc.insts, enc.top_root, enc.max_stack);
 }
 
 static float scene_radius_of(const AtnSceneConfig& cfg)
@@ -1730,15 +1739,6 @@ ATN_API int atn_upload_scene(AtnRenderer* r, const AtnSceneBlob* scene, const At
     CUDA_TRY(cudaStreamSynchronize(s));
     r->h_texviews = tv;
 
-    // host copies for atn_update_top_layer (re-encode needs triangles / positions / bottom lists)
-    r->h_objects.assign(scene->objects, scene->objects + scene->object_count);
-    r->h_matrices.assign(scene->matrices, scene->matrices + scene->matrix_count);
-    r->h_triangles.assign(scene->triangles, scene->triangles + scene->triangle_count);
-    r->h_positions.assign(scene->positions, scene->positions + scene->vertex_count);
-    r->h_lists.clear();
-    for (uint32_t k = 0; k < scene->node_list_count; k++)
-        r->h_lists.emplace_back(scene->node_lists[k], scene->node_lists[k] + scene->node_list_sizes[k]);
-
     SceneView& sv = r->sv;
     sv.objects = r->objects.p; sv.matrices = r->matrices.p; sv.materials = r->materials.p; sv.lights = r->lights.p;
     sv.triangles = r->triangles.p; sv.positions = r->positions.p; sv.normals = r->normals.p;
@@ -1787,21 +1787,29 @@ ATN_API int atn_update_top_layer(AtnRenderer* r, const AtnBvhNode* top_nodes, ui
     if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_update_top_layer: no scene uploaded");
     CUDA_TRY(cudaSetDevice(r->device));
     CUDA_TRY(cudaStreamSynchronize(r->stream));
-    r->h_lists[0].assign(top_nodes, top_nodes + node_count);
-    r->h_objects.assign(objects, objects + object_count);
-    r->h_matrices.assign(matrices, matrices + matrix_count);
+    // Only list 0 is encoded again, against the roots / stack needs / root boxes kept from the upload: the cost is that of
+    // the top layer (instances), whatever the size of the bottom trees, like the reference's updateBVH (renderer.cpp:133-153).
+    AtnSceneBlob b{};
+    b.objects = objects; b.object_count = object_count;
+    b.matrices = matrices; b.matrix_count = matrix_count;
+    WideBvh top = encode_top(top_nodes, node_count, &b, r->bottom);
+    if (!top.error.empty()) return set_error(ATN_ERR_INVALID_ARGUMENT, "top layer: %s", top.error.c_str());
+    const size_t bottom_nodes = (size_t)r->bottom.node_count, total = bottom_nodes + top.nodes.size();
+    if (total > r->node_capacity) {
+        // more top-layer nodes than the array has room for: a larger array, bottom trees copied on the device
+        DevBuf<QuadNode> grown;
+        CUDA_TRY(grown.resize(total + top.nodes.size() + 64));
+        CUDA_TRY(cudaMemcpyAsync(grown.p, r->nodes.p, bottom_nodes * sizeof(QuadNode), cudaMemcpyDeviceToDevice, r->stream));
+        CUDA_TRY(cudaStreamSynchronize(r->stream));
+        std::swap(grown.p, r->nodes.p); std::swap(grown.n, r->nodes.n);
+        r->node_capacity = r->nodes.n;
+    }
     CUDA_TRY(r->objects.upload(objects, object_count, r->stream));
     CUDA_TRY(r->matrices.upload(matrices, matrix_count, r->stream));
     r->sv.objects = r->objects.p; r->sv.matrices = r->matrices.p;
-    std::vector<const AtnBvhNode*> ptrs; std::vector<uint32_t> sizes;
-    for (auto& l : r->h_lists) { ptrs.push_back(l.data()); sizes.push_back((uint32_t)l.size()); }
-    AtnSceneBlob b{};
-    b.objects = r->h_objects.data(); b.object_count = object_count;
-    b.matrices = r->h_matrices.data(); b.matrix_count = matrix_count;
-    b.triangles = r->h_triangles.data(); b.triangle_count = (uint32_t)r->h_triangles.size();
-    b.positions = r->h_positions.data(); b.vertex_count = (uint32_t)r->h_positions.size();
-    b.node_lists = ptrs.data(); b.node_list_sizes = sizes.data(); b.node_list_count = (uint32_t)ptrs.size();
-    return upload_bvh(r, &b);
+    if (!top.nodes.empty())
+        CUDA_TRY(cudaMemcpyAsync(r->nodes.p + bottom_nodes, top.nodes.data(), top.nodes.size() * sizeof(QuadNode), cudaMemcpyHostToDevice, r->stream));
+    return bind_top_layer(r, total, top.insts, top.top_root, top.max_stack);
 }
 
 ATN_API int atn_update_materials(AtnRenderer* r, const AtnMaterialParameter* m, uint32_t count)

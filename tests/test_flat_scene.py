@@ -123,3 +123,58 @@ def test_streaming_form_renders_the_same_image(golden, monkeypatch, name):
             imgs.append(r.readback().copy())
     assert (bits(imgs[0]) == bits(imgs[1])).all()
     assert np.isfinite(imgs[0]).all() and imgs[0][..., :3].max() > 0
+
+
+def many_instances(flat, copies):
+    """`copies` translated instances per mesh of the flattened scene: new instance objects, L2W / W2L matrix pairs and a new
+    top layer over the same bottom lists (what the host hands to Renderer::updateBVH after adding instances)."""
+    import copy
+    n = len(flat.objects) // 2
+    s = copy.copy(flat)
+    objs = [flat.objects[j] for j in range(n)]
+    mats, lo, hi, oid, lid = [], [], [], [], []
+    ext = (flat.config["scene_bbox_max"][0] - flat.config["scene_bbox_min"][0]).astype(np.float32)
+    for c in range(copies):
+        for j in range(n):
+            t = np.array([(c % 4) * 1.1 * ext[0], 0.0, (c // 4) * 1.1 * ext[2]], np.float32)
+            o = flat.objects[n + j].copy()
+            o["object_id"] = j; o["mtx_id"] = len(mats)
+            L = np.eye(4, dtype=np.float32); L[:3, 3] = t
+            W = np.eye(4, dtype=np.float32); W[:3, 3] = -t
+            mats += [L.reshape(16), W.reshape(16)]
+            root = flat.node_lists[1 + j][0]
+            lo.append(root["boxmin"] + t); hi.append(root["boxmax"] + t)
+            oid.append(n + len(oid)); lid.append(1 + j)
+            objs.append(o)
+    s.objects = np.array(objs, sio.OBJ_DTYPE)
+    s.matrices = np.array(mats, np.float32)
+    lo, hi = np.array(lo, np.float32), np.array(hi, np.float32)
+    s.node_lists = [fs._top_layer(lo, hi, oid, lid)] + list(flat.node_lists[1:])
+    cfg = flat.config.copy()
+    cfg["scene_bbox_min"][0] = lo.min(axis=0); cfg["scene_bbox_max"][0] = hi.max(axis=0)
+    s.config = cfg
+    s._keep = []
+    return s
+
+
+@pytest.mark.gpu
+def test_top_layer_update_with_more_instances_than_uploaded(flat):
+    """Renderer::updateBVH with a top layer eight times the uploaded one (the device node array has to grow): only
+    list 0, objects and matrices are handed over; the result equals a fresh upload of that scene and the restatement."""
+    from aten_b200 import PathTracing
+    big = many_instances(flat, 8)
+    assert len(big.node_lists[0]) > 6 * len(flat.node_lists[0])
+    rays = random_rays(big, 100_000, 11)
+    want = ol.trace_closest(big, rays)
+    assert (want["objid"] >= 0).mean() > 0.1 and len(np.unique(want["objid"][want["objid"] >= 0])) > 20
+    with PathTracing(0) as r, PathTracing(0) as fresh:
+        r.UpdateSceneData(flat)
+        r.updateBVH(big.node_lists[0], big.objects, big.matrices)
+        got = r.trace_closest(rays)
+        assert_hits_equal(got, want)
+        fresh.UpdateSceneData(big)
+        assert fresh.trace_closest(rays).tobytes() == got.tobytes()
+        # and back to the small top layer
+        r.updateBVH(flat.node_lists[0], flat.objects, flat.matrices)
+        small_rays = random_rays(flat, 50_000, 12)
+        assert_hits_equal(r.trace_closest(small_rays), ol.trace_closest(flat, small_rays))

@@ -67,6 +67,21 @@ struct FlatScene {
     std::vector<const AtnBvhNode*> node_ptrs;
     std::vector<uint32_t> node_sizes;
 
+    /// What Renderer::updateBVH reads (renderer.cpp:133-153): objects and matrices; the caller passes list 0 itself.
+    /// Nothing that scales with the geometry is touched.
+    void GatherTopLayer(const aten::context& ctxt)
+    {
+        const auto obj_num = ctxt.GetObjectNum();
+        objects.clear();
+        int32_t max_mtx = -1;
+        for (size_t i = 0; i < obj_num; i++) {
+            objects.push_back(ctxt.GetObject(static_cast<uint32_t>(i)));
+            if (objects.back().type == aten::ObjectType::Instance) max_mtx = std::max(max_mtx, objects.back().mtx_id);
+        }
+        matrices.clear();
+        for (int32_t i = 0; i <= max_mtx + 1 && max_mtx >= 0; i++) matrices.push_back(ctxt.GetMatrix(static_cast<uint32_t>(i)));
+    }
+
     void Gather(const aten::context& ctxt, const std::vector<std::vector<aten::GPUBvhNode>>& node_lists)
     {
         const auto obj_num = ctxt.GetObjectNum();
@@ -234,9 +249,10 @@ public:
     /// Renderer::updateBVH (renderer.cpp:133-153)
     void updateBVH(const aten::context& scene_ctxt, const std::vector<std::vector<aten::GPUBvhNode>>& nodes)
     {
-        flat_.Gather(scene_ctxt, nodes);
+        if (nodes.empty()) return;
+        flat_.GatherTopLayer(scene_ctxt);
         Check(atn_update_top_layer(
-            h_, reinterpret_cast<const AtnBvhNode*>(flat_.nodes[0].data()), (uint32_t)flat_.nodes[0].size(),
+            h_, reinterpret_cast<const AtnBvhNode*>(nodes[0].data()), (uint32_t)nodes[0].size(),
             reinterpret_cast<const AtnObjectParameter*>(flat_.objects.data()), (uint32_t)flat_.objects.size(),
             reinterpret_cast<const AtnMat4*>(flat_.matrices.data()), (uint32_t)flat_.matrices.size()));
     }

@@ -634,7 +634,8 @@ int Usage()
         "  restir <name> W H frames depth rr out_prefix [mx my]       (the reference's ReSTIR steps in the device renderer's order;\n"
         "         writes <prefix>.f<k>.f32 per frame and <prefix>.reservoirs.f32)\n"
         "  cmj    out.bin                           (golden CMJ stream)\n"
-        "  device <name> W H frames spp depth out_image.f32   (device_host only: idaten_b200::PathTracing on the GPU, progressive)\n");
+        "  device <name> W H frames spp depth out_image.f32   (device_host only: idaten_b200::PathTracing on the GPU, progressive)\n"
+        "  device_update <name> W H spp depth updated.f32 fresh.f32   (device_host only: updateBVH to <name>_moved vs a fresh upload)\n");
     return 2;
 }
 
@@ -712,6 +713,36 @@ int main(int argc, char** argv)
         }
         catch (const std::exception& e) {
             fprintf(stderr, "device: %s\n", e.what());
+            return 3;
+        }
+        return 0;
+    }
+    if (cmd == "device_update") {
+        // Renderer::updateBVH through the shim (src/device_renderer/main.cpp:440-470): upload scene <name>, then hand over
+        // the top layer, objects and matrices of scene <name>_moved (same meshes, one instance displaced) and render;
+        // a second renderer gets the moved scene as a fresh upload.  Writes both images.
+        if (argc < 10) return Usage();
+        const int W = atoi(argv[4]), H = atoi(argv[5]), spp = atoi(argv[6]), depth = atoi(argv[7]);
+        Harness hs, moved;
+        if (!hs.Build(name, W, H) || !moved.Build(name + "_moved", W, H)) return 1;
+        try {
+            idaten_b200::PathTracing renderer, fresh;
+            renderer.UpdateSceneData(0, W, H, hs.camera.param(), hs.ctxt, hs.scene.getAccel()->getNodes(), 0, 0);
+            renderer.render(W, H, 1, depth);
+            renderer.updateBVH(moved.ctxt, moved.scene.getAccel()->getNodes());
+            renderer.reset();
+            renderer.render(W, H, spp, depth);
+            fresh.UpdateSceneData(0, W, H, moved.camera.param(), moved.ctxt, moved.scene.getAccel()->getNodes(), 0, 0);
+            fresh.render(W, H, spp, depth);
+            std::vector<aten::vec4> a((size_t)W * H), b((size_t)W * H);
+            renderer.ReadbackImage(a.data(), a.size());
+            fresh.ReadbackImage(b.data(), b.size());
+            WriteFile(argv[8], a.data(), a.size() * sizeof(aten::vec4));
+            WriteFile(argv[9], b.data(), b.size() * sizeof(aten::vec4));
+            printf("{\"scene\": \"%s\", \"w\": %d, \"h\": %d, \"spp\": %d}\n", name.c_str(), W, H, spp);
+        }
+        catch (const std::exception& e) {
+            fprintf(stderr, "device_update: %s\n", e.what());
             return 3;
         }
         return 0;

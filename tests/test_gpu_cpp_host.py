@@ -52,3 +52,20 @@ def test_cpp_shim_renders_like_the_ctypes_host_and_the_restatement(name, W, H, f
     want, _, _ = ol.render(scene, frames=frames * spp, max_depth=depth, rr_depth=3)
     rmse = np.sqrt(np.mean((img[..., :3] - want[..., :3]) ** 2)); scale = np.sqrt(np.mean(want[..., :3] ** 2))
     assert rmse <= 2e-3 * scale, (rmse, scale)
+
+
+@pytest.mark.skipif(not os.path.exists(DEVICE_HOST), reason="oracle/_ref/device_host not built (needs /root/reference at build time)")
+def test_cpp_shim_update_bvh_equals_fresh_upload():
+    """`idaten_b200::PathTracing::updateBVH` (the app's per-frame call for moving instances, src/device_renderer/main.cpp:
+    440-470): after handing over the top layer, objects and matrices of the scene with one instance displaced, the
+    renderer draws what a renderer freshly given that scene draws, bit for bit -- and not what it drew before."""
+    W = H = 128
+    with tempfile.TemporaryDirectory() as d:
+        pa, pb = os.path.join(d, "a.f32"), os.path.join(d, "b.f32")
+        r = subprocess.run([DEVICE_HOST, ol.REF_ASSET, "device_update", "cornell", str(W), str(H), "2", "5", pa, pb],
+                           stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        a = np.fromfile(pa, np.float32).reshape(H, W, 4); b = np.fromfile(pb, np.float32).reshape(H, W, 4)
+    assert (bits(a) == bits(b)).all() and np.isfinite(a).all() and a[..., :3].max() > 0
+    base, _ = run_device_host("cornell", W, H, 1, 2, 5)
+    assert (bits(base) != bits(a)).any()

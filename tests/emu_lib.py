@@ -47,3 +47,9 @@ def trace_closest(scene: sio.Scene, rays: np.ndarray, t_max=None, leaves_first=F
     if rc != 0:
         raise RuntimeError("encode_wide rejected the scene's node lists")
     return hits, {k: int(v) for k, v in zip(STAT_NAMES, stats)}
+
+
+def top_update_equals_fresh(base: sio.Scene, moved: sio.Scene) -> int:
+    """0 when encode_top(moved's list 0 | base's bottom trees) is byte-identical to the tail of encode_wide(moved)."""
+    b0, b1 = base.blob(), moved.blob()
+    return int(lib().emu_top_update_equals_fresh(C.byref(b0), C.byref(b1)))

@@ -192,3 +192,23 @@ extern "C" int emu_trace_wide(const AtnSceneBlob* scene, const AtnRay* rays, con
     }
     return 0;
 }
+
+// Top-layer update (Renderer::updateBVH): encode_top(list 0 of `moved`) against the bottom trees kept from `base` must
+// give exactly what a full encode of `moved` gives behind the bottom trees.  Returns 0 when identical, else a code.
+extern "C" int emu_top_update_equals_fresh(const AtnSceneBlob* base, const AtnSceneBlob* moved)
+{
+    BottomInfo bi;
+    const WideBvh a = encode_wide(base, &bi);
+    if (!a.error.empty()) return -1;
+    const WideBvh t = encode_top(moved->node_lists[0], moved->node_list_sizes[0], moved, bi);
+    const WideBvh f = encode_wide(moved);
+    if (!t.error.empty() || !f.error.empty()) return -2;
+    const size_t nb = (size_t)bi.node_count;
+    if (f.nodes.size() != nb + t.nodes.size()) return 1;
+    if (nb && memcmp(a.nodes.data(), f.nodes.data(), nb * sizeof(QuadNode)) != 0) return 2;          // bottom trees untouched
+    if (!t.nodes.empty() && memcmp(t.nodes.data(), f.nodes.data() + nb, t.nodes.size() * sizeof(QuadNode)) != 0) return 3;
+    if (t.insts.size() != f.insts.size() || (!t.insts.empty() && memcmp(t.insts.data(), f.insts.data(), t.insts.size() * sizeof(InstLeafW)) != 0)) return 4;
+    if (t.top_root != f.top_root) return 5;
+    if (t.max_stack != f.max_stack) return 6;
+    return 0;
+}

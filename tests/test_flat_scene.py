@@ -178,3 +178,11 @@ def test_top_layer_update_with_more_instances_than_uploaded(flat):
         r.updateBVH(flat.node_lists[0], flat.objects, flat.matrices)
         small_rays = random_rays(flat, 50_000, 12)
         assert_hits_equal(r.trace_closest(small_rays), ol.trace_closest(flat, small_rays))
+
+
+def test_top_layer_update_encoding_equals_full_encoding(flat):
+    """CPU: the top layer re-encoded alone against the kept bottom trees (atn_update_top_layer's path) is byte-identical
+    to what a full encoding of the changed scene holds -- QuadNodes, instance leaves with their world boxes, root, stack
+    bound -- for a top layer eight times the original and for the unchanged one."""
+    assert emu_lib.top_update_equals_fresh(flat, many_instances(flat, 8)) == 0
+    assert emu_lib.top_update_equals_fresh(flat, flat) == 0

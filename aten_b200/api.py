@@ -20,13 +20,16 @@ LIB_PATH = os.path.join(_HERE, "libaten_b200.so")
 EXPORTS = [
     "atn_create", "atn_destroy", "atn_last_error", "atn_version", "atn_upload_scene", "atn_update_camera",
     "atn_update_top_layer", "atn_update_materials", "atn_update_lights", "atn_update_config", "atn_set_seeds",
-    "atn_set_frame", "atn_get_frame", "atn_reset", "atn_set_progressive", "atn_set_hit_distance_limit",
+    "atn_set_frame", "atn_get_frame", "atn_reset", "atn_set_progressive", "atn_set_gather_mode", "atn_set_hit_distance_limit",
     "atn_render", "atn_render_region", "atn_synchronize", "atn_readback", "atn_device_image", "atn_get_stats",
     "atn_set_profiling", "atn_get_stream", "atn_trace_closest", "atn_trace_any", "atn_trace_closest_device",
     "atn_trace_any_device", "atn_set_bounce_tap", "atn_trace_closest_static", "atn_readback_aov", "atn_render_ao",
     "atn_render_svgf", "atn_set_motion_depth", "atn_readback_svgf", "atn_update_texture",
     "atn_render_restir", "atn_readback_restir",
 ]
+
+
+GATHER_OVERWRITE, GATHER_PROGRESSIVE, GATHER_SUM = 0, 1, 2      # AtnGatherMode (include/aten_b200.h)
 
 
 class AtnError(RuntimeError):
@@ -162,7 +165,14 @@ class PathTracing:
         _check(self._lib, self._lib.atn_set_frame(self._h, C.c_uint32(frame)))
 
     def SetEnableProgressive(self, b: bool):
+        """PathTracing::SetEnableProgressive (reference pathtracing.h:127-135): True = running mean across calls
+        (GATHER_PROGRESSIVE), False = every call overwrites the image with the mean of its own samples (GATHER_OVERWRITE)."""
         _check(self._lib, self._lib.atn_set_progressive(self._h, C.c_int(1 if b else 0)))
+
+    def set_gather_mode(self, mode: int):
+        """AtnGatherMode: GATHER_OVERWRITE / GATHER_PROGRESSIVE / GATHER_SUM (sum of samples + count in .w, for the
+        multi-GPU reduce)."""
+        _check(self._lib, self._lib.atn_set_gather_mode(self._h, C.c_int(mode)))
 
     def setHitDistanceLimit(self, d: float):
         _check(self._lib, self._lib.atn_set_hit_distance_limit(self._h, C.c_float(d)))

@@ -12,8 +12,9 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "atn_kernels.cu")
-DEPS = [SRC, os.path.join(HERE, "csrc", "atn_math.cuh"), os.path.join(HERE, "csrc", "atn_bvh.h"),
-        os.path.join(HERE, "..", "include", "aten_b200.h")]
+import glob
+# every file the translation unit can include: a stale library would be compared with a fresh restatement
+DEPS = sorted(glob.glob(os.path.join(HERE, "csrc", "*")) + glob.glob(os.path.join(HERE, "..", "include", "*.h")))
 OUT = os.path.join(HERE, "libaten_b200.so")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -1403,8 +1403,12 @@ k_restir_color(FrameParams fp, SceneView sc, PathBuffers pb, RestirView rv)
     }
 }
 
-// pt::gather (pathtracing_impl.cu:282-324) / FilmProgressive::put (film.cpp:61-71)
-__global__ void k_gather(FrameParams fp, PathBuffers pb, float4* image, int progressive, const Counters* cnt, Totals* totals)
+// pt::gather (pathtracing_impl.cu:282-324) / FilmProgressive::put (film.cpp:61-71).  `mode` (AtnGatherMode):
+//   OVERWRITE   the reference GPU renderer with progressive off: the pixel becomes the mean of THIS call's samples, w = 1
+//               (`first`: the pixel's old value is ignored; `last`: the sum is divided by its count);
+//   PROGRESSIVE FilmProgressive::put per sample: new = (n * old + sample) / (n + 1), w = n + 1;
+//   SUM         xyz += sample, w += 1 (what the multi-GPU reduce combines).
+__global__ void k_gather(FrameParams fp, PathBuffers pb, float4* image, int mode, int first, int last, const Counters* cnt, Totals* totals)
 {
     const int n = fp.rw * fp.rh;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -1416,9 +1420,10 @@ __global__ void k_gather(FrameParams fp, PathBuffers pb, float4* image, int prog
         const int ix = fp.x0 + s % fp.rw;
         const int iy = fp.y0 + s / fp.rw;
         float4 cur = image[iy * fp.width + ix];
+        if (mode == ATN_GATHER_OVERWRITE && first) cur = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         for (int k = 0; k < fp.batch; k++) {          // the samples of the batch, in sample order
             const float4 c = pb.contrib[(size_t)k * n + s];
-            if (progressive) {
+            if (mode == ATN_GATHER_PROGRESSIVE) {
                 const float nn = (float)((int32_t)cur.w);
                 const float cx = c.x / 1.0f, cy = c.y / 1.0f, cz = c.z / 1.0f;   // col /= cnt, cnt = 1
                 cur.x = (nn * cur.x + cx) / (nn + 1);
@@ -1429,6 +1434,9 @@ __global__ void k_gather(FrameParams fp, PathBuffers pb, float4* image, int prog
             else {
                 cur.x += c.x; cur.y += c.y; cur.z += c.z; cur.w += 1.0f;
             }
+        }
+        if (mode == ATN_GATHER_OVERWRITE && last) {     // contrib /= sample; contrib.w = 1 (pathtracing_impl.cu:313-316)
+            cur.x /= cur.w; cur.y /= cur.w; cur.z /= cur.w; cur.w = 1.0f;
         }
         image[iy * fp.width + ix] = cur;
     }
@@ -1503,7 +1511,15 @@ struct AtnRenderer {
     DevBuf<Totals> totals;
     DevBuf<Visits> visits;
     bool stream_loads{ false };    // traversal variant for scenes beyond the L2 (k_trace<.., kStream = true>), set at upload
-    bool query_pending{ false };   // a device-buffer ray query whose time / visit counts atn_get_stats has yet to collect
+    // Render calls and device-buffer ray queries return without waiting for the GPU; their counters travel to this pinned
+    // block behind the kernels and atn_get_stats collects them on demand (collect_stats).
+    struct HostStats { Totals totals; Visits visits; Counters counters; };
+    HostStats* h_stats{ nullptr };
+    enum Pending { PEND_NONE, PEND_RENDER, PEND_AO, PEND_QUERY };
+    Pending pending{ PEND_NONE };
+    size_t pend_events{ 0 };       // profiling events recorded by the pending call
+    uint64_t pend_ao_factor{ 0 };  // AO: rays per lit path of the call (num_rays * spp)
+    cudaEvent_t ev_done{ nullptr };
     PathBuffers pb{};
 
     // query scratch
@@ -1531,7 +1547,7 @@ struct AtnRenderer {
     DevBuf<AtnBounceRecord> tap_dev;
 
     uint32_t frame{ 0 };
-    int progressive{ 1 };
+    int gather_mode{ ATN_GATHER_PROGRESSIVE };
     int profiling{ 0 };
     AtnStats stats{};
     cudaEvent_t ev0{ nullptr }, ev1{ nullptr };
@@ -1625,7 +1641,7 @@ static float scene_radius_of(const AtnSceneConfig& cfg)
     return rad / tanf(theta / 2);
 }
 
-static int alloc_paths(AtnRenderer* r, size_t n)
+static int alloc_paths(AtnRenderer* r, size_t n, size_t pixels)
 {
     CUDA_TRY(r->ray_o.resize(n)); CUDA_TRY(r->ray_d.resize(n)); CUDA_TRY(r->hit0.resize(n)); CUDA_TRY(r->hit1.resize(n));
     CUDA_TRY(r->throughput.resize(n)); CUDA_TRY(r->contrib.resize(n)); CUDA_TRY(r->sampler_dim.resize(n));
@@ -1633,7 +1649,7 @@ static int alloc_paths(AtnRenderer* r, size_t n)
     CUDA_TRY(r->sh_o.resize(n)); CUDA_TRY(r->sh_d.resize(n)); CUDA_TRY(r->sh_c.resize(n));
     CUDA_TRY(cudaMemsetAsync(r->sh_c.p, 0, n * sizeof(float4), r->stream));      // ShadowRay::lightcontrib starts at zero
     CUDA_TRY(r->q_lit.resize(n)); CUDA_TRY(r->q_shadow.resize(n));
-    CUDA_TRY(r->hit_mesh.resize(n)); CUDA_TRY(r->aov_nd.resize(n)); CUDA_TRY(r->aov_am.resize(n));
+    CUDA_TRY(r->hit_mesh.resize(n)); CUDA_TRY(r->aov_nd.resize(pixels)); CUDA_TRY(r->aov_am.resize(pixels));    // AOVs are per pixel
     CUDA_TRY(r->surf0.resize(n)); CUDA_TRY(r->surf1.resize(n)); CUDA_TRY(r->surf2.resize(n));
     CUDA_TRY(r->counters.resize(1));
     CUDA_TRY(r->totals.resize(1));
@@ -1646,6 +1662,82 @@ static int alloc_paths(AtnRenderer* r, size_t n)
     pb.q_lit = r->q_lit.p; pb.q_shadow = r->q_shadow.p;
     pb.hit_mesh = r->hit_mesh.p; pb.aov_nd = r->aov_nd.p; pb.aov_am = r->aov_am.p;
     pb.surf0 = r->surf0.p; pb.surf1 = r->surf1.p; pb.surf2 = r->surf2.p;
+    return ATN_OK;
+}
+
+extern "C" ATN_API int atn_destroy(AtnRenderer* r);
+
+// Everything atn_create sets up after the allocation of the handle; on failure atn_create destroys the half-built handle.
+static int init_renderer(AtnRenderer* r)
+{
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, r->device));
+    r->sm_count = prop.multiProcessorCount;
+    CUDA_TRY(cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking));
+    CUDA_TRY(cudaEventCreate(&r->ev0));
+    CUDA_TRY(cudaEventCreate(&r->ev1));
+    CUDA_TRY(cudaEventCreateWithFlags(&r->ev_done, cudaEventDisableTiming));
+    CUDA_TRY(cudaMallocHost(&r->h_stats, sizeof(AtnRenderer::HostStats)));
+    memset(r->h_stats, 0, sizeof(AtnRenderer::HostStats));
+    int bps = 0;
+    r->l2_bytes = (size_t)prop.l2CacheSize;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace<ClosestPolicy, kLocalStackSmall, false>, kTraceBlock, 0));
+    r->trace_grid = r->sm_count * std::max(1, bps);
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace<ClosestPolicy, kLocalStackSmall, true>, kTraceBlock, 0));
+    r->trace_grid_stream = r->sm_count * std::max(1, bps);
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_surface<false, false>, kShadeBlock, 0));
+    r->surface_grid = r->sm_count * std::max(1, bps);
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_nee, kShadeBlock, 0));
+    r->nee_grid = r->sm_count * std::max(1, bps);
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_bsdf<false>, kShadeBlock, 0));
+    r->bsdf_grid = r->sm_count * std::max(1, bps);
+    return ATN_OK;
+}
+
+// End of an asynchronous call: the device counters follow the kernels into pinned host memory; nothing waits here.
+static int end_call(AtnRenderer* r, AtnRenderer::Pending kind, uint64_t launches, uint64_t samples, size_t n_events)
+{
+    cudaStream_t s = r->stream;
+    CUDA_TRY(cudaEventRecord(r->ev1, s));
+    CUDA_TRY(cudaGetLastError());
+    if (kind != AtnRenderer::PEND_QUERY) CUDA_TRY(cudaMemcpyAsync(&r->h_stats->totals, r->totals.p, sizeof(Totals), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaMemcpyAsync(&r->h_stats->visits, r->visits.p, sizeof(Visits), cudaMemcpyDeviceToHost, s));
+    if (kind == AtnRenderer::PEND_AO) CUDA_TRY(cudaMemcpyAsync(&r->h_stats->counters, r->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaEventRecord(r->ev_done, s));
+    r->stats.kernel_launches = launches;
+    r->stats.camera_samples = samples;
+    r->pend_events = n_events;
+    r->pending = kind;
+    return ATN_OK;
+}
+
+// Waits for the pending call (if any) and fills r->stats from what it left in the pinned block.
+static int collect_stats(AtnRenderer* r)
+{
+    if (r->pending == AtnRenderer::PEND_NONE) return ATN_OK;
+    CUDA_TRY(cudaSetDevice(r->device));
+    CUDA_TRY(cudaEventSynchronize(r->ev_done));
+    const AtnRenderer::Pending kind = r->pending;
+    r->pending = AtnRenderer::PEND_NONE;
+    float ms = 0.0f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
+    r->stats.device_ms = ms;
+    r->stats.nodes_visited = r->h_stats->visits.nodes;
+    r->stats.tris_tested = r->h_stats->visits.tris;
+    if (kind == AtnRenderer::PEND_QUERY) { r->stats.trace_ms = ms; return ATN_OK; }
+    r->stats.closest_rays = r->h_stats->totals.closest;
+    r->stats.shadow_rays = r->h_stats->totals.shadow;
+    if (kind == AtnRenderer::PEND_AO)      // AO rays = lit paths (last sample's count) x rays per path x samples
+        r->stats.shadow_rays = (uint64_t)r->h_stats->counters.n_lit[0] * r->pend_ao_factor;
+    r->stats.trace_ms = 0.0f;
+    float tot = 0.0f;
+    for (size_t i = 0; i + 3 < r->pend_events; i += 4) {
+        float a = 0.0f, b2 = 0.0f;
+        cudaEventElapsedTime(&a, r->trace_events[i], r->trace_events[i + 1]);
+        cudaEventElapsedTime(&b2, r->trace_events[i + 2], r->trace_events[i + 3]);
+        tot += a + b2;
+    }
+    r->stats.trace_ms = tot;
     return ATN_OK;
 }
 
@@ -1667,24 +1759,8 @@ ATN_API int atn_create(int device_ordinal, AtnRenderer** out)
     CUDA_TRY(cudaSetDevice(device_ordinal));
     AtnRenderer* r = new AtnRenderer();
     r->device = device_ordinal;
-    cudaDeviceProp prop;
-    CUDA_TRY(cudaGetDeviceProperties(&prop, device_ordinal));
-    r->sm_count = prop.multiProcessorCount;
-    CUDA_TRY(cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking));
-    CUDA_TRY(cudaEventCreate(&r->ev0));
-    CUDA_TRY(cudaEventCreate(&r->ev1));
-    int bps = 0;
-    r->l2_bytes = (size_t)prop.l2CacheSize;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace<ClosestPolicy, kLocalStackSmall, false>, kTraceBlock, 0));
-    r->trace_grid = r->sm_count * std::max(1, bps);
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_trace<ClosestPolicy, kLocalStackSmall, true>, kTraceBlock, 0));
-    r->trace_grid_stream = r->sm_count * std::max(1, bps);
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_surface<false, false>, kShadeBlock, 0));
-    r->surface_grid = r->sm_count * std::max(1, bps);
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_nee, kShadeBlock, 0));
-    r->nee_grid = r->sm_count * std::max(1, bps);
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_bsdf<false>, kShadeBlock, 0));
-    r->bsdf_grid = r->sm_count * std::max(1, bps);
+    const int rc = init_renderer(r);
+    if (rc != ATN_OK) { const std::string msg = g_last_error; atn_destroy(r); g_last_error = msg; return rc; }   // *out untouched
     *out = r;
     return ATN_OK;
 }
@@ -1693,10 +1769,12 @@ ATN_API int atn_destroy(AtnRenderer* r)
 {
     if (!r) return ATN_OK;
     cudaSetDevice(r->device);
-    cudaStreamSynchronize(r->stream);
+    if (r->stream) cudaStreamSynchronize(r->stream);
     for (auto ev : r->trace_events) cudaEventDestroy(ev);
     if (r->ev0) cudaEventDestroy(r->ev0);
     if (r->ev1) cudaEventDestroy(r->ev1);
+    if (r->ev_done) cudaEventDestroy(r->ev_done);
+    if (r->h_stats) cudaFreeHost(r->h_stats);
     if (r->bv.node_tex) cudaDestroyTextureObject(r->bv.node_tex);
     if (r->svgf_tex) cudaDestroyTextureObject(r->svgf_tex);
     cudaStream_t s = r->stream;
@@ -1756,7 +1834,7 @@ ATN_API int atn_upload_scene(AtnRenderer* r, const AtnSceneBlob* scene, const At
     // smaller frame are traced together (slot_info); ~216 B per path, 1.8 GB at the cap
     r->batch_cap = (int)std::max<size_t>(1, std::min<size_t>((size_t)ATN_MAX_BATCH, ((size_t)ATN_WAVEFRONT_PATHS + n / 2) / n));
     r->path_capacity = n * (size_t)r->batch_cap;
-    rc = alloc_paths(r, r->path_capacity);
+    rc = alloc_paths(r, r->path_capacity, n);
     if (rc != ATN_OK) return rc;
     CUDA_TRY(r->image.resize(n));
     CUDA_TRY(cudaMemsetAsync(r->image.p, 0, n * sizeof(float4), s));
@@ -1794,6 +1872,8 @@ ATN_API int atn_update_top_layer(AtnRenderer* r, const AtnBvhNode* top_nodes, ui
     b.matrices = matrices; b.matrix_count = matrix_count;
     WideBvh top = encode_top(top_nodes, node_count, &b, r->bottom);
     if (!top.error.empty()) return set_error(ATN_ERR_INVALID_ARGUMENT, "top layer: %s", top.error.c_str());
+    if (top.max_stack > kSmemStack + kLocalStackLarge)       // refused before anything on the device changes
+        return set_error(ATN_ERR_TOO_LARGE, "BVH needs a traversal stack of %d entries (limit %d)", top.max_stack, kSmemStack + kLocalStackLarge);
     const size_t bottom_nodes = (size_t)r->bottom.node_count, total = bottom_nodes + top.nodes.size();
     if (total > r->node_capacity) {
         // more top-layer nodes than the array has room for: a larger array, bottom trees copied on the device
@@ -1873,7 +1953,15 @@ ATN_API int atn_set_seeds(AtnRenderer* r, const uint32_t* seeds, uint32_t count)
 
 ATN_API int atn_set_frame(AtnRenderer* r, uint32_t frame) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->frame = frame; return ATN_OK; }
 ATN_API int atn_get_frame(AtnRenderer* r, uint32_t* frame) { if (!r || !frame) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); *frame = r->frame; return ATN_OK; }
-ATN_API int atn_set_progressive(AtnRenderer* r, int enable) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->progressive = enable ? 1 : 0; return ATN_OK; }
+ATN_API int atn_set_progressive(AtnRenderer* r, int enable) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->gather_mode = enable ? ATN_GATHER_PROGRESSIVE : ATN_GATHER_OVERWRITE; return ATN_OK; }
+ATN_API int atn_set_gather_mode(AtnRenderer* r, int mode)
+{
+    if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL");
+    if (mode != ATN_GATHER_OVERWRITE && mode != ATN_GATHER_PROGRESSIVE && mode != ATN_GATHER_SUM)
+        return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_set_gather_mode: mode %d is none of ATN_GATHER_OVERWRITE / PROGRESSIVE / SUM", mode);
+    r->gather_mode = mode;
+    return ATN_OK;
+}
 ATN_API int atn_set_hit_distance_limit(AtnRenderer* r, float d) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->hit_distance_limit = fminf(d, kInf); return ATN_OK; }
 ATN_API int atn_set_profiling(AtnRenderer* r, int enable) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->profiling = enable ? 1 : 0; return ATN_OK; }
 ATN_API int atn_get_stream(AtnRenderer* r, void** stream) { if (!r || !stream) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); *stream = (void*)r->stream; return ATN_OK; }
@@ -1993,39 +2081,18 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
         launches++;
         const int rc = launch_bounces(r, fp, r->pb, tap_now, nullptr, &ev_i, &launches);
         if (rc != ATN_OK) return rc;
-        k_gather<<<gen_grid, 256, 0, s>>>(fp, r->pb, r->image.p, r->progressive, r->counters.p, r->totals.p);
+        k_gather<<<gen_grid, 256, 0, s>>>(fp, r->pb, r->image.p, r->gather_mode, smp == sample_begin ? 1 : 0,
+                                          smp + batch >= sample_end ? 1 : 0, r->counters.p, r->totals.p);
         launches++;
         smp += batch;
     }
-    CUDA_TRY(cudaEventRecord(r->ev1, s));
-    CUDA_TRY(cudaGetLastError());
-
-    // Exact ray counts: k_gather folds every sample's queue counters into Totals on the device.
-    Totals ht;
-    CUDA_TRY(cudaMemcpyAsync(&ht, r->totals.p, sizeof(Totals), cudaMemcpyDeviceToHost, s));
-    Visits hv;
-    CUDA_TRY(cudaMemcpyAsync(&hv, r->visits.p, sizeof(Visits), cudaMemcpyDeviceToHost, s));
-    if (tap) CUDA_TRY(cudaMemcpyAsync(r->tap_host, r->tap_dev.p, (size_t)n * r->tap_cap * sizeof(AtnBounceRecord), cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(cudaStreamSynchronize(s));
-    r->stats.closest_rays = ht.closest;
-    r->stats.shadow_rays = ht.shadow;
-    r->stats.nodes_visited = hv.nodes;
-    r->stats.tris_tested = hv.tris;
-    r->stats.camera_samples = (uint64_t)n * (uint64_t)spp;
-    r->stats.kernel_launches = launches;
-    float ms = 0.0f;
-    CUDA_TRY(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
-    r->stats.device_ms = ms;
-    r->stats.trace_ms = 0.0f;
-    if (r->profiling) {
-        float tot = 0.0f;
-        for (size_t i = 0; i + 3 < ev_i; i += 4) {
-            float a = 0.0f, b2 = 0.0f;
-            cudaEventElapsedTime(&a, r->trace_events[i], r->trace_events[i + 1]);
-            cudaEventElapsedTime(&b2, r->trace_events[i + 2], r->trace_events[i + 3]);
-            tot += a + b2;
-        }
-        r->stats.trace_ms = tot;
+    // Exact ray counts: k_gather folds every sample's queue counters into Totals on the device; they are read on demand
+    // (atn_get_stats).  The call returns without waiting for the GPU unless the bounce tap has to be copied out.
+    const int rc_end = end_call(r, AtnRenderer::PEND_RENDER, launches, (uint64_t)n * (uint64_t)spp, ev_i);
+    if (rc_end != ATN_OK) return rc_end;
+    if (tap) {
+        CUDA_TRY(cudaMemcpyAsync(r->tap_host, r->tap_dev.p, (size_t)n * r->tap_cap * sizeof(AtnBounceRecord), cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(cudaStreamSynchronize(s));
     }
     return ATN_OK;
 }
@@ -2071,24 +2138,12 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
         }
         // n_active[0] primary rays + num_rays * n_lit[0] AO rays: folded into Totals by k_gather through
         // n_active[0] / n_shadow[0]; the AO rays are reported as shadow rays
-        k_gather<<<grid, 256, 0, s>>>(fp, r->pb, r->image.p, r->progressive, c, r->totals.p);
+        k_gather<<<grid, 256, 0, s>>>(fp, r->pb, r->image.p, r->gather_mode, smp == 0 ? 1 : 0, smp == spp - 1 ? 1 : 0, c, r->totals.p);
         launches++;
     }
-    CUDA_TRY(cudaEventRecord(r->ev1, s));
-    CUDA_TRY(cudaGetLastError());
-    Totals ht; Visits hv; Counters hc;
-    CUDA_TRY(cudaMemcpyAsync(&ht, r->totals.p, sizeof(Totals), cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(cudaMemcpyAsync(&hv, r->visits.p, sizeof(Visits), cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(cudaMemcpyAsync(&hc, r->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(cudaStreamSynchronize(s));
-    r->stats.closest_rays = ht.closest;
-    r->stats.shadow_rays = (uint64_t)hc.n_lit[0] * (uint64_t)num_rays * (uint64_t)spp;   // AO rays (last sample's count x spp)
-    r->stats.camera_samples = (uint64_t)n * (uint64_t)spp;
-    r->stats.kernel_launches = launches;
-    r->stats.nodes_visited = hv.nodes; r->stats.tris_tested = hv.tris;
-    float ms = 0.0f;
-    CUDA_TRY(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
-    r->stats.device_ms = ms; r->stats.trace_ms = 0.0f;
+    r->pend_ao_factor = (uint64_t)num_rays * (uint64_t)spp;
+    const int rc_end = end_call(r, AtnRenderer::PEND_AO, launches, (uint64_t)n * (uint64_t)spp, 0);
+    if (rc_end != ATN_OK) return rc_end;
     r->frame += (uint32_t)spp;
     return ATN_OK;
 }
@@ -2135,6 +2190,7 @@ ATN_API int atn_render_svgf(AtnRenderer* r, int32_t width, int32_t height, int32
 
     const bool first_frame = r->frame == 0;
     if (r->svgf_pixels != n || !r->svgf_planes.p) {
+        if (!first_frame) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_svgf: no history for frame %u (start at frame 0: atn_set_frame(0))", r->frame);
         CUDA_TRY(r->svgf_planes.resize(12 * n));
         r->svgf_pixels = n;
         if (r->svgf_tex) { cudaDestroyTextureObject(r->svgf_tex); r->svgf_tex = 0; }
@@ -2144,7 +2200,6 @@ ATN_API int atn_render_svgf(AtnRenderer* r, int32_t width, int32_t height, int32
             cudaTextureDesc td{}; td.readMode = cudaReadModeElementType;
             CUDA_TRY(cudaCreateTextureObject(&r->svgf_tex, &rd, &td, nullptr));
         }
-        if (!first_frame) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_svgf: no history for frame %u (start at frame 0: atn_set_frame(0))", r->frame);
     }
     if (first_frame) {
         r->svgf_cv_plane[0] = 2; r->svgf_cv_plane[1] = 6; r->svgf_scratch_plane = 11;
@@ -2192,31 +2247,8 @@ ATN_API int atn_render_svgf(AtnRenderer* r, int32_t width, int32_t height, int32
         k_svgf_atrous<<<grid, 256, 0, s>>>(fp, sv, camera_distance, i, atrous_iters, r->image.p, r->svgf_tex, base);
     k_svgf_copy<<<grid, 256, 0, s>>>(fp, sv);
     launches += 3 + (uint64_t)atrous_iters;
-    CUDA_TRY(cudaEventRecord(r->ev1, s));
-    CUDA_TRY(cudaGetLastError());
-
-    Totals ht; Visits hv;
-    CUDA_TRY(cudaMemcpyAsync(&ht, r->totals.p, sizeof(Totals), cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(cudaMemcpyAsync(&hv, r->visits.p, sizeof(Visits), cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(cudaStreamSynchronize(s));
-    r->stats.closest_rays = ht.closest; r->stats.shadow_rays = ht.shadow;
-    r->stats.nodes_visited = hv.nodes; r->stats.tris_tested = hv.tris;
-    r->stats.camera_samples = (uint64_t)n;
-    r->stats.kernel_launches = launches;
-    float ms = 0.0f;
-    CUDA_TRY(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
-    r->stats.device_ms = ms;
-    r->stats.trace_ms = 0.0f;
-    if (r->profiling) {
-        float tot = 0.0f;
-        for (size_t i = 0; i + 3 < ev_i; i += 4) {
-            float a = 0.0f, b2 = 0.0f;
-            cudaEventElapsedTime(&a, r->trace_events[i], r->trace_events[i + 1]);
-            cudaEventElapsedTime(&b2, r->trace_events[i + 2], r->trace_events[i + 3]);
-            tot += a + b2;
-        }
-        r->stats.trace_ms = tot;
-    }
+    const int rc_end = end_call(r, AtnRenderer::PEND_RENDER, launches, (uint64_t)n, ev_i);
+    if (rc_end != ATN_OK) return rc_end;
     r->frame += 1u;
     return ATN_OK;
 }
@@ -2323,25 +2355,11 @@ ATN_API int atn_render_restir(AtnRenderer* r, int32_t width, int32_t height, int
     // bounces > 0: the path tracer's
     const int rc = launch_bounces(r, fp, pb, false, nullptr, &ev_i, &launches, 1);
     if (rc != ATN_OK) return rc;
-    // one frame per call: without progressive accumulation the image holds this frame alone
-    if (!r->progressive) CUDA_TRY(cudaMemsetAsync(r->image.p, 0, n * sizeof(float4), s));
-    k_gather<<<grid, 256, 0, s>>>(fp, pb, r->image.p, r->progressive, c, r->totals.p);
+    // one frame of one sample per call: in overwrite mode the image holds this frame alone
+    k_gather<<<grid, 256, 0, s>>>(fp, pb, r->image.p, r->gather_mode, 1, 1, c, r->totals.p);
     launches++;
-    CUDA_TRY(cudaEventRecord(r->ev1, s));
-    CUDA_TRY(cudaGetLastError());
-
-    Totals ht; Visits hv;
-    CUDA_TRY(cudaMemcpyAsync(&ht, r->totals.p, sizeof(Totals), cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(cudaMemcpyAsync(&hv, r->visits.p, sizeof(Visits), cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(cudaStreamSynchronize(s));
-    r->stats.closest_rays = ht.closest; r->stats.shadow_rays = ht.shadow;
-    r->stats.nodes_visited = hv.nodes; r->stats.tris_tested = hv.tris;
-    r->stats.camera_samples = (uint64_t)n;
-    r->stats.kernel_launches = launches;
-    float ms = 0.0f;
-    CUDA_TRY(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
-    r->stats.device_ms = ms;
-    r->stats.trace_ms = 0.0f;
+    const int rc_end = end_call(r, AtnRenderer::PEND_RENDER, launches, (uint64_t)n, ev_i);
+    if (rc_end != ATN_OK) return rc_end;
     r->frame += 1u;
     return ATN_OK;
 }
@@ -2405,19 +2423,8 @@ ATN_API int atn_device_image(AtnRenderer* r, void** device_ptr, size_t* pixel_co
 ATN_API int atn_get_stats(AtnRenderer* r, AtnStats* out)
 {
     if (!r || !out) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_get_stats: NULL argument");
-    if (r->query_pending) {
-        // a ray query on device buffers (atn_trace_*_device) returns without waiting; its time and visit counts are
-        // collected here, on demand
-        CUDA_TRY(cudaSetDevice(r->device));
-        CUDA_TRY(cudaStreamSynchronize(r->stream));
-        float ms = 0.0f;
-        Visits hv{};
-        CUDA_TRY(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
-        CUDA_TRY(cudaMemcpy(&hv, r->visits.p, sizeof(Visits), cudaMemcpyDeviceToHost));
-        r->stats.device_ms = ms; r->stats.trace_ms = ms;
-        r->stats.nodes_visited = hv.nodes; r->stats.tris_tested = hv.tris;
-        r->query_pending = false;
-    }
+    const int rc = collect_stats(r);
+    if (rc != ATN_OK) return rc;
     *out = r->stats;
     return ATN_OK;
 }
@@ -2439,14 +2446,9 @@ static int query_launch(AtnRenderer* r, const void* rays_dev, const void* f_dev,
         QueryClosestPolicy pol{ (const AtnRay*)rays_dev, (const float*)f_dev, (AtnHit*)out_dev };
         launch_trace<QueryClosestPolicy>(r, s, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
     }
-    CUDA_TRY(cudaEventRecord(r->ev1, s));
-    CUDA_TRY(cudaGetLastError());
-    r->stats.kernel_launches = 1;
     r->stats.closest_rays = any ? 0 : n;
     r->stats.shadow_rays = any ? n : 0;
-    r->stats.camera_samples = 0;
-    r->query_pending = true;
-    return ATN_OK;
+    return end_call(r, AtnRenderer::PEND_QUERY, 1, 0, 0);
 }
 
 ATN_API int atn_trace_closest_device(AtnRenderer* r, const void* rays_dev, const void* t_max_dev, size_t n, void* hits_dev)
@@ -2481,10 +2483,7 @@ ATN_API int atn_trace_closest(AtnRenderer* r, const AtnRay* rays, const float* t
     if (rc != ATN_OK) return rc;
     CUDA_TRY(cudaMemcpyAsync(hits, r->q_hits.p, n * sizeof(AtnHit), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaStreamSynchronize(s));
-    float ms = 0.0f;
-    cudaEventElapsedTime(&ms, r->ev0, r->ev1);
-    r->stats.device_ms = ms; r->stats.trace_ms = ms;
-    return ATN_OK;
+    return collect_stats(r);
 }
 
 ATN_API int atn_trace_any(AtnRenderer* r, const AtnRay* rays, const float* dist, size_t n, uint8_t* visible)
@@ -2501,10 +2500,7 @@ ATN_API int atn_trace_any(AtnRenderer* r, const AtnRay* rays, const float* dist,
     if (rc != ATN_OK) return rc;
     CUDA_TRY(cudaMemcpyAsync(visible, r->q_vis.p, n, cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaStreamSynchronize(s));
-    float ms = 0.0f;
-    cudaEventElapsedTime(&ms, r->ev0, r->ev1);
-    r->stats.device_ms = ms; r->stats.trace_ms = ms;
-    return ATN_OK;
+    return collect_stats(r);
 }
 
 }  // extern "C"
@@ -2574,9 +2570,19 @@ extern "C" ATN_API int atn_trace_closest_static(AtnRenderer* r, const AtnRay* ra
     CUDA_TRY(cudaMemcpyAsync(sc->rays, rays, n * sizeof(AtnRay), cudaMemcpyHostToDevice, s));
     if (t_max) CUDA_TRY(cudaMemcpyAsync(sc->t_max, t_max, n * sizeof(float), cudaMemcpyHostToDevice, s));
     QueryClosestPolicy pol{ sc->rays, t_max ? sc->t_max : nullptr, sc->hits };
+    CUDA_TRY(cudaEventRecord(r->ev0, s));
     launch_trace<QueryClosestPolicy>(r, s, pol, nullptr, (int)n, &sc->cursor, nullptr);
+    CUDA_TRY(cudaEventRecord(r->ev1, s));
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaMemcpyAsync(hits, sc->hits, n * sizeof(AtnHit), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaStreamSynchronize(s));
+    // counters of this call (events and host fields allocate nothing); the visit counts are not taken on this path
+    r->pending = AtnRenderer::PEND_NONE;
+    r->stats = AtnStats{};
+    r->stats.closest_rays = n;
+    r->stats.kernel_launches = 1;
+    float ms = 0.0f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
+    r->stats.device_ms = ms; r->stats.trace_ms = ms;
     return ATN_OK;
 }

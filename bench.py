@@ -194,7 +194,7 @@ def main():
     r = PathTracing(local_rank)
     seeds = sio.mt19937_seeds(W * H)
     r.UpdateSceneData(scene, seeds=seeds)
-    r.SetEnableProgressive(False)         # sum + count in .w: the form the reduce combines
+    r.set_gather_mode(2)         # sum + count in .w: the form the reduce combines
 
     img_ptr, npix = r.device_image()
 

@@ -238,10 +238,20 @@ ATN_API int atn_set_frame(AtnRenderer* r, uint32_t frame);
 ATN_API int atn_get_frame(AtnRenderer* r, uint32_t* frame);
 /* Renderer::reset + clearing the accumulation image. */
 ATN_API int atn_reset(AtnRenderer* r);
-/* PathTracing::SetEnableProgressive (pathtracing.h:127-135): 1 = running mean in the image exactly
- * as FilmProgressive::put (src/libaten/renderer/film.cpp:61-71), 0 = sum of samples + count in .w
- * (the form the multi-GPU reduce combines). */
+/* How a render call folds its samples into the image (the reference's gather, pathtracing_impl.cu:282-324). */
+typedef enum AtnGatherMode {
+    ATN_GATHER_OVERWRITE = 0,    /* the reference GPU renderer with progressive off (its default, pathtracing.h:103): every
+                                    render call overwrites the pixel with the mean of that call's samples, w = 1 */
+    ATN_GATHER_PROGRESSIVE = 1,  /* running mean across calls, one step per sample, exactly as FilmProgressive::put
+                                    (src/libaten/renderer/film.cpp:61-71): new = (n old + sample) / (n + 1), w = n + 1.
+                                    The handle's default; with one sample per call it is also the reference GPU gather
+                                    with progressive on */
+    ATN_GATHER_SUM = 2           /* no counterpart in the reference: xyz += sample, w += 1 across calls -- the form the
+                                    multi-GPU reduce combines (one divide by w after the reduce) */
+} AtnGatherMode;
+/* PathTracing::SetEnableProgressive (pathtracing.h:127-135): 1 = ATN_GATHER_PROGRESSIVE, 0 = ATN_GATHER_OVERWRITE. */
 ATN_API int atn_set_progressive(AtnRenderer* r, int enable);
+ATN_API int atn_set_gather_mode(AtnRenderer* r, int mode /* AtnGatherMode */);
 /* Renderer::setHitDistanceLimit (renderer.h:108-111) */
 ATN_API int atn_set_hit_distance_limit(AtnRenderer* r, float d);
 
@@ -249,7 +259,9 @@ ATN_API int atn_set_hit_distance_limit(AtnRenderer* r, float d);
 /* PathTracingImplBase::render(width,height,maxSamples,maxBounce) (pathtracing.cpp:49-89) followed
  * by PathTracing::OnRender (pathtracing.cpp:91-153).  Renders `spp` samples per pixel, sample i of
  * the call using host frame index (frame + i); advances the frame counter by spp.  Asynchronous on
- * the handle's stream. */
+ * the handle's stream: the call returns once the work is queued (it waits only when a bounce tap is installed);
+ * atn_readback / atn_synchronize / atn_get_stats wait for it.  The reference synchronises after every kernel
+ * (cudautil.h:93-104). */
 ATN_API int atn_render(AtnRenderer* r, int32_t width, int32_t height,
                        int32_t spp, int32_t max_bounce, int32_t rr_bounce);
 /* Same, restricted to the pixel rectangle [x0,x1) x [y0,y1) and to samples
@@ -313,7 +325,7 @@ ATN_API int atn_readback(AtnRenderer* r, AtnVec4* host_image, size_t pixel_count
 ATN_API int atn_readback_aov(AtnRenderer* r, AtnVec4* normal_depth, AtnVec4* albedo_meshid, size_t pixel_count);
 /* Device pointer (float4[W*H]) of the image, for NCCL / torch interop; owned by the handle. */
 ATN_API int atn_device_image(AtnRenderer* r, void** device_ptr, size_t* pixel_count);
-/* Counters of the last call on the handle.  After a device-resident ray query this waits for the stream first. */
+/* Counters of the last call on the handle; waits for that call to finish on the GPU first. */
 ATN_API int atn_get_stats(AtnRenderer* r, AtnStats* out);
 /* 1: time the traversal kernels separately with CUDA events (fills AtnStats.trace_ms). */
 ATN_API int atn_set_profiling(AtnRenderer* r, int enable);

@@ -295,7 +295,9 @@ public:
 
     void reset() { Check(atn_reset(h_)); }
     uint32_t GetFrameCount() const { uint32_t f = 0; atn_get_frame(h_, &f); return f; }
-    void SetEnableProgressive(bool b) { progressive_ = b; Check(atn_set_progressive(h_, b ? 1 : 0)); }
+    void SetEnableProgressive(bool b) { progressive_ = b; Ensure(); Check(atn_set_progressive(h_, b ? 1 : 0)); }
+    /// No counterpart in the reference: ATN_GATHER_SUM keeps sum + count in the image (the multi-GPU reduce form).
+    void SetGatherMode(AtnGatherMode m) { Ensure(); progressive_ = (m == ATN_GATHER_PROGRESSIVE); Check(atn_set_gather_mode(h_, (int)m)); }
     bool IsEnableProgressive() const { return progressive_; }
     void setHitDistanceLimit(float d) { Check(atn_set_hit_distance_limit(h_, d)); }
     void SetRenderingMode(Mode m) { mode_ = m; }
@@ -313,7 +315,13 @@ public:
     FlatScene& flat() { return flat_; }
 
 protected:
-    void Ensure() { if (!h_) Check(atn_create(device_, &h_)); }
+    void Ensure()
+    {
+        if (h_) return;
+        Check(atn_create(device_, &h_));
+        // idaten::PathTracing starts with m_enableProgressive{false} (pathtracing.h:103): every render() overwrites the image
+        Check(atn_set_progressive(h_, progressive_ ? 1 : 0));
+    }
     static void Check(int rc) { if (rc != ATN_OK) throw std::runtime_error(atn_last_error()); }
 
     AtnRenderer* h_{ nullptr };

@@ -42,7 +42,7 @@ def main():
     scene = ol.ref_scene("instanced_dragon", W, H)
     r = PathTracing(local)
     r.UpdateSceneData(scene)
-    r.SetEnableProgressive(False)                      # sum mode: xyz = radiance sum, w = sample count
+    r.set_gather_mode(2)                      # sum mode: xyz = radiance sum, w = sample count
     ptr, _ = r.device_image()
 
     class _Img:

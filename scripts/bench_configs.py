@@ -24,7 +24,7 @@ def render_bench(name, W, H, spp, steps=3, warmup=2, label=""):
     scene = ol.ref_scene(name, W, H)
     r = PathTracing(0)
     r.UpdateSceneData(scene)
-    r.SetEnableProgressive(False)
+    r.set_gather_mode(2)
     for _ in range(warmup):
         r.reset(); r.render(W, H, spp, 5, 3)
     ms = rays = samples = nodes = tris = 0
@@ -49,7 +49,7 @@ def ao_bench(name, W, H, spp, steps=3, warmup=2, label=""):
     scene = ol.ref_scene(name, W, H)
     r = PathTracing(0)
     r.UpdateSceneData(scene)
-    r.SetEnableProgressive(False)
+    r.set_gather_mode(2)
     for _ in range(warmup):
         r.reset(); r.render_ao(W, H, spp, 1, 1.0)
     ms = rays = samples = 0
@@ -76,7 +76,7 @@ def svgf_bench(name, W, H, frames=8, warmup=1, label=""):
     scene = ol.ref_scene(name, W, H)
     r = PathTracing(0)
     r.UpdateSceneData(scene)
-    r.SetEnableProgressive(False)
+    r.set_gather_mode(2)
     for _ in range(warmup):
         r.set_frame(0)
         for f in range(frames):
@@ -113,7 +113,7 @@ def restir_bench(name, W, H, frames=8, warmup=1, label=""):
     scene = ol.ref_scene(name, W, H)
     r = PathTracing(0)
     r.UpdateSceneData(scene)
-    r.SetEnableProgressive(False)
+    r.set_gather_mode(2)
     for _ in range(warmup):
         r.set_frame(0)
         for f in range(frames):
@@ -279,7 +279,7 @@ def ray_stress_flat(name, n_rays, label="", parity_rays=200_000, copies=None):
     r.close()
     r = PathTracing(0)
     r.UpdateSceneData(scene.with_size(W, H))
-    r.SetEnableProgressive(False)
+    r.set_gather_mode(2)
     ms = nr = ns = 0
     for it in range(3):
         r.reset(); r.render(W, H, spp, 5, 3)

@@ -19,7 +19,7 @@ def main():
     scene = ol.ref_scene(name, W, H)
     r = PathTracing(0)
     r.UpdateSceneData(scene)
-    r.SetEnableProgressive(False)
+    r.set_gather_mode(2)
     found = []
     for s in range(s0, s1):
         r.reset()

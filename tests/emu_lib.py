@@ -53,3 +53,21 @@ def top_update_equals_fresh(base: sio.Scene, moved: sio.Scene) -> int:
     """0 when encode_top(moved's list 0 | base's bottom trees) is byte-identical to the tail of encode_wide(moved)."""
     b0, b1 = base.blob(), moved.blob()
     return int(lib().emu_top_update_equals_fresh(C.byref(b0), C.byref(b1)))
+
+
+def trace_closest_flagged(scene: sio.Scene, rays: np.ndarray, band, t_max=None):
+    """The kernel's per-ray logic with the near-tie bookkeeping (band = (rel, inv, S, M), see emu_traversal.cpp);
+    returns (hits, flags, stats): flags[i] = 1 where the exact reference-order walk has to decide the ray."""
+    rays = np.ascontiguousarray(rays, dtype=sio.RAY_DTYPE)
+    hits = np.zeros(len(rays), dtype=sio.HIT_DTYPE)
+    flags = np.zeros(len(rays), dtype=np.uint8)
+    stats = np.zeros(16, np.uint64)
+    tm = None if t_max is None else np.ascontiguousarray(t_max, dtype=np.float32)
+    b = np.ascontiguousarray(band, dtype=np.float32)
+    blob = scene.blob()
+    rc = lib().emu_trace_wide_flag(C.byref(blob), C.c_void_p(rays.ctypes.data), C.c_void_p(tm.ctypes.data) if tm is not None else None,
+                                   C.c_size_t(len(rays)), C.c_void_p(hits.ctypes.data), C.c_void_p(stats.ctypes.data),
+                                   C.c_void_p(b.ctypes.data), C.c_void_p(flags.ctypes.data))
+    if rc != 0:
+        raise RuntimeError("encode_wide rejected the scene's node lists")
+    return hits, flags, {k: int(v) for k, v in zip(STAT_NAMES, stats)}

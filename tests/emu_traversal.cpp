@@ -80,8 +80,14 @@ inline float cull_bound(float t) { return t + fabsf(t) * 2e-5f; }
 
 }  // namespace
 
-extern "C" int emu_trace_wide(const AtnSceneBlob* scene, const AtnRay* rays, const float* t_max_in, size_t n, AtnHit* hits,
-                              uint64_t* stats_out, int sort_leaves_first, int entry_filter)
+// `band` (optional, 4 floats: rel, inv, S, M) switches on the near-tie bookkeeping of the kernel: a per-ray band
+//   B(t) = |t| * rho + alpha,  rho = max(rel, inv * 1e-6 * max_k |invdir_k|),  alpha = S * sum_k |oxinvdir_k| + M * (1 + max_k |org_k|)
+// (maxima over the world ray and every instance-space ray entered so far) bounds how far the biased slab entry distance of a
+// box can lie beyond the hit distance of a triangle inside it.  Boxes are culled with t + 2 B(t); the smallest hit distance
+// of a primitive other than the best one is tracked, and a ray whose runner-up lies within B of its best hit is FLAGGED:
+// the reference's answer for it depends on the reference's visit order, and the exact (reference-order) walk decides it.
+static int trace_impl(const AtnSceneBlob* scene, const AtnRay* rays, const float* t_max_in, size_t n, AtnHit* hits,
+                      uint64_t* stats_out, int sort_leaves_first, int entry_filter, const float* band, uint8_t* flags)
 {
     WideBvh w = encode_wide(scene);
     if (!w.error.empty()) return -1;
@@ -102,6 +108,17 @@ extern "C" int emu_trace_wide(const AtnSceneBlob* scene, const AtnRay* rays, con
             const float wmargin = leaf_margin(org, dir, ri);
             float t_cull = t_max_in ? t_max_in[i] : kBig;
             Best best{ kBig, 0, 0, -1, -1 };
+            float rho = 0.0f, alpha = 0.0f, t2 = kBig;
+            auto widen = [&](const V3& o, const RayInv& r_) {
+                if (!band) return;
+                const float im = fmaxf(fmaxf(fabsf(r_.invdir.x), fabsf(r_.invdir.y)), fabsf(r_.invdir.z));
+                const float S = fabsf(r_.oxinvdir.x) + fabsf(r_.oxinvdir.y) + fabsf(r_.oxinvdir.z);
+                const float M = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
+                rho = fmaxf(rho, fmaxf(band[0], band[1] * 1e-6f * im));
+                alpha = fmaxf(alpha, band[2] * S + band[3] * (1.0f + M));
+            };
+            auto cull_of = [&](float t) { return band ? t + 2.0f * (fabsf(t) * rho + alpha) : cull_bound(t); };
+            widen(org, ri);
             stack.clear();
             int32_t cur = w.top_root, cur_inst = -1;
             for (;;) {
@@ -134,7 +151,12 @@ extern "C" int emu_trace_wide(const AtnSceneBlob* scene, const AtnRay* rays, con
                         const TriHit h = tri_edges(org, dir, V3(t.v0[0], t.v0[1], t.v0[2]), V3(t.e1[0], t.e1[1], t.e1[2]), V3(t.e2[0], t.e2[1], t.e2[2]));
                         if (h.hit && h.t < kBig && t_min < h.t) {
                             const bool closer = h.t < best.t || (h.t == best.t && (cur_inst < best.inst || (cur_inst == best.inst && leaf < best.leaf)));
-                            if (closer) { best.t = h.t; best.a = h.a; best.b = h.b; best.leaf = leaf; best.inst = cur_inst; t_cull = cull_bound(h.t); }
+                            const bool same_prim = best.leaf >= 0 && h.t == best.t && h.a == best.a && h.b == best.b;   // a duplicate SBVH leaf of the best primitive
+                            if (closer) {
+                                if (!same_prim && best.leaf >= 0) t2 = fminf(t2, best.t);
+                                best.t = h.t; best.a = h.a; best.b = h.b; best.leaf = leaf; best.inst = cur_inst; t_cull = cull_of(h.t);
+                            }
+                            else if (!same_prim) t2 = fminf(t2, h.t);
                         }
                         cur = kRefNull;
                     }
@@ -155,6 +177,8 @@ extern "C" int emu_trace_wide(const AtnSceneBlob* scene, const AtnRay* rays, con
                                 const AtnMat4& m = scene->matrices[il.w2l];
                                 const Ray tr = make_ray(mat_apply(m, org), mat_apply_xyz(m, dir));
                                 org = tr.org; dir = tr.dir; ri = ray_inv(org, dir);
+                                widen(org, ri);
+                                if (band && best.leaf >= 0) t_cull = cull_of(best.t);
                             }
                             cur = il.root;
                         }
@@ -175,6 +199,7 @@ extern "C" int emu_trace_wide(const AtnSceneBlob* scene, const AtnRay* rays, con
                 if (finished) break;
             }
             finish(w.tris, iobj.data(), imesh.data(), best, &hits[i]);
+            if (flags) flags[i] = (band && best.leaf >= 0 && t2 <= best.t + (fabsf(best.t) * rho + alpha)) ? 1 : 0;
             st.rays++;
         }
 #pragma omp critical
@@ -191,6 +216,17 @@ extern "C" int emu_trace_wide(const AtnSceneBlob* scene, const AtnRay* rays, con
         stats_out[8] = w.replaced; stats_out[9] = w.not_nested; stats_out[10] = (uint64_t)w.max_stack;
     }
     return 0;
+}
+
+extern "C" int emu_trace_wide(const AtnSceneBlob* scene, const AtnRay* rays, const float* t_max_in, size_t n, AtnHit* hits,
+                              uint64_t* stats_out, int sort_leaves_first, int entry_filter)
+{
+    return trace_impl(scene, rays, t_max_in, n, hits, stats_out, sort_leaves_first, entry_filter, nullptr, nullptr);
+}
+extern "C" int emu_trace_wide_flag(const AtnSceneBlob* scene, const AtnRay* rays, const float* t_max_in, size_t n, AtnHit* hits,
+                                   uint64_t* stats_out, const float* band, uint8_t* flags)
+{
+    return trace_impl(scene, rays, t_max_in, n, hits, stats_out, 0, 1, band, flags);
 }
 
 // Top-layer update (Renderer::updateBVH): encode_top(list 0 of `moved`) against the bottom trees kept from `base` must

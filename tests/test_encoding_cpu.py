@@ -64,3 +64,21 @@ def test_wide_encoding_random_rays_vs_oracle_and_visit_order(golden):
     # the collapse roughly halves the node steps of the binary tree and uses most slots
     assert sa["slots_used"] >= 2.5 * sa["node_count"]
     assert sa["not_nested"] <= 0.01 * sa["node_count"]
+
+
+def test_deep_chain_tree_stack_bound(golden):
+    """A maximally unbalanced tree (tests/synth_scenes.py): the traversal really holds ~depth entries on its stack, the
+    encoder's worst-case bound covers it, and the hits are the reference-order walk's.  A list deeper than the encoder
+    follows (96 levels) is refused, not truncated."""
+    from tests import synth_scenes as ss
+    base = golden.scene("cornell")
+    scene = ss.chain_scene(base, 88)
+    rays = ss.chain_rays(scene, 20000)
+    want = ol.trace_closest(scene, rays)
+    miss = want["objid"] < 0
+    want = want.copy(); want["primid"][miss] = -1; want["mtrlid"][miss] = -1; want["meshid"][miss] = -1
+    got, st = emu_lib.trace_closest(scene, rays)
+    assert got.tobytes() == want.tobytes()
+    assert 64 < st["max_sp"] <= st["stack_bound"] <= 16 + 240
+    with pytest.raises(RuntimeError):
+        emu_lib.trace_closest(ss.chain_scene(base, 120), rays[:8])

@@ -118,7 +118,7 @@ def test_streaming_form_renders_the_same_image(golden, monkeypatch, name):
         monkeypatch.setenv("ATEN_B200_STREAM", form)
         with PathTracing(0) as r:
             r.UpdateSceneData(golden.scene(name))
-            r.SetEnableProgressive(False)
+            r.set_gather_mode(2)
             r.render(m["w"], m["h"], 2, 5, 3)
             imgs.append(r.readback().copy())
     assert (bits(imgs[0]) == bits(imgs[1])).all()

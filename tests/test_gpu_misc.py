@@ -1,0 +1,96 @@
+"""GPU checks (-m gpu) of the boundary's bookkeeping rather than of the arithmetic: the three gather modes, the
+asynchronous render call and its counters, and the large-stack instantiation of the traversal kernel."""
+import numpy as np
+import pytest
+
+from aten_b200 import AtnError, PathTracing
+from aten_b200.api import GATHER_OVERWRITE, GATHER_PROGRESSIVE, GATHER_SUM
+from tests import oracle_lib as ol
+from tests import synth_scenes as ss
+from tests.conftest import bits
+
+pytestmark = pytest.mark.gpu
+
+
+def test_gather_modes(golden):
+    """OVERWRITE = the reference GPU renderer with progressive off (pathtracing_impl.cu:313-316): every call leaves the
+    mean of ITS samples with w = 1, whatever the image held; PROGRESSIVE = FilmProgressive::put per sample;
+    SUM = sum + count.  All three hold the same samples, so they agree up to float rounding."""
+    name = "cornell_mtrl"; m = golden.meta[name]
+    W, H = m["w"], m["h"]
+    with PathTracing(0) as r:
+        r.UpdateSceneData(golden.scene(name))
+        r.set_gather_mode(GATHER_SUM)
+        r.render(W, H, 3, 5, 3)
+        total = r.readback().copy()
+        assert (total[..., 3] == 3).all()
+        r.reset(); r.set_gather_mode(GATHER_PROGRESSIVE)
+        r.render(W, H, 3, 5, 3)
+        prog = r.readback().copy()
+        assert (prog[..., 3] == 3).all()
+        assert np.allclose(prog[..., :3], total[..., :3] / 3, rtol=1e-5, atol=1e-7)
+        # overwrite: two calls in a row, the second one's image does not depend on the first
+        r.reset(); r.SetEnableProgressive(False)
+        r.render(W, H, 3, 5, 3)
+        first = r.readback().copy()
+        assert (first[..., 3] == 1).all()
+        assert (bits(first[..., :3]) == bits(total[..., :3] / np.float32(3))).all()
+        r.render(W, H, 2, 5, 3)                                    # frames 3, 4
+        second = r.readback().copy()
+        assert (second[..., 3] == 1).all()
+        r.reset(); r.set_frame(3); r.set_gather_mode(GATHER_SUM)
+        r.render(W, H, 2, 5, 3)
+        alone = r.readback()
+        assert (bits(second[..., :3]) == bits(alone[..., :3] / np.float32(2))).all()
+        with pytest.raises(AtnError, match="atn_set_gather_mode"):
+            r.set_gather_mode(7)
+
+
+def test_render_is_asynchronous_and_stats_follow(golden):
+    """atn_render returns without waiting; atn_get_stats waits for the call it reports on.  Two renders queued back to
+    back give the counters of the second and the image of both."""
+    name = "sponza_atrium"; m = golden.meta[name]
+    W, H = m["w"], m["h"]
+    with PathTracing(0) as r:
+        r.UpdateSceneData(golden.scene(name))
+        r.set_gather_mode(GATHER_SUM)
+        r.render(W, H, 1, 5, 3)
+        one = r.stats()
+        r.reset(); r.set_frame(0)
+        r.render(W, H, 1, 5, 3)
+        r.render(W, H, 2, 5, 3)
+        st = r.stats()
+        assert st["camera_samples"] == 2 * W * H and one["camera_samples"] == W * H
+        assert st["closest_rays"] > one["closest_rays"] and st["device_ms"] > 0
+        img = r.readback()
+        assert (img[..., 3] == 3).all()
+
+
+def test_large_stack_instantiation_on_a_deep_chain(golden):
+    """Stack need 93 > 16 shared + 48 local entries: the upload picks the 240-entry instantiation; hits equal the
+    reference-order walk's bit for bit.  A node list deeper than the encoder follows is refused with a message."""
+    base = golden.scene("cornell")
+    scene = ss.chain_scene(base, 88)
+    rays = ss.chain_rays(scene, 100000)
+    want = ol.trace_closest(scene, rays).copy()
+    miss = want["objid"] < 0
+    want["primid"][miss] = -1; want["mtrlid"][miss] = -1; want["meshid"][miss] = -1
+    with PathTracing(0) as r:
+        r.UpdateSceneData(scene)
+        got = r.trace_closest(rays)
+        assert got.tobytes() == want.tobytes()
+        assert (got["objid"] >= 0).mean() > 0.4
+    with PathTracing(0) as r:
+        with pytest.raises(AtnError, match="deeper than 96 levels"):
+            r.UpdateSceneData(ss.chain_scene(base, 120))
+
+
+def test_static_query_reports_its_own_counters(golden):
+    scene = golden.scene("cornell")
+    rays, _ = golden.rays("cornell")
+    with PathTracing(0) as r:
+        r.UpdateSceneData(scene)
+        r.render(scene.width, scene.height, 1, 5, 3)
+        r.trace_closest_static(rays[:777])
+        st = r.stats()
+        assert st["closest_rays"] == 777 and st["shadow_rays"] == 0 and st["camera_samples"] == 0 and st["kernel_launches"] == 1

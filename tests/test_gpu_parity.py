@@ -14,6 +14,7 @@ import numpy as np
 import pytest
 
 from aten_b200 import PathTracing, AtnError, scene_io as sio
+from aten_b200.api import GATHER_OVERWRITE, GATHER_SUM
 from tests import oracle_lib as ol
 from tests.conftest import bits
 
@@ -220,7 +221,7 @@ def test_determinism_and_region_split(golden, renderers):
     r = renderers[name]
     imgs = []
     for _ in range(2):
-        r.reset(); r.SetEnableProgressive(False)
+        r.reset(); r.set_gather_mode(GATHER_SUM)
         r.render(W, H, 2, 5, 3)
         imgs.append(r.readback().copy())
     assert (bits(imgs[0]) == bits(imgs[1])).all()
@@ -260,7 +261,7 @@ def test_full_size_properties(golden):
     scene = golden.scene("sponza_atrium").with_size(1920, 1080)
     r = PathTracing(0)
     r.UpdateSceneData(scene)
-    r.SetEnableProgressive(False)
+    r.set_gather_mode(GATHER_SUM)
     r.render(1920, 1080, 2, 5, 3)
     st = r.stats()
     img = r.readback()
@@ -430,7 +431,7 @@ def test_non_finite_sample_of_the_reference_is_reproduced():
     scene = ol.ref_scene("instanced_dragon", W, H)
     with PathTracing(0) as r:
         r.UpdateSceneData(scene)
-        r.SetEnableProgressive(False)
+        r.set_gather_mode(GATHER_SUM)
         r.render_region(W, H, 0, 0, W, H, frame, frame + 1, 5, 3)
         img = r.readback()
     bad = ~np.isfinite(img[..., :3]).all(axis=2)

@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(_HERE, "libaten_b200.so")
 EXPORTS = [
     "atn_create", "atn_destroy", "atn_last_error", "atn_version", "atn_upload_scene", "atn_update_camera",
     "atn_update_top_layer", "atn_update_materials", "atn_update_lights", "atn_update_config", "atn_set_seeds",
-    "atn_set_frame", "atn_get_frame", "atn_reset", "atn_set_progressive", "atn_set_gather_mode", "atn_set_hit_distance_limit",
+    "atn_set_frame", "atn_get_frame", "atn_reset", "atn_set_progressive", "atn_set_gather_mode", "atn_set_exact_ties", "atn_set_hit_distance_limit",
     "atn_render", "atn_render_region", "atn_synchronize", "atn_readback", "atn_device_image", "atn_get_stats",
     "atn_set_profiling", "atn_get_stream", "atn_trace_closest", "atn_trace_any", "atn_trace_closest_device",
     "atn_trace_any_device", "atn_set_bounce_tap", "atn_trace_closest_static", "atn_readback_aov", "atn_render_ao",
@@ -39,7 +39,7 @@ class AtnError(RuntimeError):
 class AtnStats(C.Structure):
     _fields_ = [("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("camera_samples", C.c_uint64),
                 ("kernel_launches", C.c_uint64), ("device_ms", C.c_float), ("trace_ms", C.c_float),
-                ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64)]
+                ("nodes_visited", C.c_uint64), ("tris_tested", C.c_uint64), ("exact_rays", C.c_uint64)]
 
 
 _lib = None
@@ -173,6 +173,11 @@ class PathTracing:
         """AtnGatherMode: GATHER_OVERWRITE / GATHER_PROGRESSIVE / GATHER_SUM (sum of samples + count in .w, for the
         multi-GPU reduce)."""
         _check(self._lib, self._lib.atn_set_gather_mode(self._h, C.c_int(mode)))
+
+    def set_exact_ties(self, b: bool):
+        """True (default): rays whose two nearest primitives tie within the error of the reference's biased box test are
+        decided by the reference's own depth-first walk (bit-identical primitive ids); False: they keep the nearest."""
+        _check(self._lib, self._lib.atn_set_exact_ties(self._h, C.c_int(1 if b else 0)))
 
     def setHitDistanceLimit(self, d: float):
         _check(self._lib, self._lib.atn_set_hit_distance_limit(self._h, C.c_float(d)))

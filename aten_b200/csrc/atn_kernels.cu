@@ -83,9 +83,21 @@ struct BvhView {
     cudaTextureObject_t node_tex;   // the QuadNode array again, as a linear float4 texture (see ATN_NODE_TEX)
 };
 
+// The reference's own threaded node lists (48-byte nodes, hit / miss links), kept on the device for the exact walk that
+// decides near ties (k_exact): all lists in one array, list k starting at offsets[k].
+struct RefView {
+    const AtnBvhNode* nodes;
+    const uint32_t* offsets;
+    const AtnObjectParameter* objects;
+    const AtnMat4* matrices;
+    const AtnTriangleParameter* triangles;
+    const AtnVec4* positions;
+    float t_min;
+};
+
 constexpr int kMaxBounce = 16;
 #ifndef ATN_SMEM_STACK
-#define ATN_SMEM_STACK 16
+#define ATN_SMEM_STACK 14
 #endif
 constexpr int kSmemStack = ATN_SMEM_STACK;     // shared-memory stack entries per thread
 // overflow of the shared-memory stack, local memory: two instantiations of the kernel, picked per scene from the
@@ -113,11 +125,15 @@ struct Counters {
     int32_t fetch_closest[kMaxBounce];  // persistent-thread work cursors
     int32_t fetch_shadow[kMaxBounce];
     int32_t fetch_query;
-    int32_t pad[3];
+    int32_t n_exact_closest[kMaxBounce];  // rays handed to the exact walk (near ties), per bounce
+    int32_t n_exact_shadow[kMaxBounce];
+    int32_t n_exact_query;
+    int32_t n_lit_side[kMaxBounce];       // surface hits of the side pass (paths decided by the exact walk)
+    int32_t pad[2];
 };
 
 // Ray totals of one atn_render call (not cleared per sample).
-struct Totals { unsigned long long closest, shadow; };
+struct Totals { unsigned long long closest, shadow, exact; };
 // Traversal work of one call: QuadNodes fetched and triangle tests run (all lanes, all traversal kernels).
 struct Visits { unsigned long long nodes, tris; };
 
@@ -133,6 +149,12 @@ struct PathBuffers {
     int32_t* queue[2];    // path slots to trace at bounce b (b & 1)
     int32_t* q_lit;       // path slots that passed the surface stage
     int32_t* q_shadow;    // path slots with a shadow ray to trace
+    int32_t* q_exact;     // path slots whose closest-hit traversal ended in a near tie: the exact walk decides them (k_exact)
+    int32_t* q_exact_s;   // the same for shadow rays (its own list: the two exact walks of a bounce overlap other work)
+    int32_t* q_lit_side;  // side pass: paths of q_exact that passed the surface stage
+    uint8_t* pend;        // bounce + 1 of the bounce whose closest hit the exact walk decides (0: none since k_generate).  Written
+                          // by the traversal, read by the main surface stage, never touched by the side pass -- which
+                          // overwrites hit0 / hit1 of such a path while the main surface stage is still running
     float4* surf0;        // Surface: p.xyz, u
     float4* surf1;        //          orienting normal.xyz, v
     float4* surf2;        //          albedo.xyz, bits(mtrlid)
@@ -171,12 +193,49 @@ __device__ __forceinline__ void resolve_hit(const BvhView& bv, const TraceResult
     *meshid = mesh < 0 ? il.w : mesh;
 }
 
-// Relative slack on the running t_max used to CULL boxes once a hit is known.  The reference culls
-// with the exact running t_max through a slab test that is biased by +1e-6 on the direction
-// (aabb.h:68), which makes its answer depend on its visit order when two primitives are hit within
-// a few ulps of each other.  Culling with t*(1+2e-5) keeps triangles that tie with the current hit
-// reachable; pairs within 2e-5 relative distance can still resolve either way (DESIGN.md "Near ties").
-__device__ __forceinline__ float cull_bound(float t) { return t + fabsf(t) * 2e-5f; }
+// ---- near ties ---------------------------------------------------------------------------------------------
+// The reference culls boxes with its RUNNING closest distance through a slab test that is biased by +1e-6 on the
+// direction (aabb.h:68) and walks its trees in a fixed depth-first order (threaded_bvh_traverser.h:98-304).  A box
+// can therefore appear to start BEHIND a triangle it contains, and when two primitives are hit within that error of
+// each other, which of them the reference reports depends on its visit order: it may keep the farther one because
+// the nearer one's box was culled by then.  This kernel walks front to back, so for such rays -- and only for them --
+// its own answer can be the other primitive.  They are detected here and decided by the reference's own walk:
+//   * per ray a band  B(t) = |t| * rho + alpha  bounds how far the biased entry distance of a box can lie beyond the
+//     computed hit distance of a triangle inside it:
+//         rho   = max(kBandRel, kBandInv * 1e-6 * max_k |invdir_k|)      the bias 1e-6 / |dir_k + 1e-6| and rounding,
+//         alpha = kBandS * sum_k |oxinvdir_k| + kBandM * (1 + max_k |org_k|)   rounding of plane * inv - org * inv and of
+//                                                                         the triangle test, absolute,
+//     taken over the world ray and every instance-space ray entered so far;
+//   * boxes are culled with t + 2 B(t), so every primitive that can tie with the final hit has been tested;
+//   * the smallest hit distance of a primitive OTHER than the best one is tracked (t2); at the end of the ray, t2 within
+//     B of the best hit means the reference's answer depends on its order: the ray goes to the exact queue and
+//     k_exact repeats it as the reference's own depth-first walk over the reference's own node lists.
+// If nothing ties, the reference's answer is this kernel's: every other primitive is farther than the band, the boxes on
+// the path to the best primitive start no later than its hit plus the band, so no hit the reference accepts earlier
+// can cull them (DESIGN.md "Exactness").  scripts/exp_near_ties.py measures the rule on the CPU emulation: with these
+// constants no ray that differs from the reference goes unflagged (Sponza: 0.4 % of path rays flagged, 0.01 % differ).
+constexpr float kBandRel = 5e-5f, kBandInv = 3.0f, kBandS = 2e-6f, kBandM = 5e-5f;
+struct Band { float rho, alpha; };
+__device__ __forceinline__ Band band_of(const V3& org, const RayInv& ri)
+{
+    const float im = fmaxf(fmaxf(fabsf(ri.invdir.x), fabsf(ri.invdir.y)), fabsf(ri.invdir.z));
+    const float S = fabsf(ri.oxinvdir.x) + fabsf(ri.oxinvdir.y) + fabsf(ri.oxinvdir.z);
+    const float M = fmaxf(fmaxf(fabsf(org.x), fabsf(org.y)), fabsf(org.z));
+    Band b;
+    b.rho = fmaxf(kBandRel, kBandInv * 1e-6f * im);
+    b.alpha = kBandS * S + kBandM * (1.0f + M);
+    return b;
+}
+__device__ __forceinline__ float band_at(const Band& b, float t) { return fabsf(t) * b.rho + b.alpha; }
+// bound used to CULL boxes once a hit at distance t is known
+__device__ __forceinline__ float cull_bound(const Band& b, float t) { return fminf(t + 2.0f * band_at(b, t), kInf); }
+
+// What the traversal knows about runners-up when a ray ends.
+struct Tie {
+    bool any;      // another primitive was hit within `band` of the best hit
+    bool cls;      // ... one of another instance or another material (only tracked for Policy::kNeedClass)
+    float band;    // B(best.t)
+};
 
 // intersectTriangle (src/libaten/math/intersect.h:45-89) with e1 = v1 - v0 and e2 = v2 - v0 taken from
 // the TriLeaf record (computed on upload with the same float subtraction, so every later operation
@@ -248,12 +307,28 @@ __device__ __forceinline__ bool leaf_may_hit(float t0, float t1, float margin)
 }
 
 // ---- ray sources / sinks of the traversal kernel -------------------------------------------
-// A policy tells the kernel where ray i comes from and where its result goes.
+// A policy tells the kernels where ray i comes from and where its result goes:
+//   load(i, ...)             ray i of the queue, its distance bound and early-exit mode (k_trace)
+//   world(slot, ...)         the ray of a slot again (leaving an instance; k_exact)
+//   t_max(slot)              its distance bound (k_exact)
+//   finish(bv, slot, r, tie) end of the fast traversal: stores the result and returns true, or returns false when the
+//                            result depends on a near tie the policy cares about (the slot then goes to the exact queue)
+//   finish_hit(slot, h)      stores a resolved hit (used by finish and by k_exact)
+__device__ __forceinline__ AtnHit resolved(const BvhView& bv, const TraceResult& r)
+{
+    AtnHit h;
+    resolve_hit(bv, r, &h.objid, &h.primid, &h.mtrlid, &h.meshid);
+    h.t = r.t; h.a = r.a; h.b = r.b; h.isVoxel = 0;
+    return h;
+}
+
 struct ClosestPolicy {             // wavefront closest-hit (hitTest)
+    static constexpr bool kNeedClass = false;
     PathBuffers pb;
     const int32_t* queue;          // path slots, nullptr = identity
     float t_max_all;
     int32_t* mesh_out;             // where to keep isect.meshid (first bounce only), or nullptr
+    uint8_t pend_tag;              // bounce + 1 when the shade stage runs next to the exact walk (PathBuffers::pend), else 0
     __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* t_max, int* mode, float* exit_dist) const
     {
         const int s = queue ? queue[i] : i;
@@ -268,18 +343,39 @@ struct ClosestPolicy {             // wavefront closest-hit (hitTest)
         const float4 rd = pb.ray_d[slot];
         *o = V3(ro.x, ro.y, ro.z); *d = V3(rd.x, rd.y, rd.z);
     }
-    __device__ __forceinline__ void finish(const BvhView& bv, int slot, const TraceResult& r) const
+    __device__ __forceinline__ float t_max(int) const { return t_max_all; }
+    __device__ __forceinline__ void finish_hit(int slot, const AtnHit& h) const
     {
-        int32_t objid, primid, mtrlid, meshid;
-        resolve_hit(bv, r, &objid, &primid, &mtrlid, &meshid);
-        pb.hit0[slot] = make_float4(r.t, r.a, r.b, __int_as_float(primid));
-        pb.hit1[slot] = make_int2(objid, mtrlid);
-        if (mesh_out) mesh_out[slot] = meshid;
+        pb.hit0[slot] = make_float4(h.t, h.a, h.b, __int_as_float(h.primid));
+        pb.hit1[slot] = make_int2(h.objid, h.mtrlid);
+        if (mesh_out) mesh_out[slot] = h.meshid;
+    }
+    __device__ __forceinline__ bool finish(const BvhView& bv, int slot, const TraceResult& r, const Tie& tie) const
+    {
+        if (tie.any) { if (pend_tag) pb.pend[slot] = pend_tag; return false; }     // the main surface stage leaves this path to the side pass
+        finish_hit(slot, resolved(bv, r));
+        return true;
     }
 };
 
+// Shadow rays: the result is a yes / no (HitShadowRay, pathtracing_impl.h:353-393), so a near tie only matters when the
+// tied primitives could answer differently: another object or material (tie.cls), a material whose alpha can end the
+// lookup, or a singular light whose distance falls inside the tie.
+__device__ __forceinline__ bool shadow_tie_matters(const SceneView& sc, const AtnLightParameter& light, float dist, const AtnHit& h, const Tie& tie)
+{
+    if (h.objid < 0) return false;                               // nothing hit at all: the reference finds nothing either
+    if (light.attrib & 2u) return false;                         // infinite light: any hit hides it
+    if ((light.attrib & 1u) && h.t <= dist - tie.band) return false;   // singular light: something is clearly in front
+    if (!tie.any) return false;
+    if (tie.cls) return true;
+    if ((light.attrib & 1u) && fabsf(h.t - dist) <= tie.band) return true;
+    const AtnMaterialParameter& m = sc.materials[h.mtrlid < 0 ? 0 : h.mtrlid];
+    return h.mtrlid >= 0 && (m.albedoMap >= 0 || m.baseColor.w < 1.0f);       // isTranslucentByAlpha looks at the tied hit's texel
+}
+
 template <bool kTap>
 struct ShadowPolicy {              // wavefront shadow rays (hitShadowRay)
+    static constexpr bool kNeedClass = true;
     PathBuffers pb;
     SceneView sc;
     AtnBounceRecord* tap;
@@ -291,6 +387,7 @@ struct ShadowPolicy {              // wavefront shadow rays (hitShadowRay)
         // aten::ray(rayorg, raydir) renormalises the direction (pathtracing_impl.h:378)
         *o = V3(so.x, so.y, so.z); *d = normalize(V3(sd.x, sd.y, sd.z));
     }
+    __device__ __forceinline__ float t_max(int slot) const { return pb.sh_o[slot].w - kEps; }
     __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* t_max, int* mode, float* exit_dist) const
     {
         const int s = pb.q_shadow[i];
@@ -302,16 +399,14 @@ struct ShadowPolicy {              // wavefront shadow rays (hitShadowRay)
         *mode = (attrib & 2u) ? EXIT_ANY_HIT : ((attrib & 1u) ? EXIT_HIT_BEFORE : EXIT_NONE);
         *exit_dist = dist;
     }
-    __device__ __forceinline__ void finish(const BvhView& bv, int slot, const TraceResult& r) const
+    __device__ __forceinline__ void finish_hit(int slot, const AtnHit& h) const
     {
         const float4 so = pb.sh_o[slot];
         const float4 sd = pb.sh_d[slot];
         const float4 c = pb.sh_c[slot];
         const AtnLightParameter& light = sc.lights[__float_as_int(sd.w)];
         Ray sr; sr.org = V3(so.x, so.y, so.z); sr.dir = normalize(V3(sd.x, sd.y, sd.z));
-        int32_t objid, primid, mtrlid, meshid;
-        resolve_hit(bv, r, &objid, &primid, &mtrlid, &meshid);
-        const bool vis = shadow_visible(sc, light, sr, so.w, objid, primid, r.a, r.b, r.t, mtrlid);
+        const bool vis = shadow_visible(sc, light, sr, so.w, h.objid, h.primid, h.a, h.b, h.t, h.mtrlid);
         if (vis) {
             float4 cc = pb.contrib[slot];
             cc.x += c.x; cc.y += c.y; cc.z += c.z;
@@ -323,34 +418,49 @@ struct ShadowPolicy {              // wavefront shadow rays (hitShadowRay)
             if (vis) { const float4 cc = pb.contrib[slot]; rec.contrib[0] = cc.x; rec.contrib[1] = cc.y; rec.contrib[2] = cc.z; }
         }
     }
+    __device__ __forceinline__ bool finish(const BvhView& bv, int slot, const TraceResult& r, const Tie& tie) const
+    {
+        const AtnHit h = resolved(bv, r);
+        if (tie.any && shadow_tie_matters(sc, sc.lights[__float_as_int(pb.sh_d[slot].w)], pb.sh_o[slot].w, h, tie)) return false;
+        finish_hit(slot, h);
+        return true;
+    }
 };
 
 struct QueryClosestPolicy {        // atn_trace_closest
-    const AtnRay* rays; const float* t_max; AtnHit* hits;
+    static constexpr bool kNeedClass = false;
+    const AtnRay* rays; const float* t_max_in; AtnHit* hits;
     __device__ __forceinline__ void world(int i, V3* o, V3* d) const { const AtnRay r = rays[i]; *o = V3(r.org); *d = V3(r.dir); }
+    __device__ __forceinline__ float t_max(int i) const { return t_max_in ? fminf(t_max_in[i], kInf) : kInf; }
     __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* tm, int* mode, float* exit_dist) const
     {
-        world(i, o, d); *slot = i; *tm = t_max ? fminf(t_max[i], kInf) : kInf; *mode = EXIT_NONE; *exit_dist = 0.0f;
+        world(i, o, d); *slot = i; *tm = t_max(i); *mode = EXIT_NONE; *exit_dist = 0.0f;
     }
-    __device__ __forceinline__ void finish(const BvhView& bv, int i, const TraceResult& r) const
+    __device__ __forceinline__ void finish_hit(int i, const AtnHit& h) const { hits[i] = h; }
+    __device__ __forceinline__ bool finish(const BvhView& bv, int i, const TraceResult& r, const Tie& tie) const
     {
-        AtnHit h;
-        resolve_hit(bv, r, &h.objid, &h.primid, &h.mtrlid, &h.meshid);
-        h.t = r.t; h.a = r.a; h.b = r.b; h.isVoxel = 0;
-        hits[i] = h;
+        if (tie.any) return false;
+        hits[i] = resolved(bv, r);
+        return true;
     }
 };
 
-struct QueryAnyPolicy {            // atn_trace_any
+struct QueryAnyPolicy {            // atn_trace_any: a singular light at distance dist[i]
+    static constexpr bool kNeedClass = false;
     const AtnRay* rays; const float* dist; uint8_t* visible;
     __device__ __forceinline__ void world(int i, V3* o, V3* d) const { const AtnRay r = rays[i]; *o = V3(r.org); *d = V3(r.dir); }
+    __device__ __forceinline__ float t_max(int i) const { return fminf(dist[i] - kEps, kInf); }
     __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* tm, int* mode, float* exit_dist) const
     {
-        world(i, o, d); *slot = i; *tm = fminf(dist[i] - kEps, kInf); *mode = EXIT_HIT_BEFORE; *exit_dist = dist[i];
+        world(i, o, d); *slot = i; *tm = t_max(i); *mode = EXIT_HIT_BEFORE; *exit_dist = dist[i];
     }
-    __device__ __forceinline__ void finish(const BvhView&, int i, const TraceResult& r) const
+    __device__ __forceinline__ void finish_hit(int i, const AtnHit& h) const { visible[i] = (h.objid < 0 || h.t > dist[i]) ? 1 : 0; }
+    __device__ __forceinline__ bool finish(const BvhView&, int i, const TraceResult& r, const Tie& tie) const
     {
+        // only a tie that straddles the light's distance can change the answer
+        if (r.leaf >= 0 && tie.any && fabsf(r.t - dist[i]) <= tie.band) return false;
         visible[i] = (r.leaf < 0 || r.t > dist[i]) ? 1 : 0;
+        return true;
     }
 };
 
@@ -503,10 +613,15 @@ __device__ __forceinline__ SlabPair slab_pair(const float4 mn_xy, const float4 m
 #endif
 template <class Policy, int kLocalStack, bool kStream>
 __global__ void __launch_bounds__(kTraceBlock, kStream ? ATN_STREAM_MIN_BLOCKS : ATN_TRACE_MIN_BLOCKS)
-k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch, Visits* visits)
+k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch, Visits* visits,
+        int32_t* __restrict__ exact_q, int32_t* __restrict__ exact_count)
 {
     __shared__ int2 s_stack[kSmemStack * kTraceBlock];   // (reference, entry distance bits) per lane and level
     __shared__ float s_world[12 * kTraceBlock];          // world-space org, dir, invdir, oxinvdir of the lane's ray
+    // near-tie bookkeeping of the lane's ray (touched when a triangle is hit, an instance is entered, the ray ends):
+    // band rho, band alpha, runner-up distance (any primitive), runner-up distance (other instance / material),
+    // material of the best hit
+    __shared__ float s_tie[5 * kTraceBlock];
     int2 l_stack[kLocalStack];
     const int tid = threadIdx.x;
     const uint32_t stack_base = (uint32_t)__cvta_generic_to_shared(&s_stack[tid]);
@@ -526,7 +641,28 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
     uint32_t n_nodes = 0, n_tris = 0;
 
     for (;;) {
-        if (done) { pol.finish(bv, slot, best); done = false; }
+        bool to_exact = false;
+        if (done) {
+            Tie tie{ false, false, 0.0f };
+            if (exact_q && best.leaf >= 0) {
+                const Band bd{ s_tie[0 * kTraceBlock + tid], s_tie[1 * kTraceBlock + tid] };
+                tie.band = band_at(bd, best.t);
+                tie.any = s_tie[2 * kTraceBlock + tid] <= best.t + tie.band;
+                tie.cls = Policy::kNeedClass && s_tie[3 * kTraceBlock + tid] <= best.t + tie.band;
+            }
+            to_exact = !pol.finish(bv, slot, best, tie);
+            done = false;
+        }
+        if (exact_q) {           // rays the exact walk has to decide (rare): appended by the converged warp, one atomic per warp
+            const unsigned em = __ballot_sync(full, to_exact);
+            if (em != 0u) {
+                const int leader = __ffs(em) - 1;
+                int base = 0;
+                if (lane == leader) base = atomicAdd(exact_count, __popc(em));
+                base = __shfl_sync(full, base, leader);
+                if (to_exact) exact_q[base + __popc(em & ((1u << lane) - 1u))] = slot;
+            }
+        }
 
         // ---------------- refill idle lanes ----------------
         const unsigned idle = __ballot_sync(full, !active);
@@ -549,6 +685,13 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                     s_world[9 * kTraceBlock + tid] = ri.oxinvdir.x; s_world[10 * kTraceBlock + tid] = ri.oxinvdir.y; s_world[11 * kTraceBlock + tid] = ri.oxinvdir.z;
                     t_cull = t_max;
                     best.t = kInf; best.a = 0.0f; best.b = 0.0f; best.leaf = -1; best.inst = -1;
+#ifndef ATN_EXP_NO_BAND_LOAD
+                    {
+                        const Band bd = band_of(org, ri);
+                        s_tie[0 * kTraceBlock + tid] = bd.rho; s_tie[1 * kTraceBlock + tid] = bd.alpha;
+                        s_tie[2 * kTraceBlock + tid] = kInf; s_tie[3 * kTraceBlock + tid] = kInf;
+                    }
+#endif
                     sts64(stack_base, kRefDone, __float_as_int(-kInf));     // sentinel: popping it ends the ray
                     sp = 1; cur = bv.top_root; cur_inst = -1;
                     active = true;
@@ -676,10 +819,33 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                 if (h.hit && h.t < kInf && t_min < h.t) {
                     const bool closer = h.t < best.t ||
                         (h.t == best.t && (cur_inst < best.inst || (cur_inst == best.inst && leaf < best.leaf)));
+                    // Runner-up bookkeeping (see "near ties"): only a hit within the cull bound of the best one can tie with
+                    // it -- t_cull is already in a register, so the common cases (a far hit that loses, a first hit) cost one
+                    // comparison; the shared-memory update below runs for actual near ties only.
+                    float t2 = kInf;                           // distance of the hit that is NOT the best afterwards, if it can tie
+                    float nc = t_cull;
+                    if (closer) {
+                        const Band bd{ s_tie[0 * kTraceBlock + tid], s_tie[1 * kTraceBlock + tid] };
+                        nc = cull_bound(bd, h.t);
+                        if (best.leaf >= 0 && best.t <= nc) t2 = best.t;
+                        if (mode == EXIT_ANY_HIT || (mode == EXIT_HIT_BEFORE && h.t <= exit_dist - band_at(bd, h.t))) finished = true;
+                    }
+                    else if (h.t <= t_cull) t2 = h.t;
+#ifndef ATN_EXP_NO_T2
+                    if (t2 < kInf) {
+                        // another SBVH leaf of the best primitive gives the same t, a, b bit for bit: not a runner-up
+                        const bool same = h.t == best.t && h.a == best.a && h.b == best.b;
+                        if (!same) {
+                            s_tie[2 * kTraceBlock + tid] = fminf(s_tie[2 * kTraceBlock + tid], t2);
+                            if (Policy::kNeedClass && (cur_inst != best.inst || __float_as_int(b.w) != __float_as_int(s_tie[4 * kTraceBlock + tid])))
+                                s_tie[3 * kTraceBlock + tid] = fminf(s_tie[3 * kTraceBlock + tid], t2);
+                        }
+                    }
+#endif
                     if (closer) {
                         best.t = h.t; best.a = h.a; best.b = h.b; best.leaf = leaf; best.inst = cur_inst;
-                        t_cull = cull_bound(h.t);
-                        if (mode == EXIT_ANY_HIT || (mode == EXIT_HIT_BEFORE && h.t <= exit_dist)) finished = true;
+                        t_cull = nc;
+                        if (Policy::kNeedClass) s_tie[4 * kTraceBlock + tid] = b.w;        // material of the best hit
                     }
                 }
                 cur = kRefNull;
@@ -722,6 +888,11 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                                 const Ray tr = make_ray(mat_apply(m, org), mat_apply_xyz(m, dir));   // mat4::applyRay
                                 org = tr.org; dir = tr.dir;
                                 ri = ray_inv(org, dir);
+                                // the band covers every space the ray has been carried into; the cull bound follows it
+                                const Band nb = band_of(org, ri);
+                                const Band bd{ fmaxf(s_tie[0 * kTraceBlock + tid], nb.rho), fmaxf(s_tie[1 * kTraceBlock + tid], nb.alpha) };
+                                s_tie[0 * kTraceBlock + tid] = bd.rho; s_tie[1 * kTraceBlock + tid] = bd.alpha;
+                                if (best.leaf >= 0) t_cull = cull_bound(bd, best.t);
                             }
                             cur = il.y;
                         }
@@ -762,6 +933,128 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
     if (lane == 0 && visits) {
         atomicAdd(&visits->nodes, (unsigned long long)n_nodes);
         atomicAdd(&visits->tris, (unsigned long long)n_tris);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// The exact walk: ThreadedBvhTraverser<true>::Traverse<Closest> (threaded_bvh_traverser.h:98-304) as it stands -- the
+// reference's own node lists, its stackless hit / miss links, its depth-first order, its running t_max through the biased
+// slab test -- for the few rays whose answer depends on that order (see "near ties" above).  One thread per ray; the
+// queue holds a fraction of a percent of a wavefront, so this kernel is a short tail behind k_trace, not a second
+// traversal of the frame.
+// ---------------------------------------------------------------------------------------------
+// The walk is written as a state machine with ONE round of loads per iteration whatever the lane is doing -- a node
+// (3 x 16 B), an object record, a matrix (3 rows), a triangle record, three vertex positions -- so that the lanes of a warp,
+// which are at unrelated nodes of unrelated rays, wait for memory once per iteration instead of once per kind of step.
+__device__ __forceinline__ AtnHit ref_traverse(const RefView& rv, const V3& worg, const V3& wdir, float t_max)
+{
+    enum : int { PH_NODE, PH_OBJECT, PH_MATRIX, PH_TRIANGLE, PH_POSITIONS };
+    AtnHit isect;
+    isect.t = kInf; isect.objid = -1; isect.mtrlid = -1; isect.meshid = -1; isect.primid = -1; isect.a = 0.0f; isect.b = 0.0f; isect.isVoxel = 0;
+    const float4* const top = reinterpret_cast<const float4*>(rv.nodes + rv.offsets[0]);
+    const float4* list = top;
+    V3 org = worg, dir = wdir;
+    RayInv ri = ray_inv(org, dir);
+    int32_t objid = -1, meshid = -1, top_hit = -1, top_miss = -1;
+    int32_t link_hit = 0, link_miss = 0, exid = 0, primid = 0, mtrlid = 0, tri_mesh = 0;
+    int phase = PH_NODE;
+    const float4* a0 = list; const float4* a1 = list + 1; const float4* a2 = list + 2;      // node 0 of the top layer
+    for (;;) {
+        const float4 v0 = __ldg(a0), v1 = __ldg(a1), v2 = __ldg(a2);
+        // set when this iteration finishes a node: the reference's `is_hit`, or an entry into a bottom tree (root = node 0)
+        bool decided = false, is_hit = false, entered = false;
+        if (phase == PH_NODE) {
+            link_hit = (int32_t)v0.w; link_miss = (int32_t)v1.w;
+            if (v2.x >= 0 || v2.y >= 0) {                               // ThreadedBvhNode::isLeaf
+                if (v2.z >= 0) {                                        // a top-layer leaf with a bottom tree
+                    objid = (int32_t)v2.x; meshid = (int32_t)v2.w;
+                    exid = (int32_t)((uint32_t)__float_as_int(v2.z) & 0x7fffu);
+                    top_hit = link_hit; top_miss = link_miss;
+                    phase = PH_OBJECT;
+                    a0 = a1 = a2 = reinterpret_cast<const float4*>(rv.objects + objid);        // type, area, object_id, mtx_id
+                }
+                else if (v2.y >= 0) {                                   // a triangle
+                    primid = (int32_t)v2.y;
+                    phase = PH_TRIANGLE;
+                    a0 = reinterpret_cast<const float4*>(rv.triangles + primid); a1 = a0 + 1; a2 = a1;
+                }
+                else decided = true;                                    // a leaf that holds nothing traversable (sphere): is_hit stays false
+            }
+            else {
+                float t0;
+                is_hit = aabb_hit(ri, V3(v0.x, v0.y, v0.z), V3(v1.x, v1.y, v1.z), rv.t_min, t_max, &t0);
+                decided = true;
+            }
+        }
+        else if (phase == PH_OBJECT) {
+            const int32_t mtx_id = __float_as_int(v0.w);
+            if (mtx_id >= 0) {
+                phase = PH_MATRIX;
+                a0 = reinterpret_cast<const float4*>(rv.matrices + mtx_id + 1); a1 = a0 + 1; a2 = a0 + 2;    // rows 0-2 of W2L
+            }
+            else {
+                org = worg; dir = wdir; ri = ray_inv(org, dir);
+                list = reinterpret_cast<const float4*>(rv.nodes + rv.offsets[exid]);
+                entered = true;
+            }
+        }
+        else if (phase == PH_MATRIX) {
+            AtnMat4 m;
+            m.m[0] = v0.x; m.m[1] = v0.y; m.m[2] = v0.z; m.m[3] = v0.w; m.m[4] = v1.x; m.m[5] = v1.y; m.m[6] = v1.z; m.m[7] = v1.w;
+            m.m[8] = v2.x; m.m[9] = v2.y; m.m[10] = v2.z; m.m[11] = v2.w; m.m[12] = m.m[13] = m.m[14] = 0.0f; m.m[15] = 1.0f;
+            const Ray tr = make_ray(mat_apply(m, worg), mat_apply_xyz(m, wdir));       // mat4::applyRay
+            org = tr.org; dir = tr.dir; ri = ray_inv(org, dir);
+            list = reinterpret_cast<const float4*>(rv.nodes + rv.offsets[exid]);
+            entered = true;
+        }
+        else if (phase == PH_TRIANGLE) {
+            mtrlid = __float_as_int(v1.z); tri_mesh = __float_as_int(v1.w);
+            phase = PH_POSITIONS;
+            a0 = reinterpret_cast<const float4*>(rv.positions + __float_as_int(v0.x));
+            a1 = reinterpret_cast<const float4*>(rv.positions + __float_as_int(v0.y));
+            a2 = reinterpret_cast<const float4*>(rv.positions + __float_as_int(v0.z));
+        }
+        else {                                                          // PH_POSITIONS: triangle::hit (triangle.h:40-67)
+            const TriHit h = intersect_triangle(org, dir, V3(v0.x, v0.y, v0.z), V3(v1.x, v1.y, v1.z), V3(v2.x, v2.y, v2.z));
+            is_hit = h.hit && h.t < kInf;
+            decided = true;
+            const float tt = is_hit ? h.t : kInf;
+            if (rv.t_min < tt && is_hit && tt < isect.t) {
+                isect.t = h.t; isect.a = h.a; isect.b = h.b;
+                isect.objid = objid; isect.primid = primid; isect.mtrlid = mtrlid;
+                isect.meshid = tri_mesh < 0 ? meshid : tri_mesh;
+                t_max = isect.t;
+            }
+        }
+        if (decided || entered) {
+            int32_t next = entered ? 0 : (is_hit ? link_hit : link_miss);
+            if (next < 0) {                                             // end of a list (threaded_bvh_traverser.h:290-300)
+                next = is_hit ? top_hit : top_miss;                     // both -1 while in the top layer: the walk ends
+                top_hit = -1; top_miss = -1;
+                list = top; org = worg; dir = wdir; ri = ray_inv(org, dir);
+                if (next < 0) break;
+            }
+            phase = PH_NODE;
+            a0 = list + (size_t)next * 3; a1 = a0 + 1; a2 = a0 + 2;
+        }
+    }
+    return isect;
+}
+
+template <class Policy>
+__global__ void __launch_bounds__(128)
+k_exact(RefView rv, Policy pol, const int32_t* __restrict__ exact_q, const int32_t* __restrict__ exact_count)
+{
+#ifdef ATN_EXP_EXACT_NOOP
+    const int count = 0;      // timing experiment: what the exact walk costs beyond its own work
+#else
+    const int count = *exact_count;
+#endif
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const int slot = exact_q[i];
+        V3 o, d;
+        pol.world(slot, &o, &d);
+        pol.finish_hit(slot, ref_traverse(rv, o, d, pol.t_max(slot)));
     }
 }
 
@@ -815,6 +1108,7 @@ __global__ void k_generate(FrameParams fp, AtnCameraParameter cam, const uint32_
         pb.contrib[s] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
         pb.sampler_dim[s] = sp.dim;
         pb.flags[s] = 0u;
+        pb.pend[s] = 0;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) cnt->n_active[0] = n;
 }
@@ -849,6 +1143,15 @@ constexpr int kShadeBlock = 128;
 #define ATN_MAX_BATCH 16
 #endif
 
+// Which paths a shade kernel works on.  The main pass of a bounce takes the bounce's trace queue and fills q_lit; the side
+// pass takes the paths the exact walk has just decided (q_exact) and fills its own lit queue.  Both append to the same
+// next-bounce and shadow queues.
+struct ShadeQueues {
+    const int32_t* q_in;  const int32_t* n_in;     // paths of the surface stage (q_in == nullptr: path i = slot i)
+    int32_t* q_lit;       int32_t* n_lit;          // survivors of the surface stage = the paths of the NEE / BSDF stages
+    int32_t skip_tag;                              // main pass next to a side pass: paths with pend == skip_tag are the side pass's
+};
+
 __device__ __forceinline__ Sampler path_sampler(const FrameParams& fp, const uint32_t* seeds, const PathBuffers& pb, int slot)
 {
     const SlotInfo si = slot_info(fp, slot);
@@ -866,11 +1169,11 @@ __device__ __forceinline__ Sampler path_sampler(const FrameParams& fp, const uin
 // world-to-clip matrix of the frame and pb.aov_nd / pb.aov_am point at the current SVGF AOV set.
 template <bool kTap, bool kSvgf>
 __global__ void __launch_bounds__(kShadeBlock, ATN_SURFACE_MIN_BLOCKS)
-k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, Counters* cnt, int bounce,
+k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, ShadeQueues sq, int bounce,
           AtnBounceRecord* tap, int tap_cap, AtnMat4 w2c)
 {
-    const int count = cnt->n_active[bounce];
-    const int32_t* __restrict__ q_in = (bounce == 0) ? nullptr : pb.queue[bounce & 1];
+    const int count = *sq.n_in;
+    const int32_t* __restrict__ q_in = sq.q_in;
     const int rounds = (count + blockDim.x * gridDim.x - 1) / (blockDim.x * gridDim.x);
     for (int it = 0; it < rounds; it++) {
         const int i = (it * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
@@ -885,6 +1188,7 @@ k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, 
             const float4 th = pb.throughput[slot];
             const float4 cb = pb.contrib[slot];
             const uint32_t fl = pb.flags[slot];
+            const bool pending = sq.skip_tag != 0 && pb.pend[slot] == sq.skip_tag;     // its hit comes from the exact walk: shaded by the side pass
             Ray ray; ray.org = V3(o.x, o.y, o.z); ray.dir = V3(d.x, d.y, d.z);
             PathState st;
             st.throughput = V3(th.x, th.y, th.z); st.pdfb = th.w;
@@ -899,7 +1203,8 @@ k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, 
             const bool aov = bounce <= 1 && si.k == fp.batch - 1;
             AtnVec4* aov_nd = aov ? reinterpret_cast<AtnVec4*>(pb.aov_nd) + pix : nullptr;
             AtnVec4* aov_am = aov ? reinterpret_cast<AtnVec4*>(pb.aov_am) + pix : nullptr;
-            if (h1.x >= 0) {
+            if (pending) {}
+            else if (h1.x >= 0) {
                 Surface sf;
                 lit = shade_surface(sc, ray, h1.x, __float_as_int(h0.w), h0.y, h0.z, h0.x, h1.y, bounce, &st, &sf,
                                     aov_nd, aov_am, bounce == 0 ? pb.hit_mesh[slot] : -1, kSvgf ? &w2c : nullptr);
@@ -912,11 +1217,11 @@ k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, 
             else {
                 shade_miss(sc, cam, si.ix, si.iy, fp.width, fp.height, bounce, ray, &st, aov_nd, aov_am);
             }
-            if (!lit) {
+            if (!lit && !pending) {
                 pb.contrib[slot] = make_float4(st.contrib.x, st.contrib.y, st.contrib.z, cb.w);
                 pb.flags[slot] = 1u | (st.singular ? 2u : 0u);
             }
-            if (kTap) {
+            if (kTap && !pending) {
                 AtnBounceRecord& rec = tap[(size_t)slot * tap_cap + bounce];
                 rec.ray.org = AtnVec3{ o.x, o.y, o.z };
                 rec.ray.dir = AtnVec3{ d.x, d.y, d.z };
@@ -928,19 +1233,19 @@ k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, 
                 rec.flags = 1 | (lit ? 0 : 2);
             }
         }
-        const int pos = warp_append(lit, &cnt->n_lit[bounce]);
-        if (lit) pb.q_lit[pos] = slot;
+        const int pos = warp_append(lit, sq.n_lit);
+        if (lit) sq.q_lit[pos] = slot;
     }
 }
 
 // Stage 2, lit paths: light pick + light sample + NEE evaluation (FillShadowRay).  The shadow-ray
 // candidate is stored per slot; stage 3 decides whether it is traced.
 __global__ void __launch_bounds__(kShadeBlock, ATN_NEE_MIN_BLOCKS)
-k_nee(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb, Counters* cnt, int bounce)
+k_nee(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb, ShadeQueues sq, int bounce)
 {
-    const int count = cnt->n_lit[bounce];
+    const int count = *sq.n_lit;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-        const int slot = pb.q_lit[i];
+        const int slot = sq.q_lit[i];
         const float4 d = pb.ray_d[slot];
         const float4 s0 = pb.surf0[slot];
         const float4 s1 = pb.surf1[slot];
@@ -968,10 +1273,10 @@ k_nee(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuff
 // shadow ray (HitShadowRay drops the shadow ray of a path that terminated here).
 template <bool kTap>
 __global__ void __launch_bounds__(kShadeBlock, ATN_BSDF_MIN_BLOCKS)
-k_bsdf(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb, Counters* cnt, int bounce,
+k_bsdf(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb, Counters* cnt, ShadeQueues sq, int bounce,
        AtnBounceRecord* tap, int tap_cap)
 {
-    const int count = cnt->n_lit[bounce];
+    const int count = *sq.n_lit;
     int32_t* __restrict__ q_out = pb.queue[(bounce + 1) & 1];
     const int rounds = (count + blockDim.x * gridDim.x - 1) / (blockDim.x * gridDim.x);
     for (int it = 0; it < rounds; it++) {
@@ -979,7 +1284,7 @@ k_bsdf(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuf
         bool cont = false, shadow = false;
         int slot = 0;
         if (i < count) {
-            slot = pb.q_lit[i];
+            slot = sq.q_lit[i];
             const float4 d = pb.ray_d[slot];
             const float4 s0 = pb.surf0[slot];
             const float4 s1 = pb.surf1[slot];
@@ -1133,8 +1438,12 @@ __global__ void k_svgf_prepare(FrameParams fp, PathBuffers pb, SvgfView sv, int 
     const int n = fp.width * fp.height;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         unsigned long long c = 0, s = 0;
-        for (int b = 0; b < fp.max_bounce; b++) { c += (unsigned long long)cnt->n_active[b]; s += (unsigned long long)cnt->n_shadow[b]; }
-        totals->closest += c; totals->shadow += s;
+        unsigned long long e = 0;
+        for (int b = 0; b < fp.max_bounce; b++) {
+            c += (unsigned long long)cnt->n_active[b]; s += (unsigned long long)cnt->n_shadow[b];
+            e += (unsigned long long)cnt->n_exact_closest[b] + (unsigned long long)cnt->n_exact_shadow[b];
+        }
+        totals->closest += c; totals->shadow += s; totals->exact += e;
     }
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const float4 c = pb.contrib[i];
@@ -1331,22 +1640,22 @@ k_restir_visibility(FrameParams fp, PathBuffers pb, RestirView rv, Counters* cnt
 // the shadow traversal of that step: ShadowPolicy's decision (HitShadowRay adds the buffered lightcontrib when the
 // light is reached) + the second half of EvaluateVisibility
 struct RestirShadowPolicy {
+    static constexpr bool kNeedClass = true;
     ShadowPolicy<false> base;
     Reservoir* res;
     __device__ __forceinline__ void world(int slot, V3* o, V3* d) const { base.world(slot, o, d); }
+    __device__ __forceinline__ float t_max(int slot) const { return base.t_max(slot); }
     __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* t_max, int* mode, float* exit_dist) const
     {
         base.load(i, slot, o, d, t_max, mode, exit_dist);
     }
-    __device__ __forceinline__ void finish(const BvhView& bv, int slot, const TraceResult& r) const
+    __device__ __forceinline__ void finish_hit(int slot, const AtnHit& h) const
     {
         const float4 so = base.pb.sh_o[slot];
         const float4 sd = base.pb.sh_d[slot];
         const AtnLightParameter& light = base.sc.lights[__float_as_int(sd.w)];
         Ray sr; sr.org = V3(so.x, so.y, so.z); sr.dir = normalize(V3(sd.x, sd.y, sd.z));
-        int32_t objid, primid, mtrlid, meshid;
-        resolve_hit(bv, r, &objid, &primid, &mtrlid, &meshid);
-        const bool vis = shadow_visible(base.sc, light, sr, so.w, objid, primid, r.a, r.b, r.t, mtrlid);
+        const bool vis = shadow_visible(base.sc, light, sr, so.w, h.objid, h.primid, h.a, h.b, h.t, h.mtrlid);
         if (vis) {
             const float4 c = base.pb.sh_c[slot];
             float4 cc = base.pb.contrib[slot];
@@ -1354,6 +1663,13 @@ struct RestirShadowPolicy {
             base.pb.contrib[slot] = cc;
         }
         restir_visibility_result(&res[slot], vis);
+    }
+    __device__ __forceinline__ bool finish(const BvhView& bv, int slot, const TraceResult& r, const Tie& tie) const
+    {
+        const AtnHit h = resolved(bv, r);
+        if (tie.any && shadow_tie_matters(base.sc, base.sc.lights[__float_as_int(base.pb.sh_d[slot].w)], base.pb.sh_o[slot].w, h, tie)) return false;
+        finish_hit(slot, h);
+        return true;
     }
 };
 
@@ -1413,8 +1729,12 @@ __global__ void k_gather(FrameParams fp, PathBuffers pb, float4* image, int mode
     const int n = fp.rw * fp.rh;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         unsigned long long c = 0, s = 0;
-        for (int b = 0; b < fp.max_bounce; b++) { c += (unsigned long long)cnt->n_active[b]; s += (unsigned long long)cnt->n_shadow[b]; }
-        totals->closest += c; totals->shadow += s;
+        unsigned long long e = 0;
+        for (int b = 0; b < fp.max_bounce; b++) {
+            c += (unsigned long long)cnt->n_active[b]; s += (unsigned long long)cnt->n_shadow[b];
+            e += (unsigned long long)cnt->n_exact_closest[b] + (unsigned long long)cnt->n_exact_shadow[b];
+        }
+        totals->closest += c; totals->shadow += s; totals->exact += e;
     }
     for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < n; s += gridDim.x * blockDim.x) {
         const int ix = fp.x0 + s % fp.rw;
@@ -1487,6 +1807,19 @@ struct AtnRenderer {
     DevBuf<QuadNode> nodes;
     DevBuf<TriLeaf> tris;
     DevBuf<InstLeafW> insts;
+    // the reference's node lists as uploaded (exact walk of near ties): bottom lists first, list 0 behind them with room to grow
+    DevBuf<AtnBvhNode> ref_nodes;
+    DevBuf<uint32_t> ref_offsets;
+    std::vector<uint32_t> h_ref_offsets;
+    size_t ref_bottom_count{ 0 };      // nodes of lists 1.. (list 0 starts there)
+    RefView rv{};
+    int exact_ties{ 1 };               // 0: near ties are left as the front-to-back walk found them (atn_set_exact_ties)
+    int exact_grid{ 148 * 4 };
+    DevBuf<int32_t> q_exact, q_exact_s, q_lit_side, q_exact_query;
+    // The exact walk is a latency-bound tail (a few thousand rays, hundreds of dependent steps each).  In the bounce loop it
+    // runs on a second stream next to the main kernels instead of between them (launch_bounces).
+    cudaStream_t side_stream{ nullptr };
+    std::vector<cudaEvent_t> side_events;
     DevBuf<uint32_t> seeds;
     uint32_t seed_count{ 0 };
     SceneView sv{};
@@ -1504,6 +1837,7 @@ struct AtnRenderer {
     DevBuf<int2> hit1;
     DevBuf<uint32_t> sampler_dim, flags;
     DevBuf<int32_t> hit_mesh;
+    DevBuf<uint8_t> pend;
     DevBuf<float4> aov_nd, aov_am;
     DevBuf<int32_t> queue0, queue1, q_lit, q_shadow;
     DevBuf<float4> surf0, surf1, surf2;
@@ -1560,19 +1894,30 @@ struct AtnRenderer {
     int surface_grid{ 148 * 8 }, nee_grid{ 148 * 8 }, bsdf_grid{ 148 * 8 };
 };
 
-// One traversal launch: the instantiation whose stack covers the scene's worst case (upload_bvh checked that one does).
+// One traversal launch: the instantiation whose stack covers the scene's worst case (upload_bvh checked that one does),
+// followed by the exact walk of the rays it could not decide (a few thousand of millions; nothing when exact ties are off).
+// `exact_count` is a zeroed device counter of this launch, `exact_q` room for as many slots as the launch has rays.
 template <class Policy>
-static void launch_trace(AtnRenderer* r, cudaStream_t s, Policy pol, const int32_t* count_ptr, int count_imm, int32_t* fetch, Visits* visits)
+static void launch_exact(AtnRenderer* r, cudaStream_t s, Policy pol, const int32_t* exact_q, const int32_t* exact_count)
+{
+    k_exact<Policy><<<r->exact_grid, 128, 0, s>>>(r->rv, pol, exact_q, exact_count);
+}
+
+template <class Policy>
+static void launch_trace(AtnRenderer* r, cudaStream_t s, Policy pol, const int32_t* count_ptr, int count_imm, int32_t* fetch, Visits* visits,
+                         int32_t* exact_q, int32_t* exact_count, bool exact_here = true)
 {
     const bool small = r->stack_need <= kSmemStack + kLocalStackSmall;
+    if (!r->exact_ties) { exact_q = nullptr; exact_count = nullptr; }
     if (r->stream_loads) {
-        if (small) k_trace<Policy, kLocalStackSmall, true><<<r->trace_grid_stream, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
-        else k_trace<Policy, kLocalStackLarge, true><<<r->trace_grid_stream, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
+        if (small) k_trace<Policy, kLocalStackSmall, true><<<r->trace_grid_stream, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits, exact_q, exact_count);
+        else k_trace<Policy, kLocalStackLarge, true><<<r->trace_grid_stream, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits, exact_q, exact_count);
     }
     else {
-        if (small) k_trace<Policy, kLocalStackSmall, false><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
-        else k_trace<Policy, kLocalStackLarge, false><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits);
+        if (small) k_trace<Policy, kLocalStackSmall, false><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits, exact_q, exact_count);
+        else k_trace<Policy, kLocalStackLarge, false><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits, exact_q, exact_count);
     }
+    if (exact_q && exact_here) launch_exact<Policy>(r, s, pol, exact_q, exact_count);
 }
 
 // (Re)binds what depends on the node array and the top layer: the linear node texture of the default kernel form, the
@@ -1603,8 +1948,57 @@ static int bind_top_layer(AtnRenderer* r, size_t node_count, const std::vector<I
     return ATN_OK;
 }
 
+// The reference's node lists as they are, for k_exact: bottom lists (1..) first, list 0 behind them with room to grow
+// (a top-layer update replaces list 0 only).
+static int bind_ref_lists(AtnRenderer* r)
+{
+    RefView& rv = r->rv;
+    rv.nodes = r->ref_nodes.p; rv.offsets = r->ref_offsets.p;
+    rv.objects = r->objects.p; rv.matrices = r->matrices.p; rv.triangles = r->triangles.p; rv.positions = r->positions.p;
+    rv.t_min = r->bv.t_min;
+    return ATN_OK;
+}
+
+static int upload_ref_top(AtnRenderer* r, const AtnBvhNode* top, uint32_t count)
+{
+    const size_t need = r->ref_bottom_count + count;
+    if (need > r->ref_nodes.n) {
+        DevBuf<AtnBvhNode> grown;
+        CUDA_TRY(grown.resize(need + count + 64));
+        if (r->ref_bottom_count)
+            CUDA_TRY(cudaMemcpyAsync(grown.p, r->ref_nodes.p, r->ref_bottom_count * sizeof(AtnBvhNode), cudaMemcpyDeviceToDevice, r->stream));
+        CUDA_TRY(cudaStreamSynchronize(r->stream));
+        std::swap(grown.p, r->ref_nodes.p); std::swap(grown.n, r->ref_nodes.n);
+    }
+    if (count) CUDA_TRY(cudaMemcpyAsync(r->ref_nodes.p + r->ref_bottom_count, top, count * sizeof(AtnBvhNode), cudaMemcpyHostToDevice, r->stream));
+    return bind_ref_lists(r);
+}
+
+static int upload_ref_lists(AtnRenderer* r, const AtnSceneBlob* scene)
+{
+    const uint32_t nl = scene->node_list_count;
+    r->h_ref_offsets.assign(nl, 0u);
+    size_t total = 0;
+    for (uint32_t k = 1; k < nl; k++) { r->h_ref_offsets[k] = (uint32_t)total; total += scene->node_list_sizes[k]; }
+    if (total + scene->node_list_sizes[0] >= ((size_t)1 << 32)) return set_error(ATN_ERR_TOO_LARGE, "node lists: more than 2^32 nodes");
+    r->h_ref_offsets[0] = (uint32_t)total;
+    r->ref_bottom_count = total;
+    r->ref_nodes.release();
+    CUDA_TRY(r->ref_nodes.resize(total + 2 * (size_t)scene->node_list_sizes[0] + 64));
+    for (uint32_t k = 1; k < nl; k++)
+        if (scene->node_list_sizes[k])
+            CUDA_TRY(cudaMemcpyAsync(r->ref_nodes.p + r->h_ref_offsets[k], scene->node_lists[k], (size_t)scene->node_list_sizes[k] * sizeof(AtnBvhNode),
+                                     cudaMemcpyHostToDevice, r->stream));
+    CUDA_TRY(r->ref_offsets.upload(r->h_ref_offsets.data(), nl, r->stream));
+    return upload_ref_top(r, scene->node_lists[0], scene->node_list_sizes[0]);
+}
+
 static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene)
 {
+    {
+        const int rc = upload_ref_lists(r, scene);
+        if (rc != ATN_OK) return rc;
+    }
     WideBvh enc = encode_wide(scene, &r->bottom);
     if (!enc.error.empty()) return set_error(ATN_ERR_INVALID_ARGUMENT, "node lists: %s", enc.error.c_str());
     {
@@ -1648,7 +2042,8 @@ static int alloc_paths(AtnRenderer* r, size_t n, size_t pixels)
     CUDA_TRY(r->flags.resize(n)); CUDA_TRY(r->queue0.resize(n)); CUDA_TRY(r->queue1.resize(n));
     CUDA_TRY(r->sh_o.resize(n)); CUDA_TRY(r->sh_d.resize(n)); CUDA_TRY(r->sh_c.resize(n));
     CUDA_TRY(cudaMemsetAsync(r->sh_c.p, 0, n * sizeof(float4), r->stream));      // ShadowRay::lightcontrib starts at zero
-    CUDA_TRY(r->q_lit.resize(n)); CUDA_TRY(r->q_shadow.resize(n));
+    CUDA_TRY(r->q_lit.resize(n)); CUDA_TRY(r->q_shadow.resize(n)); CUDA_TRY(r->q_exact.resize(n));
+    CUDA_TRY(r->q_exact_s.resize(n)); CUDA_TRY(r->q_lit_side.resize(n)); CUDA_TRY(r->pend.resize(n));
     CUDA_TRY(r->hit_mesh.resize(n)); CUDA_TRY(r->aov_nd.resize(pixels)); CUDA_TRY(r->aov_am.resize(pixels));    // AOVs are per pixel
     CUDA_TRY(r->surf0.resize(n)); CUDA_TRY(r->surf1.resize(n)); CUDA_TRY(r->surf2.resize(n));
     CUDA_TRY(r->counters.resize(1));
@@ -1659,7 +2054,7 @@ static int alloc_paths(AtnRenderer* r, size_t n, size_t pixels)
     pb.throughput = r->throughput.p; pb.contrib = r->contrib.p; pb.sampler_dim = r->sampler_dim.p; pb.flags = r->flags.p;
     pb.queue[0] = r->queue0.p; pb.queue[1] = r->queue1.p;
     pb.sh_o = r->sh_o.p; pb.sh_d = r->sh_d.p; pb.sh_c = r->sh_c.p;
-    pb.q_lit = r->q_lit.p; pb.q_shadow = r->q_shadow.p;
+    pb.q_lit = r->q_lit.p; pb.q_shadow = r->q_shadow.p; pb.q_exact = r->q_exact.p; pb.q_exact_s = r->q_exact_s.p; pb.q_lit_side = r->q_lit_side.p; pb.pend = r->pend.p;
     pb.hit_mesh = r->hit_mesh.p; pb.aov_nd = r->aov_nd.p; pb.aov_am = r->aov_am.p;
     pb.surf0 = r->surf0.p; pb.surf1 = r->surf1.p; pb.surf2 = r->surf2.p;
     return ATN_OK;
@@ -1674,6 +2069,11 @@ static int init_renderer(AtnRenderer* r)
     CUDA_TRY(cudaGetDeviceProperties(&prop, r->device));
     r->sm_count = prop.multiProcessorCount;
     CUDA_TRY(cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking));
+    {
+        int lo = 0, hi = 0;
+        CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CUDA_TRY(cudaStreamCreateWithPriority(&r->side_stream, cudaStreamNonBlocking, hi));     // its few blocks go first when an SM frees up
+    }
     CUDA_TRY(cudaEventCreate(&r->ev0));
     CUDA_TRY(cudaEventCreate(&r->ev1));
     CUDA_TRY(cudaEventCreateWithFlags(&r->ev_done, cudaEventDisableTiming));
@@ -1691,6 +2091,8 @@ static int init_renderer(AtnRenderer* r)
     r->nee_grid = r->sm_count * std::max(1, bps);
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_bsdf<false>, kShadeBlock, 0));
     r->bsdf_grid = r->sm_count * std::max(1, bps);
+    r->exact_grid = r->sm_count * 4;
+    if (const char* ov = getenv("ATEN_B200_EXACT_TIES")) r->exact_ties = (ov[0] != '0');     // experiments: cost of the exact walk
     return ATN_OK;
 }
 
@@ -1702,7 +2104,7 @@ static int end_call(AtnRenderer* r, AtnRenderer::Pending kind, uint64_t launches
     CUDA_TRY(cudaGetLastError());
     if (kind != AtnRenderer::PEND_QUERY) CUDA_TRY(cudaMemcpyAsync(&r->h_stats->totals, r->totals.p, sizeof(Totals), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaMemcpyAsync(&r->h_stats->visits, r->visits.p, sizeof(Visits), cudaMemcpyDeviceToHost, s));
-    if (kind == AtnRenderer::PEND_AO) CUDA_TRY(cudaMemcpyAsync(&r->h_stats->counters, r->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, s));
+    if (kind != AtnRenderer::PEND_RENDER) CUDA_TRY(cudaMemcpyAsync(&r->h_stats->counters, r->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, s));
     CUDA_TRY(cudaEventRecord(r->ev_done, s));
     r->stats.kernel_launches = launches;
     r->stats.camera_samples = samples;
@@ -1724,9 +2126,10 @@ static int collect_stats(AtnRenderer* r)
     r->stats.device_ms = ms;
     r->stats.nodes_visited = r->h_stats->visits.nodes;
     r->stats.tris_tested = r->h_stats->visits.tris;
-    if (kind == AtnRenderer::PEND_QUERY) { r->stats.trace_ms = ms; return ATN_OK; }
+    if (kind == AtnRenderer::PEND_QUERY) { r->stats.trace_ms = ms; r->stats.exact_rays = (uint64_t)r->h_stats->counters.n_exact_query; return ATN_OK; }
     r->stats.closest_rays = r->h_stats->totals.closest;
     r->stats.shadow_rays = r->h_stats->totals.shadow;
+    r->stats.exact_rays = r->h_stats->totals.exact;
     if (kind == AtnRenderer::PEND_AO)      // AO rays = lit paths (last sample's count) x rays per path x samples
         r->stats.shadow_rays = (uint64_t)r->h_stats->counters.n_lit[0] * r->pend_ao_factor;
     r->stats.trace_ms = 0.0f;
@@ -1774,6 +2177,8 @@ ATN_API int atn_destroy(AtnRenderer* r)
     if (r->ev0) cudaEventDestroy(r->ev0);
     if (r->ev1) cudaEventDestroy(r->ev1);
     if (r->ev_done) cudaEventDestroy(r->ev_done);
+    for (auto ev : r->side_events) cudaEventDestroy(ev);
+    if (r->side_stream) { cudaStreamSynchronize(r->side_stream); cudaStreamDestroy(r->side_stream); }
     if (r->h_stats) cudaFreeHost(r->h_stats);
     if (r->bv.node_tex) cudaDestroyTextureObject(r->bv.node_tex);
     if (r->svgf_tex) cudaDestroyTextureObject(r->svgf_tex);
@@ -1887,6 +2292,10 @@ ATN_API int atn_update_top_layer(AtnRenderer* r, const AtnBvhNode* top_nodes, ui
     CUDA_TRY(r->objects.upload(objects, object_count, r->stream));
     CUDA_TRY(r->matrices.upload(matrices, matrix_count, r->stream));
     r->sv.objects = r->objects.p; r->sv.matrices = r->matrices.p;
+    {
+        const int rc = upload_ref_top(r, top_nodes, node_count);
+        if (rc != ATN_OK) return rc;
+    }
     if (!top.nodes.empty())
         CUDA_TRY(cudaMemcpyAsync(r->nodes.p + bottom_nodes, top.nodes.data(), top.nodes.size() * sizeof(QuadNode), cudaMemcpyHostToDevice, r->stream));
     return bind_top_layer(r, total, top.insts, top.top_root, top.max_stack);
@@ -1937,6 +2346,7 @@ ATN_API int atn_update_config(AtnRenderer* r, const AtnSceneConfig* cfg)
     r->sv.cfg = *cfg;
     r->sv.scene_radius = scene_radius_of(*cfg);
     r->bv.t_min = cfg->bvh_hit_min > 0 ? cfg->bvh_hit_min : kEps;
+    r->rv.t_min = r->bv.t_min;
     return ATN_OK;
 }
 
@@ -1962,6 +2372,7 @@ ATN_API int atn_set_gather_mode(AtnRenderer* r, int mode)
     r->gather_mode = mode;
     return ATN_OK;
 }
+ATN_API int atn_set_exact_ties(AtnRenderer* r, int enable) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->exact_ties = enable ? 1 : 0; return ATN_OK; }
 ATN_API int atn_set_hit_distance_limit(AtnRenderer* r, float d) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->hit_distance_limit = fminf(d, kInf); return ATN_OK; }
 ATN_API int atn_set_profiling(AtnRenderer* r, int enable) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->profiling = enable ? 1 : 0; return ATN_OK; }
 ATN_API int atn_get_stream(AtnRenderer* r, void** stream) { if (!r || !stream) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); *stream = (void*)r->stream; return ATN_OK; }
@@ -1995,40 +2406,94 @@ ATN_API int atn_synchronize(AtnRenderer* r)
 
 // The bounce loop of one camera sample: closest hit, the three shade stages, shadow rays.
 // `svgf_w2c` != nullptr: the SVGF shade variant (pb.aov_nd / pb.aov_am then point at the SVGF AOV set).
+//
+// Where the exact walk goes.  k_exact is a tail of a few thousand rays with hundreds of dependent steps each: 0.1 - 0.4 ms in
+// which it keeps a tenth of the SMs' warp slots busy.  Run between the main kernels it costs that time twice per bounce (9 %
+// of a frame); so it runs NEXT to them, on a second stream:
+//
+//   main:  trace closest b | surface  nee  bsdf (paths with a decided hit) | trace shadow b | trace closest b+1 | surface b+1 ...
+//   side:                  | exact closest b, surface' nee' bsdf' (its paths) |              | exact shadow b    |
+//
+// A path whose closest hit is with the exact walk is marked (kHitPending), left alone by the main shade kernels and shaded
+// by the side pass -- the same kernels over the exact queue -- which appends to the same next-bounce and shadow queues; the
+// main stream waits for the side pass before it traces the shadow rays.  The shadow rays of the exact walk only add to
+// their own paths' contributions: they are done next to the next bounce's closest-hit traversal, before its shade stage.
+// With the bounce tap on (parity runs) everything stays on one stream.
+static cudaEvent_t side_event(AtnRenderer* r, size_t i)
+{
+    while (r->side_events.size() <= i) {
+        cudaEvent_t ev = nullptr;
+        if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        r->side_events.push_back(ev);
+    }
+    return r->side_events[i];
+}
+
 static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffers& pb, bool tap_now, const AtnMat4* svgf_w2c,
                           size_t* ev_i, uint64_t* launches, int first_bounce = 0)
 {
-    cudaStream_t s = r->stream;
+    cudaStream_t s = r->stream, side = r->side_stream;
     AtnMat4 w2c;
     for (int i = 0; i < 16; i++) w2c.m[i] = svgf_w2c ? svgf_w2c->m[i] : 0.0f;
+    const bool overlap = r->exact_ties && !tap_now;
+    const int side_grid = r->sm_count * 2;
+    size_t se = 0;
+    cudaEvent_t shadow_done = nullptr;            // side stream: the exact walk of the previous bounce's shadow rays
     for (int b = first_bounce; b < fp.max_bounce; b++) {
         Counters* c = r->counters.p;
         const int32_t* q = (b == 0) ? nullptr : pb.queue[b & 1];
         const float tmax = (b == 0) ? kInf : r->hit_distance_limit;
+        const ShadeQueues mainq{ q, &c->n_active[b], pb.q_lit, &c->n_lit[b], overlap ? b + 1 : 0 };
+        const ShadeQueues sideq{ pb.q_exact, &c->n_exact_closest[b], pb.q_lit_side, &c->n_lit_side[b], 0 };
         if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
-        {
-            ClosestPolicy pol{ pb, q, tmax, b == 0 ? pb.hit_mesh : nullptr };
-            launch_trace<ClosestPolicy>(r, s, pol, &c->n_active[b], 0, &c->fetch_closest[b], r->visits.p);
+        ClosestPolicy cpol{ pb, q, tmax, b == 0 ? pb.hit_mesh : nullptr, (uint8_t)(overlap ? b + 1 : 0) };
+        launch_trace<ClosestPolicy>(r, s, cpol, &c->n_active[b], 0, &c->fetch_closest[b], r->visits.p, pb.q_exact, &c->n_exact_closest[b], !overlap);
+        if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
+        cudaEvent_t side_done = nullptr;
+        if (overlap) {
+            cudaEvent_t traced = side_event(r, se++); side_done = side_event(r, se++);
+            if (!traced || !side_done) return set_error(ATN_ERR_CUDA, "cudaEventCreate failed");
+            CUDA_TRY(cudaEventRecord(traced, s));
+            CUDA_TRY(cudaStreamWaitEvent(side, traced, 0));
+            launch_exact<ClosestPolicy>(r, side, cpol, pb.q_exact, &c->n_exact_closest[b]);
+            if (svgf_w2c) k_surface<false, true><<<side_grid, kShadeBlock, 0, side>>>(fp, r->camera, r->sv, pb, sideq, b, nullptr, 0, w2c);
+            else k_surface<false, false><<<side_grid, kShadeBlock, 0, side>>>(fp, r->camera, r->sv, pb, sideq, b, nullptr, 0, w2c);
+            k_nee<<<side_grid, kShadeBlock, 0, side>>>(fp, r->sv, r->seeds.p, pb, sideq, b);
+            k_bsdf<false><<<side_grid, kShadeBlock, 0, side>>>(fp, r->sv, r->seeds.p, pb, c, sideq, b, nullptr, 0);
+            CUDA_TRY(cudaEventRecord(side_done, side));
+            *launches += 4;
+            // the main shade stage touches the contributions: the previous bounce's exact shadow rays must have landed
+            if (shadow_done) { CUDA_TRY(cudaStreamWaitEvent(s, shadow_done, 0)); shadow_done = nullptr; }
         }
-        if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
-        if (svgf_w2c) k_surface<false, true><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, pb, c, b, nullptr, 0, w2c);
-        else if (tap_now) k_surface<true, false><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, pb, c, b, r->tap_dev.p, r->tap_cap, w2c);
-        else k_surface<false, false><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, pb, c, b, nullptr, 0, w2c);
-        k_nee<<<r->nee_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, b);
-        if (tap_now) k_bsdf<true><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, b, r->tap_dev.p, r->tap_cap);
-        else k_bsdf<false><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, b, nullptr, 0);
+        if (svgf_w2c) k_surface<false, true><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, pb, mainq, b, nullptr, 0, w2c);
+        else if (tap_now) k_surface<true, false><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, pb, mainq, b, r->tap_dev.p, r->tap_cap, w2c);
+        else k_surface<false, false><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, pb, mainq, b, nullptr, 0, w2c);
+        k_nee<<<r->nee_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, mainq, b);
+        if (tap_now) k_bsdf<true><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, mainq, b, r->tap_dev.p, r->tap_cap);
+        else k_bsdf<false><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, mainq, b, nullptr, 0);
+        if (side_done) CUDA_TRY(cudaStreamWaitEvent(s, side_done, 0));       // the shadow and next-bounce queues are complete
         if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
         if (tap_now) {
             ShadowPolicy<true> pol{ pb, r->sv, r->tap_dev.p, r->tap_cap, b };
-            launch_trace<ShadowPolicy<true>>(r, s, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
+            launch_trace<ShadowPolicy<true>>(r, s, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p, pb.q_exact_s, &c->n_exact_shadow[b]);
         }
         else {
             ShadowPolicy<false> pol{ pb, r->sv, nullptr, 0, b };
-            launch_trace<ShadowPolicy<false>>(r, s, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p);
+            launch_trace<ShadowPolicy<false>>(r, s, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p, pb.q_exact_s, &c->n_exact_shadow[b], !overlap);
+            if (overlap) {
+                cudaEvent_t traced = side_event(r, se++); shadow_done = side_event(r, se++);
+                if (!traced || !shadow_done) return set_error(ATN_ERR_CUDA, "cudaEventCreate failed");
+                CUDA_TRY(cudaEventRecord(traced, s));
+                CUDA_TRY(cudaStreamWaitEvent(side, traced, 0));
+                launch_exact<ShadowPolicy<false>>(r, side, pol, pb.q_exact_s, &c->n_exact_shadow[b]);
+                CUDA_TRY(cudaEventRecord(shadow_done, side));
+                *launches += 1;
+            }
         }
         if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
-        *launches += 5;
+        *launches += 5 + (r->exact_ties && !overlap ? 2 : 0);
     }
+    if (shadow_done) CUDA_TRY(cudaStreamWaitEvent(s, shadow_done, 0));       // the gather reads every contribution
     return ATN_OK;
 }
 
@@ -2123,16 +2588,17 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
         CUDA_TRY(cudaMemsetAsync(c, 0, sizeof(Counters), s));
         k_generate<<<grid, 256, 0, s>>>(fp, r->camera, r->seeds.p, r->pb, c);
         {
-            ClosestPolicy pol{ r->pb, nullptr, kInf, nullptr };
-            launch_trace<ClosestPolicy>(r, s, pol, &c->n_active[0], 0, &c->fetch_closest[0], r->visits.p);
+            ClosestPolicy pol{ r->pb, nullptr, kInf, nullptr, 0 };
+            launch_trace<ClosestPolicy>(r, s, pol, &c->n_active[0], 0, &c->fetch_closest[0], r->visits.p, r->pb.q_exact, &c->n_exact_closest[0]);
         }
         k_ao_begin<<<sgrid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, r->pb, c);
         launches += 3;
         for (int i = 0; i < num_rays; i++) {
             k_ao_ray<<<sgrid, kShadeBlock, 0, s>>>(fp, r->seeds.p, r->pb, c);
             CUDA_TRY(cudaMemsetAsync(&c->fetch_query, 0, sizeof(int32_t), s));
-            ClosestPolicy pol{ r->pb, r->pb.q_lit, radius, nullptr };
-            launch_trace<ClosestPolicy>(r, s, pol, &c->n_lit[0], 0, &c->fetch_query, r->visits.p);
+            CUDA_TRY(cudaMemsetAsync(&c->n_exact_query, 0, sizeof(int32_t), s));
+            ClosestPolicy pol{ r->pb, r->pb.q_lit, radius, nullptr, 0 };
+            launch_trace<ClosestPolicy>(r, s, pol, &c->n_lit[0], 0, &c->fetch_query, r->visits.p, r->pb.q_exact, &c->n_exact_query);
             k_ao_accum<<<sgrid, kShadeBlock, 0, s>>>(r->sv, r->pb, c, radius, i == num_rays - 1 ? 1 : 0, num_rays);
             launches += 3;
         }
@@ -2334,16 +2800,16 @@ ATN_API int atn_render_restir(AtnRenderer* r, int32_t width, int32_t height, int
     k_generate<<<grid, 256, 0, s>>>(fp, r->camera, r->seeds.p, pb, c);
     // bounce 0
     {
-        ClosestPolicy pol{ pb, nullptr, kInf, pb.hit_mesh };
-        launch_trace<ClosestPolicy>(r, s, pol, &c->n_active[0], 0, &c->fetch_closest[0], r->visits.p);
+        ClosestPolicy pol{ pb, nullptr, kInf, pb.hit_mesh, 0 };
+        launch_trace<ClosestPolicy>(r, s, pol, &c->n_active[0], 0, &c->fetch_closest[0], r->visits.p, pb.q_exact, &c->n_exact_closest[0]);
     }
     k_restir_begin<<<sgrid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, pb, rv, c, w2c);
     k_restir_candidate<<<sgrid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, rv, c);
-    k_bsdf<false><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, 0, nullptr, 0);
+    k_bsdf<false><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, ShadeQueues{ nullptr, &c->n_active[0], pb.q_lit, &c->n_lit[0], 0 }, 0, nullptr, 0);
     k_restir_visibility<<<sgrid, kShadeBlock, 0, s>>>(fp, pb, rv, c);
     {
         RestirShadowPolicy pol{ ShadowPolicy<false>{ pb, r->sv, nullptr, 0, 0 }, rv.cur };
-        launch_trace<RestirShadowPolicy>(r, s, pol, &c->n_shadow[0], 0, &c->fetch_shadow[0], r->visits.p);
+        launch_trace<RestirShadowPolicy>(r, s, pol, &c->n_shadow[0], 0, &c->fetch_shadow[0], r->visits.p, pb.q_exact, &c->n_exact_shadow[0]);
     }
     launches += 7;
     if (r->frame > 1) { k_restir_temporal<<<sgrid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, rv); launches++; }
@@ -2435,16 +2901,18 @@ static int query_launch(AtnRenderer* r, const void* rays_dev, const void* f_dev,
     cudaStream_t s = r->stream;
     CUDA_TRY(r->counters.resize(1));
     CUDA_TRY(cudaMemsetAsync(&r->counters.p->fetch_query, 0, sizeof(int32_t), s));
+    CUDA_TRY(cudaMemsetAsync(&r->counters.p->n_exact_query, 0, sizeof(int32_t), s));
+    if (r->exact_ties) CUDA_TRY(r->q_exact_query.resize(n));
     CUDA_TRY(r->visits.resize(1));
     CUDA_TRY(cudaMemsetAsync(r->visits.p, 0, sizeof(Visits), s));
     CUDA_TRY(cudaEventRecord(r->ev0, s));
     if (any) {
         QueryAnyPolicy pol{ (const AtnRay*)rays_dev, (const float*)f_dev, (uint8_t*)out_dev };
-        launch_trace<QueryAnyPolicy>(r, s, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
+        launch_trace<QueryAnyPolicy>(r, s, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p, r->q_exact_query.p, &r->counters.p->n_exact_query);
     }
     else {
         QueryClosestPolicy pol{ (const AtnRay*)rays_dev, (const float*)f_dev, (AtnHit*)out_dev };
-        launch_trace<QueryClosestPolicy>(r, s, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p);
+        launch_trace<QueryClosestPolicy>(r, s, pol, nullptr, (int)n, &r->counters.p->fetch_query, r->visits.p, r->q_exact_query.p, &r->counters.p->n_exact_query);
     }
     r->stats.closest_rays = any ? 0 : n;
     r->stats.shadow_rays = any ? n : 0;
@@ -2516,15 +2984,17 @@ ATN_API int atn_trace_any(AtnRenderer* r, const AtnRay* rays, const float* dist,
 // queries inside a frame loop) for which cudaMalloc's device-wide synchronisation is a visible
 // stall.  For them the staging area lives in the library image itself: one file-scope __device__
 // array per GPU, sized for kStaticMaxRays rays, present from the moment the library is loaded on a
-// device until the process exits (about 3.9 MB per GPU).
+// device until the process exits (about 4.2 MB per GPU).
 constexpr size_t kStaticMaxRays = 65536;
 
 struct StaticScratch {
     int32_t cursor;                    // work-fetch cursor of the persistent traversal kernel
-    int32_t pad[63];                   // keeps the arrays below 256-byte aligned
+    int32_t exact_count;               // rays handed to the exact walk (near ties)
+    int32_t pad[62];                   // keeps the arrays below 256-byte aligned
     AtnRay rays[kStaticMaxRays];
     float t_max[kStaticMaxRays];
     AtnHit hits[kStaticMaxRays];
+    int32_t exact_q[kStaticMaxRays];
 };
 
 // In host code this name is only a handle for cudaGetSymbolAddress; it is NOT a device address.
@@ -2566,12 +3036,12 @@ extern "C" ATN_API int atn_trace_closest_static(AtnRenderer* r, const AtnRay* ra
     cudaStream_t s = r->stream;
     // The array keeps whatever the previous call left in it: the cursor must restart at zero; rays,
     // bounds and hits are fully overwritten for [0, n) and never read beyond n.
-    CUDA_TRY(cudaMemsetAsync(&sc->cursor, 0, sizeof(int32_t), s));
+    CUDA_TRY(cudaMemsetAsync(&sc->cursor, 0, 2 * sizeof(int32_t), s));     // cursor and exact_count
     CUDA_TRY(cudaMemcpyAsync(sc->rays, rays, n * sizeof(AtnRay), cudaMemcpyHostToDevice, s));
     if (t_max) CUDA_TRY(cudaMemcpyAsync(sc->t_max, t_max, n * sizeof(float), cudaMemcpyHostToDevice, s));
     QueryClosestPolicy pol{ sc->rays, t_max ? sc->t_max : nullptr, sc->hits };
     CUDA_TRY(cudaEventRecord(r->ev0, s));
-    launch_trace<QueryClosestPolicy>(r, s, pol, nullptr, (int)n, &sc->cursor, nullptr);
+    launch_trace<QueryClosestPolicy>(r, s, pol, nullptr, (int)n, &sc->cursor, nullptr, sc->exact_q, &sc->exact_count);
     CUDA_TRY(cudaEventRecord(r->ev1, s));
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaMemcpyAsync(hits, sc->hits, n * sizeof(AtnHit), cudaMemcpyDeviceToHost, s));

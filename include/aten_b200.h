@@ -197,6 +197,7 @@ typedef struct AtnStats {
     float    trace_ms;         /* sum of CUDA-event times of the traversal kernels (if profiling on) */
     uint64_t nodes_visited;    /* 128-byte QuadNodes fetched by the traversal kernels (renders and ray queries) */
     uint64_t tris_tested;      /* triangle tests run by the traversal kernels (renders and ray queries) */
+    uint64_t exact_rays;       /* rays whose hit depended on a near tie and was decided by the reference-order walk */
 } AtnStats;
 
 typedef struct AtnRenderer AtnRenderer;
@@ -252,6 +253,12 @@ typedef enum AtnGatherMode {
 /* PathTracing::SetEnableProgressive (pathtracing.h:127-135): 1 = ATN_GATHER_PROGRESSIVE, 0 = ATN_GATHER_OVERWRITE. */
 ATN_API int atn_set_progressive(AtnRenderer* r, int enable);
 ATN_API int atn_set_gather_mode(AtnRenderer* r, int mode /* AtnGatherMode */);
+/* No counterpart in the reference.  1 (default): a ray whose two nearest primitives lie within the error of the reference's
+ * biased box test of each other -- the one case in which the reference's answer depends on its own visit order -- is
+ * repeated as the reference's depth-first walk (ThreadedBvhTraverser::Traverse, threaded_bvh_traverser.h:98-304) over the
+ * reference's node lists, so that the reported primitive is the reference's.  0: such rays keep the nearest of the tied
+ * primitives (a fraction of a percent of the rays of a scene with coincident surfaces; |dt| / t below 1e-4). */
+ATN_API int atn_set_exact_ties(AtnRenderer* r, int enable);
 /* Renderer::setHitDistanceLimit (renderer.h:108-111) */
 ATN_API int atn_set_hit_distance_limit(AtnRenderer* r, float d);
 
@@ -353,7 +360,7 @@ ATN_API int atn_trace_any_device(AtnRenderer* r, const void* rays_dev, const voi
  * t_max may be NULL) for callers that must not allocate device memory: hosts that run inside a fixed
  * device-memory budget which is already spent (so a cudaMalloc may fail), and frame loops that cannot
  * take cudaMalloc's device-wide synchronisation.  Rays and hits are staged in an array that is part of
- * the library image on every GPU it is loaded on (~3.9 MB, held until the process exits) instead of
+ * the library image on every GPU it is loaded on (~4.2 MB, held until the process exits) instead of
  * buffers grown on demand; the call performs no cudaMalloc / cudaFree and calls no allocating routine.
  *   - at most 65536 rays per call; more is refused with ATN_ERR_TOO_LARGE (split the batch);
  *   - the first call on each GPU looks the array's device address up (cudaGetSymbolAddress); make that

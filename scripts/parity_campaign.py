@@ -1,8 +1,9 @@
 #!/usr/bin/env python3
 """Large random-ray parity campaign: closest hits of the CUDA traversal against the CPU restatement (reference visit
 order) on scenes built on the spot by the reference's own loaders / SBVH builder.  Prints one JSON line per scene with
-the number of rays, hit/miss disagreements (must be 0), differing primitive ids and the largest relative distance gap
-among them (the documented near ties).
+the number of rays, hit/miss disagreements, differing primitive ids, the largest relative distance gap among them
+(max_rel_dt; all three must be 0 with the exact walk of near ties on, the default) and the share of rays that walk
+decided (exact_rays).  ATEN_B200_EXACT_TIES=0 shows what the front-to-back walk alone reports.
     python scripts/parity_campaign.py [rays_per_scene] > profiles/rNN_parity_campaign.jsonl"""
 import json
 import os
@@ -47,18 +48,19 @@ def main():
             scene = ol.ref_scene(name, 8, 8)
         r = PathTracing(0)
         r.UpdateSceneData(scene)
-        bad_miss = bad_id = 0
+        bad_miss = bad_id = exact = 0
         worst = 0.0
         total = 0
         for chunk in range(0, n, 1_000_000):
             m = min(1_000_000, n - chunk)
             rays = rays_for(scene, m, seed=chunk + 17)
             got = r.trace_closest(rays)
+            exact += r.stats()["exact_rays"]
             want = ol.trace_closest(scene, rays)
             hit_g, hit_w = got["objid"] >= 0, want["objid"] >= 0
             bad_miss += int((hit_g != hit_w).sum())
             both = hit_g & hit_w
-            diff = both & ((got["primid"] != want["primid"]) | (got["objid"] != want["objid"]))
+            diff = both & ((got["primid"] != want["primid"]) | (got["objid"] != want["objid"]) | (got["t"].view(np.uint32) != want["t"].view(np.uint32)))
             bad_id += int(diff.sum())
             if diff.any():
                 rel = np.abs(got["t"][diff].astype(np.float64) - want["t"][diff]) / want["t"][diff]
@@ -69,7 +71,8 @@ def main():
             total += m
         r.close()
         print(json.dumps({"scene": name, "kernel_form": form, "triangles": int(len(scene.triangles)), "rays": total, "hit_miss_disagreements": bad_miss,
-                          "differing_primitives": bad_id, "rate": bad_id / total, "largest_relative_distance_gap": worst}), flush=True)
+                          "differing_primitives": bad_id, "rate": bad_id / total, "max_rel_dt": worst,
+                          "exact_ties": os.environ.get("ATEN_B200_EXACT_TIES", "1") != "0", "exact_rays": int(exact), "exact_share": exact / total}), flush=True)
 
 
 if __name__ == "__main__":

@@ -55,6 +55,24 @@ def top_update_equals_fresh(base: sio.Scene, moved: sio.Scene) -> int:
     return int(lib().emu_top_update_equals_fresh(C.byref(b0), C.byref(b1)))
 
 
+KERNEL_BAND = (5e-5, 3.0, 2e-6, 5e-5)      # kBandRel, kBandInv, kBandS, kBandM of atn_kernels.cu
+
+
+def trace_closest_resolved(scene: sio.Scene, rays: np.ndarray, t_max=None):
+    """What the product computes: the front-to-back walk with the kernel's near-tie band, and the reference-order walk
+    (the job of k_exact; here the oracle's) for the rays it flags.  Returns (hits, stats) with stats["flagged"]."""
+    from tests import oracle_lib as ol
+    hits, flags, st = trace_closest_flagged(scene, rays, KERNEL_BAND, t_max)
+    idx = np.nonzero(flags)[0]
+    if len(idx):
+        sub = ol.trace_closest(scene, np.ascontiguousarray(rays[idx]), None if t_max is None else np.ascontiguousarray(np.asarray(t_max)[idx])).copy()
+        miss = sub["objid"] < 0
+        sub["primid"][miss] = -1; sub["mtrlid"][miss] = -1; sub["meshid"][miss] = -1
+        hits[idx] = sub
+    st["flagged"] = int(len(idx))
+    return hits, st
+
+
 def trace_closest_flagged(scene: sio.Scene, rays: np.ndarray, band, t_max=None):
     """The kernel's per-ray logic with the near-tie bookkeeping (band = (rel, inv, S, M), see emu_traversal.cpp);
     returns (hits, flags, stats): flags[i] = 1 where the exact reference-order walk has to decide the ray."""

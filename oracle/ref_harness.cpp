@@ -184,6 +184,38 @@ struct Harness {
         ctxt.scene_rendering_config.bg = AT_NAME::Background::CreateBackgroundResource(nullptr, aten::vec4(0.05f, 0.06f, 0.08f, 1.0f));
     }
 
+    // Cornell box lit by a SPHERE area light (sphere::SamplePosAndNormal + sphere::hit, src/libaten/geometry/sphere.cpp:30-150,
+    // AreaLight::sample's "geometric form" branch, src/libaten/light/arealight.h:88-130) next to the polygon light, with a
+    // second, non-emissive sphere object in the top layer: the reference's closest-hit traversal never reports a sphere
+    // (a top-layer leaf without an external tree holds nothing traversable, threaded_bvh_traverser.h:142-220), so that
+    // sphere must stay invisible and must not occlude shadow rays either.
+    void BuildCornellSphere()
+    {
+        auto emit = MakeMtrl("light", ctxt, aten::MaterialType::Emissive, aten::vec3(1.0f));
+        auto objs = aten::ObjLoader::Load(
+            g_asset + "/cornellbox/orig.obj", ctxt,
+            [&](std::string_view name, aten::context& c, aten::MaterialType type, const aten::vec3& clr,
+                const std::string&, const std::string&) -> std::shared_ptr<aten::material> {
+                return MakeMtrl(name, c, type, clr);
+            },
+            nullptr, true, true);
+        auto light = aten::TransformableFactory::createInstance<aten::PolygonObject>(
+            ctxt, objs[0], aten::vec3(0.0f), aten::vec3(0.0f), aten::vec3(1.0f));
+        scene.add(light);
+        ctxt.AddLight(std::make_shared<aten::AreaLight>(light, emit->param().baseColor, 60.0f));
+        auto emit2 = MakeMtrl("sphere_light", ctxt, aten::MaterialType::Emissive, aten::vec3(1.0f, 0.8f, 0.5f));
+        auto ball = aten::TransformableFactory::createSphere(ctxt, aten::vec3(-0.45f, 1.45f, 0.35f), 0.18f, emit2);
+        scene.add(ball);
+        ctxt.AddLight(std::make_shared<aten::AreaLight>(ball, emit2->param().baseColor, 150.0f));
+        auto grey = MakeMtrl("sphere_grey", ctxt, aten::MaterialType::Diffuse, aten::vec3(0.5f));
+        scene.add(aten::TransformableFactory::createSphere(ctxt, aten::vec3(0.35f, 0.9f, 0.4f), 0.3f, grey));
+        for (size_t i = 1; i < objs.size(); i++) {
+            scene.add(aten::TransformableFactory::createInstance<aten::PolygonObject>(ctxt, objs[i], aten::mat4::Identity));
+        }
+        SetCamera(aten::vec3(0.f, 1.f, 3.f), aten::vec3(0.f, 1.f, 0.f), 45.0f);
+        ctxt.scene_rendering_config.bg = AT_NAME::Background::CreateBackgroundResource(nullptr, aten::vec4(0.0f));
+    }
+
     // C2 stand-in: asset/sponza/sponza_lod.obj + the shipped sponza_lod.sbvh (the full-resolution
     // Sponza OBJ/SBVH are stripped from the snapshot).  Materials from the .mtl
     // (Lambert), arches/columns switched to GGX; lit by the synthetic-sky IBL plus one area light.
@@ -340,6 +372,7 @@ struct Harness {
         aten::initSampler(W, H);   // std::mt19937(0), src/libaten/sampler/sampler.cpp:8-18
         if (name == "cornell") BuildCornell();
         else if (name == "cornell_mtrl") BuildCornellMaterials();
+        else if (name == "cornell_sphere") BuildCornellSphere();
         else if (name == "sponza") BuildSponza(false, false);
         else if (name == "sponza_atrium") BuildSponza(false, true);
         else if (name == "sponza_tex") BuildSponza(true, true);

@@ -33,6 +33,7 @@ SCENES = {  # name: (W, H)
     "cornell_mtrl": (64, 48),
     "sponza_atrium": (64, 36),
     "instanced": (64, 36),
+    "cornell_sphere": (64, 64),     # a sphere area light + a sphere object in the top layer (sphere.cpp:30-150, arealight.h:88-130)
 }
 FRAME = 2
 FRAMES = 3

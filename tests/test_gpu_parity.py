@@ -20,7 +20,7 @@ from tests.conftest import bits
 
 pytestmark = pytest.mark.gpu
 
-SCENES = ["cornell", "cornell_mtrl", "sponza_atrium", "instanced"]
+SCENES = ["cornell", "cornell_mtrl", "sponza_atrium", "instanced", "cornell_sphere"]
 FLT_MAX = np.finfo(np.float32).max
 
 

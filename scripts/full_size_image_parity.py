@@ -2,7 +2,7 @@
 """Image parity at the bench workload's FULL size: sponza_atrium 1920x1080, N samples per pixel, 5 bounces -- the CUDA
 path against the CPU restatement (bit-exact against the reference) with the same seeds, per frame accumulated with
 the FilmProgressive formula.  The restatement needs ~30 s of all host cores per sample at this size, hence a script
-and not a test; prints one JSON line (relative RMSE, relMSE, share of pixels equal within 1e-4 relative).
+(the -m gpu suite asserts the same metric with bounds: tests/test_gpu_fullsize.py); prints one JSON line (relative RMSE, relMSE, share of pixels equal within 1e-4 relative).
     python scripts/full_size_image_parity.py [spp [scene]]"""
 import json
 import os

@@ -21,11 +21,11 @@ EXPORTS = [
     "atn_create", "atn_destroy", "atn_last_error", "atn_version", "atn_upload_scene", "atn_update_camera",
     "atn_update_top_layer", "atn_update_materials", "atn_update_lights", "atn_update_config", "atn_set_seeds",
     "atn_set_frame", "atn_get_frame", "atn_reset", "atn_set_progressive", "atn_set_gather_mode", "atn_set_exact_ties", "atn_set_hit_distance_limit",
-    "atn_render", "atn_render_region", "atn_synchronize", "atn_readback", "atn_device_image", "atn_get_stats",
+    "atn_render", "atn_render_region", "atn_render_tiles", "atn_synchronize", "atn_readback", "atn_device_image", "atn_get_stats",
     "atn_set_profiling", "atn_get_stream", "atn_trace_closest", "atn_trace_any", "atn_trace_closest_device",
     "atn_trace_any_device", "atn_set_bounce_tap", "atn_trace_closest_static", "atn_readback_aov", "atn_render_ao",
     "atn_render_svgf", "atn_set_motion_depth", "atn_readback_svgf", "atn_update_texture",
-    "atn_render_restir", "atn_readback_restir",
+    "atn_render_restir", "atn_readback_restir", "atn_probe_read_bandwidth",
 ]
 
 
@@ -34,6 +34,14 @@ GATHER_OVERWRITE, GATHER_PROGRESSIVE, GATHER_SUM = 0, 1, 2      # AtnGatherMode 
 
 class AtnError(RuntimeError):
     pass
+
+
+def probe_read_bandwidth(device: int, nbytes: int, passes: int):
+    """(GB/s, ms) of one persistent launch reading a resident buffer of `nbytes` `passes` times (measurement aid)."""
+    lib = load_library()
+    g, ms = C.c_float(), C.c_float()
+    _check(lib, lib.atn_probe_read_bandwidth(C.c_int(device), C.c_size_t(nbytes), C.c_int(passes), C.byref(g), C.byref(ms)))
+    return g.value, ms.value
 
 
 class AtnStats(C.Structure):
@@ -233,6 +241,12 @@ class PathTracing:
     def render_region(self, width, height, x0, y0, x1, y1, sample_begin, sample_end, maxBounce, rrBounce=3):
         _check(self._lib, self._lib.atn_render_region(
             self._h, C.c_int32(width), C.c_int32(height), C.c_int32(x0), C.c_int32(y0), C.c_int32(x1), C.c_int32(y1),
+            C.c_int32(sample_begin), C.c_int32(sample_end), C.c_int32(maxBounce), C.c_int32(rrBounce)))
+
+    def render_tiles(self, width, height, tile, world, rank, sample_begin, sample_end, maxBounce, rrBounce=3):
+        """The interleaved tile set of `rank` (tiles g with g % world == rank, scanline order) as one wavefront."""
+        _check(self._lib, self._lib.atn_render_tiles(
+            self._h, C.c_int32(width), C.c_int32(height), C.c_int32(tile), C.c_int32(world), C.c_int32(rank),
             C.c_int32(sample_begin), C.c_int32(sample_end), C.c_int32(maxBounce), C.c_int32(rrBounce)))
 
     def synchronize(self):

@@ -1068,49 +1068,37 @@ struct FrameParams {
     int32_t max_bounce, rr_bounce;
     uint32_t seed_count;
     int32_t batch;                  // camera samples traced as one wavefront: slot = k * (rw * rh) + pixel, sample k uses frame + k
+    // tile-set mode (atn_render_tiles), tile > 0: the wavefront covers the tiles g = j * tile_world + tile_rank (j = 0 ..
+    // rh - 1, scanline order over a grid of tiles_x tiles per row); rw = tile * tile slots per tile, rh = number of tiles.
+    // Slots of an edge tile that fall outside the frame are never queued.
+    int32_t tile, tiles_x, tile_world, tile_rank;
 };
 
 // Where a path slot sits: pixel of the region, sample of the batch.  Samples are independent in the reference (one
 // `render` pass per sample); a wavefront of one 1080p sample (2 M rays per launch) leaves ~6 % on the table against
 // one of 8 M rays (launch tails, refill granularity), so several samples share a wavefront when the frame is small.
-struct SlotInfo { int ix, iy, pix, k; uint32_t frame; };
+struct SlotInfo { int ix, iy, pix, k; uint32_t frame; bool valid; };
 __device__ __forceinline__ SlotInfo slot_info(const FrameParams& fp, int slot)
 {
     const int n_pix = fp.rw * fp.rh;
     SlotInfo si;
     si.k = (fp.batch > 1) ? slot / n_pix : 0;
     const int p = slot - si.k * n_pix;
-    si.ix = fp.x0 + p % fp.rw;
-    si.iy = fp.y0 + p / fp.rw;
+    if (fp.tile > 0) {
+        const int j = p / fp.rw, q = p - j * fp.rw;
+        const int g = j * fp.tile_world + fp.tile_rank;
+        si.ix = (g % fp.tiles_x) * fp.tile + q % fp.tile;
+        si.iy = (g / fp.tiles_x) * fp.tile + q / fp.tile;
+        si.valid = si.ix < fp.width && si.iy < fp.height;
+    }
+    else {
+        si.ix = fp.x0 + p % fp.rw;
+        si.iy = fp.y0 + p / fp.rw;
+        si.valid = true;
+    }
     si.pix = si.iy * fp.width + si.ix;
     si.frame = fp.frame + (uint32_t)si.k;
     return si;
-}
-
-// GeneratePath (pathtracing_impl.h:65-110)
-__global__ void k_generate(FrameParams fp, AtnCameraParameter cam, const uint32_t* __restrict__ seeds, PathBuffers pb,
-                           Counters* cnt)
-{
-    const int n = fp.rw * fp.rh * fp.batch;
-    for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < n; s += gridDim.x * blockDim.x) {
-        const SlotInfo si = slot_info(fp, s);
-        const int ix = si.ix, iy = si.iy;
-        const uint32_t idx = (uint32_t)si.pix;
-        Sampler sp = sampler_for_path(si.frame, seeds[idx % fp.seed_count]);
-        const float r1 = sp.next();
-        const float r2 = sp.next();
-        const float fs = (ix + r1) / (float)(cam.width);
-        const float ft = (iy + r2) / (float)(cam.height);
-        const Ray r = camera_sample(cam, fs, ft);
-        pb.ray_o[s] = make_float4(r.org.x, r.org.y, r.org.z, 0.0f);
-        pb.ray_d[s] = make_float4(r.dir.x, r.dir.y, r.dir.z, 0.0f);
-        pb.throughput[s] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
-        pb.contrib[s] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
-        pb.sampler_dim[s] = sp.dim;
-        pb.flags[s] = 0u;
-        pb.pend[s] = 0;
-    }
-    if (blockIdx.x == 0 && threadIdx.x == 0) cnt->n_active[0] = n;
 }
 
 // Append `value` for the lanes with `pred` to a device queue: one atomicAdd per warp.
@@ -1125,6 +1113,46 @@ __device__ __forceinline__ int warp_append(bool pred, int32_t* counter)
     base = __shfl_sync(0xffffffffu, base, leader);
     return pred ? base + __popc(mask & ((1u << lane) - 1u)) : -1;
 }
+
+// GeneratePath (pathtracing_impl.h:65-110).  Region mode: path i of bounce 0 is slot i (no queue).  Tile-set mode: the
+// slots inside the frame are appended to the bounce-0 queue.
+__global__ void k_generate(FrameParams fp, AtnCameraParameter cam, const uint32_t* __restrict__ seeds, PathBuffers pb,
+                           Counters* cnt)
+{
+    const int n = fp.rw * fp.rh * fp.batch;
+    const int rounds = (n + blockDim.x * gridDim.x - 1) / (blockDim.x * gridDim.x);
+    for (int it = 0; it < rounds; it++) {
+        const int s = (it * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+        bool live = false;
+        if (s < n) {
+            const SlotInfo si = slot_info(fp, s);
+            live = si.valid;
+            if (live) {
+                const int ix = si.ix, iy = si.iy;
+                const uint32_t idx = (uint32_t)si.pix;
+                Sampler sp = sampler_for_path(si.frame, seeds[idx % fp.seed_count]);
+                const float r1 = sp.next();
+                const float r2 = sp.next();
+                const float fs = (ix + r1) / (float)(cam.width);
+                const float ft = (iy + r2) / (float)(cam.height);
+                const Ray r = camera_sample(cam, fs, ft);
+                pb.ray_o[s] = make_float4(r.org.x, r.org.y, r.org.z, 0.0f);
+                pb.ray_d[s] = make_float4(r.dir.x, r.dir.y, r.dir.z, 0.0f);
+                pb.throughput[s] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+                pb.contrib[s] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
+                pb.sampler_dim[s] = sp.dim;
+                pb.flags[s] = 0u;
+                pb.pend[s] = 0;
+            }
+        }
+        if (fp.tile > 0) {
+            const int pos = warp_append(live, &cnt->n_active[0]);
+            if (live) pb.queue[0][pos] = s;
+        }
+    }
+    if (fp.tile == 0 && blockIdx.x == 0 && threadIdx.x == 0) cnt->n_active[0] = n;
+}
+
 
 #ifndef ATN_SURFACE_MIN_BLOCKS
 #define ATN_SURFACE_MIN_BLOCKS 8
@@ -1737,8 +1765,10 @@ __global__ void k_gather(FrameParams fp, PathBuffers pb, float4* image, int mode
         totals->closest += c; totals->shadow += s; totals->exact += e;
     }
     for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < n; s += gridDim.x * blockDim.x) {
-        const int ix = fp.x0 + s % fp.rw;
-        const int iy = fp.y0 + s / fp.rw;
+        FrameParams one = fp; one.batch = 1;
+        const SlotInfo si = slot_info(one, s);
+        if (!si.valid) continue;
+        const int ix = si.ix, iy = si.iy;
         float4 cur = image[iy * fp.width + ix];
         if (mode == ATN_GATHER_OVERWRITE && first) cur = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         for (int k = 0; k < fp.batch; k++) {          // the samples of the batch, in sample order
@@ -2441,7 +2471,7 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
     cudaEvent_t shadow_done = nullptr;            // side stream: the exact walk of the previous bounce's shadow rays
     for (int b = first_bounce; b < fp.max_bounce; b++) {
         Counters* c = r->counters.p;
-        const int32_t* q = (b == 0) ? nullptr : pb.queue[b & 1];
+        const int32_t* q = (b == 0 && fp.tile == 0) ? nullptr : pb.queue[b & 1];
         const float tmax = (b == 0) ? kInf : r->hit_distance_limit;
         const ShadeQueues mainq{ q, &c->n_active[b], pb.q_lit, &c->n_lit[b], overlap ? b + 1 : 0 };
         const ShadeQueues sideq{ pb.q_exact, &c->n_exact_closest[b], pb.q_lit_side, &c->n_lit_side[b], 0 };
@@ -2497,8 +2527,11 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
     return ATN_OK;
 }
 
-ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int32_t x0, int32_t y0, int32_t x1, int32_t y1,
-                              int32_t sample_begin, int32_t sample_end, int32_t max_bounce, int32_t rr_bounce)
+// atn_render_region and atn_render_tiles: `tile` = 0 renders the rectangle, `tile` > 0 the interleaved tile set of
+// (tile_world, tile_rank) as ONE wavefront (x0 .. y1 ignored).
+static int render_impl(AtnRenderer* r, int32_t width, int32_t height, int32_t x0, int32_t y0, int32_t x1, int32_t y1,
+                       int32_t tile, int32_t tile_world, int32_t tile_rank,
+                       int32_t sample_begin, int32_t sample_end, int32_t max_bounce, int32_t rr_bounce)
 {
     if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render: NULL handle");
     if (!r->has_scene) return set_error(ATN_ERR_NO_SCENE, "atn_render: no scene uploaded");
@@ -2514,7 +2547,26 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
     FrameParams fp;
     fp.width = width; fp.height = height; fp.x0 = x0; fp.y0 = y0; fp.rw = x1 - x0; fp.rh = y1 - y0;
     fp.max_bounce = max_bounce; fp.rr_bounce = rr_bounce; fp.seed_count = r->seed_count;
+    fp.tile = 0; fp.tiles_x = 0; fp.tile_world = 1; fp.tile_rank = 0;
+    if (tile > 0) {
+        const int tiles_x = (width + tile - 1) / tile, tiles_y = (height + tile - 1) / tile;
+        const int total = tiles_x * tiles_y;
+        const int mine = total > tile_rank ? (total - tile_rank + tile_world - 1) / tile_world : 0;
+        fp.tile = tile; fp.tiles_x = tiles_x; fp.tile_world = tile_world; fp.tile_rank = tile_rank;
+        fp.x0 = 0; fp.y0 = 0; fp.rw = tile * tile; fp.rh = mine;
+        if (mine == 0) return ATN_OK;                                  // more ranks than tiles: nothing to do
+        if (r->tap_host) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_tiles: the bounce tap is not available on a tile set");
+        if ((size_t)fp.rw * fp.rh > r->path_capacity) return set_error(ATN_ERR_TOO_LARGE, "atn_render_tiles: tile set larger than the path buffers");
+    }
     const int n = fp.rw * fp.rh;
+    uint64_t n_pixels = (uint64_t)n;                 // pixels inside the frame (an edge tile is partly outside)
+    if (tile > 0) {
+        n_pixels = 0;
+        for (int j = 0; j < fp.rh; j++) {
+            const int g = j * tile_world + tile_rank, tx = g % fp.tiles_x, ty = g / fp.tiles_x;
+            n_pixels += (uint64_t)std::min(tile, width - tx * tile) * (uint64_t)std::min(tile, height - ty * tile);
+        }
+    }
     const bool tap = r->tap_host != nullptr;
     if (tap) {
         CUDA_TRY(r->tap_dev.resize((size_t)n * r->tap_cap));
@@ -2553,13 +2605,27 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int
     }
     // Exact ray counts: k_gather folds every sample's queue counters into Totals on the device; they are read on demand
     // (atn_get_stats).  The call returns without waiting for the GPU unless the bounce tap has to be copied out.
-    const int rc_end = end_call(r, AtnRenderer::PEND_RENDER, launches, (uint64_t)n * (uint64_t)spp, ev_i);
+    const int rc_end = end_call(r, AtnRenderer::PEND_RENDER, launches, n_pixels * (uint64_t)spp, ev_i);
     if (rc_end != ATN_OK) return rc_end;
     if (tap) {
         CUDA_TRY(cudaMemcpyAsync(r->tap_host, r->tap_dev.p, (size_t)n * r->tap_cap * sizeof(AtnBounceRecord), cudaMemcpyDeviceToHost, s));
         CUDA_TRY(cudaStreamSynchronize(s));
     }
     return ATN_OK;
+}
+
+ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height, int32_t x0, int32_t y0, int32_t x1, int32_t y1,
+                              int32_t sample_begin, int32_t sample_end, int32_t max_bounce, int32_t rr_bounce)
+{
+    return render_impl(r, width, height, x0, y0, x1, y1, 0, 1, 0, sample_begin, sample_end, max_bounce, rr_bounce);
+}
+
+ATN_API int atn_render_tiles(AtnRenderer* r, int32_t width, int32_t height, int32_t tile, int32_t world, int32_t rank,
+                             int32_t sample_begin, int32_t sample_end, int32_t max_bounce, int32_t rr_bounce)
+{
+    if (tile < 8 || tile > 1024 || world < 1 || rank < 0 || rank >= world)
+        return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_tiles: tile %d (8..1024), world %d, rank %d", tile, world, rank);
+    return render_impl(r, width, height, 0, 0, width, height, tile, world, rank, sample_begin, sample_end, max_bounce, rr_bounce);
 }
 
 ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t spp, int32_t num_rays, float radius)
@@ -2573,7 +2639,7 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
     CUDA_TRY(cudaSetDevice(r->device));
     cudaStream_t s = r->stream;
     FrameParams fp;
-    fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height;
+    fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height; fp.tile = 0; fp.tiles_x = 0; fp.tile_world = 1; fp.tile_rank = 0;
     fp.max_bounce = 1; fp.rr_bounce = 1; fp.seed_count = r->seed_count; fp.batch = 1;
     const int n = width * height;
     const int grid = std::min((n + 255) / 256, r->sm_count * 8);
@@ -2674,7 +2740,7 @@ ATN_API int atn_render_svgf(AtnRenderer* r, int32_t width, int32_t height, int32
     if (r->svgf_has_motion && r->svgf_motion.n < n) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_svgf: motion buffer smaller than the image");
 
     FrameParams fp;
-    fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height;
+    fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height; fp.tile = 0; fp.tiles_x = 0; fp.tile_world = 1; fp.tile_rank = 0;
     fp.max_bounce = max_bounce; fp.rr_bounce = rr_bounce; fp.seed_count = r->seed_count; fp.batch = 1;
     fp.frame = r->frame;
     const int cur_k = (int)(r->frame & 1u);
@@ -2777,7 +2843,7 @@ ATN_API int atn_render_restir(AtnRenderer* r, int32_t width, int32_t height, int
     if (r->svgf_has_motion && r->svgf_motion.n < n) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_restir: motion buffer smaller than the image");
 
     FrameParams fp;
-    fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height;
+    fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height; fp.tile = 0; fp.tiles_x = 0; fp.tile_world = 1; fp.tile_rank = 0;
     fp.max_bounce = max_bounce; fp.rr_bounce = rr_bounce; fp.seed_count = r->seed_count; fp.batch = 1;
     fp.frame = r->frame;
     const int cur = r->restir_cur, other = (cur + 1) & 1;
@@ -3018,6 +3084,54 @@ static int static_scratch_for_device(int device, StaticScratch** out)
         g_static_ptr[device] = static_cast<StaticScratch*>(p);
     }
     *out = g_static_ptr[device];
+    return ATN_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Measurement aid (bench.py, scripts/l2_bandwidth.py): read bandwidth of a resident buffer.  One persistent launch walks a
+// buffer of `bytes` (a power-of-two multiple of 32 B per thread step) `passes` times with 256-bit loads, so a buffer that
+// fits the L2 is served from it for all but the first pass and the launch lasts milliseconds, not microseconds (a
+// sequence of small copy launches measures launch latency instead, which is what the round-1 probe did below 32 MB).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_probe_read(const float4* __restrict__ buf, size_t n_chunks, int passes, float* sink)
+{
+    float acc = 0.0f;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (int p = 0; p < passes; p++) {
+        // every pass a thread reads another part of the buffer, so that nothing is served from its SM's L1
+        const size_t shift = ((size_t)p * 1048573u) % n_chunks;
+        for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n_chunks; i += stride) {
+            size_t j = i + shift; if (j >= n_chunks) j -= n_chunks;
+            const F4x2 v = ldg8(buf + 2 * j);
+            acc += v.lo.x + v.hi.w;
+        }
+    }
+    if (acc == 12345.678f) *sink = acc;          // keeps the loads alive
+}
+
+extern "C" ATN_API int atn_probe_read_bandwidth(int device_ordinal, size_t bytes, int passes, float* gb_per_s, float* ms_out)
+{
+    if (!gb_per_s || bytes < 4096 || passes < 1) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_probe_read_bandwidth: bad argument");
+    CUDA_TRY(cudaSetDevice(device_ordinal));
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device_ordinal));
+    DevBuf<float4> buf; DevBuf<float> sink;
+    const size_t n_chunks = bytes / 32;
+    CUDA_TRY(buf.resize(n_chunks * 2)); CUDA_TRY(sink.resize(1));
+    CUDA_TRY(cudaMemset(buf.p, 0, n_chunks * 32));
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0)); CUDA_TRY(cudaEventCreate(&e1));
+    const int grid = prop.multiProcessorCount * 8;
+    k_probe_read<<<grid, 256>>>(buf.p, n_chunks, 2, sink.p);                 // warm-up: the buffer is in the L2 afterwards
+    CUDA_TRY(cudaEventRecord(e0));
+    k_probe_read<<<grid, 256>>>(buf.p, n_chunks, passes, sink.p);
+    CUDA_TRY(cudaEventRecord(e1));
+    CUDA_TRY(cudaEventSynchronize(e1));
+    float ms = 0.0f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    *gb_per_s = (float)((double)n_chunks * 32.0 * passes / (ms * 1e-3) / 1e9);
+    if (ms_out) *ms_out = ms;
     return ATN_OK;
 }
 

@@ -5,7 +5,7 @@ The reference has no multi-GPU code at all (no cudaSetDevice / NCCL anywhere); p
 are independent, so the only exchange step is the final image combine:
 
   * sample split: rank r renders samples [begin, end) of every pixel in SUM mode (xyz = sum of
-    radiance, w = sample count, ``atn_set_progressive(0)``); ``reduce(SUM)`` then one divide by w;
+    radiance, w = sample count, ``atn_set_gather_mode(ATN_GATHER_SUM)``); ``reduce(SUM)`` then one divide by w;
   * tile split: rank r renders an interleaved set of tiles; the other pixels stay (0,0,0,0), so the
     same ``reduce(SUM)`` assembles the frame (bit-identical to a single-GPU render, since no pixel
     receives more than one non-zero term).
@@ -67,7 +67,7 @@ def render_partitioned(renderer, width: int, height: int, total_spp: int, max_bo
         if e > b:
             renderer.render_region(width, height, 0, 0, width, height, b, e, max_bounce, rr_bounce)
     elif mode == "tiles":
-        for (x0, y0, x1, y1) in partition_tiles(width, height, world, rank, tile):
-            renderer.render_region(width, height, x0, y0, x1, y1, 0, total_spp, max_bounce, rr_bounce)
+        # the same tiles partition_tiles() lists, rendered as one wavefront (atn_render_tiles)
+        renderer.render_tiles(width, height, tile, world, rank, 0, total_spp, max_bounce, rr_bounce)
     else:
         raise ValueError(f"unknown partition mode {mode!r}")

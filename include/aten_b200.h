@@ -278,6 +278,12 @@ ATN_API int atn_render_region(AtnRenderer* r, int32_t width, int32_t height,
                               int32_t x0, int32_t y0, int32_t x1, int32_t y1,
                               int32_t sample_begin, int32_t sample_end,
                               int32_t max_bounce, int32_t rr_bounce);
+/* The other multi-GPU partition: the frame is cut into tile x tile squares numbered in scanline order and
+ * this call renders the squares g with g % world == rank -- all of them as ONE wavefront, so a rank's share costs what
+ * a frame of that many pixels costs -- for samples [sample_begin, sample_end).  Pixels of the other ranks' tiles are
+ * not touched.  Does not advance the frame counter; not available with the bounce tap. */
+ATN_API int atn_render_tiles(AtnRenderer* r, int32_t width, int32_t height, int32_t tile, int32_t world, int32_t rank,
+                             int32_t sample_begin, int32_t sample_end, int32_t max_bounce, int32_t rr_bounce);
 /* Row N1 of SURVEY 8f, the first renderer that sits on this path: ambient occlusion.
  * idaten::AORenderer::render (src/libidaten/ao/ao.cpp:9-51, kernels ao.cu:20-121) / aten::AORenderer
  * (src/libaten/renderer/ao/aorenderer.cpp:20-146, ShandeByAO aorenderer_impl.h:33-117): camera ray,
@@ -370,6 +376,11 @@ ATN_API int atn_trace_any_device(AtnRenderer* r, const void* rays_dev, const voi
  * Synchronous: returns when `hits` is filled. */
 ATN_API int atn_trace_closest_static(AtnRenderer* r, const AtnRay* rays, const float* t_max /* may be NULL */,
                                      size_t n, AtnHit* hits);
+
+/* No counterpart in the reference: a measurement aid for the roofline figures (bench.py).  Read bandwidth in GB/s of a
+ * device buffer of `bytes` walked `passes` times by ONE persistent launch with 256-bit loads: with bytes below the L2 size
+ * this is the L2 read bandwidth, far above it the HBM read bandwidth.  Allocates and frees its own buffer. */
+ATN_API int atn_probe_read_bandwidth(int device_ordinal, size_t bytes, int passes, float* gb_per_s, float* ms /* may be NULL */);
 
 /* ---- debug / parity taps ------------------------------------------------------------------------ */
 /* Per-bounce dump of the wavefront state for parity tests: after atn_render with a tap installed,

@@ -41,7 +41,7 @@ def render_bench(name, W, H, spp, steps=3, warmup=2, label=""):
            "msamples_per_s": round(samples / ms / 1e3, 1), "rays_per_sample": round(rays / samples, 2),
            "quad_nodes_per_ray": round(nodes / rays, 2), "tri_tests_per_ray": round(tris / rays, 2),
            "mean_radiance": float(img[..., :3].mean() / spp), "finite": bool(np.isfinite(img).all())}
-    print(json.dumps(out), flush=True)
+    return out
 
 
 def ao_bench(name, W, H, spp, steps=3, warmup=2, label=""):
@@ -197,7 +197,7 @@ def ray_stress(name, n_rays, label=""):
                       "visible_fraction": round(float(t_vis.float().mean()), 3)}), flush=True)
 
 
-def ray_stress_flat(name, n_rays, label="", parity_rays=200_000, copies=None):
+def ray_stress_flat(name, n_rays, label="", parity_rays=200_000, copies=None, render=True):
     """configs[4] proper: 100 DISTINCT dragon meshes (scripts/flat_scene.py: own vertices, triangles and bottom-layer
     node list per copy -- ~1.4 GB of QuadNodes + TriLeafs, not L2-resident), rays that start on the surfaces
     (area-uniform origins, cosine-distributed directions).  Reports closest-hit and any-hit Mrays/s, the bytes the
@@ -277,6 +277,8 @@ def ray_stress_flat(name, n_rays, label="", parity_rays=200_000, copies=None):
     torch.cuda.empty_cache()
     W, H, spp = 1920, 1080, 4
     r.close()
+    if not render:
+        return out
     r = PathTracing(0)
     r.UpdateSceneData(scene.with_size(W, H))
     r.set_gather_mode(2)
@@ -291,7 +293,7 @@ def ray_stress_flat(name, n_rays, label="", parity_rays=200_000, copies=None):
                                 "rays_per_sample": round(nr / ns, 2), "finite": bool(np.isfinite(img).all()),
                                 "mean_radiance": float(img[..., :3].mean() / spp)}
     r.close()
-    print(json.dumps(out), flush=True)
+    return out
 
 
 def main():
@@ -308,25 +310,25 @@ def main():
         restir_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 4, label="N1 ReSTIR, sponza_lod 1080p, 8-frame sequence")
         return
     if a.only == "flat":
-        ray_stress_flat("dragon_grid10", a.rays or (100_000_000 if not q else 5_000_000), copies=a.copies or (None if not q else 9),
+        print(json.dumps(ray_stress_flat("dragon_grid10", a.rays or (100_000_000 if not q else 5_000_000), copies=a.copies or (None if not q else 9),
                         label="C5: incoherent secondary rays into 100 distinct dragon meshes (10 M triangles, ~1.4 GB of nodes + triangles)"
-                        if not (a.copies or q) else f"incoherent secondary rays into {a.copies or 9} distinct dragon meshes")
+                        if not (a.copies or q) else f"incoherent secondary rays into {a.copies or 9} distinct dragon meshes")), flush=True)
         return
     if a.only == "svgf":
         svgf_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 3, label="N1 SVGF, sponza_lod 1080p, 8-frame sequence")
         return
-    render_bench("cornell", 512, 512, 1, steps=5, warmup=3, label="C1 Cornell 512x512 1spp")
-    render_bench("sponza_atrium", 1920, 1080, 16 if not q else 2, label="C2 sponza_lod 1080p 16spp (bench.py workload)")
-    render_bench("sponza_tex", 1920, 1080, 16 if not q else 2, label="C3 stand-in: sponza_lod + albedo/normal maps + synthetic-sky IBL, 1080p 16spp")
-    render_bench("instanced_dragon", 3840, 2160, 8 if not q else 1, label="C4 stand-in: instanced dragon+teapot+suzanne, Disney/refraction, 4K, 8 spp (one GPU's share of 64 spp on 8)")
-    render_bench("dragon_grid10", 1920, 1080, 4 if not q else 1, label="C5 stand-in (rendered): 100 instanced dragons = 10 M triangles, 1080p 4spp")
+    print(json.dumps(render_bench("cornell", 512, 512, 1, steps=5, warmup=3, label="C1 Cornell 512x512 1spp")), flush=True)
+    print(json.dumps(render_bench("sponza_atrium", 1920, 1080, 16 if not q else 2, label="C2 sponza_lod 1080p 16spp (bench.py workload)")), flush=True)
+    print(json.dumps(render_bench("sponza_tex", 1920, 1080, 16 if not q else 2, label="C3 stand-in: sponza_lod + albedo/normal maps + synthetic-sky IBL, 1080p 16spp")), flush=True)
+    print(json.dumps(render_bench("instanced_dragon", 3840, 2160, 8 if not q else 1, label="C4 stand-in: instanced dragon+teapot+suzanne, Disney/refraction, 4K, 8 spp (one GPU's share of 64 spp on 8)")), flush=True)
+    print(json.dumps(render_bench("dragon_grid10", 1920, 1080, 4 if not q else 1, label="C5 stand-in (rendered): 100 instanced dragons = 10 M triangles, 1080p 4spp")), flush=True)
     ao_bench("sponza_atrium", 1920, 1080, 16 if not q else 2, label="N1 ambient occlusion, sponza_lod 1080p 16spp")
     svgf_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 3, label="N1 SVGF, sponza_lod 1080p, 8-frame sequence")
     restir_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 4, label="N1 ReSTIR, sponza_lod 1080p, 8-frame sequence")
     ray_stress("dragon_grid10", 100_000_000 if not q else 5_000_000,
                label="C5 stand-in: 100 M incoherent secondary rays into 100 instanced dragons (10 M triangles), closest-hit and any-hit")
-    ray_stress_flat("dragon_grid10", 100_000_000 if not q else 5_000_000, copies=None if not q else 9,
-                    label="C5: 100 M incoherent secondary rays into 100 distinct dragon meshes (10 M triangles, ~1.4 GB of nodes + triangles)")
+    print(json.dumps(ray_stress_flat("dragon_grid10", 100_000_000 if not q else 5_000_000, copies=None if not q else 9,
+                    label="C5: 100 M incoherent secondary rays into 100 distinct dragon meshes (10 M triangles, ~1.4 GB of nodes + triangles)")), flush=True)
 
 
 if __name__ == "__main__":

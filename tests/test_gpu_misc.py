@@ -94,3 +94,30 @@ def test_static_query_reports_its_own_counters(golden):
         r.trace_closest_static(rays[:777])
         st = r.stats()
         assert st["closest_rays"] == 777 and st["shadow_rays"] == 0 and st["camera_samples"] == 0 and st["kernel_launches"] == 1
+
+
+def test_tile_set_render_equals_full_frame(golden):
+    """atn_render_tiles: the interleaved tile sets of 3 ranks (the last column and row of tiles are partly outside the
+    frame), each rendered as one wavefront into the same image, give the full-frame render bit for bit -- the property the
+    multi-GPU tile partition rests on -- and a rank's counters cover its own pixels only."""
+    name = "sponza_atrium"; m = golden.meta[name]
+    W, H = 200, 120                                   # not a multiple of the 64-pixel tile
+    scene = golden.scene(name).with_size(W, H)
+    with PathTracing(0) as r:
+        r.UpdateSceneData(scene)
+        r.set_gather_mode(GATHER_SUM)
+        r.render(W, H, 3, 5, 3)
+        full = r.readback().copy()
+        whole = r.stats()
+        r.reset(); r.set_frame(0)
+        samples = rays = 0
+        for rank in range(3):
+            r.render_tiles(W, H, 64, 3, rank, 0, 3, 5, 3)
+            st = r.stats()
+            samples += st["camera_samples"]; rays += st["closest_rays"] + st["shadow_rays"]
+        tiles = r.readback()
+        assert (bits(tiles) == bits(full)).all()
+        assert samples == whole["camera_samples"] == W * H * 3
+        assert rays == whole["closest_rays"] + whole["shadow_rays"]
+        with pytest.raises(AtnError, match="atn_render_tiles"):
+            r.render_tiles(W, H, 64, 2, 2, 0, 1, 5, 3)

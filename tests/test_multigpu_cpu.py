@@ -53,6 +53,10 @@ def _worker(rank, world, port, mode, q):
                 img[y0:y1, x0:x1, :3] += smp[y0:y1, x0:x1]
                 img[y0:y1, x0:x1, 3] += 1.0
 
+        def render_tiles(self, w, h, tile, world_, rank_, sb, se, mb, rr):      # PathTracing.render_tiles: one wavefront over
+            for (x0, y0, x1, y1) in mg.partition_tiles(w, h, world_, rank_, tile):   # exactly the tiles partition_tiles lists
+                self.render_region(w, h, x0, y0, x1, y1, sb, se, mb, rr)
+
     mg.render_partitioned(FakeRenderer(), W, H, SPP, 5, 3, world, rank, mode=mode, tile=16)
     mg.combine_images(img, dst=0)
     if rank == 0:

@@ -128,7 +128,6 @@ struct Counters {
     int32_t n_exact_closest[kMaxBounce];  // rays handed to the exact walk (near ties), per bounce
     int32_t n_exact_shadow[kMaxBounce];
     int32_t n_exact_query;
-    int32_t n_lit_side[kMaxBounce];       // surface hits of the side pass (paths decided by the exact walk)
     int32_t pad[2];
 };
 
@@ -144,6 +143,9 @@ struct PathBuffers {
     int2* hit1;           // objid, mtrlid   (objid < 0: miss)
     float4* throughput;   // xyz, pdfb
     float4* contrib;      // xyz, samples
+    float4* contrib_late; // light contributions of the shadow rays the exact walk decided (k_exact); zero for all other paths.
+                          // They arrive on the side stream at any time before the gather, which adds them: the main stream
+                          // never waits for them, and a path's sum does not depend on when they arrived
     uint32_t* sampler_dim;
     uint32_t* flags;      // bit0 terminated, bit1 singular
     int32_t* queue[2];    // path slots to trace at bounce b (b & 1)
@@ -151,7 +153,6 @@ struct PathBuffers {
     int32_t* q_shadow;    // path slots with a shadow ray to trace
     int32_t* q_exact;     // path slots whose closest-hit traversal ended in a near tie: the exact walk decides them (k_exact)
     int32_t* q_exact_s;   // the same for shadow rays (its own list: the two exact walks of a bounce overlap other work)
-    int32_t* q_lit_side;  // side pass: paths of q_exact that passed the surface stage
     uint8_t* pend;        // bounce + 1 of the bounce whose closest hit the exact walk decides (0: none since k_generate).  Written
                           // by the traversal, read by the main surface stage, never touched by the side pass -- which
                           // overwrites hit0 / hit1 of such a path while the main surface stage is still running
@@ -210,6 +211,11 @@ __device__ __forceinline__ void resolve_hit(const BvhView& bv, const TraceResult
 //   * the smallest hit distance of a primitive OTHER than the best one is tracked (t2); at the end of the ray, t2 within
 //     B of the best hit means the reference's answer depends on its order: the ray goes to the exact queue and
 //     k_exact repeats it as the reference's own depth-first walk over the reference's own node lists.
+//   * most ties are still decided here: stack keys carry the LARGEST entry distance on the path from the root (pathmax), and
+//     if the best hit is strictly nearer than every runner-up (t_best < t2) and every box on the path to its leaf starts
+//     no later than t2 (pathmax <= t2), the reference reaches that leaf whatever it has accepted before -- everything it
+//     can have accepted is at t2 or beyond -- and keeps it.  Only exact ties (t_best == t2) and paths with a box that
+//     starts behind t2 go to the exact walk.
 // If nothing ties, the reference's answer is this kernel's: every other primitive is farther than the band, the boxes on
 // the path to the best primitive start no later than its hit plus the band, so no hit the reference accepts earlier
 // can cull them (DESIGN.md "Exactness").  scripts/exp_near_ties.py measures the rule on the CPU emulation: with these
@@ -313,7 +319,8 @@ __device__ __forceinline__ bool leaf_may_hit(float t0, float t1, float margin)
 //   t_max(slot)              its distance bound (k_exact)
 //   finish(bv, slot, r, tie) end of the fast traversal: stores the result and returns true, or returns false when the
 //                            result depends on a near tie the policy cares about (the slot then goes to the exact queue)
-//   finish_hit(slot, h)      stores a resolved hit (used by finish and by k_exact)
+//   finish_hit(slot, h)      stores a resolved hit (used by finish)
+//   finish_exact(slot, h)    the same for a hit the exact walk decided (k_exact, on the side stream)
 __device__ __forceinline__ AtnHit resolved(const BvhView& bv, const TraceResult& r)
 {
     AtnHit h;
@@ -350,6 +357,7 @@ struct ClosestPolicy {             // wavefront closest-hit (hitTest)
         pb.hit1[slot] = make_int2(h.objid, h.mtrlid);
         if (mesh_out) mesh_out[slot] = h.meshid;
     }
+    __device__ __forceinline__ void finish_exact(int slot, const AtnHit& h) const { finish_hit(slot, h); }
     __device__ __forceinline__ bool finish(const BvhView& bv, int slot, const TraceResult& r, const Tie& tie) const
     {
         if (tie.any) { if (pend_tag) pb.pend[slot] = pend_tag; return false; }     // the main surface stage leaves this path to the side pass
@@ -399,7 +407,8 @@ struct ShadowPolicy {              // wavefront shadow rays (hitShadowRay)
         *mode = (attrib & 2u) ? EXIT_ANY_HIT : ((attrib & 1u) ? EXIT_HIT_BEFORE : EXIT_NONE);
         *exit_dist = dist;
     }
-    __device__ __forceinline__ void finish_hit(int slot, const AtnHit& h) const
+    template <bool kLate>
+    __device__ __forceinline__ void apply(int slot, const AtnHit& h) const
     {
         const float4 so = pb.sh_o[slot];
         const float4 sd = pb.sh_d[slot];
@@ -407,17 +416,23 @@ struct ShadowPolicy {              // wavefront shadow rays (hitShadowRay)
         const AtnLightParameter& light = sc.lights[__float_as_int(sd.w)];
         Ray sr; sr.org = V3(so.x, so.y, so.z); sr.dir = normalize(V3(sd.x, sd.y, sd.z));
         const bool vis = shadow_visible(sc, light, sr, so.w, h.objid, h.primid, h.a, h.b, h.t, h.mtrlid);
+        float4* dst = kLate ? pb.contrib_late : pb.contrib;
         if (vis) {
-            float4 cc = pb.contrib[slot];
+            float4 cc = dst[slot];
             cc.x += c.x; cc.y += c.y; cc.z += c.z;
-            pb.contrib[slot] = cc;
+            dst[slot] = cc;
         }
         if (kTap) {
             AtnBounceRecord& rec = tap[(size_t)slot * tap_cap + bounce];
             rec.shadow_visible = vis ? 1 : 0;
-            if (vis) { const float4 cc = pb.contrib[slot]; rec.contrib[0] = cc.x; rec.contrib[1] = cc.y; rec.contrib[2] = cc.z; }
+            if (vis) {
+                const float4 cc = pb.contrib[slot]; const float4 l = pb.contrib_late[slot];
+                rec.contrib[0] = cc.x + l.x; rec.contrib[1] = cc.y + l.y; rec.contrib[2] = cc.z + l.z;
+            }
         }
     }
+    __device__ __forceinline__ void finish_hit(int slot, const AtnHit& h) const { apply<false>(slot, h); }
+    __device__ __forceinline__ void finish_exact(int slot, const AtnHit& h) const { apply<true>(slot, h); }
     __device__ __forceinline__ bool finish(const BvhView& bv, int slot, const TraceResult& r, const Tie& tie) const
     {
         const AtnHit h = resolved(bv, r);
@@ -437,6 +452,7 @@ struct QueryClosestPolicy {        // atn_trace_closest
         world(i, o, d); *slot = i; *tm = t_max(i); *mode = EXIT_NONE; *exit_dist = 0.0f;
     }
     __device__ __forceinline__ void finish_hit(int i, const AtnHit& h) const { hits[i] = h; }
+    __device__ __forceinline__ void finish_exact(int i, const AtnHit& h) const { hits[i] = h; }
     __device__ __forceinline__ bool finish(const BvhView& bv, int i, const TraceResult& r, const Tie& tie) const
     {
         if (tie.any) return false;
@@ -455,6 +471,7 @@ struct QueryAnyPolicy {            // atn_trace_any: a singular light at distanc
         world(i, o, d); *slot = i; *tm = t_max(i); *mode = EXIT_HIT_BEFORE; *exit_dist = dist[i];
     }
     __device__ __forceinline__ void finish_hit(int i, const AtnHit& h) const { visible[i] = (h.objid < 0 || h.t > dist[i]) ? 1 : 0; }
+    __device__ __forceinline__ void finish_exact(int i, const AtnHit& h) const { finish_hit(i, h); }
     __device__ __forceinline__ bool finish(const BvhView&, int i, const TraceResult& r, const Tie& tie) const
     {
         // only a tie that straddles the light's distance can change the answer
@@ -526,6 +543,17 @@ __device__ __forceinline__ int2 lds64(uint32_t addr)
     int2 v;
     asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr) : "memory");
     return v;
+}
+
+// Experiment switch: bit 0 = prefetch the subtree chosen by a node step, bit 1 = the one a pop returns.
+#ifndef ATN_PREFETCH
+#define ATN_PREFETCH 0
+#endif
+__device__ __forceinline__ void prefetch_ref(const BvhView& bv, int32_t ref, int32_t cur_inst)
+{
+    const float4* p = ref >= 0 ? bv.nodes + (size_t)ref * 8
+                               : (cur_inst >= 0 ? bv.tris + (size_t)(~ref) * kTriStride : bv.insts + (size_t)(~ref) * kInstStride);
+    asm volatile("prefetch.global.L1 [%0];" :: "l"(p));
 }
 
 // Entry distance and exit distance of the two slots held by one float4 triple of a QuadNode
@@ -621,7 +649,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
     // near-tie bookkeeping of the lane's ray (touched when a triangle is hit, an instance is entered, the ray ends):
     // band rho, band alpha, runner-up distance (any primitive), runner-up distance (other instance / material),
     // material of the best hit
-    __shared__ float s_tie[5 * kTraceBlock];
+    __shared__ float s_tie[6 * kTraceBlock];           // ..., [5] pathmax of the best hit's leaf
     int2 l_stack[kLocalStack];
     const int tid = threadIdx.x;
     const uint32_t stack_base = (uint32_t)__cvta_generic_to_shared(&s_stack[tid]);
@@ -634,6 +662,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
     bool active = false, done = false, exhausted = false;
     int slot = 0, mode = EXIT_NONE, sp = 0, cur = kRefNull, cur_inst = -1;
     float exit_dist = 0.0f, t_cull = kInf;
+    float cur_key = -kInf;            // largest box entry distance on the path from the root to `cur` (pathmax)
     V3 org, dir;
     RayInv ri;
     TraceResult best;
@@ -647,8 +676,11 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
             if (exact_q && best.leaf >= 0) {
                 const Band bd{ s_tie[0 * kTraceBlock + tid], s_tie[1 * kTraceBlock + tid] };
                 tie.band = band_at(bd, best.t);
-                tie.any = s_tie[2 * kTraceBlock + tid] <= best.t + tie.band;
-                tie.cls = Policy::kNeedClass && s_tie[3 * kTraceBlock + tid] <= best.t + tie.band;
+                const float t2 = s_tie[2 * kTraceBlock + tid];
+                // a strictly nearest hit whose whole path starts no later than the runner-up is the reference's answer too
+                const bool certain = best.t < t2 && s_tie[5 * kTraceBlock + tid] <= t2;
+                tie.any = !certain && t2 <= best.t + tie.band;
+                tie.cls = Policy::kNeedClass && tie.any && s_tie[3 * kTraceBlock + tid] <= best.t + tie.band;
             }
             to_exact = !pol.finish(bv, slot, best, tie);
             done = false;
@@ -693,7 +725,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                     }
 #endif
                     sts64(stack_base, kRefDone, __float_as_int(-kInf));     // sentinel: popping it ends the ray
-                    sp = 1; cur = bv.top_root; cur_inst = -1;
+                    sp = 1; cur = bv.top_root; cur_inst = -1; cur_key = -kInf;
                     active = true;
                 }
             }
@@ -765,9 +797,18 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                 const bool h2 = k2 <= fminf(pb.t1a, t_cull);
                 const bool h3 = k3 <= fminf(pb.t1b, t_cull);
                 const int nhit = (int)h0 + (int)h1 + (int)h2 + (int)h3;
-                k0 = h0 ? k0 : kInf; k1 = h1 ? k1 : kInf; k2 = h2 ? k2 : kInf; k3 = h3 ? k3 : kInf;
+                // (taking the path maximum only for the slots that are kept -- the followed one and the pushed ones -- instead
+                // of all four measured the same: 1 806 vs 1 807 Mrays/s)
+                k0 = h0 ? fmaxf(k0, cur_key) : kInf; k1 = h1 ? fmaxf(k1, cur_key) : kInf;       // pathmax keys
+                k2 = h2 ? fmaxf(k2, cur_key) : kInf; k3 = h3 ? fmaxf(k3, cur_key) : kInf;
                 ATN_CE(k0, r0, k1, r1) ATN_CE(k2, r2, k3, r3) ATN_CE(k0, r0, k2, r2) ATN_CE(k1, r1, k3, r3) ATN_CE(k1, r1, k2, r2)
                 cur = nhit ? r0 : kRefNull;
+                cur_key = k0;
+#if ATN_PREFETCH & 1
+                // the chosen subtree's record is fetched at the top of the next iteration, after the triangle / entry / pop
+                // phases of the other lanes: start moving it towards the L1 now
+                if (!kStream && nhit) prefetch_ref(bv, cur, cur_inst);
+#endif
                 const int np_ = nhit - 1;                 // entries left behind, nearest on top
                 if (np_ > 0) {
                     if (sp + np_ <= kSmemStack) {
@@ -824,6 +865,8 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                     // comparison; the shared-memory update below runs for actual near ties only.
                     float t2 = kInf;                           // distance of the hit that is NOT the best afterwards, if it can tie
                     float nc = t_cull;
+                    // another SBVH leaf of the best primitive gives the same t, a, b bit for bit: not a runner-up
+                    const bool same = best.leaf >= 0 && h.t == best.t && h.a == best.a && h.b == best.b;
                     if (closer) {
                         const Band bd{ s_tie[0 * kTraceBlock + tid], s_tie[1 * kTraceBlock + tid] };
                         nc = cull_bound(bd, h.t);
@@ -832,9 +875,8 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                     }
                     else if (h.t <= t_cull) t2 = h.t;
 #ifndef ATN_EXP_NO_T2
+                    if (same) s_tie[5 * kTraceBlock + tid] = fminf(s_tie[5 * kTraceBlock + tid], cur_key);   // the easier path to the best primitive counts
                     if (t2 < kInf) {
-                        // another SBVH leaf of the best primitive gives the same t, a, b bit for bit: not a runner-up
-                        const bool same = h.t == best.t && h.a == best.a && h.b == best.b;
                         if (!same) {
                             s_tie[2 * kTraceBlock + tid] = fminf(s_tie[2 * kTraceBlock + tid], t2);
                             if (Policy::kNeedClass && (cur_inst != best.inst || __float_as_int(b.w) != __float_as_int(s_tie[4 * kTraceBlock + tid])))
@@ -845,6 +887,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                     if (closer) {
                         best.t = h.t; best.a = h.a; best.b = h.b; best.leaf = leaf; best.inst = cur_inst;
                         t_cull = nc;
+                        if (!same) s_tie[5 * kTraceBlock + tid] = cur_key;
                         if (Policy::kNeedClass) s_tie[4 * kTraceBlock + tid] = b.w;        // material of the best hit
                     }
                 }
@@ -912,7 +955,10 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                         sp--;
                         e = (sp < kSmemStack) ? lds64(stack_base + (uint32_t)sp * kStackStride) : l_stack[sp - kSmemStack];
                     } while (__int_as_float(e.y) > t_cull);
-                    cur = e.x;
+                    cur = e.x; cur_key = __int_as_float(e.y);
+#if ATN_PREFETCH & 2
+                    if (!kStream && cur > kRefDone) prefetch_ref(bv, cur, cur_inst);
+#endif
                     if (cur != kRefExit) break;
                     // back to the top layer with the world ray (threaded_bvh_traverser.h:290-300), then pop again
                     cur_inst = -1;
@@ -1054,7 +1100,7 @@ k_exact(RefView rv, Policy pol, const int32_t* __restrict__ exact_q, const int32
         const int slot = exact_q[i];
         V3 o, d;
         pol.world(slot, &o, &d);
-        pol.finish_hit(slot, ref_traverse(rv, o, d, pol.t_max(slot)));
+        pol.finish_exact(slot, ref_traverse(rv, o, d, pol.t_max(slot)));
     }
 }
 
@@ -1140,6 +1186,7 @@ __global__ void k_generate(FrameParams fp, AtnCameraParameter cam, const uint32_
                 pb.ray_d[s] = make_float4(r.dir.x, r.dir.y, r.dir.z, 0.0f);
                 pb.throughput[s] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
                 pb.contrib[s] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
+                pb.contrib_late[s] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                 pb.sampler_dim[s] = sp.dim;
                 pb.flags[s] = 0u;
                 pb.pend[s] = 0;
@@ -1165,7 +1212,7 @@ __global__ void k_generate(FrameParams fp, AtnCameraParameter cam, const uint32_
 #endif
 constexpr int kShadeBlock = 128;
 #ifndef ATN_WAVEFRONT_PATHS
-#define ATN_WAVEFRONT_PATHS (8 * 1024 * 1024)     // paths per wavefront the sample batching aims at
+#define ATN_WAVEFRONT_PATHS (32 * 1024 * 1024)    // paths per wavefront the sample batching aims at (8 M: -1.1 % on the bench frame)
 #endif
 #ifndef ATN_MAX_BATCH
 #define ATN_MAX_BATCH 16
@@ -1195,6 +1242,135 @@ __device__ __forceinline__ Sampler path_sampler(const FrameParams& fp, const uin
 // hit evaluation + material + implicit light for hits.  Survivors go to q_lit with a Surface record.
 // kSvgf: aten::SVGFRenderer::Shade instead of PathTracing::shade (see shade_surface); `w2c` is then the
 // world-to-clip matrix of the frame and pb.aov_nd / pb.aov_am point at the current SVGF AOV set.
+// The three stages of one path, as device functions: the wavefront kernels below run one stage over a queue, the side
+// pass (k_side) runs all three for a path right after the exact walk has decided its hit.
+template <bool kTap, bool kSvgf>
+__device__ __forceinline__ bool surface_stage(const FrameParams& fp, const AtnCameraParameter& cam, const SceneView& sc, const PathBuffers& pb,
+                                              int slot, int bounce, AtnBounceRecord* tap, int tap_cap, const AtnMat4& w2c)
+{
+    const float4 o = pb.ray_o[slot];
+    const float4 d = pb.ray_d[slot];
+    const float4 h0 = pb.hit0[slot];
+    const int2 h1 = pb.hit1[slot];
+    const float4 th = pb.throughput[slot];
+    const float4 cb = pb.contrib[slot];
+    const uint32_t fl = pb.flags[slot];
+    Ray ray; ray.org = V3(o.x, o.y, o.z); ray.dir = V3(d.x, d.y, d.z);
+    PathState st;
+    st.throughput = V3(th.x, th.y, th.z); st.pdfb = th.w;
+    st.contrib = V3(cb.x, cb.y, cb.z);
+    st.terminated = false;
+    st.singular = (fl & 2u) != 0u;
+    st.last_specular = (fl & 4u) != 0u;
+    // AOVs of the first hit are kept per pixel (the reference indexes them by pixel too)
+    // (of the last sample of a batch: the buffers hold "the last sample rendered")
+    const SlotInfo si = slot_info(fp, slot);
+    const int pix = si.pix;
+    const bool aov = bounce <= 1 && si.k == fp.batch - 1;
+    AtnVec4* aov_nd = aov ? reinterpret_cast<AtnVec4*>(pb.aov_nd) + pix : nullptr;
+    AtnVec4* aov_am = aov ? reinterpret_cast<AtnVec4*>(pb.aov_am) + pix : nullptr;
+    bool lit = false;
+    if (h1.x >= 0) {
+        Surface sf;
+        lit = shade_surface(sc, ray, h1.x, __float_as_int(h0.w), h0.y, h0.z, h0.x, h1.y, bounce, &st, &sf,
+                            aov_nd, aov_am, bounce == 0 ? pb.hit_mesh[slot] : -1, kSvgf ? &w2c : nullptr);
+        if (lit) {
+            pb.surf0[slot] = make_float4(sf.p.x, sf.p.y, sf.p.z, sf.u);
+            pb.surf1[slot] = make_float4(sf.n.x, sf.n.y, sf.n.z, sf.v);
+            pb.surf2[slot] = make_float4(sf.albedo.x, sf.albedo.y, sf.albedo.z, __int_as_float(sf.mtrlid));
+        }
+    }
+    else {
+        shade_miss(sc, cam, si.ix, si.iy, fp.width, fp.height, bounce, ray, &st, aov_nd, aov_am);
+    }
+    if (!lit) {
+        pb.contrib[slot] = make_float4(st.contrib.x, st.contrib.y, st.contrib.z, cb.w);
+        pb.flags[slot] = 1u | (st.singular ? 2u : 0u);
+    }
+    if (kTap) {
+        AtnBounceRecord& rec = tap[(size_t)slot * tap_cap + bounce];
+        rec.ray.org = AtnVec3{ o.x, o.y, o.z };
+        rec.ray.dir = AtnVec3{ d.x, d.y, d.z };
+        rec.hit.t = h0.x; rec.hit.objid = h1.x; rec.hit.mtrlid = h1.y; rec.hit.meshid = -1;
+        rec.hit.primid = __float_as_int(h0.w); rec.hit.a = h0.y; rec.hit.b = h0.z; rec.hit.isVoxel = 0;
+        rec.throughput[0] = st.throughput.x; rec.throughput[1] = st.throughput.y; rec.throughput[2] = st.throughput.z;
+        rec.pdfb = st.pdfb;
+        rec.contrib[0] = st.contrib.x; rec.contrib[1] = st.contrib.y; rec.contrib[2] = st.contrib.z;
+        rec.flags = 1 | (lit ? 0 : 2);
+    }
+    return lit;
+}
+
+__device__ __forceinline__ void nee_stage(const FrameParams& fp, const SceneView& sc, const uint32_t* __restrict__ seeds, const PathBuffers& pb, int slot)
+{
+    const float4 d = pb.ray_d[slot];
+    const float4 s0 = pb.surf0[slot];
+    const float4 s1 = pb.surf1[slot];
+    const float4 s2 = pb.surf2[slot];
+    const float4 th = pb.throughput[slot];
+    Surface sf;
+    sf.p = V3(s0.x, s0.y, s0.z); sf.u = s0.w; sf.n = V3(s1.x, s1.y, s1.z); sf.v = s1.w;
+    sf.albedo = V3(s2.x, s2.y, s2.z); sf.mtrlid = __float_as_int(s2.w);
+    PathState st;
+    st.throughput = V3(th.x, th.y, th.z); st.pdfb = th.w;
+    st.sampler = path_sampler(fp, seeds, pb, slot);
+    ShadowRayOut sh;
+    shade_nee(sc, V3(d.x, d.y, d.z), sf, &st, &sh);
+    pb.sampler_dim[slot] = st.sampler.dim;
+    // dist < 0 marks "no shadow ray"
+    pb.sh_o[slot] = make_float4(sh.org.x, sh.org.y, sh.org.z, sh.active ? sh.dist : -1.0f);
+    if (sh.active) pb.sh_d[slot] = make_float4(sh.dir.x, sh.dir.y, sh.dir.z, __int_as_float(sh.light_id));
+    // ShadowRay::lightcontrib is reset whenever a light was sampled (FillShadowRay, pathtracing_impl.h:241) and stays
+    // in the buffer: the ReSTIR visibility step of the next frame adds it again (restir_shadow_ray)
+    if (sh.sampled) pb.sh_c[slot] = make_float4(sh.lightcontrib.x, sh.lightcontrib.y, sh.lightcontrib.z, 0.0f);
+}
+
+template <bool kTap>
+__device__ __forceinline__ void bsdf_stage(const FrameParams& fp, const SceneView& sc, const uint32_t* __restrict__ seeds, const PathBuffers& pb,
+                                           int slot, int bounce, AtnBounceRecord* tap, int tap_cap, bool* cont_out, bool* shadow_out)
+{
+    const float4 d = pb.ray_d[slot];
+    const float4 s0 = pb.surf0[slot];
+    const float4 s1 = pb.surf1[slot];
+    const float4 s2 = pb.surf2[slot];
+    const float4 th = pb.throughput[slot];
+    const uint32_t fl = pb.flags[slot];
+    Surface sf;
+    sf.p = V3(s0.x, s0.y, s0.z); sf.u = s0.w; sf.n = V3(s1.x, s1.y, s1.z); sf.v = s1.w;
+    sf.albedo = V3(s2.x, s2.y, s2.z); sf.mtrlid = __float_as_int(s2.w);
+    PathState st;
+    st.throughput = V3(th.x, th.y, th.z); st.pdfb = th.w;
+    st.sampler = path_sampler(fp, seeds, pb, slot);
+    st.terminated = false;
+    st.singular = (fl & 2u) != 0u;
+    Ray next; next.org = sf.p; next.dir = V3(d.x, d.y, d.z);
+    shade_bsdf(sc, V3(d.x, d.y, d.z), sf, bounce, fp.rr_bounce, &st, &next);
+    const bool cont = !st.terminated && (bounce + 1 < fp.max_bounce);
+    const bool shadow = !st.terminated && pb.sh_o[slot].w >= 0.0f;
+    pb.throughput[slot] = make_float4(st.throughput.x, st.throughput.y, st.throughput.z, st.pdfb);
+    pb.sampler_dim[slot] = st.sampler.dim;
+    pb.flags[slot] = (st.terminated ? 1u : 0u) | (st.singular ? 2u : 0u) | (st.last_specular ? 4u : 0u);
+    if (cont) {
+        pb.ray_o[slot] = make_float4(next.org.x, next.org.y, next.org.z, 0.0f);
+        pb.ray_d[slot] = make_float4(next.dir.x, next.dir.y, next.dir.z, 0.0f);
+    }
+    if (kTap) {
+        AtnBounceRecord& rec = tap[(size_t)slot * tap_cap + bounce];
+        rec.shadow_active = shadow ? 1 : 0;
+        rec.shadow_visible = 0;
+        if (shadow) {
+            const float4 so = pb.sh_o[slot]; const float4 sd = pb.sh_d[slot]; const float4 sc4 = pb.sh_c[slot];
+            rec.shadow_org[0] = so.x; rec.shadow_org[1] = so.y; rec.shadow_org[2] = so.z; rec.shadow_dist = so.w;
+            rec.shadow_dir[0] = sd.x; rec.shadow_dir[1] = sd.y; rec.shadow_dir[2] = sd.z;
+            rec.light_contrib[0] = sc4.x; rec.light_contrib[1] = sc4.y; rec.light_contrib[2] = sc4.z;
+        }
+        rec.throughput[0] = st.throughput.x; rec.throughput[1] = st.throughput.y; rec.throughput[2] = st.throughput.z;
+        rec.pdfb = st.pdfb;
+        rec.flags = 1 | (st.terminated ? 2 : 0);
+    }
+    *cont_out = cont; *shadow_out = shadow;
+}
+
 template <bool kTap, bool kSvgf>
 __global__ void __launch_bounds__(kShadeBlock, ATN_SURFACE_MIN_BLOCKS)
 k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, ShadeQueues sq, int bounce,
@@ -1209,57 +1385,9 @@ k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, 
         int slot = 0;
         if (i < count) {
             slot = q_in ? q_in[i] : i;
-            const float4 o = pb.ray_o[slot];
-            const float4 d = pb.ray_d[slot];
-            const float4 h0 = pb.hit0[slot];
-            const int2 h1 = pb.hit1[slot];
-            const float4 th = pb.throughput[slot];
-            const float4 cb = pb.contrib[slot];
-            const uint32_t fl = pb.flags[slot];
-            const bool pending = sq.skip_tag != 0 && pb.pend[slot] == sq.skip_tag;     // its hit comes from the exact walk: shaded by the side pass
-            Ray ray; ray.org = V3(o.x, o.y, o.z); ray.dir = V3(d.x, d.y, d.z);
-            PathState st;
-            st.throughput = V3(th.x, th.y, th.z); st.pdfb = th.w;
-            st.contrib = V3(cb.x, cb.y, cb.z);
-            st.terminated = false;
-            st.singular = (fl & 2u) != 0u;
-            st.last_specular = (fl & 4u) != 0u;
-            // AOVs of the first hit are kept per pixel (the reference indexes them by pixel too)
-            // (of the last sample of a batch: the buffers hold "the last sample rendered")
-            const SlotInfo si = slot_info(fp, slot);
-            const int pix = si.pix;
-            const bool aov = bounce <= 1 && si.k == fp.batch - 1;
-            AtnVec4* aov_nd = aov ? reinterpret_cast<AtnVec4*>(pb.aov_nd) + pix : nullptr;
-            AtnVec4* aov_am = aov ? reinterpret_cast<AtnVec4*>(pb.aov_am) + pix : nullptr;
-            if (pending) {}
-            else if (h1.x >= 0) {
-                Surface sf;
-                lit = shade_surface(sc, ray, h1.x, __float_as_int(h0.w), h0.y, h0.z, h0.x, h1.y, bounce, &st, &sf,
-                                    aov_nd, aov_am, bounce == 0 ? pb.hit_mesh[slot] : -1, kSvgf ? &w2c : nullptr);
-                if (lit) {
-                    pb.surf0[slot] = make_float4(sf.p.x, sf.p.y, sf.p.z, sf.u);
-                    pb.surf1[slot] = make_float4(sf.n.x, sf.n.y, sf.n.z, sf.v);
-                    pb.surf2[slot] = make_float4(sf.albedo.x, sf.albedo.y, sf.albedo.z, __int_as_float(sf.mtrlid));
-                }
-            }
-            else {
-                shade_miss(sc, cam, si.ix, si.iy, fp.width, fp.height, bounce, ray, &st, aov_nd, aov_am);
-            }
-            if (!lit && !pending) {
-                pb.contrib[slot] = make_float4(st.contrib.x, st.contrib.y, st.contrib.z, cb.w);
-                pb.flags[slot] = 1u | (st.singular ? 2u : 0u);
-            }
-            if (kTap && !pending) {
-                AtnBounceRecord& rec = tap[(size_t)slot * tap_cap + bounce];
-                rec.ray.org = AtnVec3{ o.x, o.y, o.z };
-                rec.ray.dir = AtnVec3{ d.x, d.y, d.z };
-                rec.hit.t = h0.x; rec.hit.objid = h1.x; rec.hit.mtrlid = h1.y; rec.hit.meshid = -1;
-                rec.hit.primid = __float_as_int(h0.w); rec.hit.a = h0.y; rec.hit.b = h0.z; rec.hit.isVoxel = 0;
-                rec.throughput[0] = st.throughput.x; rec.throughput[1] = st.throughput.y; rec.throughput[2] = st.throughput.z;
-                rec.pdfb = st.pdfb;
-                rec.contrib[0] = st.contrib.x; rec.contrib[1] = st.contrib.y; rec.contrib[2] = st.contrib.z;
-                rec.flags = 1 | (lit ? 0 : 2);
-            }
+            // a path whose hit comes from the exact walk is the side pass's (k_side)
+            const bool pending = sq.skip_tag != 0 && pb.pend[slot] == sq.skip_tag;
+            if (!pending) lit = surface_stage<kTap, kSvgf>(fp, cam, sc, pb, slot, bounce, tap, tap_cap, w2c);
         }
         const int pos = warp_append(lit, sq.n_lit);
         if (lit) sq.q_lit[pos] = slot;
@@ -1272,29 +1400,8 @@ __global__ void __launch_bounds__(kShadeBlock, ATN_NEE_MIN_BLOCKS)
 k_nee(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb, ShadeQueues sq, int bounce)
 {
     const int count = *sq.n_lit;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-        const int slot = sq.q_lit[i];
-        const float4 d = pb.ray_d[slot];
-        const float4 s0 = pb.surf0[slot];
-        const float4 s1 = pb.surf1[slot];
-        const float4 s2 = pb.surf2[slot];
-        const float4 th = pb.throughput[slot];
-        Surface sf;
-        sf.p = V3(s0.x, s0.y, s0.z); sf.u = s0.w; sf.n = V3(s1.x, s1.y, s1.z); sf.v = s1.w;
-        sf.albedo = V3(s2.x, s2.y, s2.z); sf.mtrlid = __float_as_int(s2.w);
-        PathState st;
-        st.throughput = V3(th.x, th.y, th.z); st.pdfb = th.w;
-        st.sampler = path_sampler(fp, seeds, pb, slot);
-        ShadowRayOut sh;
-        shade_nee(sc, V3(d.x, d.y, d.z), sf, &st, &sh);
-        pb.sampler_dim[slot] = st.sampler.dim;
-        // dist < 0 marks "no shadow ray"
-        pb.sh_o[slot] = make_float4(sh.org.x, sh.org.y, sh.org.z, sh.active ? sh.dist : -1.0f);
-        if (sh.active) pb.sh_d[slot] = make_float4(sh.dir.x, sh.dir.y, sh.dir.z, __int_as_float(sh.light_id));
-        // ShadowRay::lightcontrib is reset whenever a light was sampled (FillShadowRay, pathtracing_impl.h:241) and stays
-        // in the buffer: the ReSTIR visibility step of the next frame adds it again (restir_shadow_ray)
-        if (sh.sampled) pb.sh_c[slot] = make_float4(sh.lightcontrib.x, sh.lightcontrib.y, sh.lightcontrib.z, 0.0f);
-    }
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+        nee_stage(fp, sc, seeds, pb, sq.q_lit[i]);
 }
 
 // Stage 3, lit paths: Russian roulette, BSDF sampling, next ray; queues the next bounce and the
@@ -1313,50 +1420,41 @@ k_bsdf(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuf
         int slot = 0;
         if (i < count) {
             slot = sq.q_lit[i];
-            const float4 d = pb.ray_d[slot];
-            const float4 s0 = pb.surf0[slot];
-            const float4 s1 = pb.surf1[slot];
-            const float4 s2 = pb.surf2[slot];
-            const float4 th = pb.throughput[slot];
-            const uint32_t fl = pb.flags[slot];
-            Surface sf;
-            sf.p = V3(s0.x, s0.y, s0.z); sf.u = s0.w; sf.n = V3(s1.x, s1.y, s1.z); sf.v = s1.w;
-            sf.albedo = V3(s2.x, s2.y, s2.z); sf.mtrlid = __float_as_int(s2.w);
-            PathState st;
-            st.throughput = V3(th.x, th.y, th.z); st.pdfb = th.w;
-            st.sampler = path_sampler(fp, seeds, pb, slot);
-            st.terminated = false;
-            st.singular = (fl & 2u) != 0u;
-            Ray next; next.org = sf.p; next.dir = V3(d.x, d.y, d.z);
-            shade_bsdf(sc, V3(d.x, d.y, d.z), sf, bounce, fp.rr_bounce, &st, &next);
-            cont = !st.terminated && (bounce + 1 < fp.max_bounce);
-            shadow = !st.terminated && pb.sh_o[slot].w >= 0.0f;
-            pb.throughput[slot] = make_float4(st.throughput.x, st.throughput.y, st.throughput.z, st.pdfb);
-            pb.sampler_dim[slot] = st.sampler.dim;
-            pb.flags[slot] = (st.terminated ? 1u : 0u) | (st.singular ? 2u : 0u) | (st.last_specular ? 4u : 0u);
-            if (cont) {
-                pb.ray_o[slot] = make_float4(next.org.x, next.org.y, next.org.z, 0.0f);
-                pb.ray_d[slot] = make_float4(next.dir.x, next.dir.y, next.dir.z, 0.0f);
-            }
-            if (kTap) {
-                AtnBounceRecord& rec = tap[(size_t)slot * tap_cap + bounce];
-                rec.shadow_active = shadow ? 1 : 0;
-                rec.shadow_visible = 0;
-                if (shadow) {
-                    const float4 so = pb.sh_o[slot]; const float4 sd = pb.sh_d[slot]; const float4 sc4 = pb.sh_c[slot];
-                    rec.shadow_org[0] = so.x; rec.shadow_org[1] = so.y; rec.shadow_org[2] = so.z; rec.shadow_dist = so.w;
-                    rec.shadow_dir[0] = sd.x; rec.shadow_dir[1] = sd.y; rec.shadow_dir[2] = sd.z;
-                    rec.light_contrib[0] = sc4.x; rec.light_contrib[1] = sc4.y; rec.light_contrib[2] = sc4.z;
-                }
-                rec.throughput[0] = st.throughput.x; rec.throughput[1] = st.throughput.y; rec.throughput[2] = st.throughput.z;
-                rec.pdfb = st.pdfb;
-                rec.flags = 1 | (st.terminated ? 2 : 0);
-            }
+            bsdf_stage<kTap>(fp, sc, seeds, pb, slot, bounce, tap, tap_cap, &cont, &shadow);
         }
         const int pos = warp_append(cont, &cnt->n_active[bounce + 1]);
         if (cont) q_out[pos] = slot;
         const int spos = warp_append(shadow, &cnt->n_shadow[bounce]);
         if (shadow) pb.q_shadow[spos] = slot;
+    }
+}
+
+// The side pass of a bounce (launch_bounces): the paths whose closest hit depends on a near tie.  One thread per path: the
+// reference's own walk decides the hit (ref_traverse), then the three shade stages run for that path right here, and the
+// path joins the next bounce's queue and the shadow queue like any other.  One launch, so that it is done long before
+// the main shade stage it runs next to.
+template <bool kSvgf>
+__global__ void __launch_bounds__(128)
+k_side(RefView rv, ClosestPolicy pol, FrameParams fp, AtnCameraParameter cam, SceneView sc, const uint32_t* __restrict__ seeds,
+       PathBuffers pb, Counters* cnt, int bounce, AtnMat4 w2c)
+{
+#ifdef ATN_EXP_EXACT_NOOP
+    const int count = 0;
+#else
+    const int count = cnt->n_exact_closest[bounce];
+#endif
+    int32_t* __restrict__ q_out = pb.queue[(bounce + 1) & 1];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const int slot = pb.q_exact[i];
+        V3 o, d;
+        pol.world(slot, &o, &d);
+        pol.finish_hit(slot, ref_traverse(rv, o, d, pol.t_max(slot)));
+        if (!surface_stage<false, kSvgf>(fp, cam, sc, pb, slot, bounce, nullptr, 0, w2c)) continue;
+        nee_stage(fp, sc, seeds, pb, slot);
+        bool cont, shadow;
+        bsdf_stage<false>(fp, sc, seeds, pb, slot, bounce, nullptr, 0, &cont, &shadow);
+        if (cont) q_out[atomicAdd(&cnt->n_active[bounce + 1], 1)] = slot;
+        if (shadow) pb.q_shadow[atomicAdd(&cnt->n_shadow[bounce], 1)] = slot;
     }
 }
 
@@ -1474,8 +1572,8 @@ __global__ void k_svgf_prepare(FrameParams fp, PathBuffers pb, SvgfView sv, int 
         totals->closest += c; totals->shadow += s; totals->exact += e;
     }
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const float4 c = pb.contrib[i];
-        AtnVec4 cc; cc.x = c.x; cc.y = c.y; cc.z = c.z; cc.w = c.w;
+        const float4 c = pb.contrib[i]; const float4 l = pb.contrib_late[i];
+        AtnVec4 cc; cc.x = c.x + l.x; cc.y = c.y + l.y; cc.z = c.z + l.z; cc.w = c.w;
         svgf_prepare(first_frame != 0, i, cc, sv.temporary, sv.cur);
     }
 }
@@ -1484,8 +1582,8 @@ __global__ void k_svgf_temporal(FrameParams fp, PathBuffers pb, SvgfView sv)
 {
     const int n = fp.width * fp.height;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const float4 c = pb.contrib[i];
-        AtnVec4 cc; cc.x = c.x; cc.y = c.y; cc.z = c.z; cc.w = c.w;
+        const float4 c = pb.contrib[i]; const float4 l = pb.contrib_late[i];
+        AtnVec4 cc; cc.x = c.x + l.x; cc.y = c.y + l.y; cc.z = c.z + l.z; cc.w = c.w;
         svgf_temporal(i % fp.width, i / fp.width, fp.width, fp.height, 0.98f, 0.05f, cc, sv.cur, sv.prev, sv.motion_depth);
     }
 }
@@ -1692,6 +1790,7 @@ struct RestirShadowPolicy {
         }
         restir_visibility_result(&res[slot], vis);
     }
+    __device__ __forceinline__ void finish_exact(int slot, const AtnHit& h) const { finish_hit(slot, h); }     // same stream, in order
     __device__ __forceinline__ bool finish(const BvhView& bv, int slot, const TraceResult& r, const Tie& tie) const
     {
         const AtnHit h = resolved(bv, r);
@@ -1772,7 +1871,8 @@ __global__ void k_gather(FrameParams fp, PathBuffers pb, float4* image, int mode
         float4 cur = image[iy * fp.width + ix];
         if (mode == ATN_GATHER_OVERWRITE && first) cur = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         for (int k = 0; k < fp.batch; k++) {          // the samples of the batch, in sample order
-            const float4 c = pb.contrib[(size_t)k * n + s];
+            float4 c = pb.contrib[(size_t)k * n + s];
+            { const float4 l = pb.contrib_late[(size_t)k * n + s]; c.x += l.x; c.y += l.y; c.z += l.z; }
             if (mode == ATN_GATHER_PROGRESSIVE) {
                 const float nn = (float)((int32_t)cur.w);
                 const float cx = c.x / 1.0f, cy = c.y / 1.0f, cz = c.z / 1.0f;   // col /= cnt, cnt = 1
@@ -1845,7 +1945,7 @@ struct AtnRenderer {
     RefView rv{};
     int exact_ties{ 1 };               // 0: near ties are left as the front-to-back walk found them (atn_set_exact_ties)
     int exact_grid{ 148 * 4 };
-    DevBuf<int32_t> q_exact, q_exact_s, q_lit_side, q_exact_query;
+    DevBuf<int32_t> q_exact, q_exact_s, q_exact_query;
     // The exact walk is a latency-bound tail (a few thousand rays, hundreds of dependent steps each).  In the bounce loop it
     // runs on a second stream next to the main kernels instead of between them (launch_bounces).
     cudaStream_t side_stream{ nullptr };
@@ -1863,7 +1963,7 @@ struct AtnRenderer {
     size_t node_capacity{ 0 };          // QuadNodes the device array holds (bottom trees + room for the top layer)
 
     // path state
-    DevBuf<float4> ray_o, ray_d, hit0, throughput, contrib, sh_o, sh_d, sh_c, image;
+    DevBuf<float4> ray_o, ray_d, hit0, throughput, contrib, contrib_late, sh_o, sh_d, sh_c, image;
     DevBuf<int2> hit1;
     DevBuf<uint32_t> sampler_dim, flags;
     DevBuf<int32_t> hit_mesh;
@@ -2068,12 +2168,12 @@ static float scene_radius_of(const AtnSceneConfig& cfg)
 static int alloc_paths(AtnRenderer* r, size_t n, size_t pixels)
 {
     CUDA_TRY(r->ray_o.resize(n)); CUDA_TRY(r->ray_d.resize(n)); CUDA_TRY(r->hit0.resize(n)); CUDA_TRY(r->hit1.resize(n));
-    CUDA_TRY(r->throughput.resize(n)); CUDA_TRY(r->contrib.resize(n)); CUDA_TRY(r->sampler_dim.resize(n));
+    CUDA_TRY(r->throughput.resize(n)); CUDA_TRY(r->contrib.resize(n)); CUDA_TRY(r->contrib_late.resize(n)); CUDA_TRY(r->sampler_dim.resize(n));
     CUDA_TRY(r->flags.resize(n)); CUDA_TRY(r->queue0.resize(n)); CUDA_TRY(r->queue1.resize(n));
     CUDA_TRY(r->sh_o.resize(n)); CUDA_TRY(r->sh_d.resize(n)); CUDA_TRY(r->sh_c.resize(n));
     CUDA_TRY(cudaMemsetAsync(r->sh_c.p, 0, n * sizeof(float4), r->stream));      // ShadowRay::lightcontrib starts at zero
     CUDA_TRY(r->q_lit.resize(n)); CUDA_TRY(r->q_shadow.resize(n)); CUDA_TRY(r->q_exact.resize(n));
-    CUDA_TRY(r->q_exact_s.resize(n)); CUDA_TRY(r->q_lit_side.resize(n)); CUDA_TRY(r->pend.resize(n));
+    CUDA_TRY(r->q_exact_s.resize(n)); CUDA_TRY(r->pend.resize(n));
     CUDA_TRY(r->hit_mesh.resize(n)); CUDA_TRY(r->aov_nd.resize(pixels)); CUDA_TRY(r->aov_am.resize(pixels));    // AOVs are per pixel
     CUDA_TRY(r->surf0.resize(n)); CUDA_TRY(r->surf1.resize(n)); CUDA_TRY(r->surf2.resize(n));
     CUDA_TRY(r->counters.resize(1));
@@ -2081,10 +2181,10 @@ static int alloc_paths(AtnRenderer* r, size_t n, size_t pixels)
     CUDA_TRY(r->visits.resize(1));
     PathBuffers& pb = r->pb;
     pb.ray_o = r->ray_o.p; pb.ray_d = r->ray_d.p; pb.hit0 = r->hit0.p; pb.hit1 = r->hit1.p;
-    pb.throughput = r->throughput.p; pb.contrib = r->contrib.p; pb.sampler_dim = r->sampler_dim.p; pb.flags = r->flags.p;
+    pb.throughput = r->throughput.p; pb.contrib = r->contrib.p; pb.contrib_late = r->contrib_late.p; pb.sampler_dim = r->sampler_dim.p; pb.flags = r->flags.p;
     pb.queue[0] = r->queue0.p; pb.queue[1] = r->queue1.p;
     pb.sh_o = r->sh_o.p; pb.sh_d = r->sh_d.p; pb.sh_c = r->sh_c.p;
-    pb.q_lit = r->q_lit.p; pb.q_shadow = r->q_shadow.p; pb.q_exact = r->q_exact.p; pb.q_exact_s = r->q_exact_s.p; pb.q_lit_side = r->q_lit_side.p; pb.pend = r->pend.p;
+    pb.q_lit = r->q_lit.p; pb.q_shadow = r->q_shadow.p; pb.q_exact = r->q_exact.p; pb.q_exact_s = r->q_exact_s.p; pb.pend = r->pend.p;
     pb.hit_mesh = r->hit_mesh.p; pb.aov_nd = r->aov_nd.p; pb.aov_am = r->aov_am.p;
     pb.surf0 = r->surf0.p; pb.surf1 = r->surf1.p; pb.surf2 = r->surf2.p;
     return ATN_OK;
@@ -2265,8 +2365,8 @@ ATN_API int atn_upload_scene(AtnRenderer* r, const AtnSceneBlob* scene, const At
     r->camera = *camera;
     r->width = width; r->height = height;
     const size_t n = (size_t)width * height;
-    // path buffers for a wavefront of about 8 M paths (what a 4K frame gives by itself): up to kMaxBatch samples of a
-    // smaller frame are traced together (slot_info); ~216 B per path, 1.8 GB at the cap
+    // path buffers for a wavefront of about 32 M paths (four samples of a 4K frame, all sixteen of a 1080p one): up to
+    // kMaxBatch samples are traced together (slot_info); ~250 B per path, 8 GB at the cap
     r->batch_cap = (int)std::max<size_t>(1, std::min<size_t>((size_t)ATN_MAX_BATCH, ((size_t)ATN_WAVEFRONT_PATHS + n / 2) / n));
     r->path_capacity = n * (size_t)r->batch_cap;
     rc = alloc_paths(r, r->path_capacity, n);
@@ -2442,12 +2542,13 @@ ATN_API int atn_synchronize(AtnRenderer* r)
 // of a frame); so it runs NEXT to them, on a second stream:
 //
 //   main:  trace closest b | surface  nee  bsdf (paths with a decided hit) | trace shadow b | trace closest b+1 | surface b+1 ...
-//   side:                  | exact closest b, surface' nee' bsdf' (its paths) |              | exact shadow b    |
+//   side:                  | k_side b: exact walk + the three stages, its paths  |              | exact shadow b    |
 //
 // A path whose closest hit is with the exact walk is marked (kHitPending), left alone by the main shade kernels and shaded
-// by the side pass -- the same kernels over the exact queue -- which appends to the same next-bounce and shadow queues; the
+// by the side pass (k_side: one launch, one thread per path), which appends to the same next-bounce and shadow queues; the
 // main stream waits for the side pass before it traces the shadow rays.  The shadow rays of the exact walk only add to
-// their own paths' contributions: they are done next to the next bounce's closest-hit traversal, before its shade stage.
+// their own paths' contributions, into a buffer of their own (contrib_late) that the gather folds in: nothing waits for
+// them before the gather.
 // With the bounce tap on (parity runs) everything stays on one stream.
 static cudaEvent_t side_event(AtnRenderer* r, size_t i)
 {
@@ -2466,7 +2567,7 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
     AtnMat4 w2c;
     for (int i = 0; i < 16; i++) w2c.m[i] = svgf_w2c ? svgf_w2c->m[i] : 0.0f;
     const bool overlap = r->exact_ties && !tap_now;
-    const int side_grid = r->sm_count * 2;
+    const int side_grid = r->sm_count * 4;
     size_t se = 0;
     cudaEvent_t shadow_done = nullptr;            // side stream: the exact walk of the previous bounce's shadow rays
     for (int b = first_bounce; b < fp.max_bounce; b++) {
@@ -2474,7 +2575,6 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
         const int32_t* q = (b == 0 && fp.tile == 0) ? nullptr : pb.queue[b & 1];
         const float tmax = (b == 0) ? kInf : r->hit_distance_limit;
         const ShadeQueues mainq{ q, &c->n_active[b], pb.q_lit, &c->n_lit[b], overlap ? b + 1 : 0 };
-        const ShadeQueues sideq{ pb.q_exact, &c->n_exact_closest[b], pb.q_lit_side, &c->n_lit_side[b], 0 };
         if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
         ClosestPolicy cpol{ pb, q, tmax, b == 0 ? pb.hit_mesh : nullptr, (uint8_t)(overlap ? b + 1 : 0) };
         launch_trace<ClosestPolicy>(r, s, cpol, &c->n_active[b], 0, &c->fetch_closest[b], r->visits.p, pb.q_exact, &c->n_exact_closest[b], !overlap);
@@ -2485,15 +2585,10 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
             if (!traced || !side_done) return set_error(ATN_ERR_CUDA, "cudaEventCreate failed");
             CUDA_TRY(cudaEventRecord(traced, s));
             CUDA_TRY(cudaStreamWaitEvent(side, traced, 0));
-            launch_exact<ClosestPolicy>(r, side, cpol, pb.q_exact, &c->n_exact_closest[b]);
-            if (svgf_w2c) k_surface<false, true><<<side_grid, kShadeBlock, 0, side>>>(fp, r->camera, r->sv, pb, sideq, b, nullptr, 0, w2c);
-            else k_surface<false, false><<<side_grid, kShadeBlock, 0, side>>>(fp, r->camera, r->sv, pb, sideq, b, nullptr, 0, w2c);
-            k_nee<<<side_grid, kShadeBlock, 0, side>>>(fp, r->sv, r->seeds.p, pb, sideq, b);
-            k_bsdf<false><<<side_grid, kShadeBlock, 0, side>>>(fp, r->sv, r->seeds.p, pb, c, sideq, b, nullptr, 0);
+            if (svgf_w2c) k_side<true><<<side_grid, 128, 0, side>>>(r->rv, cpol, fp, r->camera, r->sv, r->seeds.p, pb, c, b, w2c);
+            else k_side<false><<<side_grid, 128, 0, side>>>(r->rv, cpol, fp, r->camera, r->sv, r->seeds.p, pb, c, b, w2c);
             CUDA_TRY(cudaEventRecord(side_done, side));
-            *launches += 4;
-            // the main shade stage touches the contributions: the previous bounce's exact shadow rays must have landed
-            if (shadow_done) { CUDA_TRY(cudaStreamWaitEvent(s, shadow_done, 0)); shadow_done = nullptr; }
+            *launches += 1;
         }
         if (svgf_w2c) k_surface<false, true><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, pb, mainq, b, nullptr, 0, w2c);
         else if (tap_now) k_surface<true, false><<<r->surface_grid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, pb, mainq, b, r->tap_dev.p, r->tap_cap, w2c);

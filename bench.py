@@ -6,7 +6,7 @@ traced) and Msamples/s for "Sponza 1920x1080, 16 spp, 5 bounces" on N B200s of o
     python bench.py --impl reference --gpus N --steps K --warmup W   # the reference's CPU path (oracle/_ref)
 
 A step = one pass of the hot path over one frame: the whole 1920x1080 frame at 16 spp with 5 bounces
-(genPath -> [closest-hit, shade, shadow-ray] x 5 -> gather, in wavefronts of 4 samples).
+(genPath -> [closest-hit, shade, shadow-ray] x 5 -> gather; the 16 samples travel as one wavefront of 33 M paths).
 Scene: the `sponza_atrium` blob (asset/sponza/sponza_lod.obj + sponza_lod.sbvh, Lambert/GGX, area
 light + synthetic-sky IBL; the full-resolution Sponza OBJ is stripped from the reference snapshot,
 SURVEY.md F10).  Synthetic data: seeds = std::mt19937(0), camera fixed.
@@ -346,7 +346,7 @@ def main():
             ps = r.stats()
             tr_ms += ps["trace_ms"]; prof_ms += ps["device_ms"]
             tr_rays += ps["closest_rays"] + ps["shadow_rays"]
-            trace_launches += 2 * BOUNCE * (-(-(s_end - s_begin) // 4))      # wavefronts of 4 samples at 1080p
+            trace_launches += 2 * BOUNCE * (-(-(s_end - s_begin) // 16))     # up to 16 samples of a 1080p frame per wavefront
         r.set_profiling(False)
     barrier()
 
@@ -391,7 +391,7 @@ def main():
             "wall_ms_per_step": round(1e3 * wall_s / args.steps, 3),
             "config": {"workload": WORKLOAD, "scene": SCENE, "width": W, "height": H, "spp": total_spp, "spp_per_gpu": s_end - s_begin,
                        "bounces": BOUNCE, "rr_bounce": RR, "partition": part,
-                       "l2": "path state (8.3M paths per wavefront x ~220 B SoA = 1.8 GB touched per bounce) exceeds the 126 MB L2; "
+                       "l2": "path state (33M paths per wavefront x ~250 B SoA = 8 GB touched per bounce) exceeds the 126 MB L2; "
                              "the scene (1.2 MB nodes + 1.2 MB triangles) is L2-resident by design, as in production use"},
             "clocks": clk,
             "e2e": {"value": round(e_rays / e2e_s / 1e6, 2), "unit": "Mrays/s",

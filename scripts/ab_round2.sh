@@ -1,5 +1,5 @@
 # A/B of kernel variants on the bench workload (build them first into aten_b200/variants/, see aten_b200/build.py)
-run() { ATEN_B200_LIB=$PWD/$1 ATEN_B200_EXACT_TIES=$2 python bench.py --steps 5 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('$1 exact=$2', d['value'], d['ms_per_step'])"; }
-run aten_b200/libaten_b200.so 1
-run aten_b200/libaten_b200.so 0
-for v in "$@"; do run aten_b200/variants/lib_$v.so 1; run aten_b200/variants/lib_$v.so 0; done
+run() { ATEN_B200_LIB=$PWD/$1 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-extra 2>/dev/null | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('$1', d['value'], d['ms_per_step'])"; }
+run aten_b200/libaten_b200.so
+for v in "$@"; do run aten_b200/variants/lib_$v.so; done
+run aten_b200/libaten_b200.so

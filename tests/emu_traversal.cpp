@@ -85,7 +85,10 @@ inline float cull_bound(float t) { return t + fabsf(t) * 2e-5f; }
 // (maxima over the world ray and every instance-space ray entered so far) bounds how far the biased slab entry distance of a
 // box can lie beyond the hit distance of a triangle inside it.  Boxes are culled with t + 2 B(t); the smallest hit distance
 // of a primitive other than the best one is tracked, and a ray whose runner-up lies within B of its best hit is FLAGGED:
-// the reference's answer for it depends on the reference's visit order, and the exact (reference-order) walk decides it.
+// the reference's answer for it depends on the reference's visit order, and the exact (reference-order) walk decides it --
+// unless the best hit is strictly the nearest and every box on the path to its leaf starts no later than the runner-up
+// (stack keys carry the largest entry distance on the path, "pathmax"): the reference then reaches and keeps it whatever
+// its order.
 static int trace_impl(const AtnSceneBlob* scene, const AtnRay* rays, const float* t_max_in, size_t n, AtnHit* hits,
                       uint64_t* stats_out, int sort_leaves_first, int entry_filter, const float* band, uint8_t* flags)
 {
@@ -121,6 +124,7 @@ static int trace_impl(const AtnSceneBlob* scene, const AtnRay* rays, const float
             widen(org, ri);
             stack.clear();
             int32_t cur = w.top_root, cur_inst = -1;
+            float cur_key = -kBig, pm_best = kBig;
             for (;;) {
                 if (cur >= 0) {
                     const QuadNode& q = w.nodes[cur];
@@ -135,13 +139,14 @@ static int trace_impl(const AtnSceneBlob* scene, const AtnRay* rays, const float
                         const Slab sl = slab(ri, mn, mx, t_min, t_cull);
                         if (!sl.hit) continue;
                         e[ne].ref = q.ref[s];
-                        e[ne].t0 = (sort_leaves_first && q.ref[s] < 0) ? -kBig : sl.t0;
+                        e[ne].t0 = (sort_leaves_first && q.ref[s] < 0) ? -kBig : (band ? fmaxf(sl.t0, cur_key) : sl.t0);
                         ne++;
                     }
                     // stable insertion sort by entry distance
                     for (int a = 1; a < ne; a++) { Ent k = e[a]; int b = a - 1; while (b >= 0 && e[b].t0 > k.t0) { e[b + 1] = e[b]; b--; } e[b + 1] = k; }
                     for (int a = ne - 1; a >= 1; a--) stack.push_back(e[a]);
                     cur = ne ? e[0].ref : kRefNull;
+                    if (ne) cur_key = e[0].t0;
                 }
                 else if (cur != kRefNull && cur != kRefExit) {
                     const int32_t leaf = ~cur;
@@ -155,8 +160,10 @@ static int trace_impl(const AtnSceneBlob* scene, const AtnRay* rays, const float
                             if (closer) {
                                 if (!same_prim && best.leaf >= 0) t2 = fminf(t2, best.t);
                                 best.t = h.t; best.a = h.a; best.b = h.b; best.leaf = leaf; best.inst = cur_inst; t_cull = cull_of(h.t);
+                                pm_best = same_prim ? fminf(pm_best, cur_key) : cur_key;
                             }
                             else if (!same_prim) t2 = fminf(t2, h.t);
+                            else pm_best = fminf(pm_best, cur_key);
                         }
                         cur = kRefNull;
                     }
@@ -189,7 +196,7 @@ static int trace_impl(const AtnSceneBlob* scene, const AtnRay* rays, const float
                 while (cur == kRefNull) {
                     if (stack.empty()) { finished = true; break; }
                     const Ent e = stack.back(); stack.pop_back();
-                    cur = e.ref;
+                    cur = e.ref; cur_key = e.t0;
                     if (cur == kRefExit) {
                         if (stack.empty()) { finished = true; break; }
                         cur_inst = -1; org = worg; dir = wdir; ri = wri; cur = kRefNull; continue;
@@ -199,7 +206,8 @@ static int trace_impl(const AtnSceneBlob* scene, const AtnRay* rays, const float
                 if (finished) break;
             }
             finish(w.tris, iobj.data(), imesh.data(), best, &hits[i]);
-            if (flags) flags[i] = (band && best.leaf >= 0 && t2 <= best.t + (fabsf(best.t) * rho + alpha)) ? 1 : 0;
+            const bool certain = best.t < t2 && pm_best <= t2;
+            if (flags) flags[i] = (band && best.leaf >= 0 && !certain && t2 <= best.t + (fabsf(best.t) * rho + alpha)) ? 1 : 0;
             st.rays++;
         }
 #pragma omp critical

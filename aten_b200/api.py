@@ -26,6 +26,7 @@ EXPORTS = [
     "atn_trace_any_device", "atn_set_bounce_tap", "atn_trace_closest_static", "atn_readback_aov", "atn_render_ao",
     "atn_render_svgf", "atn_set_motion_depth", "atn_readback_svgf", "atn_update_texture",
     "atn_render_restir", "atn_readback_restir", "atn_probe_read_bandwidth",
+    "atn_upload_scene_cached", "atn_sbvh_read", "atn_sbvh_write", "atn_free", "atn_set_exact_ties", "atn_set_gather_mode",
 ]
 
 
@@ -34,6 +35,45 @@ GATHER_OVERWRITE, GATHER_PROGRESSIVE, GATHER_SUM = 0, 1, 2      # AtnGatherMode 
 
 class AtnError(RuntimeError):
     pass
+
+
+class AtnSbvhInfo(C.Structure):
+    _fields_ = [("version", C.c_uint8 * 4), ("max_depth", C.c_uint32), ("voxel_material_count", C.c_uint32),
+                ("boxmin", C.c_float * 3), ("boxmax", C.c_float * 3)]
+
+
+def sbvh_read(path: str, offset_tri_idx: int = 0, material_names=None):
+    """``sbvh::importTree`` through the C ABI (``atn_sbvh_read``): (nodes NODE_DTYPE, info dict).  No GPU needed."""
+    lib = load_library()
+    nodes = C.c_void_p()
+    count = C.c_uint32()
+    info = AtnSbvhInfo()
+    names = None
+    n_names = 0
+    if material_names is not None:
+        n_names = len(material_names)
+        names = (C.c_char_p * max(1, n_names))(*[m.encode() for m in material_names])
+    _check(lib, lib.atn_sbvh_read(C.c_char_p(os.fsencode(path)), C.c_int32(offset_tri_idx), names, C.c_uint32(n_names),
+                                  C.byref(nodes), C.byref(count), C.byref(info)))
+    try:
+        buf = C.string_at(nodes.value, count.value * sio.NODE_DTYPE.itemsize)
+        arr = np.frombuffer(buf, sio.NODE_DTYPE).copy()
+    finally:
+        lib.atn_free(nodes)
+    return arr, {"version": tuple(info.version), "max_depth": int(info.max_depth), "voxel_materials": int(info.voxel_material_count),
+                 "boxmin": np.array(info.boxmin[:], np.float32), "boxmax": np.array(info.boxmax[:], np.float32)}
+
+
+def sbvh_write(path: str, nodes: np.ndarray, max_depth: int, boxmin, boxmax, voxel_materials=None):
+    """``sbvh::exportTree``'s file layout through the C ABI (``atn_sbvh_write``)."""
+    lib = load_library()
+    nodes = np.ascontiguousarray(nodes, sio.NODE_DTYPE)
+    vm = sorted((voxel_materials or {}).items())
+    ids = (C.c_int32 * max(1, len(vm)))(*[k for k, _ in vm])
+    names = (C.c_char_p * max(1, len(vm)))(*[v.encode() for _, v in vm])
+    bmin = (C.c_float * 3)(*[float(x) for x in boxmin]); bmax = (C.c_float * 3)(*[float(x) for x in boxmax])
+    _check(lib, lib.atn_sbvh_write(C.c_char_p(os.fsencode(path)), C.c_void_p(nodes.ctypes.data), C.c_uint32(len(nodes)),
+                                   C.c_uint32(max_depth), bmin, bmax, ids, names, C.c_uint32(len(vm))))
 
 
 def probe_read_bandwidth(device: int, nbytes: int, passes: int):
@@ -111,13 +151,24 @@ class PathTracing:
         self.close()
 
     # -- Renderer::UpdateSceneData (reference renderer.cpp:12-131) ------------------------------
-    def UpdateSceneData(self, scene: sio.Scene, width: int | None = None, height: int | None = None, seeds=None):
+    def UpdateSceneData(self, scene: sio.Scene, width: int | None = None, height: int | None = None, seeds=None,
+                        cache_path: str | None = None):
+        """``cache_path``: file of the encoded bottom trees (``atn_upload_scene_cached``); ``self.cache_hit`` says
+        afterwards whether it was used (True) or (re)written (False)."""
         width = width or scene.width
         height = height or scene.height
         blob = scene.blob()
         cam = np.ascontiguousarray(scene.camera)
-        _check(self._lib, self._lib.atn_upload_scene(self._h, C.byref(blob), C.c_void_p(cam.ctypes.data),
-                                                     C.c_int32(width), C.c_int32(height)))
+        self.cache_hit = None
+        if cache_path:
+            hit = C.c_int(0)
+            _check(self._lib, self._lib.atn_upload_scene_cached(self._h, C.byref(blob), C.c_void_p(cam.ctypes.data),
+                                                                C.c_int32(width), C.c_int32(height),
+                                                                C.c_char_p(os.fsencode(cache_path)), C.byref(hit)))
+            self.cache_hit = bool(hit.value)
+        else:
+            _check(self._lib, self._lib.atn_upload_scene(self._h, C.byref(blob), C.c_void_p(cam.ctypes.data),
+                                                         C.c_int32(width), C.c_int32(height)))
         self.width, self.height = width, height
         self._scene = scene
         s = scene.seeds_for(width * height) if seeds is None else np.ascontiguousarray(seeds, np.uint32)

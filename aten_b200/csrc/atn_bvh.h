@@ -424,13 +424,30 @@ inline WideBvh encode_top(const AtnBvhNode* top_nodes, uint32_t top_count, const
     return out;
 }
 
-// The whole scene.  `info` (optional) receives what later top-layer updates need (encode_top).
-inline WideBvh encode_wide(const AtnSceneBlob* scene, BottomInfo* info = nullptr)
+// The encoded bottom trees of a scene as a unit: what an encoded-tree file holds (atn_cache.h).
+struct CachedBottom {
+    BottomInfo info;
+    std::vector<QuadNode> nodes;
+    std::vector<int32_t> stack_need;
+    std::vector<TriLeaf> tris;
+    uint64_t slots_used{ 0 }, replaced{ 0 }, not_nested{ 0 };
+};
+
+// The whole scene.  `info` (optional) receives what later top-layer updates need (encode_top).  `cached` (optional): the
+// bottom trees as an earlier encode_wide of the same node lists produced them -- only the top layer is encoded then.
+inline WideBvh encode_wide(const AtnSceneBlob* scene, BottomInfo* info = nullptr, const CachedBottom* cached = nullptr)
 {
     WideBvh out;
     if (scene->node_list_count == 0) return out;
     const uint32_t nlists = scene->node_list_count;
     BottomInfo bottom;
+    if (cached) {
+        out.nodes = cached->nodes; out.stack_need = cached->stack_need; out.tris = cached->tris;
+        out.slots_used = cached->slots_used; out.replaced = cached->replaced; out.not_nested = cached->not_nested;
+        bottom = cached->info;
+        if (bottom.roots.size() != nlists) { out.error = "cached bottom trees belong to another scene"; return out; }
+    }
+    else {
     bottom.roots.assign(nlists, kRefNull); bottom.need.assign(nlists, 0); bottom.box.assign((size_t)nlists * 6, 0.0f);
     // Bottom lists are independent of each other: each is encoded on its own (in parallel when the scene is large) with
     // list-local node and leaf numbers, then appended in list order with the numbers moved to their global positions --
@@ -485,6 +502,7 @@ inline WideBvh encode_wide(const AtnSceneBlob* scene, BottomInfo* info = nullptr
         pt = Part();                                  // release the list's partial arrays
     }
     bottom.node_count = (int32_t)out.nodes.size();
+    }       // !cached
     if (scene->node_list_sizes[0] > 0) {
         WideBvh top = encode_top(scene->node_lists[0], scene->node_list_sizes[0], scene, bottom);
         if (!top.error.empty()) { out.error = top.error; return out; }

@@ -40,6 +40,7 @@
 #include "atn_svgf.cuh"
 #include "atn_restir.cuh"
 #include "atn_bvh.h"
+#include "atn_cache.h"
 
 using namespace atn;
 
@@ -2123,13 +2124,36 @@ static int upload_ref_lists(AtnRenderer* r, const AtnSceneBlob* scene)
     return upload_ref_top(r, scene->node_lists[0], scene->node_list_sizes[0]);
 }
 
-static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene)
+// `cache_path` (optional): file of the encoded bottom trees (atn_cache.h).  A file that holds the encoding of exactly these
+// node lists, triangles and positions is used instead of encoding them again; otherwise they are encoded and the file is
+// (re)written.  *cache_hit (optional) says which happened.
+static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene, const char* cache_path = nullptr, int* cache_hit = nullptr)
 {
     {
         const int rc = upload_ref_lists(r, scene);
         if (rc != ATN_OK) return rc;
     }
-    WideBvh enc = encode_wide(scene, &r->bottom);
+    if (cache_hit) *cache_hit = 0;
+    WideBvh enc;
+    if (cache_path && cache_path[0]) {
+        const uint64_t hash = source_hash(scene);
+        CachedBottom cached;
+        const std::string why = read_encoded(cache_path, hash, scene->node_list_count, &cached);
+        if (why.empty()) {
+            enc = encode_wide(scene, &r->bottom, &cached);
+            if (cache_hit) *cache_hit = 1;
+        }
+        else {
+            enc = encode_wide(scene, &r->bottom);
+            if (enc.error.empty()) {
+                const size_t nb = (size_t)r->bottom.node_count;
+                const std::string werr = write_encoded(cache_path, hash, scene->node_list_count, r->bottom, enc.nodes.data(), enc.stack_need.data(), nb,
+                                                       enc.tris.data(), enc.tris.size(), enc.slots_used, enc.replaced, enc.not_nested);
+                if (!werr.empty()) return set_error(ATN_ERR_INVALID_ARGUMENT, "encoded-tree cache: %s", werr.c_str());
+            }
+        }
+    }
+    else enc = encode_wide(scene, &r->bottom);
     if (!enc.error.empty()) return set_error(ATN_ERR_INVALID_ARGUMENT, "node lists: %s", enc.error.c_str());
     {
         // nodes + triangles far beyond the L2: the traversal waits for device memory, not for issue slots -- use the variant
@@ -2318,8 +2342,8 @@ ATN_API int atn_destroy(AtnRenderer* r)
     return ATN_OK;
 }
 
-ATN_API int atn_upload_scene(AtnRenderer* r, const AtnSceneBlob* scene, const AtnCameraParameter* camera,
-                             int32_t width, int32_t height)
+static int upload_scene_impl(AtnRenderer* r, const AtnSceneBlob* scene, const AtnCameraParameter* camera,
+                             int32_t width, int32_t height, const char* cache_path, int* cache_hit)
 {
     if (!r || !scene || !camera) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_upload_scene: NULL argument");
     if (width <= 0 || height <= 0) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_upload_scene: bad size %dx%d", width, height);
@@ -2359,7 +2383,7 @@ ATN_API int atn_upload_scene(AtnRenderer* r, const AtnSceneBlob* scene, const At
     sv.scene_radius = scene_radius_of(scene->config);
     r->bv.t_min = scene->config.bvh_hit_min > 0 ? scene->config.bvh_hit_min : kEps;
 
-    int rc = upload_bvh(r, scene);
+    int rc = upload_bvh(r, scene, cache_path, cache_hit);
     if (rc != ATN_OK) return rc;
 
     r->camera = *camera;
@@ -2384,6 +2408,51 @@ ATN_API int atn_upload_scene(AtnRenderer* r, const AtnSceneBlob* scene, const At
     r->has_scene = true;
     return ATN_OK;
 }
+
+ATN_API int atn_upload_scene(AtnRenderer* r, const AtnSceneBlob* scene, const AtnCameraParameter* camera,
+                             int32_t width, int32_t height)
+{
+    return upload_scene_impl(r, scene, camera, width, height, nullptr, nullptr);
+}
+
+ATN_API int atn_upload_scene_cached(AtnRenderer* r, const AtnSceneBlob* scene, const AtnCameraParameter* camera,
+                                    int32_t width, int32_t height, const char* cache_path, int* cache_hit)
+{
+    if (!cache_path || !cache_path[0]) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_upload_scene_cached: no cache path");
+    return upload_scene_impl(r, scene, camera, width, height, cache_path, cache_hit);
+}
+
+// ---- .sbvh files (sbvh::importTree / exportTree, sbvh.cpp:1220-1436) ------------------------------------------------
+ATN_API int atn_sbvh_read(const char* path, int32_t offset_tri_idx, const char* const* material_names, uint32_t material_count,
+                          AtnBvhNode** nodes, uint32_t* node_count, AtnSbvhInfo* info)
+{
+    if (!path || !nodes || !node_count) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_sbvh_read: NULL argument");
+    SbvhFile f = read_sbvh(path, offset_tri_idx, material_names, material_count);
+    if (!f.error.empty()) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_sbvh_read: %s", f.error.c_str());
+    AtnBvhNode* out = static_cast<AtnBvhNode*>(malloc(std::max<size_t>(1, f.nodes.size()) * sizeof(AtnBvhNode)));
+    if (!out) return set_error(ATN_ERR_TOO_LARGE, "atn_sbvh_read: out of host memory");
+    if (!f.nodes.empty()) memcpy(out, f.nodes.data(), f.nodes.size() * sizeof(AtnBvhNode));
+    *nodes = out; *node_count = (uint32_t)f.nodes.size();
+    if (info) {
+        memcpy(info->version, f.header.version, 4);
+        info->max_depth = f.header.maxDepth; info->voxel_material_count = f.header.cntMtrlForVoxel;
+        for (int a = 0; a < 3; a++) { info->boxmin[a] = f.header.boxmin[a]; info->boxmax[a] = f.header.boxmax[a]; }
+    }
+    return ATN_OK;
+}
+
+ATN_API int atn_sbvh_write(const char* path, const AtnBvhNode* nodes, uint32_t node_count, uint32_t max_depth,
+                           const float boxmin[3], const float boxmax[3],
+                           const int32_t* voxel_material_ids, const char* const* voxel_material_names, uint32_t voxel_material_count)
+{
+    if (!path || (node_count && !nodes) || !boxmin || !boxmax || (voxel_material_count && (!voxel_material_ids || !voxel_material_names)))
+        return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_sbvh_write: NULL argument");
+    const std::string err = write_sbvh(path, nodes, node_count, max_depth, boxmin, boxmax, voxel_material_ids, voxel_material_names, voxel_material_count);
+    if (!err.empty()) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_sbvh_write: %s", err.c_str());
+    return ATN_OK;
+}
+
+ATN_API void atn_free(void* p) { free(p); }
 
 ATN_API int atn_update_camera(AtnRenderer* r, const AtnCameraParameter* camera)
 {

@@ -215,6 +215,35 @@ ATN_API const char* atn_version(void);
  * W*H path state. */
 ATN_API int atn_upload_scene(AtnRenderer* r, const AtnSceneBlob* scene,
                              const AtnCameraParameter* camera, int32_t width, int32_t height);
+/* The same upload for a scene whose bottom trees are large: `cache_path` names a file that holds the
+ * ENCODED bottom trees (the 4-slot nodes and gathered triangle records the node lists are turned into).  When it matches
+ * exactly these node lists, triangles and vertex positions (hash) and this library's encoder version, the encoding step
+ * is skipped (*cache_hit = 1); otherwise the scene is encoded as usual and the file is written for the next time
+ * (*cache_hit = 0).  The top layer is never cached.  cache_hit may be NULL. */
+ATN_API int atn_upload_scene_cached(AtnRenderer* r, const AtnSceneBlob* scene,
+                                    const AtnCameraParameter* camera, int32_t width, int32_t height,
+                                    const char* cache_path, int* cache_hit);
+
+/* ---- .sbvh tree files -------------------------------------------------------------------------- */
+typedef struct AtnSbvhInfo {
+    uint8_t version[4];
+    uint32_t max_depth;
+    uint32_t voxel_material_count;
+    float boxmin[3], boxmax[3];
+} AtnSbvhInfo;
+/* sbvh::importTree(ctxt, path, offsetTriIdx) (src/libaten/accelerator/sbvh.cpp:1345-1436): reads a tree file written by
+ * the reference (or by atn_sbvh_write) into a node array usable as one bottom-layer list of AtnSceneBlob.  Triangle
+ * numbers get offset_tri_idx added; voxel material ids are re-mapped through the file's name table to indices into
+ * material_names (context::FindMaterialIdxByName; pass NULL to keep the file's ids).  *nodes is malloc'ed: release it
+ * with atn_free.  info may be NULL. */
+ATN_API int atn_sbvh_read(const char* path, int32_t offset_tri_idx, const char* const* material_names, uint32_t material_count,
+                          AtnBvhNode** nodes, uint32_t* node_count, AtnSbvhInfo* info);
+/* sbvh::exportTree's file layout (sbvh.cpp:1236-1340) for a node list the caller holds. */
+ATN_API int atn_sbvh_write(const char* path, const AtnBvhNode* nodes, uint32_t node_count, uint32_t max_depth,
+                           const float boxmin[3], const float boxmax[3],
+                           const int32_t* voxel_material_ids, const char* const* voxel_material_names, uint32_t voxel_material_count);
+ATN_API void atn_free(void* p);
+
 /* Renderer::updateCamera (renderer.h:85-88) */
 ATN_API int atn_update_camera(AtnRenderer* r, const AtnCameraParameter* camera);
 /* Renderer::updateBVH (renderer.cpp:133-153): new top layer (list 0), objects and matrices. */

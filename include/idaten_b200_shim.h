@@ -229,10 +229,41 @@ public:
         Ensure();
         flat_.Gather(scene_ctxt, nodes);
         auto blob = flat_.View();
-        Check(atn_upload_scene(h_, &blob, reinterpret_cast<const AtnCameraParameter*>(&camera), width, height));
+        if (encoded_cache_path_.empty())
+            Check(atn_upload_scene(h_, &blob, reinterpret_cast<const AtnCameraParameter*>(&camera), width, height));
+        else {
+            int hit = 0;
+            Check(atn_upload_scene_cached(h_, &blob, reinterpret_cast<const AtnCameraParameter*>(&camera), width, height,
+                                          encoded_cache_path_.c_str(), &hit));
+            encoded_cache_hit_ = hit != 0;
+        }
         // Renderer::initSamplerParameter (renderer.h:113-124)
         const auto& rnd = aten::getRandom();
         Check(atn_set_seeds(h_, rnd.data(), static_cast<uint32_t>(rnd.size())));
+    }
+
+    /// No counterpart in the reference: the next UpdateSceneData keeps the ENCODED bottom trees in this file and skips
+    /// the encoding step when the file matches the scene (atn_upload_scene_cached); "" switches it off.
+    void SetEncodedTreeCache(const std::string& path) { encoded_cache_path_ = path; }
+    bool EncodedTreeCacheHit() const { return encoded_cache_hit_; }
+
+    /// sbvh::importTree (src/libaten/accelerator/sbvh.cpp:1345-1436) without an aten::sbvh object: the node list of a
+    /// `.sbvh` file, ready to stand as one bottom-layer list of the `nodes` argument of UpdateSceneData.  Voxel material
+    /// ids are re-mapped through `scene_ctxt`'s material names, as importTree does with FindMaterialIdxByName.
+    static std::vector<aten::GPUBvhNode> ImportSbvh(const std::string& path, int32_t offset_tri_idx = 0,
+                                                    const std::vector<std::string>* material_names = nullptr)
+    {
+        std::vector<const char*> names;
+        if (material_names) for (const auto& n : *material_names) names.push_back(n.c_str());
+        AtnBvhNode* nodes = nullptr;
+        uint32_t count = 0;
+        Check(atn_sbvh_read(path.c_str(), offset_tri_idx, material_names ? names.data() : nullptr, (uint32_t)names.size(),
+                            &nodes, &count, nullptr));
+        static_assert(sizeof(aten::GPUBvhNode) == sizeof(AtnBvhNode), "node layout");
+        std::vector<aten::GPUBvhNode> out(count);
+        if (count) memcpy(out.data(), nodes, count * sizeof(AtnBvhNode));
+        atn_free(nodes);
+        return out;
     }
 
     /// PathTracingImplBase::render (pathtracing.cpp:49-89)
@@ -327,6 +358,8 @@ protected:
     AtnRenderer* h_{ nullptr };
     int device_{ 0 };
     bool progressive_{ false };
+    std::string encoded_cache_path_;
+    bool encoded_cache_hit_{ false };
     Mode mode_{ Mode::PT };
     FlatScene flat_;
 };

@@ -14,7 +14,8 @@ from aten_b200 import scene_io as sio
 HERE = os.path.dirname(os.path.abspath(__file__))
 SO = os.path.join(HERE, "_build", "libemu_traversal.so")
 SRC = os.path.join(HERE, "emu_traversal.cpp")
-DEPS = [SRC, os.path.join(HERE, "..", "aten_b200", "csrc", "atn_bvh.h"), os.path.join(HERE, "..", "aten_b200", "csrc", "atn_math.cuh")]
+DEPS = [SRC, os.path.join(HERE, "..", "aten_b200", "csrc", "atn_bvh.h"), os.path.join(HERE, "..", "aten_b200", "csrc", "atn_math.cuh"),
+        os.path.join(HERE, "..", "aten_b200", "csrc", "atn_cache.h")]
 _lib = None
 
 STAT_NAMES = ("nodes", "tris", "entries", "entries_filtered", "pops_culled", "max_sp", "node_count", "slots_used",
@@ -89,3 +90,11 @@ def trace_closest_flagged(scene: sio.Scene, rays: np.ndarray, band, t_max=None):
     if rc != 0:
         raise RuntimeError("encode_wide rejected the scene's node lists")
     return hits, flags, {k: int(v) for k, v in zip(STAT_NAMES, stats)}
+
+
+def encoded_cache_round_trip(scene: sio.Scene, path: str, other: sio.Scene | None = None) -> int:
+    """0 when encode -> file -> read -> encode over the cached bottom trees is byte-identical to the fresh encoding (and the
+    file is refused for `other` and for a wrong hash)."""
+    b0 = scene.blob()
+    b1 = other.blob() if other is not None else None
+    return int(lib().emu_encoded_cache_round_trip(C.byref(b0), C.c_char_p(os.fsencode(path)), C.byref(b1) if b1 is not None else None))

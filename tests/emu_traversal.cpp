@@ -11,6 +11,7 @@
 
 #include "../aten_b200/csrc/atn_math.cuh"
 #include "../aten_b200/csrc/atn_bvh.h"
+#include "../aten_b200/csrc/atn_cache.h"
 
 using namespace atn;
 
@@ -254,5 +255,36 @@ extern "C" int emu_top_update_equals_fresh(const AtnSceneBlob* base, const AtnSc
     if (t.insts.size() != f.insts.size() || (!t.insts.empty() && memcmp(t.insts.data(), f.insts.data(), t.insts.size() * sizeof(InstLeafW)) != 0)) return 4;
     if (t.top_root != f.top_root) return 5;
     if (t.max_stack != f.max_stack) return 6;
+    return 0;
+}
+
+// Encoded-tree cache (atn_cache.h): encode, write, read back, encode the top layer over the cached bottom trees -- the
+// result must be byte-identical to the fresh encoding.  Returns 0 when it is; `other` (optional): a scene whose hash
+// must NOT match the file.
+extern "C" int emu_encoded_cache_round_trip(const AtnSceneBlob* scene, const char* path, const AtnSceneBlob* other)
+{
+    BottomInfo bi;
+    const WideBvh fresh = encode_wide(scene, &bi);
+    if (!fresh.error.empty()) return -1;
+    const uint64_t hash = source_hash(scene);
+    if (source_hash(scene) != hash) return -2;
+    const size_t nb = (size_t)bi.node_count;
+    if (!write_encoded(path, hash, scene->node_list_count, bi, fresh.nodes.data(), fresh.stack_need.data(), nb, fresh.tris.data(), fresh.tris.size(),
+                       fresh.slots_used, fresh.replaced, fresh.not_nested).empty()) return -3;
+    CachedBottom cb;
+    if (!read_encoded(path, hash, scene->node_list_count, &cb).empty()) return -4;
+    BottomInfo bi2;
+    const WideBvh again = encode_wide(scene, &bi2, &cb);
+    if (!again.error.empty()) return -5;
+    if (again.nodes.size() != fresh.nodes.size() || memcmp(again.nodes.data(), fresh.nodes.data(), fresh.nodes.size() * sizeof(QuadNode)) != 0) return 1;
+    if (again.tris.size() != fresh.tris.size() || memcmp(again.tris.data(), fresh.tris.data(), fresh.tris.size() * sizeof(TriLeaf)) != 0) return 2;
+    if (again.insts.size() != fresh.insts.size() || (!fresh.insts.empty() && memcmp(again.insts.data(), fresh.insts.data(), fresh.insts.size() * sizeof(InstLeafW)) != 0)) return 3;
+    if (again.top_root != fresh.top_root || again.max_stack != fresh.max_stack || again.stack_need != fresh.stack_need) return 4;
+    if (bi2.roots != bi.roots || bi2.need != bi.need || bi2.box != bi.box || bi2.node_count != bi.node_count) return 5;
+    if (other) {
+        CachedBottom cb2;
+        if (read_encoded(path, source_hash(other), other->node_list_count, &cb2).empty()) return 6;     // must be refused
+    }
+    if (read_encoded(path, hash ^ 1, scene->node_list_count, &cb).empty()) return 7;
     return 0;
 }

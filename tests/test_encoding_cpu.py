@@ -91,3 +91,11 @@ def test_deep_chain_tree_stack_bound(golden):
     assert 64 < st["max_sp"] <= st["stack_bound"] <= 16 + 240
     with pytest.raises(RuntimeError):
         emu_lib.trace_closest(ss.chain_scene(base, 120), rays[:8])
+
+
+@pytest.mark.parametrize("name", ["sponza_atrium", "instanced"])
+def test_encoded_tree_cache_round_trip(golden, tmp_path, name):
+    """The encoded-tree file (aten_b200/csrc/atn_cache.h, behind atn_upload_scene_cached): what comes back from it, with the
+    top layer encoded again, is byte-identical to a fresh encoding; a file of another scene or hash is refused."""
+    rc = emu_lib.encoded_cache_round_trip(golden.scene(name), str(tmp_path / "t.atnenc"), golden.scene("cornell"))
+    assert rc == 0, rc

@@ -129,6 +129,9 @@ struct Counters {
     int32_t n_exact_closest[kMaxBounce];  // rays handed to the exact walk (near ties), per bounce
     int32_t n_exact_shadow[kMaxBounce];
     int32_t n_exact_query;
+    // rays that restart behind an ignored hit (alpha / stencil), per bounce and lookup: queue length, work cursor of the pass
+    // that traces them, and their share of the exact walk
+    struct Retrace { int32_t n[10], fetch[10], n_exact[10]; } retrace[kMaxBounce];
     int32_t pad[2];
 };
 
@@ -154,6 +157,7 @@ struct PathBuffers {
     int32_t* q_shadow;    // path slots with a shadow ray to trace
     int32_t* q_exact;     // path slots whose closest-hit traversal ended in a near tie: the exact walk decides them (k_exact)
     int32_t* q_exact_s;   // the same for shadow rays (its own list: the two exact walks of a bounce overlap other work)
+    int32_t* q_retrace[2]; // shadow rays restarting behind an ignored hit (alpha / stencil): ping-pong between lookups
     uint8_t* pend;        // bounce + 1 of the bounce whose closest hit the exact walk decides (0: none since k_generate).  Written
                           // by the traversal, read by the main surface stage, never touched by the side pass -- which
                           // overwrites hit0 / hit1 of such a path while the main surface stage is still running
@@ -382,30 +386,42 @@ __device__ __forceinline__ bool shadow_tie_matters(const SceneView& sc, const At
     return h.mtrlid >= 0 && (m.albedoMap >= 0 || m.baseColor.w < 1.0f);       // isTranslucentByAlpha looks at the tied hit's texel
 }
 
-template <bool kTap>
+// kRetrace: HitTestToTargetLight's loop (pathtracing_impl.h:288-348) for scenes with alpha blending on or a stencil material:
+// a shadow ray whose closest hit is ignored (translucent by alpha / stencil) restarts behind it and joins the retrace queue,
+// which the next pass of the same kernel traces (launch_bounces runs up to 9 such passes).  The per-ray loop state -- lookup
+// number, stencil flag, the last object hit -- travels in the spare lane of the light-contribution record (sh_c.w).
+__device__ __forceinline__ int32_t shadow_state_pack(int lookup, bool need_stencil, int32_t hitobj) { return lookup | (need_stencil ? 256 : 0) | ((hitobj + 1) << 9); }
+
+template <bool kTap, bool kRetrace = false>
 struct ShadowPolicy {              // wavefront shadow rays (hitShadowRay)
-    static constexpr bool kNeedClass = true;
+    static constexpr bool kNeedClass = !kRetrace;
     PathBuffers pb;
     SceneView sc;
     AtnBounceRecord* tap;
     int tap_cap, bounce;
+    const int32_t* queue;          // path slots of this pass: q_shadow, or a retrace queue
+    int32_t* q_retrace;            // kRetrace: where ignored hits go, and its counter
+    int32_t* n_retrace;
     __device__ __forceinline__ void world(int slot, V3* o, V3* d) const
     {
         const float4 so = pb.sh_o[slot];
         const float4 sd = pb.sh_d[slot];
-        // aten::ray(rayorg, raydir) renormalises the direction (pathtracing_impl.h:378)
+        // aten::ray(rayorg, raydir) renormalises the direction (pathtracing_impl.h:378); a retrace ray is built from that
+        // direction with the same constructor, i.e. normalised once more (:330)
         *o = V3(so.x, so.y, so.z); *d = normalize(V3(sd.x, sd.y, sd.z));
+        if (kRetrace && (__float_as_int(pb.sh_c[slot].w) & 255) != 0) *d = normalize(*d);
     }
     __device__ __forceinline__ float t_max(int slot) const { return pb.sh_o[slot].w - kEps; }
     __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* t_max, int* mode, float* exit_dist) const
     {
-        const int s = pb.q_shadow[i];
+        const int s = queue[i];
         world(s, o, d);
         const float dist = pb.sh_o[s].w;
         const uint32_t attrib = sc.lights[__float_as_int(pb.sh_d[s].w)].attrib;
         *slot = s;
         *t_max = dist - kEps;                       // HitTestToTargetLight, pathtracing_impl.h:297-304
-        *mode = (attrib & 2u) ? EXIT_ANY_HIT : ((attrib & 1u) ? EXIT_HIT_BEFORE : EXIT_NONE);
+        // with the retrace loop the CLOSEST hit decides whether the ray goes on: no early exit
+        *mode = kRetrace ? EXIT_NONE : ((attrib & 2u) ? EXIT_ANY_HIT : ((attrib & 1u) ? EXIT_HIT_BEFORE : EXIT_NONE));
         *exit_dist = dist;
     }
     template <bool kLate>
@@ -416,7 +432,26 @@ struct ShadowPolicy {              // wavefront shadow rays (hitShadowRay)
         const float4 c = pb.sh_c[slot];
         const AtnLightParameter& light = sc.lights[__float_as_int(sd.w)];
         Ray sr; sr.org = V3(so.x, so.y, so.z); sr.dir = normalize(V3(sd.x, sd.y, sd.z));
-        const bool vis = shadow_visible(sc, light, sr, so.w, h.objid, h.primid, h.a, h.b, h.t, h.mtrlid);
+        bool vis;
+        if (kRetrace) {
+            const int32_t state = __float_as_int(c.w);
+            const int lookup = state & 255;
+            const bool need_stencil = (state & 256) != 0;
+            int32_t hitobj = (state >> 9) - 1;
+            const V3 orig_dir = sr.dir;
+            if (lookup != 0) sr.dir = normalize(sr.dir);
+            V3 next_org;
+            const int res = shadow_lookup(sc, light, sr, orig_dir, so.w, h.objid, h.primid, h.a, h.b, h.t, h.mtrlid,
+                                          lookup + 1 >= shadow_max_lookups(sc, need_stencil), need_stencil, &hitobj, &next_org);
+            if (res == kShadowRetrace) {
+                pb.sh_o[slot] = make_float4(next_org.x, next_org.y, next_org.z, so.w);
+                pb.sh_c[slot] = make_float4(c.x, c.y, c.z, __int_as_float(shadow_state_pack(lookup + 1, need_stencil, hitobj)));
+                q_retrace[atomicAdd(n_retrace, 1)] = slot;
+                return;
+            }
+            vis = res == kShadowVisible;
+        }
+        else vis = shadow_visible(sc, light, sr, so.w, h.objid, h.primid, h.a, h.b, h.t, h.mtrlid);
         float4* dst = kLate ? pb.contrib_late : pb.contrib;
         if (vis) {
             float4 cc = dst[slot];
@@ -437,7 +472,8 @@ struct ShadowPolicy {              // wavefront shadow rays (hitShadowRay)
     __device__ __forceinline__ bool finish(const BvhView& bv, int slot, const TraceResult& r, const Tie& tie) const
     {
         const AtnHit h = resolved(bv, r);
-        if (tie.any && shadow_tie_matters(sc, sc.lights[__float_as_int(pb.sh_d[slot].w)], pb.sh_o[slot].w, h, tie)) return false;
+        // (with the retrace loop every tie goes to the exact walk: which surface is the closest decides how the ray goes on)
+        if (tie.any && (kRetrace || shadow_tie_matters(sc, sc.lights[__float_as_int(pb.sh_d[slot].w)], pb.sh_o[slot].w, h, tie))) return false;
         finish_hit(slot, h);
         return true;
     }
@@ -1323,7 +1359,11 @@ __device__ __forceinline__ void nee_stage(const FrameParams& fp, const SceneView
     if (sh.active) pb.sh_d[slot] = make_float4(sh.dir.x, sh.dir.y, sh.dir.z, __int_as_float(sh.light_id));
     // ShadowRay::lightcontrib is reset whenever a light was sampled (FillShadowRay, pathtracing_impl.h:241) and stays
     // in the buffer: the ReSTIR visibility step of the next frame adds it again (restir_shadow_ray)
-    if (sh.sampled) pb.sh_c[slot] = make_float4(sh.lightcontrib.x, sh.lightcontrib.y, sh.lightcontrib.z, 0.0f);
+    // .w: the state of HitTestToTargetLight's loop for this shadow ray (ShadowPolicy<., kRetrace>): first lookup, whether the
+    // surface asks for the stencil check, and the light's own object as the "last object hit"
+    if (sh.sampled)
+        pb.sh_c[slot] = make_float4(sh.lightcontrib.x, sh.lightcontrib.y, sh.lightcontrib.z,
+                                    __int_as_float(shadow_state_pack(0, shadow_needs_stencil(sc, sf.mtrlid), shadow_light_obj(sc.lights[sh.light_id]))));
 }
 
 template <bool kTap>
@@ -1520,14 +1560,15 @@ k_ao_ray(FrameParams fp, const uint32_t* __restrict__ seeds, PathBuffers pb, Cou
     }
 }
 
-// Fold the AO ray's closest hit into the running value (aorenderer_impl.h:80-111); `last` also applies
-// `ao_color /= ao_num_rays` and spreads the value over rgb.
+// Fold the AO ray's closest hit into the running value (aorenderer_impl.h:72-111).  A hit that is translucent by alpha
+// restarts the ray behind it: its slot goes to `q_re` and the next pass traces it again (`last_lookup`: the 10th lookup).
 __global__ void __launch_bounds__(kShadeBlock)
-k_ao_accum(SceneView sc, PathBuffers pb, Counters* cnt, float radius, int last, int num_rays)
+k_ao_accum(SceneView sc, PathBuffers pb, const int32_t* __restrict__ q_in, const int32_t* __restrict__ n_in,
+           int32_t* __restrict__ q_re, int32_t* n_re, float radius, int last_lookup)
 {
-    const int count = cnt->n_lit[0];
+    const int count = *n_in;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-        const int slot = pb.q_lit[i];
+        const int slot = q_in[i];
         const float4 o = pb.ray_o[slot];
         const float4 d = pb.ray_d[slot];
         const float4 h0 = pb.hit0[slot];
@@ -1536,10 +1577,27 @@ k_ao_accum(SceneView sc, PathBuffers pb, Counters* cnt, float radius, int last, 
         const float4 s2 = pb.surf2[slot];
         Ray ar; ar.org = V3(o.x, o.y, o.z); ar.dir = V3(d.x, d.y, d.z);
         float4 c = pb.contrib[slot];
-        float ao = ao_accumulate(sc, c.x, V3(s1.x, s1.y, s1.z), V3(s2.x, s2.y, s2.z), ar, radius,
-                                 h1.x, __float_as_int(h0.w), h0.y, h0.z, h0.x, h1.y);
-        if (last) { ao /= num_rays; c.y = ao; c.z = ao; }
-        c.x = ao;
+        Ray next;
+        const bool again = ao_accumulate(sc, &c.x, V3(s1.x, s1.y, s1.z), V3(s2.x, s2.y, s2.z), ar, radius,
+                                         h1.x, __float_as_int(h0.w), h0.y, h0.z, h0.x, h1.y, last_lookup != 0, &next);
+        pb.contrib[slot] = c;
+        if (again) {
+            pb.ray_o[slot] = make_float4(next.org.x, next.org.y, next.org.z, 0.0f);
+            pb.ray_d[slot] = make_float4(next.dir.x, next.dir.y, next.dir.z, 0.0f);
+            q_re[atomicAdd(n_re, 1)] = slot;
+        }
+    }
+}
+
+// `ao_color /= ao_num_rays`, spread over rgb (aorenderer_impl.h:114-116)
+__global__ void __launch_bounds__(kShadeBlock)
+k_ao_finish(PathBuffers pb, Counters* cnt, int num_rays)
+{
+    const int count = cnt->n_lit[0];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const int slot = pb.q_lit[i];
+        float4 c = pb.contrib[slot];
+        c.x /= num_rays; c.y = c.x; c.z = c.x;
         pb.contrib[slot] = c;
     }
 }
@@ -1946,7 +2004,11 @@ struct AtnRenderer {
     RefView rv{};
     int exact_ties{ 1 };               // 0: near ties are left as the front-to-back walk found them (atn_set_exact_ties)
     int exact_grid{ 148 * 4 };
-    DevBuf<int32_t> q_exact, q_exact_s, q_exact_query;
+    DevBuf<int32_t> q_exact, q_exact_s, q_exact_query, q_retrace0, q_retrace1;
+    bool any_stencil_always{ false };
+    bool alpha_surfaces{ false };      // a material can be translucent by alpha (baseColor.a < 1, or an albedo map with such a texel): AO rays loop
+    std::vector<uint8_t> tex_has_alpha; // per texture: a texel with alpha < 1
+    bool shadow_retrace{ false };      // alpha blending on or a stencil ALWAYS material in the scene: shadow rays run HitTestToTargetLight's loop
     // The exact walk is a latency-bound tail (a few thousand rays, hundreds of dependent steps each).  In the bounce loop it
     // runs on a second stream next to the main kernels instead of between them (launch_bounces).
     cudaStream_t side_stream{ nullptr };
@@ -2176,6 +2238,29 @@ static int upload_bvh(AtnRenderer* r, const AtnSceneBlob* scene, const char* cac
     return bind_top_layer(r, enc.nodes.size(), enc.insts, enc.top_root, enc.max_stack);
 }
 
+// Shadow rays run HitTestToTargetLight's loop when alpha blending is on or a surface can ask for the stencil check.
+static void update_shadow_retrace(AtnRenderer* r, const AtnMaterialParameter* m, uint32_t count)
+{
+    if (m) {
+        r->any_stencil_always = false;
+        for (uint32_t i = 0; i < count; i++) if (m[i].stencil_type == kStencilAlways) r->any_stencil_always = true;
+    }
+    r->shadow_retrace = r->sv.alpha_blending != 0 || r->any_stencil_always;
+    if (m) {
+        r->alpha_surfaces = false;
+        for (uint32_t i = 0; i < count; i++) {
+            const bool tex = m[i].albedoMap >= 0 && (size_t)m[i].albedoMap < r->tex_has_alpha.size() && r->tex_has_alpha[m[i].albedoMap];
+            if (m[i].baseColor.w < 1.0f || tex) r->alpha_surfaces = true;
+        }
+    }
+}
+
+static bool texels_have_alpha(const AtnVec4* t, size_t n)
+{
+    for (size_t i = 0; i < n; i++) if (t[i].w < 1.0f) return true;
+    return false;
+}
+
 static float scene_radius_of(const AtnSceneConfig& cfg)
 {
     // ImageBasedLight::sample (ibl.h:105-110): ComputeDistanceToCoverBoundingSphere(Deg2Rad(30))
@@ -2198,6 +2283,7 @@ static int alloc_paths(AtnRenderer* r, size_t n, size_t pixels)
     CUDA_TRY(cudaMemsetAsync(r->sh_c.p, 0, n * sizeof(float4), r->stream));      // ShadowRay::lightcontrib starts at zero
     CUDA_TRY(r->q_lit.resize(n)); CUDA_TRY(r->q_shadow.resize(n)); CUDA_TRY(r->q_exact.resize(n));
     CUDA_TRY(r->q_exact_s.resize(n)); CUDA_TRY(r->pend.resize(n));
+    CUDA_TRY(r->q_retrace0.resize(n)); CUDA_TRY(r->q_retrace1.resize(n));
     CUDA_TRY(r->hit_mesh.resize(n)); CUDA_TRY(r->aov_nd.resize(pixels)); CUDA_TRY(r->aov_am.resize(pixels));    // AOVs are per pixel
     CUDA_TRY(r->surf0.resize(n)); CUDA_TRY(r->surf1.resize(n)); CUDA_TRY(r->surf2.resize(n));
     CUDA_TRY(r->counters.resize(1));
@@ -2208,7 +2294,7 @@ static int alloc_paths(AtnRenderer* r, size_t n, size_t pixels)
     pb.throughput = r->throughput.p; pb.contrib = r->contrib.p; pb.contrib_late = r->contrib_late.p; pb.sampler_dim = r->sampler_dim.p; pb.flags = r->flags.p;
     pb.queue[0] = r->queue0.p; pb.queue[1] = r->queue1.p;
     pb.sh_o = r->sh_o.p; pb.sh_d = r->sh_d.p; pb.sh_c = r->sh_c.p;
-    pb.q_lit = r->q_lit.p; pb.q_shadow = r->q_shadow.p; pb.q_exact = r->q_exact.p; pb.q_exact_s = r->q_exact_s.p; pb.pend = r->pend.p;
+    pb.q_lit = r->q_lit.p; pb.q_shadow = r->q_shadow.p; pb.q_exact = r->q_exact.p; pb.q_exact_s = r->q_exact_s.p; pb.pend = r->pend.p; pb.q_retrace[0] = r->q_retrace0.p; pb.q_retrace[1] = r->q_retrace1.p;
     pb.hit_mesh = r->hit_mesh.p; pb.aov_nd = r->aov_nd.p; pb.aov_am = r->aov_am.p;
     pb.surf0 = r->surf0.p; pb.surf1 = r->surf1.p; pb.surf2 = r->surf2.p;
     return ATN_OK;
@@ -2372,6 +2458,11 @@ static int upload_scene_impl(AtnRenderer* r, const AtnSceneBlob* scene, const At
         if (t.texels && n) CUDA_TRY(cudaMemcpyAsync(r->texels.p + off, t.texels, n * sizeof(AtnVec4), cudaMemcpyHostToDevice, s));
         off += n;
     }
+    r->tex_has_alpha.assign(scene->texture_count, 0);
+    for (uint32_t i = 0; i < scene->texture_count; i++) {
+        const AtnTextureDesc& t = scene->textures[i];
+        if (t.texels) r->tex_has_alpha[i] = texels_have_alpha(t.texels, (size_t)t.width * t.height) ? 1 : 0;
+    }
     CUDA_TRY(r->texviews.upload(tv.data(), tv.size(), s));
     CUDA_TRY(cudaStreamSynchronize(s));
     r->h_texviews = tv;
@@ -2381,6 +2472,8 @@ static int upload_scene_impl(AtnRenderer* r, const AtnSceneBlob* scene, const At
     sv.triangles = r->triangles.p; sv.positions = r->positions.p; sv.normals = r->normals.p;
     sv.textures = r->texviews.p; sv.light_count = (int32_t)scene->light_count; sv.material_count = (int32_t)scene->material_count; sv.cfg = scene->config;
     sv.scene_radius = scene_radius_of(scene->config);
+    sv.alpha_blending = scene->enable_alpha_blending ? 1 : 0;
+    update_shadow_retrace(r, scene->materials, scene->material_count);
     r->bv.t_min = scene->config.bvh_hit_min > 0 ? scene->config.bvh_hit_min : kEps;
 
     int rc = upload_bvh(r, scene, cache_path, cache_hit);
@@ -2508,6 +2601,7 @@ ATN_API int atn_update_materials(AtnRenderer* r, const AtnMaterialParameter* m, 
     CUDA_TRY(r->materials.upload(m, count, r->stream));
     CUDA_TRY(cudaStreamSynchronize(r->stream));
     r->sv.materials = r->materials.p; r->sv.material_count = (int32_t)count;
+    update_shadow_retrace(r, m, count);
     return ATN_OK;
 }
 
@@ -2525,6 +2619,10 @@ ATN_API int atn_update_texture(AtnRenderer* r, uint32_t index, const AtnTextureD
     CUDA_TRY(cudaMemcpyAsync(const_cast<AtnVec4*>(tv.texels), texture->texels, (size_t)tv.w * tv.h * sizeof(AtnVec4),
                              cudaMemcpyHostToDevice, r->stream));
     CUDA_TRY(cudaStreamSynchronize(r->stream));
+    if (index < r->tex_has_alpha.size()) {
+        r->tex_has_alpha[index] = texels_have_alpha(texture->texels, (size_t)tv.w * tv.h) ? 1 : 0;
+        if (r->tex_has_alpha[index]) r->alpha_surfaces = true;      // conservative until the next material update
+    }
     return ATN_OK;
 }
 
@@ -2569,6 +2667,13 @@ ATN_API int atn_set_gather_mode(AtnRenderer* r, int mode)
     if (mode != ATN_GATHER_OVERWRITE && mode != ATN_GATHER_PROGRESSIVE && mode != ATN_GATHER_SUM)
         return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_set_gather_mode: mode %d is none of ATN_GATHER_OVERWRITE / PROGRESSIVE / SUM", mode);
     r->gather_mode = mode;
+    return ATN_OK;
+}
+ATN_API int atn_set_alpha_blending(AtnRenderer* r, int enable)
+{
+    if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL");
+    r->sv.alpha_blending = enable ? 1 : 0;
+    update_shadow_retrace(r, nullptr, 0);
     return ATN_OK;
 }
 ATN_API int atn_set_exact_ties(AtnRenderer* r, int enable) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->exact_ties = enable ? 1 : 0; return ATN_OK; }
@@ -2635,7 +2740,7 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
     cudaStream_t s = r->stream, side = r->side_stream;
     AtnMat4 w2c;
     for (int i = 0; i < 16; i++) w2c.m[i] = svgf_w2c ? svgf_w2c->m[i] : 0.0f;
-    const bool overlap = r->exact_ties && !tap_now;
+    const bool overlap = r->exact_ties && !tap_now && !r->shadow_retrace;
     const int side_grid = r->sm_count * 4;
     size_t se = 0;
     cudaEvent_t shadow_done = nullptr;            // side stream: the exact walk of the previous bounce's shadow rays
@@ -2667,12 +2772,31 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
         else k_bsdf<false><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, mainq, b, nullptr, 0);
         if (side_done) CUDA_TRY(cudaStreamWaitEvent(s, side_done, 0));       // the shadow and next-bounce queues are complete
         if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
-        if (tap_now) {
-            ShadowPolicy<true> pol{ pb, r->sv, r->tap_dev.p, r->tap_cap, b };
+        if (r->shadow_retrace) {
+            // HitTestToTargetLight's loop: lookup 0 over the shadow queue, lookups 1 .. 9 over the rays that restarted behind
+            // an ignored hit (a handful; an empty pass is a few microseconds).  One stream, exact walk in line.
+            for (int pass = 0; pass < 10; pass++) {
+                const int32_t* q_in = pass == 0 ? pb.q_shadow : pb.q_retrace[(pass - 1) & 1];
+                const int32_t* n_in = pass == 0 ? &c->n_shadow[b] : &c->retrace[b].n[pass - 1];
+                int32_t* fetch = pass == 0 ? &c->fetch_shadow[b] : &c->retrace[b].fetch[pass - 1];
+                int32_t* n_ex = pass == 0 ? &c->n_exact_shadow[b] : &c->retrace[b].n_exact[pass - 1];
+                if (tap_now) {
+                    ShadowPolicy<true, true> pol{ pb, r->sv, r->tap_dev.p, r->tap_cap, b, q_in, pb.q_retrace[pass & 1], &c->retrace[b].n[pass] };
+                    launch_trace<ShadowPolicy<true, true>>(r, s, pol, n_in, 0, fetch, r->visits.p, pb.q_exact_s, n_ex);
+                }
+                else {
+                    ShadowPolicy<false, true> pol{ pb, r->sv, nullptr, 0, b, q_in, pb.q_retrace[pass & 1], &c->retrace[b].n[pass] };
+                    launch_trace<ShadowPolicy<false, true>>(r, s, pol, n_in, 0, fetch, r->visits.p, pb.q_exact_s, n_ex);
+                }
+            }
+            *launches += 9 * (r->exact_ties ? 2 : 1);
+        }
+        else if (tap_now) {
+            ShadowPolicy<true> pol{ pb, r->sv, r->tap_dev.p, r->tap_cap, b, pb.q_shadow, nullptr, nullptr };
             launch_trace<ShadowPolicy<true>>(r, s, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p, pb.q_exact_s, &c->n_exact_shadow[b]);
         }
         else {
-            ShadowPolicy<false> pol{ pb, r->sv, nullptr, 0, b };
+            ShadowPolicy<false> pol{ pb, r->sv, nullptr, 0, b, pb.q_shadow, nullptr, nullptr };
             launch_trace<ShadowPolicy<false>>(r, s, pol, &c->n_shadow[b], 0, &c->fetch_shadow[b], r->visits.p, pb.q_exact_s, &c->n_exact_shadow[b], !overlap);
             if (overlap) {
                 cudaEvent_t traced = side_event(r, se++); shadow_done = side_event(r, se++);
@@ -2829,9 +2953,23 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
             CUDA_TRY(cudaMemsetAsync(&c->n_exact_query, 0, sizeof(int32_t), s));
             ClosestPolicy pol{ r->pb, r->pb.q_lit, radius, nullptr, 0 };
             launch_trace<ClosestPolicy>(r, s, pol, &c->n_lit[0], 0, &c->fetch_query, r->visits.p, r->pb.q_exact, &c->n_exact_query);
-            k_ao_accum<<<sgrid, kShadeBlock, 0, s>>>(r->sv, r->pb, c, radius, i == num_rays - 1 ? 1 : 0, num_rays);
+            if (r->alpha_surfaces) CUDA_TRY(cudaMemsetAsync(&c->retrace[0], 0, sizeof(Counters::Retrace), s));
+            k_ao_accum<<<sgrid, kShadeBlock, 0, s>>>(r->sv, r->pb, r->pb.q_lit, &c->n_lit[0], r->pb.q_retrace[0], &c->retrace[0].n[0], radius,
+                                                     r->alpha_surfaces ? 0 : 1);
             launches += 3;
+            // the AO ray's loop through surfaces that are translucent by alpha: lookups 2 .. 10 over the rays that restarted
+            for (int pass = 1; r->alpha_surfaces && pass < 10; pass++) {
+                const int32_t* q_in = r->pb.q_retrace[(pass - 1) & 1];
+                ClosestPolicy rp{ r->pb, q_in, radius, nullptr, 0 };
+                launch_trace<ClosestPolicy>(r, s, rp, &c->retrace[0].n[pass - 1], 0, &c->retrace[0].fetch[pass - 1], r->visits.p, r->pb.q_exact,
+                                            &c->retrace[0].n_exact[pass - 1]);
+                k_ao_accum<<<sgrid, kShadeBlock, 0, s>>>(r->sv, r->pb, q_in, &c->retrace[0].n[pass - 1], r->pb.q_retrace[pass & 1],
+                                                         &c->retrace[0].n[pass], radius, pass == 9 ? 1 : 0);
+                launches += 2;
+            }
         }
+        k_ao_finish<<<sgrid, kShadeBlock, 0, s>>>(r->pb, c, num_rays);
+        launches++;
         // n_active[0] primary rays + num_rays * n_lit[0] AO rays: folded into Totals by k_gather through
         // n_active[0] / n_shadow[0]; the AO rays are reported as shadow rays
         k_gather<<<grid, 256, 0, s>>>(fp, r->pb, r->image.p, r->gather_mode, smp == 0 ? 1 : 0, smp == spp - 1 ? 1 : 0, c, r->totals.p);
@@ -3038,7 +3176,7 @@ ATN_API int atn_render_restir(AtnRenderer* r, int32_t width, int32_t height, int
     k_bsdf<false><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, ShadeQueues{ nullptr, &c->n_active[0], pb.q_lit, &c->n_lit[0], 0 }, 0, nullptr, 0);
     k_restir_visibility<<<sgrid, kShadeBlock, 0, s>>>(fp, pb, rv, c);
     {
-        RestirShadowPolicy pol{ ShadowPolicy<false>{ pb, r->sv, nullptr, 0, 0 }, rv.cur };
+        RestirShadowPolicy pol{ ShadowPolicy<false>{ pb, r->sv, nullptr, 0, 0, pb.q_shadow, nullptr, nullptr }, rv.cur };
         launch_trace<RestirShadowPolicy>(r, s, pol, &c->n_shadow[0], 0, &c->fetch_shadow[0], r->visits.p, pb.q_exact, &c->n_exact_shadow[0]);
     }
     launches += 7;

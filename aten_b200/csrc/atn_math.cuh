@@ -281,6 +281,7 @@ struct SceneView {
     int32_t material_count;
     AtnSceneConfig cfg;
     float scene_radius;      // ComputeDistanceToCoverBoundingSphere(30 deg) or 10000 (ibl.h:105-110)
+    int32_t alpha_blending;  // SceneRenderingConfig::enable_alpha_blending (scene_rendering_config.h:21): shadow rays pass alpha surfaces
 };
 
 ATN_HD AtnVec4 ld4(const AtnVec4* p)
@@ -1409,56 +1410,102 @@ ATN_HD Ray ao_ray(const V3& p, const V3& n, Sampler* sampler, V3* next_dir)
     *next_dir = lambert_dir(n, r1, r2);
     return make_ray(p, *next_dir, n);
 }
-// Result of that ray's closest hit (traced with t_max = radius): aorenderer_impl.h:80-111.
-// Occluders that are translucent by alpha are re-traced up to 10 times by the reference; that loop is
-// not reproduced (no such material in any config) -- they count as opaque here.
-ATN_HD float ao_accumulate(const SceneView& sc, float ao, const V3& n, const V3& next_dir, const Ray& ray, float radius,
-                           int32_t hit_objid, int32_t hit_primid, float hit_a, float hit_b, float hit_t, int32_t hit_mtrlid)
+// One lookup of the AO ray's loop (aorenderer_impl.h:72-111): the closest hit of `ray`, traced with t_max = radius.  A hit
+// on a surface that is translucent by alpha is ignored: the ray restarts behind it (aten::ray(p, ray.dir, normal turned
+// along the ray) -- direction normalised again, origin offset) and is traced again, up to 10 lookups; when the last one is
+// ignored too, nothing is added.  Returns true when the ray has to be traced again from *next.
+ATN_HD bool ao_accumulate(const SceneView& sc, float* ao, const V3& n, const V3& next_dir, const Ray& ray, float radius,
+                          int32_t hit_objid, int32_t hit_primid, float hit_a, float hit_b, float hit_t, int32_t hit_mtrlid,
+                          bool last_lookup, Ray* next)
 {
-    if (hit_objid < 0) return 1.0f;            // `ao_color = 1.0f` (assignment, as in the reference)
+    if (hit_objid < 0) { *ao = 1.0f; return false; }            // `ao_color = 1.0f` (assignment, as in the reference)
     HitRecord rec;
     evaluate_hit(sc, sc.objects[hit_objid], ray, hit_primid, hit_a, hit_b, hit_t, hit_mtrlid, &rec);
+    if (hit_mtrlid >= 0) {                                      // material::isTranslucentByAlpha (material.cpp:193-210)
+        const AtnMaterialParameter& m = sc.materials[hit_mtrlid];
+        const float alpha = sample_texture(sc, m.albedoMap, rec.u, rec.v, v4(1.0f)).w * m.baseColor.w;
+        if (alpha < 1.0f) {
+            if (last_lookup) return false;
+            V3 on = rec.normal;
+            if (!(dot(rec.normal, ray.dir) > 0.0f)) on = -on;
+            *next = make_ray(rec.p, ray.dir, on);
+            return true;
+        }
+    }
     const float c = dot(rec.normal, next_dir);
     if (c > 0.0f) {
         const float pdfb = lambert_pdf(n, next_dir);
-        ao += hit_t / radius * c / pdfb;
+        *ao += hit_t / radius * c / pdfb;
     }
-    return ao;
+    return false;
 }
 
-// Decision after the shadow ray's closest-hit traversal: HitTestToTargetLight
-// (pathtracing_impl.h:266-351, one lookup: alpha blending / stencil are off on this path) +
-// scene::hitLight (src/libaten/scene/scene.h:120-133).
-// `hit_*` describe the closest hit found with t_max = dist - 1e-9 (hit_objid < 0: none).
+// HitTestToTargetLight (pathtracing_impl.h:266-351) + scene::hitLight (src/libaten/scene/scene.h:120-133), one LOOKUP of
+// its loop at a time.  The reference traces the shadow ray's closest hit (t_max = dist - 1e-9, with the ORIGINAL distance
+// on every lookup); a hit on a surface that is translucent by alpha (material::isTranslucentByAlpha, material.cpp:193-210)
+// or -- when the surface the shadow ray left has stencil type ALWAYS -- on a STENCIL surface is ignored: the ray restarts
+// behind it (aten::ray(rec.p, original dir, normal turned along the ray): the direction is normalised AGAIN, the origin
+// offset) and is traced again, up to shadow_max_lookups() times; when the last lookup is ignored too the light counts as
+// not reached.  `hitobj` keeps the last object hit across lookups (the reference never resets it), so a lookup that
+// finds nothing after an ignored hit does not reach an area light.
+enum : int { kShadowHidden = 0, kShadowVisible = 1, kShadowRetrace = 2 };
+enum : int { kStencilNone = 0, kStencilAlways = 1, kStencilStencil = 2 };       // aten::StencilType (material.h:224-228)
+
+ATN_HD int32_t shadow_light_obj(const AtnLightParameter& light)
+{
+    return (light.type == 0 && light.arealight_objid >= 0) ? light.arealight_objid : -1;       // IsValidLightObjectId
+}
+// `surface_mtrlid`: the material of the surface the shadow ray starts from (HitShadowRay's surface_mtrl)
+ATN_HD bool shadow_needs_stencil(const SceneView& sc, int32_t surface_mtrlid)
+{
+    return surface_mtrlid >= 0 && sc.materials[surface_mtrlid].stencil_type == kStencilAlways;
+}
+ATN_HD int shadow_max_lookups(const SceneView& sc, bool need_stencil) { return (sc.alpha_blending || need_stencil) ? 10 : 1; }
+
+// `ray` is this lookup's ray, `orig_dir` the direction of the first one; `hit_*` its closest hit (hit_objid < 0: none);
+// `*hitobj` starts as shadow_light_obj().  kShadowRetrace: trace again from *next_org along normalize(orig_dir).
+ATN_HD int shadow_lookup(const SceneView& sc, const AtnLightParameter& light, const Ray& ray, const V3& orig_dir, float dist_to_light,
+                         int32_t hit_objid, int32_t hit_primid, float hit_a, float hit_b, float hit_t, int32_t hit_mtrlid,
+                         bool last_lookup, bool need_stencil, int32_t* hitobj, V3* next_org)
+{
+    const bool is_hit = hit_objid >= 0;
+    if (is_hit) {
+        *hitobj = hit_objid;
+        const AtnMaterialParameter& m = sc.materials[hit_mtrlid < 0 ? 0 : hit_mtrlid];
+        bool ignore = need_stencil && hit_mtrlid >= 0 && m.stencil_type == kStencilStencil;
+        const bool textured = hit_mtrlid >= 0 && m.albedoMap >= 0;
+        HitRecord rec;
+        bool have_rec = false;
+        float alpha = hit_mtrlid < 0 ? 1.0f : 1.0f * m.baseColor.w;
+        if (textured) {
+            evaluate_hit(sc, sc.objects[hit_objid], ray, hit_primid, hit_a, hit_b, hit_t, hit_mtrlid, &rec);
+            have_rec = true;
+            alpha = sample_texture(sc, m.albedoMap, rec.u, rec.v, v4(1.0f)).w * m.baseColor.w;
+        }
+        if (alpha < 1.0f) ignore = true;
+        if (ignore) {
+            if (last_lookup) return kShadowHidden;              // the loop runs out: is_hit_to_light stays false
+            if (!have_rec) evaluate_hit(sc, sc.objects[hit_objid], ray, hit_primid, hit_a, hit_b, hit_t, hit_mtrlid, &rec);
+            V3 n = rec.normal;
+            if (!(dot(rec.normal, orig_dir) > 0.0f)) n = -n;    // "to go through the object, specify the opposite normal"
+            *next_org = ray_offset(rec.p, n);
+            return kShadowRetrace;
+        }
+    }
+    if (*hitobj == shadow_light_obj(light)) return kShadowVisible;
+    if (light.attrib & 2u) return is_hit ? kShadowHidden : kShadowVisible;
+    if (light.attrib & 1u) return hit_t > dist_to_light ? kShadowVisible : kShadowHidden;
+    return kShadowHidden;
+}
+
+// The single-lookup form (alpha blending off, no stencil): what every config of BASELINE.json runs.
 ATN_HD bool shadow_visible(const SceneView& sc, const AtnLightParameter& light, const Ray& ray, float dist_to_light,
                            int32_t hit_objid, int32_t hit_primid, float hit_a, float hit_b, float hit_t, int32_t hit_mtrlid)
 {
-    const bool is_hit = hit_objid >= 0;
-    const int32_t light_obj = (light.type == 0 && light.arealight_objid >= 0) ? light.arealight_objid : -1;
-    int32_t hitobj = light_obj;
-    if (is_hit) {
-        hitobj = hit_objid;
-        // material::isTranslucentByAlpha (src/libaten/material/material.cpp:193-210): an ignored
-        // hit `continue`s the single-iteration loop, i.e. the light is reported as not reached.
-        const AtnMaterialParameter& m = sc.materials[hit_mtrlid < 0 ? 0 : hit_mtrlid];
-        float alpha = m.baseColor.w;
-        if (hit_mtrlid < 0) {
-            alpha = 1.0f;
-        }
-        else if (m.albedoMap >= 0) {
-            HitRecord rec;
-            evaluate_hit(sc, sc.objects[hit_objid], ray, hit_primid, hit_a, hit_b, hit_t, hit_mtrlid, &rec);
-            alpha = sample_texture(sc, m.albedoMap, rec.u, rec.v, v4(1.0f)).w * m.baseColor.w;
-        }
-        else {
-            alpha = 1.0f * m.baseColor.w;
-        }
-        if (alpha < 1.0f) return false;
-    }
-    if (hitobj == light_obj) return true;
-    if (light.attrib & 2u) return !is_hit;
-    if (light.attrib & 1u) return hit_t > dist_to_light;
-    return false;
+    int32_t hitobj = shadow_light_obj(light);
+    V3 unused;
+    return shadow_lookup(sc, light, ray, ray.dir, dist_to_light, hit_objid, hit_primid, hit_a, hit_b, hit_t, hit_mtrlid,
+                         true, false, &hitobj, &unused) == kShadowVisible;
 }
 
 }  // namespace atn

@@ -5,7 +5,7 @@ arrays ``Renderer::UpdateSceneData`` reads from ``aten::context`` (reference
 src/libidaten/kernel/renderer.cpp:12-131) in the reference's own struct layouts, little endian::
 
     char[8]  "ATNSCN01"
-    u32[10]  objects, matrices, materials, lights, triangles, vertices, node_lists, textures, seeds, 0
+    u32[10]  objects, matrices, materials, lights, triangles, vertices, node_lists, textures, seeds, flags (bit 0: alpha blending)
     AtnSceneConfig (56 B)   AtnCameraParameter (124 B)   i32 width, height
     objects[64 B]  matrices[64 B]  materials[248 B]  lights[80 B]  triangles[32 B]
     positions[16 B]  normals[16 B]
@@ -95,7 +95,7 @@ class AtnSceneBlob(C.Structure):
                 ("node_lists", C.POINTER(C.c_void_p)), ("node_list_sizes", C.c_void_p),
                 ("node_list_count", C.c_uint32),
                 ("textures", C.POINTER(AtnTextureDesc)), ("texture_count", C.c_uint32),
-                ("config", AtnSceneConfig)]
+                ("config", AtnSceneConfig), ("enable_alpha_blending", C.c_int32)]
 
 
 assert C.sizeof(AtnSceneConfig) == 56
@@ -118,6 +118,7 @@ class Scene:
     width: int
     height: int
     seeds: np.ndarray
+    alpha_blending: bool = False      # SceneRenderingConfig::enable_alpha_blending
     _keep: list = field(default_factory=list, repr=False)
 
     def seeds_for(self, count: int) -> np.ndarray:
@@ -184,6 +185,7 @@ class Scene:
         b.textures = C.cast(tarr, C.POINTER(AtnTextureDesc))
         b.texture_count = nt
         C.memmove(C.byref(b.config), ptr(self.config), 56)
+        b.enable_alpha_blending = 1 if self.alpha_blending else 0
         self._keep = keep
         return b
 
@@ -200,7 +202,7 @@ def load_scene(path: str) -> Scene:
         raise ValueError(f"{path}: not an .atnscene file")
     off = 8
     counts = np.frombuffer(buf, "<u4", 10, off); off += 40
-    n_obj, n_mtx, n_mtrl, n_light, n_tri, n_vtx, n_lists, n_tex, n_seed, _ = (int(c) for c in counts)
+    n_obj, n_mtx, n_mtrl, n_light, n_tri, n_vtx, n_lists, n_tex, n_seed, flags = (int(c) for c in counts)
 
     def take(dtype, n):
         nonlocal off
@@ -227,7 +229,7 @@ def load_scene(path: str) -> Scene:
         textures.append((take("<f4", w * h * 4).reshape(h, w, 4), int(hdr[2]), int(hdr[3])))
     seeds = take("<u4", n_seed) if n_seed else None
     return Scene(objects, matrices, materials, lights, triangles, positions, normals, node_lists, textures,
-                 config, camera, int(wh[0]), int(wh[1]), seeds)
+                 config, camera, int(wh[0]), int(wh[1]), seeds, bool(flags & 1))
 
 
 def save_scene(scene: Scene, path: str, with_seeds: bool = False) -> None:
@@ -237,7 +239,7 @@ def save_scene(scene: Scene, path: str, with_seeds: bool = False) -> None:
         fp.write(b"ATNSCN01")
         fp.write(np.array([len(scene.objects), len(scene.matrices), len(scene.materials), len(scene.lights),
                            len(scene.triangles), len(scene.positions), len(scene.node_lists),
-                           len(scene.textures), len(seeds), 0], "<u4").tobytes())
+                           len(scene.textures), len(seeds), 1 if scene.alpha_blending else 0], "<u4").tobytes())
         fp.write(scene.config.tobytes()); fp.write(scene.camera.tobytes())
         fp.write(np.array([scene.width, scene.height], "<i4").tobytes())
         for a in (scene.objects, scene.matrices, scene.materials, scene.lights, scene.triangles,

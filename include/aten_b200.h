@@ -185,6 +185,7 @@ typedef struct AtnSceneBlob {
     uint32_t node_list_count;
     const AtnTextureDesc* textures;          uint32_t texture_count;
     AtnSceneConfig config;
+    int32_t enable_alpha_blending;           /* SceneRenderingConfig::enable_alpha_blending (scene_rendering_config.h:21) */
 } AtnSceneBlob;
 
 /* Work counters of the last atn_render / atn_trace_* call. */
@@ -259,6 +260,11 @@ ATN_API int atn_update_texture(AtnRenderer* r, uint32_t index, const AtnTextureD
 ATN_API int atn_update_lights(AtnRenderer* r, const AtnLightParameter* l, uint32_t count);
 /* Renderer::UpdateSceneRenderingConfig (renderer.h:103-106) */
 ATN_API int atn_update_config(AtnRenderer* r, const AtnSceneConfig* cfg);
+/* SceneRenderingConfig::enable_alpha_blending (scene_rendering_config.h:21), also set by the scene blob at upload.  With it
+ * on (or for shadow rays that leave a surface of stencil type ALWAYS) a shadow ray whose closest hit is translucent by
+ * alpha (or a STENCIL surface) restarts behind that hit, up to 10 lookups -- HitTestToTargetLight,
+ * src/libaten/renderer/pathtracing/pathtracing_impl.h:266-351. */
+ATN_API int atn_set_alpha_blending(AtnRenderer* r, int enable);
 /* Renderer::initSamplerParameter (renderer.h:113-124): per-pixel seeds = aten::getRandom(). */
 ATN_API int atn_set_seeds(AtnRenderer* r, const uint32_t* seeds, uint32_t count);
 

@@ -62,6 +62,7 @@ struct FlatScene {
     std::vector<AtnTextureDesc> textures;
     std::vector<std::shared_ptr<aten::texture>> texture_refs;
     AtnSceneConfig config{};
+    bool enable_alpha_blending{ false };
 
     // scratch for the blob view
     std::vector<const AtnBvhNode*> node_ptrs;
@@ -125,6 +126,7 @@ struct FlatScene {
         config.avgIllum = cfg.bg.avgIllum;
         config.multiplyer = cfg.bg.multiplyer;
         config.enable_env_map = cfg.bg.enable_env_map ? 1 : 0;
+        enable_alpha_blending = cfg.enable_alpha_blending;
         const auto& bb = ctxt.GetSceneBoundingBox();
         const auto bmin = bb.minPos();
         const auto bmax = bb.maxPos();
@@ -160,6 +162,7 @@ struct FlatScene {
         b.textures = textures.data();
         b.texture_count = static_cast<uint32_t>(textures.size());
         b.config = config;
+        b.enable_alpha_blending = enable_alpha_blending ? 1 : 0;
         return b;
     }
 
@@ -177,7 +180,8 @@ struct FlatScene {
         uint32_t counts[10] = {
             (uint32_t)objects.size(), (uint32_t)matrices.size(), (uint32_t)materials.size(),
             (uint32_t)lights.size(), (uint32_t)triangles.size(), (uint32_t)positions.size(),
-            (uint32_t)nodes.size(), (uint32_t)textures.size(), (uint32_t)seeds.size(), 0u };
+            (uint32_t)nodes.size(), (uint32_t)textures.size(), (uint32_t)seeds.size(),
+            enable_alpha_blending ? 1u : 0u };      // flags: bit 0 = enable_alpha_blending
         w(counts, sizeof(counts));
         w(&config, sizeof(config));
         w(&camera, sizeof(camera));
@@ -321,7 +325,9 @@ public:
         tmp.config.multiplyer = cfg.bg.multiplyer;
         tmp.config.enable_env_map = cfg.bg.enable_env_map ? 1 : 0;
         flat_.config = tmp.config;
+        flat_.enable_alpha_blending = cfg.enable_alpha_blending;
         Check(atn_update_config(h_, &flat_.config));
+        Check(atn_set_alpha_blending(h_, cfg.enable_alpha_blending ? 1 : 0));
     }
 
     void reset() { Check(atn_reset(h_)); }

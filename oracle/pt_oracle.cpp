@@ -62,6 +62,7 @@ Scene MakeScene(const AtnSceneBlob* b)
         radius = r / tanf(theta / 2);
     }
     s.view.scene_radius = radius;
+    s.view.alpha_blending = b->enable_alpha_blending ? 1 : 0;
     s.t_min = b->config.bvh_hit_min > 0 ? b->config.bvh_hit_min : kEps;
     return s;
 }
@@ -237,10 +238,23 @@ int oracle_render(const AtnSceneBlob* blob, const AtnCameraParameter* cam, const
                         if (!st.terminated && sh.active) {
                             n_shadow++;
                             Ray sr; sr.org = sh.org; sr.dir = normalize(sh.dir);   // aten::ray(org, dir) renormalises
-                            AtnHit shit;
-                            Traverse(s, sr, sh.dist - kEps, &shit, want_cnt ? &cnt : nullptr);
-                            const bool vis = shadow_visible(s.view, s.view.lights[sh.light_id], sr, sh.dist,
-                                                            shit.objid, shit.primid, shit.a, shit.b, shit.t, shit.mtrlid);
+                            // HitTestToTargetLight's loop (pathtracing_impl.h:288-348): one lookup unless alpha blending is on
+                            // or the surface has stencil type ALWAYS
+                            const AtnLightParameter& light = s.view.lights[sh.light_id];
+                            const bool need_stencil = shadow_needs_stencil(s.view, isect.mtrlid);
+                            const int lookups = shadow_max_lookups(s.view, need_stencil);
+                            const V3 orig_dir = sr.dir;
+                            int32_t hitobj = shadow_light_obj(light);
+                            bool vis = false;
+                            for (int k = 0; k < lookups; k++) {
+                                AtnHit shit;
+                                Traverse(s, sr, sh.dist - kEps, &shit, want_cnt ? &cnt : nullptr);
+                                V3 next_org;
+                                const int res = shadow_lookup(s.view, light, sr, orig_dir, sh.dist, shit.objid, shit.primid, shit.a, shit.b,
+                                                              shit.t, shit.mtrlid, k + 1 >= lookups, need_stencil, &hitobj, &next_org);
+                                if (res != kShadowRetrace) { vis = res == kShadowVisible; break; }
+                                sr.org = next_org; sr.dir = normalize(orig_dir);      // aten::ray(rec.p, original_ray.dir, normal)
+                            }
                             if (vis) st.contrib = st.contrib + sh.lightcontrib;
                             rec.shadow_active = 1;
                             rec.shadow_org[0] = sh.org.x; rec.shadow_org[1] = sh.org.y; rec.shadow_org[2] = sh.org.z;
@@ -320,10 +334,14 @@ int oracle_render_ao(const AtnSceneBlob* blob, const AtnCameraParameter* cam, co
                     ao_surface(s.view, ray, isect.objid, isect.primid, isect.a, isect.b, isect.t, isect.mtrlid, &p, &n);
                     for (int32_t i = 0; i < num_rays; i++) {
                         V3 next_dir;
-                        const Ray ar = ao_ray(p, n, &sp, &next_dir);
-                        AtnHit ah;
-                        Traverse(s, ar, radius, &ah, nullptr);
-                        ao = ao_accumulate(s.view, ao, n, next_dir, ar, radius, ah.objid, ah.primid, ah.a, ah.b, ah.t, ah.mtrlid);
+                        Ray ar = ao_ray(p, n, &sp, &next_dir);
+                        for (int k = 0; k < 10; k++) {          // MAX_LOOP (aorenderer_impl.h:68)
+                            AtnHit ah;
+                            Traverse(s, ar, radius, &ah, nullptr);
+                            Ray next;
+                            if (!ao_accumulate(s.view, &ao, n, next_dir, ar, radius, ah.objid, ah.primid, ah.a, ah.b, ah.t, ah.mtrlid, k == 9, &next)) break;
+                            ar = next;
+                        }
                     }
                     ao /= num_rays;
                 }

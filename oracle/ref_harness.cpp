@@ -216,6 +216,41 @@ struct Harness {
         ctxt.scene_rendering_config.bg = AT_NAME::Background::CreateBackgroundResource(nullptr, aten::vec4(0.0f));
     }
 
+    // The reference's AlphaBlendedObjCornellBoxScene (src/common/scenedefs.cpp:888-926): Cornell box whose back wall, left
+    // wall and tall box are translucent by alpha, with SceneRenderingConfig::enable_alpha_blending on -- shadow rays pass
+    // through those surfaces in up to 10 lookups (HitTestToTargetLight, pathtracing_impl.h:266-351).  The floor gets
+    // stencil type ALWAYS and the short box STENCIL, so that the stencil branch of the same loop is exercised too.
+    void BuildCornellAlpha()
+    {
+        ctxt.scene_rendering_config.enable_alpha_blending = true;
+        auto emit = MakeMtrl("light", ctxt, aten::MaterialType::Emissive, aten::vec3(1.0f));
+        auto objs = aten::ObjLoader::Load(
+            g_asset + "/cornellbox/orig.obj", ctxt,
+            [&](std::string_view name, aten::context& c, aten::MaterialType type, const aten::vec3& clr,
+                const std::string&, const std::string&) -> std::shared_ptr<aten::material> {
+                auto m = MakeMtrl(name, c, type, clr);
+                if (name == "backWall") m->param().baseColor.a = 0.0f;
+                if (name == "leftWall") m->param().baseColor.a = 0.5f;
+                if (name == "tallBox") m->param().baseColor.a = 0.25f;
+                if (name == "floor") m->param().stencil_type = aten::StencilType::ALWAYS;
+                if (name == "shortBox") m->param().stencil_type = aten::StencilType::STENCIL;
+                return m;
+            },
+            nullptr, true, true);
+        auto light = aten::TransformableFactory::createInstance<aten::PolygonObject>(
+            ctxt, objs[0], aten::vec3(0.0f), aten::vec3(0.0f), aten::vec3(1.0f));
+        scene.add(light);
+        ctxt.AddLight(std::make_shared<aten::AreaLight>(light, emit->param().baseColor, 100.0f));
+        // lights behind the translucent walls: their shadow rays have to pass the walls
+        ctxt.AddLight(std::make_shared<aten::PointLight>(aten::vec3(-2.5f, 1.2f, 0.3f), aten::vec3(1.0f, 0.8f, 0.6f), 40.0f));
+        ctxt.AddLight(std::make_shared<aten::DirectionalLight>(aten::vec3(0.1f, -0.3f, 1.0f), aten::vec3(0.6f, 0.8f, 1.0f), 1.5f));
+        for (size_t i = 1; i < objs.size(); i++) {
+            scene.add(aten::TransformableFactory::createInstance<aten::PolygonObject>(ctxt, objs[i], aten::mat4::Identity));
+        }
+        SetCamera(aten::vec3(0.f, 1.f, 3.f), aten::vec3(0.f, 1.f, 0.f), 45.0f);
+        ctxt.scene_rendering_config.bg = AT_NAME::Background::CreateBackgroundResource(nullptr, aten::vec4(0.0f));
+    }
+
     // C2 stand-in: asset/sponza/sponza_lod.obj + the shipped sponza_lod.sbvh (the full-resolution
     // Sponza OBJ/SBVH are stripped from the snapshot).  Materials from the .mtl
     // (Lambert), arches/columns switched to GGX; lit by the synthetic-sky IBL plus one area light.
@@ -373,6 +408,7 @@ struct Harness {
         if (name == "cornell") BuildCornell();
         else if (name == "cornell_mtrl") BuildCornellMaterials();
         else if (name == "cornell_sphere") BuildCornellSphere();
+        else if (name == "cornell_alpha") BuildCornellAlpha();
         else if (name == "sponza") BuildSponza(false, false);
         else if (name == "sponza_atrium") BuildSponza(false, true);
         else if (name == "sponza_tex") BuildSponza(true, true);

@@ -34,6 +34,7 @@ SCENES = {  # name: (W, H)
     "sponza_atrium": (64, 36),
     "instanced": (64, 36),
     "cornell_sphere": (64, 64),     # a sphere area light + a sphere object in the top layer (sphere.cpp:30-150, arealight.h:88-130)
+    "cornell_alpha": (64, 64),      # alpha blending on + stencil materials: shadow rays re-traced through ignored hits (pathtracing_impl.h:266-351)
 }
 FRAME = 2
 FRAMES = 3
@@ -101,11 +102,17 @@ def main():
         make_restir()
         return
     meta = {}
-    with tempfile.TemporaryDirectory() as d:
-        p = os.path.join(d, "cmj.bin")
-        ol.ref_run("cmj", p)
-        gz_write(os.path.join(HERE, "cmj.f32.gz"), open(p, "rb").read())
+    only = sys.argv[2:] if len(sys.argv) > 2 and sys.argv[1] == "only" else None     # `only <scene> ...`: add scenes, keep the rest
+    if only:
+        meta = json.load(open(os.path.join(HERE, "meta.json")))
+    else:
+        with tempfile.TemporaryDirectory() as d:
+            p = os.path.join(d, "cmj.bin")
+            ol.ref_run("cmj", p)
+            gz_write(os.path.join(HERE, "cmj.f32.gz"), open(p, "rb").read())
     for name, (W, H) in SCENES.items():
+        if only and name not in only:
+            continue
         with tempfile.TemporaryDirectory() as d:
             ps = os.path.join(d, "s.atnscene")
             info = ol.ref_run("scene", name, W, H, ps)
@@ -128,6 +135,8 @@ def main():
                       "hit_fraction": float((hits["objid"] >= 0).mean())}
         print(name, meta[name])
     json.dump(meta, open(os.path.join(HERE, "meta.json"), "w"), indent=1, sort_keys=True)
+    if only:
+        return
     make_svgf()
     make_restir()
 

@@ -12,7 +12,7 @@ from tests import emu_lib
 from tests import oracle_lib as ol
 from tests.test_gpu_parity import assert_hits_equal
 
-SCENES = ["cornell", "cornell_mtrl", "instanced", "sponza_atrium", "cornell_sphere"]
+SCENES = ["cornell", "cornell_mtrl", "instanced", "sponza_atrium", "cornell_sphere", "cornell_alpha"]
 
 
 @pytest.mark.parametrize("name", SCENES)

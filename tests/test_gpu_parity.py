@@ -20,7 +20,7 @@ from tests.conftest import bits
 
 pytestmark = pytest.mark.gpu
 
-SCENES = ["cornell", "cornell_mtrl", "sponza_atrium", "instanced", "cornell_sphere"]
+SCENES = ["cornell", "cornell_mtrl", "sponza_atrium", "instanced", "cornell_sphere", "cornell_alpha"]
 FLT_MAX = np.finfo(np.float32).max
 
 
@@ -464,7 +464,7 @@ def test_first_hit_aovs_vs_oracle(golden, renderers, name):
     assert np.allclose(np.linalg.norm(nd[..., :3][hit], axis=-1), 1.0, atol=1e-5)
 
 
-@pytest.mark.parametrize("name", ["sponza_atrium", "instanced", "cornell"])
+@pytest.mark.parametrize("name", ["sponza_atrium", "instanced", "cornell", "cornell_alpha"])
 def test_ao_renderer_vs_oracle(golden, renderers, name):
     """Row N1 on the GPU (atn_render_ao) against the restatement in per-pixel mode, and against the stock
     aten::AORenderer film wherever the host renderer wrote a pixel.  The AO value involves sin/cos

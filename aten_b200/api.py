@@ -26,7 +26,7 @@ EXPORTS = [
     "atn_trace_any_device", "atn_set_bounce_tap", "atn_trace_closest_static", "atn_readback_aov", "atn_render_ao",
     "atn_render_svgf", "atn_set_motion_depth", "atn_readback_svgf", "atn_update_texture",
     "atn_render_restir", "atn_readback_restir", "atn_probe_read_bandwidth",
-    "atn_upload_scene_cached", "atn_set_alpha_blending", "atn_sbvh_read", "atn_sbvh_write", "atn_free",
+    "atn_upload_scene_cached", "atn_set_alpha_blending", "atn_set_texture_fetch", "atn_sbvh_read", "atn_sbvh_write", "atn_free",
 ]
 
 
@@ -232,6 +232,11 @@ class PathTracing:
         """AtnGatherMode: GATHER_OVERWRITE / GATHER_PROGRESSIVE / GATHER_SUM (sum of samples + count in .w, for the
         multi-GPU reduce)."""
         _check(self._lib, self._lib.atn_set_gather_mode(self._h, C.c_int(mode)))
+
+    def set_texture_fetch(self, device_semantics: bool):
+        """False (default): the reference's host texel rule (parity runs); True: its GPU renderer's tex2DLod semantics with
+        each texture's filter / address mode, in software (parity unpinned, see include/aten_b200.h)."""
+        _check(self._lib, self._lib.atn_set_texture_fetch(self._h, C.c_int(1 if device_semantics else 0)))
 
     def set_alpha_blending(self, b: bool):
         """SceneRenderingConfig::enable_alpha_blending (also taken from the scene at upload): shadow rays restart behind

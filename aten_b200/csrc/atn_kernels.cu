@@ -2454,7 +2454,7 @@ static int upload_scene_impl(AtnRenderer* r, const AtnSceneBlob* scene, const At
         const AtnTextureDesc& t = scene->textures[i];
         const size_t n = (size_t)t.width * t.height;
         tv[i].texels = t.texels ? r->texels.p + off : nullptr;
-        tv[i].w = t.width; tv[i].h = t.height;
+        tv[i].w = t.width; tv[i].h = t.height; tv[i].filter = t.filter_mode; tv[i].address = t.address_mode;
         if (t.texels && n) CUDA_TRY(cudaMemcpyAsync(r->texels.p + off, t.texels, n * sizeof(AtnVec4), cudaMemcpyHostToDevice, s));
         off += n;
     }
@@ -2667,6 +2667,12 @@ ATN_API int atn_set_gather_mode(AtnRenderer* r, int mode)
     if (mode != ATN_GATHER_OVERWRITE && mode != ATN_GATHER_PROGRESSIVE && mode != ATN_GATHER_SUM)
         return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_set_gather_mode: mode %d is none of ATN_GATHER_OVERWRITE / PROGRESSIVE / SUM", mode);
     r->gather_mode = mode;
+    return ATN_OK;
+}
+ATN_API int atn_set_texture_fetch(AtnRenderer* r, int device_semantics)
+{
+    if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL");
+    r->sv.device_texture_fetch = device_semantics ? 1 : 0;
     return ATN_OK;
 }
 ATN_API int atn_set_alpha_blending(AtnRenderer* r, int enable)

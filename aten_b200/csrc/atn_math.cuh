@@ -266,7 +266,7 @@ ATN_HD bool sphere_hit(const V3& center, float radius, const Ray& r, float* t_ou
 // ---------------------------------------------------------------------------------------------
 // Scene view: the flat arrays of AtnSceneBlob as the math sees them
 // ---------------------------------------------------------------------------------------------
-struct TexView { const AtnVec4* texels; int32_t w, h; };
+struct TexView { const AtnVec4* texels; int32_t w, h; int32_t filter, address; };   // aten::TextureFilterMode / TextureAddressMode
 
 struct SceneView {
     const AtnObjectParameter* objects;
@@ -281,6 +281,7 @@ struct SceneView {
     int32_t material_count;
     AtnSceneConfig cfg;
     float scene_radius;      // ComputeDistanceToCoverBoundingSphere(30 deg) or 10000 (ibl.h:105-110)
+    int32_t device_texture_fetch;   // 0: aten::texture::at (host rule, parity runs); 1: the GPU renderer's tex2DLod semantics per texture
     int32_t alpha_blending;  // SceneRenderingConfig::enable_alpha_blending (scene_rendering_config.h:21): shadow rays pass alpha surfaces
 };
 
@@ -302,11 +303,60 @@ ATN_HD int32_t wrap_repeat(int32_t value, int32_t wrap)
     else if (value < 0) { int32_t n = value / wrap; if (n < 0) n = -n; value += (n + 1) * wrap; }
     return value;
 }
+// The fetch the reference's GPU renderer does instead (device sampleTexture, sample_texture.h:18-35: tex2DLod<float4> on a
+// texture object with normalised coordinates and the texture's own filter and address mode, cudaTextureResource.cpp:210-236),
+// written out in software after the texture-fetch formulas of the CUDA programming guide: with N texels along an axis and
+// x = N * coordinate, point filtering reads T[floor(x)]; linear filtering reads T[i], T[i+1] with i = floor(x - 0.5) and the
+// weight frac(x - 0.5) held in 8 fractional bits; wrap takes the fractional part of the coordinate and wraps indices, clamp
+// clamps indices to the edge, mirror reflects every other period, border reads zeros outside.  PARITY UNPINNED: there is no
+// GPU build of the reference on this box to compare with (no graphics stack for libidaten); pinned only to an independent
+// restatement of the same published formulas (tests/test_texture_fetch.py).  Only mip level 0 exists (lod is ignored).
+ATN_HD float tex_coord(float c, int32_t address)
+{
+    if (address == 0) return c - floorf(c);                                    // Wrap
+    if (address == 2) { const float f = floorf(c); const float r = c - f; return ((int32_t)f & 1) ? 1.0f - r : r; }     // Mirror
+    return c;                                                                   // Clamp, Border: as is
+}
+ATN_HD AtnVec4 tex_texel(const TexView& t, int32_t i, int32_t j)
+{
+    if (t.address == 0) {                                                       // Wrap: indices modulo the size
+        i %= t.w; if (i < 0) i += t.w;
+        j %= t.h; if (j < 0) j += t.h;
+    }
+    else if (t.address == 3) {                                                  // Border
+        if (i < 0 || i >= t.w || j < 0 || j >= t.h) { AtnVec4 z; z.x = z.y = z.z = z.w = 0.0f; return z; }
+    }
+    else {                                                                      // Clamp, Mirror: to the edge
+        i = i < 0 ? 0 : (i >= t.w ? t.w - 1 : i);
+        j = j < 0 ? 0 : (j >= t.h ? t.h - 1 : j);
+    }
+    return ld4(&t.texels[(uint32_t)(j * t.w + i)]);
+}
+ATN_HD_CALL AtnVec4 tex_fetch_device(const TexView& t, float u, float v)
+{
+    const float x = tex_coord(u, t.address) * (float)t.w;
+    const float y = tex_coord(v, t.address) * (float)t.h;
+    if (t.filter != 1) return tex_texel(t, (int32_t)floorf(x), (int32_t)floorf(y));          // Point
+    const float xb = x - 0.5f, yb = y - 0.5f;
+    const float fi = floorf(xb), fj = floorf(yb);
+    const float a = floorf((xb - fi) * 256.0f + 0.5f) * (1.0f / 256.0f);        // 1.8 fixed point
+    const float b = floorf((yb - fj) * 256.0f + 0.5f) * (1.0f / 256.0f);
+    const int32_t i = (int32_t)fi, j = (int32_t)fj;
+    const AtnVec4 t00 = tex_texel(t, i, j), t10 = tex_texel(t, i + 1, j), t01 = tex_texel(t, i, j + 1), t11 = tex_texel(t, i + 1, j + 1);
+    AtnVec4 r;
+    r.x = (1 - a) * (1 - b) * t00.x + a * (1 - b) * t10.x + (1 - a) * b * t01.x + a * b * t11.x;
+    r.y = (1 - a) * (1 - b) * t00.y + a * (1 - b) * t10.y + (1 - a) * b * t01.y + a * b * t11.y;
+    r.z = (1 - a) * (1 - b) * t00.z + a * (1 - b) * t10.z + (1 - a) * b * t01.z + a * b * t11.z;
+    r.w = (1 - a) * (1 - b) * t00.w + a * (1 - b) * t10.w + (1 - a) * b * t01.w + a * b * t11.w;
+    return r;
+}
+
 ATN_HD_CALL AtnVec4 sample_texture(const SceneView& sc, int32_t texid, float u, float v, const AtnVec4& def)
 {
     if (texid < 0) return def;
     const TexView t = sc.textures[texid];
     if (!t.texels) return def;
+    if (sc.device_texture_fetch) return tex_fetch_device(t, u, v);
     const int32_t iu = (int32_t)(u * (t.w - 1));
     const int32_t iv = (int32_t)(v * (t.h - 1));
     const int32_t x = wrap_repeat(iu, t.w - 1);

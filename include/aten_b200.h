@@ -159,13 +159,15 @@ typedef struct AtnSceneConfig {
     float scene_bbox_max[3];
 } AtnSceneConfig;
 
-/* aten::texture: float4 texels, row major (src/libaten/image/texture.h).  The path point-samples
- * with the host rule int(u*(w-1)) + repeat wrap (texture.cpp:64-75), as the CPU oracle does. */
+/* aten::texture: float4 texels, row major (src/libaten/image/texture.h).  By default the path point-samples with the
+ * host rule int(u*(w-1)) + repeat wrap (aten::texture::at, texture.cpp:64-75), as the CPU oracle does; with
+ * atn_set_texture_fetch(1) every texture is fetched the way the reference's GPU renderer fetches it, with its own
+ * filter and address mode. */
 typedef struct AtnTextureDesc {
     const AtnVec4* texels;
     int32_t width, height;
-    int32_t filter_mode;   /* aten::TextureFilterMode, recorded; see DESIGN.md (Q12) */
-    int32_t address_mode;  /* aten::TextureAddressMode */
+    int32_t filter_mode;   /* aten::TextureFilterMode: 0 Point, 1 Linear */
+    int32_t address_mode;  /* aten::TextureAddressMode: 0 Wrap, 1 Clamp, 2 Mirror, 3 Border */
 } AtnTextureDesc;
 
 /* Everything Renderer::UpdateSceneData reads from aten::context
@@ -260,6 +262,14 @@ ATN_API int atn_update_texture(AtnRenderer* r, uint32_t index, const AtnTextureD
 ATN_API int atn_update_lights(AtnRenderer* r, const AtnLightParameter* l, uint32_t count);
 /* Renderer::UpdateSceneRenderingConfig (renderer.h:103-106) */
 ATN_API int atn_update_config(AtnRenderer* r, const AtnSceneConfig* cfg);
+/* Which texel a texture lookup returns.  0 (default): the reference's HOST rule, aten::texture::at -- point
+ * sample at int(u * (w - 1)) with repeat wrap (src/libaten/image/texture.cpp:64-75) -- which is what the CPU oracle
+ * computes and every parity test runs.  1: the reference's DEVICE rule, tex2DLod on a texture object with normalised
+ * coordinates and the texture's own filter (point / bilinear) and address mode (wrap / clamp / mirror / border)
+ * (src/libaten/material/sample_texture.h:18-35, src/libidaten/cuda/cudaTextureResource.cpp:210-236), computed in software
+ * after the CUDA programming guide's texture-fetch formulas.  The device rule has no runnable reference on this box:
+ * parity unpinned (pinned to an independent restatement of the formulas only). */
+ATN_API int atn_set_texture_fetch(AtnRenderer* r, int device_semantics);
 /* SceneRenderingConfig::enable_alpha_blending (scene_rendering_config.h:21), also set by the scene blob at upload.  With it
  * on (or for shadow rays that leave a surface of stencil type ALWAYS) a shadow ray whose closest hit is translucent by
  * alpha (or a STENCIL surface) restarts behind that hit, up to 10 lookups -- HitTestToTargetLight,

@@ -246,6 +246,11 @@ public:
         Check(atn_set_seeds(h_, rnd.data(), static_cast<uint32_t>(rnd.size())));
     }
 
+    /// No counterpart in the reference.  false (default): textures are read with the reference's HOST rule
+    /// (aten::texture::at), which is what its CPU path tracer -- the parity oracle -- computes.  true: with the rule of the
+    /// renderer this class stands in for, tex2DLod with each texture's filter / address mode (sample_texture.h:18-35).
+    void SetDeviceTextureFetch(bool device_rule) { Ensure(); Check(atn_set_texture_fetch(h_, device_rule ? 1 : 0)); }
+
     /// No counterpart in the reference: the next UpdateSceneData keeps the ENCODED bottom trees in this file and skips
     /// the encoding step when the file matches the scene (atn_upload_scene_cached); "" switches it off.
     void SetEncodedTreeCache(const std::string& path) { encoded_cache_path_ = path; }

@@ -31,6 +31,8 @@ using namespace atn;
 
 namespace {
 
+int32_t g_device_texture_fetch = 0;     // oracle_set_texture_fetch: 1 = the GPU renderer's fetch semantics (atn_math.cuh tex_fetch_device)
+
 struct Scene {
     SceneView view;
     std::vector<const AtnBvhNode*> lists;
@@ -46,6 +48,7 @@ Scene MakeScene(const AtnSceneBlob* b)
     s.view.normals = b->normals; s.view.light_count = (int32_t)b->light_count; s.view.material_count = (int32_t)b->material_count; s.view.cfg = b->config;
     for (uint32_t i = 0; i < b->texture_count; i++) {
         TexView t; t.texels = b->textures[i].texels; t.w = b->textures[i].width; t.h = b->textures[i].height;
+        t.filter = b->textures[i].filter_mode; t.address = b->textures[i].address_mode;
         s.tex.push_back(t);
     }
     s.view.textures = s.tex.data();
@@ -63,6 +66,7 @@ Scene MakeScene(const AtnSceneBlob* b)
     }
     s.view.scene_radius = radius;
     s.view.alpha_blending = b->enable_alpha_blending ? 1 : 0;
+    s.view.device_texture_fetch = g_device_texture_fetch;
     s.t_min = b->config.bvh_hit_min > 0 ? b->config.bvh_hit_min : kEps;
     return s;
 }
@@ -143,6 +147,17 @@ bool Traverse(const Scene& s, const Ray& r, float t_max, AtnHit* isect, Counters
 }  // namespace
 
 extern "C" {
+
+__attribute__((visibility("default")))
+void oracle_set_texture_fetch(int32_t device_semantics) { g_device_texture_fetch = device_semantics ? 1 : 0; }
+
+// tex_fetch_device on one texture for a list of coordinates (tests/test_texture_fetch.py pins it to an independent restatement)
+__attribute__((visibility("default")))
+void oracle_tex_fetch(const AtnVec4* texels, int32_t w, int32_t h, int32_t filter, int32_t address, const float* uv, int32_t n, AtnVec4* out)
+{
+    TexView t; t.texels = texels; t.w = w; t.h = h; t.filter = filter; t.address = address;
+    for (int32_t i = 0; i < n; i++) out[i] = tex_fetch_device(t, uv[2 * i], uv[2 * i + 1]);
+}
 
 __attribute__((visibility("default")))
 int oracle_trace_closest(const AtnSceneBlob* blob, const AtnRay* rays, const float* t_max, size_t n, AtnHit* hits,

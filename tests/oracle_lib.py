@@ -259,3 +259,19 @@ def ref_render_restir(name, W, H, frames=1, depth=5, rr=3, motion=(0.0, 0.0)):
         imgs = [np.fromfile(f"{prefix}.f{k}.f32", np.float32).reshape(H, W, 4) for k in range(frames)]
         res = np.fromfile(f"{prefix}.reservoirs.f32", np.float32).reshape(H * W, 5)
     return imgs, res
+
+
+# ---- texture fetch modes -------------------------------------------------------------
+def set_texture_fetch(device_semantics: bool):
+    """Switch the restatement between the reference's host texel rule (default) and its GPU renderer's fetch semantics."""
+    lib().oracle_set_texture_fetch(C.c_int32(1 if device_semantics else 0))
+
+
+def tex_fetch(texels: np.ndarray, filter_mode: int, address_mode: int, uv: np.ndarray) -> np.ndarray:
+    """tex_fetch_device (aten_b200/csrc/atn_math.cuh) on one float32 [h, w, 4] texture for uv [n, 2]."""
+    t = np.ascontiguousarray(texels, np.float32)
+    uv = np.ascontiguousarray(uv, np.float32)
+    out = np.zeros((len(uv), 4), np.float32)
+    lib().oracle_tex_fetch(C.c_void_p(t.ctypes.data), C.c_int32(t.shape[1]), C.c_int32(t.shape[0]), C.c_int32(filter_mode),
+                           C.c_int32(address_mode), C.c_void_p(uv.ctypes.data), C.c_int32(len(uv)), C.c_void_p(out.ctypes.data))
+    return out

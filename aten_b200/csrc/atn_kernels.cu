@@ -1441,6 +1441,10 @@ __global__ void __launch_bounds__(kShadeBlock, ATN_NEE_MIN_BLOCKS)
 k_nee(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb, ShadeQueues sq, int bounce)
 {
     const int count = *sq.n_lit;
+    // (Regrouping the 128 paths of a block by the light picked and the material, so that a warp runs one light-sampling
+    // routine and one BSDF, was built and measured: bit-identical images, -1.3 % with the NEE stage regrouped and -15 %
+    // with the BSDF stage -- warps of one kind finish at different times and wait for each other at the block's
+    // barriers, and a warp's path-state loads spread over four times as many lines.  Not kept.)
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
         nee_stage(fp, sc, seeds, pb, sq.q_lit[i]);
 }

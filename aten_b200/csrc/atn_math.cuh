@@ -1349,32 +1349,42 @@ ATN_HD bool shade_surface(const SceneView& sc, const Ray& ray, int32_t objid, in
 }
 
 // Stage 2: FillShadowRay / SampleLight (pathtracing_impl.h:178-264) + ComputeRadianceNEE.
+// In two steps, so that the GPU kernel can regroup its paths by the light that was picked before it samples it (k_nee):
+// the pick (one random number) and the rest.  shade_nee() is the two in a row, which is what the CPU restatement runs.
+ATN_HD int32_t shade_nee_pick(const SceneView& sc, uint32_t mtrl_attrib, Sampler* sampler)      // light index, or -1: no NEE
+{
+    const int32_t lightnum = sc.light_count;
+    if (!(lightnum > 0) || (mtrl_attrib & (2u | 4u))) return -1;          // singular or translucent material
+    int32_t target = (int32_t)(sampler->next() * lightnum);
+    return (lightnum - 1 < target) ? (lightnum - 1) : target;
+}
+ATN_HD void shade_nee_light(const SceneView& sc, const V3& ray_dir, const Surface& sf, const Mtrl& mtrl, int32_t target,
+                            PathState* st, ShadowRayOut* sh)
+{
+    const float select_prob = 1.0f / sc.light_count;
+    const AtnLightParameter& light = sc.lights[target];
+    LightSample ls;
+    light_sample(&ls, light, sc, sf.p, sf.n, &st->sampler);
+
+    sh->dir = normalize(ls.dir);
+    sh->dist = length(ls.pos - sf.p);
+    sh->org = ray_offset(sf.p, sf.n);
+    sh->light_id = target;
+    sh->lightcontrib = V3(0.0f);
+    sh->sampled = true;
+    V3 radiance;
+    if (radiance_nee(&radiance, sc, ray_dir, sf.n, mtrl, sf.u, sf.v, select_prob, ls)) {
+        sh->lightcontrib = st->throughput * radiance * sf.albedo;
+        sh->active = true;
+    }
+}
 ATN_HD void shade_nee(const SceneView& sc, const V3& ray_dir, const Surface& sf, PathState* st, ShadowRayOut* sh)
 {
     sh->active = false;
     sh->sampled = false;
     const Mtrl mtrl = fill_material(sc, sf.mtrlid);
-    const int32_t lightnum = sc.light_count;
-    if (lightnum > 0 && !(mtrl.is_singular() || mtrl.is_translucent())) {
-        int32_t target = (int32_t)(st->sampler.next() * lightnum);
-        target = (lightnum - 1 < target) ? (lightnum - 1) : target;
-        const float select_prob = 1.0f / lightnum;
-        const AtnLightParameter& light = sc.lights[target];
-        LightSample ls;
-        light_sample(&ls, light, sc, sf.p, sf.n, &st->sampler);
-
-        sh->dir = normalize(ls.dir);
-        sh->dist = length(ls.pos - sf.p);
-        sh->org = ray_offset(sf.p, sf.n);
-        sh->light_id = target;
-        sh->lightcontrib = V3(0.0f);
-        sh->sampled = true;
-        V3 radiance;
-        if (radiance_nee(&radiance, sc, ray_dir, sf.n, mtrl, sf.u, sf.v, select_prob, ls)) {
-            sh->lightcontrib = st->throughput * radiance * sf.albedo;
-            sh->active = true;
-        }
-    }
+    const int32_t target = shade_nee_pick(sc, mtrl.attrib, &st->sampler);
+    if (target >= 0) shade_nee_light(sc, ray_dir, sf, mtrl, target, st, sh);
 }
 
 // Stage 3: ComputeRussianProbability (:680-698), material::sampleMaterial, PrepareForNextBounce (:700-743).

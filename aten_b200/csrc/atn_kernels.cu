@@ -412,17 +412,42 @@ struct ShadowPolicy {              // wavefront shadow rays (hitShadowRay)
         if (kRetrace && (__float_as_int(pb.sh_c[slot].w) & 255) != 0) *d = normalize(*d);
     }
     __device__ __forceinline__ float t_max(int slot) const { return pb.sh_o[slot].w - kEps; }
+    // Area light: a shadow ray is visible iff its closest hit lies on the light's object (or nothing is hit).  Every point of
+    // that object is inside its world bounds (SceneView::light_bounds), so an accepted hit clearly in front of the ray's
+    // entry into those bounds settles it: the closest hit is that one or a nearer one, never the light.  Returns the
+    // distance in front of which a hit ends the ray, -inf when the rule does not apply.
+    __device__ __forceinline__ float area_exit_dist(int32_t light_id, const V3& o, const V3& d) const
+    {
+        if (!sc.light_bounds) return -kInf;
+        const float4 lo = __ldg(reinterpret_cast<const float4*>(sc.light_bounds) + 2 * light_id);
+        if (lo.w == 0.0f) return -kInf;
+        const float4 hi = __ldg(reinterpret_cast<const float4*>(sc.light_bounds) + 2 * light_id + 1);
+        if (!(fabsf(d.x) > 1e-12f && fabsf(d.y) > 1e-12f && fabsf(d.z) > 1e-12f)) return -kInf;
+        const float ax = (lo.x - o.x) / d.x, bx = (hi.x - o.x) / d.x;
+        const float ay = (lo.y - o.y) / d.y, by = (hi.y - o.y) / d.y;
+        const float az = (lo.z - o.z) / d.z, bz = (hi.z - o.z) / d.z;
+        const float t_in = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
+        const float t_out = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+        if (!(t_in > 0.0f && t_in <= t_out)) return -kInf;
+        // well clear of the bounds: 0.1 % of the distance and of the origin's magnitude (the bounds are padded already)
+        return t_in - 1e-3f * (t_in + 1.0f + fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z)));
+    }
     __device__ __forceinline__ void load(int i, int* slot, V3* o, V3* d, float* t_max, int* mode, float* exit_dist) const
     {
         const int s = queue[i];
         world(s, o, d);
         const float dist = pb.sh_o[s].w;
-        const uint32_t attrib = sc.lights[__float_as_int(pb.sh_d[s].w)].attrib;
+        const int32_t light_id = __float_as_int(pb.sh_d[s].w);
+        const uint32_t attrib = sc.lights[light_id].attrib;
         *slot = s;
         *t_max = dist - kEps;                       // HitTestToTargetLight, pathtracing_impl.h:297-304
         // with the retrace loop the CLOSEST hit decides whether the ray goes on: no early exit
         *mode = kRetrace ? EXIT_NONE : ((attrib & 2u) ? EXIT_ANY_HIT : ((attrib & 1u) ? EXIT_HIT_BEFORE : EXIT_NONE));
         *exit_dist = dist;
+        if (!kRetrace && (attrib & 3u) == 0u) {
+            const float e = area_exit_dist(light_id, *o, *d);
+            if (e > 0.0f) { *mode = EXIT_HIT_BEFORE; *exit_dist = e; }
+        }
     }
     template <bool kLate>
     __device__ __forceinline__ void apply(int slot, const AtnHit& h) const
@@ -473,7 +498,17 @@ struct ShadowPolicy {              // wavefront shadow rays (hitShadowRay)
     {
         const AtnHit h = resolved(bv, r);
         // (with the retrace loop every tie goes to the exact walk: which surface is the closest decides how the ray goes on)
-        if (tie.any && (kRetrace || shadow_tie_matters(sc, sc.lights[__float_as_int(pb.sh_d[slot].w)], pb.sh_o[slot].w, h, tie))) return false;
+        if (tie.any) {
+            const int32_t light_id = __float_as_int(pb.sh_d[slot].w);
+            const AtnLightParameter& light = sc.lights[light_id];
+            bool matters = kRetrace || shadow_tie_matters(sc, light, pb.sh_o[slot].w, h, tie);
+            if (matters && !kRetrace && (light.attrib & 3u) == 0u && h.objid >= 0) {
+                // area light, and hit and runner-up both clearly in front of the light's bounds: hidden whichever is closest
+                V3 o, d; world(slot, &o, &d);
+                if (h.t <= area_exit_dist(light_id, o, d) - 2.0f * tie.band) matters = false;
+            }
+            if (matters) return false;
+        }
         finish_hit(slot, h);
         return true;
     }
@@ -1513,7 +1548,7 @@ k_side(RefView rv, ClosestPolicy pol, FrameParams fp, AtnCameraParameter cam, Sc
 __global__ void __launch_bounds__(kShadeBlock)
 k_ao_begin(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuffers pb, Counters* cnt)
 {
-    const int count = fp.rw * fp.rh;
+    const int count = fp.rw * fp.rh * fp.batch;
     const int rounds = (count + blockDim.x * gridDim.x - 1) / (blockDim.x * gridDim.x);
     for (int it = 0; it < rounds; it++) {
         const int slot = (it * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
@@ -1549,9 +1584,8 @@ k_ao_ray(FrameParams fp, const uint32_t* __restrict__ seeds, PathBuffers pb, Cou
     const int count = cnt->n_lit[0];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
         const int slot = pb.q_lit[i];
-        const int ix = fp.x0 + slot % fp.rw;
-        const int iy = fp.y0 + slot / fp.rw;
-        Sampler sp = ao_sampler_for_path(fp.frame, seeds[(uint32_t)(iy * fp.width + ix) % fp.seed_count]);
+        const SlotInfo si = slot_info(fp, slot);       // sample k of a batch is frame + k, as in the path tracer
+        Sampler sp = ao_sampler_for_path(si.frame, seeds[(uint32_t)si.pix % fp.seed_count]);
         sp.dim = pb.sampler_dim[slot];
         const float4 s0 = pb.surf0[slot];
         const float4 s1 = pb.surf1[slot];
@@ -1992,6 +2026,9 @@ struct AtnRenderer {
     DevBuf<AtnMat4> matrices;
     DevBuf<AtnMaterialParameter> materials;
     DevBuf<AtnLightParameter> lights;
+    DevBuf<float4> light_bounds;                 // SceneView::light_bounds (area lights: bounds of the light's object)
+    std::vector<int32_t> h_light_obj;            // per light: the area light's object id, -1 otherwise
+    std::vector<InstLeafW> h_insts;              // the top layer's leaves (object id + conservative world bounds)
     DevBuf<AtnTriangleParameter> triangles;
     DevBuf<AtnVec4> positions, normals;
     DevBuf<AtnVec4> texels;
@@ -2050,6 +2087,7 @@ struct AtnRenderer {
     Pending pending{ PEND_NONE };
     size_t pend_events{ 0 };       // profiling events recorded by the pending call
     uint64_t pend_ao_factor{ 0 };  // AO: rays per lit path of the call (num_rays * spp)
+    uint64_t pend_ao_batch{ 1 };   // AO: samples in the call's last wavefront (n_lit[0] counts their lit paths)
     cudaEvent_t ev_done{ nullptr };
     PathBuffers pb{};
 
@@ -2119,11 +2157,48 @@ static void launch_trace(AtnRenderer* r, cudaStream_t s, Policy pol, const int32
 
 // (Re)binds what depends on the node array and the top layer: the linear node texture of the default kernel form, the
 // instance leaves, the root and the stack bound.
+// SceneView::light_bounds from the host copies of the lights' object ids and the top layer's leaves; called whenever either
+// changes (upload, atn_update_top_layer, atn_update_lights).
+static int refresh_light_bounds(AtnRenderer* r)
+{
+    const size_t n = r->h_light_obj.size();
+    std::vector<float4> lb(2 * n, make_float4(0.0f, 0.0f, 0.0f, 0.0f));
+    for (size_t l = 0; l < n; l++) {
+        const int32_t obj = r->h_light_obj[l];
+        if (obj < 0) continue;
+        float mn[3] = { kInf, kInf, kInf }, mx[3] = { -kInf, -kInf, -kInf };
+        bool found = false, finite = true;
+        for (const InstLeafW& w : r->h_insts) {
+            if (w.objid != obj) continue;
+            found = true;
+            for (int a = 0; a < 3; a++) {
+                mn[a] = std::min(mn[a], w.wmin[a]); mx[a] = std::max(mx[a], w.wmax[a]);
+                finite = finite && std::isfinite(w.wmin[a]) && std::isfinite(w.wmax[a]);
+            }
+        }
+        if (!found || !finite) continue;
+        lb[2 * l] = make_float4(mn[0], mn[1], mn[2], 1.0f);
+        lb[2 * l + 1] = make_float4(mx[0], mx[1], mx[2], 1.0f);
+    }
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
+    CUDA_TRY(r->light_bounds.upload(lb.data(), lb.size(), r->stream));
+    CUDA_TRY(cudaStreamSynchronize(r->stream));
+    r->sv.light_bounds = n ? reinterpret_cast<const AtnVec4*>(r->light_bounds.p) : nullptr;
+    return ATN_OK;
+}
+static void remember_lights(AtnRenderer* r, const AtnLightParameter* l, uint32_t count)
+{
+    r->h_light_obj.assign(count, -1);
+    for (uint32_t i = 0; i < count; i++) r->h_light_obj[i] = atn::shadow_light_obj(l[i]);
+}
+
 static int bind_top_layer(AtnRenderer* r, size_t node_count, const std::vector<InstLeafW>& insts, int32_t top_root, int32_t max_stack)
 {
     if (max_stack > kSmemStack + kLocalStackLarge)
         return set_error(ATN_ERR_TOO_LARGE, "BVH needs a traversal stack of %d entries (limit %d)", max_stack, kSmemStack + kLocalStackLarge);
     r->stack_need = max_stack;
+    r->h_insts = insts;
+    if (int rc = refresh_light_bounds(r)) return rc;
     CUDA_TRY(r->insts.upload(insts.data(), insts.size(), r->stream));
     CUDA_TRY(cudaStreamSynchronize(r->stream));   // the caller's host arrays go out of scope
     r->bv.nodes = reinterpret_cast<const float4*>(r->nodes.p);
@@ -2374,8 +2449,8 @@ static int collect_stats(AtnRenderer* r)
     r->stats.closest_rays = r->h_stats->totals.closest;
     r->stats.shadow_rays = r->h_stats->totals.shadow;
     r->stats.exact_rays = r->h_stats->totals.exact;
-    if (kind == AtnRenderer::PEND_AO)      // AO rays = lit paths (last sample's count) x rays per path x samples
-        r->stats.shadow_rays = (uint64_t)r->h_stats->counters.n_lit[0] * r->pend_ao_factor;
+    if (kind == AtnRenderer::PEND_AO)      // AO rays = lit paths per sample (from the last wavefront) x rays per path x samples
+        r->stats.shadow_rays = (uint64_t)r->h_stats->counters.n_lit[0] * r->pend_ao_factor / r->pend_ao_batch;
     r->stats.trace_ms = 0.0f;
     float tot = 0.0f;
     for (size_t i = 0; i + 3 < r->pend_events; i += 4) {
@@ -2445,6 +2520,7 @@ static int upload_scene_impl(AtnRenderer* r, const AtnSceneBlob* scene, const At
     CUDA_TRY(r->matrices.upload(scene->matrices, scene->matrix_count, s));
     CUDA_TRY(r->materials.upload(scene->materials, scene->material_count, s));
     CUDA_TRY(r->lights.upload(scene->lights, scene->light_count, s));
+    remember_lights(r, scene->lights, scene->light_count);
     CUDA_TRY(r->triangles.upload(scene->triangles, scene->triangle_count, s));
     CUDA_TRY(r->positions.upload(scene->positions, scene->vertex_count, s));
     CUDA_TRY(r->normals.upload(scene->normals, scene->vertex_count, s));
@@ -2638,7 +2714,8 @@ ATN_API int atn_update_lights(AtnRenderer* r, const AtnLightParameter* l, uint32
     CUDA_TRY(r->lights.upload(l, count, r->stream));
     CUDA_TRY(cudaStreamSynchronize(r->stream));
     r->sv.lights = r->lights.p; r->sv.light_count = (int32_t)count;
-    return ATN_OK;
+    remember_lights(r, l, count);
+    return refresh_light_bounds(r);
 }
 
 ATN_API int atn_update_config(AtnRenderer* r, const AtnSceneConfig* cfg)
@@ -2946,11 +3023,17 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
     CUDA_TRY(cudaMemsetAsync(r->totals.p, 0, sizeof(Totals), s));
     CUDA_TRY(cudaMemsetAsync(r->visits.p, 0, sizeof(Visits), s));
     CUDA_TRY(cudaEventRecord(r->ev0, s));
-    for (int smp = 0; smp < spp; smp++) {
+    // samples share a wavefront as in the path tracer (slot_info): the launches of a 2 M-ray sample are short enough for
+    // their tails and the exact walk's latency to show
+    const int batch_max = std::max<int>(1, (int)std::min<size_t>((size_t)r->batch_cap, r->path_capacity / (size_t)n));
+    for (int smp = 0; smp < spp;) {
+        const int batch = std::min(batch_max, spp - smp);
         fp.frame = r->frame + (uint32_t)smp;
+        fp.batch = batch;
+        const int grid_b = std::min((n * batch + 255) / 256, r->sm_count * 8);
         Counters* c = r->counters.p;
         CUDA_TRY(cudaMemsetAsync(c, 0, sizeof(Counters), s));
-        k_generate<<<grid, 256, 0, s>>>(fp, r->camera, r->seeds.p, r->pb, c);
+        k_generate<<<grid_b, 256, 0, s>>>(fp, r->camera, r->seeds.p, r->pb, c);
         {
             ClosestPolicy pol{ r->pb, nullptr, kInf, nullptr, 0 };
             launch_trace<ClosestPolicy>(r, s, pol, &c->n_active[0], 0, &c->fetch_closest[0], r->visits.p, r->pb.q_exact, &c->n_exact_closest[0]);
@@ -2982,8 +3065,10 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
         launches++;
         // n_active[0] primary rays + num_rays * n_lit[0] AO rays: folded into Totals by k_gather through
         // n_active[0] / n_shadow[0]; the AO rays are reported as shadow rays
-        k_gather<<<grid, 256, 0, s>>>(fp, r->pb, r->image.p, r->gather_mode, smp == 0 ? 1 : 0, smp == spp - 1 ? 1 : 0, c, r->totals.p);
+        k_gather<<<grid, 256, 0, s>>>(fp, r->pb, r->image.p, r->gather_mode, smp == 0 ? 1 : 0, smp + batch >= spp ? 1 : 0, c, r->totals.p);
         launches++;
+        smp += batch;
+        r->pend_ao_batch = (uint64_t)batch;
     }
     r->pend_ao_factor = (uint64_t)num_rays * (uint64_t)spp;
     const int rc_end = end_call(r, AtnRenderer::PEND_AO, launches, (uint64_t)n * (uint64_t)spp, 0);

@@ -282,7 +282,10 @@ struct SceneView {
     AtnSceneConfig cfg;
     float scene_radius;      // ComputeDistanceToCoverBoundingSphere(30 deg) or 10000 (ibl.h:105-110)
     int32_t device_texture_fetch;   // 0: aten::texture::at (host rule, parity runs); 1: the GPU renderer's tex2DLod semantics per texture
-    int32_t alpha_blending;  // SceneRenderingConfig::enable_alpha_blending (scene_rendering_config.h:21): shadow rays pass alpha surfaces
+    int32_t alpha_blending;  // SceneRenderingConfig::enable_alpha_blending (scene_rendering_config.h:21): shadow rays pass alpha surfaces    // Two float4 per light: conservative world-space bounds of an area light's object in the top layer (min, max; min.w != 0
+    // when valid).  A shadow ray towards that light that hits anything clearly in front of these bounds is hidden whatever
+    // else it would hit (the closest hit cannot be the light's object).  NULL in the CPU restatement.
+    const AtnVec4* light_bounds;
 };
 
 ATN_HD AtnVec4 ld4(const AtnVec4* p)

@@ -314,6 +314,15 @@ def main():
                         label="C5: incoherent secondary rays into 100 distinct dragon meshes (10 M triangles, ~1.4 GB of nodes + triangles)"
                         if not (a.copies or q) else f"incoherent secondary rays into {a.copies or 9} distinct dragon meshes")), flush=True)
         return
+    if a.only in ("ao", "small"):
+        ao_bench("sponza_atrium", 1920, 1080, 16 if not q else 2, label="N1 ambient occlusion, sponza_lod 1080p 16spp")
+        if a.only == "ao":
+            return
+    if a.only == "small":       # the configs whose wavefronts are one sample of a frame
+        print(json.dumps(render_bench("cornell", 512, 512, 1, steps=5, warmup=3, label="C1 Cornell 512x512 1spp")), flush=True)
+        svgf_bench("sponza_atrium", 1920, 1080, frames=8, label="N1 SVGF, sponza_lod 1080p, 8-frame sequence")
+        restir_bench("sponza_atrium", 1920, 1080, frames=8, label="N1 ReSTIR, sponza_lod 1080p, 8-frame sequence")
+        return
     if a.only == "svgf":
         svgf_bench("sponza_atrium", 1920, 1080, frames=8 if not q else 3, label="N1 SVGF, sponza_lod 1080p, 8-frame sequence")
         return

@@ -129,6 +129,7 @@ struct Counters {
     int32_t n_exact_closest[kMaxBounce];  // rays handed to the exact walk (near ties), per bounce
     int32_t n_exact_shadow[kMaxBounce];
     int32_t n_exact_query;
+    int32_t fetch_shade[kMaxBounce][4]; // work cursors of the shade kernels of bounce b (surface, nee, bsdf)
     // rays that restart behind an ignored hit (alpha / stencil), per bounce and lookup: queue length, work cursor of the pass
     // that traces them, and their share of the exact walk
     struct Retrace { int32_t n[10], fetch[10], n_exact[10]; } retrace[kMaxBounce];
@@ -1297,7 +1298,33 @@ struct ShadeQueues {
     const int32_t* q_in;  const int32_t* n_in;     // paths of the surface stage (q_in == nullptr: path i = slot i)
     int32_t* q_lit;       int32_t* n_lit;          // survivors of the surface stage = the paths of the NEE / BSDF stages
     int32_t skip_tag;                              // main pass next to a side pass: paths with pend == skip_tag are the side pass's
+    int32_t* work;                                 // three zeroed work cursors: surface, NEE, BSDF stage (shade_chunk)
 };
+
+// Work distribution of the shade kernels: every warp takes 32 consecutive queue entries at a time from a cursor until
+// the queue is empty.  A fixed share per block (the grid-stride loop these kernels had) makes a kernel as slow as its
+// slowest block, and next to the side pass some blocks start late: k_side's blocks take register space that a full
+// grid of these kernels needs, the blocks left without a slot started only when others had finished, and a side pass
+// of 0.23 ms cost 0.15 ms per bounce of a 2 M-path wavefront (7 % of an SVGF or ReSTIR frame, 4 % of the bench frame).
+// Measured on the bench frame (33 M-entry queues, one atomic per fetch on a single address): 32 / 64 / 128 / 256 / 384
+// entries per fetch 1 963 / 1 961 / 1 953 / 1 934 / 1 922 Mrays/s -- the finer the better; sixteen cursors over sixteen
+// segments of the queue instead of one: no gain.  A queue with no more than 32 entries per warp of the grid needs no
+// cursor: warp w takes entries 32 w .. (a Cornell-box frame).  `*base` starts at -1.
+__device__ __forceinline__ bool shade_chunk(int32_t* cursor, int count, int* base)
+{
+    int b;
+    if (gridDim.x * blockDim.x >= count) {
+        if (*base >= 0) return false;
+        b = (blockIdx.x * blockDim.x + threadIdx.x) & ~31;
+    }
+    else {
+        b = 0;
+        if ((threadIdx.x & 31) == 0) b = atomicAdd(cursor, 32);
+        b = __shfl_sync(0xffffffffu, b, 0);
+    }
+    *base = b;
+    return b < count;
+}
 
 __device__ __forceinline__ Sampler path_sampler(const FrameParams& fp, const uint32_t* seeds, const PathBuffers& pb, int slot)
 {
@@ -1454,9 +1481,9 @@ k_surface(FrameParams fp, AtnCameraParameter cam, SceneView sc, PathBuffers pb, 
 {
     const int count = *sq.n_in;
     const int32_t* __restrict__ q_in = sq.q_in;
-    const int rounds = (count + blockDim.x * gridDim.x - 1) / (blockDim.x * gridDim.x);
-    for (int it = 0; it < rounds; it++) {
-        const int i = (it * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+    int base = -1;
+    while (shade_chunk(sq.work + 0, count, &base)) {
+        const int i = base + (threadIdx.x & 31);
         bool lit = false;
         int slot = 0;
         if (i < count) {
@@ -1480,8 +1507,11 @@ k_nee(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuff
     // routine and one BSDF, was built and measured: bit-identical images, -1.3 % with the NEE stage regrouped and -15 %
     // with the BSDF stage -- warps of one kind finish at different times and wait for each other at the block's
     // barriers, and a warp's path-state loads spread over four times as many lines.  Not kept.)
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
-        nee_stage(fp, sc, seeds, pb, sq.q_lit[i]);
+    int base = -1;
+    while (shade_chunk(sq.work + 1, count, &base)) {
+        const int i = base + (threadIdx.x & 31);
+        if (i < count) nee_stage(fp, sc, seeds, pb, sq.q_lit[i]);
+    }
 }
 
 // Stage 3, lit paths: Russian roulette, BSDF sampling, next ray; queues the next bounce and the
@@ -1493,9 +1523,9 @@ k_bsdf(FrameParams fp, SceneView sc, const uint32_t* __restrict__ seeds, PathBuf
 {
     const int count = *sq.n_lit;
     int32_t* __restrict__ q_out = pb.queue[(bounce + 1) & 1];
-    const int rounds = (count + blockDim.x * gridDim.x - 1) / (blockDim.x * gridDim.x);
-    for (int it = 0; it < rounds; it++) {
-        const int i = (it * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+    int base = -1;
+    while (shade_chunk(sq.work + 2, count, &base)) {
+        const int i = base + (threadIdx.x & 31);
         bool cont = false, shadow = false;
         int slot = 0;
         if (i < count) {
@@ -2026,6 +2056,7 @@ struct AtnRenderer {
     DevBuf<AtnMat4> matrices;
     DevBuf<AtnMaterialParameter> materials;
     DevBuf<AtnLightParameter> lights;
+    int exp_bits{ 0 };
     DevBuf<float4> light_bounds;                 // SceneView::light_bounds (area lights: bounds of the light's object)
     std::vector<int32_t> h_light_obj;            // per light: the area light's object id, -1 otherwise
     std::vector<InstLeafW> h_insts;              // the top layer's leaves (object id + conservative world bounds)
@@ -2412,6 +2443,7 @@ static int init_renderer(AtnRenderer* r)
     r->bsdf_grid = r->sm_count * std::max(1, bps);
     r->exact_grid = r->sm_count * 4;
     if (const char* ov = getenv("ATEN_B200_EXACT_TIES")) r->exact_ties = (ov[0] != '0');     // experiments: cost of the exact walk
+    if (const char* ov = getenv("ATEN_B200_EXP")) r->exp_bits = atoi(ov);                     // experiments: 1 serial exact walk, 2 no k_side, 4 no shadow k_exact
     return ATN_OK;
 }
 
@@ -2827,7 +2859,7 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
     cudaStream_t s = r->stream, side = r->side_stream;
     AtnMat4 w2c;
     for (int i = 0; i < 16; i++) w2c.m[i] = svgf_w2c ? svgf_w2c->m[i] : 0.0f;
-    const bool overlap = r->exact_ties && !tap_now && !r->shadow_retrace;
+    const bool overlap = r->exact_ties && !tap_now && !r->shadow_retrace && !(r->exp_bits & 1);
     const int side_grid = r->sm_count * 4;
     size_t se = 0;
     cudaEvent_t shadow_done = nullptr;            // side stream: the exact walk of the previous bounce's shadow rays
@@ -2835,7 +2867,7 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
         Counters* c = r->counters.p;
         const int32_t* q = (b == 0 && fp.tile == 0) ? nullptr : pb.queue[b & 1];
         const float tmax = (b == 0) ? kInf : r->hit_distance_limit;
-        const ShadeQueues mainq{ q, &c->n_active[b], pb.q_lit, &c->n_lit[b], overlap ? b + 1 : 0 };
+        const ShadeQueues mainq{ q, &c->n_active[b], pb.q_lit, &c->n_lit[b], overlap ? b + 1 : 0, c->fetch_shade[b] };
         if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
         ClosestPolicy cpol{ pb, q, tmax, b == 0 ? pb.hit_mesh : nullptr, (uint8_t)(overlap ? b + 1 : 0) };
         launch_trace<ClosestPolicy>(r, s, cpol, &c->n_active[b], 0, &c->fetch_closest[b], r->visits.p, pb.q_exact, &c->n_exact_closest[b], !overlap);
@@ -2846,7 +2878,8 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
             if (!traced || !side_done) return set_error(ATN_ERR_CUDA, "cudaEventCreate failed");
             CUDA_TRY(cudaEventRecord(traced, s));
             CUDA_TRY(cudaStreamWaitEvent(side, traced, 0));
-            if (svgf_w2c) k_side<true><<<side_grid, 128, 0, side>>>(r->rv, cpol, fp, r->camera, r->sv, r->seeds.p, pb, c, b, w2c);
+            if (r->exp_bits & 2) {}
+            else if (svgf_w2c) k_side<true><<<side_grid, 128, 0, side>>>(r->rv, cpol, fp, r->camera, r->sv, r->seeds.p, pb, c, b, w2c);
             else k_side<false><<<side_grid, 128, 0, side>>>(r->rv, cpol, fp, r->camera, r->sv, r->seeds.p, pb, c, b, w2c);
             CUDA_TRY(cudaEventRecord(side_done, side));
             *launches += 1;
@@ -2890,7 +2923,7 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
                 if (!traced || !shadow_done) return set_error(ATN_ERR_CUDA, "cudaEventCreate failed");
                 CUDA_TRY(cudaEventRecord(traced, s));
                 CUDA_TRY(cudaStreamWaitEvent(side, traced, 0));
-                launch_exact<ShadowPolicy<false>>(r, side, pol, pb.q_exact_s, &c->n_exact_shadow[b]);
+                if (!(r->exp_bits & 4)) launch_exact<ShadowPolicy<false>>(r, side, pol, pb.q_exact_s, &c->n_exact_shadow[b]);
                 CUDA_TRY(cudaEventRecord(shadow_done, side));
                 *launches += 1;
             }
@@ -3268,7 +3301,7 @@ ATN_API int atn_render_restir(AtnRenderer* r, int32_t width, int32_t height, int
     }
     k_restir_begin<<<sgrid, kShadeBlock, 0, s>>>(fp, r->camera, r->sv, pb, rv, c, w2c);
     k_restir_candidate<<<sgrid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, rv, c);
-    k_bsdf<false><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, ShadeQueues{ nullptr, &c->n_active[0], pb.q_lit, &c->n_lit[0], 0 }, 0, nullptr, 0);
+    k_bsdf<false><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, ShadeQueues{ nullptr, &c->n_active[0], pb.q_lit, &c->n_lit[0], 0, c->fetch_shade[0] }, 0, nullptr, 0);
     k_restir_visibility<<<sgrid, kShadeBlock, 0, s>>>(fp, pb, rv, c);
     {
         RestirShadowPolicy pol{ ShadowPolicy<false>{ pb, r->sv, nullptr, 0, 0, pb.q_shadow, nullptr, nullptr }, rv.cur };

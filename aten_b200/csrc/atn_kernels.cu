@@ -1283,7 +1283,10 @@ __global__ void k_generate(FrameParams fp, AtnCameraParameter cam, const uint32_
 #ifndef ATN_BSDF_MIN_BLOCKS
 #define ATN_BSDF_MIN_BLOCKS 8
 #endif
-constexpr int kShadeBlock = 128;
+#ifndef ATN_SHADE_BLOCK
+#define ATN_SHADE_BLOCK 128
+#endif
+constexpr int kShadeBlock = ATN_SHADE_BLOCK;
 #ifndef ATN_WAVEFRONT_PATHS
 #define ATN_WAVEFRONT_PATHS (32 * 1024 * 1024)    // paths per wavefront the sample batching aims at (8 M: -1.1 % on the bench frame)
 #endif

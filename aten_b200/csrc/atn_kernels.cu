@@ -2445,6 +2445,9 @@ static int init_renderer(AtnRenderer* r)
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_bsdf<false>, kShadeBlock, 0));
     r->bsdf_grid = r->sm_count * std::max(1, bps);
     r->exact_grid = r->sm_count * 4;
+    // experiments (two renderers side by side on one GPU): blocks per SM of the traversal and of the shade kernels
+    if (const char* ov = getenv("ATEN_B200_TRACE_BPS")) r->trace_grid = r->sm_count * std::max(1, atoi(ov));
+    if (const char* ov = getenv("ATEN_B200_SHADE_BPS")) r->surface_grid = r->nee_grid = r->bsdf_grid = r->sm_count * std::max(1, atoi(ov));
     if (const char* ov = getenv("ATEN_B200_EXACT_TIES")) r->exact_ties = (ov[0] != '0');     // experiments: cost of the exact walk
     if (const char* ov = getenv("ATEN_B200_EXP")) r->exp_bits = atoi(ov);                     // experiments: 1 serial exact walk, 2 no k_side, 4 no shadow k_exact
     return ATN_OK;

@@ -2449,7 +2449,7 @@ static int init_renderer(AtnRenderer* r)
     if (const char* ov = getenv("ATEN_B200_TRACE_BPS")) r->trace_grid = r->sm_count * std::max(1, atoi(ov));
     if (const char* ov = getenv("ATEN_B200_SHADE_BPS")) r->surface_grid = r->nee_grid = r->bsdf_grid = r->sm_count * std::max(1, atoi(ov));
     if (const char* ov = getenv("ATEN_B200_EXACT_TIES")) r->exact_ties = (ov[0] != '0');     // experiments: cost of the exact walk
-    if (const char* ov = getenv("ATEN_B200_EXP")) r->exp_bits = atoi(ov);                     // experiments: 1 serial exact walk, 2 no k_side, 4 no shadow k_exact
+    if (const char* ov = getenv("ATEN_B200_EXP")) r->exp_bits = atoi(ov);                     // experiments: 1 = the exact walk in line on the main stream (no side stream)
     return ATN_OK;
 }
 
@@ -2884,8 +2884,7 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
             if (!traced || !side_done) return set_error(ATN_ERR_CUDA, "cudaEventCreate failed");
             CUDA_TRY(cudaEventRecord(traced, s));
             CUDA_TRY(cudaStreamWaitEvent(side, traced, 0));
-            if (r->exp_bits & 2) {}
-            else if (svgf_w2c) k_side<true><<<side_grid, 128, 0, side>>>(r->rv, cpol, fp, r->camera, r->sv, r->seeds.p, pb, c, b, w2c);
+            if (svgf_w2c) k_side<true><<<side_grid, 128, 0, side>>>(r->rv, cpol, fp, r->camera, r->sv, r->seeds.p, pb, c, b, w2c);
             else k_side<false><<<side_grid, 128, 0, side>>>(r->rv, cpol, fp, r->camera, r->sv, r->seeds.p, pb, c, b, w2c);
             CUDA_TRY(cudaEventRecord(side_done, side));
             *launches += 1;
@@ -2929,7 +2928,7 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
                 if (!traced || !shadow_done) return set_error(ATN_ERR_CUDA, "cudaEventCreate failed");
                 CUDA_TRY(cudaEventRecord(traced, s));
                 CUDA_TRY(cudaStreamWaitEvent(side, traced, 0));
-                if (!(r->exp_bits & 4)) launch_exact<ShadowPolicy<false>>(r, side, pol, pb.q_exact_s, &c->n_exact_shadow[b]);
+                launch_exact<ShadowPolicy<false>>(r, side, pol, pb.q_exact_s, &c->n_exact_shadow[b]);
                 CUDA_TRY(cudaEventRecord(shadow_done, side));
                 *launches += 1;
             }

@@ -384,6 +384,16 @@ def test_top_layer_update_moving_instance(golden):
         fresh = PathTracing(0)
         fresh.UpdateSceneData(moved)
         assert fresh.trace_closest(rays).tobytes() == after.tobytes()
+        # the moved instance IS the area light: shadow rays towards it end early in front of the light object's bounds
+        # (SceneView::light_bounds), which the update has to move with it -- images bit-identical to a fresh upload and
+        # within the shading tolerance of the restatement
+        r.reset(); r.render(64, 64, 4, 5, 3)
+        fresh.reset(); fresh.render(64, 64, 4, 5, 3)
+        img = r.readback()
+        assert img.tobytes() == fresh.readback().tobytes()
+        want_img, _, _ = ol.render(moved, frames=4)
+        a = img[..., :3].reshape(-1, 3); b = want_img[..., :3].reshape(-1, 3)
+        assert np.sqrt(np.mean((a - b) ** 2)) <= 2e-3 * np.sqrt(np.mean(b ** 2))
         fresh.close()
     finally:
         r.close()

@@ -1180,6 +1180,9 @@ k_exact(RefView rv, Policy pol, const int32_t* __restrict__ exact_q, const int32
 // ---------------------------------------------------------------------------------------------
 // generate / shade / gather
 // ---------------------------------------------------------------------------------------------
+#ifndef ATN_PIXEL_BLOCKS
+#define ATN_PIXEL_BLOCKS 1
+#endif
 struct FrameParams {
     int32_t width, height;          // full image
     int32_t x0, y0, rw, rh;         // region rendered by this call; slot s <-> (x0 + s % rw, y0 + s / rw)
@@ -1191,6 +1194,10 @@ struct FrameParams {
     // rh - 1, scanline order over a grid of tiles_x tiles per row); rw = tile * tile slots per tile, rh = number of tiles.
     // Slots of an edge tile that fall outside the frame are never queued.
     int32_t tile, tiles_x, tile_world, tile_rank;
+    // region mode: consecutive slots walk 8 x 4 pixel blocks instead of scanlines (a warp's 32 primary rays and first hits
+    // are neighbours in both directions).  Only where nothing indexes path state by pixel: not with the bounce tap, not
+    // in the AO / SVGF / ReSTIR renderers.
+    int32_t swizzle;
 };
 
 // Where a path slot sits: pixel of the region, sample of the batch.  Samples are independent in the reference (one
@@ -1209,6 +1216,13 @@ __device__ __forceinline__ SlotInfo slot_info(const FrameParams& fp, int slot)
         si.ix = (g % fp.tiles_x) * fp.tile + q % fp.tile;
         si.iy = (g / fp.tiles_x) * fp.tile + q / fp.tile;
         si.valid = si.ix < fp.width && si.iy < fp.height;
+    }
+    else if (fp.swizzle) {
+        const int blk = p >> 5, in = p & 31, per_row = fp.rw >> 3;
+        const int by = blk / per_row, bx = blk - by * per_row;
+        si.ix = fp.x0 + bx * 8 + (in & 7);
+        si.iy = fp.y0 + by * 4 + (in >> 3);
+        si.valid = true;
     }
     else {
         si.ix = fp.x0 + p % fp.rw;
@@ -2960,7 +2974,7 @@ static int render_impl(AtnRenderer* r, int32_t width, int32_t height, int32_t x0
     FrameParams fp;
     fp.width = width; fp.height = height; fp.x0 = x0; fp.y0 = y0; fp.rw = x1 - x0; fp.rh = y1 - y0;
     fp.max_bounce = max_bounce; fp.rr_bounce = rr_bounce; fp.seed_count = r->seed_count;
-    fp.tile = 0; fp.tiles_x = 0; fp.tile_world = 1; fp.tile_rank = 0;
+    fp.tile = 0; fp.tiles_x = 0; fp.tile_world = 1; fp.tile_rank = 0; fp.swizzle = 0;
     if (tile > 0) {
         const int tiles_x = (width + tile - 1) / tile, tiles_y = (height + tile - 1) / tile;
         const int total = tiles_x * tiles_y;
@@ -2981,6 +2995,9 @@ static int render_impl(AtnRenderer* r, int32_t width, int32_t height, int32_t x0
         }
     }
     const bool tap = r->tap_host != nullptr;
+#if ATN_PIXEL_BLOCKS
+    fp.swizzle = (!tap && tile == 0 && fp.rw % 8 == 0 && fp.rh % 4 == 0) ? 1 : 0;      // the tap's records are indexed by pixel
+#endif
     if (tap) {
         CUDA_TRY(r->tap_dev.resize((size_t)n * r->tap_cap));
         if (r->tap_cap < max_bounce) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render: tap capacity %d < max_bounce %d", r->tap_cap, max_bounce);
@@ -3052,7 +3069,7 @@ ATN_API int atn_render_ao(AtnRenderer* r, int32_t width, int32_t height, int32_t
     CUDA_TRY(cudaSetDevice(r->device));
     cudaStream_t s = r->stream;
     FrameParams fp;
-    fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height; fp.tile = 0; fp.tiles_x = 0; fp.tile_world = 1; fp.tile_rank = 0;
+    fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height; fp.tile = 0; fp.tiles_x = 0; fp.tile_world = 1; fp.tile_rank = 0; fp.swizzle = 0;
     fp.max_bounce = 1; fp.rr_bounce = 1; fp.seed_count = r->seed_count; fp.batch = 1;
     const int n = width * height;
     const int grid = std::min((n + 255) / 256, r->sm_count * 8);
@@ -3175,7 +3192,7 @@ ATN_API int atn_render_svgf(AtnRenderer* r, int32_t width, int32_t height, int32
     if (r->svgf_has_motion && r->svgf_motion.n < n) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_svgf: motion buffer smaller than the image");
 
     FrameParams fp;
-    fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height; fp.tile = 0; fp.tiles_x = 0; fp.tile_world = 1; fp.tile_rank = 0;
+    fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height; fp.tile = 0; fp.tiles_x = 0; fp.tile_world = 1; fp.tile_rank = 0; fp.swizzle = 0;
     fp.max_bounce = max_bounce; fp.rr_bounce = rr_bounce; fp.seed_count = r->seed_count; fp.batch = 1;
     fp.frame = r->frame;
     const int cur_k = (int)(r->frame & 1u);
@@ -3278,7 +3295,7 @@ ATN_API int atn_render_restir(AtnRenderer* r, int32_t width, int32_t height, int
     if (r->svgf_has_motion && r->svgf_motion.n < n) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render_restir: motion buffer smaller than the image");
 
     FrameParams fp;
-    fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height; fp.tile = 0; fp.tiles_x = 0; fp.tile_world = 1; fp.tile_rank = 0;
+    fp.width = width; fp.height = height; fp.x0 = 0; fp.y0 = 0; fp.rw = width; fp.rh = height; fp.tile = 0; fp.tiles_x = 0; fp.tile_world = 1; fp.tile_rank = 0; fp.swizzle = 0;
     fp.max_bounce = max_bounce; fp.rr_bounce = rr_bounce; fp.seed_count = r->seed_count; fp.batch = 1;
     fp.frame = r->frame;
     const int cur = r->restir_cur, other = (cur + 1) & 1;

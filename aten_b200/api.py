@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(_HERE, "libaten_b200.so")
 EXPORTS = [
     "atn_create", "atn_destroy", "atn_last_error", "atn_version", "atn_upload_scene", "atn_update_camera",
     "atn_update_top_layer", "atn_update_materials", "atn_update_lights", "atn_update_config", "atn_set_seeds",
-    "atn_set_frame", "atn_get_frame", "atn_reset", "atn_set_progressive", "atn_set_gather_mode", "atn_set_exact_ties", "atn_set_hit_distance_limit",
+    "atn_set_frame", "atn_get_frame", "atn_reset", "atn_set_progressive", "atn_set_gather_mode", "atn_set_exact_ties", "atn_set_wavefront_paths", "atn_set_hit_distance_limit",
     "atn_render", "atn_render_region", "atn_render_tiles", "atn_synchronize", "atn_readback", "atn_device_image", "atn_get_stats",
     "atn_set_profiling", "atn_get_stream", "atn_trace_closest", "atn_trace_any", "atn_trace_closest_device",
     "atn_trace_any_device", "atn_set_bounce_tap", "atn_trace_closest_static", "atn_readback_aov", "atn_render_ao",
@@ -247,6 +247,10 @@ class PathTracing:
         """True (default): rays whose two nearest primitives tie within the error of the reference's biased box test are
         decided by the reference's own depth-first walk (bit-identical primitive ids); False: they keep the nearest."""
         _check(self._lib, self._lib.atn_set_exact_ties(self._h, C.c_int(1 if b else 0)))
+
+    def set_wavefront_paths(self, max_paths: int):
+        """Upper bound on the paths of one wavefront (memory: ~265 B per path; default 32 Mi).  Before UpdateSceneData."""
+        _check(self._lib, self._lib.atn_set_wavefront_paths(self._h, C.c_uint64(int(max_paths))))
 
     def setHitDistanceLimit(self, d: float):
         _check(self._lib, self._lib.atn_set_hit_distance_limit(self._h, C.c_float(d)))

@@ -2172,6 +2172,7 @@ struct AtnRenderer {
     int trace_grid{ 148 * 8 }, trace_grid_stream{ 148 * 6 };
     size_t l2_bytes{ 0 };
     int batch_cap{ 1 };                 // camera samples per wavefront (atn_upload_scene sizes the path buffers for it)
+    size_t wavefront_paths{ (size_t)ATN_WAVEFRONT_PATHS };    // atn_set_wavefront_paths
     size_t path_capacity{ 0 };          // path slots allocated
     int stack_need{ 0 };                // worst-case traversal stack depth of the uploaded scene (WideBvh::max_stack)
     int surface_grid{ 148 * 8 }, nee_grid{ 148 * 8 }, bsdf_grid{ 148 * 8 };
@@ -2616,7 +2617,7 @@ static int upload_scene_impl(AtnRenderer* r, const AtnSceneBlob* scene, const At
     const size_t n = (size_t)width * height;
     // path buffers for a wavefront of about 32 M paths (four samples of a 4K frame, all sixteen of a 1080p one): up to
     // kMaxBatch samples are traced together (slot_info); ~250 B per path, 8 GB at the cap
-    r->batch_cap = (int)std::max<size_t>(1, std::min<size_t>((size_t)ATN_MAX_BATCH, ((size_t)ATN_WAVEFRONT_PATHS + n / 2) / n));
+    r->batch_cap = (int)std::max<size_t>(1, std::min<size_t>((size_t)ATN_MAX_BATCH, (r->wavefront_paths + n / 2) / n));
     r->path_capacity = n * (size_t)r->batch_cap;
     rc = alloc_paths(r, r->path_capacity, n);
     if (rc != ATN_OK) return rc;
@@ -2815,6 +2816,13 @@ ATN_API int atn_set_alpha_blending(AtnRenderer* r, int enable)
     update_shadow_retrace(r, nullptr, 0);
     return ATN_OK;
 }
+ATN_API int atn_set_wavefront_paths(AtnRenderer* r, uint64_t max_paths)
+{
+    if (!r || max_paths == 0) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_set_wavefront_paths: NULL handle or zero paths");
+    r->wavefront_paths = (size_t)std::min<uint64_t>(max_paths, (uint64_t)1 << 30);
+    return ATN_OK;
+}
+
 ATN_API int atn_set_exact_ties(AtnRenderer* r, int enable) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->exact_ties = enable ? 1 : 0; return ATN_OK; }
 ATN_API int atn_set_hit_distance_limit(AtnRenderer* r, float d) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->hit_distance_limit = fminf(d, kInf); return ATN_OK; }
 ATN_API int atn_set_profiling(AtnRenderer* r, int enable) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->profiling = enable ? 1 : 0; return ATN_OK; }

@@ -304,6 +304,14 @@ ATN_API int atn_set_gather_mode(AtnRenderer* r, int mode /* AtnGatherMode */);
  * reference's node lists, so that the reported primitive is the reference's.  0: such rays keep the nearest of the tied
  * primitives (a fraction of a percent of the rays of a scene with coincident surfaces; |dt| / t below 1e-4). */
 ATN_API int atn_set_exact_ties(AtnRenderer* r, int enable);
+/* No counterpart in the reference (its device renderer traces one sample of the frame per pass and sizes its path
+ * buffers by the pixel count, renderer.cpp:30-60).  Upper bound on the paths of one wavefront, i.e. on the device memory the
+ * path state takes: about 265 bytes per path.  Default 32 Mi paths (8.8 GB): the camera samples of a frame share wavefronts
+ * up to that size (all 16 samples of a 1080p frame, 4 of a 4K frame).  A smaller bound trades a few percent of throughput
+ * for memory (1080p, 16 spp: 8 Mi paths 2.2 GB -2 %, 4 Mi 1.1 GB -5 %, 2 Mi = one sample per wavefront 0.55 GB -10 %);
+ * images and ray counts do not depend on it.  Takes
+ * effect at the next atn_upload_scene; at least one sample of the frame always fits. */
+ATN_API int atn_set_wavefront_paths(AtnRenderer* r, uint64_t max_paths);
 /* Renderer::setHitDistanceLimit (renderer.h:108-111) */
 ATN_API int atn_set_hit_distance_limit(AtnRenderer* r, float d);
 

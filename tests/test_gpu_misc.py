@@ -121,3 +121,28 @@ def test_tile_set_render_equals_full_frame(golden):
         assert rays == whole["closest_rays"] + whole["shadow_rays"]
         with pytest.raises(AtnError, match="atn_render_tiles"):
             r.render_tiles(W, H, 64, 2, 2, 0, 1, 5, 3)
+
+
+def test_wavefront_size_does_not_change_the_image(golden):
+    """atn_set_wavefront_paths bounds the path-state memory (samples per wavefront); the image and the ray counts are those
+    of the default wavefront, bit for bit, whether 1, 2 or all 5 samples of the frame share a wavefront -- and with the
+    scanline slot order of a frame whose size is not a multiple of the 8 x 4 pixel blocks."""
+    name = "sponza_atrium"
+    for W, H in ((96, 56), (90, 50)):
+        scene = golden.scene(name).with_size(W, H)
+        images, rays = [], []
+        for cap in (None, W * H, 2 * W * H):
+            with PathTracing(0) as r:
+                if cap is not None:
+                    r.set_wavefront_paths(cap)
+                r.UpdateSceneData(scene)
+                r.set_gather_mode(GATHER_SUM)
+                r.render(W, H, 5, 5, 3)
+                images.append(r.readback().copy())
+                st = r.stats()
+                rays.append((st["closest_rays"], st["shadow_rays"], st["camera_samples"]))
+        assert (bits(images[1]) == bits(images[0])).all() and (bits(images[2]) == bits(images[0])).all()
+        assert rays[0] == rays[1] == rays[2] and rays[0][2] == W * H * 5
+    with PathTracing(0) as r:
+        with pytest.raises(AtnError, match="atn_set_wavefront_paths"):
+            r.set_wavefront_paths(0)

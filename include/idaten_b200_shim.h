@@ -256,6 +256,10 @@ public:
     void SetEncodedTreeCache(const std::string& path) { encoded_cache_path_ = path; }
     bool EncodedTreeCacheHit() const { return encoded_cache_hit_; }
 
+    /// No counterpart in the reference: upper bound on the paths of one wavefront, i.e. on the device memory of the path
+    /// state (~265 B per path; default 32 Mi paths).  Before UpdateSceneData (atn_set_wavefront_paths).
+    void SetWavefrontPaths(uint64_t max_paths) { Ensure(); Check(atn_set_wavefront_paths(h_, max_paths)); }
+
     /// sbvh::importTree (src/libaten/accelerator/sbvh.cpp:1345-1436) without an aten::sbvh object: the node list of a
     /// `.sbvh` file, ready to stand as one bottom-layer list of the `nodes` argument of UpdateSceneData.  Voxel material
     /// ids are re-mapped through `scene_ctxt`'s material names, as importTree does with FindMaterialIdxByName.

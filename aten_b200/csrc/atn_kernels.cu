@@ -2214,7 +2214,7 @@ static int refresh_light_bounds(AtnRenderer* r)
     std::vector<float4> lb(2 * n, make_float4(0.0f, 0.0f, 0.0f, 0.0f));
     for (size_t l = 0; l < n; l++) {
         const int32_t obj = r->h_light_obj[l];
-        if (obj < 0) continue;
+        if (obj < 0 || (r->exp_bits & 8)) continue;      // bit 8: no early exit for area-light shadow rays (same images, by construction)
         float mn[3] = { kInf, kInf, kInf }, mx[3] = { -kInf, -kInf, -kInf };
         bool found = false, finite = true;
         for (const InstLeafW& w : r->h_insts) {
@@ -2464,7 +2464,7 @@ static int init_renderer(AtnRenderer* r)
     if (const char* ov = getenv("ATEN_B200_TRACE_BPS")) r->trace_grid = r->sm_count * std::max(1, atoi(ov));
     if (const char* ov = getenv("ATEN_B200_SHADE_BPS")) r->surface_grid = r->nee_grid = r->bsdf_grid = r->sm_count * std::max(1, atoi(ov));
     if (const char* ov = getenv("ATEN_B200_EXACT_TIES")) r->exact_ties = (ov[0] != '0');     // experiments: cost of the exact walk
-    if (const char* ov = getenv("ATEN_B200_EXP")) r->exp_bits = atoi(ov);                     // experiments: 1 = the exact walk in line on the main stream (no side stream)
+    if (const char* ov = getenv("ATEN_B200_EXP")) r->exp_bits = atoi(ov);                     // experiments, none changes a result: 1 = the exact walk in line on the main stream, 8 = no area-light early exit
     return ATN_OK;
 }
 

@@ -146,3 +146,21 @@ def test_wavefront_size_does_not_change_the_image(golden):
     with PathTracing(0) as r:
         with pytest.raises(AtnError, match="atn_set_wavefront_paths"):
             r.set_wavefront_paths(0)
+
+
+def test_area_light_early_exit_and_side_stream_do_not_change_the_image(golden, monkeypatch):
+    """Two things that are allowed to change the schedule only: shadow rays towards an area light end at the first hit
+    clearly in front of the light object's bounds (instead of running the full closest hit), and the exact walk of
+    near-tie rays runs on a side stream next to the shade kernels.  With either switched off (ATEN_B200_EXP, read when
+    the handle is created) the image is the same bit for bit -- scenes with quad, sphere and instanced area lights."""
+    for name in ("cornell", "cornell_mtrl", "cornell_sphere", "sponza_atrium", "instanced"):
+        m = golden.meta[name]
+        images = []
+        for exp in ("0", "8", "1", "9"):
+            monkeypatch.setenv("ATEN_B200_EXP", exp)
+            with PathTracing(0) as r:
+                r.UpdateSceneData(golden.scene(name))
+                r.render(m["w"], m["h"], 3, m["depth"], m["rr"])
+                images.append(r.readback().copy())
+        for img in images[1:]:
+            assert (bits(img) == bits(images[0])).all(), name

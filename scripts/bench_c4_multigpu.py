@@ -81,6 +81,7 @@ def main():
         counts_ok = bool((full[..., 3] == a.spp).all())
         # the same frame on rank 0 alone: the partitioned result differs from it by the order of the float additions only
         r.reset(); r.render_region(W, H, 0, 0, W, H, 0, a.spp, BOUNCE, RR)
+        r.synchronize()            # render calls are asynchronous; the resolve below runs on torch's stream
         one = multigpu.resolve(image).cpu().numpy()
         bad = ~np.isfinite(full[..., :3]).all(axis=2)
         same_bad = bool((bad == ~np.isfinite(one[..., :3]).all(axis=2)).all())

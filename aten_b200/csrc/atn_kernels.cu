@@ -105,6 +105,9 @@ constexpr int kSmemStack = ATN_SMEM_STACK;     // shared-memory stack entries pe
 // encoder's exact worst-case depth (a larger local frame costs ~1 % even when it is never touched)
 constexpr int kLocalStackSmall = 48, kLocalStackLarge = 240;
 constexpr int kTraceBlock = 128;
+#ifndef ATN_HIT_BRANCHES
+#define ATN_HIT_BRANCHES 1
+#endif
 #ifndef ATN_REFILL_THRESHOLD
 #define ATN_REFILL_THRESHOLD 20
 #endif
@@ -931,6 +934,23 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                 const TriHit h = intersect_triangle_edges(org, dir, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), V3(c.x, c.y, c.z));
                 n_tris++;
                 if (h.hit && h.t < kInf && t_min < h.t) {
+#if ATN_HIT_BRANCHES
+                    // Three cases, as branches: only a couple of lanes of a warp are here at a time, so skipped instructions
+                    // are saved issue slots.  (1) The ray's first hit: nothing to compare with.  (2) A hit beyond the cull
+                    // bound of the best one (its box survived, the triangle is farther): it neither wins nor ties.  (3) The
+                    // general case below.
+                    if (best.leaf < 0) {
+                        const Band bd{ s_tie[0 * kTraceBlock + tid], s_tie[1 * kTraceBlock + tid] };
+                        if (mode == EXIT_ANY_HIT || (mode == EXIT_HIT_BEFORE && h.t <= exit_dist - band_at(bd, h.t))) finished = true;
+                        best.t = h.t; best.a = h.a; best.b = h.b; best.leaf = leaf; best.inst = cur_inst;
+                        t_cull = cull_bound(bd, h.t);
+                        s_tie[5 * kTraceBlock + tid] = cur_key;
+                        if (Policy::kNeedClass) s_tie[4 * kTraceBlock + tid] = b.w;        // material of the best hit
+                    }
+                    else if (h.t > t_cull) {}
+                    else
+#endif
+                    {
                     const bool closer = h.t < best.t ||
                         (h.t == best.t && (cur_inst < best.inst || (cur_inst == best.inst && leaf < best.leaf)));
                     // Runner-up bookkeeping (see "near ties"): only a hit within the cull bound of the best one can tie with
@@ -962,6 +982,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                         t_cull = nc;
                         if (!same) s_tie[5 * kTraceBlock + tid] = cur_key;
                         if (Policy::kNeedClass) s_tie[4 * kTraceBlock + tid] = b.w;        // material of the best hit
+                    }
                     }
                 }
                 cur = kRefNull;

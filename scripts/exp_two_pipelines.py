@@ -10,7 +10,7 @@ if len(sys.argv) > 2:
     os.environ["ATEN_B200_TRACE_BPS"] = sys.argv[1]; os.environ["ATEN_B200_SHADE_BPS"] = sys.argv[2]
 import numpy as np
 from aten_b200 import PathTracing, scene_io as sio
-W, H, SPP = 1920, 1080, 16
+W, H, SPP = 1920, 1080, int(os.environ.get("EXP_SPP", "16"))
 scene = sio.load_scene(os.path.join(ROOT, "tests/golden/sponza_atrium.atnscene.gz")).with_size(W, H)
 def mk():
     r = PathTracing(0); r.UpdateSceneData(scene); r.set_gather_mode(2); return r
@@ -28,7 +28,8 @@ def run(rs, spp_each, reps=4):
     return rays / best / 1e6, best * 1e3
 out = {"trace_bps": os.environ.get("ATEN_B200_TRACE_BPS"), "shade_bps": os.environ.get("ATEN_B200_SHADE_BPS")}
 a = mk()
-out["one_renderer_16spp"] = run([a], SPP)
+out["one_renderer_all_samples"] = run([a], SPP)
 b = mk()
-out["two_renderers_8spp_each"] = run([a, b], SPP // 2)
+out["spp_total"] = SPP
+out["two_renderers_half_each"] = run([a, b], SPP // 2)
 print(json.dumps(out), flush=True)

@@ -255,8 +255,10 @@ class PathTracing:
     def setHitDistanceLimit(self, d: float):
         _check(self._lib, self._lib.atn_set_hit_distance_limit(self._h, C.c_float(d)))
 
-    def set_profiling(self, b: bool):
-        _check(self._lib, self._lib.atn_set_profiling(self._h, C.c_int(1 if b else 0)))
+    def set_profiling(self, b):
+        """False / True (= 1): CUDA events around the traversal kernels (stats trace_ms); 2: count node fetches and triangle
+        tests (stats nodes_visited, tris_tested; a slightly slower form of the kernels); 3: both."""
+        _check(self._lib, self._lib.atn_set_profiling(self._h, C.c_int(int(b))))
 
     # -- render ----------------------------------------------------------------------------------
     def render(self, width: int, height: int, maxSamples: int, maxBounce: int, rrBounce: int = 3):

@@ -715,7 +715,9 @@ __device__ __forceinline__ SlabPair slab_pair(const float4 mn_xy, const float4 m
 #ifndef ATN_STREAM_MIN_BLOCKS
 #define ATN_STREAM_MIN_BLOCKS 7
 #endif
-template <class Policy, int kLocalStack, bool kStream>
+// kCount: QuadNodes fetched and triangle tests run are counted (AtnStats.nodes_visited / tris_tested).  Only with
+// atn_set_profiling(2): the two per-lane counters cost two registers of a 64-register kernel, 1.4 % of the bench frame.
+template <class Policy, int kLocalStack, bool kStream, bool kCount = false>
 __global__ void __launch_bounds__(kTraceBlock, kStream ? ATN_STREAM_MIN_BLOCKS : ATN_TRACE_MIN_BLOCKS)
 k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count_imm, int32_t* __restrict__ fetch, Visits* visits,
         int32_t* __restrict__ exact_q, int32_t* __restrict__ exact_count)
@@ -863,7 +865,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                 const float2 inv_zz = make_float2(ri.invdir.z, ri.invdir.z);
                 const SlabPair pa = slab_pair(a0, a1, a2, inv_xy, inv_zz, ri.oxinvdir);
                 const SlabPair pb = slab_pair(b0, b1, b2, inv_xy, inv_zz, ri.oxinvdir);
-                n_nodes++;
+                if (kCount) n_nodes++;
                 // t0 = max(entry, t_min) <= min(exit, running cull bound); empty slots carry an infinite box and never
                 // pass (t_cull is finite: every source clamps it to kInf = FLT_MAX)
                 float k0 = fmaxf(pa.t0a, t_min), k1 = fmaxf(pa.t0b, t_min), k2 = fmaxf(pb.t0a, t_min), k3 = fmaxf(pb.t0b, t_min);
@@ -932,7 +934,7 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
                 const float4 a = c0.lo, b = c0.hi;
                 const float4 c = c1.lo;
                 const TriHit h = intersect_triangle_edges(org, dir, V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), V3(c.x, c.y, c.z));
-                n_tris++;
+                if (kCount) n_tris++;
                 if (h.hit && h.t < kInf && t_min < h.t) {
 #if ATN_HIT_BRANCHES
                     // Three cases, as branches: only a couple of lanes of a warp are here at a time, so skipped instructions
@@ -1066,13 +1068,15 @@ k_trace(BvhView bv, Policy pol, const int32_t* __restrict__ count_ptr, int count
             if (finished) { active = false; done = true; }
         }
     }
-    for (int o = 16; o > 0; o >>= 1) {
-        n_nodes += __shfl_xor_sync(full, n_nodes, o);
-        n_tris += __shfl_xor_sync(full, n_tris, o);
-    }
-    if (lane == 0 && visits) {
-        atomicAdd(&visits->nodes, (unsigned long long)n_nodes);
-        atomicAdd(&visits->tris, (unsigned long long)n_tris);
+    if (kCount) {
+        for (int o = 16; o > 0; o >>= 1) {
+            n_nodes += __shfl_xor_sync(full, n_nodes, o);
+            n_tris += __shfl_xor_sync(full, n_tris, o);
+        }
+        if (lane == 0 && visits) {
+            atomicAdd(&visits->nodes, (unsigned long long)n_nodes);
+            atomicAdd(&visits->tris, (unsigned long long)n_tris);
+        }
     }
 }
 
@@ -2214,14 +2218,18 @@ static void launch_trace(AtnRenderer* r, cudaStream_t s, Policy pol, const int32
 {
     const bool small = r->stack_need <= kSmemStack + kLocalStackSmall;
     if (!r->exact_ties) { exact_q = nullptr; exact_count = nullptr; }
+    const bool count = (r->profiling & 2) && visits;  // atn_set_profiling bit 2
+#define ATN_LAUNCH_TRACE(LOCAL, STREAM, COUNT, GRID) \
+    k_trace<Policy, LOCAL, STREAM, COUNT><<<GRID, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits, exact_q, exact_count)
     if (r->stream_loads) {
-        if (small) k_trace<Policy, kLocalStackSmall, true><<<r->trace_grid_stream, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits, exact_q, exact_count);
-        else k_trace<Policy, kLocalStackLarge, true><<<r->trace_grid_stream, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits, exact_q, exact_count);
+        if (small) { if (count) ATN_LAUNCH_TRACE(kLocalStackSmall, true, true, r->trace_grid_stream); else ATN_LAUNCH_TRACE(kLocalStackSmall, true, false, r->trace_grid_stream); }
+        else { if (count) ATN_LAUNCH_TRACE(kLocalStackLarge, true, true, r->trace_grid_stream); else ATN_LAUNCH_TRACE(kLocalStackLarge, true, false, r->trace_grid_stream); }
     }
     else {
-        if (small) k_trace<Policy, kLocalStackSmall, false><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits, exact_q, exact_count);
-        else k_trace<Policy, kLocalStackLarge, false><<<r->trace_grid, kTraceBlock, 0, s>>>(r->bv, pol, count_ptr, count_imm, fetch, visits, exact_q, exact_count);
+        if (small) { if (count) ATN_LAUNCH_TRACE(kLocalStackSmall, false, true, r->trace_grid); else ATN_LAUNCH_TRACE(kLocalStackSmall, false, false, r->trace_grid); }
+        else { if (count) ATN_LAUNCH_TRACE(kLocalStackLarge, false, true, r->trace_grid); else ATN_LAUNCH_TRACE(kLocalStackLarge, false, false, r->trace_grid); }
     }
+#undef ATN_LAUNCH_TRACE
     if (exact_q && exact_here) launch_exact<Policy>(r, s, pol, exact_q, exact_count);
 }
 
@@ -2846,7 +2854,7 @@ ATN_API int atn_set_wavefront_paths(AtnRenderer* r, uint64_t max_paths)
 
 ATN_API int atn_set_exact_ties(AtnRenderer* r, int enable) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->exact_ties = enable ? 1 : 0; return ATN_OK; }
 ATN_API int atn_set_hit_distance_limit(AtnRenderer* r, float d) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->hit_distance_limit = fminf(d, kInf); return ATN_OK; }
-ATN_API int atn_set_profiling(AtnRenderer* r, int enable) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->profiling = enable ? 1 : 0; return ATN_OK; }
+ATN_API int atn_set_profiling(AtnRenderer* r, int enable) { if (!r) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); r->profiling = enable & 3; return ATN_OK; }
 ATN_API int atn_get_stream(AtnRenderer* r, void** stream) { if (!r || !stream) return set_error(ATN_ERR_INVALID_ARGUMENT, "NULL"); *stream = (void*)r->stream; return ATN_OK; }
 
 ATN_API int atn_reset(AtnRenderer* r)
@@ -2917,10 +2925,10 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
         const int32_t* q = (b == 0 && fp.tile == 0) ? nullptr : pb.queue[b & 1];
         const float tmax = (b == 0) ? kInf : r->hit_distance_limit;
         const ShadeQueues mainq{ q, &c->n_active[b], pb.q_lit, &c->n_lit[b], overlap ? b + 1 : 0, c->fetch_shade[b] };
-        if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
+        if (r->profiling & 1) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
         ClosestPolicy cpol{ pb, q, tmax, b == 0 ? pb.hit_mesh : nullptr, (uint8_t)(overlap ? b + 1 : 0) };
         launch_trace<ClosestPolicy>(r, s, cpol, &c->n_active[b], 0, &c->fetch_closest[b], r->visits.p, pb.q_exact, &c->n_exact_closest[b], !overlap);
-        if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
+        if (r->profiling & 1) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
         cudaEvent_t side_done = nullptr;
         if (overlap) {
             cudaEvent_t traced = side_event(r, se++); side_done = side_event(r, se++);
@@ -2939,7 +2947,7 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
         if (tap_now) k_bsdf<true><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, mainq, b, r->tap_dev.p, r->tap_cap);
         else k_bsdf<false><<<r->bsdf_grid, kShadeBlock, 0, s>>>(fp, r->sv, r->seeds.p, pb, c, mainq, b, nullptr, 0);
         if (side_done) CUDA_TRY(cudaStreamWaitEvent(s, side_done, 0));       // the shadow and next-bounce queues are complete
-        if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
+        if (r->profiling & 1) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
         if (r->shadow_retrace) {
             // HitTestToTargetLight's loop: lookup 0 over the shadow queue, lookups 1 .. 9 over the rays that restarted behind
             // an ignored hit (a handful; an empty pass is a few microseconds).  One stream, exact walk in line.
@@ -2976,7 +2984,7 @@ static int launch_bounces(AtnRenderer* r, const FrameParams& fp, const PathBuffe
                 *launches += 1;
             }
         }
-        if (r->profiling) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
+        if (r->profiling & 1) CUDA_TRY(cudaEventRecord(r->trace_events[(*ev_i)++], s));
         *launches += 5 + (r->exact_ties && !overlap ? 2 : 0);
     }
     if (shadow_done) CUDA_TRY(cudaStreamWaitEvent(s, shadow_done, 0));       // the gather reads every contribution
@@ -3032,7 +3040,7 @@ static int render_impl(AtnRenderer* r, int32_t width, int32_t height, int32_t x0
         if (r->tap_cap < max_bounce) return set_error(ATN_ERR_INVALID_ARGUMENT, "atn_render: tap capacity %d < max_bounce %d", r->tap_cap, max_bounce);
     }
     const int spp = sample_end - sample_begin;
-    const size_t n_ev = r->profiling ? (size_t)spp * max_bounce * 4 : 0;
+    const size_t n_ev = (r->profiling & 1) ? (size_t)spp * max_bounce * 4 : 0;
     while (r->trace_events.size() < n_ev) { cudaEvent_t ev; CUDA_TRY(cudaEventCreate(&ev)); r->trace_events.push_back(ev); }
     size_t ev_i = 0;
     uint64_t launches = 0;
@@ -3237,7 +3245,7 @@ ATN_API int atn_render_svgf(AtnRenderer* r, int32_t width, int32_t height, int32
     const AtnMat4 w2c = camera_w2c(r->camera);
     const float camera_distance = screen_distance(r->camera, height);
 
-    const size_t n_ev = r->profiling ? (size_t)max_bounce * 4 : 0;
+    const size_t n_ev = (r->profiling & 1) ? (size_t)max_bounce * 4 : 0;
     while (r->trace_events.size() < n_ev) { cudaEvent_t ev; CUDA_TRY(cudaEventCreate(&ev)); r->trace_events.push_back(ev); }
     size_t ev_i = 0;
     uint64_t launches = 0;
@@ -3336,7 +3344,7 @@ ATN_API int atn_render_restir(AtnRenderer* r, int32_t width, int32_t height, int
     const AtnMat4 w2c = camera_w2c(r->camera);
     Counters* c = r->counters.p;
 
-    const size_t n_ev = r->profiling ? (size_t)max_bounce * 4 : 0;
+    const size_t n_ev = (r->profiling & 1) ? (size_t)max_bounce * 4 : 0;
     while (r->trace_events.size() < n_ev) { cudaEvent_t ev; CUDA_TRY(cudaEventCreate(&ev)); r->trace_events.push_back(ev); }
     size_t ev_i = 0;
     uint64_t launches = 0;

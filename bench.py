@@ -321,7 +321,7 @@ def main():
     rays = (st["closest_rays"] + st["shadow_rays"]) * args.steps
     samples = st["camera_samples"] * args.steps
     launches = st["kernel_launches"] * args.steps
-    nodes = st["nodes_visited"] * args.steps; tris = st["tris_tested"] * args.steps
+    nodes = tris = 0                      # counted in the profiling pass below (the counting kernels are not the timed ones)
     exact = st["exact_rays"] * args.steps
 
     # ---- timed: end to end through the public API with host buffers ----
@@ -347,6 +347,10 @@ def main():
             tr_ms += ps["trace_ms"]; prof_ms += ps["device_ms"]
             tr_rays += ps["closest_rays"] + ps["shadow_rays"]
             trace_launches += 2 * BOUNCE * (-(-(s_end - s_begin) // 16))     # up to 16 samples of a 1080p frame per wavefront
+        r.set_profiling(2)                # node fetches / triangle tests per step: the counting form of the kernels, untimed
+        render_share()
+        cs = r.stats()
+        nodes = cs["nodes_visited"] * args.steps; tris = cs["tris_tested"] * args.steps
         r.set_profiling(False)
     barrier()
 

@@ -198,8 +198,9 @@ typedef struct AtnStats {
     uint64_t kernel_launches;  /* CUDA kernels launched by the call */
     float    device_ms;        /* CUDA-event time of the call on the handle's stream */
     float    trace_ms;         /* sum of CUDA-event times of the traversal kernels (if profiling on) */
-    uint64_t nodes_visited;    /* 128-byte QuadNodes fetched by the traversal kernels (renders and ray queries) */
-    uint64_t tris_tested;      /* triangle tests run by the traversal kernels (renders and ray queries) */
+    uint64_t nodes_visited;    /* 128-byte QuadNodes fetched by the traversal kernels (renders and ray queries); counted only
+                                  with atn_set_profiling(2), 0 otherwise */
+    uint64_t tris_tested;      /* triangle tests run by the traversal kernels; likewise */
     uint64_t exact_rays;       /* rays whose hit depended on a near tie and was decided by the reference-order walk */
 } AtnStats;
 
@@ -393,7 +394,9 @@ ATN_API int atn_readback_aov(AtnRenderer* r, AtnVec4* normal_depth, AtnVec4* alb
 ATN_API int atn_device_image(AtnRenderer* r, void** device_ptr, size_t* pixel_count);
 /* Counters of the last call on the handle; waits for that call to finish on the GPU first. */
 ATN_API int atn_get_stats(AtnRenderer* r, AtnStats* out);
-/* 1: time the traversal kernels separately with CUDA events (fills AtnStats.trace_ms). */
+/* Bit mask, default 0.  1: time the traversal kernels separately with CUDA events (fills AtnStats.trace_ms).  2: count
+ * their node fetches and triangle tests (AtnStats.nodes_visited / tris_tested; the counting form of the kernels keeps two
+ * more registers per lane alive and is 1.4 % slower, so it is not the default). */
 ATN_API int atn_set_profiling(AtnRenderer* r, int enable);
 /* CUDA stream of the handle (Renderer::GetCudaStream, renderer.h:113-116) as an opaque pointer. */
 ATN_API int atn_get_stream(AtnRenderer* r, void** stream);

@@ -32,7 +32,11 @@ def render_bench(name, W, H, spp, steps=3, warmup=2, label=""):
         r.reset(); r.render(W, H, spp, 5, 3)
         st = r.stats()
         ms += st["device_ms"]; rays += st["closest_rays"] + st["shadow_rays"]; samples += st["camera_samples"]
-        nodes += st["nodes_visited"]; tris += st["tris_tested"]
+    r.set_profiling(2)             # node / triangle counts come from the counting form of the kernels, outside the timing
+    r.reset(); r.render(W, H, spp, 5, 3)
+    st = r.stats(); nodes = st["nodes_visited"] * steps; tris = st["tris_tested"] * steps
+    r.set_profiling(False)
+    r.reset(); r.render(W, H, spp, 5, 3)
     img = r.readback()
     r.close()
     out = {"config": label, "scene": name, "w": W, "h": H, "spp": spp, "bounces": 5, "triangles": int(len(scene.triangles)),
@@ -237,6 +241,15 @@ def ray_stress_flat(name, n_rays, label="", parity_rays=200_000, copies=None, re
             st = r.stats()
             if it > 0 and (best is None or st["device_ms"] < best["device_ms"]):
                 best = st
+        # node / triangle counts: one more pass with the counting form of the kernel (atn_set_profiling), not timed
+        r.set_profiling(2)
+        if kind == "closest":
+            r.trace_closest_device(rays.data_ptr(), None, n_rays, hits.data_ptr())
+        else:
+            r.trace_any_device(rays.data_ptr(), dist.data_ptr(), n_rays, vis.data_ptr())
+        cst = r.stats()
+        r.set_profiling(False)
+        best = dict(best); best["nodes_visited"] = cst["nodes_visited"]; best["tris_tested"] = cst["tris_tested"]
         res[kind] = best
     peaks = {}
     try:
